@@ -1,0 +1,224 @@
+// Runtime part of the C ABI: contexts, device memory, the host-mirror registry, shape arithmetic.
+#include <math.h>
+
+#include "common.cuh"
+
+static thread_local char g_err[1024] = "";
+
+void dl4j_set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+void *dl4j_workspace(dl4jb200_ctx *ctx, int slot, size_t bytes) {
+    if (bytes <= ctx->ws_bytes[slot] && ctx->ws[slot]) return ctx->ws[slot];
+    // grow: the old region may still be in use by enqueued kernels -> drain the stream first
+    size_t want = bytes + bytes / 4 + (1 << 20);
+    if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { dl4j_set_error("workspace: stream sync failed"); return nullptr; }
+    if (ctx->ws[slot]) cudaFree(ctx->ws[slot]);
+    ctx->ws[slot] = nullptr;
+    ctx->ws_bytes[slot] = 0;
+    cudaError_t e = cudaMalloc(&ctx->ws[slot], want);
+    if (e != cudaSuccess) {
+        dl4j_set_error("workspace: cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e));
+        return nullptr;
+    }
+    ctx->ws_bytes[slot] = want;
+    return ctx->ws[slot];
+}
+
+extern "C" {
+
+const char *dl4jb200_last_error(void) { return g_err; }
+int dl4jb200_version(void) { return 100; }
+
+int dl4jb200_ctx_create(int device, void *stream, dl4jb200_ctx **out) {
+    DL4J_REQUIRE(out != nullptr, "ctx_create: out is NULL");
+    int n = 0;
+    DL4J_CUDA_TRY(cudaGetDeviceCount(&n));
+    DL4J_REQUIRE(device >= 0 && device < n, "ctx_create: device %d out of range (%d devices)", device, n);
+    DL4J_CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    DL4J_CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        dl4j_set_error("ctx_create: device %d is sm_%d%d; this library is built for sm_100a (B200) only", device,
+                       prop.major, prop.minor);
+        return DL4JB200_NOT_SUPPORTED;
+    }
+    dl4jb200_ctx *c = new dl4jb200_ctx();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    for (int i = 0; i < 4; i++) { c->ws[i] = nullptr; c->ws_bytes[i] = 0; }
+    if (stream) {
+        c->stream = (cudaStream_t)stream;
+        c->own_stream = false;
+    } else {
+        cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) { delete c; dl4j_set_error("ctx_create: stream: %s", cudaGetErrorString(e)); return DL4JB200_ERR_CUDA; }
+        c->own_stream = true;
+    }
+    *out = c;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_ctx_destroy(dl4jb200_ctx *ctx) {
+    if (!ctx) return DL4JB200_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto &kv : ctx->mirrors) cudaFree(kv.second.dev);
+    for (int i = 0; i < 4; i++) if (ctx->ws[i]) cudaFree(ctx->ws[i]);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_ctx_set_stream(dl4jb200_ctx *ctx, void *stream) {
+    DL4J_REQUIRE(ctx, "ctx is NULL");
+    if (ctx->own_stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); ctx->own_stream = false; }
+    ctx->stream = (cudaStream_t)stream;
+    return DL4JB200_OK;
+}
+
+void *dl4jb200_ctx_stream(dl4jb200_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+
+int dl4jb200_ctx_sync(dl4jb200_ctx *ctx) {
+    DL4J_REQUIRE(ctx, "ctx is NULL");
+    DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return DL4JB200_OK;
+}
+
+size_t dl4jb200_ctx_workspace_bytes(dl4jb200_ctx *ctx) {
+    size_t s = 0;
+    if (ctx) for (int i = 0; i < 4; i++) s += ctx->ws_bytes[i];
+    return s;
+}
+
+int dl4jb200_ctx_sm_count(dl4jb200_ctx *ctx) { return ctx ? ctx->sm_count : 0; }
+
+int dl4jb200_malloc(dl4jb200_ctx *ctx, size_t bytes, void **out) {
+    DL4J_REQUIRE(ctx && out, "malloc: NULL argument");
+    DL4J_CUDA_TRY(cudaSetDevice(ctx->device));
+    DL4J_CUDA_TRY(cudaMalloc(out, bytes ? bytes : 16));
+    return DL4JB200_OK;
+}
+
+int dl4jb200_free(dl4jb200_ctx *ctx, void *ptr) {
+    DL4J_REQUIRE(ctx, "ctx is NULL");
+    if (ptr) {
+        DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        DL4J_CUDA_TRY(cudaFree(ptr));
+    }
+    return DL4JB200_OK;
+}
+
+int dl4jb200_memset(dl4jb200_ctx *ctx, void *dst, int value, size_t bytes) {
+    DL4J_REQUIRE(ctx && dst, "memset: NULL argument");
+    DL4J_CUDA_TRY(cudaMemsetAsync(dst, value, bytes, ctx->stream));
+    return DL4JB200_OK;
+}
+
+int dl4jb200_memcpy_h2d(dl4jb200_ctx *ctx, void *dst, const void *src_host, size_t bytes) {
+    DL4J_REQUIRE(ctx && dst && src_host, "memcpy_h2d: NULL argument");
+    DL4J_CUDA_TRY(cudaMemcpyAsync(dst, src_host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return DL4JB200_OK;
+}
+
+int dl4jb200_memcpy_d2h(dl4jb200_ctx *ctx, void *dst_host, const void *src, size_t bytes) {
+    DL4J_REQUIRE(ctx && dst_host && src, "memcpy_d2h: NULL argument");
+    DL4J_CUDA_TRY(cudaMemcpyAsync(dst_host, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));  // the host may read dst as soon as we return
+    return DL4JB200_OK;
+}
+
+int dl4jb200_memcpy_d2d(dl4jb200_ctx *ctx, void *dst, const void *src, size_t bytes) {
+    DL4J_REQUIRE(ctx && dst && src, "memcpy_d2d: NULL argument");
+    DL4J_CUDA_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_register(dl4jb200_ctx *ctx, const void *host_ptr, size_t bytes, void **device_out) {
+    DL4J_REQUIRE(ctx && host_ptr && device_out, "buf_register: NULL argument");
+    auto it = ctx->mirrors.find(host_ptr);
+    if (it != ctx->mirrors.end()) {
+        if (it->second.bytes >= bytes) { *device_out = it->second.dev; return DL4JB200_OK; }
+        DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        cudaFree(it->second.dev);
+        ctx->mirrors.erase(it);
+    }
+    void *d = nullptr;
+    DL4J_CUDA_TRY(cudaMalloc(&d, bytes ? bytes : 16));
+    ctx->mirrors[host_ptr] = MirrorBuf{d, bytes};
+    *device_out = d;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_lookup(dl4jb200_ctx *ctx, const void *host_ptr, void **device_out, size_t *bytes_out) {
+    DL4J_REQUIRE(ctx && host_ptr, "buf_lookup: NULL argument");
+    auto it = ctx->mirrors.find(host_ptr);
+    if (it == ctx->mirrors.end()) { dl4j_set_error("buf_lookup: %p is not registered", host_ptr); return DL4JB200_ERR_INVALID_ARG; }
+    if (device_out) *device_out = it->second.dev;
+    if (bytes_out) *bytes_out = it->second.bytes;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_upload(dl4jb200_ctx *ctx, const void *host_ptr) {
+    void *d; size_t n;
+    int rc = dl4jb200_buf_lookup(ctx, host_ptr, &d, &n);
+    if (rc) return rc;
+    DL4J_CUDA_TRY(cudaMemcpyAsync(d, host_ptr, n, cudaMemcpyHostToDevice, ctx->stream));
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_download(dl4jb200_ctx *ctx, void *host_ptr) {
+    void *d; size_t n;
+    int rc = dl4jb200_buf_lookup(ctx, host_ptr, &d, &n);
+    if (rc) return rc;
+    DL4J_CUDA_TRY(cudaMemcpyAsync(host_ptr, d, n, cudaMemcpyDeviceToHost, ctx->stream));
+    DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_release(dl4jb200_ctx *ctx, const void *host_ptr) {
+    DL4J_REQUIRE(ctx && host_ptr, "buf_release: NULL argument");
+    auto it = ctx->mirrors.find(host_ptr);
+    if (it == ctx->mirrors.end()) return DL4JB200_OK;
+    DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    cudaFree(it->second.dev);
+    ctx->mirrors.erase(it);
+    return DL4JB200_OK;
+}
+
+// NN/util/ConvolutionUtils.java:96-131, 133-211, 213-221, 243-266 (Java int division truncates, as C++ does)
+int dl4jb200_out_size(int in, int kernel, int stride, int pad, int dilation, int mode, int *out, int *pad_lo,
+                      int *pad_hi) {
+    DL4J_REQUIRE(out && pad_lo && pad_hi, "out_size: NULL output");
+    DL4J_REQUIRE(stride > 0 && dilation > 0 && in > 0, "out_size: stride/dilation/input must be positive");
+    DL4J_REQUIRE(mode >= 0 && mode <= 2, "out_size: unknown ConvolutionMode %d", mode);
+    int ke = dilation == 1 ? kernel : kernel + (kernel - 1) * (dilation - 1);
+    if (mode != DL4JB200_MODE_SAME && (ke <= 0 || ke > in + 2 * pad)) {
+        dl4j_set_error("Invalid input data or configuration: (effective) kernel = %d, input = %d and padding = %d "
+                       "do not satisfy 0 < %d <= %d", ke, in, pad, ke, in + 2 * pad);
+        return DL4JB200_ERR_INVALID_INPUT;
+    }
+    if (mode == DL4JB200_MODE_STRICT && (in - ke + 2 * pad) % stride != 0) {
+        dl4j_set_error("Invalid input data or configuration: ConvolutionMode.Strict requires (input - kernelSize + "
+                       "2*padding)/stride + 1 to be an integer. Got: (%d - %d + 2*%d)/%d + 1 = %.2f", in, ke, pad,
+                       stride, (in - ke + 2 * pad) / (double)stride + 1.0);
+        return DL4JB200_ERR_INVALID_CONFIG;
+    }
+    if (mode == DL4JB200_MODE_SAME) {
+        int o = (int)ceil(in / (double)stride);
+        *out = o;
+        *pad_lo = ((o - 1) * stride + ke - in) / 2;
+        *pad_hi = ((o - 1) * stride + ke - in + 1) / 2;
+    } else {
+        *out = (in - ke + 2 * pad) / stride + 1;
+        *pad_lo = pad;
+        *pad_hi = pad;
+    }
+    return DL4JB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,393 @@
+// Batch normalisation forward (train / inference) and backward (BatchNormalization.java:93-219, 239-395).
+//
+// HBM-bound. Each direction is: (1) one streaming pass producing per-block partial sums for every channel
+// (128-bit loads, per-thread accumulation, shared-memory fold; partials go to context scratch), (2) a tiny
+// finalize kernel that folds the partials in double, applies the reference's exact formulas (biased
+// variance, eps stored into the running variance, ...) and emits per-channel coefficients, (3) one
+// streaming pass applying them. Forward sums are taken about a per-channel pivot (the channel's first
+// element) so that var = E[(x-K)^2] - E[x-K]^2 does not cancel catastrophically in fp32.
+// Algorithmic traffic: forward 8 B/elem + one extra read (12 moved), backward 12 B/elem + extra read of x
+// and eps (20 moved); the extra reads are what a conv-epilogue fusion removes later.
+#include "common.cuh"
+
+#define BN_THREADS 256
+
+// ------------------------------------------------------------------ pass 1: partial sums
+// MODE 0 (forward):  s1 = sum (x-K),  s2 = sum (x-K)^2          K = pivot[c]
+// MODE 1 (backward): s1 = sum e,      s2 = sum e*(x-mean[c])    e = eps (masked by act_out > 0 if given)
+template <int MODE>
+__global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__restrict__ x, const float *__restrict__ e,
+                                                                const float *__restrict__ act_out,
+                                                                const float *__restrict__ center, int center_stride,
+                                                                float *__restrict__ partial, int M, int cs) {
+    __shared__ float4 red[2][BN_THREADS];
+    const int Q = cs >> 2;
+    const int rows_per_blk = (M + gridDim.x - 1) / gridDim.x;
+    const int r0 = blockIdx.x * rows_per_blk, r1 = min(M, r0 + rows_per_blk);
+    for (int qb = 0; qb < Q; qb += BN_THREADS) {
+        const int qc = min(BN_THREADS, Q - qb);   // quads handled in this sweep
+        const int R = BN_THREADS / qc;            // rows in flight per iteration
+        const int q = qb + (threadIdx.x % qc), rl = threadIdx.x / qc;
+        float4 a1 = make_float4(0, 0, 0, 0), a2 = a1;
+        if (rl < R) {
+            // forward pivot = first row of the tensor; backward centre = saved mean (stride 1 array)
+            float4 k;
+            if (MODE == 0) k = *reinterpret_cast<const float4 *>(center + (size_t)q * 4);
+            else {
+                int c = q * 4;
+                k.x = c + 0 < center_stride ? center[c + 0] : 0.f; k.y = c + 1 < center_stride ? center[c + 1] : 0.f;
+                k.z = c + 2 < center_stride ? center[c + 2] : 0.f; k.w = c + 3 < center_stride ? center[c + 3] : 0.f;
+            }
+            for (int r = r0 + rl; r < r1; r += R) {
+                size_t o = (size_t)r * cs + (size_t)q * 4;
+                float4 v = *reinterpret_cast<const float4 *>(x + o);
+                v.x -= k.x; v.y -= k.y; v.z -= k.z; v.w -= k.w;
+                if (MODE == 0) {
+                    a1.x += v.x; a1.y += v.y; a1.z += v.z; a1.w += v.w;
+                    a2.x += v.x * v.x; a2.y += v.y * v.y; a2.z += v.z * v.z; a2.w += v.w * v.w;
+                } else {
+                    float4 g = *reinterpret_cast<const float4 *>(e + o);
+                    if (act_out) {
+                        float4 m = *reinterpret_cast<const float4 *>(act_out + o);
+                        g.x = m.x > 0.f ? g.x : 0.f; g.y = m.y > 0.f ? g.y : 0.f;
+                        g.z = m.z > 0.f ? g.z : 0.f; g.w = m.w > 0.f ? g.w : 0.f;
+                    }
+                    a1.x += g.x; a1.y += g.y; a1.z += g.z; a1.w += g.w;
+                    a2.x += g.x * v.x; a2.y += g.y * v.y; a2.z += g.z * v.z; a2.w += g.w * v.w;
+                }
+            }
+        }
+        red[0][threadIdx.x] = a1;
+        red[1][threadIdx.x] = a2;
+        __syncthreads();
+        if (rl == 0) {
+            for (int j = 1; j < R; j++) {
+                float4 b1 = red[0][threadIdx.x + j * qc], b2 = red[1][threadIdx.x + j * qc];
+                a1.x += b1.x; a1.y += b1.y; a1.z += b1.z; a1.w += b1.w;
+                a2.x += b2.x; a2.y += b2.y; a2.z += b2.z; a2.w += b2.w;
+            }
+            float *p = partial + (size_t)blockIdx.x * 2 * cs;
+            *reinterpret_cast<float4 *>(p + (size_t)q * 4) = a1;
+            *reinterpret_cast<float4 *>(p + cs + (size_t)q * 4) = a2;
+        }
+        __syncthreads();
+    }
+}
+
+// NCHW: grid (C, S); block (c, s) reduces elements [s*chunk, (s+1)*chunk) of the B*HW values of channel c.
+template <int MODE, bool VEC>
+__global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nchw(const float *__restrict__ x, const float *__restrict__ e,
+                                                                const float *__restrict__ act_out,
+                                                                const float *__restrict__ center, float *__restrict__ partial,
+                                                                int B, int C, int HW, long long chunk) {
+    __shared__ float red[2][BN_THREADS];
+    const int c = blockIdx.x;
+    const long long total = (long long)B * HW;
+    const long long j0 = (long long)blockIdx.y * chunk, j1 = min(total, j0 + chunk);
+    const float k = MODE == 0 ? x[(size_t)c * HW] : center[c];
+    float a1 = 0.f, a2 = 0.f;
+    constexpr int V = VEC ? 4 : 1;
+    for (long long j = j0 + (long long)threadIdx.x * V; j < j1; j += (long long)BN_THREADS * V) {
+        long long b = j / HW;
+        size_t o = ((size_t)b * C + c) * HW + (size_t)(j - b * HW);
+        float xv[V], ev[V], mv[V];
+        if (VEC) {
+            float4 t = *reinterpret_cast<const float4 *>(x + o);
+            xv[0] = t.x; xv[1 % V] = t.y; xv[2 % V] = t.z; xv[3 % V] = t.w;
+            if (MODE == 1) {
+                t = *reinterpret_cast<const float4 *>(e + o);
+                ev[0] = t.x; ev[1 % V] = t.y; ev[2 % V] = t.z; ev[3 % V] = t.w;
+                if (act_out) {
+                    t = *reinterpret_cast<const float4 *>(act_out + o);
+                    mv[0] = t.x; mv[1 % V] = t.y; mv[2 % V] = t.z; mv[3 % V] = t.w;
+                }
+            }
+        } else {
+            xv[0] = x[o];
+            if (MODE == 1) { ev[0] = e[o]; if (act_out) mv[0] = act_out[o]; }
+        }
+#pragma unroll
+        for (int i = 0; i < V; i++) {
+            float d = xv[i] - k;
+            if (MODE == 0) { a1 += d; a2 += d * d; }
+            else {
+                float g = (act_out && !(mv[i] > 0.f)) ? 0.f : ev[i];
+                a1 += g; a2 += g * d;
+            }
+        }
+    }
+    red[0][threadIdx.x] = a1;
+    red[1][threadIdx.x] = a2;
+    __syncthreads();
+    for (int o = BN_THREADS / 2; o; o >>= 1) {
+        if (threadIdx.x < o) { red[0][threadIdx.x] += red[0][threadIdx.x + o]; red[1][threadIdx.x] += red[1][threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        float *p = partial + (size_t)blockIdx.y * 2 * C;
+        p[c] = red[0][0];
+        p[C + c] = red[1][0];
+    }
+}
+
+// ------------------------------------------------------------------ pass 2: finalize (one thread per channel)
+// coef layout: [4][cpad] = centre, a, b, c   with  y = (x-centre)*a + c            (forward; b unused)
+//                                              dx = a*e + b*(x-centre) + c          (backward)
+__global__ void k_bn_finalize_fwd(const float *__restrict__ partial, int nblk, const float *__restrict__ pivot,
+                                  int pivot_stride, const float *__restrict__ gamma, const float *__restrict__ beta,
+                                  float *gmean, float *gvar, float *save_mean, float *save_std, float *coef, int C,
+                                  int cpad, double N, double decay, double eps, int training, int minibatch) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cpad) return;
+    if (c >= C) {  // NHWC padding channel: stays zero
+        coef[c] = 0.f; coef[cpad + c] = 0.f; coef[2 * cpad + c] = 0.f; coef[3 * cpad + c] = 0.f;
+        return;
+    }
+    double mean, std;
+    if (training) {
+        double s1 = 0.0, s2 = 0.0;
+        for (int b = 0; b < nblk; b++) { s1 += (double)partial[(size_t)b * 2 * cpad + c]; s2 += (double)partial[(size_t)b * 2 * cpad + cpad + c]; }
+        double k = (double)pivot[(size_t)c * pivot_stride];
+        double m1 = s1 / N;
+        mean = k + m1;                              // BatchNormalization.java:264
+        double var = s2 / N - m1 * m1;              // biased, :265
+        if (var < 0.0) var = 0.0;
+        double v = var + eps;                       // :273 (in place: eps becomes part of the stored variance)
+        std = sqrt(v);                              // :279
+        if (minibatch) {                            // :377-384
+            gmean[c] = (float)(decay * (double)gmean[c] + (1.0 - decay) * mean);
+            gvar[c] = (float)(decay * (double)gvar[c] + (1.0 - decay) * v);
+        } else {                                    // :386-390
+            gmean[c] = (float)mean;
+            gvar[c] = (float)v;
+        }
+    } else {                                        // :274-279, no eps added in test mode
+        mean = (double)gmean[c];
+        std = sqrt((double)gvar[c]);
+    }
+    if (save_mean) save_mean[c] = (float)mean;
+    if (save_std) save_std[c] = (float)std;
+    double g = gamma ? (double)gamma[c] : 1.0, bt = beta ? (double)beta[c] : 0.0;
+    coef[c] = (float)mean;
+    coef[cpad + c] = (float)(g / std);
+    coef[2 * cpad + c] = 0.f;
+    coef[3 * cpad + c] = (float)bt;
+}
+
+__global__ void k_bn_finalize_bwd(const float *__restrict__ partial, int nblk, const float *__restrict__ gamma,
+                                  const float *__restrict__ save_mean, const float *__restrict__ save_std,
+                                  float *dgamma, float *dbeta, float *coef, int C, int cpad, double N) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cpad) return;
+    if (c >= C) {
+        coef[c] = 0.f; coef[cpad + c] = 0.f; coef[2 * cpad + c] = 0.f; coef[3 * cpad + c] = 0.f;
+        return;
+    }
+    double s1 = 0.0, s2 = 0.0;
+    for (int b = 0; b < nblk; b++) { s1 += (double)partial[(size_t)b * 2 * cpad + c]; s2 += (double)partial[(size_t)b * 2 * cpad + cpad + c]; }
+    double std = (double)save_std[c], g = gamma ? (double)gamma[c] : 1.0;
+    // BatchNormalization.java:172-196 with dxhat = e*gamma:
+    //   dVar = sum(dxhat*xMu) * -0.5 * std^-3 ; dMu = -sum(dxhat)/std (+ dVar*(-2/N)*sum xMu, sum xMu == 0)
+    //   dx = dxhat/std + xMu*dVar*2/N + dMu/N
+    if (dbeta) dbeta[c] = (float)s1;
+    if (dgamma) dgamma[c] = (float)(s2 / std);
+    coef[c] = save_mean[c];
+    coef[cpad + c] = (float)(g / std);
+    coef[2 * cpad + c] = (float)(-g * s2 / (N * std * std * std));
+    coef[3 * cpad + c] = (float)(-g * s1 / (N * std));
+}
+
+// ------------------------------------------------------------------ pass 3: apply
+// MODE 0: y = act((x-centre)*a + c).  MODE 1: dx = a*e' + b*(x-centre) + c, e' = eps masked by act_out.
+template <int MODE>
+__global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__ x, const float *__restrict__ e,
+                                                       const float *__restrict__ act_out, float *__restrict__ out,
+                                                       const float *__restrict__ coef, size_t total4, int cs, int act) {
+    const int Q = cs >> 2;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += stride) {
+        int q = (int)(i % Q);
+        float4 k = __ldg(reinterpret_cast<const float4 *>(coef) + q);
+        float4 a = __ldg(reinterpret_cast<const float4 *>(coef + cs) + q);
+        float4 c = __ldg(reinterpret_cast<const float4 *>(coef + 3 * (size_t)cs) + q);
+        float4 v = reinterpret_cast<const float4 *>(x)[i];
+        v.x -= k.x; v.y -= k.y; v.z -= k.z; v.w -= k.w;
+        float4 r;
+        if (MODE == 0) {
+            r.x = dl4j_act(v.x * a.x + c.x, act); r.y = dl4j_act(v.y * a.y + c.y, act);
+            r.z = dl4j_act(v.z * a.z + c.z, act); r.w = dl4j_act(v.w * a.w + c.w, act);
+        } else {
+            float4 b = __ldg(reinterpret_cast<const float4 *>(coef + 2 * (size_t)cs) + q);
+            float4 g = reinterpret_cast<const float4 *>(e)[i];
+            if (act_out) {
+                float4 m = reinterpret_cast<const float4 *>(act_out)[i];
+                g.x = m.x > 0.f ? g.x : 0.f; g.y = m.y > 0.f ? g.y : 0.f;
+                g.z = m.z > 0.f ? g.z : 0.f; g.w = m.w > 0.f ? g.w : 0.f;
+            }
+            r.x = a.x * g.x + b.x * v.x + c.x; r.y = a.y * g.y + b.y * v.y + c.y;
+            r.z = a.z * g.z + b.z * v.z + c.z; r.w = a.w * g.w + b.w * v.w + c.w;
+        }
+        reinterpret_cast<float4 *>(out)[i] = r;
+    }
+}
+
+template <int MODE, bool VEC>
+__global__ void __launch_bounds__(256) k_bn_apply_nchw(const float *__restrict__ x, const float *__restrict__ e,
+                                                       const float *__restrict__ act_out, float *__restrict__ out,
+                                                       const float *__restrict__ coef, size_t total, int C, int HW,
+                                                       int act) {
+    constexpr int V = VEC ? 4 : 1;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i * V < total; i += stride) {
+        size_t o = i * V;
+        int ch = (int)((o / HW) % C);
+        float k = __ldg(coef + ch), a = __ldg(coef + C + ch), b = __ldg(coef + 2 * C + ch), c = __ldg(coef + 3 * C + ch);
+        float xv[V], ev[V], mv[V], r[V];
+        if (VEC) {
+            float4 t = *reinterpret_cast<const float4 *>(x + o);
+            xv[0] = t.x; xv[1 % V] = t.y; xv[2 % V] = t.z; xv[3 % V] = t.w;
+            if (MODE == 1) {
+                t = *reinterpret_cast<const float4 *>(e + o);
+                ev[0] = t.x; ev[1 % V] = t.y; ev[2 % V] = t.z; ev[3 % V] = t.w;
+                if (act_out) { t = *reinterpret_cast<const float4 *>(act_out + o); mv[0] = t.x; mv[1 % V] = t.y; mv[2 % V] = t.z; mv[3 % V] = t.w; }
+            }
+        } else {
+            xv[0] = x[o];
+            if (MODE == 1) { ev[0] = e[o]; if (act_out) mv[0] = act_out[o]; }
+        }
+#pragma unroll
+        for (int j = 0; j < V; j++) {
+            float d = xv[j] - k;
+            if (MODE == 0) r[j] = dl4j_act(d * a + c, act);
+            else {
+                float g = (act_out && !(mv[j] > 0.f)) ? 0.f : ev[j];
+                r[j] = a * g + b * d + c;
+            }
+        }
+        if (VEC) *reinterpret_cast<float4 *>(out + o) = make_float4(r[0], r[1 % V], r[2 % V], r[3 % V]);
+        else out[o] = r[0];
+    }
+}
+
+static inline bool al16(const void *p) { return ((uintptr_t)p & 15) == 0; }
+
+struct BnPlan {
+    int nblk;         // partial blocks
+    long long chunk;  // NCHW: elements per split
+    float *partial, *coef;
+    int cpad;
+};
+
+static int bn_plan(dl4jb200_ctx *ctx, int B, int C, int H, int W, int layout, int cs, BnPlan &p) {
+    long long HW = (long long)H * W, M = (long long)B * HW;
+    if (layout == DL4JB200_NHWC) {
+        p.cpad = cs;
+        int Q = cs / 4, qc = Q < BN_THREADS ? Q : BN_THREADS, R = BN_THREADS / qc;
+        long long want = M / ((long long)R * 8);
+        long long cap = (long long)ctx->sm_count * 4;
+        p.nblk = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+        p.chunk = 0;
+    } else {
+        p.cpad = C;
+        long long per = M;  // elements per channel
+        long long cap = ((long long)ctx->sm_count * 8 + C - 1) / C;  // aim at ~8 blocks per SM overall
+        long long s = per / 4096;
+        if (s > cap) s = cap;
+        if (s < 1) s = 1;
+        long long chunk = (per + s - 1) / s;
+        chunk = (chunk + 3) / 4 * 4;
+        p.nblk = (int)((per + chunk - 1) / chunk);
+        p.chunk = chunk;
+    }
+    size_t bytes = ((size_t)p.nblk * 2 + 4) * p.cpad * sizeof(float);
+    float *ws = (float *)dl4j_workspace(ctx, 0, bytes);
+    if (!ws) return DL4JB200_ERR_CUDA;
+    p.coef = ws;  // first: 16-byte aligned coefficient block (cpad % 4 == 0 for NHWC)
+    p.partial = ws + 4 * (size_t)p.cpad;
+    return DL4JB200_OK;
+}
+
+static inline int bn_grid(dl4jb200_ctx *ctx, size_t items) {
+    size_t blocks = (items + 255) / 256, cap = (size_t)ctx->sm_count * 16;
+    return (int)(blocks > cap ? cap : (blocks ? blocks : 1));
+}
+
+extern "C" {
+
+int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *gamma, const float *beta,
+                    float *gmean, float *gvar, float *save_mean, float *save_std, int B, int C, int H, int W,
+                    int layout, int cs, double decay, double eps, int training, int minibatch, int act) {
+    DL4J_REQUIRE(ctx && x && y && gmean && gvar, "bn_fwd: NULL argument");
+    DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, "bn_fwd: bad shape");
+    DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "bn_fwd: unknown layout %d", layout);
+    DL4J_REQUIRE(layout == DL4JB200_NCHW || (cs >= C && cs % 4 == 0 && al16(x) && al16(y)), "bn_fwd: NHWC needs cs %% 4 == 0, cs >= C and 16-byte aligned tensors");
+    DL4J_REQUIRE(C <= 65535 * 8, "bn_fwd: too many channels");
+    BnPlan p;
+    int rc = bn_plan(ctx, B, C, H, W, layout, cs, p);
+    if (rc) return rc;
+    const int HW = H * W;
+    const long long M = (long long)B * HW;
+    const size_t total = (size_t)M * (layout == DL4JB200_NHWC ? cs : C);
+    if (training) {
+        if (layout == DL4JB200_NHWC) {
+            k_bn_partial_nhwc<0><<<p.nblk, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, x, cs, p.partial, (int)M, cs);
+        } else {
+            dim3 grid(C, p.nblk);
+            bool vec = (HW % 4 == 0) && al16(x);
+            if (vec) k_bn_partial_nchw<0, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, nullptr, p.partial, B, C, HW, p.chunk);
+            else k_bn_partial_nchw<0, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, nullptr, p.partial, B, C, HW, p.chunk);
+        }
+        DL4J_CHECK_LAUNCH();
+    }
+    k_bn_finalize_fwd<<<dl4j_ceil_div(p.cpad, 128), 128, 0, ctx->stream>>>(
+        p.partial, p.nblk, x, layout == DL4JB200_NHWC ? 1 : HW, gamma, beta, gmean, gvar, save_mean, save_std, p.coef, C,
+        p.cpad, (double)M, decay, eps, training, minibatch);
+    DL4J_CHECK_LAUNCH();
+    if (layout == DL4JB200_NHWC) {
+        k_bn_apply_nhwc<0><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, p.coef, total / 4, cs, act);
+    } else {
+        bool vec = (HW % 4 == 0) && al16(x) && al16(y);
+        if (vec) k_bn_apply_nchw<0, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, p.coef, total, C, HW, act);
+        else k_bn_apply_nchw<0, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, p.coef, total, C, HW, act);
+    }
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const float *gamma,
+                    const float *save_mean, const float *save_std, const float *act_out, float *dx,
+                    float *dgamma, float *dbeta, int B, int C, int H, int W, int layout, int cs) {
+    DL4J_REQUIRE(ctx && x && eps && save_mean && save_std && dx, "bn_bwd: NULL argument");
+    DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, "bn_bwd: bad shape");
+    DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "bn_bwd: unknown layout %d", layout);
+    DL4J_REQUIRE(layout == DL4JB200_NCHW || (cs >= C && cs % 4 == 0 && al16(x) && al16(eps) && al16(dx) && al16(act_out)),
+                 "bn_bwd: NHWC needs cs %% 4 == 0, cs >= C and 16-byte aligned tensors");
+    BnPlan p;
+    int rc = bn_plan(ctx, B, C, H, W, layout, cs, p);
+    if (rc) return rc;
+    const int HW = H * W;
+    const long long M = (long long)B * HW;
+    const size_t total = (size_t)M * (layout == DL4JB200_NHWC ? cs : C);
+    bool vec = (HW % 4 == 0) && al16(x) && al16(eps) && al16(dx) && al16(act_out);
+    if (layout == DL4JB200_NHWC) {
+        k_bn_partial_nhwc<1><<<p.nblk, BN_THREADS, 0, ctx->stream>>>(x, eps, act_out, save_mean, C, p.partial, (int)M, cs);
+    } else {
+        dim3 grid(C, p.nblk);
+        if (vec) k_bn_partial_nchw<1, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, act_out, save_mean, p.partial, B, C, HW, p.chunk);
+        else k_bn_partial_nchw<1, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, act_out, save_mean, p.partial, B, C, HW, p.chunk);
+    }
+    DL4J_CHECK_LAUNCH();
+    k_bn_finalize_bwd<<<dl4j_ceil_div(p.cpad, 128), 128, 0, ctx->stream>>>(p.partial, p.nblk, gamma, save_mean, save_std,
+                                                                         dgamma, dbeta, p.coef, C, p.cpad, (double)M);
+    DL4J_CHECK_LAUNCH();
+    if (layout == DL4JB200_NHWC) {
+        k_bn_apply_nhwc<1><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, act_out, dx, p.coef, total / 4, cs, 0);
+    } else {
+        if (vec) k_bn_apply_nchw<1, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, act_out, dx, p.coef, total, C, HW, 0);
+        else k_bn_apply_nchw<1, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, eps, act_out, dx, p.coef, total, C, HW, 0);
+    }
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+}  // extern "C"

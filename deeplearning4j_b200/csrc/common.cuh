@@ -1,0 +1,100 @@
+// Shared host/device plumbing of libdl4jb200: context, error reporting, scratch workspace.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <unordered_map>
+
+#include "../../include/dl4jb200.h"
+
+struct MirrorBuf {
+    void *dev;
+    size_t bytes;
+};
+
+struct dl4jb200_ctx {
+    int device;
+    cudaStream_t stream;
+    bool own_stream;
+    int sm_count;
+    // scratch, grown on demand (never shrunk); slot 0: kernel partials / packed filters, slot 1: NHWC staging
+    void *ws[4];
+    size_t ws_bytes[4];
+    std::unordered_map<const void *, MirrorBuf> mirrors;
+};
+
+void dl4j_set_error(const char *fmt, ...);
+// Returns a scratch region of at least `bytes` in slot `slot`; nullptr (and error set) on failure.
+void *dl4j_workspace(dl4jb200_ctx *ctx, int slot, size_t bytes);
+
+#define DL4J_CUDA_TRY(expr)                                                                       \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess) {                                                                  \
+            dl4j_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return DL4JB200_ERR_CUDA;                                                             \
+        }                                                                                         \
+    } while (0)
+
+#define DL4J_CHECK_LAUNCH() DL4J_CUDA_TRY(cudaGetLastError())
+
+#define DL4J_REQUIRE(cond, ...)            \
+    do {                                   \
+        if (!(cond)) {                     \
+            dl4j_set_error(__VA_ARGS__);   \
+            return DL4JB200_ERR_INVALID_ARG; \
+        }                                  \
+    } while (0)
+
+static inline int dl4j_ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+static inline int dl4j_round_up(int a, int b) { return (a + b - 1) / b * b; }
+
+// Unsigned division by a runtime constant via multiply-high (divisor < 2^31, dividend < 2^31).
+struct FastDiv {
+    uint32_t d, mul, shr;
+    FastDiv() : d(1), mul(0), shr(0) {}
+    explicit FastDiv(uint32_t div) : d(div) {
+        if (div == 1) { mul = 0; shr = 0; return; }
+        uint32_t l = 0;
+        while ((1u << l) < div) l++;  // ceil(log2(d))
+        uint64_t m = ((uint64_t)1 << (32 + l)) / div + 1;  // fits: result in [2^32, 2^33)
+        mul = (uint32_t)(m - ((uint64_t)1 << 32));
+        shr = l;
+    }
+    __host__ __device__ __forceinline__ uint32_t div(uint32_t n) const {
+#ifdef __CUDA_ARCH__
+        if (d == 1) return n;
+        uint32_t t = __umulhi(n, mul);
+        return (t + ((n - t) >> 1)) >> (shr - 1);
+#else
+        return n / d;
+#endif
+    }
+    __host__ __device__ __forceinline__ void divmod(uint32_t n, uint32_t &q, uint32_t &r) const {
+        q = div(n);
+        r = n - q * d;
+    }
+};
+
+// activation codes shared by every epilogue (DL4JB200_ACT_*)
+__device__ __forceinline__ float dl4j_act(float z, int kind) {
+    switch (kind) {
+    case DL4JB200_ACT_RELU: return z > 0.f ? z : 0.f;
+    case DL4JB200_ACT_SIGMOID: return 1.f / (1.f + expf(-z));
+    case DL4JB200_ACT_TANH: return tanhf(z);
+    case DL4JB200_ACT_LEAKYRELU: return z > 0.f ? z : 0.01f * z;
+    default: return z;
+    }
+}
+__device__ __forceinline__ float dl4j_act_grad(float z, int kind) {
+    switch (kind) {
+    case DL4JB200_ACT_RELU: return z > 0.f ? 1.f : 0.f;
+    case DL4JB200_ACT_SIGMOID: { float s = 1.f / (1.f + expf(-z)); return s * (1.f - s); }
+    case DL4JB200_ACT_TANH: { float t = tanhf(z); return 1.f - t * t; }
+    case DL4JB200_ACT_LEAKYRELU: return z > 0.f ? 1.f : 0.01f;
+    default: return 1.f;
+    }
+}

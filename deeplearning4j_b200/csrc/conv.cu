@@ -1,0 +1,257 @@
+// Convolution entry points: geometry, filter packing, algorithm dispatch, split-K reduction, bias gradient,
+// and NCHW staging for callers that hold DL4J-layout ('c' order NCHW) tensors.
+#include "conv_common.cuh"
+
+// ------------------------------------------------------------------ geometry
+static void geom_finish(ConvGeom &g) {
+    g.taps = g.kH * g.kW;
+    g.K = g.taps * g.Cg;
+    g.Kp = dl4j_round_up(g.K, 32);
+    g.M = g.B * g.Hm * g.Wm;
+    g.div_Wm = FastDiv((uint32_t)g.Wm);
+    g.div_HWm = FastDiv((uint32_t)(g.Hm * g.Wm));
+    g.div_Cg = FastDiv((uint32_t)g.Cg);
+    g.div_kW = FastDiv((uint32_t)g.kW);
+}
+
+ConvGeom conv_geom_fwd(const dl4jb200_conv_desc *d, int x_cs) {
+    ConvGeom g;
+    g.B = d->batch; g.Hs = d->in_h; g.Ws = d->in_w; g.cs_src = x_cs;
+    g.Hm = d->out_h; g.Wm = d->out_w;
+    g.kH = d->k_h; g.kW = d->k_w; g.sH = d->stride_h; g.sW = d->stride_w;
+    g.pT = d->pad_top; g.pL = d->pad_left; g.dH = d->dil_h; g.dW = d->dil_w;
+    g.Cg = dl4j_round_up(d->c_in, 4);
+    g.transposed = 0;
+    geom_finish(g);
+    return g;
+}
+
+ConvGeom conv_geom_bwd_data(const dl4jb200_conv_desc *d, int delta_cs) {
+    ConvGeom g;
+    g.B = d->batch; g.Hs = d->out_h; g.Ws = d->out_w; g.cs_src = delta_cs;
+    g.Hm = d->in_h; g.Wm = d->in_w;
+    g.kH = d->k_h; g.kW = d->k_w; g.sH = d->stride_h; g.sW = d->stride_w;
+    g.pT = d->pad_top; g.pL = d->pad_left; g.dH = d->dil_h; g.dW = d->dil_w;
+    g.Cg = dl4j_round_up(d->c_out, 4);
+    g.transposed = 1;
+    geom_finish(g);
+    return g;
+}
+
+// ------------------------------------------------------------------ filter packing
+// DL4J filter W[co][ci][kh][kw] ('c' order, ConvolutionParamInitializer.java:144-155) ->
+//   forward operand  Wf[n = co][k = (kh*kW+kw)*Cg + ci]       (transposed = 0)
+//   backprop-data    Wb[n = ci][k = (kh*kW+kw)*Cg + co]       (transposed = 1)
+// rows padded with zeros to `rows_p`, K padded to Kp. round_tf32: round-to-nearest into TF32 so that the
+// tensor core's truncation of operand mantissas does not bias the filter side.
+__global__ void __launch_bounds__(256) k_pack_filter(const float *__restrict__ w, float *__restrict__ wp, int Cout, int Cin,
+                                                     int kH, int kW, int Cg, int Kp, int rows_p, int transposed,
+                                                     int round_tf32) {
+    size_t total = (size_t)rows_p * Kp, stride = (size_t)gridDim.x * blockDim.x;
+    const int taps = kH * kW;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        int n = (int)(i / Kp), k = (int)(i % Kp);
+        int tap = k / Cg, c = k % Cg;
+        float v = 0.f;
+        if (tap < taps) {
+            int co = transposed ? c : n, ci = transposed ? n : c;
+            if (co < Cout && ci < Cin) v = w[((size_t)co * Cin + ci) * taps + tap];
+        }
+        wp[i] = round_tf32 ? to_tf32_rna(v) : v;
+    }
+}
+
+// dW[co][ci][kh][kw] = sum_s partial[s][co][(kh*kW+kw)*Cg + ci]   (fixed order: deterministic)
+__global__ void __launch_bounds__(256) k_wgrad_finalize(const float *__restrict__ partial, float *__restrict__ dw, int Cout,
+                                                        int Cin, int taps, int Cg, int Kp, int rows_p, int splits) {
+    size_t total = (size_t)Cout * Cin * taps, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        int tap = (int)(i % taps);
+        size_t t = i / taps;
+        int ci = (int)(t % Cin), co = (int)(t / Cin);
+        const float *p = partial + (size_t)co * Kp + (size_t)tap * Cg + ci;
+        float acc = 0.f;
+        for (int s = 0; s < splits; s++) acc += p[(size_t)s * rows_p * Kp];
+        dw[i] = acc;
+    }
+}
+
+// bias gradient: column sums of delta[M, cs] (ConvolutionLayer.java:257). Two deterministic stages.
+__global__ void __launch_bounds__(256) k_colsum_partial(const float *__restrict__ d, float *__restrict__ partial, int M, int cs) {
+    __shared__ float4 red[256];
+    const int Q = cs >> 2;
+    const int rows_per_blk = (M + gridDim.x - 1) / gridDim.x;
+    const int r0 = blockIdx.x * rows_per_blk, r1 = min(M, r0 + rows_per_blk);
+    for (int qb = 0; qb < Q; qb += 256) {
+        const int qc = min(256, Q - qb), R = 256 / qc;
+        const int q = qb + (threadIdx.x % qc), rl = threadIdx.x / qc;
+        float4 a = make_float4(0, 0, 0, 0);
+        if (rl < R)
+            for (int r = r0 + rl; r < r1; r += R) {
+                float4 v = *reinterpret_cast<const float4 *>(d + (size_t)r * cs + (size_t)q * 4);
+                a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+            }
+        red[threadIdx.x] = a;
+        __syncthreads();
+        if (rl == 0) {
+            for (int j = 1; j < R; j++) { float4 b = red[threadIdx.x + j * qc]; a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+            *reinterpret_cast<float4 *>(partial + (size_t)blockIdx.x * cs + (size_t)q * 4) = a;
+        }
+        __syncthreads();
+    }
+}
+__global__ void k_colsum_final(const float *__restrict__ partial, float *__restrict__ out, int nblk, int cs, int C) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    double acc = 0.0;
+    for (int b = 0; b < nblk; b++) acc += (double)partial[(size_t)b * cs + c];
+    out[c] = (float)acc;
+}
+
+static inline int grid_for(dl4jb200_ctx *ctx, size_t items) {
+    size_t blocks = (items + 255) / 256, cap = (size_t)ctx->sm_count * 8;
+    return (int)(blocks > cap ? cap : (blocks ? blocks : 1));
+}
+
+static int check_desc(const dl4jb200_conv_desc *d, const char *who) {
+    DL4J_REQUIRE(d, "%s: desc is NULL", who);
+    DL4J_REQUIRE(d->batch > 0 && d->c_in > 0 && d->in_h > 0 && d->in_w > 0 && d->c_out > 0 && d->k_h > 0 && d->k_w > 0 &&
+                     d->stride_h > 0 && d->stride_w > 0 && d->dil_h > 0 && d->dil_w > 0 && d->out_h > 0 && d->out_w > 0,
+                 "%s: non-positive dimension in descriptor", who);
+    DL4J_REQUIRE((long long)d->batch * d->in_h * d->in_w < (1LL << 31) / 4 && (long long)d->batch * d->out_h * d->out_w < (1LL << 31) / 4,
+                 "%s: more than 2^29 pixels per tensor is not supported", who);
+    return DL4JB200_OK;
+}
+
+static int check_layout(int layout, int cs, int C, const void *p, const char *who, const char *name) {
+    DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "%s: unknown layout for %s", who, name);
+    if (layout == DL4JB200_NHWC)
+        DL4J_REQUIRE(cs >= C && cs % 4 == 0 && ((uintptr_t)p & 15) == 0, "%s: NHWC %s needs cs %% 4 == 0, cs >= C, 16-byte alignment", who, name);
+    return DL4JB200_OK;
+}
+
+extern "C" {
+
+int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs,
+                      const float *w, const float *bias, float *z, int z_layout, int z_cs, int act, int algo) {
+    DL4J_REQUIRE(ctx && x && w && z, "conv_fwd: NULL argument");
+    int rc = check_desc(d, "conv_fwd");
+    if (rc) return rc;
+    if ((rc = check_layout(x_layout, x_cs, d->c_in, x, "conv_fwd", "x"))) return rc;
+    if ((rc = check_layout(z_layout, z_cs, d->c_out, z, "conv_fwd", "z"))) return rc;
+    DL4J_REQUIRE(algo == DL4JB200_CONV_ALGO_TC_TF32 || algo == DL4JB200_CONV_ALGO_FP32, "conv_fwd: unknown algo %d", algo);
+    if (act < 0 || act > DL4JB200_ACT_LEAKYRELU) { dl4j_set_error("conv_fwd: activation %d not handled by the helper", act); return DL4JB200_NOT_SUPPORTED; }
+
+    // stage DL4J-layout tensors into the resident NHWC layout
+    const float *xs = x;
+    if (x_layout == DL4JB200_NCHW) {
+        x_cs = dl4j_round_up(d->c_in, 4);
+        float *t = (float *)dl4j_workspace(ctx, 1, (size_t)d->batch * d->in_h * d->in_w * x_cs * sizeof(float));
+        if (!t) return DL4JB200_ERR_CUDA;
+        if ((rc = dl4jb200_nchw_to_nhwc(ctx, x, t, d->batch, d->c_in, d->in_h, d->in_w, x_cs))) return rc;
+        xs = t;
+    }
+    float *zs = z;
+    if (z_layout == DL4JB200_NCHW) {
+        z_cs = dl4j_round_up(d->c_out, 4);
+        zs = (float *)dl4j_workspace(ctx, 2, (size_t)d->batch * d->out_h * d->out_w * z_cs * sizeof(float));
+        if (!zs) return DL4JB200_ERR_CUDA;
+    }
+    ConvGeom g = conv_geom_fwd(d, x_cs);
+    DL4J_REQUIRE(x_cs >= g.Cg, "conv_fwd: x pixel stride %d < %d", x_cs, g.Cg);
+    const int rows_p = dl4j_round_up(z_cs > d->c_out ? z_cs : d->c_out, 128);
+    float *wp = (float *)dl4j_workspace(ctx, 0, (size_t)rows_p * g.Kp * sizeof(float));
+    if (!wp) return DL4JB200_ERR_CUDA;
+    k_pack_filter<<<grid_for(ctx, (size_t)rows_p * g.Kp), 256, 0, ctx->stream>>>(w, wp, d->c_out, d->c_in, d->k_h, d->k_w, g.Cg,
+                                                                               g.Kp, rows_p, 0, algo == DL4JB200_CONV_ALGO_TC_TF32);
+    DL4J_CHECK_LAUNCH();
+    if (algo == DL4JB200_CONV_ALGO_TC_TF32) rc = conv_tc_gemm(ctx, g, xs, wp, rows_p, bias, zs, d->c_out, z_cs, act);
+    else rc = conv_ffma_gemm(ctx, g, xs, wp, bias, zs, d->c_out, z_cs, act);
+    if (rc) return rc;
+    if (z_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, zs, z, d->batch, d->c_out, d->out_h, d->out_w, z_cs);
+    return DL4JB200_OK;
+}
+
+int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs,
+                      const float *w, const float *delta, int delta_layout, int delta_cs, float *dw, float *db,
+                      float *dx, int dx_layout, int dx_cs, int algo) {
+    DL4J_REQUIRE(ctx && x && w && delta && dw, "conv_bwd: NULL argument");
+    int rc = check_desc(d, "conv_bwd");
+    if (rc) return rc;
+    if ((rc = check_layout(x_layout, x_cs, d->c_in, x, "conv_bwd", "x"))) return rc;
+    if ((rc = check_layout(delta_layout, delta_cs, d->c_out, delta, "conv_bwd", "delta"))) return rc;
+    if (dx && (rc = check_layout(dx_layout, dx_cs, d->c_in, dx, "conv_bwd", "dx"))) return rc;
+    DL4J_REQUIRE(algo == DL4JB200_CONV_ALGO_TC_TF32 || algo == DL4JB200_CONV_ALGO_FP32, "conv_bwd: unknown algo %d", algo);
+    const bool tcore = algo == DL4JB200_CONV_ALGO_TC_TF32;
+
+    const float *xs = x, *ds = delta;
+    if (x_layout == DL4JB200_NCHW) {
+        x_cs = dl4j_round_up(d->c_in, 4);
+        float *t = (float *)dl4j_workspace(ctx, 1, (size_t)d->batch * d->in_h * d->in_w * x_cs * sizeof(float));
+        if (!t) return DL4JB200_ERR_CUDA;
+        if ((rc = dl4jb200_nchw_to_nhwc(ctx, x, t, d->batch, d->c_in, d->in_h, d->in_w, x_cs))) return rc;
+        xs = t;
+    }
+    if (delta_layout == DL4JB200_NCHW) {
+        delta_cs = dl4j_round_up(d->c_out, 4);
+        float *t = (float *)dl4j_workspace(ctx, 2, (size_t)d->batch * d->out_h * d->out_w * delta_cs * sizeof(float));
+        if (!t) return DL4JB200_ERR_CUDA;
+        if ((rc = dl4jb200_nchw_to_nhwc(ctx, delta, t, d->batch, d->c_out, d->out_h, d->out_w, delta_cs))) return rc;
+        ds = t;
+    }
+    float *dxs = dx;
+    if (dx && dx_layout == DL4JB200_NCHW) {
+        dx_cs = dl4j_round_up(d->c_in, 4);
+        dxs = (float *)dl4j_workspace(ctx, 3, (size_t)d->batch * d->in_h * d->in_w * dx_cs * sizeof(float));
+        if (!dxs) return DL4JB200_ERR_CUDA;
+    }
+
+    // ---- filter gradient: split over pixel ranges, partials in scratch, fixed-order reduction into dw
+    ConvGeom gf = conv_geom_fwd(d, x_cs);
+    DL4J_REQUIRE(x_cs >= gf.Cg, "conv_bwd: x pixel stride %d < %d", x_cs, gf.Cg);
+    const int rows_w = dl4j_round_up(d->c_out, 128);
+    int splits;
+    if (tcore) splits = conv_tc_wgrad_splits(ctx, gf, d->c_out);
+    else {
+        int tiles = dl4j_ceil_div(gf.Kp, 64) * dl4j_ceil_div(rows_w, 64);
+        splits = dl4j_ceil_div(4 * ctx->sm_count, tiles);
+        int maxs = dl4j_ceil_div(gf.M, 256);
+        if (splits > maxs) splits = maxs;
+        if (splits < 1) splits = 1;
+    }
+    // ---- data gradient operand sizes (computed first so that one scratch request covers everything)
+    ConvGeom gb = conv_geom_bwd_data(d, delta_cs);
+    const int rows_b = dx ? dl4j_round_up(dx_cs > d->c_in ? dx_cs : d->c_in, 128) : 0;
+    const int nblk = gf.M < 4096 ? 1 : (gf.M / 1024 > ctx->sm_count * 4 ? ctx->sm_count * 4 : gf.M / 1024);
+    size_t part_f = (size_t)splits * rows_w * gf.Kp, pack_f = (size_t)rows_b * gb.Kp, col_f = (size_t)nblk * delta_cs;
+    float *ws = (float *)dl4j_workspace(ctx, 0, (part_f + pack_f + col_f) * sizeof(float));
+    if (!ws) return DL4JB200_ERR_CUDA;
+    float *partial = ws, *wb = ws + part_f, *colp = wb + pack_f;
+
+    if (tcore) rc = conv_tc_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
+    else rc = conv_ffma_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
+    if (rc) return rc;
+    k_wgrad_finalize<<<grid_for(ctx, (size_t)d->c_out * d->c_in * gf.taps), 256, 0, ctx->stream>>>(
+        partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w, splits);
+    DL4J_CHECK_LAUNCH();
+
+    if (db) {
+        k_colsum_partial<<<nblk, 256, 0, ctx->stream>>>(ds, colp, gf.M, delta_cs);
+        DL4J_CHECK_LAUNCH();
+        k_colsum_final<<<dl4j_ceil_div(d->c_out, 128), 128, 0, ctx->stream>>>(colp, db, nblk, delta_cs, d->c_out);
+        DL4J_CHECK_LAUNCH();
+    }
+
+    if (dx) {
+        DL4J_REQUIRE(delta_cs >= gb.Cg, "conv_bwd: delta pixel stride %d < %d", delta_cs, gb.Cg);
+        k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, tcore);
+        DL4J_CHECK_LAUNCH();
+        if (tcore) rc = conv_tc_gemm(ctx, gb, ds, wb, rows_b, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);
+        else rc = conv_ffma_gemm(ctx, gb, ds, wb, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);
+        if (rc) return rc;
+        if (dx_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, dxs, dx, d->batch, d->c_in, d->in_h, d->in_w, dx_cs);
+    }
+    return DL4JB200_OK;
+}
+
+}  // extern "C"

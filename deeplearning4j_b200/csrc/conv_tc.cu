@@ -1,0 +1,425 @@
+// TF32 tensor-core implicit-GEMM convolution for sm_100a: tcgen05.mma with the accumulator in TMEM,
+// operands staged in 128-byte-swizzled shared memory through a multi-stage mbarrier pipeline.
+//
+// Warp roles per CTA (160 threads): warps 0-3 gather operand tiles (16-byte cp.async with zero-fill for
+// padding / stride holes / ragged edges -- the im2col matrix is never materialised) and later run the
+// epilogue (tcgen05.ld -> bias + activation -> global); warp 4 allocates TMEM and its lane 0 issues the MMAs.
+// Two CTAs fit per SM (<= 100 KB smem, <= 128 TMEM columns each) so one CTA's epilogue overlaps the
+// other's main loop.
+//
+//   k_conv_tc_gemm : forward / backprop-data.  D[128 pixels, BN channels] += A[128, 32] * B[BN, 32]^T,
+//                    both operands K-major (a row = 32 consecutive K values = 128 bytes).
+//   k_conv_tc_wgrad: backprop-filter. D[128 co, BN k] += delta[32 px, 128 co]^T * im2col[32 px, BN k]:
+//                    the reduction runs over pixels, so both operands are MN-major (a row = 32 consecutive
+//                    M/N values of one pixel); split over pixel ranges, partials reduced by conv.cu.
+#include "conv_common.cuh"
+
+namespace tc {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 32;  // fp32 elements: one 128-byte swizzle row
+constexpr int PRODUCERS = 128;
+constexpr int THREADS = 160;
+constexpr int LOOKAHEAD = 2;  // k-chunks in flight per producer thread beyond the one being published
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// Bounded wait: a protocol bug must surface as a CUDA error, never as a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (mbar_try(bar, parity)) return;
+    long long t0 = clock64();
+    uint32_t spins = 0;
+    while (!mbar_try(bar, parity)) {
+        if ((++spins & 1023u) == 0 && clock64() - t0 > 6000000000LL) {
+            printf("dl4jb200: mbarrier wait timed out (block %d,%d thread %d)\n", blockIdx.x, blockIdx.y, threadIdx.x);
+            __trap();
+        }
+    }
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "n"(COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns: thread i of the warp receives row (lane base + i)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+}
+
+// UMMA shared-memory descriptor, 128-byte swizzle (cute/arch/mma_sm100_desc.hpp SmemDescriptor):
+// [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4, [46,48) version=1, [61,64) layout=2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
+           ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// Instruction descriptor (InstrDescriptor): c_format F32 [4,6)=1, a/b_format TF32 [7,10)=[10,13)=2,
+// a_major bit 15, b_major bit 16 (1 = MN-major), N>>3 at [17,23), M>>4 at [24,29)
+__host__ __device__ constexpr uint32_t umma_idesc(int M, int N, int a_mn, int b_mn) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+template <int BN, int STAGES>
+struct SmemLayout {
+    static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 4;  // 16 KB (gemm: 128 rows x 128 B; wgrad: 32 px x 512 B)
+    static constexpr int B_BYTES = BN * BLOCK_K * 4;
+    static constexpr int BAR_OFF = STAGES * (A_BYTES + B_BYTES);
+    static constexpr int BYTES = BAR_OFF + 256 + 1024;  // barriers + slack for 1024-byte alignment
+};
+
+// ------------------------------------------------------------------------------------------------
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restrict__ src, const float *__restrict__ wpack,
+                                                          const float *__restrict__ bias, float *__restrict__ out,
+                                                          ConvGeom g, int n_valid, int out_cs, int act) {
+    using L = SmemLayout<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    const uint32_t acc_bar = bar_base + 8u * (2 * STAGES), tmem_slot = bar_base + 8u * (2 * STAGES + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.x * BLOCK_M, n0 = blockIdx.y * BN;
+    const int num_k = g.Kp / BLOCK_K;
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), PRODUCERS); mbar_init(empty_bar(s), 1); }
+        mbar_init(acc_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) tmem_alloc<BN>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_d;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_d) : "r"(tmem_slot));
+
+    if (warp < 4) {
+        // ------------------------------ producers
+        const int j = tid & 7, rb = tid >> 3;
+        const uint32_t off0 = ((uint32_t)(rb >> 3) << 10) + ((uint32_t)(rb & 7) << 7) + ((uint32_t)(j ^ (rb & 7)) << 4);
+        int rowB[8], rowY[8], rowX[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            int m = m0 + rb + 16 * i;
+            if (m < g.M) conv_m_decode(g, m, rowB[i], rowY[i], rowX[i]);
+            else { rowB[i] = -1; rowY[i] = 0; rowX[i] = 0; }
+        }
+        const float *wrow = wpack + (size_t)(n0 + rb) * g.Kp + j * 4;
+        for (int it = 0; it < num_k + LOOKAHEAD; ++it) {
+            if (it < num_k) {
+                const int s = it % STAGES;
+                mbar_wait(empty_bar(s), ((it / STAGES) & 1) ^ 1);
+                int kh, kw, c; bool kvalid;
+                conv_k_decode(g, it * BLOCK_K + j * 4, kh, kw, c, kvalid);
+                const uint32_t a_dst = a_base + s * L::A_BYTES + off0;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    long long o = (kvalid && rowB[i] >= 0) ? conv_src_offset(g, rowB[i], rowY[i], rowX[i], kh, kw) : -1;
+                    const float *p = o >= 0 ? src + o + c : src;
+                    cp_async16(a_dst + i * 2048u, p, o >= 0 ? 16u : 0u);
+                }
+                const uint32_t b_dst = b_base + s * L::B_BYTES + off0;
+#pragma unroll
+                for (int i = 0; i < BN / 16; i++)
+                    cp_async16(b_dst + i * 2048u, wrow + (size_t)(16 * i) * g.Kp + (size_t)it * BLOCK_K, 16u);
+            }
+            cp_async_commit();
+            if (it >= LOOKAHEAD) {
+                cp_async_wait<LOOKAHEAD>();
+                fence_proxy_async();
+                mbar_arrive(full_bar((it - LOOKAHEAD) % STAGES));
+            }
+        }
+        // ------------------------------ epilogue: thread = one output pixel row, 32 channels per TMEM load
+        mbar_wait(acc_bar, 0);
+        tc_fence_after();
+        const int m = m0 + warp * 32 + lane;
+        float *orow = out + (size_t)m * out_cs;
+#pragma unroll 1
+        for (int cb = 0; cb < BN / 32; cb++) {
+            float v[32];
+            tmem_ld32(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cb * 32), v);
+            const int nb = n0 + cb * 32;
+            if (m < g.M) {
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const int n = nb + q * 4;
+                    if (n < out_cs) {
+                        float r[4];
+#pragma unroll
+                        for (int e = 0; e < 4; e++) {
+                            const int nn = n + e;
+                            r[e] = nn < n_valid ? dl4j_act(v[q * 4 + e] + (bias ? __ldg(bias + nn) : 0.f), act) : 0.f;
+                        }
+                        *reinterpret_cast<float4 *>(orow + n) = make_float4(r[0], r[1], r[2], r[3]);
+                    }
+                }
+            }
+        }
+    } else {
+        // ------------------------------ MMA issuer
+        constexpr uint32_t idesc = umma_idesc(BLOCK_M, BN, 0, 0);
+        for (int it = 0; it < num_k; ++it) {
+            const int s = it % STAGES;
+            mbar_wait(full_bar(s), (it / STAGES) & 1);
+            tc_fence_after();
+            if (lane == 0) {
+                const uint64_t ad = umma_desc(a_base + s * L::A_BYTES, 16, 1024);
+                const uint64_t bd = umma_desc(b_base + s * L::B_BYTES, 16, 1024);
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / 8; k++)  // UMMA_K = 8 tf32 = 32 bytes = +2 in the address field
+                    umma_tf32(tmem_d, ad + 2u * k, bd + 2u * k, idesc, (it | k) ? 1u : 0u);
+                umma_commit(empty_bar(s));
+            }
+            __syncwarp();
+        }
+        if (lane == 0) umma_commit(acc_bar);
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc<BN>(tmem_d);
+}
+
+// ------------------------------------------------------------------------------------------------
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restrict__ x, const float *__restrict__ delta,
+                                                           float *__restrict__ partial, ConvGeom g, int delta_cs,
+                                                           int rows_p, int m_per_split, int k_tiles) {
+    using L = SmemLayout<BN, STAGES>;
+    constexpr int NB_ATOMS = BN / 32;  // 32-float MN atoms across the im2col tile
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    const uint32_t acc_bar = bar_base + 8u * (2 * STAGES), tmem_slot = bar_base + 8u * (2 * STAGES + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int kt = blockIdx.x % k_tiles, ct = blockIdx.x / k_tiles;
+    const int kcol0 = kt * BN, co0 = ct * BLOCK_M;
+    const int ms = blockIdx.y * m_per_split, me = min(g.M, ms + m_per_split);
+    const int num_k = (me - ms + BLOCK_K - 1) / BLOCK_K;  // >= 1 by construction of the split count
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), PRODUCERS); mbar_init(empty_bar(s), 1); }
+        mbar_init(acc_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) tmem_alloc<BN>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_d;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_d) : "r"(tmem_slot));
+
+    if (warp < 4) {
+        // A' = delta[px, co0 .. co0+127]: 32 pieces per pixel row, 4 rows per pass, 8 passes
+        const int pa = tid & 31, ra = tid >> 5;
+        const bool a_col_ok = co0 + pa * 4 < delta_cs;
+        // B' = im2col[px, kcol0 .. kcol0+BN-1]: BN/4 pieces per row
+        constexpr int PPR = BN / 4, RPP = PRODUCERS / PPR, PASSES = BLOCK_K / RPP;
+        const int pb = tid % PPR, rbb = tid / PPR;
+        int kh, kw, c; bool kvalid;
+        conv_k_decode(g, kcol0 + pb * 4, kh, kw, c, kvalid);
+        kvalid = kvalid && (kcol0 + pb * 4) < g.Kp;
+        for (int it = 0; it < num_k + LOOKAHEAD; ++it) {
+            if (it < num_k) {
+                const int s = it % STAGES;
+                mbar_wait(empty_bar(s), ((it / STAGES) & 1) ^ 1);
+                const int mrow0 = ms + it * BLOCK_K;
+                const uint32_t a_stage = a_base + s * L::A_BYTES, b_stage = b_base + s * L::B_BYTES;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const int r = ra + 4 * i, m = mrow0 + r;
+                    const bool ok = a_col_ok && m < me;
+                    const uint32_t dst = a_stage + (uint32_t)(((r >> 3) * 4 + (pa >> 3)) << 10) + ((uint32_t)(r & 7) << 7) +
+                                         ((uint32_t)((pa & 7) ^ (r & 7)) << 4);
+                    cp_async16(dst, ok ? delta + (size_t)m * delta_cs + co0 + pa * 4 : delta, ok ? 16u : 0u);
+                }
+#pragma unroll
+                for (int i = 0; i < PASSES; i++) {
+                    const int r = rbb + RPP * i, m = mrow0 + r;
+                    long long o = -1;
+                    if (kvalid && m < me) {
+                        int b, y0, x0;
+                        conv_m_decode(g, m, b, y0, x0);
+                        o = conv_src_offset(g, b, y0, x0, kh, kw);
+                    }
+                    const uint32_t dst = b_stage + (uint32_t)(((r >> 3) * NB_ATOMS + (pb >> 3)) << 10) +
+                                         ((uint32_t)(r & 7) << 7) + ((uint32_t)((pb & 7) ^ (r & 7)) << 4);
+                    cp_async16(dst, o >= 0 ? x + o + c : x, o >= 0 ? 16u : 0u);
+                }
+            }
+            cp_async_commit();
+            if (it >= LOOKAHEAD) {
+                cp_async_wait<LOOKAHEAD>();
+                fence_proxy_async();
+                mbar_arrive(full_bar((it - LOOKAHEAD) % STAGES));
+            }
+        }
+        mbar_wait(acc_bar, 0);
+        tc_fence_after();
+        const int co = co0 + warp * 32 + lane;
+        float *prow = partial + ((size_t)blockIdx.y * rows_p + co) * g.Kp;
+#pragma unroll 1
+        for (int cb = 0; cb < BN / 32; cb++) {
+            float v[32];
+            tmem_ld32(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cb * 32), v);
+            if (co < rows_p) {
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const int k = kcol0 + cb * 32 + q * 4;
+                    if (k < g.Kp) *reinterpret_cast<float4 *>(prow + k) = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+                }
+            }
+        }
+    } else {
+        constexpr uint32_t idesc = umma_idesc(BLOCK_M, BN, 1, 1);
+        for (int it = 0; it < num_k; ++it) {
+            const int s = it % STAGES;
+            mbar_wait(full_bar(s), (it / STAGES) & 1);
+            tc_fence_after();
+            if (lane == 0) {
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / 8; k++) {  // one 8-pixel group per MMA
+                    const uint64_t ad = umma_desc(a_base + s * L::A_BYTES + k * 4 * 1024, 1024, 4 * 1024);
+                    const uint64_t bd = umma_desc(b_base + s * L::B_BYTES + k * NB_ATOMS * 1024, 1024, NB_ATOMS * 1024);
+                    umma_tf32(tmem_d, ad, bd, idesc, (it | k) ? 1u : 0u);
+                }
+                umma_commit(empty_bar(s));
+            }
+            __syncwarp();
+        }
+        if (lane == 0) umma_commit(acc_bar);
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc<BN>(tmem_d);
+}
+
+template <int BN, int STAGES>
+static int launch_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, const float *bias,
+                       float *out, int n_valid, int out_cs, int act) {
+    using L = SmemLayout<BN, STAGES>;
+    auto kern = k_conv_tc_gemm<BN, STAGES>;
+    static bool configured[16] = {false};
+    if (!configured[ctx->device & 15]) {
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        configured[ctx->device & 15] = true;
+    }
+    dim3 grid(dl4j_ceil_div(g.M, BLOCK_M), dl4j_ceil_div(out_cs, BN));
+    kern<<<grid, THREADS, L::BYTES, ctx->stream>>>(src, wpack, bias, out, g, n_valid, out_cs, act);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+template <int BN, int STAGES>
+static int launch_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const float *delta, int delta_cs,
+                        float *partial, int rows_p, int splits, int m_per_split) {
+    using L = SmemLayout<BN, STAGES>;
+    auto kern = k_conv_tc_wgrad<BN, STAGES>;
+    static bool configured[16] = {false};
+    if (!configured[ctx->device & 15]) {
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        configured[ctx->device & 15] = true;
+    }
+    int k_tiles = dl4j_ceil_div(g.Kp, BN), c_tiles = dl4j_ceil_div(rows_p, BLOCK_M);
+    dim3 grid(k_tiles * c_tiles, splits);
+    kern<<<grid, THREADS, L::BYTES, ctx->stream>>>(x, delta, partial, g, delta_cs, rows_p, m_per_split, k_tiles);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+static inline int wgrad_bn(const ConvGeom &g) { return g.Kp >= 128 ? 128 : (g.Kp >= 64 ? 64 : 32); }
+
+}  // namespace tc
+
+int conv_tc_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
+                 const float *bias, float *out, int n_valid, int out_cs, int act) {
+    (void)n_rows_packed;
+    if (out_cs > 64) return tc::launch_gemm<128, 3>(ctx, g, src, wpack, bias, out, n_valid, out_cs, act);
+    if (out_cs > 32) return tc::launch_gemm<64, 4>(ctx, g, src, wpack, bias, out, n_valid, out_cs, act);
+    return tc::launch_gemm<32, 4>(ctx, g, src, wpack, bias, out, n_valid, out_cs, act);
+}
+
+// number of pixel-range splits: enough CTAs for ~2 waves, every split non-empty
+int conv_tc_wgrad_splits(dl4jb200_ctx *ctx, const ConvGeom &g, int c_out) {
+    int bn = tc::wgrad_bn(g);
+    int tiles = dl4j_ceil_div(g.Kp, bn) * dl4j_ceil_div(c_out, tc::BLOCK_M);
+    int want = dl4j_ceil_div(2 * ctx->sm_count, tiles);
+    int max_splits = dl4j_ceil_div(g.M, 8 * tc::BLOCK_K);  // at least 8 k-chunks per split
+    if (want > max_splits) want = max_splits;
+    if (want < 1) want = 1;
+    int mps = dl4j_round_up(dl4j_ceil_div(g.M, want), tc::BLOCK_K);
+    return dl4j_ceil_div(g.M, mps);
+}
+
+int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const float *delta, int delta_cs, int c_out,
+                  float *partial, int rows_p, int splits) {
+    (void)c_out;
+    int mps = dl4j_round_up(dl4j_ceil_div(g.M, splits), tc::BLOCK_K);
+    if (dl4j_ceil_div(g.M, mps) != splits) {
+        dl4j_set_error("conv_tc_wgrad: split count %d leaves an empty split (M=%d)", splits, g.M);
+        return DL4JB200_ERR_INVALID_ARG;
+    }
+    switch (tc::wgrad_bn(g)) {
+    case 128: return tc::launch_wgrad<128, 3>(ctx, g, x, delta, delta_cs, partial, rows_p, splits, mps);
+    case 64: return tc::launch_wgrad<64, 4>(ctx, g, x, delta, delta_cs, partial, rows_p, splits, mps);
+    default: return tc::launch_wgrad<32, 4>(ctx, g, x, delta, delta_cs, partial, rows_p, splits, mps);
+    }
+}

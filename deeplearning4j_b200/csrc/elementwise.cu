@@ -1,0 +1,270 @@
+// HBM-bandwidth kernels without reductions: re-layout, activations, residual add, epsilon fan-in,
+// softmax-NLL output delta, updater. All vectorised 128-bit where alignment allows; grids are sized
+// in multiples of the SM count with a grid-stride loop.
+#include "common.cuh"
+
+static inline int ew_grid(dl4jb200_ctx *ctx, size_t work_items, int threads) {
+    size_t blocks = (work_items + threads - 1) / threads;
+    size_t cap = (size_t)ctx->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+// ---------------------------------------------------------------- NCHW <-> NHWC
+// One block transposes a 32(channels) x 32(pixels) tile of one image through shared memory so that both
+// the global read (contiguous pixels) and the global write (contiguous channels) are coalesced.
+__global__ void __launch_bounds__(256) k_nchw_to_nhwc(const float *__restrict__ src, float *__restrict__ dst, int C,
+                                                      int HW, int cs) {
+    __shared__ float tile[32][33];
+    int b = blockIdx.z;
+    int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const float *s = src + (size_t)b * C * HW;
+    float *d = dst + (size_t)b * HW * cs;
+    int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int c = c0 + ty + i * 8, p = p0 + tx;
+        tile[ty + i * 8][tx] = (c < C && p < HW) ? s[(size_t)c * HW + p] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int p = p0 + ty + i * 8, c = c0 + tx;
+        if (p < HW && c < cs) d[(size_t)p * cs + c] = tile[tx][ty + i * 8];
+    }
+}
+
+__global__ void __launch_bounds__(256) k_nhwc_to_nchw(const float *__restrict__ src, float *__restrict__ dst, int C,
+                                                      int HW, int cs) {
+    __shared__ float tile[32][33];
+    int b = blockIdx.z;
+    int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const float *s = src + (size_t)b * HW * cs;
+    float *d = dst + (size_t)b * C * HW;
+    int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int p = p0 + ty + i * 8, c = c0 + tx;
+        tile[ty + i * 8][tx] = (p < HW && c < C) ? s[(size_t)p * cs + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int c = c0 + ty + i * 8, p = p0 + tx;
+        if (c < C && p < HW) d[(size_t)c * HW + p] = tile[tx][ty + i * 8];
+    }
+}
+
+// ---------------------------------------------------------------- activations
+template <bool VEC>
+__global__ void __launch_bounds__(256) k_act_fwd(const float *__restrict__ z, float *__restrict__ a, size_t n, int act) {
+    size_t stride = (size_t)gridDim.x * blockDim.x, i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (VEC) {
+        size_t n4 = n >> 2;
+        for (; i < n4; i += stride) {
+            float4 v = reinterpret_cast<const float4 *>(z)[i];
+            v.x = dl4j_act(v.x, act); v.y = dl4j_act(v.y, act); v.z = dl4j_act(v.z, act); v.w = dl4j_act(v.w, act);
+            reinterpret_cast<float4 *>(a)[i] = v;
+        }
+    } else {
+        for (; i < n; i += stride) a[i] = dl4j_act(z[i], act);
+    }
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256) k_act_bwd(const float *__restrict__ z, const float *__restrict__ e,
+                                                 float *__restrict__ d, size_t n, int act) {
+    size_t stride = (size_t)gridDim.x * blockDim.x, i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (VEC) {
+        size_t n4 = n >> 2;
+        for (; i < n4; i += stride) {
+            float4 v = reinterpret_cast<const float4 *>(z)[i], g = reinterpret_cast<const float4 *>(e)[i];
+            g.x *= dl4j_act_grad(v.x, act); g.y *= dl4j_act_grad(v.y, act);
+            g.z *= dl4j_act_grad(v.z, act); g.w *= dl4j_act_grad(v.w, act);
+            reinterpret_cast<float4 *>(d)[i] = g;
+        }
+    } else {
+        for (; i < n; i += stride) d[i] = e[i] * dl4j_act_grad(z[i], act);
+    }
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256) k_add_act(const float *__restrict__ a, const float *__restrict__ b,
+                                                 float *__restrict__ o, size_t n, int act) {
+    size_t stride = (size_t)gridDim.x * blockDim.x, i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (VEC) {
+        size_t n4 = n >> 2;
+        for (; i < n4; i += stride) {
+            float4 x = reinterpret_cast<const float4 *>(a)[i], y = reinterpret_cast<const float4 *>(b)[i];
+            x.x = dl4j_act(x.x + y.x, act); x.y = dl4j_act(x.y + y.y, act);
+            x.z = dl4j_act(x.z + y.z, act); x.w = dl4j_act(x.w + y.w, act);
+            reinterpret_cast<float4 *>(o)[i] = x;
+        }
+    } else {
+        for (; i < n; i += stride) o[i] = dl4j_act(a[i] + b[i], act);
+    }
+}
+
+static inline bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
+
+// ---------------------------------------------------------------- softmax + NLL (one warp per row)
+__global__ void __launch_bounds__(256) k_softmax_nll(const float *__restrict__ z, const float *__restrict__ labels,
+                                                     float *__restrict__ delta, float *loss_rows, int B, int K) {
+    int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= B) return;
+    const float *zr = z + (size_t)row * K;
+    const float *lr = labels + (size_t)row * K;
+    float m = -INFINITY;
+    for (int k = lane; k < K; k += 32) m = fmaxf(m, zr[k]);
+    for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    float s = 0.f;
+    for (int k = lane; k < K; k += 32) s += expf(zr[k] - m);
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    float logs = logf(s), loss = 0.f, inv = 1.f / s;
+    for (int k = lane; k < K; k += 32) {
+        float zz = zr[k] - m, l = lr[k];
+        delta[(size_t)row * K + k] = expf(zz) * inv - l;
+        if (l != 0.f) loss -= l * (zz - logs);
+    }
+    for (int o = 16; o; o >>= 1) loss += __shfl_xor_sync(0xffffffffu, loss, o);
+    if (lane == 0) loss_rows[row] = loss;
+}
+
+// deterministic single-block sum of the per-row losses
+__global__ void __launch_bounds__(256) k_sum_rows(const float *__restrict__ v, float *out, int n) {
+    __shared__ double sm[256];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256) acc += (double)v[i];
+    sm[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o; o >>= 1) {
+        if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[0] = (float)sm[0];
+}
+
+// ---------------------------------------------------------------- updater (UpdaterBlock.java:142,170-193)
+__global__ void __launch_bounds__(256) k_updater(float *__restrict__ w, const float *__restrict__ g,
+                                                 float *__restrict__ state, size_t n, int kind, float lr, float h1,
+                                                 float h2, float l1, float l2, float inv_batch) {
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float gi = g[i], wi = w[i], u;
+        switch (kind) {
+        case DL4JB200_UPD_NESTEROVS: {
+            float v = state[i], vn = h1 * v - lr * gi;
+            u = h1 * v - (1.f + h1) * vn;
+            state[i] = vn;
+        } break;
+        case DL4JB200_UPD_RMSPROP: {
+            float c = h1 * state[i] + (1.f - h1) * gi * gi;
+            state[i] = c;
+            u = lr * gi / sqrtf(c + h2);
+        } break;
+        case DL4JB200_UPD_ADADELTA: {
+            float msg = h1 * state[i] + (1.f - h1) * gi * gi, msdx = state[n + i];
+            u = gi * sqrtf(msdx + h2) / sqrtf(msg + h2);
+            state[i] = msg;
+            state[n + i] = h1 * msdx + (1.f - h1) * u * u;
+        } break;
+        case DL4JB200_UPD_NOOP: u = 0.f; break;
+        default: u = lr * gi;
+        }
+        if (l2 > 0.f) u += l2 * wi;
+        if (l1 > 0.f) u += l1 * (wi > 0.f ? 1.f : (wi < 0.f ? -1.f : 0.f));
+        w[i] = wi - u * inv_batch;
+    }
+}
+
+extern "C" {
+
+int dl4jb200_nchw_to_nhwc(dl4jb200_ctx *ctx, const float *src, float *dst, int B, int C, int H, int W, int cs) {
+    DL4J_REQUIRE(ctx && src && dst, "nchw_to_nhwc: NULL argument");
+    DL4J_REQUIRE(cs >= C && B > 0 && C > 0 && H > 0 && W > 0, "nchw_to_nhwc: bad shape");
+    DL4J_REQUIRE(B <= 65535, "nchw_to_nhwc: batch > 65535");
+    int HW = H * W;
+    dim3 grid(dl4j_ceil_div(HW, 32), dl4j_ceil_div(cs, 32), B);
+    k_nchw_to_nhwc<<<grid, 256, 0, ctx->stream>>>(src, dst, C, HW, cs);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_nhwc_to_nchw(dl4jb200_ctx *ctx, const float *src, float *dst, int B, int C, int H, int W, int cs) {
+    DL4J_REQUIRE(ctx && src && dst, "nhwc_to_nchw: NULL argument");
+    DL4J_REQUIRE(cs >= C && B > 0 && C > 0 && H > 0 && W > 0, "nhwc_to_nchw: bad shape");
+    DL4J_REQUIRE(B <= 65535, "nhwc_to_nchw: batch > 65535");
+    int HW = H * W;
+    dim3 grid(dl4j_ceil_div(HW, 32), dl4j_ceil_div(C, 32), B);
+    k_nhwc_to_nchw<<<grid, 256, 0, ctx->stream>>>(src, dst, C, HW, cs);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_act_fwd(dl4jb200_ctx *ctx, const float *z, float *a, size_t n, int act) {
+    DL4J_REQUIRE(ctx && z && a, "act_fwd: NULL argument");
+    if (act < 0 || act > DL4JB200_ACT_LEAKYRELU) { dl4j_set_error("act_fwd: activation %d not handled by the helper", act); return DL4JB200_NOT_SUPPORTED; }
+    if (n == 0) return DL4JB200_OK;
+    if ((n & 3) == 0 && aligned16(z) && aligned16(a))
+        k_act_fwd<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(z, a, n, act);
+    else
+        k_act_fwd<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(z, a, n, act);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_act_bwd(dl4jb200_ctx *ctx, const float *z, const float *eps, float *delta, size_t n, int act) {
+    DL4J_REQUIRE(ctx && z && eps && delta, "act_bwd: NULL argument");
+    if (act < 0 || act > DL4JB200_ACT_LEAKYRELU) { dl4j_set_error("act_bwd: activation %d not handled by the helper", act); return DL4JB200_NOT_SUPPORTED; }
+    if (n == 0) return DL4JB200_OK;
+    if ((n & 3) == 0 && aligned16(z) && aligned16(eps) && aligned16(delta))
+        k_act_bwd<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(z, eps, delta, n, act);
+    else
+        k_act_bwd<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(z, eps, delta, n, act);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_add_act_fwd(dl4jb200_ctx *ctx, const float *a, const float *b, float *out, size_t n, int act) {
+    DL4J_REQUIRE(ctx && a && b && out, "add_act_fwd: NULL argument");
+    if (n == 0) return DL4JB200_OK;
+    if ((n & 3) == 0 && aligned16(a) && aligned16(b) && aligned16(out))
+        k_add_act<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(a, b, out, n, act);
+    else
+        k_add_act<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(a, b, out, n, act);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_accumulate(dl4jb200_ctx *ctx, float *dst, const float *src, size_t n) {
+    return dl4jb200_add_act_fwd(ctx, dst, src, dst, n, DL4JB200_ACT_IDENTITY);
+}
+
+int dl4jb200_softmax_nll(dl4jb200_ctx *ctx, const float *z, const float *labels, float *delta, float *loss_sum_out,
+                         int B, int K) {
+    DL4J_REQUIRE(ctx && z && labels && delta && loss_sum_out, "softmax_nll: NULL argument");
+    DL4J_REQUIRE(B > 0 && K > 0, "softmax_nll: bad shape");
+    float *rows = (float *)dl4j_workspace(ctx, 0, (size_t)B * sizeof(float));
+    if (!rows) return DL4JB200_ERR_CUDA;
+    k_softmax_nll<<<dl4j_ceil_div(B, 8), 256, 0, ctx->stream>>>(z, labels, delta, rows, B, K);
+    DL4J_CHECK_LAUNCH();
+    k_sum_rows<<<1, 256, 0, ctx->stream>>>(rows, loss_sum_out, B);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_updater_apply(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n, int kind, double lr,
+                           double h1, double h2, double l1, double l2, double batch_div) {
+    DL4J_REQUIRE(ctx && w && g, "updater_apply: NULL argument");
+    DL4J_REQUIRE(kind >= 0 && kind <= DL4JB200_UPD_NOOP, "updater_apply: unknown updater %d", kind);
+    DL4J_REQUIRE(state || kind == DL4JB200_UPD_SGD || kind == DL4JB200_UPD_NOOP, "updater_apply: state is NULL");
+    DL4J_REQUIRE(batch_div > 0, "updater_apply: batch_div must be positive");
+    if (n == 0) return DL4JB200_OK;
+    k_updater<<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(w, g, state, n, kind, (float)lr, (float)h1, (float)h2,
+                                                           (float)l1, (float)l2, (float)(1.0 / batch_div));
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+}  // extern "C"

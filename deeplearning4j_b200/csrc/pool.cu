@@ -1,0 +1,256 @@
+// Max / average / p-norm pooling forward and backward (SubsamplingLayer.java:112-268, 285-363).
+// Bandwidth kernels: one thread per output element (NCHW, coalesced along W) or per 4 channels of one
+// output pixel (NHWC, 128-bit loads/stores along C). Backward is a GATHER over the windows that contain
+// an input cell -- no atomics, fixed summation order (kh, kw ascending), so results are deterministic and
+// the first-maximum tie-break of the reference's IsMax (SubsamplingLayerTest.java:85-101) is bit-exact.
+#include <float.h>
+
+#include "common.cuh"
+
+struct PoolGeom {
+    int B, C, H, W, Ho, Wo, kH, kW, sH, sW, pT, pL, dH, dW;
+    int xcs, ycs;  // NHWC pixel strides
+};
+
+template <int V>
+struct Vec {
+    float v[V];
+};
+template <int V>
+__device__ __forceinline__ Vec<V> vload(const float *p) {
+    Vec<V> r;
+    if (V == 4) {
+        float4 t = *reinterpret_cast<const float4 *>(p);
+        r.v[0] = t.x; r.v[1 % V] = t.y; r.v[2 % V] = t.z; r.v[3 % V] = t.w;
+    } else {
+        r.v[0] = *p;
+    }
+    return r;
+}
+template <int V>
+__device__ __forceinline__ void vstore(float *p, const Vec<V> &r) {
+    if (V == 4) *reinterpret_cast<float4 *>(p) = make_float4(r.v[0], r.v[1 % V], r.v[2 % V], r.v[3 % V]);
+    else *p = r.v[0];
+}
+template <int V>
+__device__ __forceinline__ void vstore_i(int32_t *p, const int (&r)[V]) {
+    if (V == 4) *reinterpret_cast<int4 *>(p) = make_int4(r[0], r[1 % V], r[2 % V], r[3 % V]);
+    else *p = r[0];
+}
+
+// NHWC: V = 4, a work item is (b, y, x, channel quad). NCHW: V = 1, a work item is (b, c, y, x).
+template <bool NHWC>
+__device__ __forceinline__ void decode(size_t idx, int C, int Hh, int Ww, int cs, int &b, int &c, int &y, int &x) {
+    if (NHWC) {
+        int Q = cs >> 2;
+        c = (int)(idx % Q) * 4; idx /= Q;
+        x = (int)(idx % Ww); idx /= Ww;
+        y = (int)(idx % Hh); b = (int)(idx / Hh);
+    } else {
+        x = (int)(idx % Ww); idx /= Ww;
+        y = (int)(idx % Hh); idx /= Hh;
+        c = (int)(idx % C); b = (int)(idx / C);
+    }
+}
+template <bool NHWC>
+__device__ __forceinline__ size_t offs(int b, int c, int y, int x, int C, int Hh, int Ww, int cs) {
+    return NHWC ? (((size_t)b * Hh + y) * Ww + x) * cs + c : (((size_t)b * C + c) * Hh + y) * Ww + x;
+}
+
+template <bool NHWC>
+__global__ void __launch_bounds__(256) k_pool_fwd(const float *__restrict__ x, float *__restrict__ y,
+                                                  int32_t *__restrict__ argmax, PoolGeom g, int type, int pnorm,
+                                                  size_t total) {
+    constexpr int V = NHWC ? 4 : 1;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+        int b, c, oh, ow;
+        decode<NHWC>(idx, g.C, g.Ho, g.Wo, g.ycs, b, c, oh, ow);
+        float acc[V];
+        int best[V];
+#pragma unroll
+        for (int i = 0; i < V; i++) { acc[i] = type == DL4JB200_POOL_MAX ? -FLT_MAX : 0.f; best[i] = 0; }
+        for (int kh = 0; kh < g.kH; kh++) {
+            int ih = oh * g.sH - g.pT + kh * g.dH;
+            if (ih < 0 || ih >= g.H) continue;  // padding: -FLT_MAX for max (never wins), 0 for sums
+            for (int kw = 0; kw < g.kW; kw++) {
+                int iw = ow * g.sW - g.pL + kw * g.dW;
+                if (iw < 0 || iw >= g.W) continue;
+                Vec<V> v = vload<V>(x + offs<NHWC>(b, c, ih, iw, g.C, g.H, g.W, g.xcs));
+#pragma unroll
+                for (int i = 0; i < V; i++) {
+                    if (type == DL4JB200_POOL_MAX) {
+                        if (v.v[i] > acc[i]) { acc[i] = v.v[i]; best[i] = kh * g.kW + kw; }
+                    } else if (type == DL4JB200_POOL_PNORM) {
+                        acc[i] += powf(fabsf(v.v[i]), (float)pnorm);
+                    } else {
+                        acc[i] += v.v[i];
+                    }
+                }
+            }
+        }
+        Vec<V> out;
+#pragma unroll
+        for (int i = 0; i < V; i++) {
+            if (type == DL4JB200_POOL_AVG) out.v[i] = acc[i] / (float)(g.kH * g.kW);
+            else if (type == DL4JB200_POOL_PNORM) out.v[i] = powf(acc[i], 1.f / (float)pnorm);
+            else out.v[i] = acc[i];
+        }
+        size_t o = offs<NHWC>(b, c, oh, ow, g.C, g.Ho, g.Wo, g.ycs);
+        vstore<V>(y + o, out);
+        if (argmax && type == DL4JB200_POOL_MAX) vstore_i<V>(argmax + o, best);
+    }
+}
+
+template <bool NHWC>
+__global__ void __launch_bounds__(256) k_pool_bwd(const float *__restrict__ x, const float *__restrict__ y,
+                                                  const float *__restrict__ eps, const int32_t *__restrict__ argmax,
+                                                  float *__restrict__ dx, PoolGeom g, int type, int pnorm,
+                                                  float pnorm_eps, size_t total) {
+    constexpr int V = NHWC ? 4 : 1;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+        int b, c, h, w;
+        decode<NHWC>(idx, g.C, g.H, g.W, g.xcs, b, c, h, w);
+        Vec<V> xv;
+        if (type != DL4JB200_POOL_AVG && !(type == DL4JB200_POOL_MAX && argmax))
+            xv = vload<V>(x + offs<NHWC>(b, c, h, w, g.C, g.H, g.W, g.xcs));
+        float acc[V];
+#pragma unroll
+        for (int i = 0; i < V; i++) acc[i] = 0.f;
+        for (int kh = 0; kh < g.kH; kh++) {
+            int t = h + g.pT - kh * g.dH;
+            if (t < 0 || t % g.sH) continue;
+            int oh = t / g.sH;
+            if (oh >= g.Ho) continue;
+            for (int kw = 0; kw < g.kW; kw++) {
+                int u = w + g.pL - kw * g.dW;
+                if (u < 0 || u % g.sW) continue;
+                int ow = u / g.sW;
+                if (ow >= g.Wo) continue;
+                size_t o = offs<NHWC>(b, c, oh, ow, g.C, g.Ho, g.Wo, g.ycs);
+                Vec<V> e = vload<V>(eps + o);
+                if (type == DL4JB200_POOL_AVG) {
+#pragma unroll
+                    for (int i = 0; i < V; i++) acc[i] += e.v[i];
+                } else if (type == DL4JB200_POOL_MAX) {
+                    if (argmax) {
+                        int me = kh * g.kW + kw;
+                        if (V == 4) {
+                            int4 a = *reinterpret_cast<const int4 *>(argmax + o);
+                            acc[0] += a.x == me ? e.v[0] : 0.f; acc[1 % V] += a.y == me ? e.v[1 % V] : 0.f;
+                            acc[2 % V] += a.z == me ? e.v[2 % V] : 0.f; acc[3 % V] += a.w == me ? e.v[3 % V] : 0.f;
+                        } else {
+                            acc[0] += argmax[o] == me ? e.v[0] : 0.f;
+                        }
+                    } else {
+                        // IsMax recomputed: this cell is the window's first maximum iff it is strictly greater
+                        // than every earlier cell (row-major) and >= every later one; padding cells are -FLT_MAX.
+                        bool win[V];
+#pragma unroll
+                        for (int i = 0; i < V; i++) win[i] = true;
+                        for (int k2 = 0; k2 < g.kH; k2++) {
+                            int ih = oh * g.sH - g.pT + k2 * g.dH;
+                            for (int k3 = 0; k3 < g.kW; k3++) {
+                                if (k2 == kh && k3 == kw) continue;
+                                int iw = ow * g.sW - g.pL + k3 * g.dW;
+                                bool inside = ih >= 0 && ih < g.H && iw >= 0 && iw < g.W;
+                                Vec<V> o2;
+                                if (inside) o2 = vload<V>(x + offs<NHWC>(b, c, ih, iw, g.C, g.H, g.W, g.xcs));
+                                bool earlier = (k2 * g.kW + k3) < (kh * g.kW + kw);
+#pragma unroll
+                                for (int i = 0; i < V; i++) {
+                                    float ov = inside ? o2.v[i] : -FLT_MAX;
+                                    win[i] = win[i] && (earlier ? (xv.v[i] > ov) : (xv.v[i] >= ov));
+                                }
+                            }
+                        }
+#pragma unroll
+                        for (int i = 0; i < V; i++) acc[i] += win[i] ? e.v[i] : 0.f;
+                    }
+                } else {  // PNORM: dx += eps * x|x|^(p-2) / max(y^(p-1), eps_p)   (SubsamplingLayer.java:225-250)
+                    Vec<V> yv = vload<V>(y + o);
+#pragma unroll
+                    for (int i = 0; i < V; i++) {
+                        float den = fmaxf(powf(yv.v[i], (float)(pnorm - 1)), pnorm_eps);
+                        acc[i] += e.v[i] * xv.v[i] * powf(fabsf(xv.v[i]), (float)(pnorm - 2)) / den;
+                    }
+                }
+            }
+        }
+        Vec<V> out;
+#pragma unroll
+        for (int i = 0; i < V; i++) out.v[i] = type == DL4JB200_POOL_AVG ? acc[i] / (float)(g.kH * g.kW) : acc[i];
+        vstore<V>(dx + offs<NHWC>(b, c, h, w, g.C, g.H, g.W, g.xcs), out);
+    }
+}
+
+static int pool_geom(const dl4jb200_conv_desc *d, int layout, int x_cs, int y_cs, PoolGeom &g, const char *who) {
+    DL4J_REQUIRE(d, "%s: desc is NULL", who);
+    DL4J_REQUIRE(d->batch > 0 && d->c_in > 0 && d->in_h > 0 && d->in_w > 0 && d->out_h > 0 && d->out_w > 0 &&
+                     d->k_h > 0 && d->k_w > 0 && d->stride_h > 0 && d->stride_w > 0 && d->dil_h > 0 && d->dil_w > 0,
+                 "%s: non-positive dimension in descriptor", who);
+    DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "%s: unknown layout %d", who, layout);
+    if (layout == DL4JB200_NHWC)
+        DL4J_REQUIRE(x_cs >= d->c_in && y_cs >= d->c_in && x_cs % 4 == 0 && y_cs % 4 == 0 && x_cs == y_cs,
+                     "%s: NHWC pixel strides must be equal multiples of 4 and >= C", who);
+    g = PoolGeom{d->batch, d->c_in, d->in_h, d->in_w, d->out_h, d->out_w, d->k_h, d->k_w, d->stride_h, d->stride_w,
+                 d->pad_top, d->pad_left, d->dil_h, d->dil_w, x_cs, y_cs};
+    return DL4JB200_OK;
+}
+
+static inline int pool_grid(dl4jb200_ctx *ctx, size_t total) {
+    size_t blocks = (total + 255) / 256, cap = (size_t)ctx->sm_count * 16;
+    return (int)(blocks > cap ? cap : (blocks ? blocks : 1));
+}
+
+extern "C" {
+
+int dl4jb200_pool_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, float *y, int32_t *argmax,
+                      int layout, int x_cs, int y_cs, int pool_type, int pnorm) {
+    DL4J_REQUIRE(ctx && x && y, "pool_fwd: NULL argument");
+    PoolGeom g;
+    int rc = pool_geom(d, layout, x_cs, y_cs, g, "pool_fwd");
+    if (rc) return rc;
+    DL4J_REQUIRE(pool_type >= DL4JB200_POOL_MAX && pool_type <= DL4JB200_POOL_PNORM, "pool_fwd: unknown pooling type %d", pool_type);
+    DL4J_REQUIRE(pool_type != DL4JB200_POOL_PNORM || pnorm >= 1, "pool_fwd: pnorm must be >= 1");
+    if (layout == DL4JB200_NHWC) {
+        size_t total = (size_t)g.B * g.Ho * g.Wo * (g.ycs / 4);
+        k_pool_fwd<true><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, argmax, g, pool_type, pnorm, total);
+    } else {
+        size_t total = (size_t)g.B * g.C * g.Ho * g.Wo;
+        k_pool_fwd<false><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, argmax, g, pool_type, pnorm, total);
+    }
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_pool_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, const float *y,
+                      const float *eps, const int32_t *argmax, float *dx, int layout, int x_cs, int y_cs,
+                      int pool_type, int pnorm, double pnorm_eps) {
+    DL4J_REQUIRE(ctx && eps && dx, "pool_bwd: NULL argument");
+    PoolGeom g;
+    int rc = pool_geom(d, layout, x_cs, y_cs, g, "pool_bwd");
+    if (rc) return rc;
+    if (pool_type == DL4JB200_POOL_SUM) {  // SubsamplingLayer.java:251-253 throws; the helper declines
+        dl4j_set_error("pool_bwd: SUM pooling has no backprop in the reference");
+        return DL4JB200_NOT_SUPPORTED;
+    }
+    DL4J_REQUIRE(pool_type == DL4JB200_POOL_MAX || pool_type == DL4JB200_POOL_AVG || pool_type == DL4JB200_POOL_PNORM,
+                 "pool_bwd: unknown pooling type %d", pool_type);
+    DL4J_REQUIRE(pool_type == DL4JB200_POOL_AVG || argmax || x, "pool_bwd: x is required when argmax is NULL");
+    DL4J_REQUIRE(pool_type != DL4JB200_POOL_PNORM || (x && y && pnorm >= 1), "pool_bwd: PNORM needs x, y and pnorm >= 1");
+    if (layout == DL4JB200_NHWC) {
+        size_t total = (size_t)g.B * g.H * g.W * (g.xcs / 4);
+        k_pool_bwd<true><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, eps, argmax, dx, g, pool_type, pnorm,
+                                                                         (float)pnorm_eps, total);
+    } else {
+        size_t total = (size_t)g.B * g.C * g.H * g.W;
+        k_pool_bwd<false><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, eps, argmax, dx, g, pool_type, pnorm,
+                                                                          (float)pnorm_eps, total);
+    }
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,220 @@
+/*
+ * dl4jb200.h -- C ABI of the B200-native back-end for Deeplearning4j's CNN layer helpers.
+ *
+ * This is the drop-in boundary: the four Java helper classes that DL4J's layers look up by
+ * reflection each marshal their INDArray arguments and make exactly one of the
+ * calls below (INTEGRATION.md shows the JavaCPP/JNI stubs). Paths cited are relative to
+ * /root/reference/deeplearning4j-nn/src/main/java/org/deeplearning4j/ ("NN/") unless noted.
+ *
+ * Conventions
+ *   - every function returns an int status: 0 OK; 1 NOT_SUPPORTED (Java helper returns null, the
+ *     layer runs its built-in path: NN/nn/layers/convolution/ConvolutionLayer.java:197-199,372-374);
+ *     <0 error (Java helper throws; conv/pool layers then fall back when cudnnAllowFallback,
+ *     ConvolutionLayer.java:189-196). dl4jb200_last_error() describes the last failure of the
+ *     calling thread.
+ *   - tensors are fp32. Every data pointer is a DEVICE pointer valid on the context's device
+ *     (obtained from dl4jb200_malloc, from the host-mirror registry, or from any other CUDA
+ *     allocator such as torch) unless the parameter name ends in _host.
+ *   - activations are rank 4, described by (B, C, H, W), a layout tag and, for NHWC, the pixel
+ *     stride in floats ("cs", >= C, multiple of 4; channels [C,cs) are padding and hold zeros).
+ *     NCHW is DL4J's layout ('c' order INDArray); NHWC is the resident layout the tensor-core
+ *     kernels consume. Functions taking a layout accept either and produce the same layout.
+ *   - work is enqueued on the context's stream and is asynchronous with respect to the host, as
+ *     the cuDNN helper is on nd4j's stream (deeplearning4j-cuda/.../CudnnConvolutionHelper.java:476-477).
+ *   - there is no CPU fallback anywhere behind this header.
+ */
+#ifndef DL4JB200_H
+#define DL4JB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DL4JB200_OK 0
+#define DL4JB200_NOT_SUPPORTED 1
+#define DL4JB200_ERR_INVALID_ARG (-1)
+#define DL4JB200_ERR_CUDA (-2)
+#define DL4JB200_ERR_INVALID_INPUT (-3)  /* DL4JInvalidInputException, NN/util/ConvolutionUtils.java:136-167 */
+#define DL4JB200_ERR_INVALID_CONFIG (-4) /* DL4JInvalidConfigException (Strict mode), ConvolutionUtils.java:169-211 */
+
+/* NN/nn/conf/ConvolutionMode.java */
+#define DL4JB200_MODE_STRICT 0
+#define DL4JB200_MODE_TRUNCATE 1
+#define DL4JB200_MODE_SAME 2
+
+#define DL4JB200_NCHW 0
+#define DL4JB200_NHWC 1
+
+/* NN/nn/conf/layers/PoolingType.java */
+#define DL4JB200_POOL_MAX 0
+#define DL4JB200_POOL_AVG 1
+#define DL4JB200_POOL_SUM 2
+#define DL4JB200_POOL_PNORM 3
+
+/* IActivation kinds the helper accepts (the cuDNN helper handles sigmoid/relu/tanh/identity,
+ * deeplearning4j-cuda/.../CudnnConvolutionHelper.java:527-558; anything else => NOT_SUPPORTED). */
+#define DL4JB200_ACT_IDENTITY 0
+#define DL4JB200_ACT_RELU 1
+#define DL4JB200_ACT_SIGMOID 2
+#define DL4JB200_ACT_TANH 3
+#define DL4JB200_ACT_LEAKYRELU 4
+
+/* convolution arithmetic: TF32 tensor cores with FP32 accumulate (throughput), or FP32 CUDA cores
+ * (parity mode, plays the role AlgoMode.NO_WORKSPACE plays in the reference's tests). */
+#define DL4JB200_CONV_ALGO_TC_TF32 0
+#define DL4JB200_CONV_ALGO_FP32 1
+
+/* IUpdater kinds on the flat parameter vector (NN/nn/updater/UpdaterBlock.java:115-193) */
+#define DL4JB200_UPD_SGD 0
+#define DL4JB200_UPD_NESTEROVS 1
+#define DL4JB200_UPD_RMSPROP 2
+#define DL4JB200_UPD_ADADELTA 3
+#define DL4JB200_UPD_NOOP 4
+
+typedef struct dl4jb200_ctx dl4jb200_ctx;
+
+/* Geometry of one conv / pooling call. out_h/out_w/pad_* are what dl4jb200_out_size returns for the
+ * layer's ConvolutionMode (pad_top/pad_left: ConvolutionLayer.java:148-150; the extra bottom/right cell
+ * of Same mode is implied by out_h/out_w). For pooling c_out is ignored. */
+typedef struct dl4jb200_conv_desc {
+    int32_t batch, c_in, in_h, in_w;
+    int32_t c_out, k_h, k_w;
+    int32_t stride_h, stride_w;
+    int32_t pad_top, pad_left;
+    int32_t dil_h, dil_w;
+    int32_t out_h, out_w;
+} dl4jb200_conv_desc;
+
+/* ------------------------------------------------------------------ runtime ------------------ */
+const char *dl4jb200_last_error(void);
+int dl4jb200_version(void);
+
+/* One context per (worker thread, device): ParallelWrapper pins each worker thread to one device for
+ * life (deeplearning4j-scaleout/.../parallelism/ParallelWrapper.java:125-141). stream == NULL makes the
+ * context create its own non-blocking stream; otherwise it enqueues on the caller's cudaStream_t. */
+int dl4jb200_ctx_create(int device, void *stream, dl4jb200_ctx **out);
+int dl4jb200_ctx_destroy(dl4jb200_ctx *ctx);
+int dl4jb200_ctx_set_stream(dl4jb200_ctx *ctx, void *stream);
+void *dl4jb200_ctx_stream(dl4jb200_ctx *ctx);
+int dl4jb200_ctx_sync(dl4jb200_ctx *ctx);
+/* bytes of internal scratch (split-K partials, BN partial sums, packed filters) currently held */
+size_t dl4jb200_ctx_workspace_bytes(dl4jb200_ctx *ctx);
+int dl4jb200_ctx_sm_count(dl4jb200_ctx *ctx);
+
+int dl4jb200_malloc(dl4jb200_ctx *ctx, size_t bytes, void **out);
+int dl4jb200_free(dl4jb200_ctx *ctx, void *ptr);
+int dl4jb200_memset(dl4jb200_ctx *ctx, void *dst, int value, size_t bytes);
+int dl4jb200_memcpy_h2d(dl4jb200_ctx *ctx, void *dst, const void *src_host, size_t bytes);
+int dl4jb200_memcpy_d2h(dl4jb200_ctx *ctx, void *dst_host, const void *src, size_t bytes);
+int dl4jb200_memcpy_d2d(dl4jb200_ctx *ctx, void *dst, const void *src, size_t bytes);
+
+/* Host-mirror registry: maps an INDArray's host address (INDArray.data().addressPointer() under
+ * nd4j-native) to a device buffer owned by the context, so that chained helper calls stay on the device
+ * and bytes cross PCIe only when the host side reads or writes (replaces nd4j-cuda's
+ * AtomicAllocator.getPointer, CudnnConvolutionHelper.java:442-447). */
+int dl4jb200_buf_register(dl4jb200_ctx *ctx, const void *host_ptr, size_t bytes, void **device_out);
+int dl4jb200_buf_lookup(dl4jb200_ctx *ctx, const void *host_ptr, void **device_out, size_t *bytes_out);
+int dl4jb200_buf_upload(dl4jb200_ctx *ctx, const void *host_ptr);  /* host -> device mirror */
+int dl4jb200_buf_download(dl4jb200_ctx *ctx, void *host_ptr);      /* device mirror -> host */
+int dl4jb200_buf_release(dl4jb200_ctx *ctx, const void *host_ptr);
+
+/* ------------------------------------------------------------------ shapes ------------------- */
+/* NN/util/ConvolutionUtils.java:96-131 getOutputSize, :213-221 effectiveKernelSize, :243-266
+ * getSameModeTopLeftPadding / getSameModeBottomRightPadding, :133-211 validateShapes. One spatial axis.
+ * Returns DL4JB200_ERR_INVALID_INPUT / _CONFIG where the reference throws. */
+int dl4jb200_out_size(int in, int kernel, int stride, int pad, int dilation, int mode, int *out,
+                      int *pad_lo, int *pad_hi);
+
+/* NCHW <-> NHWC (pixel stride cs) re-layout on the device; pad channels are written as zeros. */
+int dl4jb200_nchw_to_nhwc(dl4jb200_ctx *ctx, const float *src, float *dst, int B, int C, int H, int W, int cs);
+int dl4jb200_nhwc_to_nchw(dl4jb200_ctx *ctx, const float *src, float *dst, int B, int C, int H, int W, int cs);
+
+/* ------------------------------------------------------------------ convolution -------------- */
+/* ConvolutionHelper.preOutput (NN/nn/layers/convolution/ConvolutionHelper.java:42-43; CPU semantics
+ * ConvolutionLayer.java:385-417): z = conv2d(x, W) + b, cross-correlation, zero padding.
+ * w: DL4J layout [c_out, c_in, k_h, k_w] 'c' order (a view into the flat parameter vector);
+ * bias [c_out] or NULL (hasBias=false, ConvolutionLayer.java:351-358). act: activation fused into the
+ * epilogue (ConvolutionHelper.activate applied to z in place, ConvolutionLayer.java:456-461);
+ * pass DL4JB200_ACT_IDENTITY for a plain preOutput. x_cs/z_cs: NHWC pixel strides (ignored for NCHW). */
+int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs,
+                      const float *w, const float *bias, float *z, int z_layout, int z_cs, int act, int algo);
+
+/* ConvolutionHelper.backpropGradient (ConvolutionHelper.java:37-40; CPU semantics
+ * ConvolutionLayer.java:202-257). delta = dL/dz (the Java helper applies afn.backprop first, as
+ * CudnnConvolutionHelper.java:212 does). dw / db are the weightGradView / biasGradView: written IN PLACE,
+ * overwritten (not accumulated), summed over the batch, DL4J layout. db and dx may be NULL. */
+int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs,
+                      const float *w, const float *delta, int delta_layout, int delta_cs, float *dw, float *db,
+                      float *dx, int dx_layout, int dx_cs, int algo);
+
+/* ConvolutionHelper.activate (ConvolutionHelper.java:45) and IActivation.backprop
+ * (ConvolutionLayer.java:171): elementwise over n floats; in place allowed (a == z, delta == eps). */
+int dl4jb200_act_fwd(dl4jb200_ctx *ctx, const float *z, float *a, size_t n, int act);
+int dl4jb200_act_bwd(dl4jb200_ctx *ctx, const float *z, const float *eps, float *delta, size_t n, int act);
+
+/* ------------------------------------------------------------------ pooling ------------------ */
+/* SubsamplingHelper.activate (NN/nn/layers/convolution/subsampling/SubsamplingHelper.java:36-38; CPU
+ * semantics SubsamplingLayer.java:339-360). MAX ignores padding; AVG divides by k_h*k_w including
+ * padding; PNORM uses exponent pnorm. argmax (int32, same shape/layout as y, MAX only) may be NULL;
+ * it receives kh*k_w+kw of the first maximum in row-major window order. SUM => NOT_SUPPORTED on bwd. */
+int dl4jb200_pool_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, float *y, int32_t *argmax,
+                      int layout, int x_cs, int y_cs, int pool_type, int pnorm);
+/* SubsamplingHelper.backpropGradient (SubsamplingHelper.java:33-34; CPU semantics
+ * SubsamplingLayer.java:205-266). argmax NULL => recomputed from x exactly as the reference's
+ * im2col + IsMax does. y (forward output) is required for PNORM only. */
+int dl4jb200_pool_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, const float *y,
+                      const float *eps, const int32_t *argmax, float *dx, int layout, int x_cs, int y_cs,
+                      int pool_type, int pnorm, double pnorm_eps);
+
+/* ------------------------------------------------------------------ batch normalisation ------ */
+/* BatchNormalizationHelper.preOutput (NN/nn/layers/normalization/BatchNormalizationHelper.java:34-35; CPU
+ * semantics BatchNormalization.java:255-390). training: batch mean / biased variance over (B,H,W),
+ * std = sqrt(var+eps); running stats gmean = decay*gmean + (1-decay)*mean and
+ * gvar = decay*gvar + (1-decay)*(var+eps) updated IN PLACE (minibatch==0: plain assignment);
+ * save_mean / save_std [C] receive what the layer keeps for backward. inference (training==0):
+ * std = sqrt(gvar) with no eps added. gamma/beta NULL => 1 / 0 (lockGammaBeta). act: optional fused
+ * activation of the following ActivationLayer (IDENTITY or RELU). */
+int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *gamma, const float *beta,
+                    float *gmean, float *gvar, float *save_mean, float *save_std, int B, int C, int H, int W,
+                    int layout, int cs, double decay, double eps, int training, int minibatch, int act);
+/* BatchNormalizationHelper.backpropGradient (BatchNormalizationHelper.java:31-32; CPU semantics
+ * BatchNormalization.java:171-210). dgamma / dbeta are the gradient views, written in place. act_out:
+ * NULL, or the fused-ReLU forward output whose mask is applied to eps first. */
+int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const float *gamma,
+                    const float *save_mean, const float *save_std, const float *act_out, float *dx,
+                    float *dgamma, float *dbeta, int B, int C, int H, int W, int layout, int cs);
+
+/* ------------------------------------------------------------------ LRN ---------------------- */
+/* LocalResponseNormalizationHelper.activate / backpropGradient
+ * (NN/nn/layers/normalization/LocalResponseNormalizationHelper.java:31-35; CPU semantics
+ * LocalResponseNormalization.java:150-190 / 117-147): halfN=(int)n/2, unitScale = k + alpha*sum x^2
+ * (alpha NOT divided by n), y = x*unitScale^-beta. */
+int dl4jb200_lrn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, int B, int C, int H, int W, int layout, int cs,
+                     double k, double n, double alpha, double beta);
+int dl4jb200_lrn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, float *dx, int B, int C, int H, int W,
+                     int layout, int cs, double k, double n, double alpha, double beta);
+
+/* ------------------------------------------------------------------ callers either side (§8f) - */
+/* ElementWiseVertex Add (+ following ActivationLayer ReLU): out = act(a + b); backward mask from out.
+ * NN/nn/graph/vertex/impl/ElementWiseVertex.java:81-86,126-131; NN/nn/layers/ActivationLayer.java:68-92 */
+int dl4jb200_add_act_fwd(dl4jb200_ctx *ctx, const float *a, const float *b, float *out, size_t n, int act);
+/* ComputationGraph epsilon fan-in: dst += src (NN/nn/graph/ComputationGraph.java:2044-2063) */
+int dl4jb200_accumulate(dl4jb200_ctx *ctx, float *dst, const float *src, size_t n);
+/* softmax + NEGATIVELOGLIKELIHOOD / MCXENT output layer: p = softmax(z) row-wise, delta = p - labels,
+ * loss_sum_out[0] = -sum labels*log p (device scalar). NN/nn/layers/BaseOutputLayer.java:82-100,147-190 */
+int dl4jb200_softmax_nll(dl4jb200_ctx *ctx, const float *z, const float *labels, float *delta, float *loss_sum_out,
+                         int B, int K);
+/* One updater block over n contiguous floats of the flat vectors: u = Updater(g); u += l2*w;
+ * u += l1*sign(w); u /= batch_div; w -= u. state: n floats (2n for ADADELTA), may be NULL for SGD/NOOP.
+ * NN/nn/updater/UpdaterBlock.java:142,170-193; BaseMultiLayerUpdater.java:296-307;
+ * NN/optimize/solvers/StochasticGradientDescent.java:78 */
+int dl4jb200_updater_apply(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n, int kind, double lr,
+                           double h1, double h2, double l1, double l2, double batch_div);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DL4JB200_H */

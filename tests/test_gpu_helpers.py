@@ -1,0 +1,402 @@
+"""-m gpu parity tests: the CUDA path (through the C ABI, via the helper-SPI mirror) against the CPU oracle on
+identical seeded inputs -- the pattern of deeplearning4j-cuda/src/test/.../TestConvolution.java:71-151
+(helper vs built-in) -- plus the reference's golden vectors replayed through the GPU path.
+
+Tolerances: pooling / BN / LRN fp32 kernels rel <= 1e-5 of max|ref|; pooling argmax and max
+values bit-exact; convolution FP32 mode <= 1e-4 (the reference's own helper-vs-builtin bound,
+TestConvolution.java:145,151), TF32 tensor-core mode <= 2e-3 of max|ref|.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import load_golden
+from gpu_util import Dev, from_nhwc, rel_err, to_nhwc
+
+pytestmark = pytest.mark.gpu
+
+TOL_BW = 1e-5
+TOL_CONV_FP32 = 1e-4
+TOL_CONV_TF32 = 2e-3
+
+
+@pytest.fixture(scope="module")
+def H():
+    from deeplearning4j_b200 import build
+    build.build()
+    from deeplearning4j_b200 import helpers
+    return helpers
+
+
+@pytest.fixture(scope="module")
+def ctx(H):
+    c = H.Context(0)
+    yield c
+    c.close()
+
+
+def _a(v, shape):
+    return np.asarray(v, np.float32).reshape(shape)
+
+
+MODES = {0: "Strict", 1: "Truncate", 2: "Same"}
+
+CONV_CASES = [  # B, Cin, H, W, Cout, k, s, p, d, mode
+    (2, 3, 7, 8, 4, (3, 3), (1, 1), (1, 1), (1, 1), 1),
+    (2, 3, 8, 9, 5, (3, 3), (2, 2), (0, 0), (1, 1), 2),
+    (1, 2, 9, 9, 3, (3, 3), (1, 1), (0, 0), (2, 2), 2),
+    (2, 4, 6, 6, 3, (1, 1), (2, 2), (0, 0), (1, 1), 1),
+    (2, 1, 12, 12, 2, (5, 5), (2, 2), (2, 2), (1, 1), 1),
+    (3, 1, 28, 28, 20, (5, 5), (1, 1), (0, 0), (1, 1), 2),      # LeNet conv1 (SAME)
+    (3, 20, 14, 14, 50, (5, 5), (1, 1), (0, 0), (1, 1), 2),     # LeNet conv2: Cout=50 (not a multiple of 4)
+    (2, 3, 38, 38, 64, (7, 7), (2, 2), (0, 0), (1, 1), 1),      # ResNet-50 stem shape class (K=7*7*4)
+    (2, 64, 9, 9, 64, (1, 1), (2, 2), (0, 0), (1, 1), 1),       # ResNet-50 strided 1x1
+    (2, 64, 7, 7, 256, (1, 1), (1, 1), (0, 0), (1, 1), 1),      # 1x1 expand, N=256 -> two 128-column tiles
+    (2, 128, 7, 7, 128, (3, 3), (1, 1), (0, 0), (1, 1), 2),     # 3x3 SAME, K=1152
+    (5, 3, 23, 23, 64, (11, 11), (4, 4), (2, 2), (1, 1), 1),    # AlexNet conv1 class
+    (2, 192, 7, 7, 136, (3, 3), (1, 1), (0, 0), (1, 1), 2),     # ragged N (136 = 128 + 8)
+    (1, 8, 4, 4, 8, (3, 3), (1, 1), (0, 0), (1, 1), 2),         # M=16 << one tile
+]
+
+
+@pytest.mark.parametrize("algo_name", ["fp32", "tf32"])
+@pytest.mark.parametrize("case", CONV_CASES, ids=[str(i) for i in range(len(CONV_CASES))])
+def test_conv_forward_backward_vs_oracle(H, ctx, oracle, case, algo_name):
+    B, Cin, Hh, W, Cout, k, s, p, d, mode = case
+    algo = H.ALGO_FP32 if algo_name == "fp32" else H.ALGO_TC_TF32
+    tol = TOL_CONV_FP32 if algo_name == "fp32" else TOL_CONV_TF32
+    rng = np.random.default_rng(12345)
+    x = rng.random((B, Cin, Hh, W), dtype=np.float32)  # U[0,1) like BenchmarkDataSetIterator
+    w = (rng.standard_normal((Cout, Cin) + k) * 0.5).astype(np.float32)
+    b = rng.standard_normal(Cout).astype(np.float32)
+    helper = H.CudnnConvolutionHelper(ctx, algo=algo)
+    assert helper.checkSupported()
+    z = helper.preOutput(x, w, b, k, s, p, None, None, MODES[mode], d)
+    zr = oracle.conv_fwd(x, w, b, stride=s, pad=p, dilation=d, mode=mode)
+    assert z.shape == zr.shape
+    assert rel_err(z, zr) <= tol, ("z", rel_err(z, zr))
+    delta = rng.standard_normal(zr.shape).astype(np.float32)
+    flat = np.full(Cout + w.size, np.nan, np.float32)  # bias first, then W: ConvolutionParamInitializer.java:116-123
+    bview, wview = flat[:Cout].reshape(1, Cout), flat[Cout:].reshape(w.shape)
+    grad, eps_next = helper.backpropGradient(x, w, delta, k, s, p, bview, wview, "identity", None, None, None,
+                                             MODES[mode], d)
+    dwr, dbr, dxr = oracle.conv_bwd(x, w, delta, stride=s, pad=p, dilation=d, mode=mode)
+    assert grad["W"] is wview and not np.isnan(flat).any()  # written in place into the flat gradient vector
+    assert rel_err(wview, dwr) <= tol, ("dW", rel_err(wview, dwr))
+    assert rel_err(bview.ravel(), dbr) <= max(tol, 1e-5), ("db", rel_err(bview.ravel(), dbr))
+    assert rel_err(eps_next, dxr) <= tol, ("dx", rel_err(eps_next, dxr))
+
+
+def test_conv_golden_contained(H, ctx):
+    # ConvolutionLayerTest.java:264-278 replayed through the helper: preOutput then activate(sigmoid)
+    g = load_golden("conv_contained")
+    x, w, b = _a(g["input"], g["input_shape"]), _a(g["w"], g["w_shape"]), _a(g["b"], [1, 2])
+    for algo in (H.ALGO_FP32, H.ALGO_TC_TF32):  # 0.5 and small integers are exact in TF32
+        helper = H.CudnnConvolutionHelper(ctx, algo=algo)
+        z = helper.preOutput(x, w, b, g["kernel"], g["stride"], g["pad"], None, None, "Truncate", (1, 1))
+        a = helper.activate(z, "sigmoid")
+        assert a is z
+        np.testing.assert_allclose(a, _a(g["out"], g["out_shape"]), rtol=0, atol=1e-6)
+    assert helper.activate(z, "softsign") is None  # unsupported activation => null => layer falls back
+    assert helper.preOutput(x.astype(np.float64), w.astype(np.float64), None, g["kernel"], g["stride"], g["pad"]) is None
+
+
+def test_conv_no_bias_and_fused_activation(H, ctx, oracle):
+    from deeplearning4j_b200 import _lib
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((2, 8, 6, 6)).astype(np.float32)
+    w = rng.standard_normal((16, 8, 3, 3)).astype(np.float32) * 0.2
+    zr = oracle.conv_fwd(x, w, None, stride=(1, 1), pad=(1, 1))
+    d = H.conv_desc(x.shape, 16, (3, 3), (1, 1), (1, 1), (1, 1), "Truncate")
+    dev = Dev(ctx)
+    try:
+        for algo, tol in ((H.ALGO_FP32, TOL_CONV_FP32), (H.ALGO_TC_TF32, TOL_CONV_TF32)):
+            for act, kind in (("relu", oracle.ACT_RELU), ("tanh", oracle.ACT_TANH), ("sigmoid", oracle.ACT_SIGMOID)):
+                px, pw = dev.put(to_nhwc(x)), dev.put(w)
+                pz = dev.empty(2 * 6 * 6 * 16 * 4)
+                _lib.call("dl4jb200_conv_fwd", ctx.handle, C.byref(d), px, H.NHWC, 8, pw, None, pz, H.NHWC, 16,
+                          H.ACTIVATIONS[act], algo)
+                got = from_nhwc(dev.get(pz, (2, 6, 6, 16)), 16)
+                assert rel_err(got, oracle.act_fwd(zr, kind)) <= tol
+    finally:
+        dev.free()
+
+
+def test_conv_invalid_shapes_raise_like_reference(H, ctx):
+    from deeplearning4j_b200 import DL4JInvalidConfigException, DL4JInvalidInputException
+    helper = H.CudnnConvolutionHelper(ctx)
+    x = np.zeros((1, 1, 10, 10), np.float32)
+    w = np.zeros((1, 1, 3, 3), np.float32)
+    with pytest.raises(DL4JInvalidConfigException):  # TestConvolutionModes.java:33-110: Strict, 10x10, k3 s3
+        helper.preOutput(x, w, None, (3, 3), (3, 3), (0, 0), None, None, "Strict", (1, 1))
+    with pytest.raises(DL4JInvalidInputException):
+        helper.preOutput(np.zeros((1, 1, 2, 2), np.float32), w, None, (3, 3), (1, 1), (0, 0), None, None, "Truncate", (1, 1))
+
+
+# ------------------------------------------------------------------ pooling
+def test_subsampling_golden(H, ctx):
+    # SubsamplingLayerTest.java:47-133 through the helper; the max-backprop case contains ties
+    g = load_golden("subsampling")
+    x = _a(g["input"], g["input_shape"])
+    h = H.CudnnSubsamplingHelper(ctx)
+    y = h.activate(x, True, g["kernel"], g["stride"], g["pad"], "MAX", "Truncate", (1, 1))
+    np.testing.assert_array_equal(y, _a(g["max_out"], g["out_shape"]))
+    np.testing.assert_array_equal(h.argmax()[0, 1], [[2, 1], [0, 0]])
+    _, dx = h.backpropGradient(x, _a(g["max_bwd_eps"], g["out_shape"]), g["kernel"], g["stride"], g["pad"], "MAX")
+    np.testing.assert_array_equal(dx, _a(g["max_bwd_out"], g["input_shape"]))
+    y = h.activate(x, True, g["kernel"], g["stride"], g["pad"], "AVG")
+    np.testing.assert_array_equal(y, _a(g["avg_out"], g["out_shape"]))
+    _, dx = h.backpropGradient(x, _a(g["avg_bwd_eps"], g["out_shape"]), g["kernel"], g["stride"], g["pad"], "AVG")
+    np.testing.assert_array_equal(dx, _a(g["avg_bwd_out"], g["input_shape"]))
+    assert h.backpropGradient(x, _a(g["avg_bwd_eps"], g["out_shape"]), g["kernel"], g["stride"], g["pad"], "SUM") is None
+
+
+POOL_CASES = [  # B, C, H, W, k, s, p, d, mode
+    (2, 3, 9, 10, (3, 3), (2, 2), (1, 1), (1, 1), 1),
+    (2, 5, 12, 12, (3, 3), (2, 2), (0, 0), (1, 1), 1),   # ResNet-50 stem pool class
+    (2, 4, 7, 7, (3, 3), (2, 2), (0, 0), (1, 1), 2),     # SAME, asymmetric padding
+    (1, 2, 14, 14, (3, 3), (7, 7), (0, 0), (1, 1), 2),   # AlexNet pool3 class (stride 7)
+    (2, 3, 8, 8, (2, 2), (2, 2), (0, 0), (1, 1), 0),
+    (1, 2, 11, 11, (3, 3), (1, 1), (0, 0), (2, 2), 1),   # dilated
+    (2, 8, 4, 4, (3, 3), (2, 2), (0, 0), (1, 1), 1),     # ResNet-50 head pool 4x4 -> 1x1
+]
+
+
+@pytest.mark.parametrize("layout", ["NCHW", "NHWC"])
+@pytest.mark.parametrize("case", POOL_CASES, ids=[str(i) for i in range(len(POOL_CASES))])
+def test_pool_vs_oracle(H, ctx, oracle, case, layout):
+    from deeplearning4j_b200 import _lib
+    B, Cc, Hh, W, k, s, p, d, mode = case
+    rng = np.random.default_rng(99)
+    # quantised values => plenty of ties inside windows: exercises the first-max rule
+    x = (rng.integers(-3, 4, (B, Cc, Hh, W))).astype(np.float32) * 0.5
+    desc = H.conv_desc(x.shape, Cc, k, s, p, d, MODES[mode])
+    yshape = (B, Cc, desc.out_h, desc.out_w)
+    eps = rng.standard_normal(yshape).astype(np.float32)
+    nh = layout == "NHWC"
+    cs = (Cc + 3) // 4 * 4 if nh else 0
+    lay = H.NHWC if nh else H.NCHW
+    enc = (lambda a: to_nhwc(a)) if nh else (lambda a: a)
+    dec = (lambda a, shp: from_nhwc(a.reshape(shp[0], shp[2], shp[3], cs), shp[1])) if nh else (lambda a, shp: a.reshape(shp))
+    n_y = B * desc.out_h * desc.out_w * (cs if nh else Cc)
+    n_x = B * Hh * W * (cs if nh else Cc)
+    dev = Dev(ctx)
+    try:
+        px, pe = dev.put(enc(x)), dev.put(enc(eps))
+        for ptype, oname in ((H.POOL_MAX, oracle.POOL_MAX), (H.POOL_AVG, oracle.POOL_AVG), (H.POOL_PNORM, oracle.POOL_PNORM)):
+            py, pa, pdx = dev.empty(n_y * 4), dev.empty(n_y * 4), dev.empty(n_x * 4)
+            _lib.call("dl4jb200_pool_fwd", ctx.handle, C.byref(desc), px, py, pa, lay, cs, cs, ptype, 2)
+            y = dec(dev.get(py, (n_y,)), yshape)
+            if ptype == H.POOL_MAX:
+                yr, amr = oracle.pool_fwd(x, k, s, p, d, mode, oname, want_argmax=True)
+                np.testing.assert_array_equal(y, yr)  # bit-exact
+                am = dev.get(pa, (n_y,), np.int32)
+                am = from_nhwc(am.reshape(B, desc.out_h, desc.out_w, cs), Cc) if nh else am.reshape(yshape)
+                np.testing.assert_array_equal(am, amr)  # bit-exact indices, first max wins
+            else:
+                yr = oracle.pool_fwd(x, k, s, p, d, mode, oname, pnorm=2)
+                assert rel_err(y, yr) <= TOL_BW
+            dxr = oracle.pool_bwd(x, eps, k, s, p, d, mode, oname, pnorm=2)
+            for use_saved in ((True, False) if ptype == H.POOL_MAX else (False,)):
+                _lib.call("dl4jb200_pool_bwd", ctx.handle, C.byref(desc), px, py, pe, pa if use_saved else None, pdx,
+                          lay, cs, cs, ptype, 2, 1e-8)
+                dx = dec(dev.get(pdx, (n_x,)), x.shape)
+                assert rel_err(dx, dxr) <= TOL_BW, (ptype, use_saved, rel_err(dx, dxr))
+    finally:
+        dev.free()
+
+
+# ------------------------------------------------------------------ batch norm
+@pytest.mark.parametrize("shape", [(4, 3, 5, 6), (8, 64, 14, 14), (3, 20, 7, 9), (2, 260, 4, 4), (16, 8, 1, 1)])
+def test_batchnorm_helper_vs_oracle(H, ctx, oracle, shape):
+    rng = np.random.default_rng(12345)
+    B, Cc, Hh, W = shape
+    x = (rng.standard_normal(shape) * 3 + 2).astype(np.float32)
+    gamma = (rng.random(Cc) + 0.5).astype(np.float32)
+    beta = rng.standard_normal(Cc).astype(np.float32)
+    # params view layout gamma|beta|mean|var (BatchNormalizationParamInitializer.java:80-113)
+    flat = np.concatenate([gamma, beta, np.zeros(Cc, np.float32), np.ones(Cc, np.float32)])
+    gm, gv = flat[2 * Cc:3 * Cc].reshape(1, Cc), flat[3 * Cc:].reshape(1, Cc)
+    gm_r, gv_r = np.zeros(Cc, np.float32), np.ones(Cc, np.float32)
+    h = H.CudnnBatchNormalizationHelper(ctx)
+    assert h.checkSupported(1e-5)
+    for it in range(2):  # two iterations: running statistics accumulate
+        y = h.preOutput(x, True, list(shape), gamma.reshape(1, Cc), beta.reshape(1, Cc), gm, gv, 0.9, 1e-5)
+        yr, m_r, s_r = oracle.bn_fwd(x, gamma, beta, gm_r, gv_r, 0.9, 1e-5, True)
+        assert rel_err(y, yr) <= TOL_BW
+        np.testing.assert_allclose(gm.ravel(), gm_r, rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(gv.ravel(), gv_r, rtol=1e-5, atol=1e-6)  # var + eps is what gets stored
+    e = rng.standard_normal(shape).astype(np.float32)
+    gflat = np.full(4 * Cc, np.nan, np.float32)
+    dg, db = gflat[:Cc].reshape(1, Cc), gflat[Cc:2 * Cc].reshape(1, Cc)
+    grad, dx = h.backpropGradient(x, e, list(shape), gamma.reshape(1, Cc), dg, db, 1e-5)
+    dxr, dgr, dbr = oracle.bn_bwd(x, e, gamma, m_r, s_r)
+    assert rel_err(dx, dxr) <= 2e-5, rel_err(dx, dxr)
+    assert rel_err(dg.ravel(), dgr) <= TOL_BW and rel_err(db.ravel(), dbr) <= TOL_BW
+    # inference: sqrt(gVar) with no eps added (BatchNormalization.java:274-279); running stats untouched
+    before = flat.copy()
+    yt = h.preOutput(x, False, list(shape), gamma.reshape(1, Cc), beta.reshape(1, Cc), gm, gv, 0.9, 1e-5)
+    ytr, _, _ = oracle.bn_fwd(x, gamma, beta, gm_r.copy(), gv_r.copy(), 0.9, 1e-5, False)
+    assert rel_err(yt, ytr) <= TOL_BW
+    np.testing.assert_array_equal(flat, before)
+
+
+def test_batchnorm_mean0_std1_property(H, ctx):
+    # BatchNormalizationTest.java:178-208
+    rng = np.random.default_rng(1)
+    x = (rng.standard_normal((10, 6, 9, 9)) * 5 + 11).astype(np.float32)
+    h = H.CudnnBatchNormalizationHelper(ctx)
+    gm, gv = np.zeros((1, 6), np.float32), np.ones((1, 6), np.float32)
+    y = h.preOutput(x, True, [10, 6, 9, 9], np.ones((1, 6), np.float32), np.zeros((1, 6), np.float32), gm, gv, 0.9, 1e-5)
+    np.testing.assert_allclose(y.astype(np.float64).mean((0, 2, 3)), 0, atol=1e-5)
+    np.testing.assert_allclose(y.astype(np.float64).std((0, 2, 3)), 1, atol=1e-4)
+
+
+@pytest.mark.parametrize("shape", [(4, 8, 5, 6), (8, 64, 14, 14), (3, 50, 7, 7), (2, 2048, 4, 4)])
+def test_batchnorm_nhwc_fused_relu(H, ctx, oracle, shape):
+    from deeplearning4j_b200 import _lib
+    rng = np.random.default_rng(3)
+    B, Cc, Hh, W = shape
+    cs = (Cc + 3) // 4 * 4
+    x = (rng.standard_normal(shape) * 2 + 1).astype(np.float32)
+    gamma = (rng.random(Cc) + 0.5).astype(np.float32)
+    beta = rng.standard_normal(Cc).astype(np.float32)
+    e = rng.standard_normal(shape).astype(np.float32)
+    gm_r, gv_r = np.zeros(Cc, np.float32), np.ones(Cc, np.float32)
+    yr, m_r, s_r = oracle.bn_fwd(x, gamma, beta, gm_r, gv_r, 0.9, 1e-5, True)
+    ar = oracle.act_fwd(yr, oracle.ACT_RELU)
+    dxr, dgr, dbr = oracle.bn_bwd(x, oracle.act_bwd(yr, e, oracle.ACT_RELU), gamma, m_r, s_r)
+    dev = Dev(ctx)
+    try:
+        px, pe = dev.put(to_nhwc(x)), dev.put(to_nhwc(e))
+        pg, pb = dev.put(gamma), dev.put(beta)
+        pm, pv = dev.put(np.zeros(Cc, np.float32)), dev.put(np.ones(Cc, np.float32))
+        n = B * Hh * W * cs
+        py, pdx = dev.empty(n * 4), dev.empty(n * 4)
+        psm, pss, pdg, pdb = (dev.empty(Cc * 4) for _ in range(4))
+        _lib.call("dl4jb200_bn_fwd", ctx.handle, px, py, pg, pb, pm, pv, psm, pss, B, Cc, Hh, W, H.NHWC, cs, 0.9, 1e-5, 1, 1,
+                  H.ACT_RELU)
+        a = dev.get(py, (B, Hh, W, cs))
+        assert rel_err(from_nhwc(a, Cc), ar) <= TOL_BW
+        assert not a[..., Cc:].any()  # padding channels stay zero
+        np.testing.assert_allclose(dev.get(pm, (Cc,)), gm_r, rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(dev.get(pv, (Cc,)), gv_r, rtol=1e-5, atol=1e-6)
+        _lib.call("dl4jb200_bn_bwd", ctx.handle, px, pe, pg, psm, pss, py, pdx, pdg, pdb, B, Cc, Hh, W, H.NHWC, cs)
+        # elements with BN output exactly 0 are measure-zero for random data; masks agree
+        assert rel_err(from_nhwc(dev.get(pdx, (B, Hh, W, cs)), Cc), dxr) <= 2e-5
+        assert rel_err(dev.get(pdg, (Cc,)), dgr) <= TOL_BW and rel_err(dev.get(pdb, (Cc,)), dbr) <= TOL_BW
+    finally:
+        dev.free()
+
+
+# ------------------------------------------------------------------ LRN
+def test_lrn_golden_and_oracle(H, ctx, oracle):
+    g = load_golden("lrn")
+    x, e = _a(g["x"], g["shape"]), _a(g["eps"], g["shape"])
+    h = H.CudnnLocalResponseNormalizationHelper(ctx)
+    assert h.checkSupported(g["k"], g["n"], g["alpha"], g["beta"])
+    y = h.activate(x, True, g["k"], g["n"], g["alpha"], g["beta"])
+    np.testing.assert_allclose(y, _a(g["y"], g["shape"]), rtol=0, atol=1e-5)  # LocalResponseTest.java:36-60
+    _, dx = h.backpropGradient(x, e, g["k"], g["n"], g["alpha"], g["beta"])
+    exp = _a(g["dx"], g["shape"]).ravel()
+    for i in g["dx_asserted_indices"]:  # :110-117
+        assert abs(dx.ravel()[i] - exp[i]) <= g["dx_tol"]
+    assert rel_err(dx, oracle.lrn_bwd(x, e, g["k"], g["n"], g["alpha"], g["beta"])) <= TOL_BW
+
+
+@pytest.mark.parametrize("layout", ["NCHW", "NHWC"])
+def test_lrn_vs_oracle(H, ctx, oracle, layout):
+    from deeplearning4j_b200 import _lib
+    rng = np.random.default_rng(8)
+    B, Cc, Hh, W = 3, 18, 5, 7
+    x = rng.standard_normal((B, Cc, Hh, W)).astype(np.float32) * 3
+    e = rng.standard_normal(x.shape).astype(np.float32)
+    nh = layout == "NHWC"
+    cs = 20 if nh else 0
+    dev = Dev(ctx)
+    try:
+        for (k, n, alpha, beta) in ((2.0, 5.0, 1e-4, 0.75), (1.0, 4.0, 1e-2, 0.5), (2.0, 1.0, 1e-3, 0.75)):
+            px = dev.put(to_nhwc(x, cs) if nh else x)
+            pe = dev.put(to_nhwc(e, cs) if nh else e)
+            n_el = B * Hh * W * (cs if nh else Cc)
+            py, pdx = dev.empty(n_el * 4), dev.empty(n_el * 4)
+            lay = H.NHWC if nh else H.NCHW
+            _lib.call("dl4jb200_lrn_fwd", ctx.handle, px, py, B, Cc, Hh, W, lay, cs, k, n, alpha, beta)
+            _lib.call("dl4jb200_lrn_bwd", ctx.handle, px, pe, pdx, B, Cc, Hh, W, lay, cs, k, n, alpha, beta)
+            y, dx = dev.get(py, (n_el,)), dev.get(pdx, (n_el,))
+            if nh:
+                y, dx = from_nhwc(y.reshape(B, Hh, W, cs), Cc), from_nhwc(dx.reshape(B, Hh, W, cs), Cc)
+            else:
+                y, dx = y.reshape(x.shape), dx.reshape(x.shape)
+            assert rel_err(y, oracle.lrn_fwd(x, k, n, alpha, beta)) <= TOL_BW
+            assert rel_err(dx, oracle.lrn_bwd(x, e, k, n, alpha, beta)) <= TOL_BW
+    finally:
+        dev.free()
+
+
+# ------------------------------------------------------------------ callers either side (§8f)
+def test_elementwise_softmax_updater(H, ctx, oracle):
+    from deeplearning4j_b200 import _lib
+    rng = np.random.default_rng(21)
+    dev = Dev(ctx)
+    try:
+        n = 4099  # odd: exercises the scalar path
+        for nn in (n, 4096):
+            a, b = rng.standard_normal(nn).astype(np.float32), rng.standard_normal(nn).astype(np.float32)
+            pa, pb, po = dev.put(a), dev.put(b), dev.empty(nn * 4)
+            _lib.call("dl4jb200_add_act_fwd", ctx.handle, pa, pb, po, nn, H.ACT_RELU)
+            np.testing.assert_array_equal(dev.get(po, (nn,)), np.maximum(a + b, 0))
+            for name, kind in (("relu", oracle.ACT_RELU), ("sigmoid", oracle.ACT_SIGMOID), ("tanh", oracle.ACT_TANH),
+                               ("leakyrelu", oracle.ACT_LEAKYRELU), ("identity", oracle.ACT_IDENTITY)):
+                _lib.call("dl4jb200_act_fwd", ctx.handle, pa, po, nn, H.ACTIVATIONS[name])
+                assert rel_err(dev.get(po, (nn,)), oracle.act_fwd(a, kind)) <= TOL_BW
+                _lib.call("dl4jb200_act_bwd", ctx.handle, pa, pb, po, nn, H.ACTIVATIONS[name])
+                assert rel_err(dev.get(po, (nn,)), oracle.act_bwd(a, b, kind)) <= TOL_BW
+            _lib.call("dl4jb200_accumulate", ctx.handle, pa, pb, nn)
+            np.testing.assert_array_equal(dev.get(pa, (nn,)), a + b)
+        # softmax + NLL, labels = column 1 (BenchmarkDataSetIterator.java:132-139)
+        B, K = 37, 1000
+        z = rng.standard_normal((B, K)).astype(np.float32) * 4
+        lab = np.zeros((B, K), np.float32)
+        lab[:, 1] = 1
+        pz, pl, pd, ploss = dev.put(z), dev.put(lab), dev.empty(B * K * 4), dev.empty(4)
+        _lib.call("dl4jb200_softmax_nll", ctx.handle, pz, pl, pd, ploss, B, K)
+        loss_r, _, delta_r = oracle.softmax_nll(z, lab)
+        assert rel_err(dev.get(pd, (B, K)), delta_r) <= TOL_BW
+        assert abs(dev.get(ploss, (1,))[0] - loss_r) <= 1e-5 * abs(loss_r)
+        # updaters (TestUpdaters.java formulas), two steps each, with l1/l2 and minibatch division
+        m = 1000
+        g = rng.standard_normal(m).astype(np.float32)
+        w0 = rng.standard_normal(m).astype(np.float32)
+        for kind, okind, ns, args in ((H._lib.UPD_RMSPROP, oracle.UPD_RMSPROP, 1, dict(lr=0.1, h1=0.96, h2=1e-3)),
+                                      (H._lib.UPD_NESTEROVS, oracle.UPD_NESTEROVS, 1, dict(lr=1e-2, h1=0.9)),
+                                      (H._lib.UPD_ADADELTA, oracle.UPD_ADADELTA, 2, dict(h1=0.95, h2=1e-6)),
+                                      (H._lib.UPD_SGD, oracle.UPD_SGD, 1, dict(lr=0.05)),
+                                      (H._lib.UPD_NOOP, oracle.UPD_NOOP, 1, dict())):
+            wr, sr = w0.copy(), np.zeros(ns * m, np.float32)
+            pw, pg, ps = dev.put(w0), dev.put(g), dev.put(np.zeros(ns * m, np.float32))
+            for _ in range(2):
+                oracle.updater_apply(wr, g, sr, okind, l1=1e-7, l2=5e-5, batch_div=16.0, **args)
+                _lib.call("dl4jb200_updater_apply", ctx.handle, pw, pg, ps, m, kind, args.get("lr", 0.0), args.get("h1", 0.0),
+                          args.get("h2", 0.0), 1e-7, 5e-5, 16.0)
+            assert rel_err(dev.get(pw, (m,)), wr) <= TOL_BW, kind
+    finally:
+        dev.free()
+
+
+def test_relayout_roundtrip(H, ctx):
+    from deeplearning4j_b200 import _lib
+    rng = np.random.default_rng(4)
+    dev = Dev(ctx)
+    try:
+        for shape, cs in (((2, 3, 5, 7), 4), ((3, 50, 7, 7), 52), ((2, 64, 9, 9), 64), ((1, 33, 33, 31), 36)):
+            x = rng.standard_normal(shape).astype(np.float32)
+            B, Cc, Hh, W = shape
+            px, pn, pb = dev.put(x), dev.empty(B * Hh * W * cs * 4, fill=0xFF), dev.empty(x.nbytes)
+            _lib.call("dl4jb200_nchw_to_nhwc", ctx.handle, px, pn, B, Cc, Hh, W, cs)
+            np.testing.assert_array_equal(dev.get(pn, (B, Hh, W, cs)), to_nhwc(x, cs))
+            _lib.call("dl4jb200_nhwc_to_nchw", ctx.handle, pn, pb, B, Cc, Hh, W, cs)
+            np.testing.assert_array_equal(dev.get(pb, shape), x)
+    finally:
+        dev.free()
