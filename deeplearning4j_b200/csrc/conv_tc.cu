@@ -98,9 +98,20 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 
 // UMMA shared-memory descriptor, 128-byte swizzle (cute/arch/mma_sm100_desc.hpp SmemDescriptor):
 // [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4, [46,48) version=1, [61,64) layout=2 (SWIZZLE_128B)
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout: 2 = SWIZZLE_128B (16-byte chunks XOR row%8; K-major operands), 1 = SWIZZLE_128B_BASE32B (32-byte chunks
+// XOR row%4, 4-row atoms) -- the only swizzle the hardware offers for MN-major 32-bit operands
+// (cutlass/gemm/collective/builders/sm100_common.inl:89-93).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout = 2) {
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo_bytes >> 4) << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) |
-           ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+           ((uint64_t)1 << 46) | ((uint64_t)layout << 61);
+}
+// byte offset of 16-byte piece `piece` (0..7) of pixel row r inside an MN-major tile whose MN extent is NATOMS
+// 32-float atoms: atoms are 4 rows x 128 B = 512 B, ordered [row group r/4][atom]; within a row the 32-byte
+// chunk index is XORed with r%4.
+template <int NATOMS>
+__device__ __forceinline__ uint32_t mn_tile_off(int r, int atom, int piece) {
+    return (uint32_t)(((r >> 2) * NATOMS + atom) << 9) + ((uint32_t)(r & 3) << 7) +
+           ((uint32_t)(((piece >> 1) ^ (r & 3))) << 5) + ((uint32_t)(piece & 1) << 4);
 }
 // Instruction descriptor (InstrDescriptor): c_format F32 [4,6)=1, a/b_format TF32 [7,10)=[10,13)=2,
 // a_major bit 15, b_major bit 16 (1 = MN-major), N>>3 at [17,23), M>>4 at [24,29)
@@ -286,8 +297,7 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
                 for (int i = 0; i < 8; i++) {
                     const int r = ra + 4 * i, m = mrow0 + r;
                     const bool ok = a_col_ok && m < me;
-                    const uint32_t dst = a_stage + (uint32_t)(((r >> 3) * 4 + (pa >> 3)) << 10) + ((uint32_t)(r & 7) << 7) +
-                                         ((uint32_t)((pa & 7) ^ (r & 7)) << 4);
+                    const uint32_t dst = a_stage + mn_tile_off<4>(r, pa >> 3, pa & 7);
                     cp_async16(dst, ok ? delta + (size_t)m * delta_cs + co0 + pa * 4 : delta, ok ? 16u : 0u);
                 }
 #pragma unroll
@@ -299,8 +309,7 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
                         conv_m_decode(g, m, b, y0, x0);
                         o = conv_src_offset(g, b, y0, x0, kh, kw);
                     }
-                    const uint32_t dst = b_stage + (uint32_t)(((r >> 3) * NB_ATOMS + (pb >> 3)) << 10) +
-                                         ((uint32_t)(r & 7) << 7) + ((uint32_t)((pb & 7) ^ (r & 7)) << 4);
+                    const uint32_t dst = b_stage + mn_tile_off<NB_ATOMS>(r, pb >> 3, pb & 7);
                     cp_async16(dst, o >= 0 ? x + o + c : x, o >= 0 ? 16u : 0u);
                 }
             }
@@ -335,9 +344,10 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
             tc_fence_after();
             if (lane == 0) {
 #pragma unroll
-                for (int k = 0; k < BLOCK_K / 8; k++) {  // one 8-pixel group per MMA
-                    const uint64_t ad = umma_desc(a_base + s * L::A_BYTES + k * 4 * 1024, 1024, 4 * 1024);
-                    const uint64_t bd = umma_desc(b_base + s * L::B_BYTES + k * NB_ATOMS * 1024, 1024, NB_ATOMS * 1024);
+                for (int k = 0; k < BLOCK_K / 8; k++) {  // 8 pixels = two 4-row groups per MMA; LBO = atom stride along
+                                                         // MN (512 B), SBO = stride between 4-row groups along K
+                    const uint64_t ad = umma_desc(a_base + s * L::A_BYTES + k * 2 * 4 * 512, 512, 4 * 512, 1);
+                    const uint64_t bd = umma_desc(b_base + s * L::B_BYTES + k * 2 * NB_ATOMS * 512, 512, NB_ATOMS * 512, 1);
                     umma_tf32(tmem_d, ad, bd, idesc, (it | k) ? 1u : 0u);
                 }
                 umma_commit(empty_bar(s));
