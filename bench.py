@@ -1,0 +1,304 @@
+#!/usr/bin/env python
+"""bench.py -- ResNet-50 (DL4J zoo variant) training images/sec on N B200s, BASELINE.json's metric.
+
+  python bench.py --gpus N --steps K --warmup W            this repo's CUDA path (one rank per GPU under torchrun)
+  python bench.py --impl reference ...                     the reference's CPU algorithm (im2col + BLAS sgemm + col2im,
+                                                           multi-pass BN/pool; oracle/ -- the reference itself needs a JVM
+                                                           and un-vendored nd4j, unavailable on this box) on the host cores
+
+A step = one fit() iteration (forward, backward, score, updater, params -= update) on one synthetic minibatch
+(BenchmarkDataSetIterator semantics: one fixed U[0,1) feature tensor, every label = class 1). `value` is measured
+with the minibatch already resident in HBM; `e2e` goes through Network.fit(host features, host labels) with the
+pinned host->device copy and the device->host read of the score inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+MODEL, BATCH, LABELS = "resnet50", 256, 1000
+REF_SAMPLE_BATCH = 4
+
+
+def peaks():
+    p = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "src": "fallback"}
+    f = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(f):
+        try:
+            j = json.load(open(f))
+            p.update({k: j[k] for k in ("hbm_gbs", "bf16_tflops", "bf16_tflops_sustained") if k in j})
+            p["src"] = "measured"
+        except Exception:
+            pass
+    return p
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 3 + i and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]) if self.rows[0][1].replace(".", "").isdigit() else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def synthetic(model, B, K):
+    rng = np.random.default_rng(12345)
+    x = rng.random((B,) + tuple(model["input"]), dtype=np.float32)
+    lab = np.zeros((B, K), np.float32)
+    lab[:, 1] = 1.0
+    return x, lab
+
+
+def conv_flops(net):
+    """{vertex: (fwd_flops, bwd_flops)} algorithmic FLOPs 2*B*Ho*Wo*Cout*Cin*kH*kW per pass."""
+    out = {}
+    first = net.model["vertices"][0]["name"]
+    for v in net.model["vertices"]:
+        if v["op"] == "conv":
+            src, d = net._conv_desc(v)
+            f = 2.0 * d.batch * d.out_h * d.out_w * d.c_out * d.c_in * d.k_h * d.k_w
+            out[v["name"]] = (f, f * (1 if src == first else 2))
+        elif v["op"] in ("dense", "output"):
+            d = net._dense_desc(v)
+            f = 2.0 * d.batch * d.c_out * d.c_in
+            out[v["name"]] = (f, 2 * f)
+    return out
+
+
+def run_reference(args, rank, world):
+    """The reference arm: the reference's CPU algorithm for the same step, timed on the host cores (rank 0 only)."""
+    if rank != 0:
+        return
+    from deeplearning4j_b200 import zoo
+    from oracle import oracle as o
+    from oracle.net_oracle import OracleNet
+    o.build()
+    m = zoo.MODELS[MODEL]()
+    P, layout = zoo.param_layout(m)
+    Bs = REF_SAMPLE_BATCH
+    x, lab = synthetic(m, Bs, LABELS)
+    net = OracleNet(m, layout, P, zoo.init_params(m), fast=True)
+    steps, warm = max(1, min(args.steps, 8)), max(1, min(args.warmup, 2))
+    for _ in range(warm):
+        net.fit(x, lab)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        net.fit(x, lab)
+    dt = (time.perf_counter() - t0) / steps
+    v = Bs / dt
+    cores = os.cpu_count() or 1
+    print(json.dumps({
+        "impl": "reference", "metric": "resnet50_train_images_per_sec", "value": v, "unit": "images/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"ResNet-50 (DL4J zoo) 3x224x224 train step, reference CPU algorithm, sample batch {Bs}",
+                   "global_batch": Bs},
+        "cpu_baseline": {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
+                         "sample": f"{steps} full fit() iterations at batch {Bs} (im2col + OpenBLAS sgemm + col2im, OpenMP over all cores)"},
+        "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--algo", default="tf32", choices=["tf32", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dump-profile", default=None, help="write the per-layer event timings to this JSON file")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+    from deeplearning4j_b200 import _lib, network, parallel, zoo
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    m = zoo.MODELS[MODEL]()
+    B = args.batch
+    algo = _lib.ALGO_TC_TF32 if args.algo == "tf32" else _lib.ALGO_FP32
+    net = network.Network(m, B, device=local, algo=algo)
+    pw = parallel.ParallelWrapper(net) if world > 1 else None
+    step = (lambda f=None, l=None: pw.fit(f, l)) if pw else (lambda f=None, l=None: net.fit(f, l))
+    x, lab = synthetic(m, B, LABELS)
+    xh, labh = torch.from_numpy(x).pin_memory(), torch.from_numpy(lab).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up (also grows the library's scratch to its final size)
+    net.set_batch(xh, labh)
+    for _ in range(args.warmup):
+        step()
+    barrier()
+
+    # ---- timed region 1: device-resident minibatch. Per-call CUDA events on the launching stream for the roofline.
+    net.profile(["dl4jb200_conv_fwd", "dl4jb200_conv_bwd", "dl4jb200_bn_fwd", "dl4jb200_bn_bwd", "dl4jb200_pool_fwd",
+                 "dl4jb200_pool_bwd"])
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = _lib.cdll().dl4jb200_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(net.stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(net.stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = _lib.cdll().dl4jb200_launch_count() - l0
+    prof = net.profile_results()
+    net.prof = None
+
+    # ---- timed region 2: end to end through the public API with host buffers
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    f0.record(net.stream)
+    last = None
+    for _ in range(args.steps):
+        s = step(xh, labh)
+        net.sync()
+        last = float(s.cpu()[0])  # device -> host read of the step's score
+    f1.record(net.stream)
+    barrier()
+    ms_e2e = f0.elapsed_time(f1)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    t = torch.tensor([ms, ms_e2e], device=net.dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    pk = peaks()
+    total_imgs = B * world * args.steps
+    value, e2e = total_imgs / (ms / 1e3), total_imgs / (ms_e2e / 1e3)
+    # ---- roofline of the dominant kernel family: the tcgen05 implicit-GEMM convolutions
+    fl = conv_flops(net)
+    conv_ms = conv_fl = 0.0
+    n_conv_calls = 0
+    per_layer = {}
+    for (fn, tag), times in prof.items():
+        if fn in ("dl4jb200_conv_fwd", "dl4jb200_conv_bwd") and tag in fl:
+            f = fl[tag][0 if fn.endswith("fwd") else 1]
+            conv_ms += sum(times)
+            conv_fl += f * len(times)
+            n_conv_calls += len(times)
+            per_layer[f"{tag}:{fn[9:]}"] = {"ms": sum(times) / len(times), "tflops": f / (sum(times) / len(times) * 1e-3) / 1e12}
+    tf32_peak = pk["bf16_tflops_sustained"] / 2.0
+    ach = conv_fl / (conv_ms * 1e-3) / 1e12 if conv_ms else 0.0
+    roofline = {"bound": "tensor", "kernel": "k_conv_tc_gemm/k_conv_tc_wgrad (all conv_fwd + conv_bwd calls of the step)",
+                "achieved": ach, "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak, "traffic": None,
+                "peak_note": f"TF32 dense = 0.5 x bf16_tflops_sustained ({pk['src']}); kernel timed inside a long step",
+                "share_of_step": conv_ms / ms, "calls": n_conv_calls}
+    # ---- HBM kernels (BN / pool): achieved GB/s on algorithmic bytes
+    bw = {}
+    for fn, bpe in (("dl4jb200_bn_fwd", 8), ("dl4jb200_bn_bwd", 12)):
+        tot_ms = tot_b = 0.0
+        for (f2, tag), times in prof.items():
+            if f2 == fn:
+                s = net.shapes[tag]
+                tot_ms += sum(times)
+                tot_b += float(B) * s[0] * s[1] * s[2] * bpe * len(times)
+        if tot_ms:
+            bw[fn[9:]] = {"achieved_gbs": tot_b / (tot_ms * 1e-3) / 1e9, "frac_of_hbm": tot_b / (tot_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                          "share_of_step": tot_ms / ms}
+    for fn in ("dl4jb200_pool_fwd", "dl4jb200_pool_bwd"):
+        tot_ms = tot_b = 0.0
+        for (f2, tag), times in prof.items():
+            if f2 == fn:
+                so, si = net.shapes[tag], net.shapes[net.vmap[tag]["in"][0]]
+                n_in, n_out = float(B) * si[0] * si[1] * si[2], float(B) * so[0] * so[1] * so[2]
+                tot_ms += sum(times)
+                tot_b += (4 * (n_in + n_out) + 4 * n_out) * len(times)
+        if tot_ms:
+            bw[fn[9:]] = {"achieved_gbs": tot_b / (tot_ms * 1e-3) / 1e9, "frac_of_hbm": tot_b / (tot_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                          "share_of_step": tot_ms / ms}
+    if args.dump_profile:
+        os.makedirs(os.path.dirname(os.path.abspath(args.dump_profile)), exist_ok=True)
+        json.dump({"per_layer": per_layer, "bandwidth": bw, "roofline": roofline, "ms_per_step": ms / args.steps},
+                  open(args.dump_profile, "w"), indent=1)
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import oracle as o
+        from oracle.net_oracle import OracleNet
+        o.build()
+        P, layout = zoo.param_layout(m)
+        xs, ls = synthetic(m, REF_SAMPLE_BATCH, LABELS)
+        ref = OracleNet(m, layout, P, zoo.init_params(m), fast=True)
+        ref.fit(xs, ls)
+        t0 = time.perf_counter()
+        nref = 2
+        for _ in range(nref):
+            ref.fit(xs, ls)
+        dt = (time.perf_counter() - t0) / nref
+        cpu = {"value": REF_SAMPLE_BATCH / dt, "unit": "images/s", "cores": os.cpu_count() or 1, "kind": "port",
+               "sample": f"{nref} full fit() iterations of the same network at batch {REF_SAMPLE_BATCH} "
+                         "(reference CPU algorithm: im2col + OpenBLAS sgemm + col2im, OpenMP over all cores)"}
+
+    line = {
+        "metric": "resnet50_train_images_per_sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "tf32" if args.algo == "tf32" else "f32", "data": "synthetic",
+        "config": {"workload": "ResNet-50 (DL4J zoo ComputationGraph, BatchNormalization) 3x224x224 full training step "
+                               "(forward, backward, score, RmsProp+L1/L2 updater)", "global_batch": B * world,
+                   "per_gpu_batch": B, "parallelism": f"dp{world}" if world > 1 else "single",
+                   "l2_flush": "working set (>= 10 GB of activations per step) exceeds the 126 MB L2"},
+        "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": int(x.nbytes + lab.nbytes), "d2h_bytes_per_step": 4,
+                "ms_per_step": ms_e2e / args.steps, "last_score": last},
+        "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roofline, "hbm_kernels": bw,
+    }
+    if cpu:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -78,13 +78,16 @@ PROTOTYPES = {
     "dl4jb200_lrn_bwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _d, _d, _d, _d],
     "dl4jb200_add_act_fwd": [_vp, _vp, _vp, _vp, _sz, _i],
     "dl4jb200_accumulate": [_vp, _vp, _vp, _sz],
-    "dl4jb200_softmax_nll": [_vp, _vp, _vp, _vp, _vp, _i, _i],
+    "dl4jb200_softmax_nll": [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i],
+    "dl4jb200_l1l2_score": [_vp, _vp, _sz, _d, _d, _vp],
+    "dl4jb200_copy2d": [_vp, _vp, _i, _vp, _i, _i, _i],
     "dl4jb200_updater_apply": [_vp, _vp, _vp, _vp, _sz, _i, _d, _d, _d, _d, _d, _d],
 }
 # entry points whose return value is not a status
 _SPECIAL = {
     "dl4jb200_last_error": (C.c_char_p, []),
     "dl4jb200_version": (_i, []),
+    "dl4jb200_launch_count": (C.c_ulonglong, []),
     "dl4jb200_ctx_stream": (_vp, [_vp]),
     "dl4jb200_ctx_workspace_bytes": (_sz, [_vp]),
     "dl4jb200_ctx_sm_count": (_i, [_vp]),

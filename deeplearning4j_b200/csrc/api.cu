@@ -4,6 +4,7 @@
 #include "common.cuh"
 
 static thread_local char g_err[1024] = "";
+unsigned long long g_dl4j_launches = 0;
 
 void dl4j_set_error(const char *fmt, ...) {
     va_list ap;
@@ -33,6 +34,7 @@ extern "C" {
 
 const char *dl4jb200_last_error(void) { return g_err; }
 int dl4jb200_version(void) { return 100; }
+unsigned long long dl4jb200_launch_count(void) { return g_dl4j_launches; }
 
 int dl4jb200_ctx_create(int device, void *stream, dl4jb200_ctx **out) {
     DL4J_REQUIRE(out != nullptr, "ctx_create: out is NULL");

@@ -39,7 +39,13 @@ void *dl4j_workspace(dl4jb200_ctx *ctx, int slot, size_t bytes);
         }                                                                                         \
     } while (0)
 
-#define DL4J_CHECK_LAUNCH() DL4J_CUDA_TRY(cudaGetLastError())
+// every kernel launch in the library is followed by this macro: it also feeds dl4jb200_launch_count()
+extern unsigned long long g_dl4j_launches;
+#define DL4J_CHECK_LAUNCH()                  \
+    do {                                     \
+        ++g_dl4j_launches;                   \
+        DL4J_CUDA_TRY(cudaGetLastError());   \
+    } while (0)
 
 #define DL4J_REQUIRE(cond, ...)            \
     do {                                   \

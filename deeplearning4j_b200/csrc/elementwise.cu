@@ -109,11 +109,11 @@ __global__ void __launch_bounds__(256) k_add_act(const float *__restrict__ a, co
 static inline bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 
 // ---------------------------------------------------------------- softmax + NLL (one warp per row)
-__global__ void __launch_bounds__(256) k_softmax_nll(const float *__restrict__ z, const float *__restrict__ labels,
-                                                     float *__restrict__ delta, float *loss_rows, int B, int K) {
+__global__ void __launch_bounds__(256) k_softmax_nll(const float *__restrict__ z, int z_ld, const float *__restrict__ labels,
+                                                     float *__restrict__ delta, int d_ld, float *loss_rows, int B, int K) {
     int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= B) return;
-    const float *zr = z + (size_t)row * K;
+    const float *zr = z + (size_t)row * z_ld;
     const float *lr = labels + (size_t)row * K;
     float m = -INFINITY;
     for (int k = lane; k < K; k += 32) m = fmaxf(m, zr[k]);
@@ -124,9 +124,10 @@ __global__ void __launch_bounds__(256) k_softmax_nll(const float *__restrict__ z
     float logs = logf(s), loss = 0.f, inv = 1.f / s;
     for (int k = lane; k < K; k += 32) {
         float zz = zr[k] - m, l = lr[k];
-        delta[(size_t)row * K + k] = expf(zz) * inv - l;
+        delta[(size_t)row * d_ld + k] = expf(zz) * inv - l;
         if (l != 0.f) loss -= l * (zz - logs);
     }
+    for (int k = K + lane; k < d_ld; k += 32) delta[(size_t)row * d_ld + k] = 0.f;
     for (int o = 16; o; o >>= 1) loss += __shfl_xor_sync(0xffffffffu, loss, o);
     if (lane == 0) loss_rows[row] = loss;
 }
@@ -143,6 +144,39 @@ __global__ void __launch_bounds__(256) k_sum_rows(const float *__restrict__ v, f
         __syncthreads();
     }
     if (threadIdx.x == 0) out[0] = (float)sm[0];
+}
+
+// score regularisation terms: per-block partials, then a deterministic single-block fold into score_acc
+__global__ void __launch_bounds__(256) k_l1l2_partial(const float *__restrict__ w, size_t n, double *partial) {
+    __shared__ double s1[256], s2[256];
+    double a = 0.0, b = 0.0;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float v = w[i];
+        a += fabsf(v);
+        b += (double)v * (double)v;
+    }
+    s1[threadIdx.x] = a; s2[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = 128; o; o >>= 1) {
+        if (threadIdx.x < o) { s1[threadIdx.x] += s1[threadIdx.x + o]; s2[threadIdx.x] += s2[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { partial[2 * blockIdx.x] = s1[0]; partial[2 * blockIdx.x + 1] = s2[0]; }
+}
+__global__ void k_l1l2_final(const double *partial, int nblk, double l1, double l2, float *score_acc) {
+    double a = 0.0, b = 0.0;
+    for (int i = 0; i < nblk; i++) { a += partial[2 * i]; b += partial[2 * i + 1]; }
+    score_acc[0] += (float)(l1 * a + 0.5 * l2 * b);
+}
+
+__global__ void __launch_bounds__(256) k_copy2d(const float *__restrict__ src, int src_ld, float *__restrict__ dst, int dst_ld,
+                                                int rows, int cols) {
+    size_t total = (size_t)rows * dst_ld, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        int r = (int)(i / dst_ld), c = (int)(i % dst_ld);
+        dst[i] = c < cols ? src[(size_t)r * src_ld + c] : 0.f;
+    }
 }
 
 // ---------------------------------------------------------------- updater (UpdaterBlock.java:142,170-193)
@@ -241,15 +275,37 @@ int dl4jb200_accumulate(dl4jb200_ctx *ctx, float *dst, const float *src, size_t 
     return dl4jb200_add_act_fwd(ctx, dst, src, dst, n, DL4JB200_ACT_IDENTITY);
 }
 
-int dl4jb200_softmax_nll(dl4jb200_ctx *ctx, const float *z, const float *labels, float *delta, float *loss_sum_out,
-                         int B, int K) {
+int dl4jb200_softmax_nll(dl4jb200_ctx *ctx, const float *z, int z_ld, const float *labels, float *delta, int delta_ld,
+                         float *loss_sum_out, int B, int K) {
     DL4J_REQUIRE(ctx && z && labels && delta && loss_sum_out, "softmax_nll: NULL argument");
-    DL4J_REQUIRE(B > 0 && K > 0, "softmax_nll: bad shape");
+    DL4J_REQUIRE(B > 0 && K > 0 && z_ld >= K && delta_ld >= K, "softmax_nll: bad shape");
     float *rows = (float *)dl4j_workspace(ctx, 0, (size_t)B * sizeof(float));
     if (!rows) return DL4JB200_ERR_CUDA;
-    k_softmax_nll<<<dl4j_ceil_div(B, 8), 256, 0, ctx->stream>>>(z, labels, delta, rows, B, K);
+    k_softmax_nll<<<dl4j_ceil_div(B, 8), 256, 0, ctx->stream>>>(z, z_ld, labels, delta, delta_ld, rows, B, K);
     DL4J_CHECK_LAUNCH();
     k_sum_rows<<<1, 256, 0, ctx->stream>>>(rows, loss_sum_out, B);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_l1l2_score(dl4jb200_ctx *ctx, const float *w, size_t n, double l1, double l2, float *score_acc) {
+    DL4J_REQUIRE(ctx && w && score_acc, "l1l2_score: NULL argument");
+    if (n == 0 || (l1 == 0.0 && l2 == 0.0)) return DL4JB200_OK;
+    int nblk = ew_grid(ctx, n, 256);
+    if (nblk > 1024) nblk = 1024;
+    double *partial = (double *)dl4j_workspace(ctx, 0, (size_t)nblk * 2 * sizeof(double));
+    if (!partial) return DL4JB200_ERR_CUDA;
+    k_l1l2_partial<<<nblk, 256, 0, ctx->stream>>>(w, n, partial);
+    DL4J_CHECK_LAUNCH();
+    k_l1l2_final<<<1, 1, 0, ctx->stream>>>(partial, nblk, l1, l2, score_acc);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_copy2d(dl4jb200_ctx *ctx, const float *src, int src_ld, float *dst, int dst_ld, int rows, int cols) {
+    DL4J_REQUIRE(ctx && src && dst, "copy2d: NULL argument");
+    DL4J_REQUIRE(rows > 0 && cols > 0 && src_ld >= cols && dst_ld >= cols, "copy2d: bad shape");
+    k_copy2d<<<ew_grid(ctx, (size_t)rows * dst_ld, 256), 256, 0, ctx->stream>>>(src, src_ld, dst, dst_ld, rows, cols);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }

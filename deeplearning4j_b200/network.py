@@ -1,0 +1,442 @@
+"""Device-resident training-step driver for the BASELINE configs.
+
+Replays, per minibatch, the call sequence that MultiLayerNetwork / ComputationGraph issue
+(computeGradientAndScore -> feedForward -> calcBackpropGradients -> updater -> params.subi:
+nn/multilayer/MultiLayerNetwork.java:2360-2420, nn/graph/ComputationGraph.java:1321-1360,1604-1739,1977-2097,
+optimize/solvers/StochasticGradientDescent.java:58-91) as a chain of C-ABI calls on device-resident NHWC
+buffers: activations, the flat parameter vector, the flat gradient vector (layout of zoo.param_layout ==
+DL4J's flat views) and the updater state never leave HBM. torch is used only to own device memory and the
+stream (and, in parallel.py, for NCCL); all arithmetic runs in libdl4jb200's hand-written kernels.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib, zoo
+from ._lib import ConvDesc
+
+_ACT = {"identity": _lib.ACT_IDENTITY, "relu": _lib.ACT_RELU, "sigmoid": _lib.ACT_SIGMOID, "tanh": _lib.ACT_TANH}
+_POOL = {"MAX": _lib.POOL_MAX, "AVG": _lib.POOL_AVG, "PNORM": _lib.POOL_PNORM}
+_MODE = {"Strict": 0, "Truncate": 1, "Same": 2}
+
+
+def _r4(n):
+    return (n + 3) // 4 * 4
+
+
+class Network:
+    def __init__(self, model, batch, device=0, algo=_lib.ALGO_TC_TF32, params=None, with_score=True):
+        import torch
+        self.torch = torch
+        self.model, self.B, self.algo, self.with_score = model, int(batch), algo, with_score
+        self.dev = torch.device("cuda", device)
+        torch.cuda.set_device(self.dev)
+        # a dedicated stream shared by torch (memory ops, NCCL) and the C-ABI context: one ordered queue
+        self.stream = torch.cuda.Stream(self.dev)
+        h = C.c_void_p()
+        _lib.call("dl4jb200_ctx_create", device, C.c_void_p(self.stream.cuda_stream), C.byref(h))
+        self.h = h
+        self.launches = 0
+        self.prof, self.prof_fns, self._cur = None, set(), None
+        self.batch_div_scale = 1  # data-parallel replicas: global minibatch = scale * B (parallel.py)
+        self.shapes = zoo.infer_shapes(model)
+        self.P, self.layout = zoo.param_layout(model)
+        self.vmap = {v["name"]: v for v in model["vertices"]}
+        host = zoo.init_params(model) if params is None else np.ascontiguousarray(params, np.float32)
+        assert host.size == self.P
+        self.params = torch.from_numpy(host.copy()).to(self.dev)
+        self.grads = torch.zeros(self.P, device=self.dev)
+        kind = model["updater"]["kind"]
+        self.state = torch.zeros(self.P * (2 if kind == "adadelta" else 1), device=self.dev)
+        self.pidx = {}
+        for name, key, off, shp, pk in self.layout:
+            self.pidx[(name, key)] = (off, int(np.prod(shp)), shp, pk)
+        self._plan()
+        torch.cuda.synchronize(self.dev)  # allocations / fills above ran on torch's default stream
+
+    # ------------------------------------------------------------------ planning
+    def _buf(self, *shape, dtype=None):
+        t = self.torch
+        return t.zeros(*shape, device=self.dev, dtype=dtype or t.float32)
+
+    def _plan(self):
+        B = self.B
+        self.consumers = {v["name"]: [] for v in self.model["vertices"]}
+        for v in self.model["vertices"]:
+            for u in v["in"]:
+                self.consumers[u].append(v["name"])
+        self.out, self.cs, self.eps, self.aux = {}, {}, {}, {}
+        self.fold_pad = {}
+        for v in self.model["vertices"]:
+            n, op, s = v["name"], v["op"], self.shapes[v["name"]]
+            if len(s) == 3:
+                cs = _r4(s[0])
+                self.cs[n] = cs
+                shape = (B, s[1], s[2], cs)
+            else:
+                cs = _r4(s[0])
+                self.cs[n] = cs
+                shape = (B, cs)
+            if op == "zeropad":
+                # ZeroPaddingLayer feeding exactly one Truncate-mode conv is the same arithmetic as that conv with
+                # explicit zero padding (nn/layers/convolution/ZeroPaddingLayer.java:50-75): fold, no copy.
+                cons = self.consumers[n]
+                t, b, l, r = v["pad"]
+                ok = len(cons) == 1 and self.vmap[cons[0]]["op"] == "conv" and self.vmap[cons[0]]["mode"] != "Same" and t == b and l == r
+                if not ok:
+                    raise NotImplementedError("stand-alone ZeroPaddingLayer")
+                self.fold_pad[cons[0]] = (v["in"][0], t, l)
+                continue
+            if op == "flatten":
+                src = self.shapes[v["in"][0]]
+                if src[1] * src[2] == 1 and self.cs[v["in"][0]] == src[0]:
+                    self.out[n] = None  # alias of the input buffer ([B,1,1,C] NHWC == [B,C])
+                    continue
+                self.aux[n] = self._buf(B, src[0] * src[1] * src[2])
+            self.out[n] = self._buf(*shape)
+            if op == "pool" and v["type"] == "MAX":
+                self.aux[n] = self._buf(*shape, dtype=self.torch.int32)
+            if op == "bn":
+                self.aux[n] = (self._buf(s[0]), self._buf(s[0]))  # saved mean / std
+            if op == "output":
+                self.aux[n] = self._buf(B, cs)  # delta = p - labels
+        self.loss = self._buf(1)
+        self.score_reg = self._buf(1)
+        self.tmp_eps = {}
+        self.labels = None
+
+    def _ptr(self, t, off=0):
+        return C.c_void_p(t.data_ptr() + 4 * off)
+
+    def _p(self, name, key):
+        off, n, shp, pk = self.pidx[(name, key)]
+        return self._ptr(self.params, off), self._ptr(self.grads, off), off, n
+
+    def _call(self, fn, *args):
+        self.launches += 1
+        if self.prof is not None and fn in self.prof_fns:
+            ev = self.torch.cuda.Event
+            a, b = ev(enable_timing=True), ev(enable_timing=True)
+            a.record(self.stream)
+            _lib.call(fn, self.h, *args)
+            b.record(self.stream)
+            self.prof.append((fn, self._cur, a, b))
+        else:
+            _lib.call(fn, self.h, *args)
+
+    def profile(self, fns):
+        """Start recording CUDA-event pairs (on the network's stream) around the given C-ABI calls."""
+        self.prof, self.prof_fns = [], set(fns)
+
+    def profile_results(self):
+        """-> {(fn, vertex): [ms, ...]} ; call after sync()."""
+        out = {}
+        for fn, tag, a, b in self.prof or []:
+            out.setdefault((fn, tag), []).append(a.elapsed_time(b))
+        return out
+
+    def _src(self, u):
+        """(tensor, cs) of vertex u's output, resolving flatten aliases."""
+        while self.out.get(u, 0) is None:
+            u = self.vmap[u]["in"][0]
+        return self.out[u], self.cs[u]
+
+    def _conv_desc(self, v):
+        n = v["name"]
+        if n in self.fold_pad:
+            src, pt, pl = self.fold_pad[n]
+        else:
+            src, pt, pl = v["in"][0], None, None
+        s_in, s_out = self.shapes[src], self.shapes[n]
+        k, st, d = v["kernel"], v["stride"], v["dilation"]
+        if pt is None:
+            m = _MODE[v["mode"]]
+            pt = _lib.out_size(s_in[1], k[0], st[0], v["pad"][0], d[0], m)[1]
+            pl = _lib.out_size(s_in[2], k[1], st[1], v["pad"][1], d[1], m)[1]
+        return src, ConvDesc(self.B, s_in[0], s_in[1], s_in[2], v["nOut"], k[0], k[1], st[0], st[1], pt, pl, d[0], d[1],
+                             s_out[1], s_out[2])
+
+    def _dense_desc(self, v):
+        nin = self.shapes[v["in"][0]][0]
+        return ConvDesc(self.B, nin, 1, 1, v["nOut"], 1, 1, 1, 1, 0, 0, 1, 1, 1, 1)
+
+    # ------------------------------------------------------------------ data
+    def set_batch(self, features, labels):
+        """features: float32 [B,C,H,W] (host numpy / pinned or device torch tensor, NCHW as DL4J feeds it);
+        labels: [B,K]. Copies to the device (async on the context's stream) and re-lays out to NHWC."""
+        t = self.torch
+        inp = self.model["vertices"][0]["name"]
+        Cc, Hh, W = self.shapes[inp]
+        with t.cuda.stream(self.stream):
+            f = t.as_tensor(features) if not isinstance(features, t.Tensor) else features
+            if f.device != self.dev:
+                f = f.to(self.dev, non_blocking=True)
+            lab = t.as_tensor(labels) if not isinstance(labels, t.Tensor) else labels
+            self.labels = lab.to(self.dev, non_blocking=True).contiguous()
+            self._feat = f.contiguous()
+        self._call("dl4jb200_nchw_to_nhwc", self._ptr(self._feat), self._ptr(self.out[inp]), self.B, Cc, Hh, W, self.cs[inp])
+
+    # ------------------------------------------------------------------ forward (feedForward, train mode)
+    def forward(self, train=True):
+        L, B = _lib, self.B
+        for v in self.model["vertices"]:
+            n, op = v["name"], v["op"]
+            self._cur = n
+            if op in ("input", "zeropad") or self.out.get(n, 0) is None:
+                continue
+            if op == "conv":
+                src, d = self._conv_desc(v)
+                x, xcs = self._src(src)
+                pw, _, _, _ = self._p(n, "W")
+                pb, _, _, _ = self._p(n, "b")
+                self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
+                           self.cs[n], _ACT[v["act"]], self.algo)
+            elif op == "bn":
+                x, xcs = self._src(v["in"][0])
+                s = self.shapes[n]
+                pg, _, _, _ = self._p(n, "gamma")
+                pbeta, _, _, _ = self._p(n, "beta")
+                pm, _, _, _ = self._p(n, "mean")
+                pv, _, _, _ = self._p(n, "var")
+                sm, ss = self.aux[n]
+                self._call("dl4jb200_bn_fwd", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm), self._ptr(ss),
+                           B, s[0], s[1], s[2], L.NHWC, xcs, float(v["decay"]), float(v["eps"]), int(train),
+                           int(self.model["minibatch"]), _ACT[v["act"]])
+            elif op == "pool":
+                d = self._pool_desc(v)
+                x, xcs = self._src(v["in"][0])
+                am = self._ptr(self.aux[n]) if v["type"] == "MAX" else None
+                self._call("dl4jb200_pool_fwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), am, L.NHWC, xcs, self.cs[n],
+                           _POOL[v["type"]], int(v.get("pnorm", 2)))
+            elif op == "add":
+                a, _ = self._src(v["in"][0])
+                b, _ = self._src(v["in"][1])
+                self._call("dl4jb200_add_act_fwd", self._ptr(a), self._ptr(b), self._ptr(self.out[n]), self.out[n].numel(),
+                           _ACT[v["act"]])
+            elif op == "act":
+                a, _ = self._src(v["in"][0])
+                self._call("dl4jb200_act_fwd", self._ptr(a), self._ptr(self.out[n]), a.numel(), _ACT[v["act"]])
+            elif op == "flatten":
+                x, xcs = self._src(v["in"][0])
+                s = self.shapes[v["in"][0]]
+                chw = s[0] * s[1] * s[2]
+                dst = self.out[n] if self.cs[n] == chw else self.aux[n]
+                self._call("dl4jb200_nhwc_to_nchw", self._ptr(x), self._ptr(dst), B, s[0], s[1], s[2], xcs)
+                if dst is not self.out[n]:
+                    self._call("dl4jb200_copy2d", self._ptr(dst), chw, self._ptr(self.out[n]), self.cs[n], B, chw)
+            elif op in ("dense", "output"):
+                x, xcs = self._src(v["in"][0])
+                d = self._dense_desc(v)
+                pw, _, _, _ = self._p(n, "W")
+                pb, _, _, _ = self._p(n, "b")
+                act = _ACT[v["act"]] if op == "dense" else L.ACT_IDENTITY
+                self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
+                           self.cs[n], act, self.algo)
+                if op == "output" and self.labels is not None:
+                    self._call("dl4jb200_softmax_nll", self._ptr(self.out[n]), self.cs[n], self._ptr(self.labels),
+                               self._ptr(self.aux[n]), self.cs[n], self._ptr(self.loss), B, v["nOut"])
+            else:
+                raise NotImplementedError(op)
+
+    def _pool_desc(self, v):
+        s_in, s_out = self.shapes[v["in"][0]], self.shapes[v["name"]]
+        k, st = v["kernel"], v["stride"]
+        m = _MODE[v["mode"]]
+        pt = _lib.out_size(s_in[1], k[0], st[0], v["pad"][0], 1, m)[1]
+        pl = _lib.out_size(s_in[2], k[1], st[1], v["pad"][1], 1, m)[1]
+        return ConvDesc(self.B, s_in[0], s_in[1], s_in[2], s_in[0], k[0], k[1], st[0], st[1], pt, pl, 1, 1, s_out[1], s_out[2])
+
+    # ------------------------------------------------------------------ backward (calcBackpropGradients)
+    def _eps_buf(self, u):
+        if u not in self.eps:
+            self.eps[u] = self.torch.zeros_like(self.out[u])
+        return self.eps[u]
+
+    def _needs_eps(self, u):
+        return self.vmap[u]["op"] not in ("input", "zeropad")
+
+    def _emit(self, u, fn):
+        """Run fn(ptr) producing dL/d(out[u]); the first producer writes eps[u] directly, later ones are summed
+        (ComputationGraph.java:2044-2063 epsilon fan-in)."""
+        if not self._needs_eps(u):
+            return
+        if self.out.get(u, 0) is None:  # flatten alias: pass straight through to its input
+            return self._emit(self.vmap[u]["in"][0], fn)
+        e = self._eps_buf(u)
+        if u not in self._written:
+            fn(self._ptr(e))
+            self._written.add(u)
+        else:
+            key = tuple(e.shape)
+            if key not in self.tmp_eps:
+                self.tmp_eps[key] = self.torch.zeros_like(e)
+            t = self.tmp_eps[key]
+            fn(self._ptr(t))
+            self._call("dl4jb200_accumulate", self._ptr(e), self._ptr(t), e.numel())
+
+    def _lend(self, u, tensor):
+        if not self._needs_eps(u):
+            return
+        if self.out.get(u, 0) is None:
+            return self._lend(self.vmap[u]["in"][0], tensor)
+        self._borrowed.setdefault(u, []).append(tensor)
+
+    def _resolve(self, n):
+        lent = self._borrowed.get(n, [])
+        if n in self._written:
+            e = self.eps[n]
+            for t in lent:
+                self._call("dl4jb200_accumulate", self._ptr(e), self._ptr(t), e.numel())
+            return e
+        if len(lent) == 1:
+            return lent[0]
+        if not lent:
+            raise RuntimeError(f"no epsilon reached vertex {n}")
+        e = self._eps_buf(n)
+        self._call("dl4jb200_memcpy_d2d", self._ptr(e), self._ptr(lent[0]), e.numel() * 4)
+        for t in lent[1:]:
+            self._call("dl4jb200_accumulate", self._ptr(e), self._ptr(t), e.numel())
+        return e
+
+    def backward(self):
+        L, B = _lib, self.B
+        self._written, self._borrowed = set(), {}
+        for v in reversed(self.model["vertices"]):
+            n, op = v["name"], v["op"]
+            self._cur = n
+            if op in ("input", "zeropad") or self.out.get(n, 0) is None:
+                continue
+            if op == "output":
+                e = self.aux[n]
+            else:
+                e = self._resolve(n)
+            if op in ("conv", "dense", "output"):
+                if op != "output" and v["act"] == "relu":  # delta = afn.backprop(z, eps); relu'(z) == (a > 0)
+                    self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(), L.ACT_RELU)
+                if op == "conv":
+                    src, d = self._conv_desc(v)
+                else:
+                    src, d = v["in"][0], self._dense_desc(v)
+                x, xcs = self._src(src)
+                pw, gw, _, _ = self._p(n, "W")
+                _, gb, _, _ = self._p(n, "b")
+
+                def run(dx, d=d, x=x, xcs=xcs, pw=pw, gw=gw, gb=gb, e=e, n=n):
+                    self._call("dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
+                               gw, gb, dx, L.NHWC, xcs, self.algo)
+                if self._needs_eps(src):
+                    self._emit(src, run)
+                else:
+                    run(None)
+            elif op == "bn":
+                u = v["in"][0]
+                x, xcs = self._src(u)
+                s = self.shapes[n]
+                pg, gg, _, _ = self._p(n, "gamma")
+                _, gbeta, _, _ = self._p(n, "beta")
+                sm, ss = self.aux[n]
+                ao = self._ptr(self.out[n]) if v["act"] == "relu" else None
+                self._emit(u, lambda dx: self._call("dl4jb200_bn_bwd", self._ptr(x), self._ptr(e), pg, self._ptr(sm), self._ptr(ss), ao,
+                                                    dx, gg, gbeta, B, s[0], s[1], s[2], L.NHWC, xcs))
+            elif op == "pool":
+                u = v["in"][0]
+                x, xcs = self._src(u)
+                d = self._pool_desc(v)
+                am = self._ptr(self.aux[n]) if v["type"] == "MAX" else None
+                self._emit(u, lambda dx: self._call("dl4jb200_pool_bwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), self._ptr(e), am,
+                                                    dx, L.NHWC, xcs, self.cs[n], _POOL[v["type"]], int(v.get("pnorm", 2)), 1e-8))
+            elif op in ("add", "act"):
+                if v["act"] != "identity":
+                    self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(), _ACT[v["act"]])
+                for u in v["in"]:
+                    self._lend(u, e)
+            elif op == "flatten":
+                u = v["in"][0]
+                s = self.shapes[u]
+                chw = s[0] * s[1] * s[2]
+                srcbuf = e
+                if self.cs[n] != chw:
+                    self._call("dl4jb200_copy2d", self._ptr(e), self.cs[n], self._ptr(self.aux[n]), chw, B, chw)
+                    srcbuf = self.aux[n]
+                self._emit(u, lambda dx: self._call("dl4jb200_nchw_to_nhwc", self._ptr(srcbuf), dx, B, s[0], s[1], s[2], self.cs[u]))
+            else:
+                raise NotImplementedError(op)
+
+    # ------------------------------------------------------------------ updater + step (BaseMultiLayerUpdater.update)
+    def _upd_args(self, cfg):
+        k = cfg["kind"]
+        if k == "rmsprop":
+            return _lib.UPD_RMSPROP, cfg["lr"], cfg["decay"], cfg["eps"]
+        if k == "nesterovs":
+            return _lib.UPD_NESTEROVS, cfg["lr"], cfg["momentum"], 0.0
+        if k == "adadelta":
+            return _lib.UPD_ADADELTA, 0.0, cfg["rho"], cfg["eps"]
+        if k == "sgd":
+            return _lib.UPD_SGD, cfg["lr"], 0.0, 0.0
+        raise NotImplementedError(k)
+
+    def update(self):
+        m = self.model
+        if m.get("grad_norm"):
+            raise NotImplementedError("gradient normalisation " + str(m["grad_norm"]))
+        div = float(self.B * self.batch_div_scale) if m["minibatch"] else 1.0
+        main = self._upd_args(m["updater"])
+        bias = self._upd_args(m.get("bias_updater", m["updater"]))
+        adadelta = m["updater"]["kind"] == "adadelta"
+        for name, key, off, shp, pk in self.layout:
+            if pk == "bn_stat":  # NoOp updater, gradient view is zero (BatchNormalization.java:205-208)
+                continue
+            n = int(np.prod(shp))
+            kind, lr, h1, h2 = bias if pk == "b" else main
+            l1, l2 = (m["l1"], m["l2"]) if pk == "w" else (0.0, 0.0)
+            if adadelta:
+                # AdaDelta keeps msg|msdx per updater block: block-local 2n layout inside the 2P state vector
+                st = self._ptr(self.state, 2 * off)
+            else:
+                st = self._ptr(self.state, off)
+            self._call("dl4jb200_updater_apply", self._ptr(self.params, off), self._ptr(self.grads, off), st, n, kind,
+                       float(lr), float(h1), float(h2), float(l1), float(l2), div)
+
+    def score_terms(self):
+        """Queues the L1/L2 part of the score (BaseOutputLayer.java:82-100): call before update()."""
+        m = self.model
+        self._call("dl4jb200_memset", self._ptr(self.score_reg), 0, 4)
+        if m["l1"] or m["l2"]:
+            for name, key, off, shp, pk in self.layout:
+                if pk == "w":
+                    self._call("dl4jb200_l1l2_score", self._ptr(self.params, off), int(np.prod(shp)), float(m["l1"]),
+                               float(m["l2"]), self._ptr(self.score_reg))
+
+    def fit(self, features=None, labels=None, hook=None):
+        """One MultiLayerNetwork/ComputationGraph.fit(DataSet) iteration. Returns the score tensor (device)."""
+        if features is not None:
+            self.set_batch(features, labels)
+        self.forward(True)
+        self.backward()
+        if self.with_score:
+            self.score_terms()
+        if hook is not None:
+            hook(self)  # data-parallel gradient exchange (parallel.py)
+        self.update()
+        with self.torch.cuda.stream(self.stream):
+            return (self.loss + self.score_reg) / float(self.B)
+
+    def sync(self):
+        """Host waits for everything queued on the network's stream (results are then safe to read from any stream)."""
+        self.stream.synchronize()
+
+    def output_host(self, name):
+        """NCHW host copy of a vertex activation (tests)."""
+        t, cs = self._src(name)
+        s = self.shapes[name]
+        self.stream.synchronize()
+        a = t.cpu().numpy()
+        if len(s) == 3:
+            return np.ascontiguousarray(a[..., :s[0]].transpose(0, 3, 1, 2))
+        return a[:, :s[0]].copy()
+
+    def close(self):
+        if self.h:
+            self.torch.cuda.synchronize(self.dev)
+            _lib.call("dl4jb200_ctx_destroy", self.h)
+            self.h = None

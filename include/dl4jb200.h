@@ -91,6 +91,8 @@ typedef struct dl4jb200_conv_desc {
 /* ------------------------------------------------------------------ runtime ------------------ */
 const char *dl4jb200_last_error(void);
 int dl4jb200_version(void);
+/* number of CUDA kernels this library has launched in this process (diagnostics / bench accounting) */
+unsigned long long dl4jb200_launch_count(void);
 
 /* One context per (worker thread, device): ParallelWrapper pins each worker thread to one device for
  * life (deeplearning4j-scaleout/.../parallelism/ParallelWrapper.java:125-141). stream == NULL makes the
@@ -143,8 +145,8 @@ int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
                       const float *w, const float *bias, float *z, int z_layout, int z_cs, int act, int algo);
 
 /* ConvolutionHelper.backpropGradient (ConvolutionHelper.java:37-40; CPU semantics
- * ConvolutionLayer.java:202-257). delta = dL/dz (the Java helper applies afn.backprop first, as
- * CudnnConvolutionHelper.java:212 does). dw / db are the weightGradView / biasGradView: written IN PLACE,
+ * ConvolutionLayer.java:202-257). delta = dL/dz (the layer applies afn.backprop before calling the helper,
+ * ConvolutionLayer.java:170-171). dw / db are the weightGradView / biasGradView: written IN PLACE,
  * overwritten (not accumulated), summed over the batch, DL4J layout. db and dx may be NULL. */
 int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs,
                       const float *w, const float *delta, int delta_layout, int delta_cs, float *dw, float *db,
@@ -204,9 +206,17 @@ int dl4jb200_add_act_fwd(dl4jb200_ctx *ctx, const float *a, const float *b, floa
 /* ComputationGraph epsilon fan-in: dst += src (NN/nn/graph/ComputationGraph.java:2044-2063) */
 int dl4jb200_accumulate(dl4jb200_ctx *ctx, float *dst, const float *src, size_t n);
 /* softmax + NEGATIVELOGLIKELIHOOD / MCXENT output layer: p = softmax(z) row-wise, delta = p - labels,
- * loss_sum_out[0] = -sum labels*log p (device scalar). NN/nn/layers/BaseOutputLayer.java:82-100,147-190 */
-int dl4jb200_softmax_nll(dl4jb200_ctx *ctx, const float *z, const float *labels, float *delta, float *loss_sum_out,
-                         int B, int K);
+ * loss_sum_out[0] = -sum labels*log p (device scalar). z / delta rows are z_ld / delta_ld floats apart
+ * (>= K; delta's padding columns are zeroed); labels is dense [B,K].
+ * NN/nn/layers/BaseOutputLayer.java:82-100,147-190 */
+int dl4jb200_softmax_nll(dl4jb200_ctx *ctx, const float *z, int z_ld, const float *labels, float *delta, int delta_ld,
+                         float *loss_sum_out, int B, int K);
+/* Regularisation part of the score: score_acc[0] += l1*sum|w| + 0.5*l2*sum w^2 over n weights
+ * (ConvolutionLayer.calcL1/calcL2, NN/nn/layers/convolution/ConvolutionLayer.java:98-123; BaseLayer likewise). */
+int dl4jb200_l1l2_score(dl4jb200_ctx *ctx, const float *w, size_t n, double l1, double l2, float *score_acc);
+/* Row-strided copy dst[r, 0:cols] = src[r, 0:cols], dst[r, cols:dst_ld] = 0 (CnnToFeedForwardPreProcessor
+ * reshape when the row length is not a multiple of the 4-float channel granule). */
+int dl4jb200_copy2d(dl4jb200_ctx *ctx, const float *src, int src_ld, float *dst, int dst_ld, int rows, int cols);
 /* One updater block over n contiguous floats of the flat vectors: u = Updater(g); u += l2*w;
  * u += l1*sign(w); u /= batch_div; w -= u. state: n floats (2n for ADADELTA), may be NULL for SGD/NOOP.
  * NN/nn/updater/UpdaterBlock.java:142,170-193; BaseMultiLayerUpdater.java:296-307;

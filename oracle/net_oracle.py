@@ -1,0 +1,178 @@
+"""CPU restatement of one DL4J training iteration on a zoo-style model graph (TEST INFRASTRUCTURE ONLY).
+
+Follows computeGradientAndScore -> updater -> params.subi exactly as SURVEY.md Appendix A states it
+(nn/multilayer/MultiLayerNetwork.java:2360-2420; nn/graph/ComputationGraph.java:1321-1360, 2044-2063 for the
+epsilon fan-in; nn/updater/BaseMultiLayerUpdater.java:223-309; optimize/solvers/StochasticGradientDescent.java:78).
+The model dict and the flat parameter layout are passed in by the caller (tests / bench); nothing here is
+imported by the product package. fast=True runs the reference's literal im2col + BLAS sgemm + col2im pipeline in
+fp32 (the form timed as the CPU baseline); fast=False runs the direct double-accumulate form (parity oracle).
+"""
+import numpy as np
+
+from . import oracle as o
+
+_ACT = {"identity": o.ACT_IDENTITY, "relu": o.ACT_RELU, "sigmoid": o.ACT_SIGMOID, "tanh": o.ACT_TANH}
+_MODE = {"Strict": o.STRICT, "Truncate": o.TRUNCATE, "Same": o.SAME}
+_POOL = {"MAX": o.POOL_MAX, "AVG": o.POOL_AVG, "PNORM": o.POOL_PNORM}
+
+
+class OracleNet:
+    def __init__(self, model, layout, P, params, fast=False):
+        self.model, self.layout, self.P, self.fast = model, layout, P, fast
+        self.params = np.ascontiguousarray(params, np.float32).copy()
+        self.grads = np.zeros(P, np.float32)
+        k = model["updater"]["kind"]
+        self.state = np.zeros(P * (2 if k == "adadelta" else 1), np.float32)
+        self.pidx = {(n, key): (off, int(np.prod(shp)), shp, pk) for n, key, off, shp, pk in layout}
+        self.vmap = {v["name"]: v for v in model["vertices"]}
+
+    def _p(self, n, key, arr=None):
+        off, cnt, shp, _ = self.pidx[(n, key)]
+        a = self.params if arr is None else arr
+        return a[off:off + cnt].reshape(shp)
+
+    def forward(self, x, labels=None, train=True):
+        m = self.model
+        act = {}
+        self.bn_saved = {}
+        for v in m["vertices"]:
+            n, op = v["name"], v["op"]
+            if op == "input":
+                act[n] = np.ascontiguousarray(x, np.float32)
+                continue
+            a = act[v["in"][0]]
+            if op == "zeropad":
+                t, b, l, r = v["pad"]
+                act[n] = np.pad(a, ((0, 0), (0, 0), (t, b), (l, r)))
+            elif op == "conv":
+                f = o.conv_fwd_im2col if self.fast else o.conv_fwd
+                z = f(a, self._p(n, "W"), self._p(n, "b"), stride=v["stride"], pad=v["pad"], dilation=v["dilation"],
+                      mode=_MODE[v["mode"]])
+                act[n] = o.act_fwd(z, _ACT[v["act"]]) if v["act"] != "identity" else z
+            elif op == "bn":
+                y, mean, std = o.bn_fwd(a, self._p(n, "gamma"), self._p(n, "beta"), self._p(n, "mean"), self._p(n, "var"),
+                                        v["decay"], v["eps"], train, m["minibatch"])
+                self.bn_saved[n] = (mean, std, y)
+                act[n] = o.act_fwd(y, _ACT[v["act"]]) if v["act"] != "identity" else y
+            elif op == "pool":
+                act[n] = o.pool_fwd(a, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]])
+            elif op == "add":
+                s = a + act[v["in"][1]]
+                act[n] = o.act_fwd(s, _ACT[v["act"]]) if v["act"] != "identity" else s
+            elif op == "act":
+                act[n] = o.act_fwd(a, _ACT[v["act"]])
+            elif op == "flatten":
+                act[n] = a.reshape(a.shape[0], -1)
+            elif op in ("dense", "output"):
+                if self.fast:
+                    z = a @ self._p(n, "W").T + self._p(n, "b")[None, :]
+                else:
+                    z = o.dense_fwd(a, self._p(n, "W"), self._p(n, "b"))
+                if op == "dense":
+                    act[n] = o.act_fwd(z, _ACT[v["act"]]) if v["act"] != "identity" else z
+                else:
+                    act[n] = z
+                    if labels is not None:
+                        self.loss, self.probs, self.delta = o.softmax_nll(z, labels)
+            else:
+                raise NotImplementedError(op)
+        self.act = act
+        return act
+
+    def backward(self):
+        m, act = self.model, self.act
+        eps = {}
+
+        def give(u, e):
+            if self.vmap[u]["op"] in ("input",):
+                return
+            eps[u] = e if u not in eps else eps[u] + e
+
+        for v in reversed(m["vertices"]):
+            n, op = v["name"], v["op"]
+            if op == "input":
+                continue
+            u = v["in"][0]
+            e = self.delta if op == "output" else eps.get(n)
+            if e is None:
+                continue
+            if op == "zeropad":
+                t, b, l, r = v["pad"]
+                give(u, np.ascontiguousarray(e[:, :, t:e.shape[2] - b, l:e.shape[3] - r]))
+            elif op == "conv":
+                d = o.act_bwd(act[n], e, _ACT[v["act"]]) if v["act"] == "relu" else e
+                f = o.conv_bwd_im2col if self.fast else o.conv_bwd
+                dw, db, dx = f(act[u], self._p(n, "W"), d, stride=v["stride"], pad=v["pad"], dilation=v["dilation"],
+                               mode=_MODE[v["mode"]])
+                self._p(n, "W", self.grads)[...] = dw
+                self._p(n, "b", self.grads)[...] = db
+                give(u, dx)
+            elif op in ("dense", "output"):
+                d = o.act_bwd(act[n], e, _ACT[v["act"]]) if (op == "dense" and v["act"] == "relu") else e
+                if self.fast:
+                    dwf, db, dx = d.T @ act[u], d.sum(0), d @ self._p(n, "W")
+                else:
+                    dwf, db, dx = o.dense_bwd(act[u], self._p(n, "W"), d)
+                self._p(n, "W", self.grads)[...] = dwf
+                self._p(n, "b", self.grads)[...] = db
+                give(u, dx)
+            elif op == "bn":
+                mean, std, y = self.bn_saved[n]
+                d = o.act_bwd(y, e, _ACT[v["act"]]) if v["act"] == "relu" else e
+                dx, dg, dbt = o.bn_bwd(act[u], d, self._p(n, "gamma"), mean, std)
+                self._p(n, "gamma", self.grads)[...] = dg
+                self._p(n, "beta", self.grads)[...] = dbt
+                self._p(n, "mean", self.grads)[...] = 0  # BatchNormalization.java:205-208
+                self._p(n, "var", self.grads)[...] = 0
+                give(u, dx)
+            elif op == "pool":
+                give(u, o.pool_bwd(act[u], e, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]]))
+            elif op in ("add", "act"):
+                d = o.act_bwd(act[n], e, _ACT[v["act"]]) if v["act"] == "relu" else e
+                for uu in v["in"]:
+                    give(uu, d)
+            elif op == "flatten":
+                give(u, e.reshape(act[u].shape))
+            else:
+                raise NotImplementedError(op)
+
+    def _upd(self, cfg):
+        k = cfg["kind"]
+        if k == "rmsprop":
+            return o.UPD_RMSPROP, dict(lr=cfg["lr"], h1=cfg["decay"], h2=cfg["eps"])
+        if k == "nesterovs":
+            return o.UPD_NESTEROVS, dict(lr=cfg["lr"], h1=cfg["momentum"])
+        if k == "adadelta":
+            return o.UPD_ADADELTA, dict(h1=cfg["rho"], h2=cfg["eps"])
+        return o.UPD_SGD, dict(lr=cfg["lr"])
+
+    def score(self, B):
+        m = self.model
+        reg = 0.0
+        for n, key, off, shp, pk in self.layout:
+            if pk == "w":
+                w = self.params[off:off + int(np.prod(shp))].astype(np.float64)
+                reg += m["l1"] * np.abs(w).sum() + 0.5 * m["l2"] * (w * w).sum()
+        return (self.loss + reg) / B
+
+    def update(self, B):
+        m = self.model
+        div = float(B) if m["minibatch"] else 1.0
+        main, bias = self._upd(m["updater"]), self._upd(m.get("bias_updater", m["updater"]))
+        ada = m["updater"]["kind"] == "adadelta"
+        for n, key, off, shp, pk in self.layout:
+            if pk == "bn_stat":
+                continue
+            cnt = int(np.prod(shp))
+            kind, args = bias if pk == "b" else main
+            l1, l2 = (m["l1"], m["l2"]) if pk == "w" else (0.0, 0.0)
+            st = self.state[2 * off:2 * off + 2 * cnt] if ada else self.state[off:off + cnt]
+            o.updater_apply(self.params[off:off + cnt], self.grads[off:off + cnt], st, kind, l1=l1, l2=l2, batch_div=div, **args)
+
+    def fit(self, x, labels):
+        B = x.shape[0]
+        self.forward(x, labels, True)
+        self.backward()
+        s = self.score(B)
+        self.update(B)
+        return s

@@ -361,7 +361,7 @@ def test_elementwise_softmax_updater(H, ctx, oracle):
         lab = np.zeros((B, K), np.float32)
         lab[:, 1] = 1
         pz, pl, pd, ploss = dev.put(z), dev.put(lab), dev.empty(B * K * 4), dev.empty(4)
-        _lib.call("dl4jb200_softmax_nll", ctx.handle, pz, pl, pd, ploss, B, K)
+        _lib.call("dl4jb200_softmax_nll", ctx.handle, pz, K, pl, pd, K, ploss, B, K)
         loss_r, _, delta_r = oracle.softmax_nll(z, lab)
         assert rel_err(dev.get(pd, (B, K)), delta_r) <= TOL_BW
         assert abs(dev.get(ploss, (1,))[0] - loss_r) <= 1e-5 * abs(loss_r)

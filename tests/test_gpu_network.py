@@ -1,0 +1,123 @@
+"""-m gpu parity of the device-resident training step against the CPU restatement of one DL4J
+iteration: score, flat gradient vector and post-update flat parameter vector after fit() on identical
+host-generated parameters and BenchmarkDataSetIterator-style data (U[0,1) features, every label = class 1)."""
+import numpy as np
+import pytest
+
+from gpu_util import rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _data(model, B, K, seed=12345):
+    rng = np.random.default_rng(seed)
+    x = rng.random((B,) + tuple(model["input"]), dtype=np.float32)
+    lab = np.zeros((B, K), np.float32)
+    lab[:, 1] = 1.0
+    return x, lab
+
+
+def _block_errs(layout, got, ref, floor, skip=()):
+    """Per parameter block: max|got-ref| / max(max|ref|, floor). The floor keeps blocks whose true value is ~0 -- the
+    bias gradient of a convolution that feeds a BatchNormalization is analytically zero -- from being judged on noise."""
+    worst = {}
+    for name, key, off, shp, pk in layout:
+        if (name, key) in skip:
+            continue
+        n = int(np.prod(shp))
+        g, r = got[off:off + n].astype(np.float64), ref[off:off + n].astype(np.float64)
+        worst[(name, key)] = float(np.abs(g - r).max() / max(np.abs(r).max(), floor))
+    return worst
+
+
+def _noise_blocks(layout, ref_grads):
+    """Blocks whose reference gradient is numerically zero (|g| < 1e-5 of the largest gradient): their update is
+    round-off noise passed through the adaptive updater, different on every implementation."""
+    gmax = float(np.abs(ref_grads).max())
+    return {(n, k) for n, k, off, shp, pk in layout
+            if float(np.abs(ref_grads[off:off + int(np.prod(shp))]).max()) < 1e-5 * gmax}
+
+
+def _tiny_resnet():
+    """conv block + identity block at toy sizes: exercises BN+ReLU fusion, Add fan-in, strided 1x1, SAME 3x3."""
+    from deeplearning4j_b200 import zoo
+    v = [{"name": "input", "op": "input", "in": []},
+         {"name": "zp", "op": "zeropad", "in": ["input"], "pad": (3, 3, 3, 3)},
+         zoo._conv("stem", "zp", 16, (7, 7), (2, 2)), zoo._bn("stem_bn", "stem", "relu"),
+         zoo._pool("stem_pool", "stem_bn", "MAX", (3, 3), (2, 2)),
+         zoo._conv("a2a", "stem_pool", 8, (1, 1), (2, 2)), zoo._bn("a2a_bn", "a2a", "relu"),
+         zoo._conv("a2b", "a2a_bn", 8, (3, 3), mode="Same"), zoo._bn("a2b_bn", "a2b", "relu"),
+         zoo._conv("a2c", "a2b_bn", 32, (1, 1)), zoo._bn("a2c_bn", "a2c"),
+         zoo._conv("a1", "stem_pool", 32, (1, 1), (2, 2)), zoo._bn("a1_bn", "a1"),
+         {"name": "a_add", "op": "add", "in": ["a2c_bn", "a1_bn"], "act": "relu"},
+         zoo._conv("b2a", "a_add", 8, (1, 1)), zoo._bn("b2a_bn", "b2a", "relu"),
+         zoo._conv("b2b", "b2a_bn", 8, (3, 3), mode="Same"), zoo._bn("b2b_bn", "b2b", "relu"),
+         zoo._conv("b2c", "b2b_bn", 32, (1, 1)), zoo._bn("b2c_bn", "b2c"),
+         {"name": "b_add", "op": "add", "in": ["b2c_bn", "a_add"], "act": "relu"},
+         zoo._pool("head", "b_add", "MAX", (3, 3), (2, 2)),
+         {"name": "flat", "op": "flatten", "in": ["head"]},
+         {"name": "output", "op": "output", "in": ["flat"], "nOut": 10}]
+    return {"name": "tiny_resnet", "input": (3, 33, 33), "vertices": v, "weight_init": ("normal", 0.5),
+            "updater": {"kind": "rmsprop", "lr": 0.1, "decay": 0.96, "eps": 1e-3}, "l1": 1e-7, "l2": 5e-5,
+            "minibatch": True, "grad_norm": None, "seed": 123}
+
+
+def _run_case(model, B, K, algo, steps, fast_oracle, tol_grad, tol_param, tol_score):
+    from deeplearning4j_b200 import network, zoo
+    from oracle.net_oracle import OracleNet
+    P, layout = zoo.param_layout(model)
+    p0 = zoo.init_params(model)
+    x, lab = _data(model, B, K)
+    ref = OracleNet(model, layout, P, p0, fast=fast_oracle)
+    net = network.Network(model, B, algo=algo, params=p0)
+    try:
+        for it in range(steps):
+            s_ref = ref.fit(x, lab)
+            s = net.fit(x, lab)
+            net.sync()
+            s = float(s.cpu()[0])
+            g = net.grads.cpu().numpy()
+            p = net.params.cpu().numpy()
+            assert abs(s - s_ref) <= tol_score * max(1.0, abs(s_ref)), (it, s, s_ref)
+            ge = _block_errs(layout, g, ref.grads, 1e-3 * float(np.abs(ref.grads).max()))
+            worst = max(ge.items(), key=lambda kv: kv[1])
+            assert worst[1] <= tol_grad, ("grad", it, worst)
+            pe = _block_errs(layout, p, ref.params, 1e-3 * float(np.abs(ref.params).max()), _noise_blocks(layout, ref.grads))
+            worstp = max(pe.items(), key=lambda kv: kv[1])
+            assert worstp[1] <= tol_param, ("param", it, worstp)
+        return worst[1], worstp[1]
+    finally:
+        net.close()
+
+
+@pytest.mark.parametrize("algo_name", ["fp32", "tf32"])
+def test_lenet_step_parity(algo_name):
+    from deeplearning4j_b200 import _lib, zoo
+    algo = _lib.ALGO_FP32 if algo_name == "fp32" else _lib.ALGO_TC_TF32
+    # whole-step TF32 bound: per-layer TF32 error (<= 2e-3) is amplified by the softmax (d p / p = d z, |z| ~ 10 for
+    # an untrained net on U[0,1) inputs) before it reaches the gradients
+    tol = 1e-4 if algo_name == "fp32" else 5e-2
+    _run_case(zoo.lenet(), 16, 10, algo, 2, False, tol, tol, 5e-3 if algo_name == "tf32" else tol)
+
+
+@pytest.mark.parametrize("algo_name", ["fp32", "tf32"])
+def test_tiny_resnet_step_parity(algo_name):
+    from deeplearning4j_b200 import _lib
+    algo = _lib.ALGO_FP32 if algo_name == "fp32" else _lib.ALGO_TC_TF32
+    # BN backward divides by small batch std: fp32 round-off is amplified; TF32 operand truncation adds ~1e-3/layer
+    tol = 2e-4 if algo_name == "fp32" else 2e-1
+    _run_case(_tiny_resnet(), 8, 10, algo, 2 if algo_name == "fp32" else 1, False, tol, tol, 5e-3 if algo_name == "tf32" else tol)
+
+
+def test_vgg_like_step_parity():
+    from deeplearning4j_b200 import _lib, zoo
+    m = zoo.vgg16(num_labels=10, input_shape=(3, 32, 32))
+    _run_case(m, 4, 10, _lib.ALGO_FP32, 1, True, 2e-4, 2e-4, 2e-4)
+    _run_case(m, 4, 10, _lib.ALGO_TC_TF32, 1, True, 2e-1, 2e-1, 5e-3)
+
+
+def test_resnet50_step_parity_small_batch():
+    """The BASELINE model itself (224x224, 1000 classes) at batch 4 against the im2col+BLAS CPU pipeline."""
+    from deeplearning4j_b200 import _lib, zoo
+    m = zoo.resnet50()
+    _run_case(m, 4, 1000, _lib.ALGO_FP32, 1, True, 5e-3, 5e-3, 1e-3)
