@@ -38,22 +38,38 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__r
                 k.x = c + 0 < center_stride ? center[c + 0] : 0.f; k.y = c + 1 < center_stride ? center[c + 1] : 0.f;
                 k.z = c + 2 < center_stride ? center[c + 2] : 0.f; k.w = c + 3 < center_stride ? center[c + 3] : 0.f;
             }
-            for (int r = r0 + rl; r < r1; r += R) {
-                size_t o = (size_t)r * cs + (size_t)q * 4;
-                float4 v = *reinterpret_cast<const float4 *>(x + o);
-                v.x -= k.x; v.y -= k.y; v.z -= k.z; v.w -= k.w;
-                if (MODE == 0) {
-                    a1.x += v.x; a1.y += v.y; a1.z += v.z; a1.w += v.w;
-                    a2.x += v.x * v.x; a2.y += v.y * v.y; a2.z += v.z * v.z; a2.w += v.w * v.w;
-                } else {
-                    float4 g = *reinterpret_cast<const float4 *>(e + o);
-                    if (act_out) {
-                        float4 m = *reinterpret_cast<const float4 *>(act_out + o);
-                        g.x = m.x > 0.f ? g.x : 0.f; g.y = m.y > 0.f ? g.y : 0.f;
-                        g.z = m.z > 0.f ? g.z : 0.f; g.w = m.w > 0.f ? g.w : 0.f;
+            constexpr int U = 4;  // independent loads in flight per thread (latency hiding)
+            for (int rb = r0 + rl; rb < r1; rb += U * R) {
+                float4 v[U], g[U], m[U];
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    int r = rb + u * R;
+                    size_t o = (size_t)r * cs + (size_t)q * 4;
+                    if (r < r1) {
+                        v[u] = *reinterpret_cast<const float4 *>(x + o);
+                        if (MODE == 1) {
+                            g[u] = *reinterpret_cast<const float4 *>(e + o);
+                            if (act_out) m[u] = *reinterpret_cast<const float4 *>(act_out + o);
+                        }
                     }
-                    a1.x += g.x; a1.y += g.y; a1.z += g.z; a1.w += g.w;
-                    a2.x += g.x * v.x; a2.y += g.y * v.y; a2.z += g.z * v.z; a2.w += g.w * v.w;
+                }
+#pragma unroll
+                for (int u = 0; u < U; u++) {
+                    if (rb + u * R >= r1) break;
+                    float4 w = v[u];
+                    w.x -= k.x; w.y -= k.y; w.z -= k.z; w.w -= k.w;
+                    if (MODE == 0) {
+                        a1.x += w.x; a1.y += w.y; a1.z += w.z; a1.w += w.w;
+                        a2.x += w.x * w.x; a2.y += w.y * w.y; a2.z += w.z * w.z; a2.w += w.w * w.w;
+                    } else {
+                        float4 gg = g[u];
+                        if (act_out) {
+                            gg.x = m[u].x > 0.f ? gg.x : 0.f; gg.y = m[u].y > 0.f ? gg.y : 0.f;
+                            gg.z = m[u].z > 0.f ? gg.z : 0.f; gg.w = m[u].w > 0.f ? gg.w : 0.f;
+                        }
+                        a1.x += gg.x; a1.y += gg.y; a1.z += gg.z; a1.w += gg.w;
+                        a2.x += gg.x * w.x; a2.y += gg.y * w.y; a2.z += gg.z * w.z; a2.w += gg.w * w.w;
+                    }
                 }
             }
         }
@@ -133,20 +149,38 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nchw(const float *__r
 // ------------------------------------------------------------------ pass 2: finalize (one thread per channel)
 // coef layout: [4][cpad] = centre, a, b, c   with  y = (x-centre)*a + c            (forward; b unused)
 //                                              dx = a*e + b*(x-centre) + c          (backward)
+// Folds partial[nblk][2][cpad] for channel c over the 8 threads (threadIdx.y) that share it; result valid for y == 0.
+__device__ __forceinline__ void bn_fold_partials(const float *__restrict__ partial, int nblk, int cpad, int c, bool active,
+                                                 double &s1, double &s2) {
+    __shared__ double sh1[8][33], sh2[8][33];
+    double a = 0.0, b = 0.0;
+    if (active)
+        for (int i = threadIdx.y; i < nblk; i += 8) {
+            a += (double)partial[(size_t)i * 2 * cpad + c];
+            b += (double)partial[(size_t)i * 2 * cpad + cpad + c];
+        }
+    sh1[threadIdx.y][threadIdx.x] = a;
+    sh2[threadIdx.y][threadIdx.x] = b;
+    __syncthreads();
+    s1 = 0.0; s2 = 0.0;
+    if (threadIdx.y == 0)
+        for (int j = 0; j < 8; j++) { s1 += sh1[j][threadIdx.x]; s2 += sh2[j][threadIdx.x]; }
+}
+
 __global__ void k_bn_finalize_fwd(const float *__restrict__ partial, int nblk, const float *__restrict__ pivot,
                                   int pivot_stride, const float *__restrict__ gamma, const float *__restrict__ beta,
                                   float *gmean, float *gvar, float *save_mean, float *save_std, float *coef, int C,
                                   int cpad, double N, double decay, double eps, int training, int minibatch) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= cpad) return;
+    int c = blockIdx.x * 32 + threadIdx.x;
+    double s1, s2;
+    bn_fold_partials(partial, training ? nblk : 0, cpad, c, c < C, s1, s2);
+    if (threadIdx.y != 0 || c >= cpad) return;
     if (c >= C) {  // NHWC padding channel: stays zero
         coef[c] = 0.f; coef[cpad + c] = 0.f; coef[2 * cpad + c] = 0.f; coef[3 * cpad + c] = 0.f;
         return;
     }
     double mean, std;
     if (training) {
-        double s1 = 0.0, s2 = 0.0;
-        for (int b = 0; b < nblk; b++) { s1 += (double)partial[(size_t)b * 2 * cpad + c]; s2 += (double)partial[(size_t)b * 2 * cpad + cpad + c]; }
         double k = (double)pivot[(size_t)c * pivot_stride];
         double m1 = s1 / N;
         mean = k + m1;                              // BatchNormalization.java:264
@@ -177,14 +211,14 @@ __global__ void k_bn_finalize_fwd(const float *__restrict__ partial, int nblk, c
 __global__ void k_bn_finalize_bwd(const float *__restrict__ partial, int nblk, const float *__restrict__ gamma,
                                   const float *__restrict__ save_mean, const float *__restrict__ save_std,
                                   float *dgamma, float *dbeta, float *coef, int C, int cpad, double N) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= cpad) return;
+    int c = blockIdx.x * 32 + threadIdx.x;
+    double s1, s2;
+    bn_fold_partials(partial, nblk, cpad, c, c < C, s1, s2);
+    if (threadIdx.y != 0 || c >= cpad) return;
     if (c >= C) {
         coef[c] = 0.f; coef[cpad + c] = 0.f; coef[2 * cpad + c] = 0.f; coef[3 * cpad + c] = 0.f;
         return;
     }
-    double s1 = 0.0, s2 = 0.0;
-    for (int b = 0; b < nblk; b++) { s1 += (double)partial[(size_t)b * 2 * cpad + c]; s2 += (double)partial[(size_t)b * 2 * cpad + cpad + c]; }
     double std = (double)save_std[c], g = gamma ? (double)gamma[c] : 1.0;
     // BatchNormalization.java:172-196 with dxhat = e*gamma:
     //   dVar = sum(dxhat*xMu) * -0.5 * std^-3 ; dMu = -sum(dxhat)/std (+ dVar*(-2/N)*sum xMu, sum xMu == 0)
@@ -339,7 +373,7 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
         }
         DL4J_CHECK_LAUNCH();
     }
-    k_bn_finalize_fwd<<<dl4j_ceil_div(p.cpad, 128), 128, 0, ctx->stream>>>(
+    k_bn_finalize_fwd<<<dl4j_ceil_div(p.cpad, 32), dim3(32, 8), 0, ctx->stream>>>(
         p.partial, p.nblk, x, layout == DL4JB200_NHWC ? 1 : HW, gamma, beta, gmean, gvar, save_mean, save_std, p.coef, C,
         p.cpad, (double)M, decay, eps, training, minibatch);
     DL4J_CHECK_LAUNCH();
@@ -377,7 +411,7 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
         else k_bn_partial_nchw<1, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, act_out, save_mean, p.partial, B, C, HW, p.chunk);
     }
     DL4J_CHECK_LAUNCH();
-    k_bn_finalize_bwd<<<dl4j_ceil_div(p.cpad, 128), 128, 0, ctx->stream>>>(p.partial, p.nblk, gamma, save_mean, save_std,
+    k_bn_finalize_bwd<<<dl4j_ceil_div(p.cpad, 32), dim3(32, 8), 0, ctx->stream>>>(p.partial, p.nblk, gamma, save_mean, save_std,
                                                                          dgamma, dbeta, p.coef, C, p.cpad, (double)M);
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {

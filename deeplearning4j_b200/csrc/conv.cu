@@ -12,6 +12,7 @@ static void geom_finish(ConvGeom &g) {
     g.div_HWm = FastDiv((uint32_t)(g.Hm * g.Wm));
     g.div_Cg = FastDiv((uint32_t)g.Cg);
     g.div_kW = FastDiv((uint32_t)g.kW);
+    g.fast = g.kH <= 16 && g.kW <= 16 && (!g.transposed || (g.sH == 1 && g.sW == 1) || g.taps == 1);
 }
 
 ConvGeom conv_geom_fwd(const dl4jb200_conv_desc *d, int x_cs) {
@@ -100,12 +101,20 @@ __global__ void __launch_bounds__(256) k_colsum_partial(const float *__restrict_
         __syncthreads();
     }
 }
+// blockDim = (32 channels, 8 partial-row groups)
 __global__ void k_colsum_final(const float *__restrict__ partial, float *__restrict__ out, int nblk, int cs, int C) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
+    __shared__ double sh[8][33];
+    int c = blockIdx.x * 32 + threadIdx.x;
     double acc = 0.0;
-    for (int b = 0; b < nblk; b++) acc += (double)partial[(size_t)b * cs + c];
-    out[c] = (float)acc;
+    if (c < C)
+        for (int b = threadIdx.y; b < nblk; b += 8) acc += (double)partial[(size_t)b * cs + c];
+    sh[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < C) {
+        double t = 0.0;
+        for (int j = 0; j < 8; j++) t += sh[j][threadIdx.x];
+        out[c] = (float)t;
+    }
 }
 
 static inline int grid_for(dl4jb200_ctx *ctx, size_t items) {
@@ -222,7 +231,9 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     // ---- data gradient operand sizes (computed first so that one scratch request covers everything)
     ConvGeom gb = conv_geom_bwd_data(d, delta_cs);
     const int rows_b = dx ? dl4j_round_up(dx_cs > d->c_in ? dx_cs : d->c_in, 128) : 0;
-    const int nblk = gf.M < 4096 ? 1 : (gf.M / 1024 > ctx->sm_count * 4 ? ctx->sm_count * 4 : gf.M / 1024);
+    int nblk = gf.M / 8;  // bias-gradient partial blocks: >= 8 pixel rows each, up to 4 per SM
+    if (nblk > ctx->sm_count * 4) nblk = ctx->sm_count * 4;
+    if (nblk < 1) nblk = 1;
     size_t part_f = (size_t)splits * rows_w * gf.Kp, pack_f = (size_t)rows_b * gb.Kp, col_f = (size_t)nblk * delta_cs;
     float *ws = (float *)dl4j_workspace(ctx, 0, (part_f + pack_f + col_f) * sizeof(float));
     if (!ws) return DL4JB200_ERR_CUDA;
@@ -238,7 +249,7 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     if (db) {
         k_colsum_partial<<<nblk, 256, 0, ctx->stream>>>(ds, colp, gf.M, delta_cs);
         DL4J_CHECK_LAUNCH();
-        k_colsum_final<<<dl4j_ceil_div(d->c_out, 128), 128, 0, ctx->stream>>>(colp, db, nblk, delta_cs, d->c_out);
+        k_colsum_final<<<dl4j_ceil_div(d->c_out, 32), dim3(32, 8), 0, ctx->stream>>>(colp, db, nblk, delta_cs, d->c_out);
         DL4J_CHECK_LAUNCH();
     }
 

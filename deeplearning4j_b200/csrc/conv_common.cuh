@@ -15,6 +15,7 @@ struct ConvGeom {
     int kH, kW, sH, sW, pT, pL, dH, dW;
     int Cg, taps, K, Kp, M;
     int transposed;         // 0: iy = y*sH - pT + kh*dH      1: iy = (y + pT - kh*dH)/sH when divisible
+    int fast;               // taps are an affine offset from a per-row base pointer (see conv_row_setup)
     FastDiv div_Wm, div_HWm, div_Cg, div_kW;
 };
 
@@ -51,6 +52,32 @@ __device__ __forceinline__ long long conv_src_offset(const ConvGeom &g, int b, i
     }
     if (iy >= g.Hs || ix >= g.Ws) return -1;
     return (((long long)b * g.Hs + iy) * g.Ws + ix) * g.cs_src;
+}
+
+// Fast gather set-up for one GEMM row (g.fast): element offset of the row's tap-(0,0) source pixel and a validity
+// mask -- bit kh says "tap row kh is inside the image", bit 16+kw the same for tap column kw -- so that per K-chunk a
+// producer needs only `rowoff + tapoff` and one mask test per 16-byte copy.
+__device__ __forceinline__ void conv_row_setup(const ConvGeom &g, int m, long long &rowoff, uint32_t &mask) {
+    int b, y0, x0;
+    conv_m_decode(g, m, b, y0, x0);
+    mask = 0;
+    if (g.transposed && (g.sH != 1 || g.sW != 1)) {  // 1x1 strided backprop-data: a single tap
+        int iy = y0 / g.sH, ix = x0 / g.sW;
+        bool ok = y0 >= 0 && x0 >= 0 && iy * g.sH == y0 && ix * g.sW == x0 && iy < g.Hs && ix < g.Ws;
+        rowoff = ok ? (((long long)b * g.Hs + iy) * g.Ws + ix) * g.cs_src : 0;
+        mask = ok ? 0x00010001u : 0u;
+        return;
+    }
+    const int sgn = g.transposed ? -1 : 1;
+    for (int kh = 0; kh < g.kH; kh++) { int iy = y0 + sgn * kh * g.dH; if (iy >= 0 && iy < g.Hs) mask |= 1u << kh; }
+    for (int kw = 0; kw < g.kW; kw++) { int ix = x0 + sgn * kw * g.dW; if (ix >= 0 && ix < g.Ws) mask |= 1u << (16 + kw); }
+    rowoff = (((long long)b * g.Hs + y0) * g.Ws + x0) * g.cs_src;
+}
+// per-chunk part: offset of tap (kh,kw) channel c relative to the row base, and the mask bits that must be set
+__device__ __forceinline__ void conv_tap_setup(const ConvGeom &g, int kh, int kw, int c, int &tapoff, uint32_t &need) {
+    const int sgn = g.transposed ? -1 : 1;
+    tapoff = sgn * (kh * g.dH * g.Ws + kw * g.dW) * g.cs_src + c;
+    need = (1u << kh) | (1u << (16 + kw));
 }
 
 __device__ __forceinline__ float to_tf32_rna(float v) {

@@ -113,6 +113,31 @@ __device__ __forceinline__ uint32_t mn_tile_off(int r, int atom, int piece) {
     return (uint32_t)(((r >> 2) * NATOMS + atom) << 9) + ((uint32_t)(r & 3) << 7) +
            ((uint32_t)(((piece >> 1) ^ (r & 3))) << 5) + ((uint32_t)(piece & 1) << 4);
 }
+// Epilogue store of one warp's 32 rows x 32 fp32 columns (thread = row, v = its 32 columns) through a 4 KB
+// shared-memory staging tile so that every global store instruction writes four complete 128-byte row segments
+// (lane = 16-byte chunk c of row 4i + lane/8) instead of 32 scattered 16-byte pieces. 16-byte chunks are
+// XOR-swizzled with the row so that both the row-wise writes and the transposed reads are bank-conflict free.
+__device__ __forceinline__ void store_tile_32x32(uint32_t stage_smem, const float (&v)[32], int lane, float *out_base,
+                                                 size_t row_stride, int rows_valid) {
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        const uint32_t a = stage_smem + (uint32_t)lane * 128u + (uint32_t)((q ^ (lane & 7)) << 4);
+        asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v[q * 4]), "f"(v[q * 4 + 1]), "f"(v[q * 4 + 2]),
+                     "f"(v[q * 4 + 3]) : "memory");
+    }
+    __syncwarp();
+    const int c = lane & 7;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int row = 4 * i + (lane >> 3);
+        float4 t;
+        const uint32_t a = stage_smem + (uint32_t)row * 128u + (uint32_t)((c ^ (row & 7)) << 4);
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(a));
+        if (row < rows_valid) *reinterpret_cast<float4 *>(out_base + (size_t)row * row_stride + c * 4) = t;
+    }
+}
+
 // Instruction descriptor (InstrDescriptor): c_format F32 [4,6)=1, a/b_format TF32 [7,10)=[10,13)=2,
 // a_major bit 15, b_major bit 16 (1 = MN-major), N>>3 at [17,23), M>>4 at [24,29)
 __host__ __device__ constexpr uint32_t umma_idesc(int M, int N, int a_mn, int b_mn) {
@@ -125,11 +150,12 @@ struct SmemLayout {
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 4;  // 16 KB (gemm: 128 rows x 128 B; wgrad: 32 px x 512 B)
     static constexpr int B_BYTES = BN * BLOCK_K * 4;
     static constexpr int BAR_OFF = STAGES * (A_BYTES + B_BYTES);
-    static constexpr int BYTES = BAR_OFF + 256 + 1024;  // barriers + slack for 1024-byte alignment
+    static constexpr int BIAS_OFF = BAR_OFF + 256;          // BN floats: the tile's bias slice
+    static constexpr int BYTES = BIAS_OFF + BN * 4 + 1024;  // + slack for 1024-byte alignment
 };
 
 // ------------------------------------------------------------------------------------------------
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool FAST>
 __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restrict__ src, const float *__restrict__ wpack,
                                                           const float *__restrict__ bias, float *__restrict__ out,
                                                           ConvGeom g, int n_valid, int out_cs, int act) {
@@ -151,6 +177,8 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restric
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 4) tmem_alloc<BN>(tmem_slot);
+    float *bias_s = reinterpret_cast<float *>(smem_raw + (base - smem_u32(smem_raw)) + L::BIAS_OFF);
+    if (tid < BN) bias_s[tid] = (bias && n0 + tid < n_valid) ? __ldg(bias + n0 + tid) : 0.f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -161,14 +189,24 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restric
         // ------------------------------ producers
         const int j = tid & 7, rb = tid >> 3;
         const uint32_t off0 = ((uint32_t)(rb >> 3) << 10) + ((uint32_t)(rb & 7) << 7) + ((uint32_t)(j ^ (rb & 7)) << 4);
+        // per-row state, set up once per tile. FAST: base offset + tap validity mask (a copy then costs ~5
+        // instructions); otherwise the generic (b, y, x) decode is replayed per copy.
+        long long rowoff[8];
+        uint32_t rowmask[8];
         int rowB[8], rowY[8], rowX[8];
 #pragma unroll
         for (int i = 0; i < 8; i++) {
             int m = m0 + rb + 16 * i;
-            if (m < g.M) conv_m_decode(g, m, rowB[i], rowY[i], rowX[i]);
-            else { rowB[i] = -1; rowY[i] = 0; rowX[i] = 0; }
+            if (FAST) {
+                if (m < g.M) conv_row_setup(g, m, rowoff[i], rowmask[i]);
+                else { rowoff[i] = 0; rowmask[i] = 0; }
+            } else {
+                if (m < g.M) conv_m_decode(g, m, rowB[i], rowY[i], rowX[i]);
+                else { rowB[i] = -1; rowY[i] = 0; rowX[i] = 0; }
+            }
         }
         const float *wrow = wpack + (size_t)(n0 + rb) * g.Kp + j * 4;
+        const size_t wstep = (size_t)16 * g.Kp;
         for (int it = 0; it < num_k + LOOKAHEAD; ++it) {
             if (it < num_k) {
                 const int s = it % STAGES;
@@ -176,16 +214,26 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restric
                 int kh, kw, c; bool kvalid;
                 conv_k_decode(g, it * BLOCK_K + j * 4, kh, kw, c, kvalid);
                 const uint32_t a_dst = a_base + s * L::A_BYTES + off0;
+                if (FAST) {
+                    int tapoff = 0; uint32_t need = 0xFFFFFFFFu;
+                    if (kvalid) conv_tap_setup(g, kh, kw, c, tapoff, need);
 #pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    long long o = (kvalid && rowB[i] >= 0) ? conv_src_offset(g, rowB[i], rowY[i], rowX[i], kh, kw) : -1;
-                    const float *p = o >= 0 ? src + o + c : src;
-                    cp_async16(a_dst + i * 2048u, p, o >= 0 ? 16u : 0u);
+                    for (int i = 0; i < 8; i++) {
+                        const bool ok = (rowmask[i] & need) == need;
+                        cp_async16(a_dst + i * 2048u, ok ? src + (rowoff[i] + tapoff) : src, ok ? 16u : 0u);
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; i++) {
+                        long long o = (kvalid && rowB[i] >= 0) ? conv_src_offset(g, rowB[i], rowY[i], rowX[i], kh, kw) : -1;
+                        const float *p = o >= 0 ? src + o + c : src;
+                        cp_async16(a_dst + i * 2048u, p, o >= 0 ? 16u : 0u);
+                    }
                 }
                 const uint32_t b_dst = b_base + s * L::B_BYTES + off0;
+                const float *wp = wrow + (size_t)it * BLOCK_K;
 #pragma unroll
-                for (int i = 0; i < BN / 16; i++)
-                    cp_async16(b_dst + i * 2048u, wrow + (size_t)(16 * i) * g.Kp + (size_t)it * BLOCK_K, 16u);
+                for (int i = 0; i < BN / 16; i++, wp += wstep) cp_async16(b_dst + i * 2048u, wp, 16u);
             }
             cp_async_commit();
             if (it >= LOOKAHEAD) {
@@ -199,24 +247,38 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restric
         tc_fence_after();
         const int m = m0 + warp * 32 + lane;
         float *orow = out + (size_t)m * out_cs;
+        const bool full_n = n0 + BN <= n_valid;  // whole tile inside the valid channels: no per-element guards
+        const uint32_t stage_smem = a_base + warp * 4096u;  // operand stages are idle once acc_bar has fired
+        const int rows_valid = g.M - (m0 + warp * 32);
 #pragma unroll 1
         for (int cb = 0; cb < BN / 32; cb++) {
             float v[32];
             tmem_ld32(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cb * 32), v);
             const int nb = n0 + cb * 32;
-            if (m < g.M) {
+            if (full_n) {
 #pragma unroll
                 for (int q = 0; q < 8; q++) {
-                    const int n = nb + q * 4;
-                    if (n < out_cs) {
-                        float r[4];
+                    const float4 bq = *reinterpret_cast<const float4 *>(bias_s + cb * 32 + q * 4);
+                    v[q * 4 + 0] += bq.x; v[q * 4 + 1] += bq.y; v[q * 4 + 2] += bq.z; v[q * 4 + 3] += bq.w;
+                }
+                if (act == DL4JB200_ACT_RELU) {
 #pragma unroll
-                        for (int e = 0; e < 4; e++) {
-                            const int nn = n + e;
-                            r[e] = nn < n_valid ? dl4j_act(v[q * 4 + e] + (bias ? __ldg(bias + nn) : 0.f), act) : 0.f;
-                        }
-                        *reinterpret_cast<float4 *>(orow + n) = make_float4(r[0], r[1], r[2], r[3]);
-                    }
+                    for (int e = 0; e < 32; e++) v[e] = fmaxf(v[e], 0.f);
+                } else if (act != DL4JB200_ACT_IDENTITY) {
+#pragma unroll 1
+                    for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);
+                }
+                store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
+            } else if (m < g.M) {
+#pragma unroll 1
+                for (int q = 0; q < 8; q++) {
+                    const int n = nb + q * 4;
+                    if (n >= out_cs) break;
+                    float r[4];
+#pragma unroll
+                    for (int e = 0; e < 4; e++)
+                        r[e] = n + e < n_valid ? dl4j_act(v[q * 4 + e] + bias_s[cb * 32 + q * 4 + e], act) : 0.f;
+                    *reinterpret_cast<float4 *>(orow + n) = make_float4(r[0], r[1], r[2], r[3]);
                 }
             }
         }
@@ -287,6 +349,10 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
         int kh, kw, c; bool kvalid;
         conv_k_decode(g, kcol0 + pb * 4, kh, kw, c, kvalid);
         kvalid = kvalid && (kcol0 + pb * 4) < g.Kp;
+        // this thread's im2col column is one fixed (tap, channel quad): fold the tap into the pixel arithmetic
+        const int dy = kh * g.dH - g.pT, dx = kw * g.dW - g.pL;
+        const float *xcol = x + c;
+        const float *dcol = delta + co0 + pa * 4;
         for (int it = 0; it < num_k + LOOKAHEAD; ++it) {
             if (it < num_k) {
                 const int s = it % STAGES;
@@ -298,19 +364,23 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
                     const int r = ra + 4 * i, m = mrow0 + r;
                     const bool ok = a_col_ok && m < me;
                     const uint32_t dst = a_stage + mn_tile_off<4>(r, pa >> 3, pa & 7);
-                    cp_async16(dst, ok ? delta + (size_t)m * delta_cs + co0 + pa * 4 : delta, ok ? 16u : 0u);
+                    cp_async16(dst, ok ? dcol + (size_t)m * delta_cs : delta, ok ? 16u : 0u);
                 }
 #pragma unroll
                 for (int i = 0; i < PASSES; i++) {
                     const int r = rbb + RPP * i, m = mrow0 + r;
-                    long long o = -1;
-                    if (kvalid && m < me) {
-                        int b, y0, x0;
-                        conv_m_decode(g, m, b, y0, x0);
-                        o = conv_src_offset(g, b, y0, x0, kh, kw);
+                    bool ok = kvalid && m < me;
+                    size_t o = 0;
+                    if (ok) {
+                        uint32_t bb, rr, yy, xx;
+                        g.div_HWm.divmod((uint32_t)m, bb, rr);
+                        g.div_Wm.divmod(rr, yy, xx);
+                        const int iy = (int)yy * g.sH + dy, ix = (int)xx * g.sW + dx;
+                        ok = (unsigned)iy < (unsigned)g.Hs && (unsigned)ix < (unsigned)g.Ws;
+                        o = (((size_t)bb * g.Hs + iy) * g.Ws + ix) * g.cs_src;
                     }
                     const uint32_t dst = b_stage + mn_tile_off<NB_ATOMS>(r, pb >> 3, pb & 7);
-                    cp_async16(dst, o >= 0 ? x + o + c : x, o >= 0 ? 16u : 0u);
+                    cp_async16(dst, ok ? xcol + o : x, ok ? 16u : 0u);
                 }
             }
             cp_async_commit();
@@ -324,11 +394,15 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
         tc_fence_after();
         const int co = co0 + warp * 32 + lane;
         float *prow = partial + ((size_t)blockIdx.y * rows_p + co) * g.Kp;
+        const uint32_t stage_smem = a_base + warp * 4096u;
 #pragma unroll 1
         for (int cb = 0; cb < BN / 32; cb++) {
             float v[32];
             tmem_ld32(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cb * 32), v);
-            if (co < rows_p) {
+            if (kcol0 + cb * 32 + 32 <= g.Kp) {
+                store_tile_32x32(stage_smem, v, lane, partial + ((size_t)blockIdx.y * rows_p + co0 + warp * 32) * g.Kp + kcol0 + cb * 32,
+                                 (size_t)g.Kp, rows_p - (co0 + warp * 32));
+            } else if (co < rows_p) {
 #pragma unroll
                 for (int q = 0; q < 8; q++) {
                     const int k = kcol0 + cb * 32 + q * 4;
@@ -362,11 +436,11 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
     if (warp == 4) tmem_dealloc<BN>(tmem_d);
 }
 
-template <int BN, int STAGES>
-static int launch_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, const float *bias,
-                       float *out, int n_valid, int out_cs, int act) {
+template <int BN, int STAGES, bool FAST>
+static int launch_gemm_impl(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, const float *bias,
+                            float *out, int n_valid, int out_cs, int act) {
     using L = SmemLayout<BN, STAGES>;
-    auto kern = k_conv_tc_gemm<BN, STAGES>;
+    auto kern = k_conv_tc_gemm<BN, STAGES, FAST>;
     static bool configured[16] = {false};
     if (!configured[ctx->device & 15]) {
         DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
@@ -376,6 +450,13 @@ static int launch_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, c
     kern<<<grid, THREADS, L::BYTES, ctx->stream>>>(src, wpack, bias, out, g, n_valid, out_cs, act);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
+}
+
+template <int BN, int STAGES>
+static int launch_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, const float *bias,
+                       float *out, int n_valid, int out_cs, int act) {
+    return g.fast ? launch_gemm_impl<BN, STAGES, true>(ctx, g, src, wpack, bias, out, n_valid, out_cs, act)
+                  : launch_gemm_impl<BN, STAGES, false>(ctx, g, src, wpack, bias, out, n_valid, out_cs, act);
 }
 
 template <int BN, int STAGES>

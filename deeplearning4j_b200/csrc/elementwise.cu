@@ -164,10 +164,17 @@ __global__ void __launch_bounds__(256) k_l1l2_partial(const float *__restrict__ 
     }
     if (threadIdx.x == 0) { partial[2 * blockIdx.x] = s1[0]; partial[2 * blockIdx.x + 1] = s2[0]; }
 }
-__global__ void k_l1l2_final(const double *partial, int nblk, double l1, double l2, float *score_acc) {
+__global__ void __launch_bounds__(128) k_l1l2_final(const double *partial, int nblk, double l1, double l2, float *score_acc) {
+    __shared__ double s1[128], s2[128];
     double a = 0.0, b = 0.0;
-    for (int i = 0; i < nblk; i++) { a += partial[2 * i]; b += partial[2 * i + 1]; }
-    score_acc[0] += (float)(l1 * a + 0.5 * l2 * b);
+    for (int i = threadIdx.x; i < nblk; i += 128) { a += partial[2 * i]; b += partial[2 * i + 1]; }
+    s1[threadIdx.x] = a; s2[threadIdx.x] = b;
+    __syncthreads();
+    for (int o = 64; o; o >>= 1) {
+        if (threadIdx.x < o) { s1[threadIdx.x] += s1[threadIdx.x + o]; s2[threadIdx.x] += s2[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) score_acc[0] += (float)(l1 * s1[0] + 0.5 * l2 * s2[0]);
 }
 
 __global__ void __launch_bounds__(256) k_copy2d(const float *__restrict__ src, int src_ld, float *__restrict__ dst, int dst_ld,
@@ -297,7 +304,7 @@ int dl4jb200_l1l2_score(dl4jb200_ctx *ctx, const float *w, size_t n, double l1, 
     if (!partial) return DL4JB200_ERR_CUDA;
     k_l1l2_partial<<<nblk, 256, 0, ctx->stream>>>(w, n, partial);
     DL4J_CHECK_LAUNCH();
-    k_l1l2_final<<<1, 1, 0, ctx->stream>>>(partial, nblk, l1, l2, score_acc);
+    k_l1l2_final<<<1, 128, 0, ctx->stream>>>(partial, nblk, l1, l2, score_acc);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
