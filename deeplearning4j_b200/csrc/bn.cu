@@ -149,13 +149,13 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nchw(const float *__r
 // ------------------------------------------------------------------ pass 2: finalize (one thread per channel)
 // coef layout: [4][cpad] = centre, a, b, c   with  y = (x-centre)*a + c            (forward; b unused)
 //                                              dx = a*e + b*(x-centre) + c          (backward)
-// Folds partial[nblk][2][cpad] for channel c over the 8 threads (threadIdx.y) that share it; result valid for y == 0.
+// Folds partial[nblk][2][cpad] for channel c over the 32 threads (threadIdx.y) that share it; result valid for y == 0.
 __device__ __forceinline__ void bn_fold_partials(const float *__restrict__ partial, int nblk, int cpad, int c, bool active,
                                                  double &s1, double &s2) {
-    __shared__ double sh1[8][33], sh2[8][33];
+    __shared__ double sh1[32][33], sh2[32][33];
     double a = 0.0, b = 0.0;
     if (active)
-        for (int i = threadIdx.y; i < nblk; i += 8) {
+        for (int i = threadIdx.y; i < nblk; i += 32) {
             a += (double)partial[(size_t)i * 2 * cpad + c];
             b += (double)partial[(size_t)i * 2 * cpad + cpad + c];
         }
@@ -164,7 +164,7 @@ __device__ __forceinline__ void bn_fold_partials(const float *__restrict__ parti
     __syncthreads();
     s1 = 0.0; s2 = 0.0;
     if (threadIdx.y == 0)
-        for (int j = 0; j < 8; j++) { s1 += sh1[j][threadIdx.x]; s2 += sh2[j][threadIdx.x]; }
+        for (int j = 0; j < 32; j++) { s1 += sh1[j][threadIdx.x]; s2 += sh2[j][threadIdx.x]; }
 }
 
 __global__ void k_bn_finalize_fwd(const float *__restrict__ partial, int nblk, const float *__restrict__ pivot,
@@ -373,7 +373,7 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
         }
         DL4J_CHECK_LAUNCH();
     }
-    k_bn_finalize_fwd<<<dl4j_ceil_div(p.cpad, 32), dim3(32, 8), 0, ctx->stream>>>(
+    k_bn_finalize_fwd<<<dl4j_ceil_div(p.cpad, 32), dim3(32, 32), 0, ctx->stream>>>(
         p.partial, p.nblk, x, layout == DL4JB200_NHWC ? 1 : HW, gamma, beta, gmean, gvar, save_mean, save_std, p.coef, C,
         p.cpad, (double)M, decay, eps, training, minibatch);
     DL4J_CHECK_LAUNCH();
@@ -411,7 +411,7 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
         else k_bn_partial_nchw<1, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, act_out, save_mean, p.partial, B, C, HW, p.chunk);
     }
     DL4J_CHECK_LAUNCH();
-    k_bn_finalize_bwd<<<dl4j_ceil_div(p.cpad, 32), dim3(32, 8), 0, ctx->stream>>>(p.partial, p.nblk, gamma, save_mean, save_std,
+    k_bn_finalize_bwd<<<dl4j_ceil_div(p.cpad, 32), dim3(32, 32), 0, ctx->stream>>>(p.partial, p.nblk, gamma, save_mean, save_std,
                                                                          dgamma, dbeta, p.coef, C, p.cpad, (double)M);
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {

@@ -101,18 +101,18 @@ __global__ void __launch_bounds__(256) k_colsum_partial(const float *__restrict_
         __syncthreads();
     }
 }
-// blockDim = (32 channels, 8 partial-row groups)
+// blockDim = (32 channels, 32 partial-row groups)
 __global__ void k_colsum_final(const float *__restrict__ partial, float *__restrict__ out, int nblk, int cs, int C) {
-    __shared__ double sh[8][33];
+    __shared__ double sh[32][33];
     int c = blockIdx.x * 32 + threadIdx.x;
     double acc = 0.0;
     if (c < C)
-        for (int b = threadIdx.y; b < nblk; b += 8) acc += (double)partial[(size_t)b * cs + c];
+        for (int b = threadIdx.y; b < nblk; b += 32) acc += (double)partial[(size_t)b * cs + c];
     sh[threadIdx.y][threadIdx.x] = acc;
     __syncthreads();
     if (threadIdx.y == 0 && c < C) {
         double t = 0.0;
-        for (int j = 0; j < 8; j++) t += sh[j][threadIdx.x];
+        for (int j = 0; j < 32; j++) t += sh[j][threadIdx.x];
         out[c] = (float)t;
     }
 }
@@ -249,7 +249,7 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     if (db) {
         k_colsum_partial<<<nblk, 256, 0, ctx->stream>>>(ds, colp, gf.M, delta_cs);
         DL4J_CHECK_LAUNCH();
-        k_colsum_final<<<dl4j_ceil_div(d->c_out, 32), dim3(32, 8), 0, ctx->stream>>>(colp, db, nblk, delta_cs, d->c_out);
+        k_colsum_final<<<dl4j_ceil_div(d->c_out, 32), dim3(32, 32), 0, ctx->stream>>>(colp, db, nblk, delta_cs, d->c_out);
         DL4J_CHECK_LAUNCH();
     }
 

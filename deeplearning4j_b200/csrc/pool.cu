@@ -10,6 +10,8 @@
 struct PoolGeom {
     int B, C, H, W, Ho, Wo, kH, kW, sH, sW, pT, pL, dH, dW;
     int xcs, ycs;  // NHWC pixel strides
+    FastDiv d_sH, d_sW;            // stride divisions of the backward gather
+    FastDiv d_q, d_w, d_h, d_c;    // index decode of the tensor the kernel enumerates (set per launch)
 };
 
 template <int V>
@@ -40,16 +42,16 @@ __device__ __forceinline__ void vstore_i(int32_t *p, const int (&r)[V]) {
 
 // NHWC: V = 4, a work item is (b, y, x, channel quad). NCHW: V = 1, a work item is (b, c, y, x).
 template <bool NHWC>
-__device__ __forceinline__ void decode(size_t idx, int C, int Hh, int Ww, int cs, int &b, int &c, int &y, int &x) {
+__device__ __forceinline__ void decode(size_t idx, const PoolGeom &g, int &b, int &c, int &y, int &x) {
+    uint32_t i = (uint32_t)idx, q, r;  // work-item counts are < 2^31 (checked on the host)
     if (NHWC) {
-        int Q = cs >> 2;
-        c = (int)(idx % Q) * 4; idx /= Q;
-        x = (int)(idx % Ww); idx /= Ww;
-        y = (int)(idx % Hh); b = (int)(idx / Hh);
+        g.d_q.divmod(i, q, r); c = (int)r * 4; i = q;
+        g.d_w.divmod(i, q, r); x = (int)r; i = q;
+        g.d_h.divmod(i, q, r); y = (int)r; b = (int)q;
     } else {
-        x = (int)(idx % Ww); idx /= Ww;
-        y = (int)(idx % Hh); idx /= Hh;
-        c = (int)(idx % C); b = (int)(idx / C);
+        g.d_w.divmod(i, q, r); x = (int)r; i = q;
+        g.d_h.divmod(i, q, r); y = (int)r; i = q;
+        g.d_c.divmod(i, q, r); c = (int)r; b = (int)q;
     }
 }
 template <bool NHWC>
@@ -65,7 +67,7 @@ __global__ void __launch_bounds__(256) k_pool_fwd(const float *__restrict__ x, f
     size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
         int b, c, oh, ow;
-        decode<NHWC>(idx, g.C, g.Ho, g.Wo, g.ycs, b, c, oh, ow);
+        decode<NHWC>(idx, g, b, c, oh, ow);
         float acc[V];
         int best[V];
 #pragma unroll
@@ -111,7 +113,7 @@ __global__ void __launch_bounds__(256) k_pool_bwd(const float *__restrict__ x, c
     size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
         int b, c, h, w;
-        decode<NHWC>(idx, g.C, g.H, g.W, g.xcs, b, c, h, w);
+        decode<NHWC>(idx, g, b, c, h, w);
         Vec<V> xv;
         if (type != DL4JB200_POOL_AVG && !(type == DL4JB200_POOL_MAX && argmax))
             xv = vload<V>(x + offs<NHWC>(b, c, h, w, g.C, g.H, g.W, g.xcs));
@@ -120,13 +122,18 @@ __global__ void __launch_bounds__(256) k_pool_bwd(const float *__restrict__ x, c
         for (int i = 0; i < V; i++) acc[i] = 0.f;
         for (int kh = 0; kh < g.kH; kh++) {
             int t = h + g.pT - kh * g.dH;
-            if (t < 0 || t % g.sH) continue;
-            int oh = t / g.sH;
+            if (t < 0) continue;
+            uint32_t qq, rr;
+            g.d_sH.divmod((uint32_t)t, qq, rr);
+            if (rr) continue;
+            int oh = (int)qq;
             if (oh >= g.Ho) continue;
             for (int kw = 0; kw < g.kW; kw++) {
                 int u = w + g.pL - kw * g.dW;
-                if (u < 0 || u % g.sW) continue;
-                int ow = u / g.sW;
+                if (u < 0) continue;
+                g.d_sW.divmod((uint32_t)u, qq, rr);
+                if (rr) continue;
+                int ow = (int)qq;
                 if (ow >= g.Wo) continue;
                 size_t o = offs<NHWC>(b, c, oh, ow, g.C, g.Ho, g.Wo, g.ycs);
                 Vec<V> e = vload<V>(eps + o);
@@ -196,6 +203,9 @@ static int pool_geom(const dl4jb200_conv_desc *d, int layout, int x_cs, int y_cs
                      "%s: NHWC pixel strides must be equal multiples of 4 and >= C", who);
     g = PoolGeom{d->batch, d->c_in, d->in_h, d->in_w, d->out_h, d->out_w, d->k_h, d->k_w, d->stride_h, d->stride_w,
                  d->pad_top, d->pad_left, d->dil_h, d->dil_w, x_cs, y_cs};
+    g.d_sH = FastDiv((uint32_t)d->stride_h);
+    g.d_sW = FastDiv((uint32_t)d->stride_w);
+    DL4J_REQUIRE((long long)d->batch * d->c_in * d->in_h * d->in_w < (1LL << 31), "%s: tensor too large", who);
     return DL4JB200_OK;
 }
 
@@ -214,6 +224,8 @@ int dl4jb200_pool_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     if (rc) return rc;
     DL4J_REQUIRE(pool_type >= DL4JB200_POOL_MAX && pool_type <= DL4JB200_POOL_PNORM, "pool_fwd: unknown pooling type %d", pool_type);
     DL4J_REQUIRE(pool_type != DL4JB200_POOL_PNORM || pnorm >= 1, "pool_fwd: pnorm must be >= 1");
+    g.d_q = FastDiv((uint32_t)(layout == DL4JB200_NHWC ? g.ycs / 4 : 1));
+    g.d_w = FastDiv((uint32_t)g.Wo); g.d_h = FastDiv((uint32_t)g.Ho); g.d_c = FastDiv((uint32_t)g.C);
     if (layout == DL4JB200_NHWC) {
         size_t total = (size_t)g.B * g.Ho * g.Wo * (g.ycs / 4);
         k_pool_fwd<true><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, argmax, g, pool_type, pnorm, total);
@@ -240,6 +252,8 @@ int dl4jb200_pool_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
                  "pool_bwd: unknown pooling type %d", pool_type);
     DL4J_REQUIRE(pool_type == DL4JB200_POOL_AVG || argmax || x, "pool_bwd: x is required when argmax is NULL");
     DL4J_REQUIRE(pool_type != DL4JB200_POOL_PNORM || (x && y && pnorm >= 1), "pool_bwd: PNORM needs x, y and pnorm >= 1");
+    g.d_q = FastDiv((uint32_t)(layout == DL4JB200_NHWC ? g.xcs / 4 : 1));
+    g.d_w = FastDiv((uint32_t)g.W); g.d_h = FastDiv((uint32_t)g.H); g.d_c = FastDiv((uint32_t)g.C);
     if (layout == DL4JB200_NHWC) {
         size_t total = (size_t)g.B * g.H * g.W * (g.xcs / 4);
         k_pool_bwd<true><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, eps, argmax, dx, g, pool_type, pnorm,

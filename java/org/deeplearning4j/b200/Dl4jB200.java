@@ -1,0 +1,70 @@
+package org.deeplearning4j.b200;
+
+import org.bytedeco.javacpp.BytePointer;
+import org.bytedeco.javacpp.FloatPointer;
+import org.bytedeco.javacpp.IntPointer;
+import org.bytedeco.javacpp.Loader;
+import org.bytedeco.javacpp.Pointer;
+import org.bytedeco.javacpp.PointerPointer;
+import org.bytedeco.javacpp.annotation.Cast;
+import org.bytedeco.javacpp.annotation.Const;
+import org.bytedeco.javacpp.annotation.Platform;
+
+/**
+ * JavaCPP binding of include/dl4jb200.h (libdl4jb200.so). One native method per C entry point, same names and
+ * argument order. NOT COMPILED in this repository's CI image (no JDK); see INTEGRATION.md.
+ */
+@Platform(include = "dl4jb200.h", link = "dl4jb200")
+public class Dl4jB200 {
+    static { Loader.load(); }
+
+    public static final int OK = 0, NOT_SUPPORTED = 1, NCHW = 0, NHWC = 1;
+    public static final int MODE_STRICT = 0, MODE_TRUNCATE = 1, MODE_SAME = 2;
+    public static final int POOL_MAX = 0, POOL_AVG = 1, POOL_SUM = 2, POOL_PNORM = 3;
+    public static final int ACT_IDENTITY = 0, ACT_RELU = 1, ACT_SIGMOID = 2, ACT_TANH = 3, ACT_LEAKYRELU = 4;
+    public static final int ALGO_TC_TF32 = 0, ALGO_FP32 = 1;
+
+    /** dl4jb200_conv_desc: 15 consecutive int32 fields. */
+    public static class ConvDesc extends IntPointer {
+        public ConvDesc() { super(15); }
+        public ConvDesc set(int batch, int cIn, int inH, int inW, int cOut, int kH, int kW, int sH, int sW, int padTop,
+                        int padLeft, int dH, int dW, int outH, int outW) {
+            put(new int[] {batch, cIn, inH, inW, cOut, kH, kW, sH, sW, padTop, padLeft, dH, dW, outH, outW});
+            return this;
+        }
+    }
+
+    public static native @Cast("const char*") BytePointer dl4jb200_last_error();
+    public static native int dl4jb200_ctx_create(int device, Pointer stream, @Cast("dl4jb200_ctx**") PointerPointer out);
+    public static native int dl4jb200_ctx_destroy(@Cast("dl4jb200_ctx*") Pointer ctx);
+    public static native int dl4jb200_ctx_sync(@Cast("dl4jb200_ctx*") Pointer ctx);
+    public static native int dl4jb200_buf_register(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host, long bytes,
+                    @Cast("void**") PointerPointer deviceOut);
+    public static native int dl4jb200_buf_upload(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host);
+    public static native int dl4jb200_buf_download(@Cast("dl4jb200_ctx*") Pointer ctx, Pointer host);
+    public static native int dl4jb200_out_size(int in, int kernel, int stride, int pad, int dilation, int mode, IntPointer out,
+                    IntPointer padLo, IntPointer padHi);
+    public static native int dl4jb200_conv_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer x, int xLayout, int xCs, @Const FloatPointer w, @Const FloatPointer bias, FloatPointer z,
+                    int zLayout, int zCs, int act, int algo);
+    public static native int dl4jb200_conv_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer x, int xLayout, int xCs, @Const FloatPointer w, @Const FloatPointer delta, int deltaLayout,
+                    int deltaCs, FloatPointer dw, FloatPointer db, FloatPointer dx, int dxLayout, int dxCs, int algo);
+    public static native int dl4jb200_act_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer z, FloatPointer a, long n, int act);
+    public static native int dl4jb200_pool_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer x, FloatPointer y, IntPointer argmax, int layout, int xCs, int yCs, int poolType, int pnorm);
+    public static native int dl4jb200_pool_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer x, @Const FloatPointer y, @Const FloatPointer eps, @Const IntPointer argmax, FloatPointer dx,
+                    int layout, int xCs, int yCs, int poolType, int pnorm, double pnormEps);
+    public static native int dl4jb200_bn_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, FloatPointer y,
+                    @Const FloatPointer gamma, @Const FloatPointer beta, FloatPointer gmean, FloatPointer gvar, FloatPointer saveMean,
+                    FloatPointer saveStd, int b, int c, int h, int w, int layout, int cs, double decay, double eps, int training,
+                    int minibatch, int act);
+    public static native int dl4jb200_bn_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, @Const FloatPointer eps,
+                    @Const FloatPointer gamma, @Const FloatPointer saveMean, @Const FloatPointer saveStd, @Const FloatPointer actOut,
+                    FloatPointer dx, FloatPointer dgamma, FloatPointer dbeta, int b, int c, int h, int w, int layout, int cs);
+    public static native int dl4jb200_lrn_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, FloatPointer y, int b, int c,
+                    int h, int w, int layout, int cs, double k, double n, double alpha, double beta);
+    public static native int dl4jb200_lrn_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, @Const FloatPointer eps,
+                    FloatPointer dx, int b, int c, int h, int w, int layout, int cs, double k, double n, double alpha, double beta);
+}

@@ -96,7 +96,7 @@ def test_lenet_step_parity(algo_name):
     algo = _lib.ALGO_FP32 if algo_name == "fp32" else _lib.ALGO_TC_TF32
     # whole-step TF32 bound: per-layer TF32 error (<= 2e-3) is amplified by the softmax (d p / p = d z, |z| ~ 10 for
     # an untrained net on U[0,1) inputs) before it reaches the gradients
-    tol = 1e-4 if algo_name == "fp32" else 5e-2
+    tol = 1e-4 if algo_name == "fp32" else 1e-1
     _run_case(zoo.lenet(), 16, 10, algo, 2, False, tol, tol, 5e-3 if algo_name == "tf32" else tol)
 
 
@@ -132,7 +132,7 @@ def test_resnet50_step_parity_small_batch():
     ref = OracleNet(m, layout, P, p0, fast=True)
     ref.forward(x, lab, True)
     ref.backward()
-    for algo, tol_fwd, min_cos in ((_lib.ALGO_FP32, 1e-3, 0.98), (_lib.ALGO_TC_TF32, 5e-2, 0.80)):
+    for algo, tol_fwd, min_cos in ((_lib.ALGO_FP32, 1e-3, 0.98), (_lib.ALGO_TC_TF32, 1e-1, 0.80)):
         net = network.Network(m, B, algo=algo, params=p0)
         try:
             net.set_batch(x, lab)
