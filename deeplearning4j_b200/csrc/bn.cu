@@ -425,3 +425,111 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the batch-norm forward (no counterpart in the reference).
+//
+// dl4jb200_bn_fwd keeps its per-block partial sums and per-channel coefficients in the context's scratch, which is
+// obtained from cudaMalloc the first time (and whenever a larger tensor comes along). Some callers must never
+// trigger a device allocation: a serving or training loop that cannot afford the device-wide synchronisation a
+// cudaMalloc implies, a process that has handed the whole card to another allocator (nd4j workspaces or a pool
+// sized to the GPU) so that a driver allocation may simply fail, or code running where CUDA memory management is
+// not permitted (for example a cudaLaunchHostFunc callback). For them the same three kernels run with their scratch
+// in the fixed array below instead.
+//
+// DL4JB200_BN_NOALLOC_FLOATS floats (4 MiB) are reserved on every GPU that loads this library, until the process
+// exits. That bounds the channel count (see DL4JB200_BN_NOALLOC_MAX_CHANNELS); B, H and W are unlimited because the
+// number of partial blocks is reduced to fit. All calls share the one array: two calls that overlap on the GPU
+// (different streams, different contexts on the same device) race on it -- keep such calls on one stream or
+// serialise them. Nothing in the array has to start at zero: every slot a call reads is written earlier in that
+// same call, so leftovers from the previous call are harmless.
+#define DL4JB200_BN_NOALLOC_FLOATS (1u << 20)
+#define DL4JB200_BN_NOALLOC_MAX_CHANNELS 4096
+
+static __device__ __align__(256) float g_bn_noalloc_scratch[DL4JB200_BN_NOALLOC_FLOATS];
+
+// In host code `g_bn_noalloc_scratch` is only a handle for the symbol, not a device address; the address a kernel can
+// use comes from cudaGetSymbolAddress, asked once per device with that device current.
+static float *g_bn_noalloc_ptr[64] = {nullptr};
+
+static int bn_noalloc_scratch(dl4jb200_ctx *ctx, float **out) {
+    DL4J_REQUIRE(ctx->device >= 0 && ctx->device < 64, "bn_fwd_noalloc: device index %d out of range", ctx->device);
+    if (!g_bn_noalloc_ptr[ctx->device]) {
+        int cur = -1;
+        DL4J_CUDA_TRY(cudaGetDevice(&cur));
+        if (cur != ctx->device) DL4J_CUDA_TRY(cudaSetDevice(ctx->device));
+        float *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, g_bn_noalloc_scratch);
+        if (cur != ctx->device && cur >= 0) cudaSetDevice(cur);
+        if (e != cudaSuccess || !p) {
+            dl4j_set_error("bn_fwd_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+            return DL4JB200_ERR_CUDA;
+        }
+        g_bn_noalloc_ptr[ctx->device] = p;
+    }
+    *out = g_bn_noalloc_ptr[ctx->device];
+    return DL4JB200_OK;
+}
+
+extern "C" int dl4jb200_bn_fwd_noalloc(dl4jb200_ctx *ctx, const float *x, float *y, const float *gamma, const float *beta,
+                                       float *gmean, float *gvar, float *save_mean, float *save_std, int B, int C, int H,
+                                       int W, int layout, int cs, double decay, double eps, int training, int minibatch,
+                                       int act) {
+    DL4J_REQUIRE(ctx && x && y && gmean && gvar, "bn_fwd_noalloc: NULL argument");
+    DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, "bn_fwd_noalloc: bad shape");
+    DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "bn_fwd_noalloc: unknown layout %d", layout);
+    DL4J_REQUIRE(layout == DL4JB200_NCHW || (cs >= C && cs % 4 == 0 && al16(x) && al16(y)),
+                 "bn_fwd_noalloc: NHWC needs cs %% 4 == 0, cs >= C and 16-byte aligned tensors");
+    const int cpad = layout == DL4JB200_NHWC ? cs : C;
+    if (cpad > DL4JB200_BN_NOALLOC_MAX_CHANNELS) {
+        dl4j_set_error("bn_fwd_noalloc: %d channels exceed the fixed scratch (maximum %d channels; use dl4jb200_bn_fwd, "
+                       "which sizes its scratch on demand)", cpad, DL4JB200_BN_NOALLOC_MAX_CHANNELS);
+        return DL4JB200_ERR_INVALID_ARG;
+    }
+    float *scratch = nullptr;
+    int rc = bn_noalloc_scratch(ctx, &scratch);
+    if (rc) return rc;
+    // same plan as bn_plan(), with the number of partial blocks capped so that 4*cpad + nblk*2*cpad floats fit
+    const int HW = H * W;
+    const long long M = (long long)B * HW;
+    const int max_blk = (int)((DL4JB200_BN_NOALLOC_FLOATS - 4u * (unsigned)cpad) / (2u * (unsigned)cpad));
+    int nblk;
+    long long chunk = 0;
+    if (layout == DL4JB200_NHWC) {
+        int Q = cs / 4, qc = Q < BN_THREADS ? Q : BN_THREADS, R = BN_THREADS / qc;
+        long long want = M / ((long long)R * 8), cap = (long long)ctx->sm_count * 4;
+        nblk = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+        if (nblk > max_blk) nblk = max_blk;
+    } else {
+        long long cap = ((long long)ctx->sm_count * 8 + C - 1) / C, s = M / 4096;
+        if (s > cap) s = cap;
+        if (s > max_blk) s = max_blk;
+        if (s < 1) s = 1;
+        chunk = ((M + s - 1) / s + 3) / 4 * 4;
+        nblk = (int)((M + chunk - 1) / chunk);
+    }
+    float *coef = scratch, *partial = scratch + 4 * (size_t)cpad;
+    const size_t total = (size_t)M * cpad;
+    if (training) {
+        if (layout == DL4JB200_NHWC) {
+            k_bn_partial_nhwc<0><<<nblk, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, x, cs, partial, (int)M, cs);
+        } else {
+            dim3 grid(C, nblk);
+            if ((HW % 4 == 0) && al16(x)) k_bn_partial_nchw<0, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, nullptr, partial, B, C, HW, chunk);
+            else k_bn_partial_nchw<0, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, nullptr, partial, B, C, HW, chunk);
+        }
+        DL4J_CHECK_LAUNCH();
+    }
+    k_bn_finalize_fwd<<<dl4j_ceil_div(cpad, 32), dim3(32, 32), 0, ctx->stream>>>(
+        partial, nblk, x, layout == DL4JB200_NHWC ? 1 : HW, gamma, beta, gmean, gvar, save_mean, save_std, coef, C, cpad,
+        (double)M, decay, eps, training, minibatch);
+    DL4J_CHECK_LAUNCH();
+    if (layout == DL4JB200_NHWC) {
+        k_bn_apply_nhwc<0><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, coef, total / 4, cs, act);
+    } else {
+        if ((HW % 4 == 0) && al16(x) && al16(y)) k_bn_apply_nchw<0, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, coef, total, C, HW, act);
+        else k_bn_apply_nchw<0, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, coef, total, C, HW, act);
+    }
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}

@@ -189,6 +189,20 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
                     const float *save_mean, const float *save_std, const float *act_out, float *dx,
                     float *dgamma, float *dbeta, int B, int C, int H, int W, int layout, int cs);
 
+/* Allocation-free batch-norm forward. No counterpart in the reference: it exists for callers of this library that
+ * must not cause a device allocation while they run -- a loop that cannot take the device-wide stall of a cudaMalloc,
+ * a process whose GPU memory already belongs to another allocator (so a driver allocation may fail), or code
+ * running where CUDA memory management is off limits. Same arguments, results and status codes as dl4jb200_bn_fwd,
+ * but the per-block partial sums and per-channel coefficients live in a fixed 4 MiB array inside the library (held on
+ * every GPU that loads it, until exit) instead of the context's on-demand scratch; it calls no cudaMalloc / cudaFree.
+ * Limit: at most 4096 channels (cs for NHWC), otherwise DL4JB200_ERR_INVALID_ARG; B, H, W are unlimited.
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress): make that first call
+ * before starting any stream capture. All calls share the array, so calls that overlap on the GPU race: keep them on
+ * one stream or serialise them. Nothing needs clearing between calls. */
+int dl4jb200_bn_fwd_noalloc(dl4jb200_ctx *ctx, const float *x, float *y, const float *gamma, const float *beta,
+                            float *gmean, float *gvar, float *save_mean, float *save_std, int B, int C, int H, int W,
+                            int layout, int cs, double decay, double eps, int training, int minibatch, int act);
+
 /* ------------------------------------------------------------------ LRN ---------------------- */
 /* LocalResponseNormalizationHelper.activate / backpropGradient
  * (NN/nn/layers/normalization/LocalResponseNormalizationHelper.java:31-35; CPU semantics
