@@ -132,7 +132,7 @@ def test_resnet50_step_parity_small_batch():
     ref = OracleNet(m, layout, P, p0, fast=True)
     ref.forward(x, lab, True)
     ref.backward()
-    for algo, tol_fwd, min_cos in ((_lib.ALGO_FP32, 1e-3, 0.98), (_lib.ALGO_TC_TF32, 1e-1, 0.80)):
+    for algo, tol_fwd, min_cos in ((_lib.ALGO_FP32, 1e-3, 0.98), (_lib.ALGO_TC_TF32, 2.5e-1, 0.80)):
         net = network.Network(m, B, algo=algo, params=p0)
         try:
             net.set_batch(x, lab)
