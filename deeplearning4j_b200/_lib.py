@@ -72,9 +72,9 @@ PROTOTYPES = {
     "dl4jb200_act_bwd": [_vp, _vp, _vp, _vp, _sz, _i],
     "dl4jb200_pool_fwd": [_vp, _desc_p, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "dl4jb200_pool_bwd": [_vp, _desc_p, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _d],
-    "dl4jb200_bn_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _d, _d, _i, _i, _i],
+    "dl4jb200_bn_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _d, _d, _i, _i, _i, _vp],
     "dl4jb200_bn_fwd_noalloc": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _d, _d, _i, _i, _i],
-    "dl4jb200_bn_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i],
+    "dl4jb200_bn_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i],
     "dl4jb200_lrn_fwd": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _d, _d, _d, _d],
     "dl4jb200_lrn_bwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _d, _d, _d, _d],
     "dl4jb200_add_act_fwd": [_vp, _vp, _vp, _vp, _sz, _i],

@@ -14,10 +14,23 @@
 
 // ------------------------------------------------------------------ pass 1: partial sums
 // MODE 0 (forward):  s1 = sum (x-K),  s2 = sum (x-K)^2          K = pivot[c]
-// MODE 1 (backward): s1 = sum e,      s2 = sum e*(x-mean[c])    e = eps (masked by act_out > 0 if given)
+// MODE 1 (backward): s1 = sum e,      s2 = sum e*(x-mean[c])    e = eps, zeroed where the fused ReLU was inactive; the
+//                    mask is RECOMPUTED as (x-mean)*gamma/std + beta > 0 (same expression as the forward apply), which
+//                    saves reading the activation tensor back from HBM
+struct BnMask {  // fused-ReLU mask inputs for the backward kernels (relu == 0: no mask)
+    const float *gamma, *beta, *std;
+    int relu;
+};
+__device__ __forceinline__ void bn_mask_coef(const BnMask &mk, int c, int C, float &a, float &b) {
+    if (c < C) {
+        a = (float)((mk.gamma ? (double)mk.gamma[c] : 1.0) / (double)mk.std[c]);  // identical to k_bn_finalize_fwd's coef
+        b = mk.beta ? mk.beta[c] : 0.f;
+    } else { a = 0.f; b = 0.f; }
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__restrict__ x, const float *__restrict__ e,
-                                                                const float *__restrict__ act_out,
+                                                                BnMask mk,
                                                                 const float *__restrict__ center, int center_stride,
                                                                 float *__restrict__ partial, int M, int cs) {
     __shared__ float4 red[2][BN_THREADS];
@@ -38,9 +51,15 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__r
                 k.x = c + 0 < center_stride ? center[c + 0] : 0.f; k.y = c + 1 < center_stride ? center[c + 1] : 0.f;
                 k.z = c + 2 < center_stride ? center[c + 2] : 0.f; k.w = c + 3 < center_stride ? center[c + 3] : 0.f;
             }
+            float4 ma = make_float4(0, 0, 0, 0), mb = ma;
+            if (MODE == 1 && mk.relu) {
+                int c = q * 4;
+                bn_mask_coef(mk, c, center_stride, ma.x, mb.x); bn_mask_coef(mk, c + 1, center_stride, ma.y, mb.y);
+                bn_mask_coef(mk, c + 2, center_stride, ma.z, mb.z); bn_mask_coef(mk, c + 3, center_stride, ma.w, mb.w);
+            }
             constexpr int U = 4;  // independent loads in flight per thread (latency hiding)
             for (int rb = r0 + rl; rb < r1; rb += U * R) {
-                float4 v[U], g[U], m[U];
+                float4 v[U], g[U];
 #pragma unroll
                 for (int u = 0; u < U; u++) {
                     int r = rb + u * R;
@@ -49,7 +68,6 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__r
                         v[u] = *reinterpret_cast<const float4 *>(x + o);
                         if (MODE == 1) {
                             g[u] = *reinterpret_cast<const float4 *>(e + o);
-                            if (act_out) m[u] = *reinterpret_cast<const float4 *>(act_out + o);
                         }
                     }
                 }
@@ -63,9 +81,9 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__r
                         a2.x += w.x * w.x; a2.y += w.y * w.y; a2.z += w.z * w.z; a2.w += w.w * w.w;
                     } else {
                         float4 gg = g[u];
-                        if (act_out) {
-                            gg.x = m[u].x > 0.f ? gg.x : 0.f; gg.y = m[u].y > 0.f ? gg.y : 0.f;
-                            gg.z = m[u].z > 0.f ? gg.z : 0.f; gg.w = m[u].w > 0.f ? gg.w : 0.f;
+                        if (mk.relu) {
+                            gg.x = w.x * ma.x + mb.x > 0.f ? gg.x : 0.f; gg.y = w.y * ma.y + mb.y > 0.f ? gg.y : 0.f;
+                            gg.z = w.z * ma.z + mb.z > 0.f ? gg.z : 0.f; gg.w = w.w * ma.w + mb.w > 0.f ? gg.w : 0.f;
                         }
                         a1.x += gg.x; a1.y += gg.y; a1.z += gg.z; a1.w += gg.w;
                         a2.x += gg.x * w.x; a2.y += gg.y * w.y; a2.z += gg.z * w.z; a2.w += gg.w * w.w;
@@ -93,7 +111,7 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__r
 // NCHW: grid (C, S); block (c, s) reduces elements [s*chunk, (s+1)*chunk) of the B*HW values of channel c.
 template <int MODE, bool VEC>
 __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nchw(const float *__restrict__ x, const float *__restrict__ e,
-                                                                const float *__restrict__ act_out,
+                                                                BnMask mk,
                                                                 const float *__restrict__ center, float *__restrict__ partial,
                                                                 int B, int C, int HW, long long chunk) {
     __shared__ float red[2][BN_THREADS];
@@ -101,33 +119,31 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nchw(const float *__r
     const long long total = (long long)B * HW;
     const long long j0 = (long long)blockIdx.y * chunk, j1 = min(total, j0 + chunk);
     const float k = MODE == 0 ? x[(size_t)c * HW] : center[c];
+    float ma = 0.f, mb = 0.f;
+    if (MODE == 1 && mk.relu) bn_mask_coef(mk, c, C, ma, mb);
     float a1 = 0.f, a2 = 0.f;
     constexpr int V = VEC ? 4 : 1;
     for (long long j = j0 + (long long)threadIdx.x * V; j < j1; j += (long long)BN_THREADS * V) {
         long long b = j / HW;
         size_t o = ((size_t)b * C + c) * HW + (size_t)(j - b * HW);
-        float xv[V], ev[V], mv[V];
+        float xv[V], ev[V];
         if (VEC) {
             float4 t = *reinterpret_cast<const float4 *>(x + o);
             xv[0] = t.x; xv[1 % V] = t.y; xv[2 % V] = t.z; xv[3 % V] = t.w;
             if (MODE == 1) {
                 t = *reinterpret_cast<const float4 *>(e + o);
                 ev[0] = t.x; ev[1 % V] = t.y; ev[2 % V] = t.z; ev[3 % V] = t.w;
-                if (act_out) {
-                    t = *reinterpret_cast<const float4 *>(act_out + o);
-                    mv[0] = t.x; mv[1 % V] = t.y; mv[2 % V] = t.z; mv[3 % V] = t.w;
-                }
             }
         } else {
             xv[0] = x[o];
-            if (MODE == 1) { ev[0] = e[o]; if (act_out) mv[0] = act_out[o]; }
+            if (MODE == 1) ev[0] = e[o];
         }
 #pragma unroll
         for (int i = 0; i < V; i++) {
             float d = xv[i] - k;
             if (MODE == 0) { a1 += d; a2 += d * d; }
             else {
-                float g = (act_out && !(mv[i] > 0.f)) ? 0.f : ev[i];
+                float g = (mk.relu && !(d * ma + mb > 0.f)) ? 0.f : ev[i];
                 a1 += g; a2 += g * d;
             }
         }
@@ -210,11 +226,13 @@ __global__ void k_bn_finalize_fwd(const float *__restrict__ partial, int nblk, c
 
 __global__ void k_bn_finalize_bwd(const float *__restrict__ partial, int nblk, const float *__restrict__ gamma,
                                   const float *__restrict__ save_mean, const float *__restrict__ save_std,
-                                  float *dgamma, float *dbeta, float *coef, int C, int cpad, double N) {
+                                  const float *__restrict__ beta, float *dgamma, float *dbeta, float *coef, int C,
+                                  int cpad, double N) {
     int c = blockIdx.x * 32 + threadIdx.x;
     double s1, s2;
     bn_fold_partials(partial, nblk, cpad, c, c < C, s1, s2);
     if (threadIdx.y != 0 || c >= cpad) return;
+    coef[4 * cpad + c] = (c < C && beta) ? beta[c] : 0.f;  // fused-ReLU mask: (x-mean)*a + beta > 0
     if (c >= C) {
         coef[c] = 0.f; coef[cpad + c] = 0.f; coef[2 * cpad + c] = 0.f; coef[3 * cpad + c] = 0.f;
         return;
@@ -235,7 +253,7 @@ __global__ void k_bn_finalize_bwd(const float *__restrict__ partial, int nblk, c
 // MODE 0: y = act((x-centre)*a + c).  MODE 1: dx = a*e' + b*(x-centre) + c, e' = eps masked by act_out.
 template <int MODE>
 __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__ x, const float *__restrict__ e,
-                                                       const float *__restrict__ act_out, float *__restrict__ out,
+                                                       const float *__restrict__ mask_beta, float *__restrict__ out,
                                                        const float *__restrict__ coef, size_t total4, int cs, int act) {
     const int Q = cs >> 2;
     size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -248,15 +266,17 @@ __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__
         v.x -= k.x; v.y -= k.y; v.z -= k.z; v.w -= k.w;
         float4 r;
         if (MODE == 0) {
-            r.x = dl4j_act(v.x * a.x + c.x, act); r.y = dl4j_act(v.y * a.y + c.y, act);
-            r.z = dl4j_act(v.z * a.z + c.z, act); r.w = dl4j_act(v.w * a.w + c.w, act);
+            float4 res = make_float4(0, 0, 0, 0);
+            if (e) res = reinterpret_cast<const float4 *>(e)[i];  // fused ElementWiseVertex(Add): y = act(bn(x) + residual)
+            r.x = dl4j_act(v.x * a.x + c.x + res.x, act); r.y = dl4j_act(v.y * a.y + c.y + res.y, act);
+            r.z = dl4j_act(v.z * a.z + c.z + res.z, act); r.w = dl4j_act(v.w * a.w + c.w + res.w, act);
         } else {
             float4 b = __ldg(reinterpret_cast<const float4 *>(coef + 2 * (size_t)cs) + q);
             float4 g = reinterpret_cast<const float4 *>(e)[i];
-            if (act_out) {
-                float4 m = reinterpret_cast<const float4 *>(act_out)[i];
-                g.x = m.x > 0.f ? g.x : 0.f; g.y = m.y > 0.f ? g.y : 0.f;
-                g.z = m.z > 0.f ? g.z : 0.f; g.w = m.w > 0.f ? g.w : 0.f;
+            if (mask_beta) {  // fused ReLU of the forward: recompute its mask instead of re-reading the activation
+                float4 m = __ldg(reinterpret_cast<const float4 *>(mask_beta) + q);
+                g.x = v.x * a.x + m.x > 0.f ? g.x : 0.f; g.y = v.y * a.y + m.y > 0.f ? g.y : 0.f;
+                g.z = v.z * a.z + m.z > 0.f ? g.z : 0.f; g.w = v.w * a.w + m.w > 0.f ? g.w : 0.f;
             }
             r.x = a.x * g.x + b.x * v.x + c.x; r.y = a.y * g.y + b.y * v.y + c.y;
             r.z = a.z * g.z + b.z * v.z + c.z; r.w = a.w * g.w + b.w * v.w + c.w;
@@ -267,7 +287,7 @@ __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__
 
 template <int MODE, bool VEC>
 __global__ void __launch_bounds__(256) k_bn_apply_nchw(const float *__restrict__ x, const float *__restrict__ e,
-                                                       const float *__restrict__ act_out, float *__restrict__ out,
+                                                       const float *__restrict__ mask_beta, float *__restrict__ out,
                                                        const float *__restrict__ coef, size_t total, int C, int HW,
                                                        int act) {
     constexpr int V = VEC ? 4 : 1;
@@ -276,25 +296,29 @@ __global__ void __launch_bounds__(256) k_bn_apply_nchw(const float *__restrict__
         size_t o = i * V;
         int ch = (int)((o / HW) % C);
         float k = __ldg(coef + ch), a = __ldg(coef + C + ch), b = __ldg(coef + 2 * C + ch), c = __ldg(coef + 3 * C + ch);
-        float xv[V], ev[V], mv[V], r[V];
+        const float mb = (MODE == 1 && mask_beta) ? __ldg(mask_beta + ch) : 0.f;
+        float xv[V], ev[V], r[V];
         if (VEC) {
             float4 t = *reinterpret_cast<const float4 *>(x + o);
             xv[0] = t.x; xv[1 % V] = t.y; xv[2 % V] = t.z; xv[3 % V] = t.w;
             if (MODE == 1) {
                 t = *reinterpret_cast<const float4 *>(e + o);
                 ev[0] = t.x; ev[1 % V] = t.y; ev[2 % V] = t.z; ev[3 % V] = t.w;
-                if (act_out) { t = *reinterpret_cast<const float4 *>(act_out + o); mv[0] = t.x; mv[1 % V] = t.y; mv[2 % V] = t.z; mv[3 % V] = t.w; }
             }
         } else {
             xv[0] = x[o];
-            if (MODE == 1) { ev[0] = e[o]; if (act_out) mv[0] = act_out[o]; }
+            if (MODE == 1) ev[0] = e[o];
+        }
+        if (MODE == 0) {
+#pragma unroll
+            for (int j = 0; j < V; j++) ev[j] = e ? e[o + j] : 0.f;  // optional residual
         }
 #pragma unroll
         for (int j = 0; j < V; j++) {
             float d = xv[j] - k;
-            if (MODE == 0) r[j] = dl4j_act(d * a + c, act);
+            if (MODE == 0) r[j] = dl4j_act(d * a + c + ev[j], act);
             else {
-                float g = (act_out && !(mv[j] > 0.f)) ? 0.f : ev[j];
+                float g = (mask_beta && !(d * a + mb > 0.f)) ? 0.f : ev[j];
                 r[j] = a * g + b * d + c;
             }
         }
@@ -333,11 +357,11 @@ static int bn_plan(dl4jb200_ctx *ctx, int B, int C, int H, int W, int layout, in
         p.nblk = (int)((per + chunk - 1) / chunk);
         p.chunk = chunk;
     }
-    size_t bytes = ((size_t)p.nblk * 2 + 4) * p.cpad * sizeof(float);
+    size_t bytes = ((size_t)p.nblk * 2 + 5) * p.cpad * sizeof(float);
     float *ws = (float *)dl4j_workspace(ctx, 0, bytes);
     if (!ws) return DL4JB200_ERR_CUDA;
     p.coef = ws;  // first: 16-byte aligned coefficient block (cpad % 4 == 0 for NHWC)
-    p.partial = ws + 4 * (size_t)p.cpad;
+    p.partial = ws + 5 * (size_t)p.cpad;  // coef rows: centre, a, b, c, mask beta
     return DL4JB200_OK;
 }
 
@@ -350,8 +374,10 @@ extern "C" {
 
 int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *gamma, const float *beta,
                     float *gmean, float *gvar, float *save_mean, float *save_std, int B, int C, int H, int W,
-                    int layout, int cs, double decay, double eps, int training, int minibatch, int act) {
+                    int layout, int cs, double decay, double eps, int training, int minibatch, int act,
+                    const float *residual) {
     DL4J_REQUIRE(ctx && x && y && gmean && gvar, "bn_fwd: NULL argument");
+    DL4J_REQUIRE(!residual || layout == DL4JB200_NCHW || al16(residual), "bn_fwd: residual must be 16-byte aligned");
     DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, "bn_fwd: bad shape");
     DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "bn_fwd: unknown layout %d", layout);
     DL4J_REQUIRE(layout == DL4JB200_NCHW || (cs >= C && cs % 4 == 0 && al16(x) && al16(y)), "bn_fwd: NHWC needs cs %% 4 == 0, cs >= C and 16-byte aligned tensors");
@@ -364,12 +390,12 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
     const size_t total = (size_t)M * (layout == DL4JB200_NHWC ? cs : C);
     if (training) {
         if (layout == DL4JB200_NHWC) {
-            k_bn_partial_nhwc<0><<<p.nblk, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, x, cs, p.partial, (int)M, cs);
+            k_bn_partial_nhwc<0><<<p.nblk, BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, x, cs, p.partial, (int)M, cs);
         } else {
             dim3 grid(C, p.nblk);
             bool vec = (HW % 4 == 0) && al16(x);
-            if (vec) k_bn_partial_nchw<0, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, nullptr, p.partial, B, C, HW, p.chunk);
-            else k_bn_partial_nchw<0, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, nullptr, p.partial, B, C, HW, p.chunk);
+            if (vec) k_bn_partial_nchw<0, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, nullptr, p.partial, B, C, HW, p.chunk);
+            else k_bn_partial_nchw<0, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, nullptr, p.partial, B, C, HW, p.chunk);
         }
         DL4J_CHECK_LAUNCH();
     }
@@ -378,47 +404,52 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
         p.cpad, (double)M, decay, eps, training, minibatch);
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
-        k_bn_apply_nhwc<0><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, p.coef, total / 4, cs, act);
+        k_bn_apply_nhwc<0><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total / 4, cs, act);
     } else {
         bool vec = (HW % 4 == 0) && al16(x) && al16(y);
-        if (vec) k_bn_apply_nchw<0, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, p.coef, total, C, HW, act);
-        else k_bn_apply_nchw<0, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, p.coef, total, C, HW, act);
+        if (vec) k_bn_apply_nchw<0, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total, C, HW, act);
+        else k_bn_apply_nchw<0, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total, C, HW, act);
     }
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
 
-int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const float *gamma,
-                    const float *save_mean, const float *save_std, const float *act_out, float *dx,
-                    float *dgamma, float *dbeta, int B, int C, int H, int W, int layout, int cs) {
+int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const float *gamma, const float *beta,
+                    const float *save_mean, const float *save_std, int act, float *dx, float *dgamma, float *dbeta, int B,
+                    int C, int H, int W, int layout, int cs) {
     DL4J_REQUIRE(ctx && x && eps && save_mean && save_std && dx, "bn_bwd: NULL argument");
     DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, "bn_bwd: bad shape");
     DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "bn_bwd: unknown layout %d", layout);
-    DL4J_REQUIRE(layout == DL4JB200_NCHW || (cs >= C && cs % 4 == 0 && al16(x) && al16(eps) && al16(dx) && al16(act_out)),
+    DL4J_REQUIRE(layout == DL4JB200_NCHW || (cs >= C && cs % 4 == 0 && al16(x) && al16(eps) && al16(dx)),
                  "bn_bwd: NHWC needs cs %% 4 == 0, cs >= C and 16-byte aligned tensors");
+    DL4J_REQUIRE(act == DL4JB200_ACT_IDENTITY || act == DL4JB200_ACT_RELU, "bn_bwd: only IDENTITY / RELU can be fused (got %d)", act);
     BnPlan p;
     int rc = bn_plan(ctx, B, C, H, W, layout, cs, p);
     if (rc) return rc;
     const int HW = H * W;
     const long long M = (long long)B * HW;
     const size_t total = (size_t)M * (layout == DL4JB200_NHWC ? cs : C);
-    bool vec = (HW % 4 == 0) && al16(x) && al16(eps) && al16(dx) && al16(act_out);
+    const bool relu = act == DL4JB200_ACT_RELU;
+    const BnMask mk{gamma, beta, save_std, relu ? 1 : 0};
+    const float *mask_beta = relu ? p.coef + 4 * (size_t)p.cpad : nullptr;
+    bool vec = (HW % 4 == 0) && al16(x) && al16(eps) && al16(dx);
     if (layout == DL4JB200_NHWC) {
-        k_bn_partial_nhwc<1><<<p.nblk, BN_THREADS, 0, ctx->stream>>>(x, eps, act_out, save_mean, C, p.partial, (int)M, cs);
+        k_bn_partial_nhwc<1><<<p.nblk, BN_THREADS, 0, ctx->stream>>>(x, eps, mk, save_mean, C, p.partial, (int)M, cs);
     } else {
         dim3 grid(C, p.nblk);
-        if (vec) k_bn_partial_nchw<1, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, act_out, save_mean, p.partial, B, C, HW, p.chunk);
-        else k_bn_partial_nchw<1, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, act_out, save_mean, p.partial, B, C, HW, p.chunk);
+        if (vec) k_bn_partial_nchw<1, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, mk, save_mean, p.partial, B, C, HW, p.chunk);
+        else k_bn_partial_nchw<1, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, mk, save_mean, p.partial, B, C, HW, p.chunk);
     }
     DL4J_CHECK_LAUNCH();
     k_bn_finalize_bwd<<<dl4j_ceil_div(p.cpad, 32), dim3(32, 32), 0, ctx->stream>>>(p.partial, p.nblk, gamma, save_mean, save_std,
-                                                                         dgamma, dbeta, p.coef, C, p.cpad, (double)M);
+                                                                               relu ? beta : nullptr, dgamma, dbeta, p.coef, C,
+                                                                               p.cpad, (double)M);
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
-        k_bn_apply_nhwc<1><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, act_out, dx, p.coef, total / 4, cs, 0);
+        k_bn_apply_nhwc<1><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total / 4, cs, 0);
     } else {
-        if (vec) k_bn_apply_nchw<1, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, act_out, dx, p.coef, total, C, HW, 0);
-        else k_bn_apply_nchw<1, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, eps, act_out, dx, p.coef, total, C, HW, 0);
+        if (vec) k_bn_apply_nchw<1, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total, C, HW, 0);
+        else k_bn_apply_nchw<1, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total, C, HW, 0);
     }
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
@@ -512,11 +543,11 @@ extern "C" int dl4jb200_bn_fwd_noalloc(dl4jb200_ctx *ctx, const float *x, float 
     const size_t total = (size_t)M * cpad;
     if (training) {
         if (layout == DL4JB200_NHWC) {
-            k_bn_partial_nhwc<0><<<nblk, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, x, cs, partial, (int)M, cs);
+            k_bn_partial_nhwc<0><<<nblk, BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, x, cs, partial, (int)M, cs);
         } else {
             dim3 grid(C, nblk);
-            if ((HW % 4 == 0) && al16(x)) k_bn_partial_nchw<0, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, nullptr, partial, B, C, HW, chunk);
-            else k_bn_partial_nchw<0, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, nullptr, nullptr, partial, B, C, HW, chunk);
+            if ((HW % 4 == 0) && al16(x)) k_bn_partial_nchw<0, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, nullptr, partial, B, C, HW, chunk);
+            else k_bn_partial_nchw<0, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, nullptr, partial, B, C, HW, chunk);
         }
         DL4J_CHECK_LAUNCH();
     }

@@ -13,6 +13,7 @@ static void geom_finish(ConvGeom &g) {
     g.div_Cg = FastDiv((uint32_t)g.Cg);
     g.div_kW = FastDiv((uint32_t)g.kW);
     g.fast = g.kH <= 16 && g.kW <= 16 && (!g.transposed || (g.sH == 1 && g.sW == 1) || g.taps == 1);
+    g.use_tma = 0;
 }
 
 ConvGeom conv_geom_fwd(const dl4jb200_conv_desc *d, int x_cs) {
@@ -47,7 +48,7 @@ ConvGeom conv_geom_bwd_data(const dl4jb200_conv_desc *d, int delta_cs) {
 // tensor core's truncation of operand mantissas does not bias the filter side.
 __global__ void __launch_bounds__(256) k_pack_filter(const float *__restrict__ w, float *__restrict__ wp, int Cout, int Cin,
                                                      int kH, int kW, int Cg, int Kp, int rows_p, int transposed,
-                                                     int round_tf32) {
+                                                     int round_tf32, int flip) {
     size_t total = (size_t)rows_p * Kp, stride = (size_t)gridDim.x * blockDim.x;
     const int taps = kH * kW;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
@@ -56,7 +57,7 @@ __global__ void __launch_bounds__(256) k_pack_filter(const float *__restrict__ w
         float v = 0.f;
         if (tap < taps) {
             int co = transposed ? c : n, ci = transposed ? n : c;
-            if (co < Cout && ci < Cin) v = w[((size_t)co * Cin + ci) * taps + tap];
+            if (co < Cout && ci < Cin) v = w[((size_t)co * Cin + ci) * taps + (flip ? taps - 1 - tap : tap)];
         }
         wp[i] = round_tf32 ? to_tf32_rna(v) : v;
     }
@@ -88,9 +89,15 @@ __global__ void __launch_bounds__(256) k_colsum_partial(const float *__restrict_
         const int q = qb + (threadIdx.x % qc), rl = threadIdx.x / qc;
         float4 a = make_float4(0, 0, 0, 0);
         if (rl < R)
-            for (int r = r0 + rl; r < r1; r += R) {
-                float4 v = *reinterpret_cast<const float4 *>(d + (size_t)r * cs + (size_t)q * 4);
-                a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+            for (int rb = r0 + rl; rb < r1; rb += 4 * R) {  // 4 independent 128-bit loads in flight per thread
+                float4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    int r = rb + u * R;
+                    v[u] = r < r1 ? *reinterpret_cast<const float4 *>(d + (size_t)r * cs + (size_t)q * 4) : make_float4(0, 0, 0, 0);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) { a.x += v[u].x; a.y += v[u].y; a.z += v[u].z; a.w += v[u].w; }
             }
         red[threadIdx.x] = a;
         __syncthreads();
@@ -168,11 +175,12 @@ int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     }
     ConvGeom g = conv_geom_fwd(d, x_cs);
     DL4J_REQUIRE(x_cs >= g.Cg, "conv_fwd: x pixel stride %d < %d", x_cs, g.Cg);
+    g.use_tma = algo == DL4JB200_CONV_ALGO_TC_TF32 && conv_tc_gemm_can_tma(g);
     const int rows_p = dl4j_round_up(z_cs > d->c_out ? z_cs : d->c_out, 128);
     float *wp = (float *)dl4j_workspace(ctx, 0, (size_t)rows_p * g.Kp * sizeof(float));
     if (!wp) return DL4JB200_ERR_CUDA;
     k_pack_filter<<<grid_for(ctx, (size_t)rows_p * g.Kp), 256, 0, ctx->stream>>>(w, wp, d->c_out, d->c_in, d->k_h, d->k_w, g.Cg,
-                                                                               g.Kp, rows_p, 0, algo == DL4JB200_CONV_ALGO_TC_TF32);
+                                                                               g.Kp, rows_p, 0, algo == DL4JB200_CONV_ALGO_TC_TF32, 0);
     DL4J_CHECK_LAUNCH();
     if (algo == DL4JB200_CONV_ALGO_TC_TF32) rc = conv_tc_gemm(ctx, g, xs, wp, rows_p, bias, zs, d->c_out, z_cs, act);
     else rc = conv_ffma_gemm(ctx, g, xs, wp, bias, zs, d->c_out, z_cs, act);
@@ -218,6 +226,7 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     // ---- filter gradient: split over pixel ranges, partials in scratch, fixed-order reduction into dw
     ConvGeom gf = conv_geom_fwd(d, x_cs);
     DL4J_REQUIRE(x_cs >= gf.Cg, "conv_bwd: x pixel stride %d < %d", x_cs, gf.Cg);
+    gf.use_tma = tcore && conv_tc_gemm_can_tma(gf);
     const int rows_w = dl4j_round_up(d->c_out, 128);
     int splits;
     if (tcore) splits = conv_tc_wgrad_splits(ctx, gf, d->c_out);
@@ -230,6 +239,7 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     }
     // ---- data gradient operand sizes (computed first so that one scratch request covers everything)
     ConvGeom gb = conv_geom_bwd_data(d, delta_cs);
+    gb.use_tma = tcore && dx && conv_tc_gemm_can_tma(gb);
     const int rows_b = dx ? dl4j_round_up(dx_cs > d->c_in ? dx_cs : d->c_in, 128) : 0;
     int nblk = gf.M / 8;  // bias-gradient partial blocks: >= 8 pixel rows each, up to 4 per SM
     if (nblk > ctx->sm_count * 4) nblk = ctx->sm_count * 4;
@@ -255,7 +265,7 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
 
     if (dx) {
         DL4J_REQUIRE(delta_cs >= gb.Cg, "conv_bwd: delta pixel stride %d < %d", delta_cs, gb.Cg);
-        k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, tcore);
+        k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, tcore, gb.use_tma);
         DL4J_CHECK_LAUNCH();
         if (tcore) rc = conv_tc_gemm(ctx, gb, ds, wb, rows_b, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);
         else rc = conv_ffma_gemm(ctx, gb, ds, wb, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);

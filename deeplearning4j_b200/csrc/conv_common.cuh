@@ -16,6 +16,7 @@ struct ConvGeom {
     int Cg, taps, K, Kp, M;
     int transposed;         // 0: iy = y*sH - pT + kh*dH      1: iy = (y + pT - kh*dH)/sH when divisible
     int fast;               // taps are an affine offset from a per-row base pointer (see conv_row_setup)
+    int use_tma;            // operands fetched by TMA (im2col mode); backprop-data then needs the filter packed tap-flipped
     FastDiv div_Wm, div_HWm, div_Cg, div_kW;
 };
 
@@ -100,3 +101,4 @@ int conv_tc_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const f
 int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const float *delta, int delta_cs, int c_out,
                   float *partial, int rows_p, int splits);
 int conv_tc_wgrad_splits(dl4jb200_ctx *ctx, const ConvGeom &g, int c_out);
+bool conv_tc_gemm_can_tma(const ConvGeom &g);

@@ -13,6 +13,7 @@
 //                    the reduction runs over pixels, so both operands are MN-major (a row = 32 consecutive
 //                    M/N values of one pixel); split over pixel ranges, partials reduced by conv.cu.
 #include "conv_common.cuh"
+#include "conv_tma.cuh"
 
 namespace tc {
 
@@ -436,6 +437,289 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
     if (warp == 4) tmem_dealloc<BN>(tmem_d);
 }
 
+// ------------------------------------------------------------------------------------------------
+// TMA-fed variant of k_conv_tc_gemm (channels per tap a multiple of 32, unit stride for backprop-data):
+// one elected thread issues, per K-chunk, ONE im2col-mode TMA for the 128-pixel x 32-channel A tile and ONE tiled
+// TMA for the BN x 32 filter tile; both signal the stage's mbarrier with their byte count. No per-element address
+// arithmetic is left on the SM; padding, stride and image borders are resolved by the TMA unit (zero fill).
+struct TmaGemmGeom {
+    int M, num_k, kW, dH, dW, sH, sW, lowH, lowW;
+    FastDiv div_Wm, div_HWm, div_Cg, div_kW;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_constant__ CUtensorMap tmA,
+                                                              const __grid_constant__ CUtensorMap tmB,
+                                                              const float *__restrict__ bias, float *__restrict__ out,
+                                                              TmaGemmGeom g, int n_valid, int out_cs, int act) {
+    using L = SmemLayout<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    const uint32_t acc_bar = bar_base + 8u * (2 * STAGES), tmem_slot = bar_base + 8u * (2 * STAGES + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.x * BLOCK_M, n0 = blockIdx.y * BN;
+
+    if (tid == 0) {
+        tma::prefetch_desc(&tmA);
+        tma::prefetch_desc(&tmB);
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        mbar_init(acc_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) tmem_alloc<BN>(tmem_slot);
+    float *bias_s = reinterpret_cast<float *>(smem_raw + (base - smem_u32(smem_raw)) + L::BIAS_OFF);
+    if (tid < BN) bias_s[tid] = (bias && n0 + tid < n_valid) ? __ldg(bias + n0 + tid) : 0.f;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_d;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_d) : "r"(tmem_slot));
+
+    if (warp < 4) {
+        if (tid == 0) {
+            // ------------------------------ TMA producer (one thread)
+            uint32_t img, r, oy, ox;
+            g.div_HWm.divmod((uint32_t)m0, img, r);
+            g.div_Wm.divmod(r, oy, ox);
+            const int w0 = (int)ox * g.sW + g.lowW, h0 = (int)oy * g.sH + g.lowH;
+            for (int it = 0; it < g.num_k; ++it) {
+                const int s = it % STAGES;
+                mbar_wait(empty_bar(s), ((it / STAGES) & 1) ^ 1);
+                uint32_t tap, c0, kh, kw;
+                g.div_Cg.divmod((uint32_t)(it * BLOCK_K), tap, c0);
+                g.div_kW.divmod(tap, kh, kw);
+                tma::expect_tx(full_bar(s), (uint32_t)(L::A_BYTES + L::B_BYTES));
+                tma::load_im2col_4d(a_base + s * L::A_BYTES, &tmA, full_bar(s), (int)c0, w0, h0, (int)img,
+                                    (uint16_t)(kw * g.dW), (uint16_t)(kh * g.dH));
+                tma::load_2d(b_base + s * L::B_BYTES, &tmB, full_bar(s), it * BLOCK_K, n0);
+            }
+        }
+        __syncwarp();
+        // ------------------------------ epilogue (same as k_conv_tc_gemm)
+        mbar_wait(acc_bar, 0);
+        tc_fence_after();
+        const int m = m0 + warp * 32 + lane;
+        float *orow = out + (size_t)m * out_cs;
+        const bool full_n = n0 + BN <= n_valid;
+        const uint32_t stage_smem = a_base + warp * 4096u;
+        const int rows_valid = g.M - (m0 + warp * 32);
+#pragma unroll 1
+        for (int cb = 0; cb < BN / 32; cb++) {
+            float v[32];
+            tmem_ld32(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cb * 32), v);
+            const int nb = n0 + cb * 32;
+            if (full_n) {
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const float4 bq = *reinterpret_cast<const float4 *>(bias_s + cb * 32 + q * 4);
+                    v[q * 4 + 0] += bq.x; v[q * 4 + 1] += bq.y; v[q * 4 + 2] += bq.z; v[q * 4 + 3] += bq.w;
+                }
+                if (act == DL4JB200_ACT_RELU) {
+#pragma unroll
+                    for (int e = 0; e < 32; e++) v[e] = fmaxf(v[e], 0.f);
+                } else if (act != DL4JB200_ACT_IDENTITY) {
+#pragma unroll 1
+                    for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);
+                }
+                store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
+            } else if (m < g.M) {
+#pragma unroll 1
+                for (int q = 0; q < 8; q++) {
+                    const int n = nb + q * 4;
+                    if (n >= out_cs) break;
+                    float r4[4];
+#pragma unroll
+                    for (int e = 0; e < 4; e++)
+                        r4[e] = n + e < n_valid ? dl4j_act(v[q * 4 + e] + bias_s[cb * 32 + q * 4 + e], act) : 0.f;
+                    *reinterpret_cast<float4 *>(orow + n) = make_float4(r4[0], r4[1], r4[2], r4[3]);
+                }
+            }
+        }
+    } else {
+        constexpr uint32_t idesc = umma_idesc(BLOCK_M, BN, 0, 0);
+        for (int it = 0; it < g.num_k; ++it) {
+            const int s = it % STAGES;
+            mbar_wait(full_bar(s), (it / STAGES) & 1);
+            tc_fence_after();
+            if (lane == 0) {
+                const uint64_t ad = umma_desc(a_base + s * L::A_BYTES, 16, 1024);
+                const uint64_t bd = umma_desc(b_base + s * L::B_BYTES, 16, 1024);
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / 8; k++) umma_tf32(tmem_d, ad + 2u * k, bd + 2u * k, idesc, (it | k) ? 1u : 0u);
+                umma_commit(empty_bar(s));
+            }
+            __syncwarp();
+        }
+        if (lane == 0) umma_commit(acc_bar);
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc<BN>(tmem_d);
+}
+
+template <int BN, int STAGES>
+static int launch_gemm_tma(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const TmaGemmGeom &g,
+                           const float *bias, float *out, int n_valid, int out_cs, int act) {
+    using L = SmemLayout<BN, STAGES>;
+    auto kern = k_conv_tc_gemm_tma<BN, STAGES>;
+    static bool configured[16] = {false};
+    if (!configured[ctx->device & 15]) {
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        configured[ctx->device & 15] = true;
+    }
+    dim3 grid(dl4j_ceil_div(g.M, BLOCK_M), dl4j_ceil_div(out_cs, BN));
+    kern<<<grid, THREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// TMA-fed backprop-filter. Per 32-pixel K-chunk: 4 tiled TMA loads bring delta[32 px, 128 co] (one 32-channel MN atom
+// each) and BN/32 im2col-mode loads bring the 32-pixel x 32-channel slabs of the taps this CTA's k-columns cover.
+// TMA lays a 32-row x 128-byte box out as 8 consecutive 4-row / 512-byte groups with SWIZZLE_128B_ATOM_32B, which is
+// exactly the MN-major UMMA atom: LBO (next 32-float MN atom) = 4096 B, SBO (next 4-row group) = 512 B.
+struct TmaWgradGeom {
+    int M, kW, dH, dW, sH, sW, lowH, lowW, Kp;
+    FastDiv div_Wm, div_HWm, div_Cg, div_kW;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad_tma(const __grid_constant__ CUtensorMap tmD,
+                                                               const __grid_constant__ CUtensorMap tmX,
+                                                               float *__restrict__ partial, TmaWgradGeom g, int rows_p,
+                                                               int m_per_split, int k_tiles) {
+    using L = SmemLayout<BN, STAGES>;
+    constexpr int NB_ATOMS = BN / 32;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    const uint32_t acc_bar = bar_base + 8u * (2 * STAGES), tmem_slot = bar_base + 8u * (2 * STAGES + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int kt = blockIdx.x % k_tiles, ct = blockIdx.x / k_tiles;
+    const int kcol0 = kt * BN, co0 = ct * BLOCK_M;
+    const int ms = blockIdx.y * m_per_split, me = min(g.M, ms + m_per_split);
+    const int num_k = (me - ms + BLOCK_K - 1) / BLOCK_K;
+
+    if (tid == 0) {
+        tma::prefetch_desc(&tmD);
+        tma::prefetch_desc(&tmX);
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        mbar_init(acc_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) tmem_alloc<BN>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_d;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_d) : "r"(tmem_slot));
+
+    if (warp < 4) {
+        if (tid == 0) {
+            // taps / channel offsets of this CTA's k-column chunks are fixed for the whole kernel
+            int c0[NB_ATOMS];
+            uint16_t offw[NB_ATOMS], offh[NB_ATOMS];
+            bool live[NB_ATOMS];
+#pragma unroll
+            for (int a = 0; a < NB_ATOMS; a++) {
+                const int k = kcol0 + a * 32;
+                live[a] = k < g.Kp;
+                uint32_t tap, cc, kh, kw;
+                g.div_Cg.divmod((uint32_t)k, tap, cc);
+                g.div_kW.divmod(tap, kh, kw);
+                c0[a] = (int)cc; offw[a] = (uint16_t)(kw * g.dW); offh[a] = (uint16_t)(kh * g.dH);
+            }
+            for (int it = 0; it < num_k; ++it) {
+                const int s = it % STAGES;
+                mbar_wait(empty_bar(s), ((it / STAGES) & 1) ^ 1);
+                const int mrow0 = ms + it * BLOCK_K;
+                uint32_t img, r, oy, ox;
+                g.div_HWm.divmod((uint32_t)mrow0, img, r);
+                g.div_Wm.divmod(r, oy, ox);
+                const int w0 = (int)ox * g.sW + g.lowW, h0 = (int)oy * g.sH + g.lowH;
+                tma::expect_tx(full_bar(s), (uint32_t)(L::A_BYTES + L::B_BYTES));
+                const uint32_t a_stage = a_base + s * L::A_BYTES, b_stage = b_base + s * L::B_BYTES;
+#pragma unroll
+                for (int a = 0; a < 4; a++) tma::load_2d(a_stage + a * 4096u, &tmD, full_bar(s), co0 + a * 32, mrow0);
+#pragma unroll
+                for (int a = 0; a < NB_ATOMS; a++) {
+                    // a chunk past Kp still has to deliver its bytes: fetch channel block 0 far outside the image => zeros
+                    if (live[a]) tma::load_im2col_4d(b_stage + a * 4096u, &tmX, full_bar(s), c0[a], w0, h0, (int)img, offw[a], offh[a]);
+                    else tma::load_2d(b_stage + a * 4096u, &tmD, full_bar(s), 0, 0x3fffffff);
+                }
+            }
+        }
+        __syncwarp();
+        mbar_wait(acc_bar, 0);
+        tc_fence_after();
+        const int co = co0 + warp * 32 + lane;
+        float *prow = partial + ((size_t)blockIdx.y * rows_p + co) * g.Kp;
+        const uint32_t stage_smem = a_base + warp * 4096u;
+#pragma unroll 1
+        for (int cb = 0; cb < BN / 32; cb++) {
+            float v[32];
+            tmem_ld32(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)(cb * 32), v);
+            if (kcol0 + cb * 32 + 32 <= g.Kp) {
+                store_tile_32x32(stage_smem, v, lane, partial + ((size_t)blockIdx.y * rows_p + co0 + warp * 32) * g.Kp + kcol0 + cb * 32,
+                                 (size_t)g.Kp, rows_p - (co0 + warp * 32));
+            } else if (co < rows_p) {
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const int k = kcol0 + cb * 32 + q * 4;
+                    if (k < g.Kp) *reinterpret_cast<float4 *>(prow + k) = make_float4(v[q * 4], v[q * 4 + 1], v[q * 4 + 2], v[q * 4 + 3]);
+                }
+            }
+        }
+    } else {
+        constexpr uint32_t idesc = umma_idesc(BLOCK_M, BN, 1, 1);
+        for (int it = 0; it < num_k; ++it) {
+            const int s = it % STAGES;
+            mbar_wait(full_bar(s), (it / STAGES) & 1);
+            tc_fence_after();
+            if (lane == 0) {
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / 8; k++) {  // 8 pixels = two 4-row groups = 1024 B further down every atom
+                    const uint64_t ad = umma_desc(a_base + s * L::A_BYTES + k * 1024, 4096, 512, 1);
+                    const uint64_t bd = umma_desc(b_base + s * L::B_BYTES + k * 1024, 4096, 512, 1);
+                    umma_tf32(tmem_d, ad, bd, idesc, (it | k) ? 1u : 0u);
+                }
+                umma_commit(empty_bar(s));
+            }
+            __syncwarp();
+        }
+        if (lane == 0) umma_commit(acc_bar);
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc<BN>(tmem_d);
+}
+
+template <int BN, int STAGES>
+static int launch_wgrad_tma(dl4jb200_ctx *ctx, const CUtensorMap &tmD, const CUtensorMap &tmX, const TmaWgradGeom &g,
+                            float *partial, int rows_p, int splits, int m_per_split) {
+    using L = SmemLayout<BN, STAGES>;
+    auto kern = k_conv_tc_wgrad_tma<BN, STAGES>;
+    static bool configured[16] = {false};
+    if (!configured[ctx->device & 15]) {
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        configured[ctx->device & 15] = true;
+    }
+    int k_tiles = dl4j_ceil_div(g.Kp, BN), c_tiles = dl4j_ceil_div(rows_p, BLOCK_M);
+    dim3 grid(k_tiles * c_tiles, splits);
+    kern<<<grid, THREADS, L::BYTES, ctx->stream>>>(tmD, tmX, partial, g, rows_p, m_per_split, k_tiles);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
 template <int BN, int STAGES, bool FAST>
 static int launch_gemm_impl(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, const float *bias,
                             float *out, int n_valid, int out_cs, int act) {
@@ -480,9 +764,42 @@ static inline int wgrad_bn(const ConvGeom &g) { return g.Kp >= 128 ? 128 : (g.Kp
 
 }  // namespace tc
 
+// TMA path applies when every K-chunk is 32 channels of one tap and the gather is a plain (strided) window walk.
+bool conv_tc_gemm_can_tma(const ConvGeom &g) {
+    if (g.Cg % 32 != 0 || g.Kp != g.K) return false;
+    if (g.transposed && (g.sH != 1 || g.sW != 1)) return false;
+    if (g.kH > 16 || g.kW > 16 || g.dH * (g.kH - 1) > 255 || g.dW * (g.kW - 1) > 255) return false;
+    const int lowH = g.transposed ? g.pT - (g.kH - 1) * g.dH : -g.pT, lowW = g.transposed ? g.pL - (g.kW - 1) * g.dW : -g.pL;
+    const int sH = g.transposed ? 1 : g.sH, sW = g.transposed ? 1 : g.sW;
+    const int upH = lowH + (g.Hm - 1) * sH + 1 - g.Hs, upW = lowW + (g.Wm - 1) * sW + 1 - g.Ws;
+    if (lowH < -128 || lowH > 127 || lowW < -128 || lowW > 127 || upH < -128 || upH > 127 || upW < -128 || upW > 127) return false;
+    if (sH > 8 || sW > 8) return false;
+    return tma_driver_ready();
+}
+
+static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
+                            const float *bias, float *out, int n_valid, int out_cs, int act) {
+    // backprop-data runs as a forward walk over delta with flipped taps (the filter is packed flipped, conv.cu)
+    const int lowH = g.transposed ? g.pT - (g.kH - 1) * g.dH : -g.pT, lowW = g.transposed ? g.pL - (g.kW - 1) * g.dW : -g.pL;
+    const int sH = g.transposed ? 1 : g.sH, sW = g.transposed ? 1 : g.sW;
+    alignas(64) CUtensorMap tmA, tmB;
+    int rc = tma_make_im2col(&tmA, src, g.B, g.Hs, g.Ws, g.Cg, g.cs_src, lowW, lowH, g.Wm, g.Hm, sW, sH, tc::BLOCK_M,
+                             CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    const int bn = out_cs > 64 ? 128 : (out_cs > 32 ? 64 : 32);
+    rc = tma_make_2d(&tmB, wpack, (uint64_t)n_rows_packed, (uint64_t)g.Kp, (uint64_t)g.Kp, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    tc::TmaGemmGeom t;
+    t.M = g.M; t.num_k = g.Kp / tc::BLOCK_K; t.kW = g.kW; t.dH = g.dH; t.dW = g.dW; t.sH = sH; t.sW = sW; t.lowH = lowH; t.lowW = lowW;
+    t.div_Wm = g.div_Wm; t.div_HWm = g.div_HWm; t.div_Cg = g.div_Cg; t.div_kW = g.div_kW;
+    if (bn == 128) return tc::launch_gemm_tma<128, 3>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    if (bn == 64) return tc::launch_gemm_tma<64, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    return tc::launch_gemm_tma<32, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+}
+
 int conv_tc_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
                  const float *bias, float *out, int n_valid, int out_cs, int act) {
-    (void)n_rows_packed;
+    if (g.use_tma) return conv_tc_gemm_tma(ctx, g, src, wpack, n_rows_packed, bias, out, n_valid, out_cs, act);
     if (out_cs > 64) return tc::launch_gemm<128, 3>(ctx, g, src, wpack, bias, out, n_valid, out_cs, act);
     if (out_cs > 32) return tc::launch_gemm<64, 4>(ctx, g, src, wpack, bias, out, n_valid, out_cs, act);
     return tc::launch_gemm<32, 4>(ctx, g, src, wpack, bias, out, n_valid, out_cs, act);
@@ -507,6 +824,22 @@ int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const fl
     if (dl4j_ceil_div(g.M, mps) != splits) {
         dl4j_set_error("conv_tc_wgrad: split count %d leaves an empty split (M=%d)", splits, g.M);
         return DL4JB200_ERR_INVALID_ARG;
+    }
+    if (g.use_tma) {
+        alignas(64) CUtensorMap tmD, tmX;
+        int rc = tma_make_2d(&tmD, delta, (uint64_t)g.M, (uint64_t)delta_cs, (uint64_t)delta_cs, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+        if (rc) return rc;
+        rc = tma_make_im2col(&tmX, x, g.B, g.Hs, g.Ws, g.Cg, g.cs_src, -g.pL, -g.pT, g.Wm, g.Hm, g.sW, g.sH, tc::BLOCK_K,
+                             CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+        if (rc) return rc;
+        tc::TmaWgradGeom t;
+        t.M = g.M; t.kW = g.kW; t.dH = g.dH; t.dW = g.dW; t.sH = g.sH; t.sW = g.sW; t.lowH = -g.pT; t.lowW = -g.pL; t.Kp = g.Kp;
+        t.div_Wm = g.div_Wm; t.div_HWm = g.div_HWm; t.div_Cg = g.div_Cg; t.div_kW = g.div_kW;
+        switch (tc::wgrad_bn(g)) {
+        case 128: return tc::launch_wgrad_tma<128, 3>(ctx, tmD, tmX, t, partial, rows_p, splits, mps);
+        case 64: return tc::launch_wgrad_tma<64, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, mps);
+        default: return tc::launch_wgrad_tma<32, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, mps);
+        }
     }
     switch (tc::wgrad_bn(g)) {
     case 128: return tc::launch_wgrad<128, 3>(ctx, g, x, delta, delta_cs, partial, rows_p, splits, mps);

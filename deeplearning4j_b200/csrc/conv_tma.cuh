@@ -1,0 +1,53 @@
+// TMA plumbing for the convolution kernels: tensor-map construction on the host (driver entry points are fetched
+// through the runtime, so the library does not link libcuda) and the cp.async.bulk.tensor PTX wrappers.
+//
+// Activations are NHWC with pixel stride cs, i.e. a rank-4 tensor {C, W, H, N} (innermost first). The A operand of
+// the implicit GEMM is loaded in TMA *im2col* mode: one instruction fetches 128 consecutive output pixels
+// (traversing w -> h -> n inside the padded bounding box, with the convolution stride as traversal stride) x 32
+// channels of one filter tap (tap offset passed per instruction), zero-filling whatever falls outside the image.
+#pragma once
+#include <cuda.h>
+
+#include "conv_common.cuh"
+
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                        const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                        CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*PFN_tmapEncodeIm2col)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                         const cuuint64_t *, const int *, const int *, cuuint32_t, cuuint32_t,
+                                         const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                         CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// returns false (and sets the error string) if the driver does not expose the encoders
+bool tma_driver_ready();
+// rows x cols fp32 row-major matrix (row stride ld floats); box = box_rows x 32 floats, given swizzle
+int tma_make_2d(CUtensorMap *out, const float *base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                CUtensorMapSwizzle swizzle);
+// NHWC activation tensor for im2col loads: `pixels` base pixels x 32 channels per instruction.
+// lower_w/h: bounding-box lower corner (= -pad for a forward convolution); out_w/h: number of base pixels per row/col;
+// stride_w/h: traversal stride.
+int tma_make_im2col(CUtensorMap *out, const float *base, int N, int H, int W, int C, int cs, int lower_w, int lower_h,
+                    int out_w, int out_h, int stride_w, int stride_h, uint32_t pixels, CUtensorMapSwizzle swizzle);
+
+#ifdef __CUDACC__
+namespace tma {
+__device__ __forceinline__ void prefetch_desc(const CUtensorMap *m) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+}
+__device__ __forceinline__ void expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void load_2d(uint32_t dst, const CUtensorMap *m, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+                 "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void load_im2col_4d(uint32_t dst, const CUtensorMap *m, uint32_t bar, int c, int w, int h, int n,
+                                               uint16_t off_w, uint16_t off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+        : "memory");
+}
+}  // namespace tma
+#endif

@@ -256,7 +256,7 @@ class CudnnBatchNormalizationHelper(_BaseHelper):
         psm = c.scratch("bn.save_mean", Cc * 4)
         pss = c.scratch("bn.save_std", Cc * 4)
         _lib.call("dl4jb200_bn_fwd", c.handle, px, py, pg, pb, pm, pv, psm, pss, B, Cc, H, W, NCHW, 0, float(decay),
-                  float(eps), int(bool(training)), int(bool(minibatch)), ACT_IDENTITY)
+                  float(eps), int(bool(training)), int(bool(minibatch)), ACT_IDENTITY, None)
         if training:  # running statistics are parameters, updated in place in the flat vector
             _write_view(mean, c.download(pm, (Cc,)))
             _write_view(var, c.download(pv, (Cc,)))
@@ -277,7 +277,7 @@ class CudnnBatchNormalizationHelper(_BaseHelper):
         pdx = c.scratch("bn.dx", input.size * 4)
         pdg = c.scratch("bn.dgamma", Cc * 4)
         pdb = c.scratch("bn.dbeta", Cc * 4)
-        _lib.call("dl4jb200_bn_bwd", c.handle, px, pe, pg, psm, pss, None, pdx, pdg, pdb, B, Cc, H, W, NCHW, 0)
+        _lib.call("dl4jb200_bn_bwd", c.handle, px, pe, pg, None, psm, pss, ACT_IDENTITY, pdx, pdg, pdb, B, Cc, H, W, NCHW, 0)
         _write_view(dGammaView, c.download(pdg, (Cc,)))
         _write_view(dBetaView, c.download(pdb, (Cc,)))
         return {"gamma": dGammaView, "beta": dBetaView}, c.download(pdx, input.shape)

@@ -67,6 +67,17 @@ class Network:
                 self.consumers[u].append(v["name"])
         self.out, self.cs, self.eps, self.aux = {}, {}, {}, {}
         self.fold_pad = {}
+        # BatchNormalization (identity activation) consumed only by an ElementWiseVertex(Add): the add (+ its ReLU) is
+        # folded into the BN apply pass, y = act(bn(x) + other). fused_bn[bn] = add vertex; fused_add[add] = (bn, other)
+        self.fused_bn, self.fused_add = {}, {}
+        for v in self.model["vertices"]:
+            if v["op"] == "add" and len(v["in"]) == 2:
+                for i, u in enumerate(v["in"]):
+                    uv = self.vmap[u]
+                    if uv["op"] == "bn" and uv["act"] == "identity" and self.consumers[u] == [v["name"]] and v["in"][1 - i] != u:
+                        self.fused_bn[u] = v["name"]
+                        self.fused_add[v["name"]] = (u, v["in"][1 - i])
+                        break
         for v in self.model["vertices"]:
             n, op, s = v["name"], v["op"], self.shapes[v["name"]]
             if len(s) == 3:
@@ -86,6 +97,9 @@ class Network:
                 if not ok:
                     raise NotImplementedError("stand-alone ZeroPaddingLayer")
                 self.fold_pad[cons[0]] = (v["in"][0], t, l)
+                continue
+            if n in self.fused_bn:
+                self.aux[n] = (self._buf(s[0]), self._buf(s[0]))  # saved mean / std; the output itself is never stored
                 continue
             if op == "flatten":
                 src = self.shapes[v["in"][0]]
@@ -182,7 +196,7 @@ class Network:
         for v in self.model["vertices"]:
             n, op = v["name"], v["op"]
             self._cur = n
-            if op in ("input", "zeropad") or self.out.get(n, 0) is None:
+            if op in ("input", "zeropad") or self.out.get(n, 0) is None or n in self.fused_bn:
                 continue
             if op == "conv":
                 src, d = self._conv_desc(v)
@@ -191,17 +205,23 @@ class Network:
                 pb, _, _, _ = self._p(n, "b")
                 self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
                            self.cs[n], _ACT[v["act"]], self.algo)
-            elif op == "bn":
-                x, xcs = self._src(v["in"][0])
-                s = self.shapes[n]
-                pg, _, _, _ = self._p(n, "gamma")
-                pbeta, _, _, _ = self._p(n, "beta")
-                pm, _, _, _ = self._p(n, "mean")
-                pv, _, _, _ = self._p(n, "var")
-                sm, ss = self.aux[n]
+            elif op == "bn" or n in self.fused_add:
+                if op == "bn":
+                    bnv, res, act = v, None, _ACT[v["act"]]
+                else:  # Add(+ReLU) folded into the BatchNormalization that feeds it
+                    bname, other = self.fused_add[n]
+                    bnv, res, act = self.vmap[bname], self._ptr(self._src(other)[0]), _ACT[v["act"]]
+                bn = bnv["name"]
+                x, xcs = self._src(bnv["in"][0])
+                s = self.shapes[bn]
+                pg, _, _, _ = self._p(bn, "gamma")
+                pbeta, _, _, _ = self._p(bn, "beta")
+                pm, _, _, _ = self._p(bn, "mean")
+                pv, _, _, _ = self._p(bn, "var")
+                sm, ss = self.aux[bn]
                 self._call("dl4jb200_bn_fwd", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm), self._ptr(ss),
-                           B, s[0], s[1], s[2], L.NHWC, xcs, float(v["decay"]), float(v["eps"]), int(train),
-                           int(self.model["minibatch"]), _ACT[v["act"]])
+                           B, s[0], s[1], s[2], L.NHWC, xcs, float(bnv["decay"]), float(bnv["eps"]), int(train),
+                           int(self.model["minibatch"]), act, res)
             elif op == "pool":
                 d = self._pool_desc(v)
                 x, xcs = self._src(v["in"][0])
@@ -304,7 +324,7 @@ class Network:
         for v in reversed(self.model["vertices"]):
             n, op = v["name"], v["op"]
             self._cur = n
-            if op in ("input", "zeropad") or self.out.get(n, 0) is None:
+            if op in ("input", "zeropad") or (self.out.get(n, 0) is None and n not in self.fused_bn):
                 continue
             if op == "output":
                 e = self.aux[n]
@@ -333,11 +353,10 @@ class Network:
                 x, xcs = self._src(u)
                 s = self.shapes[n]
                 pg, gg, _, _ = self._p(n, "gamma")
-                _, gbeta, _, _ = self._p(n, "beta")
+                pbeta, gbeta, _, _ = self._p(n, "beta")
                 sm, ss = self.aux[n]
-                ao = self._ptr(self.out[n]) if v["act"] == "relu" else None
-                self._emit(u, lambda dx: self._call("dl4jb200_bn_bwd", self._ptr(x), self._ptr(e), pg, self._ptr(sm), self._ptr(ss), ao,
-                                                    dx, gg, gbeta, B, s[0], s[1], s[2], L.NHWC, xcs))
+                self._emit(u, lambda dx: self._call("dl4jb200_bn_bwd", self._ptr(x), self._ptr(e), pg, pbeta, self._ptr(sm),
+                                                    self._ptr(ss), _ACT[v["act"]], dx, gg, gbeta, B, s[0], s[1], s[2], L.NHWC, xcs))
             elif op == "pool":
                 u = v["in"][0]
                 x, xcs = self._src(u)

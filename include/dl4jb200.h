@@ -178,16 +178,20 @@ int dl4jb200_pool_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
  * gvar = decay*gvar + (1-decay)*(var+eps) updated IN PLACE (minibatch==0: plain assignment);
  * save_mean / save_std [C] receive what the layer keeps for backward. inference (training==0):
  * std = sqrt(gvar) with no eps added. gamma/beta NULL => 1 / 0 (lockGammaBeta). act: optional fused
- * activation of the following ActivationLayer (IDENTITY or RELU). */
+ * activation of the following ActivationLayer (IDENTITY or RELU). residual: NULL, or a tensor of x's shape/layout
+ * added before the activation, y = act(bn(x) + residual) -- the ElementWiseVertex(Add) + ActivationLayer that
+ * close a ResNet block (NN/nn/graph/vertex/impl/ElementWiseVertex.java:81-86) folded into the BN apply pass. */
 int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *gamma, const float *beta,
                     float *gmean, float *gvar, float *save_mean, float *save_std, int B, int C, int H, int W,
-                    int layout, int cs, double decay, double eps, int training, int minibatch, int act);
+                    int layout, int cs, double decay, double eps, int training, int minibatch, int act,
+                    const float *residual);
 /* BatchNormalizationHelper.backpropGradient (BatchNormalizationHelper.java:31-32; CPU semantics
- * BatchNormalization.java:171-210). dgamma / dbeta are the gradient views, written in place. act_out:
- * NULL, or the fused-ReLU forward output whose mask is applied to eps first. */
-int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const float *gamma,
-                    const float *save_mean, const float *save_std, const float *act_out, float *dx,
-                    float *dgamma, float *dbeta, int B, int C, int H, int W, int layout, int cs);
+ * BatchNormalization.java:171-210). dgamma / dbeta are the gradient views, written in place. act: IDENTITY, or RELU
+ * when the forward call fused the following ActivationLayer -- eps is then masked with relu'(gamma*xhat+beta), the
+ * mask being recomputed from x (beta is read only in that case) instead of re-reading the activation. */
+int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const float *gamma, const float *beta,
+                    const float *save_mean, const float *save_std, int act, float *dx, float *dgamma, float *dbeta,
+                    int B, int C, int H, int W, int layout, int cs);
 
 /* Allocation-free batch-norm forward. No counterpart in the reference: it exists for callers of this library that
  * must not cause a device allocation while they run -- a loop that cannot take the device-wide stall of a cudaMalloc,

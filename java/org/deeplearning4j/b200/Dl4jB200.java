@@ -59,9 +59,9 @@ public class Dl4jB200 {
     public static native int dl4jb200_bn_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, FloatPointer y,
                     @Const FloatPointer gamma, @Const FloatPointer beta, FloatPointer gmean, FloatPointer gvar, FloatPointer saveMean,
                     FloatPointer saveStd, int b, int c, int h, int w, int layout, int cs, double decay, double eps, int training,
-                    int minibatch, int act);
+                    int minibatch, int act, @Const FloatPointer residual);
     public static native int dl4jb200_bn_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, @Const FloatPointer eps,
-                    @Const FloatPointer gamma, @Const FloatPointer saveMean, @Const FloatPointer saveStd, @Const FloatPointer actOut,
+                    @Const FloatPointer gamma, @Const FloatPointer beta, @Const FloatPointer saveMean, @Const FloatPointer saveStd, int act,
                     FloatPointer dx, FloatPointer dgamma, FloatPointer dbeta, int b, int c, int h, int w, int layout, int cs);
     public static native int dl4jb200_lrn_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, FloatPointer y, int b, int c,
                     int h, int w, int layout, int cs, double k, double n, double alpha, double beta);

@@ -27,7 +27,7 @@ public class CudnnBatchNormalizationHelper implements BatchNormalizationHelper {
         // gVar = decay*gVar + (1-decay)*(var+eps) (BatchNormalization.java:377-384), NOT cuDNN's exponentialAverageFactor
         B200Context.check(Dl4jB200.dl4jb200_bn_fwd(ctx.handle(), ctx.in(x), ctx.out(y), ctx.in(gamma), ctx.in(beta), ctx.inout(mean),
                         ctx.inout(var), ctx.out(saveMean), ctx.out(saveStd), shape[0], shape[1], shape[2], shape[3], Dl4jB200.NCHW, 0,
-                        decay, eps, training ? 1 : 0, 1, Dl4jB200.ACT_IDENTITY));
+                        decay, eps, training ? 1 : 0, 1, Dl4jB200.ACT_IDENTITY, null));
         if (training) { ctx.done(mean); ctx.done(var); }
         return ctx.done(y);
     }
@@ -38,8 +38,8 @@ public class CudnnBatchNormalizationHelper implements BatchNormalizationHelper {
         input = B200Context.dense(input);
         epsilon = B200Context.dense(epsilon);
         INDArray epsNext = B200Context.createOutput(input.shape());
-        B200Context.check(Dl4jB200.dl4jb200_bn_bwd(ctx.handle(), ctx.in(input), ctx.in(epsilon), ctx.in(gamma), ctx.in(saveMean),
-                        ctx.in(saveStd), null, ctx.out(epsNext), ctx.out(dGammaView), ctx.out(dBetaView), shape[0], shape[1], shape[2],
+        B200Context.check(Dl4jB200.dl4jb200_bn_bwd(ctx.handle(), ctx.in(input), ctx.in(epsilon), ctx.in(gamma), null, ctx.in(saveMean),
+                        ctx.in(saveStd), Dl4jB200.ACT_IDENTITY, ctx.out(epsNext), ctx.out(dGammaView), ctx.out(dBetaView), shape[0], shape[1], shape[2],
                         shape[3], Dl4jB200.NCHW, 0));
         Gradient g = new DefaultGradient();
         g.setGradientFor(BatchNormalizationParamInitializer.GAMMA, ctx.done(dGammaView));

@@ -23,7 +23,7 @@ def re(a, b): return float(np.abs(a.astype(np.float64) - b).max() / max(np.abs(b
 print("== forward")
 for v in m["vertices"]:
     n = v["name"]
-    if v["op"] in ("input", "zeropad"): continue
+    if v["op"] in ("input", "zeropad") or n in net.fused_bn: continue
     got = net.output_host(n); r = ref.act[n]
     print(f"{n:24s} {v['op']:8s} {re(got, r.reshape(got.shape)):.3e}")
 print("== grads (reverse)")

@@ -276,13 +276,13 @@ def test_batchnorm_nhwc_fused_relu(H, ctx, oracle, shape):
         py, pdx = dev.empty(n * 4), dev.empty(n * 4)
         psm, pss, pdg, pdb = (dev.empty(Cc * 4) for _ in range(4))
         _lib.call("dl4jb200_bn_fwd", ctx.handle, px, py, pg, pb, pm, pv, psm, pss, B, Cc, Hh, W, H.NHWC, cs, 0.9, 1e-5, 1, 1,
-                  H.ACT_RELU)
+                  H.ACT_RELU, None)
         a = dev.get(py, (B, Hh, W, cs))
         assert rel_err(from_nhwc(a, Cc), ar) <= TOL_BW
         assert not a[..., Cc:].any()  # padding channels stay zero
         np.testing.assert_allclose(dev.get(pm, (Cc,)), gm_r, rtol=1e-5, atol=1e-6)
         np.testing.assert_allclose(dev.get(pv, (Cc,)), gv_r, rtol=1e-5, atol=1e-6)
-        _lib.call("dl4jb200_bn_bwd", ctx.handle, px, pe, pg, psm, pss, py, pdx, pdg, pdb, B, Cc, Hh, W, H.NHWC, cs)
+        _lib.call("dl4jb200_bn_bwd", ctx.handle, px, pe, pg, pb, psm, pss, H.ACT_RELU, pdx, pdg, pdb, B, Cc, Hh, W, H.NHWC, cs)
         # elements with BN output exactly 0 are measure-zero for random data; masks agree
         assert rel_err(from_nhwc(dev.get(pdx, (B, Hh, W, cs)), Cc), dxr) <= 2e-5
         assert rel_err(dev.get(pdg, (Cc,)), dgr) <= TOL_BW and rel_err(dev.get(pdb, (Cc,)), dbr) <= TOL_BW
