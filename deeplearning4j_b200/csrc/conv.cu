@@ -176,7 +176,7 @@ int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     ConvGeom g = conv_geom_fwd(d, x_cs);
     DL4J_REQUIRE(x_cs >= g.Cg, "conv_fwd: x pixel stride %d < %d", x_cs, g.Cg);
     g.use_tma = algo == DL4JB200_CONV_ALGO_TC_TF32 && conv_tc_gemm_can_tma(g);
-    const int rows_p = dl4j_round_up(z_cs > d->c_out ? z_cs : d->c_out, 128);
+    const int rows_p = dl4j_round_up(z_cs > d->c_out ? z_cs : d->c_out, 256);
     float *wp = (float *)dl4j_workspace(ctx, 0, (size_t)rows_p * g.Kp * sizeof(float));
     if (!wp) return DL4JB200_ERR_CUDA;
     k_pack_filter<<<grid_for(ctx, (size_t)rows_p * g.Kp), 256, 0, ctx->stream>>>(w, wp, d->c_out, d->c_in, d->k_h, d->k_w, g.Cg,
@@ -240,7 +240,7 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     // ---- data gradient operand sizes (computed first so that one scratch request covers everything)
     ConvGeom gb = conv_geom_bwd_data(d, delta_cs);
     gb.use_tma = tcore && dx && conv_tc_gemm_can_tma(gb);
-    const int rows_b = dx ? dl4j_round_up(dx_cs > d->c_in ? dx_cs : d->c_in, 128) : 0;
+    const int rows_b = dx ? dl4j_round_up(dx_cs > d->c_in ? dx_cs : d->c_in, 256) : 0;
     int nblk = gf.M / 8;  // bias-gradient partial blocks: >= 8 pixel rows each, up to 4 per SM
     if (nblk > ctx->sm_count * 4) nblk = ctx->sm_count * 4;
     if (nblk < 1) nblk = 1;

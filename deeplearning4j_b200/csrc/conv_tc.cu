@@ -266,15 +266,15 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restric
 #pragma unroll
                     for (int e = 0; e < 32; e++) v[e] = fmaxf(v[e], 0.f);
                 } else if (act != DL4JB200_ACT_IDENTITY) {
-#pragma unroll 1
-                    for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);
+#pragma unroll
+                    for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);  // static indices keep v[] in registers
                 }
                 store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
             } else if (m < g.M) {
-#pragma unroll 1
+#pragma unroll
                 for (int q = 0; q < 8; q++) {
                     const int n = nb + q * 4;
-                    if (n >= out_cs) break;
+                    if (n >= out_cs) continue;
                     float r[4];
 #pragma unroll
                     for (int e = 0; e < 4; e++)
@@ -522,15 +522,15 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
 #pragma unroll
                     for (int e = 0; e < 32; e++) v[e] = fmaxf(v[e], 0.f);
                 } else if (act != DL4JB200_ACT_IDENTITY) {
-#pragma unroll 1
-                    for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);
+#pragma unroll
+                    for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);  // static indices keep v[] in registers
                 }
                 store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
             } else if (m < g.M) {
-#pragma unroll 1
+#pragma unroll
                 for (int q = 0; q < 8; q++) {
                     const int n = nb + q * 4;
-                    if (n >= out_cs) break;
+                    if (n >= out_cs) continue;
                     float r4[4];
 #pragma unroll
                     for (int e = 0; e < 4; e++)
@@ -560,6 +560,182 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
     tc_fence_before();
     __syncthreads();
     if (warp == 4) tmem_dealloc<BN>(tmem_d);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Persistent form of the TMA-fed GEMM: one CTA per SM loops over output tiles. Six warps: 0-3 epilogue, 4 MMA issuer,
+// 5 TMA producer. The accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i (TMEM ->
+// registers -> staging smem -> coalesced global stores) overlaps the TMA loads and MMAs of tile i+1, and the operand
+// pipeline never drains between tiles. This is what the small-K 1x1 convolutions need: their per-tile main loop is
+// only 2-8 K-chunks long, so set-up, drain and epilogue dominated the one-tile-per-CTA kernel.
+constexpr int PTHREADS = 192;
+
+template <int BN, int STAGES>
+struct PersistSmem {
+    static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 4;
+    static constexpr int B_BYTES = BN * BLOCK_K * 4;
+    static constexpr int STAGING_OFF = STAGES * (A_BYTES + B_BYTES);  // 4 warps x 4 KB epilogue staging
+    static constexpr int BAR_OFF = STAGING_OFF + 4 * 4096;
+    static constexpr int BYTES = BAR_OFF + 256 + 1024;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const __grid_constant__ CUtensorMap tmA,
+                                                                          const __grid_constant__ CUtensorMap tmB,
+                                                                          const float *__restrict__ bias,
+                                                                          float *__restrict__ out, TmaGemmGeom g,
+                                                                          int n_valid, int out_cs, int act, int n_tiles,
+                                                                          int total_tiles) {
+    using L = PersistSmem<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    auto tfull_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + b); };
+    auto tempty_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + 2 + b); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        tma::prefetch_desc(&tmA);
+        tma::prefetch_desc(&tmB);
+        for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int b = 0; b < 2; b++) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) tmem_alloc<2 * BN>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_d;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_d) : "r"(tmem_slot));
+
+    if (warp == 5) {
+        // ------------------------------ TMA producer
+        if (lane == 0) {
+            int kit = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * BN;
+                uint32_t img, r, oy, ox;
+                g.div_HWm.divmod((uint32_t)m0, img, r);
+                g.div_Wm.divmod(r, oy, ox);
+                const int w0 = (int)ox * g.sW + g.lowW, h0 = (int)oy * g.sH + g.lowH;
+                for (int it = 0; it < g.num_k; ++it, ++kit) {
+                    const int s = kit % STAGES;
+                    mbar_wait(empty_bar(s), ((kit / STAGES) & 1) ^ 1);
+                    uint32_t tap, c0, kh, kw;
+                    g.div_Cg.divmod((uint32_t)(it * BLOCK_K), tap, c0);
+                    g.div_kW.divmod(tap, kh, kw);
+                    tma::expect_tx(full_bar(s), (uint32_t)(L::A_BYTES + L::B_BYTES));
+                    tma::load_im2col_4d(a_base + s * L::A_BYTES, &tmA, full_bar(s), (int)c0, w0, h0, (int)img,
+                                        (uint16_t)(kw * g.dW), (uint16_t)(kh * g.dH));
+                    tma::load_2d(b_base + s * L::B_BYTES, &tmB, full_bar(s), it * BLOCK_K, n0);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 4) {
+        // ------------------------------ MMA issuer
+        constexpr uint32_t idesc = umma_idesc(BLOCK_M, BN, 0, 0);
+        int kit = 0, i = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+            const int buf = i & 1;
+            mbar_wait(tempty_bar(buf), ((i >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+            tc_fence_after();
+            const uint32_t acc = tmem_d + (uint32_t)(buf * BN);
+            for (int it = 0; it < g.num_k; ++it, ++kit) {
+                const int s = kit % STAGES;
+                mbar_wait(full_bar(s), (kit / STAGES) & 1);
+                tc_fence_after();
+                if (lane == 0) {
+                    const uint64_t ad = umma_desc(a_base + s * L::A_BYTES, 16, 1024);
+                    const uint64_t bd = umma_desc(b_base + s * L::B_BYTES, 16, 1024);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / 8; k++) umma_tf32(acc, ad + 2u * k, bd + 2u * k, idesc, (it | k) ? 1u : 0u);
+                    umma_commit(empty_bar(s));
+                }
+                __syncwarp();
+            }
+            if (lane == 0) umma_commit(tfull_bar(buf));
+            __syncwarp();
+        }
+    } else {
+        // ------------------------------ epilogue warps 0-3
+        const uint32_t stage_smem = base + L::STAGING_OFF + warp * 4096u;
+        int i = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+            const int buf = i & 1;
+            const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * BN;
+            const bool full_n = n0 + BN <= n_valid;
+            const int m = m0 + warp * 32 + lane;
+            const int rows_valid = g.M - (m0 + warp * 32);
+            mbar_wait(tfull_bar(buf), (i >> 1) & 1);
+            tc_fence_after();
+            const uint32_t acc = tmem_d + (uint32_t)(buf * BN) + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+            for (int cb = 0; cb < BN / 32; cb++) {
+                float v[32];
+                tmem_ld32(acc + (uint32_t)(cb * 32), v);
+                if (cb == BN / 32 - 1) {  // last TMEM read of this tile: hand the accumulator back to the MMA warp
+                    tc_fence_before();
+                    mbar_arrive(tempty_bar(buf));
+                }
+                const int nb = n0 + cb * 32;
+                if (full_n) {
+                    if (bias) {
+#pragma unroll
+                        for (int q = 0; q < 8; q++) {
+                            const float4 bq = __ldg(reinterpret_cast<const float4 *>(bias + nb) + q);
+                            v[q * 4 + 0] += bq.x; v[q * 4 + 1] += bq.y; v[q * 4 + 2] += bq.z; v[q * 4 + 3] += bq.w;
+                        }
+                    }
+                    if (act == DL4JB200_ACT_RELU) {
+#pragma unroll
+                        for (int e = 0; e < 32; e++) v[e] = fmaxf(v[e], 0.f);
+                    } else if (act != DL4JB200_ACT_IDENTITY) {
+#pragma unroll
+                        for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);  // static indices keep v[] in registers
+                    }
+                    store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
+                } else if (m < g.M) {
+                    float *orow = out + (size_t)m * out_cs;
+#pragma unroll
+                    for (int q = 0; q < 8; q++) {
+                        const int n = nb + q * 4;
+                        if (n >= out_cs) continue;
+                        float r4[4];
+#pragma unroll
+                        for (int e = 0; e < 4; e++) {
+                            const int nn = n + e;
+                            r4[e] = nn < n_valid ? dl4j_act(v[q * 4 + e] + (bias ? __ldg(bias + nn) : 0.f), act) : 0.f;
+                        }
+                        *reinterpret_cast<float4 *>(orow + n) = make_float4(r4[0], r4[1], r4[2], r4[3]);
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc<2 * BN>(tmem_d);
+}
+
+template <int BN, int STAGES>
+static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const TmaGemmGeom &g,
+                                   const float *bias, float *out, int n_valid, int out_cs, int act) {
+    using L = PersistSmem<BN, STAGES>;
+    auto kern = k_conv_tc_gemm_tma_persist<BN, STAGES>;
+    static bool configured[16] = {false};
+    if (!configured[ctx->device & 15]) {
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        configured[ctx->device & 15] = true;
+    }
+    const int n_tiles = dl4j_ceil_div(out_cs, BN), total = dl4j_ceil_div(g.M, BLOCK_M) * n_tiles;
+    const int grid = total < ctx->sm_count ? total : ctx->sm_count;
+    kern<<<grid, PTHREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act, n_tiles, total);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
 }
 
 template <int BN, int STAGES>
@@ -786,15 +962,26 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
     int rc = tma_make_im2col(&tmA, src, g.B, g.Hs, g.Ws, g.Cg, g.cs_src, lowW, lowH, g.Wm, g.Hm, sW, sH, tc::BLOCK_M,
                              CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
-    const int bn = out_cs > 64 ? 128 : (out_cs > 32 ? 64 : 32);
+    const bool aligned_bias = !bias || ((uintptr_t)bias & 15) == 0;
+    // 256-wide tiles (one UMMA of N=256, the whole TMEM as a double-buffered accumulator) when the layer is wide and
+    // there are still at least ~2 tiles per SM
+    const bool wide = aligned_bias && out_cs >= 256 && n_rows_packed % 256 == 0 && g.Kp >= 256 &&
+                      (long long)dl4j_ceil_div(g.M, tc::BLOCK_M) * dl4j_ceil_div(out_cs, 256) >= 2LL * ctx->sm_count;
+    const int bn = wide ? 256 : (out_cs > 64 ? 128 : (out_cs > 32 ? 64 : 32));
     rc = tma_make_2d(&tmB, wpack, (uint64_t)n_rows_packed, (uint64_t)g.Kp, (uint64_t)g.Kp, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
     tc::TmaGemmGeom t;
     t.M = g.M; t.num_k = g.Kp / tc::BLOCK_K; t.kW = g.kW; t.dH = g.dH; t.dW = g.dW; t.sH = sH; t.sW = sW; t.lowH = lowH; t.lowW = lowW;
     t.div_Wm = g.div_Wm; t.div_HWm = g.div_HWm; t.div_Cg = g.div_Cg; t.div_kW = g.div_kW;
-    if (bn == 128) return tc::launch_gemm_tma<128, 3>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
-    if (bn == 64) return tc::launch_gemm_tma<64, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
-    return tc::launch_gemm_tma<32, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    if (!aligned_bias) {  // the persistent epilogue reads the bias with 128-bit loads
+        if (bn == 128) return tc::launch_gemm_tma<128, 3>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+        if (bn == 64) return tc::launch_gemm_tma<64, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+        return tc::launch_gemm_tma<32, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    }
+    if (bn == 128) return tc::launch_gemm_tma_persist<128, 5>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    if (bn == 64) return tc::launch_gemm_tma_persist<64, 6>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    return tc::launch_gemm_tma_persist<32, 6>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
 }
 
 int conv_tc_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
