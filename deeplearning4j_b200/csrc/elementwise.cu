@@ -219,7 +219,120 @@ __global__ void __launch_bounds__(256) k_updater(float *__restrict__ w, const fl
     }
 }
 
+// ---------------------------------------------------------------- whole-vector updater (all UpdaterBlocks in one launch)
+// The flat parameter vector is a sequence of segments (one per parameter array), each with its own updater
+// configuration. One launch walks the whole vector; a thread finds its segment by binary search over the
+// segment starts, applies updater + L1/L2 + minibatch division, and the L1/L2 score terms of the regularised
+// segments are reduced per block (double) for a second, tiny launch to fold into the score.
+struct UpdSegCfg {  // per-configuration constants (few distinct ones per network)
+    int kind;
+    float lr, h1, h2, l1, l2;
+};
+#define DL4J_MAX_UPD_CFGS 8
+struct UpdCfgTable { UpdSegCfg c[DL4J_MAX_UPD_CFGS]; };
+
+__global__ void __launch_bounds__(256) k_updater_segments(float *__restrict__ w, const float *__restrict__ g,
+                                                          float *__restrict__ state, long long n,
+                                                          const long long *__restrict__ seg_start,
+                                                          const int *__restrict__ seg_cfg, int nseg, UpdCfgTable tab,
+                                                          float inv_batch, int adadelta, double *score_partial) {
+    __shared__ double sred[256];
+    double score = 0.0;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        int lo = 0, hi = nseg - 1;  // last segment whose start <= i
+        while (lo < hi) {
+            int mid = (lo + hi + 1) >> 1;
+            if (seg_start[mid] <= i) lo = mid; else hi = mid - 1;
+        }
+        const int ci = seg_cfg[lo];
+        if (ci < 0) continue;  // NoOp segment (BatchNormalization running statistics)
+        const UpdSegCfg c = tab.c[ci];
+        const float gi = g[i], wi = w[i];
+        float u;
+        switch (c.kind) {
+        case DL4JB200_UPD_NESTEROVS: {
+            float v = state[i], vn = c.h1 * v - c.lr * gi;
+            u = c.h1 * v - (1.f + c.h1) * vn;
+            state[i] = vn;
+        } break;
+        case DL4JB200_UPD_RMSPROP: {
+            float r = c.h1 * state[i] + (1.f - c.h1) * gi * gi;
+            state[i] = r;
+            u = c.lr * gi / sqrtf(r + c.h2);
+        } break;
+        case DL4JB200_UPD_ADADELTA: {
+            // block-local msg | msdx layout: state[2*start + j] and state[2*start + len + j]
+            const long long s0 = seg_start[lo], len = seg_start[lo + 1] - s0, j = i - s0;
+            float msg = c.h1 * state[2 * s0 + j] + (1.f - c.h1) * gi * gi, msdx = state[2 * s0 + len + j];
+            u = gi * sqrtf(msdx + c.h2) / sqrtf(msg + c.h2);
+            state[2 * s0 + j] = msg;
+            state[2 * s0 + len + j] = c.h1 * msdx + (1.f - c.h1) * u * u;
+        } break;
+        case DL4JB200_UPD_NOOP: u = 0.f; break;
+        default: u = c.lr * gi;
+        }
+        if (c.l2 > 0.f) { u += c.l2 * wi; score += 0.5 * (double)c.l2 * (double)wi * (double)wi; }
+        if (c.l1 > 0.f) { u += c.l1 * (wi > 0.f ? 1.f : (wi < 0.f ? -1.f : 0.f)); score += (double)c.l1 * fabs((double)wi); }
+        w[i] = wi - u * inv_batch;
+    }
+    (void)adadelta;
+    if (score_partial) {
+        sred[threadIdx.x] = score;
+        __syncthreads();
+        for (int o = 128; o; o >>= 1) {
+            if (threadIdx.x < o) sred[threadIdx.x] += sred[threadIdx.x + o];
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) score_partial[blockIdx.x] = sred[0];
+    }
+}
+__global__ void __launch_bounds__(256) k_score_fold(const double *partial, int nblk, float *score_out) {
+    __shared__ double s[256];
+    double a = 0.0;
+    for (int i = threadIdx.x; i < nblk; i += 256) a += partial[i];
+    s[threadIdx.x] = a;
+    __syncthreads();
+    for (int o = 128; o; o >>= 1) {
+        if (threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) score_out[0] = (float)s[0];
+}
+
 extern "C" {
+
+int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n,
+                                    const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
+                                    const double *cfg_host, int ncfg, double batch_div, float *score_reg_out) {
+    DL4J_REQUIRE(ctx && w && g && seg_start_dev && seg_cfg_dev && cfg_host, "updater_apply_segments: NULL argument");
+    DL4J_REQUIRE(nseg > 0 && ncfg > 0 && ncfg <= DL4J_MAX_UPD_CFGS, "updater_apply_segments: 1..%d configurations supported", DL4J_MAX_UPD_CFGS);
+    DL4J_REQUIRE(batch_div > 0, "updater_apply_segments: batch_div must be positive");
+    UpdCfgTable tab;
+    int any_state = 0;
+    for (int i = 0; i < ncfg; i++) {
+        const double *c = cfg_host + 6 * i;
+        tab.c[i] = UpdSegCfg{(int)c[0], (float)c[1], (float)c[2], (float)c[3], (float)c[4], (float)c[5]};
+        DL4J_REQUIRE(tab.c[i].kind >= 0 && tab.c[i].kind <= DL4JB200_UPD_NOOP, "updater_apply_segments: unknown updater %d", tab.c[i].kind);
+        if (tab.c[i].kind != DL4JB200_UPD_SGD && tab.c[i].kind != DL4JB200_UPD_NOOP) any_state = 1;
+    }
+    DL4J_REQUIRE(state || !any_state, "updater_apply_segments: state is NULL");
+    if (n == 0) return DL4JB200_OK;
+    int nblk = ew_grid(ctx, n, 256);
+    double *partial = nullptr;
+    if (score_reg_out) {
+        partial = (double *)dl4j_workspace(ctx, 0, (size_t)nblk * sizeof(double));
+        if (!partial) return DL4JB200_ERR_CUDA;
+    }
+    k_updater_segments<<<nblk, 256, 0, ctx->stream>>>(w, g, state, (long long)n, (const long long *)seg_start_dev, seg_cfg_dev, nseg,
+                                                      tab, (float)(1.0 / batch_div), 0, partial);
+    DL4J_CHECK_LAUNCH();
+    if (score_reg_out) {
+        k_score_fold<<<1, 256, 0, ctx->stream>>>(partial, nblk, score_reg_out);
+        DL4J_CHECK_LAUNCH();
+    }
+    return DL4JB200_OK;
+}
 
 int dl4jb200_nchw_to_nhwc(dl4jb200_ctx *ctx, const float *src, float *dst, int B, int C, int H, int W, int cs) {
     DL4J_REQUIRE(ctx && src && dst, "nchw_to_nhwc: NULL argument");

@@ -394,7 +394,44 @@ class Network:
             return _lib.UPD_SGD, cfg["lr"], 0.0, 0.0
         raise NotImplementedError(k)
 
+    def _build_segments(self):
+        """Segment / configuration tables for dl4jb200_updater_apply_segments (one UpdaterBlock per parameter array)."""
+        m, t = self.model, self.torch
+        main, bias = self._upd_args(m["updater"]), self._upd_args(m.get("bias_updater", m["updater"]))
+        cfgs, starts, idx = [], [], []
+
+        def cfg_id(c):
+            if c not in cfgs:
+                cfgs.append(c)
+            return cfgs.index(c)
+
+        for name, key, off, shp, pk in self.layout:
+            starts.append(off)
+            if pk == "bn_stat":
+                idx.append(-1)
+                continue
+            kind, lr, h1, h2 = bias if pk == "b" else main
+            l1, l2 = (m["l1"], m["l2"]) if pk == "w" else (0.0, 0.0)
+            idx.append(cfg_id((float(kind), float(lr), float(h1), float(h2), float(l1), float(l2))))
+        starts.append(self.P)
+        self.seg_start = t.tensor(starts, dtype=t.int64, device=self.dev)
+        self.seg_cfg = t.tensor(idx, dtype=t.int32, device=self.dev)
+        self.seg_cfg_host = (C.c_double * (6 * len(cfgs)))(*[x for c in cfgs for x in c])
+        self.n_cfg = len(cfgs)
+
     def update(self):
+        """All updater blocks + the L1/L2 score terms in one launch (update_per_block is the per-array form)."""
+        m = self.model
+        if m.get("grad_norm"):
+            raise NotImplementedError("gradient normalisation " + str(m["grad_norm"]))
+        if not hasattr(self, "seg_start"):
+            self._build_segments()
+        div = float(self.B * self.batch_div_scale) if m["minibatch"] else 1.0
+        self._call("dl4jb200_updater_apply_segments", self._ptr(self.params), self._ptr(self.grads), self._ptr(self.state), self.P,
+                   self._ptr(self.seg_start), self._ptr(self.seg_cfg), len(self.layout), self.seg_cfg_host, self.n_cfg, div,
+                   self._ptr(self.score_reg) if self.with_score else None)
+
+    def update_per_block(self):
         m = self.model
         if m.get("grad_norm"):
             raise NotImplementedError("gradient normalisation " + str(m["grad_norm"]))
@@ -432,11 +469,9 @@ class Network:
             self.set_batch(features, labels)
         self.forward(True)
         self.backward()
-        if self.with_score:
-            self.score_terms()
         if hook is not None:
             hook(self)  # data-parallel gradient exchange (parallel.py)
-        self.update()
+        self.update()  # also leaves the L1/L2 part of the score (pre-update weights) in score_reg
         with self.torch.cuda.stream(self.stream):
             return (self.loss + self.score_reg) / float(self.B)
 

@@ -242,6 +242,18 @@ int dl4jb200_copy2d(dl4jb200_ctx *ctx, const float *src, int src_ld, float *dst,
 int dl4jb200_updater_apply(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n, int kind, double lr,
                            double h1, double h2, double l1, double l2, double batch_div);
 
+/* All updater blocks of a network in ONE launch (BaseMultiLayerUpdater.update walks its UpdaterBlocks,
+ * NN/nn/updater/BaseMultiLayerUpdater.java:223-309): the flat vectors w / g / state of n floats are split into nseg
+ * segments; seg_start_dev[0..nseg] (device, int64, seg_start[nseg] == n) gives their bounds and seg_cfg_dev[s]
+ * (device, int32) the index of the segment's configuration in cfg_host, or -1 for a NoOp segment (BatchNormalization
+ * running statistics). cfg_host: ncfg x 6 doubles {kind, lr, h1, h2, l1, l2} (host). Same arithmetic as
+ * dl4jb200_updater_apply per element (AdaDelta state is block-local: 2*start .. 2*start+2*len). If score_reg_out is
+ * not NULL it receives sum over segments of l1*|w|_1 + 0.5*l2*|w|_2^2 evaluated on the PRE-update weights (the
+ * regularisation part of the score, BaseOutputLayer.java:82-100), replacing the per-layer dl4jb200_l1l2_score calls. */
+int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n,
+                                    const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
+                                    const double *cfg_host, int ncfg, double batch_div, float *score_reg_out);
+
 #ifdef __cplusplus
 }
 #endif
