@@ -173,8 +173,8 @@ def main():
     barrier()
 
     # ---- timed region 1: device-resident minibatch. Per-call CUDA events on the launching stream for the roofline.
-    net.profile(["dl4jb200_conv_fwd", "dl4jb200_conv_bwd", "dl4jb200_bn_fwd", "dl4jb200_bn_bwd", "dl4jb200_pool_fwd",
-                 "dl4jb200_pool_bwd"])
+    net.profile(["dl4jb200_conv_fwd", "dl4jb200_conv_bwd", "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_wgrad",
+                 "dl4jb200_bn_fwd", "dl4jb200_bn_bwd", "dl4jb200_pool_fwd", "dl4jb200_pool_bwd"])
     sampler = ClockSampler(local)
     sampler.start()
     l0 = _lib.cdll().dl4jb200_launch_count()
@@ -223,7 +223,7 @@ def main():
     n_conv_calls = 0
     per_layer = {}
     for (fn, tag), times in prof.items():
-        if fn in ("dl4jb200_conv_fwd", "dl4jb200_conv_bwd") and tag in fl:
+        if fn in ("dl4jb200_conv_fwd", "dl4jb200_conv_bwd", "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_wgrad") and tag in fl:
             f = fl[tag][0 if fn.endswith("fwd") else 1]
             conv_ms += sum(times)
             conv_fl += f * len(times)
@@ -231,7 +231,7 @@ def main():
             per_layer[f"{tag}:{fn[9:]}"] = {"ms": sum(times) / len(times), "tflops": f / (sum(times) / len(times) * 1e-3) / 1e12}
     tf32_peak = pk["bf16_tflops_sustained"] / 2.0
     ach = conv_fl / (conv_ms * 1e-3) / 1e12 if conv_ms else 0.0
-    roofline = {"bound": "tensor", "kernel": "k_conv_tc_gemm/k_conv_tc_wgrad (all conv_fwd + conv_bwd calls of the step)",
+    roofline = {"bound": "tensor", "kernel": "k_conv_tc_gemm_tma_persist / k_conv_tc_wgrad_tma (all convolution + dense calls of the step)",
                 "achieved": ach, "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak, "traffic": None,
                 "peak_note": f"TF32 dense = 0.5 x bf16_tflops_sustained ({pk['src']}); kernel timed inside a long step",
                 "share_of_step": conv_ms / ms, "calls": n_conv_calls}

@@ -148,6 +148,21 @@ static int check_layout(int layout, int cs, int C, const void *p, const char *wh
 
 extern "C" {
 
+int dl4jb200_bias_grad(dl4jb200_ctx *ctx, const float *delta, int M, int cs, int C, float *db) {
+    DL4J_REQUIRE(ctx && delta && db, "bias_grad: NULL argument");
+    DL4J_REQUIRE(M > 0 && C > 0 && cs >= C && cs % 4 == 0 && ((uintptr_t)delta & 15) == 0, "bias_grad: bad shape / alignment");
+    int nblk = M / 8;
+    if (nblk > ctx->sm_count * 4) nblk = ctx->sm_count * 4;
+    if (nblk < 1) nblk = 1;
+    float *colp = (float *)dl4j_workspace(ctx, 0, (size_t)nblk * cs * sizeof(float));
+    if (!colp) return DL4JB200_ERR_CUDA;
+    k_colsum_partial<<<nblk, 256, 0, ctx->stream>>>(delta, colp, M, cs);
+    DL4J_CHECK_LAUNCH();
+    k_colsum_final<<<dl4j_ceil_div(C, 32), dim3(32, 32), 0, ctx->stream>>>(colp, db, nblk, cs, C);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
 int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs,
                       const float *w, const float *bias, float *z, int z_layout, int z_cs, int act, int algo) {
     DL4J_REQUIRE(ctx && x && w && z, "conv_fwd: NULL argument");

@@ -1,0 +1,146 @@
+// Few-channel, stride-2 "stem" convolution (ResNet-50's 7x7 s2 on 3 channels; AlexNet/VGG-style first layers with
+// stride_w == 2) on the TMA + tcgen05 path.
+//
+// With C_in <= 4 a K-chunk of 32 values spans 8 filter taps, which im2col-mode TMA (one tap per instruction, >= 32
+// channels) cannot deliver. But in NHWC4 memory the taps of one filter ROW are contiguous: for output column ow and
+// filter row kh, pixels 2ow-pL .. 2ow-pL+kW-1 of input row (oh*sH-pT+kh) are <= 8 pixels x 4 floats = one 128-byte
+// run. So the input is described to TMA as a tensor whose "pixel" pitch is 8 floats (two real pixels) and whose
+// "channel" extent is 32 floats -- consecutive pixels OVERLAP -- and the convolution becomes kH taps of 32 channels
+// with unit stride along W: exactly what the generic TMA kernels consume. The caller stores the image row-packed:
+// [B][H][row_pitch_px][4] with the image starting at pixel pL+1 (so every window start is pixel-pair aligned with one
+// leading dummy tap) and zeros in the padding columns; padding in H is resolved by the TMA unit.
+#include "conv_common.cuh"
+#include "conv_tma.cuh"
+
+int conv_tc_wgrad_splits(dl4jb200_ctx *ctx, const ConvGeom &g, int c_out);
+
+// W[co][ci][kh][kw] -> Wp[n][kh*32 + kp*8 + j*4 + ci],  kw = 2*kp + j - 1  (kw == -1 / >= kW / ci >= Cin: zero)
+__global__ void __launch_bounds__(256) k_pack_stem_filter(const float *__restrict__ w, float *__restrict__ wp, int Cout, int Cin,
+                                                          int kH, int kW, int Kp, int rows_p) {
+    size_t total = (size_t)rows_p * Kp, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        int n = (int)(i / Kp), k = (int)(i % Kp);
+        int kh = k >> 5, r = k & 31, kp = r >> 3, j = (r >> 2) & 1, ci = r & 3, kw = 2 * kp + j - 1;
+        float v = 0.f;
+        if (n < Cout && kh < kH && kw >= 0 && kw < kW && ci < Cin) v = w[(((size_t)n * Cin + ci) * kH + kh) * kW + kw];
+        wp[i] = to_tf32_rna(v);
+    }
+}
+
+// dW[co][ci][kh][kw] = sum_s partial[s][co][kh*32 + ((kw+1)>>1)*8 + ((kw+1)&1)*4 + ci]
+__global__ void __launch_bounds__(256) k_stem_wgrad_finalize(const float *__restrict__ partial, float *__restrict__ dw, int Cout,
+                                                             int Cin, int kH, int kW, int Kp, int rows_p, int splits) {
+    size_t total = (size_t)Cout * Cin * kH * kW, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        int kw = (int)(i % kW);
+        size_t t = i / kW;
+        int kh = (int)(t % kH); t /= kH;
+        int ci = (int)(t % Cin), co = (int)(t / Cin);
+        int k = kh * 32 + ((kw + 1) >> 1) * 8 + ((kw + 1) & 1) * 4 + ci;
+        const float *p = partial + (size_t)co * Kp + k;
+        float acc = 0.f;
+        for (int s = 0; s < splits; s++) acc += p[(size_t)s * rows_p * Kp];
+        dw[i] = acc;
+    }
+}
+
+// NCHW image -> row-packed NHWC4: dst[b][y][x_off + x][c], c < C <= 4 (padding columns / channel 3 untouched: keep them zero)
+__global__ void __launch_bounds__(256) k_nchw_to_rowpack4(const float *__restrict__ src, float *__restrict__ dst, int B, int C, int H,
+                                                          int W, int row_pitch_px, int x_off) {
+    size_t total = (size_t)B * H * W, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        int x = (int)(i % W);
+        size_t t = i / W;
+        int y = (int)(t % H), b = (int)(t / H);
+        float v[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int c = 0; c < C; c++) v[c] = src[(((size_t)b * C + c) * H + y) * W + x];
+        *reinterpret_cast<float4 *>(dst + (((size_t)b * H + y) * row_pitch_px + x_off + x) * 4) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+}
+
+static int stem_check(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int row_pitch_px, const char *who) {
+    DL4J_REQUIRE(ctx && d, "%s: NULL argument", who);
+    if (d->c_in > 4 || d->stride_w != 2 || d->k_w > 7 || d->k_h > 16 || d->dil_h != 1 || d->dil_w != 1 || !tma_driver_ready() ||
+        d->pad_top > 127 || d->stride_h > 8) {
+        dl4j_set_error("%s: row-packed path needs c_in <= 4, stride_w == 2, k_w <= 7, no dilation", who);
+        return DL4JB200_NOT_SUPPORTED;
+    }
+    DL4J_REQUIRE(row_pitch_px % 2 == 0 && row_pitch_px >= 2 * d->out_w + 6 && row_pitch_px >= d->pad_left + 1 + d->in_w,
+                 "%s: row_pitch_px must be even and >= max(2*out_w + 6, pad_left + 1 + in_w)", who);
+    return DL4JB200_OK;
+}
+
+static int stem_xmap(CUtensorMap *tm, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px, uint32_t pixels,
+                     CUtensorMapSwizzle swz) {
+    // tensor {C = 32 floats, W = out_w window starts (pitch 8 floats), H = in_h rows, N}; taps only along H
+    return tma_make_im2col_pitched(tm, xp, d->batch, d->in_h, d->out_w, 32, 8, (long long)row_pitch_px * 4,
+                                   (long long)d->in_h * row_pitch_px * 4, 0, -d->pad_top, d->out_w, d->out_h, 1, d->stride_h, pixels, swz);
+}
+
+extern "C" {
+
+int dl4jb200_nchw_to_rowpack4(dl4jb200_ctx *ctx, const float *src, float *dst, int B, int C, int H, int W, int row_pitch_px,
+                              int x_off) {
+    DL4J_REQUIRE(ctx && src && dst, "nchw_to_rowpack4: NULL argument");
+    DL4J_REQUIRE(C >= 1 && C <= 4 && B > 0 && H > 0 && W > 0 && x_off >= 0 && x_off + W <= row_pitch_px, "nchw_to_rowpack4: bad shape");
+    size_t total = (size_t)B * H * W;
+    size_t blocks = (total + 255) / 256, cap = (size_t)ctx->sm_count * 16;
+    k_nchw_to_rowpack4<<<(int)(blocks > cap ? cap : blocks), 256, 0, ctx->stream>>>(src, dst, B, C, H, W, row_pitch_px, x_off);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_conv_rowpack_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px, const float *w,
+                              const float *bias, float *z, int z_cs, int act) {
+    int rc = stem_check(ctx, d, row_pitch_px, "conv_rowpack_fwd");
+    if (rc) return rc;
+    DL4J_REQUIRE(xp && w && z && z_cs >= d->c_out && z_cs % 4 == 0 && ((uintptr_t)z & 15) == 0 && ((uintptr_t)xp & 15) == 0,
+                 "conv_rowpack_fwd: bad output / input buffer");
+    if (act < 0 || act > DL4JB200_ACT_LEAKYRELU) { dl4j_set_error("conv_rowpack_fwd: activation %d not handled", act); return DL4JB200_NOT_SUPPORTED; }
+    if (bias && ((uintptr_t)bias & 15)) { dl4j_set_error("conv_rowpack_fwd: bias must be 16-byte aligned"); return DL4JB200_NOT_SUPPORTED; }
+    const int Kp = d->k_h * 32, rows_p = dl4j_round_up(z_cs, 256);
+    float *wp = (float *)dl4j_workspace(ctx, 0, (size_t)rows_p * Kp * sizeof(float));
+    if (!wp) return DL4JB200_ERR_CUDA;
+    k_pack_stem_filter<<<dl4j_ceil_div((long long)rows_p * Kp, 256), 256, 0, ctx->stream>>>(w, wp, d->c_out, d->c_in, d->k_h, d->k_w, Kp, rows_p);
+    DL4J_CHECK_LAUNCH();
+    alignas(64) CUtensorMap tmA, tmB;
+    if ((rc = stem_xmap(&tmA, d, xp, row_pitch_px, 128, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    const int bn = z_cs > 64 ? 128 : (z_cs > 32 ? 64 : 32);
+    if ((rc = tma_make_2d(&tmB, wp, (uint64_t)rows_p, (uint64_t)Kp, (uint64_t)Kp, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+    tcgeom::TmaGemmGeom t;
+    t.M = d->batch * d->out_h * d->out_w; t.num_k = d->k_h; t.kW = 1; t.dH = 1; t.dW = 1; t.sH = d->stride_h; t.sW = 1;
+    t.lowH = -d->pad_top; t.lowW = 0;
+    t.div_Wm = FastDiv((uint32_t)d->out_w); t.div_HWm = FastDiv((uint32_t)(d->out_h * d->out_w));
+    t.div_Cg = FastDiv(32u); t.div_kW = FastDiv(1u);
+    return conv_tc_gemm_tma_raw(ctx, tmA, tmB, t, bias, z, d->c_out, z_cs, act, bn);
+}
+
+int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px,
+                                const float *delta, int delta_cs, float *dw) {
+    int rc = stem_check(ctx, d, row_pitch_px, "conv_rowpack_wgrad");
+    if (rc) return rc;
+    DL4J_REQUIRE(xp && delta && dw && delta_cs >= d->c_out && delta_cs % 4 == 0 && ((uintptr_t)delta & 15) == 0 && ((uintptr_t)xp & 15) == 0,
+                 "conv_rowpack_wgrad: bad buffer");
+    const int Kp = d->k_h * 32, rows_w = dl4j_round_up(d->c_out, 128), M = d->batch * d->out_h * d->out_w;
+    ConvGeom g;  // only the fields the split heuristic reads
+    g.Kp = Kp; g.M = M;
+    const int splits = conv_tc_wgrad_splits(ctx, g, d->c_out);
+    const int mps = dl4j_round_up(dl4j_ceil_div(M, splits), 32);
+    float *partial = (float *)dl4j_workspace(ctx, 0, (size_t)splits * rows_w * Kp * sizeof(float));
+    if (!partial) return DL4JB200_ERR_CUDA;
+    alignas(64) CUtensorMap tmD, tmX;
+    if ((rc = tma_make_2d(&tmD, delta, (uint64_t)M, (uint64_t)delta_cs, (uint64_t)delta_cs, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))) return rc;
+    if ((rc = stem_xmap(&tmX, d, xp, row_pitch_px, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))) return rc;
+    tcgeom::TmaWgradGeom t;
+    t.M = M; t.kW = 1; t.dH = 1; t.dW = 1; t.sH = d->stride_h; t.sW = 1; t.lowH = -d->pad_top; t.lowW = 0; t.Kp = Kp;
+    t.div_Wm = FastDiv((uint32_t)d->out_w); t.div_HWm = FastDiv((uint32_t)(d->out_h * d->out_w));
+    t.div_Cg = FastDiv(32u); t.div_kW = FastDiv(1u);
+    if ((rc = conv_tc_wgrad_tma_raw(ctx, tmD, tmX, t, partial, rows_w, splits, mps))) return rc;
+    size_t total = (size_t)d->c_out * d->c_in * d->k_h * d->k_w;
+    k_stem_wgrad_finalize<<<dl4j_ceil_div((long long)total, 256), 256, 0, ctx->stream>>>(partial, dw, d->c_out, d->c_in, d->k_h, d->k_w,
+                                                                                    Kp, rows_w, splits);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+}  // extern "C"

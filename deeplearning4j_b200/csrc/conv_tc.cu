@@ -15,6 +15,9 @@
 #include "conv_common.cuh"
 #include "conv_tma.cuh"
 
+using tcgeom::TmaGemmGeom;
+using tcgeom::TmaWgradGeom;
+
 namespace tc {
 
 constexpr int BLOCK_M = 128;
@@ -442,10 +445,6 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
 // one elected thread issues, per K-chunk, ONE im2col-mode TMA for the 128-pixel x 32-channel A tile and ONE tiled
 // TMA for the BN x 32 filter tile; both signal the stage's mbarrier with their byte count. No per-element address
 // arithmetic is left on the SM; padding, stride and image borders are resolved by the TMA unit (zero fill).
-struct TmaGemmGeom {
-    int M, num_k, kW, dH, dW, sH, sW, lowH, lowW;
-    FastDiv div_Wm, div_HWm, div_Cg, div_kW;
-};
 
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_constant__ CUtensorMap tmA,
@@ -759,10 +758,6 @@ static int launch_gemm_tma(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUte
 // each) and BN/32 im2col-mode loads bring the 32-pixel x 32-channel slabs of the taps this CTA's k-columns cover.
 // TMA lays a 32-row x 128-byte box out as 8 consecutive 4-row / 512-byte groups with SWIZZLE_128B_ATOM_32B, which is
 // exactly the MN-major UMMA atom: LBO (next 32-float MN atom) = 4096 B, SBO (next 4-row group) = 512 B.
-struct TmaWgradGeom {
-    int M, kW, dH, dW, sH, sW, lowH, lowW, Kp;
-    FastDiv div_Wm, div_HWm, div_Cg, div_kW;
-};
 
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad_tma(const __grid_constant__ CUtensorMap tmD,
@@ -970,7 +965,7 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
     const int bn = wide ? 256 : (out_cs > 64 ? 128 : (out_cs > 32 ? 64 : 32));
     rc = tma_make_2d(&tmB, wpack, (uint64_t)n_rows_packed, (uint64_t)g.Kp, (uint64_t)g.Kp, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
-    tc::TmaGemmGeom t;
+    TmaGemmGeom t;
     t.M = g.M; t.num_k = g.Kp / tc::BLOCK_K; t.kW = g.kW; t.dH = g.dH; t.dW = g.dW; t.sH = sH; t.sW = sW; t.lowH = lowH; t.lowW = lowW;
     t.div_Wm = g.div_Wm; t.div_HWm = g.div_HWm; t.div_Cg = g.div_Cg; t.div_kW = g.div_kW;
     if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
@@ -1019,7 +1014,7 @@ int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const fl
         rc = tma_make_im2col(&tmX, x, g.B, g.Hs, g.Ws, g.Cg, g.cs_src, -g.pL, -g.pT, g.Wm, g.Hm, g.sW, g.sH, tc::BLOCK_K,
                              CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
         if (rc) return rc;
-        tc::TmaWgradGeom t;
+        TmaWgradGeom t;
         t.M = g.M; t.kW = g.kW; t.dH = g.dH; t.dW = g.dW; t.sH = g.sH; t.sW = g.sW; t.lowH = -g.pT; t.lowW = -g.pL; t.Kp = g.Kp;
         t.div_Wm = g.div_Wm; t.div_HWm = g.div_HWm; t.div_Cg = g.div_Cg; t.div_kW = g.div_kW;
         switch (tc::wgrad_bn(g)) {
@@ -1032,5 +1027,28 @@ int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const fl
     case 128: return tc::launch_wgrad<128, 3>(ctx, g, x, delta, delta_cs, partial, rows_p, splits, mps);
     case 64: return tc::launch_wgrad<64, 4>(ctx, g, x, delta, delta_cs, partial, rows_p, splits, mps);
     default: return tc::launch_wgrad<32, 4>(ctx, g, x, delta, delta_cs, partial, rows_p, splits, mps);
+    }
+}
+
+// ---- raw launchers for callers that build their own tensor maps (conv_stem.cu)
+int conv_tc_gemm_tma_raw(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const TmaGemmGeom &t, const float *bias,
+                         float *out, int n_valid, int out_cs, int act, int bn) {
+    if (bias && ((uintptr_t)bias & 15)) {
+        dl4j_set_error("conv_tc_gemm_tma_raw: bias must be 16-byte aligned");
+        return DL4JB200_NOT_SUPPORTED;
+    }
+    if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    if (bn == 128) return tc::launch_gemm_tma_persist<128, 5>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    if (bn == 64) return tc::launch_gemm_tma_persist<64, 6>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    return tc::launch_gemm_tma_persist<32, 6>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+}
+
+int conv_tc_wgrad_tma_raw(dl4jb200_ctx *ctx, const CUtensorMap &tmD, const CUtensorMap &tmX, const TmaWgradGeom &t, float *partial,
+                          int rows_p, int splits, int m_per_split) {
+    const int bn = t.Kp >= 128 ? 128 : (t.Kp >= 64 ? 64 : 32);
+    switch (bn) {
+    case 128: return tc::launch_wgrad_tma<128, 3>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split);
+    case 64: return tc::launch_wgrad_tma<64, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split);
+    default: return tc::launch_wgrad_tma<32, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split);
     }
 }

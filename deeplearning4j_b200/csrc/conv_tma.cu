@@ -43,9 +43,17 @@ int tma_make_2d(CUtensorMap *out, const float *base, uint64_t rows, uint64_t col
 
 int tma_make_im2col(CUtensorMap *out, const float *base, int N, int H, int W, int C, int cs, int lower_w, int lower_h,
                     int out_w, int out_h, int stride_w, int stride_h, uint32_t pixels, CUtensorMapSwizzle swizzle) {
+    return tma_make_im2col_pitched(out, base, N, H, W, C, cs, (long long)W * cs, (long long)H * W * cs, lower_w, lower_h, out_w,
+                                   out_h, stride_w, stride_h, pixels, swizzle);
+}
+
+int tma_make_im2col_pitched(CUtensorMap *out, const float *base, int N, int H, int W, int C, long long pix_pitch,
+                            long long row_pitch, long long img_pitch, int lower_w, int lower_h, int out_w, int out_h,
+                            int stride_w, int stride_h, uint32_t pixels, CUtensorMapSwizzle swizzle) {
     DL4J_REQUIRE(tma_driver_ready(), "TMA: driver does not expose cuTensorMapEncodeIm2col");
+    const int cs = (int)pix_pitch;
     cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-    cuuint64_t strides[3] = {(cuuint64_t)cs * 4, (cuuint64_t)W * cs * 4, (cuuint64_t)H * W * cs * 4};
+    cuuint64_t strides[3] = {(cuuint64_t)pix_pitch * 4, (cuuint64_t)row_pitch * 4, (cuuint64_t)img_pitch * 4};
     // number of base pixels along an axis = (dim + upper - lower - 1) / stride + 1  ==> upper chosen for `out` pixels
     int lower[2] = {lower_w, lower_h};
     int upper[2] = {lower_w + (out_w - 1) * stride_w + 1 - W, lower_h + (out_h - 1) * stride_h + 1 - H};

@@ -29,6 +29,27 @@ int tma_make_2d(CUtensorMap *out, const float *base, uint64_t rows, uint64_t col
 int tma_make_im2col(CUtensorMap *out, const float *base, int N, int H, int W, int C, int cs, int lower_w, int lower_h,
                     int out_w, int out_h, int stride_w, int stride_h, uint32_t pixels, CUtensorMapSwizzle swizzle);
 
+// same, with explicit pixel / row / image pitches (floats): lets a caller describe a tensor whose "pixels" overlap
+// (pixel pitch < channel extent), which is how the 3-channel stem convolution is fed (conv_stem.cu)
+int tma_make_im2col_pitched(CUtensorMap *out, const float *base, int N, int H, int W, int C, long long pix_pitch,
+                            long long row_pitch, long long img_pitch, int lower_w, int lower_h, int out_w, int out_h,
+                            int stride_w, int stride_h, uint32_t pixels, CUtensorMapSwizzle swizzle);
+
+namespace tcgeom {
+struct TmaGemmGeom {
+    int M, num_k, kW, dH, dW, sH, sW, lowH, lowW;
+    FastDiv div_Wm, div_HWm, div_Cg, div_kW;
+};
+struct TmaWgradGeom {
+    int M, kW, dH, dW, sH, sW, lowH, lowW, Kp;
+    FastDiv div_Wm, div_HWm, div_Cg, div_kW;
+};
+}  // namespace tcgeom
+int conv_tc_gemm_tma_raw(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const tcgeom::TmaGemmGeom &t,
+                         const float *bias, float *out, int n_valid, int out_cs, int act, int bn);
+int conv_tc_wgrad_tma_raw(dl4jb200_ctx *ctx, const CUtensorMap &tmD, const CUtensorMap &tmX, const tcgeom::TmaWgradGeom &t,
+                          float *partial, int rows_p, int splits, int m_per_split);
+
 #ifdef __CUDACC__
 namespace tma {
 __device__ __forceinline__ void prefetch_desc(const CUtensorMap *m) {

@@ -114,10 +114,33 @@ class Network:
                 self.aux[n] = (self._buf(s[0]), self._buf(s[0]))  # saved mean / std
             if op == "output":
                 self.aux[n] = self._buf(B, cs)  # delta = p - labels
+        self._plan_stem()
         self.loss = self._buf(1)
         self.score_reg = self._buf(1)
         self.tmp_eps = {}
         self.labels = None
+
+    def _plan_stem(self):
+        """First-layer convolution on <= 4 channels with stride_w 2 (ResNet-50's 7x7/2): keep the minibatch row-packed
+        so the TMA-fed kernels can run it (dl4jb200_conv_rowpack_*)."""
+        self.stem = None
+        if self.algo != _lib.ALGO_TC_TF32:
+            return
+        inp = self.model["vertices"][0]["name"]
+        users = [c for c in self.consumers[inp]]
+        if len(users) == 1 and self.vmap[users[0]]["op"] == "zeropad":
+            users = self.consumers[users[0]]
+        if len(users) != 1 or self.vmap[users[0]]["op"] != "conv":
+            return
+        v = self.vmap[users[0]]
+        src, d = self._conv_desc(v)
+        if src != inp or d.c_in > 4 or d.stride_w != 2 or d.k_w > 7 or d.k_h > 16 or d.dil_h != 1 or d.dil_w != 1 \
+                or v["act"] not in ("identity", "relu"):
+            return
+        pitch = max(2 * d.out_w + 6, d.pad_left + 1 + d.in_w)
+        pitch += pitch % 2
+        self.stem = (v["name"], pitch, d.pad_left + 1)
+        self.out[inp] = self._buf(self.B, d.in_h, pitch, 4)  # padding columns stay zero
 
     def _ptr(self, t, off=0):
         return C.c_void_p(t.data_ptr() + 4 * off)
@@ -188,7 +211,11 @@ class Network:
             lab = t.as_tensor(labels) if not isinstance(labels, t.Tensor) else labels
             self.labels = lab.to(self.dev, non_blocking=True).contiguous()
             self._feat = f.contiguous()
-        self._call("dl4jb200_nchw_to_nhwc", self._ptr(self._feat), self._ptr(self.out[inp]), self.B, Cc, Hh, W, self.cs[inp])
+        if self.stem:
+            self._call("dl4jb200_nchw_to_rowpack4", self._ptr(self._feat), self._ptr(self.out[inp]), self.B, Cc, Hh, W,
+                       self.stem[1], self.stem[2])
+        else:
+            self._call("dl4jb200_nchw_to_nhwc", self._ptr(self._feat), self._ptr(self.out[inp]), self.B, Cc, Hh, W, self.cs[inp])
 
     # ------------------------------------------------------------------ forward (feedForward, train mode)
     def forward(self, train=True):
@@ -203,8 +230,12 @@ class Network:
                 x, xcs = self._src(src)
                 pw, _, _, _ = self._p(n, "W")
                 pb, _, _, _ = self._p(n, "b")
-                self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
-                           self.cs[n], _ACT[v["act"]], self.algo)
+                if self.stem and self.stem[0] == n:
+                    self._call("dl4jb200_conv_rowpack_fwd", C.byref(d), self._ptr(x), self.stem[1], pw, pb, self._ptr(self.out[n]),
+                               self.cs[n], _ACT[v["act"]])
+                else:
+                    self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
+                               self.cs[n], _ACT[v["act"]], self.algo)
             elif op == "bn" or n in self.fused_add:
                 if op == "bn":
                     bnv, res, act = v, None, _ACT[v["act"]]
@@ -344,7 +375,10 @@ class Network:
                 def run(dx, d=d, x=x, xcs=xcs, pw=pw, gw=gw, gb=gb, e=e, n=n):
                     self._call("dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
                                gw, gb, dx, L.NHWC, xcs, self.algo)
-                if self._needs_eps(src):
+                if self.stem and self.stem[0] == n:
+                    self._call("dl4jb200_conv_rowpack_wgrad", C.byref(d), self._ptr(x), self.stem[1], self._ptr(e), self.cs[n], gw)
+                    self._call("dl4jb200_bias_grad", self._ptr(e), B * d.out_h * d.out_w, self.cs[n], d.c_out, gb)
+                elif self._needs_eps(src):
                     self._emit(src, run)
                 else:
                     run(None)

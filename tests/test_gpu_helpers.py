@@ -400,3 +400,39 @@ def test_relayout_roundtrip(H, ctx):
             np.testing.assert_array_equal(dev.get(pb, shape), x)
     finally:
         dev.free()
+
+
+@pytest.mark.parametrize("case", [(4, 3, 32, 32, 64, 7, 2, 3), (2, 3, 30, 26, 16, 7, 2, 3), (3, 1, 28, 28, 20, 5, 2, 2), (2, 4, 17, 19, 40, 3, 2, 1)])
+def test_rowpacked_stem_conv_vs_oracle(H, ctx, oracle, case):
+    """dl4jb200_conv_rowpack_fwd / _wgrad (TMA-fed stem path) against the oracle's ordinary convolution."""
+    from deeplearning4j_b200 import _lib
+    B, Cin, Hh, W, Cout, k, s, p = case
+    rng = np.random.default_rng(77)
+    x = rng.random((B, Cin, Hh, W), dtype=np.float32)
+    w = (rng.standard_normal((Cout, Cin, k, k)) * 0.3).astype(np.float32)
+    b = rng.standard_normal(Cout).astype(np.float32)
+    d = H.conv_desc(x.shape, Cout, (k, k), (s, s), (p, p), (1, 1), "Truncate")
+    zr = oracle.conv_fwd(x, w, b, stride=(s, s), pad=(p, p))
+    delta = rng.standard_normal(zr.shape).astype(np.float32)
+    dwr, dbr, _ = oracle.conv_bwd(x, w, delta, stride=(s, s), pad=(p, p), need_dx=False)
+    pitch = max(2 * d.out_w + 6, p + 1 + W)
+    pitch += pitch % 2
+    zcs = (Cout + 3) // 4 * 4
+    dev = Dev(ctx)
+    try:
+        px = dev.put(x)
+        pxp = dev.empty(B * Hh * pitch * 4 * 4, fill=0)
+        _lib.call("dl4jb200_nchw_to_rowpack4", ctx.handle, px, pxp, B, Cin, Hh, W, pitch, p + 1)
+        pw, pb = dev.put(w), dev.put(b)
+        pz = dev.empty(B * d.out_h * d.out_w * zcs * 4)
+        _lib.call("dl4jb200_conv_rowpack_fwd", ctx.handle, C.byref(d), pxp, pitch, pw, pb, pz, zcs, H.ACT_IDENTITY)
+        z = from_nhwc(dev.get(pz, (B, d.out_h, d.out_w, zcs)), Cout)
+        assert rel_err(z, zr) <= TOL_CONV_TF32, rel_err(z, zr)
+        pd = dev.put(to_nhwc(delta, zcs))
+        pdw, pdb = dev.empty(w.nbytes), dev.empty(Cout * 4)
+        _lib.call("dl4jb200_conv_rowpack_wgrad", ctx.handle, C.byref(d), pxp, pitch, pd, zcs, pdw)
+        _lib.call("dl4jb200_bias_grad", ctx.handle, pd, B * d.out_h * d.out_w, zcs, Cout, pdb)
+        assert rel_err(dev.get(pdw, w.shape), dwr) <= TOL_CONV_TF32
+        assert rel_err(dev.get(pdb, (Cout,)), dbr) <= 1e-5
+    finally:
+        dev.free()
