@@ -192,6 +192,37 @@ __global__ void __launch_bounds__(256) k_pool_bwd(const float *__restrict__ x, c
     }
 }
 
+// Hot case of the backward pass (MAX, saved argmax, NHWC, no dilation): walk only the <= ceil(k/s)^2 windows that can
+// contain the cell instead of testing all k*k taps for stride divisibility. Same summation order (kh, kw ascending).
+__global__ void __launch_bounds__(256, 4) k_maxpool_bwd_nhwc_fast(const float *__restrict__ eps, const int32_t *__restrict__ argmax,
+                                                                 float *__restrict__ dx, PoolGeom g, size_t total) {
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+        int b, c, h, w;
+        decode<true>(idx, g, b, c, h, w);
+        const int th = h + g.pT, tw = w + g.pL;
+        // SAME mode with stride > kernel yields NEGATIVE padding (ConvolutionUtils.java:243-253): th / tw may be < 0
+        const int oh_hi = th < 0 ? -1 : min((int)g.d_sH.div((uint32_t)th), g.Ho - 1);
+        const int ow_hi = tw < 0 ? -1 : min((int)g.d_sW.div((uint32_t)tw), g.Wo - 1);
+        const int lh = th - g.kH + 1, lw = tw - g.kW + 1;
+        const int oh_lo = lh <= 0 ? 0 : (int)g.d_sH.div((uint32_t)(lh + g.sH - 1));
+        const int ow_lo = lw <= 0 ? 0 : (int)g.d_sW.div((uint32_t)(lw + g.sW - 1));
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int oh = oh_hi; oh >= oh_lo; oh--) {       // kh = th - oh*sH ascending
+            const int kh = th - oh * g.sH;
+            for (int ow = ow_hi; ow >= ow_lo; ow--) {   // kw ascending
+                const int me = kh * g.kW + (tw - ow * g.sW);
+                const size_t o = (((size_t)b * g.Ho + oh) * g.Wo + ow) * g.ycs + c;
+                const int4 a = *reinterpret_cast<const int4 *>(argmax + o);
+                const float4 e = *reinterpret_cast<const float4 *>(eps + o);
+                acc.x += a.x == me ? e.x : 0.f; acc.y += a.y == me ? e.y : 0.f;
+                acc.z += a.z == me ? e.z : 0.f; acc.w += a.w == me ? e.w : 0.f;
+            }
+        }
+        *reinterpret_cast<float4 *>(dx + (((size_t)b * g.H + h) * g.W + w) * g.xcs + c) = acc;
+    }
+}
+
 static int pool_geom(const dl4jb200_conv_desc *d, int layout, int x_cs, int y_cs, PoolGeom &g, const char *who) {
     DL4J_REQUIRE(d, "%s: desc is NULL", who);
     DL4J_REQUIRE(d->batch > 0 && d->c_in > 0 && d->in_h > 0 && d->in_w > 0 && d->out_h > 0 && d->out_w > 0 &&
@@ -254,7 +285,10 @@ int dl4jb200_pool_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     DL4J_REQUIRE(pool_type != DL4JB200_POOL_PNORM || (x && y && pnorm >= 1), "pool_bwd: PNORM needs x, y and pnorm >= 1");
     g.d_q = FastDiv((uint32_t)(layout == DL4JB200_NHWC ? g.xcs / 4 : 1));
     g.d_w = FastDiv((uint32_t)g.W); g.d_h = FastDiv((uint32_t)g.H); g.d_c = FastDiv((uint32_t)g.C);
-    if (layout == DL4JB200_NHWC) {
+    if (layout == DL4JB200_NHWC && pool_type == DL4JB200_POOL_MAX && argmax && g.dH == 1 && g.dW == 1) {
+        size_t total = (size_t)g.B * g.H * g.W * (g.xcs / 4);
+        k_maxpool_bwd_nhwc_fast<<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(eps, argmax, dx, g, total);
+    } else if (layout == DL4JB200_NHWC) {
         size_t total = (size_t)g.B * g.H * g.W * (g.xcs / 4);
         k_pool_bwd<true><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, eps, argmax, dx, g, pool_type, pnorm,
                                                                          (float)pnorm_eps, total);
