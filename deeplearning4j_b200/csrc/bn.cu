@@ -170,11 +170,21 @@ __device__ __forceinline__ void bn_fold_partials(const float *__restrict__ parti
                                                  double &s1, double &s2) {
     __shared__ double sh1[32][33], sh2[32][33];
     double a = 0.0, b = 0.0;
-    if (active)
-        for (int i = threadIdx.y; i < nblk; i += 32) {
+    if (active) {
+        int i = threadIdx.y;
+        for (; i + 96 < nblk; i += 128) {  // 8 independent loads in flight: the fold is latency-, not bandwidth-bound
+            float p0 = partial[(size_t)i * 2 * cpad + c], q0 = partial[(size_t)i * 2 * cpad + cpad + c];
+            float p1 = partial[(size_t)(i + 32) * 2 * cpad + c], q1 = partial[(size_t)(i + 32) * 2 * cpad + cpad + c];
+            float p2 = partial[(size_t)(i + 64) * 2 * cpad + c], q2 = partial[(size_t)(i + 64) * 2 * cpad + cpad + c];
+            float p3 = partial[(size_t)(i + 96) * 2 * cpad + c], q3 = partial[(size_t)(i + 96) * 2 * cpad + cpad + c];
+            a += ((double)p0 + (double)p1) + ((double)p2 + (double)p3);
+            b += ((double)q0 + (double)q1) + ((double)q2 + (double)q3);
+        }
+        for (; i < nblk; i += 32) {
             a += (double)partial[(size_t)i * 2 * cpad + c];
             b += (double)partial[(size_t)i * 2 * cpad + cpad + c];
         }
+    }
     sh1[threadIdx.y][threadIdx.x] = a;
     sh2[threadIdx.y][threadIdx.x] = b;
     __syncthreads();

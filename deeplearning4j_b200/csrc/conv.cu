@@ -14,6 +14,7 @@ static void geom_finish(ConvGeom &g) {
     g.div_kW = FastDiv((uint32_t)g.kW);
     g.fast = g.kH <= 16 && g.kW <= 16 && (!g.transposed || (g.sH == 1 && g.sW == 1) || g.taps == 1);
     g.use_tma = 0;
+    g.remap = 0; g.rm_sy = g.rm_sx = 1; g.rm_H = g.Hm; g.rm_W = g.Wm;
 }
 
 ConvGeom conv_geom_fwd(const dl4jb200_conv_desc *d, int x_cs) {
@@ -278,6 +279,23 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
         DL4J_CHECK_LAUNCH();
     }
 
+    if (dx && tcore && d->k_h == 1 && d->k_w == 1 && (d->stride_h > 1 || d->stride_w > 1) && d->pad_top == 0 && d->pad_left == 0) {
+        // strided 1x1: dx is non-zero only at the sampled pixels. Run the GEMM on the compact pixel set (a plain
+        // unit-stride 1x1 walk over delta, TMA-able) and scatter its rows; everything else is zero.
+        ConvGeom gc = gb;
+        gc.transposed = 0; gc.Hm = d->out_h; gc.Wm = d->out_w; gc.sH = gc.sW = 1;
+        geom_finish(gc);
+        gc.remap = 1; gc.rm_sy = d->stride_h; gc.rm_sx = d->stride_w; gc.rm_H = d->in_h; gc.rm_W = d->in_w;
+        gc.use_tma = conv_tc_gemm_can_tma(gc);
+        if (gc.use_tma) {
+            DL4J_CUDA_TRY(cudaMemsetAsync(dxs, 0, (size_t)d->batch * d->in_h * d->in_w * dx_cs * sizeof(float), ctx->stream));
+            k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, 1, 1, gc.Cg, gc.Kp, rows_b, 1, 1, 0);
+            DL4J_CHECK_LAUNCH();
+            if ((rc = conv_tc_gemm(ctx, gc, ds, wb, rows_b, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY))) return rc;
+            if (dx_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, dxs, dx, d->batch, d->c_in, d->in_h, d->in_w, dx_cs);
+            return DL4JB200_OK;
+        }
+    }
     if (dx) {
         DL4J_REQUIRE(delta_cs >= gb.Cg, "conv_bwd: delta pixel stride %d < %d", delta_cs, gb.Cg);
         k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, tcore, gb.use_tma);

@@ -17,6 +17,7 @@ struct ConvGeom {
     int transposed;         // 0: iy = y*sH - pT + kh*dH      1: iy = (y + pT - kh*dH)/sH when divisible
     int fast;               // taps are an affine offset from a per-row base pointer (see conv_row_setup)
     int use_tma;            // operands fetched by TMA (im2col mode); backprop-data then needs the filter packed tap-flipped
+    int remap, rm_sy, rm_sx, rm_H, rm_W;  // output-row scatter (see TmaGemmGeom)
     FastDiv div_Wm, div_HWm, div_Cg, div_kW;
 };
 

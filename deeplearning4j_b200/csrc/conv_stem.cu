@@ -112,6 +112,7 @@ int dl4jb200_conv_rowpack_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, co
     t.lowH = -d->pad_top; t.lowW = 0;
     t.div_Wm = FastDiv((uint32_t)d->out_w); t.div_HWm = FastDiv((uint32_t)(d->out_h * d->out_w));
     t.div_Cg = FastDiv(32u); t.div_kW = FastDiv(1u);
+    t.remap = 0; t.rm_sy = t.rm_sx = 1; t.rm_H = d->out_h; t.rm_W = d->out_w;
     return conv_tc_gemm_tma_raw(ctx, tmA, tmB, t, bias, z, d->c_out, z_cs, act, bn);
 }
 

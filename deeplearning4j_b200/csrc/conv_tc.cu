@@ -142,6 +142,28 @@ __device__ __forceinline__ void store_tile_32x32(uint32_t stage_smem, const floa
     }
 }
 
+// Same, but every row has its own destination (element offset from `out`, or < 0 to skip): output-row scatter.
+__device__ __forceinline__ void store_tile_32x32_rows(uint32_t stage_smem, const float (&v)[32], int lane, float *out,
+                                                      const long long (&rowoff)[8], int col0) {
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        const uint32_t a = stage_smem + (uint32_t)lane * 128u + (uint32_t)((q ^ (lane & 7)) << 4);
+        asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v[q * 4]), "f"(v[q * 4 + 1]), "f"(v[q * 4 + 2]),
+                     "f"(v[q * 4 + 3]) : "memory");
+    }
+    __syncwarp();
+    const int c = lane & 7;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int row = 4 * i + (lane >> 3);
+        float4 t;
+        const uint32_t a = stage_smem + (uint32_t)row * 128u + (uint32_t)((c ^ (row & 7)) << 4);
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(a));
+        if (rowoff[i] >= 0) *reinterpret_cast<float4 *>(out + rowoff[i] + col0 + c * 4) = t;
+    }
+}
+
 // Instruction descriptor (InstrDescriptor): c_format F32 [4,6)=1, a/b_format TF32 [7,10)=[10,13)=2,
 // a_major bit 15, b_major bit 16 (1 = MN-major), N>>3 at [17,23), M>>4 at [24,29)
 __host__ __device__ constexpr uint32_t umma_idesc(int M, int N, int a_mn, int b_mn) {
@@ -578,7 +600,7 @@ struct PersistSmem {
     static constexpr int BYTES = BAR_OFF + 256 + 1024;
 };
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool REMAP>
 __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const __grid_constant__ CUtensorMap tmA,
                                                                           const __grid_constant__ CUtensorMap tmB,
                                                                           const float *__restrict__ bias,
@@ -669,6 +691,20 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
             const bool full_n = n0 + BN <= n_valid;
             const int m = m0 + warp * 32 + lane;
             const int rows_valid = g.M - (m0 + warp * 32);
+            long long rowoff[8];
+            if (REMAP) {
+#pragma unroll
+                for (int r8 = 0; r8 < 8; r8++) {
+                    const int mm = m0 + warp * 32 + 4 * r8 + (lane >> 3);
+                    rowoff[r8] = -1;
+                    if (mm < g.M) {
+                        uint32_t img, rr, oy, ox;
+                        g.div_HWm.divmod((uint32_t)mm, img, rr);
+                        g.div_Wm.divmod(rr, oy, ox);
+                        rowoff[r8] = (((long long)img * g.rm_H + (long long)oy * g.rm_sy) * g.rm_W + (long long)ox * g.rm_sx) * out_cs;
+                    }
+                }
+            }
             mbar_wait(tfull_bar(buf), (i >> 1) & 1);
             tc_fence_after();
             const uint32_t acc = tmem_d + (uint32_t)(buf * BN) + ((uint32_t)(warp * 32) << 16);
@@ -696,9 +732,17 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
 #pragma unroll
                         for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);  // static indices keep v[] in registers
                     }
-                    store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
+                    if (REMAP) store_tile_32x32_rows(stage_smem, v, lane, out, rowoff, nb);
+                    else store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
                 } else if (m < g.M) {
-                    float *orow = out + (size_t)m * out_cs;
+                    long long ro = (long long)m * out_cs;
+                    if (REMAP) {
+                        uint32_t img, rr, oy, ox;
+                        g.div_HWm.divmod((uint32_t)m, img, rr);
+                        g.div_Wm.divmod(rr, oy, ox);
+                        ro = (((long long)img * g.rm_H + (long long)oy * g.rm_sy) * g.rm_W + (long long)ox * g.rm_sx) * out_cs;
+                    }
+                    float *orow = out + ro;
 #pragma unroll
                     for (int q = 0; q < 8; q++) {
                         const int n = nb + q * 4;
@@ -724,15 +768,18 @@ template <int BN, int STAGES>
 static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const TmaGemmGeom &g,
                                    const float *bias, float *out, int n_valid, int out_cs, int act) {
     using L = PersistSmem<BN, STAGES>;
-    auto kern = k_conv_tc_gemm_tma_persist<BN, STAGES>;
     static bool configured[16] = {false};
     if (!configured[ctx->device & 15]) {
-        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
         configured[ctx->device & 15] = true;
     }
     const int n_tiles = dl4j_ceil_div(out_cs, BN), total = dl4j_ceil_div(g.M, BLOCK_M) * n_tiles;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
-    kern<<<grid, PTHREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act, n_tiles, total);
+    if (g.remap)
+        k_conv_tc_gemm_tma_persist<BN, STAGES, true><<<grid, PTHREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act, n_tiles, total);
+    else
+        k_conv_tc_gemm_tma_persist<BN, STAGES, false><<<grid, PTHREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act, n_tiles, total);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
@@ -968,6 +1015,8 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
     TmaGemmGeom t;
     t.M = g.M; t.num_k = g.Kp / tc::BLOCK_K; t.kW = g.kW; t.dH = g.dH; t.dW = g.dW; t.sH = sH; t.sW = sW; t.lowH = lowH; t.lowW = lowW;
     t.div_Wm = g.div_Wm; t.div_HWm = g.div_HWm; t.div_Cg = g.div_Cg; t.div_kW = g.div_kW;
+    t.remap = g.remap; t.rm_sy = g.rm_sy; t.rm_sx = g.rm_sx; t.rm_H = g.rm_H; t.rm_W = g.rm_W;
+    if (g.remap && !aligned_bias) { dl4j_set_error("conv_tc_gemm_tma: row scatter needs the persistent kernel"); return DL4JB200_ERR_INVALID_ARG; }
     if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
     if (!aligned_bias) {  // the persistent epilogue reads the bias with 128-bit loads
         if (bn == 128) return tc::launch_gemm_tma<128, 3>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);

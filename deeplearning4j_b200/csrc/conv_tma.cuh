@@ -39,6 +39,9 @@ namespace tcgeom {
 struct TmaGemmGeom {
     int M, num_k, kW, dH, dW, sH, sW, lowH, lowW;
     FastDiv div_Wm, div_HWm, div_Cg, div_kW;
+    // optional output-row scatter: GEMM row (b, oy, ox) is stored at pixel (b, oy*rm_sy, ox*rm_sx) of an rm_H x rm_W image
+    // (backprop-data of a strided 1x1 convolution computed on the compact pixel set; the rest of dx is pre-zeroed)
+    int remap, rm_sy, rm_sx, rm_H, rm_W;
 };
 struct TmaWgradGeom {
     int M, kW, dH, dW, sH, sW, lowH, lowW, Kp;
