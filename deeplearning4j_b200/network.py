@@ -211,11 +211,17 @@ class Network:
             lab = t.as_tensor(labels) if not isinstance(labels, t.Tensor) else labels
             self.labels = lab.to(self.dev, non_blocking=True).contiguous()
             self._feat = f.contiguous()
+        self._relayout_input()
+
+    def _relayout_input(self, src=None):
+        inp = self.model["vertices"][0]["name"]
+        Cc, Hh, W = self.shapes[inp]
+        src = self._feat if src is None else src
         if self.stem:
-            self._call("dl4jb200_nchw_to_rowpack4", self._ptr(self._feat), self._ptr(self.out[inp]), self.B, Cc, Hh, W,
+            self._call("dl4jb200_nchw_to_rowpack4", self._ptr(src), self._ptr(self.out[inp]), self.B, Cc, Hh, W,
                        self.stem[1], self.stem[2])
         else:
-            self._call("dl4jb200_nchw_to_nhwc", self._ptr(self._feat), self._ptr(self.out[inp]), self.B, Cc, Hh, W, self.cs[inp])
+            self._call("dl4jb200_nchw_to_nhwc", self._ptr(src), self._ptr(self.out[inp]), self.B, Cc, Hh, W, self.cs[inp])
 
     # ------------------------------------------------------------------ forward (feedForward, train mode)
     def forward(self, train=True):
@@ -508,6 +514,91 @@ class Network:
         self.update()  # also leaves the L1/L2 part of the score (pre-update weights) in score_reg
         with self.torch.cuda.stream(self.stream):
             return (self.loss + self.score_reg) / float(self.B)
+
+    # ------------------------------------------------------------------ CUDA graph of one iteration
+    def capture(self, hook=None, include_input=True):
+        """Record one fit() iteration (input re-layout, forward, backward, [gradient exchange], updater, score) into a
+        CUDA graph on the network's stream. Every buffer the step touches is static, so the graph can be replayed for
+        every minibatch; this removes the ~800 per-kernel launch gaps of the eager chain. Call after at least one eager
+        fit() (scratch regions and epsilon buffers must already exist: nothing may be allocated while capturing)."""
+        t = self.torch
+        assert self.labels is not None and self._feat is not None, "run one eager fit(features, labels) first"
+        self.stream.synchronize()
+        self._graph = t.cuda.CUDAGraph()
+        self._graph_has_input = include_input
+        with t.cuda.graph(self._graph, stream=self.stream):
+            if include_input:
+                self._relayout_input()
+            self.forward(True)
+            self.backward()
+            if hook is not None:
+                hook(self)
+            self.update()
+            self._graph_score = (self.loss + self.score_reg) / float(self.B)
+        return self._graph
+
+    def fit_graph(self, features=None, labels=None):
+        """fit() through the captured graph. New minibatches are copied into the static input buffers first."""
+        t = self.torch
+        if features is not None:
+            with t.cuda.stream(self.stream):
+                f = t.as_tensor(features) if not isinstance(features, t.Tensor) else features
+                lab = t.as_tensor(labels) if not isinstance(labels, t.Tensor) else labels
+                self._feat.copy_(f, non_blocking=True)
+                self.labels.copy_(lab, non_blocking=True)
+            if not self._graph_has_input:
+                self._relayout_input()
+        with t.cuda.stream(self.stream):
+            self._graph.replay()
+        return self._graph_score
+
+    # ------------------------------------------------------------------ prefetching input pipeline
+    def prefetch(self, features, labels):
+        """Start the host->device copy of the NEXT minibatch on a separate copy stream (double-buffered), so it overlaps
+        the step that is running -- what MultiLayerNetwork.fit(DataSetIterator) gets from wrapping its iterator in an
+        AsyncDataSetIterator (nn/multilayer/MultiLayerNetwork.java:1272-1275). Pair with fit_prefetched()."""
+        t = self.torch
+        if not hasattr(self, "_pf"):
+            inp = self.model["vertices"][0]["name"]
+            Cc, Hh, W = self.shapes[inp]
+            K = self.shapes[self.model["vertices"][-1]["name"]][0]
+            self._pf = {"stream": t.cuda.Stream(self.dev), "head": 0, "tail": 0,
+                        "x": [t.empty(self.B, Cc, Hh, W, device=self.dev) for _ in range(2)],
+                        "y": [t.empty(self.B, K, device=self.dev) for _ in range(2)],
+                        "ready": [t.cuda.Event() for _ in range(2)], "free": [None, None]}
+        pf = self._pf
+        slot = pf["head"] % 2
+        pf["head"] += 1
+        f = t.as_tensor(features) if not isinstance(features, t.Tensor) else features
+        lab = t.as_tensor(labels) if not isinstance(labels, t.Tensor) else labels
+        with t.cuda.stream(pf["stream"]):
+            if pf["free"][slot] is not None:
+                pf["stream"].wait_event(pf["free"][slot])  # the step that consumed this slot has finished reading it
+            pf["x"][slot].copy_(f, non_blocking=True)
+            pf["y"][slot].copy_(lab, non_blocking=True)
+            pf["ready"][slot].record(pf["stream"])
+
+    def fit_prefetched(self, hook=None):
+        """One iteration on the oldest prefetched minibatch (graph replay when capture(include_input=False) was made)."""
+        t = self.torch
+        pf = self._pf
+        assert pf["tail"] < pf["head"], "nothing prefetched"
+        slot = pf["tail"] % 2
+        pf["tail"] += 1
+        self.stream.wait_event(pf["ready"][slot])
+        self._relayout_input(pf["x"][slot])
+        with t.cuda.stream(self.stream):
+            if self.labels is None:
+                self.labels = t.empty_like(pf["y"][slot])
+            self.labels.copy_(pf["y"][slot], non_blocking=True)
+            ev = t.cuda.Event()
+            ev.record(self.stream)
+        pf["free"][slot] = ev
+        if getattr(self, "_graph", None) is not None and not self._graph_has_input:
+            with t.cuda.stream(self.stream):
+                self._graph.replay()
+            return self._graph_score
+        return self.fit(hook=hook)
 
     def sync(self):
         """Host waits for everything queued on the network's stream (results are then safe to read from any stream)."""

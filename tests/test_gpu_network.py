@@ -153,3 +153,38 @@ def test_resnet50_step_parity_small_batch():
             assert cos >= min_cos, (algo, cos)
         finally:
             net.close()
+
+
+def test_graph_replay_and_prefetch_match_eager():
+    """CUDA-graph replay of the step and the prefetching input pipeline are scheduling changes only: after three
+    iterations on three different minibatches the parameters are bit-identical to the eager chain's."""
+    from deeplearning4j_b200 import network
+    m = _tiny_resnet()
+    B = 8
+    from deeplearning4j_b200 import zoo
+    p0 = zoo.init_params(m)
+    batches = [_data(m, B, 10, seed=s) for s in (1, 2, 3, 4)]
+    ref = network.Network(m, B, params=p0)
+    for x, lab in batches:
+        ref.fit(x, lab)
+    ref.sync()
+    want = ref.params.cpu().numpy().copy()
+    ref.close()
+    for mode in ("graph", "prefetch"):
+        net = network.Network(m, B, params=p0)
+        try:
+            net.fit(*batches[0])  # eager warm-up step (allocates scratch / epsilon buffers)
+            net.capture(include_input=(mode == "graph"))
+            if mode == "graph":
+                for x, lab in batches[1:]:
+                    net.fit_graph(x, lab)
+            else:
+                net.prefetch(*batches[1])
+                for k in range(1, 4):
+                    if k + 1 < 4:
+                        net.prefetch(*batches[k + 1])
+                    net.fit_prefetched()
+            net.sync()
+            np.testing.assert_array_equal(net.params.cpu().numpy(), want)
+        finally:
+            net.close()
