@@ -239,10 +239,18 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = float(t[0]), float(t[1])
-    if rank != 0:
+    def finish():
+        # NCCL communicators referenced by a captured CUDA graph make destroy_process_group() block: drop the graph,
+        # drain, flush and leave without the collective teardown
+        sys.stdout.flush()
+        sys.stderr.flush()
         if world > 1:
-            dist.destroy_process_group()
-        return
+            net._graph = None
+            torch.cuda.synchronize()
+            os._exit(0)
+
+    if rank != 0:
+        return finish()
 
     pk = peaks()
     total_imgs = B * world * args.steps
@@ -328,8 +336,7 @@ def main():
     if cpu:
         line["cpu_baseline"] = cpu
     print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    finish()
 
 
 if __name__ == "__main__":
