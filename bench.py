@@ -264,9 +264,9 @@ def main():
         if fn in ("dl4jb200_conv_fwd", "dl4jb200_conv_bwd", "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_wgrad") and tag in fl:
             f = fl[tag][0 if fn.endswith("fwd") else 1]
             conv_ms += sum(times)
-            conv_fl += f * len(times)
+            conv_fl += f * psteps  # one layer pass set per step, however many calls it is split into
             n_conv_calls += len(times)
-            per_layer[f"{tag}:{fn[9:]}"] = {"ms": sum(times) / len(times), "tflops": f / (sum(times) / len(times) * 1e-3) / 1e12}
+            per_layer[f"{tag}:{fn[9:]}"] = {"ms": sum(times) / psteps, "tflops": f / (sum(times) / psteps * 1e-3) / 1e12}
     tf32_peak = pk["bf16_tflops_sustained"] / 2.0
     ach = conv_fl / (conv_ms * 1e-3) / 1e12 if conv_ms else 0.0
     roofline = {"bound": "tensor", "kernel": "k_conv_tc_gemm_tma_persist / k_conv_tc_wgrad_tma (all convolution + dense calls of the step)",

@@ -208,7 +208,8 @@ int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
 int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs,
                       const float *w, const float *delta, int delta_layout, int delta_cs, float *dw, float *db,
                       float *dx, int dx_layout, int dx_cs, int algo) {
-    DL4J_REQUIRE(ctx && x && w && delta && dw, "conv_bwd: NULL argument");
+    DL4J_REQUIRE(ctx && x && w && delta, "conv_bwd: NULL argument");
+    DL4J_REQUIRE(dw || db || dx, "conv_bwd: nothing to compute (dw, db and dx are all NULL)");
     int rc = check_desc(d, "conv_bwd");
     if (rc) return rc;
     if ((rc = check_layout(x_layout, x_cs, d->c_in, x, "conv_bwd", "x"))) return rc;
@@ -265,12 +266,14 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     if (!ws) return DL4JB200_ERR_CUDA;
     float *partial = ws, *wb = ws + part_f, *colp = wb + pack_f;
 
-    if (tcore) rc = conv_tc_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
-    else rc = conv_ffma_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
-    if (rc) return rc;
-    k_wgrad_finalize<<<grid_for(ctx, (size_t)d->c_out * d->c_in * gf.taps), 256, 0, ctx->stream>>>(
-        partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w, splits);
-    DL4J_CHECK_LAUNCH();
+    if (dw) {
+        if (tcore) rc = conv_tc_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
+        else rc = conv_ffma_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
+        if (rc) return rc;
+        k_wgrad_finalize<<<grid_for(ctx, (size_t)d->c_out * d->c_in * gf.taps), 256, 0, ctx->stream>>>(
+            partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w, splits);
+        DL4J_CHECK_LAUNCH();
+    }
 
     if (db) {
         k_colsum_partial<<<nblk, 256, 0, ctx->stream>>>(ds, colp, gf.M, delta_cs);

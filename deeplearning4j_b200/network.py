@@ -36,6 +36,13 @@ class Network:
         h = C.c_void_p()
         _lib.call("dl4jb200_ctx_create", device, C.c_void_p(self.stream.cuda_stream), C.byref(h))
         self.h = h
+        # Filter / bias gradients do not feed the backward chain: they run on a second stream + context (own scratch),
+        # forked from the main stream once a layer's delta is final and joined before the gradient exchange / updater.
+        self.side_stream = torch.cuda.Stream(self.dev)
+        h2 = C.c_void_p()
+        _lib.call("dl4jb200_ctx_create", device, C.c_void_p(self.side_stream.cuda_stream), C.byref(h2))
+        self.h2 = h2
+        self.overlap_wgrad = True
         self.launches = 0
         self.prof, self.prof_fns, self._cur = None, set(), None
         self.batch_div_scale = 1  # data-parallel replicas: global minibatch = scale * B (parallel.py)
@@ -160,6 +167,19 @@ class Network:
             self.prof.append((fn, self._cur, a, b))
         else:
             _lib.call(fn, self.h, *args)
+
+    def _call_side(self, fn, *args):
+        """Same as _call on the side (filter-gradient) context / stream."""
+        self.launches += 1
+        if self.prof is not None and fn in self.prof_fns:
+            ev = self.torch.cuda.Event
+            a, b = ev(enable_timing=True), ev(enable_timing=True)
+            a.record(self.side_stream)
+            _lib.call(fn, self.h2, *args)
+            b.record(self.side_stream)
+            self.prof.append((fn, self._cur, a, b))
+        else:
+            _lib.call(fn, self.h2, *args)
 
     def profile(self, fns):
         """Start recording CUDA-event pairs (on the network's stream) around the given C-ABI calls."""
@@ -358,6 +378,7 @@ class Network:
     def backward(self):
         L, B = _lib, self.B
         self._written, self._borrowed = set(), {}
+        self._side_used = False
         for v in reversed(self.model["vertices"]):
             n, op = v["name"], v["op"]
             self._cur = n
@@ -378,16 +399,23 @@ class Network:
                 pw, gw, _, _ = self._p(n, "W")
                 _, gb, _, _ = self._p(n, "b")
 
-                def run(dx, d=d, x=x, xcs=xcs, pw=pw, gw=gw, gb=gb, e=e, n=n):
-                    self._call("dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
-                               gw, gb, dx, L.NHWC, xcs, self.algo)
+                side = self.overlap_wgrad
+                wcall = self._call_side if side else self._call
+                if side:  # fork: the side stream may start once everything queued so far (delta is final) has run
+                    fork = self.torch.cuda.Event()
+                    fork.record(self.stream)
+                    self.side_stream.wait_event(fork)
+                    self._side_used = True
                 if self.stem and self.stem[0] == n:
-                    self._call("dl4jb200_conv_rowpack_wgrad", C.byref(d), self._ptr(x), self.stem[1], self._ptr(e), self.cs[n], gw)
-                    self._call("dl4jb200_bias_grad", self._ptr(e), B * d.out_h * d.out_w, self.cs[n], d.c_out, gb)
-                elif self._needs_eps(src):
-                    self._emit(src, run)
+                    wcall("dl4jb200_conv_rowpack_wgrad", C.byref(d), self._ptr(x), self.stem[1], self._ptr(e), self.cs[n], gw)
+                    wcall("dl4jb200_bias_grad", self._ptr(e), B * d.out_h * d.out_w, self.cs[n], d.c_out, gb)
                 else:
-                    run(None)
+                    wcall("dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
+                          gw, gb, None, L.NHWC, xcs, self.algo)
+                    if self._needs_eps(src):
+                        self._emit(src, lambda dx, d=d, x=x, xcs=xcs, pw=pw, e=e, n=n: self._call(
+                            "dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
+                            None, None, dx, L.NHWC, xcs, self.algo))
             elif op == "bn":
                 u = v["in"][0]
                 x, xcs = self._src(u)
@@ -420,6 +448,10 @@ class Network:
                 self._emit(u, lambda dx: self._call("dl4jb200_nchw_to_nhwc", self._ptr(srcbuf), dx, B, s[0], s[1], s[2], self.cs[u]))
             else:
                 raise NotImplementedError(op)
+        if self._side_used:  # join: gradient exchange / updater must see every filter gradient
+            join = self.torch.cuda.Event()
+            join.record(self.side_stream)
+            self.stream.wait_event(join)
 
     # ------------------------------------------------------------------ updater + step (BaseMultiLayerUpdater.update)
     def _upd_args(self, cfg):
@@ -618,4 +650,5 @@ class Network:
         if self.h:
             self.torch.cuda.synchronize(self.dev)
             _lib.call("dl4jb200_ctx_destroy", self.h)
+            _lib.call("dl4jb200_ctx_destroy", self.h2)
             self.h = None

@@ -147,7 +147,9 @@ int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
 /* ConvolutionHelper.backpropGradient (ConvolutionHelper.java:37-40; CPU semantics
  * ConvolutionLayer.java:202-257). delta = dL/dz (the layer applies afn.backprop before calling the helper,
  * ConvolutionLayer.java:170-171). dw / db are the weightGradView / biasGradView: written IN PLACE,
- * overwritten (not accumulated), summed over the batch, DL4J layout. db and dx may be NULL. */
+ * overwritten (not accumulated), summed over the batch, DL4J layout. Any of dw, db, dx may be NULL (that part is then
+ * skipped), which lets a caller run the filter/bias gradients and the data gradient of one layer on two contexts /
+ * streams concurrently: they are independent of each other. */
 int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs,
                       const float *w, const float *delta, int delta_layout, int delta_cs, float *dw, float *db,
                       float *dx, int dx_layout, int dx_cs, int algo);
