@@ -1,0 +1,109 @@
+"""-m gpu checks at BASELINE.json's full sizes (ResNet-50 batch 256 shapes), where the CPU oracle would take minutes:
+size-independent properties instead of element-wise comparison."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def env():
+    import torch
+    from deeplearning4j_b200 import _lib, helpers
+    stream = torch.cuda.Stream()
+    h = C.c_void_p()
+    _lib.call("dl4jb200_ctx_create", 0, C.c_void_p(stream.cuda_stream), C.byref(h))
+    yield torch, _lib, helpers, h, stream
+    stream.synchronize()
+    _lib.call("dl4jb200_ctx_destroy", h)
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr())
+
+
+def test_batchnorm_full_size_mean0_std1_and_gradient_sums(env):
+    # stem BN of ResNet-50 at batch 256: [256,64,112,112] (205 M elements). BatchNormalizationTest.java:178-208 property
+    torch, L, H, h, stream = env
+    B, Cc, Hh, W = 256, 64, 112, 112
+    with torch.cuda.stream(stream):
+        g = torch.Generator(device="cuda").manual_seed(1)
+        x = torch.randn(B, Hh, W, Cc, device="cuda", generator=g) * 3 + 5
+        y = torch.empty_like(x)
+        gamma, beta = torch.ones(Cc, device="cuda"), torch.zeros(Cc, device="cuda")
+        gm, gv = torch.zeros(Cc, device="cuda"), torch.ones(Cc, device="cuda")
+        sm, ss = torch.empty(Cc, device="cuda"), torch.empty(Cc, device="cuda")
+    stream.synchronize()
+    L.call("dl4jb200_bn_fwd", h, _p(x), _p(y), _p(gamma), _p(beta), _p(gm), _p(gv), _p(sm), _p(ss), B, Cc, Hh, W, L.NHWC, Cc,
+           0.9, 1e-5, 1, 1, L.ACT_IDENTITY, None)
+    stream.synchronize()
+    yd = y.double()
+    assert float(yd.mean((0, 1, 2)).abs().max()) < 1e-4
+    assert float((yd.std((0, 1, 2), unbiased=False) - 1).abs().max()) < 1e-4
+    np.testing.assert_allclose(sm.cpu().numpy(), x.double().mean((0, 1, 2)).cpu().numpy(), rtol=1e-5)
+    # backward: sum_pixels dx == 0 and sum_pixels dx*xhat == 0 per channel (dx is orthogonal to 1 and to xhat)
+    with torch.cuda.stream(stream):
+        e = torch.randn(B, Hh, W, Cc, device="cuda", generator=g)
+        dx, dg, db = torch.empty_like(x), torch.empty(Cc, device="cuda"), torch.empty(Cc, device="cuda")
+    stream.synchronize()
+    L.call("dl4jb200_bn_bwd", h, _p(x), _p(e), _p(gamma), None, _p(sm), _p(ss), L.ACT_IDENTITY, _p(dx), _p(dg), _p(db), B, Cc, Hh,
+           W, L.NHWC, Cc)
+    stream.synchronize()
+    n = B * Hh * W
+    assert float(dx.double().sum((0, 1, 2)).abs().max()) / n < 1e-6
+    assert float((dx.double() * yd).sum((0, 1, 2)).abs().max()) / n < 1e-5
+    np.testing.assert_allclose(db.cpu().numpy(), e.double().sum((0, 1, 2)).cpu().numpy(), rtol=1e-4, atol=1e-2)
+
+
+def test_maxpool_full_size_conservation_and_bounds(env):
+    # stem max-pool of ResNet-50: [256,64,112,112] -> 55x55, k3 s2. Every window routes its epsilon to exactly one cell,
+    # so sum(dx) == sum(eps) per (image, channel); y >= every cell of its window; argmax in range.
+    torch, L, H, h, stream = env
+    B, Cc, Hh, W = 256, 64, 112, 112
+    d = H.conv_desc((B, Cc, Hh, W), Cc, (3, 3), (2, 2), (0, 0), (1, 1), "Truncate")
+    with torch.cuda.stream(stream):
+        g = torch.Generator(device="cuda").manual_seed(2)
+        x = torch.randn(B, Hh, W, Cc, device="cuda", generator=g)
+        y = torch.empty(B, d.out_h, d.out_w, Cc, device="cuda")
+        am = torch.empty(B, d.out_h, d.out_w, Cc, device="cuda", dtype=torch.int32)
+        e = torch.randn(B, d.out_h, d.out_w, Cc, device="cuda", generator=g)
+        dx = torch.empty_like(x)
+    stream.synchronize()
+    L.call("dl4jb200_pool_fwd", h, C.byref(d), _p(x), _p(y), _p(am), L.NHWC, Cc, Cc, L.POOL_MAX, 2)
+    L.call("dl4jb200_pool_bwd", h, C.byref(d), _p(x), _p(y), _p(e), _p(am), _p(dx), L.NHWC, Cc, Cc, L.POOL_MAX, 2, 1e-8)
+    stream.synchronize()
+    ref = torch.nn.functional.max_pool2d(x.permute(0, 3, 1, 2), 3, 2).permute(0, 2, 3, 1)
+    assert torch.equal(y, ref)  # bit-exact values
+    assert int(am.min()) >= 0 and int(am.max()) <= 8
+    np.testing.assert_allclose(dx.double().sum((1, 2)).cpu().numpy(), e.double().sum((1, 2)).cpu().numpy(), rtol=1e-5, atol=1e-4)
+
+
+def test_conv_full_size_linearity_and_identity(env):
+    # res2x_branch2b of ResNet-50 at batch 256: 3x3 SAME 64->64 on 28x28 (M = 200 704). With TF32-exact operands
+    # (small integers) the tensor-core path is exact: a one-hot filter reproduces a shifted copy of the input, and
+    # conv(x, w1 + w2) == conv(x, w1) + conv(x, w2) bit for bit.
+    torch, L, H, h, stream = env
+    B, Cc, Hh, W = 256, 64, 28, 28
+    d = H.conv_desc((B, Cc, Hh, W), Cc, (3, 3), (1, 1), (0, 0), (1, 1), "Same")
+    with torch.cuda.stream(stream):
+        g = torch.Generator(device="cuda").manual_seed(3)
+        x = torch.randint(-8, 9, (B, Hh, W, Cc), device="cuda", generator=g).float()
+        w1 = torch.randint(-2, 3, (Cc, Cc, 3, 3), device="cuda", generator=g).float()
+        w2 = torch.randint(-2, 3, (Cc, Cc, 3, 3), device="cuda", generator=g).float()
+        eye = torch.zeros(Cc, Cc, 3, 3, device="cuda")
+        eye[torch.arange(Cc), torch.arange(Cc), 0, 2] = 1.0  # tap (kh=0, kw=2): z[y,x] = x[y-1, x+1]
+        z1, z2, z12, zi = (torch.empty(B, Hh, W, Cc, device="cuda") for _ in range(4))
+        w12 = w1 + w2
+    stream.synchronize()
+    for w, z in ((w1, z1), (w2, z2), (w12, z12), (eye, zi)):
+        L.call("dl4jb200_conv_fwd", h, C.byref(d), _p(x), L.NHWC, Cc, _p(w), None, _p(z), L.NHWC, Cc, L.ACT_IDENTITY, L.ALGO_TC_TF32)
+    stream.synchronize()
+    assert torch.equal(z12, z1 + z2)
+    shifted = torch.zeros_like(x)
+    shifted[:, 1:, :-1, :] = x[:, :-1, 1:, :]
+    assert torch.equal(zi, shifted)
+    # and the whole thing agrees with an fp32 reference convolution exactly (all partial sums are small integers)
+    ref = torch.nn.functional.conv2d(x.permute(0, 3, 1, 2), w1, padding=1).permute(0, 2, 3, 1)
+    assert torch.equal(z1, ref.contiguous())
