@@ -300,7 +300,63 @@ __global__ void __launch_bounds__(256) k_score_fold(const double *partial, int n
     if (threadIdx.x == 0) score_out[0] = (float)s[0];
 }
 
+// ---------------------------------------------------------------- gradient normalisation (BaseMultiLayerUpdater.preApply)
+__global__ void __launch_bounds__(256) k_sumsq_partial(const float *__restrict__ g, size_t n, double *partial) {
+    __shared__ double s[256];
+    double a = 0.0;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) { double v = g[i]; a += v * v; }
+    s[threadIdx.x] = a;
+    __syncthreads();
+    for (int o = 128; o; o >>= 1) {
+        if (threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partial[blockIdx.x] = s[0];
+}
+// mode 1 RenormalizeL2PerLayer: g /= ||g||2 ; mode 2 ClipL2PerLayer: g *= thr/||g||2 if ||g||2 > thr ; mode 3 clip elementwise
+__global__ void __launch_bounds__(256) k_grad_scale(float *__restrict__ g, size_t n, const double *partial, int nblk, int mode,
+                                                    float thr) {
+    __shared__ float scale_s;
+    if (mode != 3) {
+        __shared__ double s[256];
+        double a = 0.0;
+        for (int i = threadIdx.x; i < nblk; i += 256) a += partial[i];
+        s[threadIdx.x] = a;
+        __syncthreads();
+        for (int o = 128; o; o >>= 1) {
+            if (threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) {
+            double l2 = sqrt(s[0]);
+            scale_s = mode == 1 ? (float)(1.0 / l2) : (l2 > (double)thr ? (float)((double)thr / l2) : 1.f);
+        }
+        __syncthreads();
+    }
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+        g[i] = mode == 3 ? fminf(fmaxf(g[i], -thr), thr) : g[i] * scale_s;
+}
+
 extern "C" {
+
+int dl4jb200_grad_normalize(dl4jb200_ctx *ctx, float *g, size_t n, int mode, double threshold) {
+    DL4J_REQUIRE(ctx && g, "grad_normalize: NULL argument");
+    DL4J_REQUIRE(mode >= 1 && mode <= 3, "grad_normalize: mode 1 (RenormalizeL2PerLayer), 2 (ClipL2PerLayer) or 3 (ClipElementWiseAbsoluteValue)");
+    if (n == 0) return DL4JB200_OK;
+    int nblk = ew_grid(ctx, n, 256);
+    if (nblk > 256) nblk = 256;
+    double *partial = (double *)dl4j_workspace(ctx, 0, (size_t)nblk * sizeof(double));
+    if (!partial) return DL4JB200_ERR_CUDA;
+    if (mode != 3) {
+        k_sumsq_partial<<<nblk, 256, 0, ctx->stream>>>(g, n, partial);
+        DL4J_CHECK_LAUNCH();
+    }
+    k_grad_scale<<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(g, n, partial, nblk, mode, (float)threshold);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
 
 int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n,
                                     const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,

@@ -494,8 +494,7 @@ class Network:
     def update(self):
         """All updater blocks + the L1/L2 score terms in one launch (update_per_block is the per-array form)."""
         m = self.model
-        if m.get("grad_norm"):
-            raise NotImplementedError("gradient normalisation " + str(m["grad_norm"]))
+        self._grad_normalize()
         if not hasattr(self, "seg_start"):
             self._build_segments()
         div = float(self.B * self.batch_div_scale) if m["minibatch"] else 1.0
@@ -503,10 +502,25 @@ class Network:
                    self._ptr(self.seg_start), self._ptr(self.seg_cfg), len(self.layout), self.seg_cfg_host, self.n_cfg, div,
                    self._ptr(self.score_reg) if self.with_score else None)
 
+    def _grad_normalize(self):
+        """GradientNormalization over each layer's gradient view (BaseMultiLayerUpdater.java:322-380)."""
+        gn = self.model.get("grad_norm")
+        if not gn:
+            return
+        mode = {"RenormalizeL2PerLayer": 1, "ClipL2PerLayer": 2, "ClipElementWiseAbsoluteValue": 3}.get(gn)
+        if mode is None:
+            raise NotImplementedError("gradient normalisation " + str(gn))
+        thr = float(self.model.get("grad_norm_threshold", 1.0))
+        spans = {}
+        for name, key, off, shp, pk in self.layout:  # a layer's parameters are contiguous in the flat vector
+            lo, hi = spans.get(name, (off, off))
+            spans[name] = (min(lo, off), max(hi, off + int(np.prod(shp))))
+        for name, (lo, hi) in spans.items():
+            self._call("dl4jb200_grad_normalize", self._ptr(self.grads, lo), hi - lo, mode, thr)
+
     def update_per_block(self):
         m = self.model
-        if m.get("grad_norm"):
-            raise NotImplementedError("gradient normalisation " + str(m["grad_norm"]))
+        self._grad_normalize()
         div = float(self.B * self.batch_div_scale) if m["minibatch"] else 1.0
         main = self._upd_args(m["updater"])
         bias = self._upd_args(m.get("bias_updater", m["updater"]))

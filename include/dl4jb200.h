@@ -262,6 +262,12 @@ int dl4jb200_copy2d(dl4jb200_ctx *ctx, const float *src, int src_ld, float *dst,
 int dl4jb200_updater_apply(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n, int kind, double lr,
                            double h1, double h2, double l1, double l2, double batch_div);
 
+/* Gradient normalisation of one layer's gradient view, in place, before the updater
+ * (BaseMultiLayerUpdater.preApply, NN/nn/updater/BaseMultiLayerUpdater.java:322-380). mode 1 RenormalizeL2PerLayer:
+ * g /= ||g||_2; mode 2 ClipL2PerLayer: g *= threshold/||g||_2 when the norm exceeds threshold; mode 3
+ * ClipElementWiseAbsoluteValue: clamp to [-threshold, threshold]. */
+int dl4jb200_grad_normalize(dl4jb200_ctx *ctx, float *g, size_t n, int mode, double threshold);
+
 /* All updater blocks of a network in ONE launch (BaseMultiLayerUpdater.update walks its UpdaterBlocks,
  * NN/nn/updater/BaseMultiLayerUpdater.java:223-309): the flat vectors w / g / state of n floats are split into nseg
  * segments; seg_start_dev[0..nseg] (device, int64, seg_start[nseg] == n) gives their bounds and seg_cfg_dev[s]

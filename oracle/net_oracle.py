@@ -155,8 +155,32 @@ class OracleNet:
                 reg += m["l1"] * np.abs(w).sum() + 0.5 * m["l2"] * (w * w).sum()
         return (self.loss + reg) / B
 
+    def grad_normalize(self):
+        # BaseMultiLayerUpdater.preApply, nn/updater/BaseMultiLayerUpdater.java:322-380 (per layer gradient view)
+        gn = self.model.get("grad_norm")
+        if not gn:
+            return
+        thr = float(self.model.get("grad_norm_threshold", 1.0))
+        spans = {}
+        for n, key, off, shp, pk in self.layout:
+            lo, hi = spans.get(n, (off, off))
+            spans[n] = (min(lo, off), max(hi, off + int(np.prod(shp))))
+        for n, (lo, hi) in spans.items():
+            g = self.grads[lo:hi]
+            l2 = float(np.sqrt((g.astype(np.float64) ** 2).sum()))
+            if gn == "RenormalizeL2PerLayer":
+                g /= np.float32(l2)
+            elif gn == "ClipL2PerLayer":
+                if l2 > thr:
+                    g *= np.float32(thr / l2)
+            elif gn == "ClipElementWiseAbsoluteValue":
+                np.clip(g, -thr, thr, out=g)
+            else:
+                raise NotImplementedError(gn)
+
     def update(self, B):
         m = self.model
+        self.grad_normalize()
         div = float(B) if m["minibatch"] else 1.0
         main, bias = self._upd(m["updater"]), self._upd(m.get("bias_updater", m["updater"]))
         ada = m["updater"]["kind"] == "adadelta"

@@ -188,3 +188,11 @@ def test_graph_replay_and_prefetch_match_eager():
             np.testing.assert_array_equal(net.params.cpu().numpy(), want)
         finally:
             net.close()
+
+
+def test_alexnet_step_parity_with_gradient_normalisation():
+    """AlexNet (zoo config, dropout off) at 64x64: Nesterovs with a separate bias updater, l2, miniBatch(false) and
+    RenormalizeL2PerLayer gradient normalisation, FP32 mode, two iterations."""
+    from deeplearning4j_b200 import _lib, zoo
+    m = zoo.alexnet(num_labels=10, input_shape=(3, 64, 64))
+    _run_case(m, 4, 10, _lib.ALGO_FP32, 2, False, 2e-4, 2e-4, 2e-4)
