@@ -15,6 +15,7 @@ NCHW, NHWC = 0, 1
 POOL_MAX, POOL_AVG, POOL_SUM, POOL_PNORM = 0, 1, 2, 3
 ACT_IDENTITY, ACT_RELU, ACT_SIGMOID, ACT_TANH, ACT_LEAKYRELU = 0, 1, 2, 3, 4
 ALGO_TC_TF32, ALGO_FP32 = 0, 1
+OPT_TF32_ACTIVATIONS = 1
 UPD_SGD, UPD_NESTEROVS, UPD_RMSPROP, UPD_ADADELTA, UPD_NOOP = 0, 1, 2, 3, 4
 
 
@@ -51,6 +52,7 @@ PROTOTYPES = {
     "dl4jb200_ctx_create": [_i, _vp, C.POINTER(_vp)],
     "dl4jb200_ctx_destroy": [_vp],
     "dl4jb200_ctx_set_stream": [_vp, _vp],
+    "dl4jb200_ctx_set_option": [_vp, _i, _i],
     "dl4jb200_ctx_sync": [_vp],
     "dl4jb200_malloc": [_vp, _sz, C.POINTER(_vp)],
     "dl4jb200_free": [_vp, _vp],

@@ -52,6 +52,7 @@ int dl4jb200_ctx_create(int device, void *stream, dl4jb200_ctx **out) {
     dl4jb200_ctx *c = new dl4jb200_ctx();
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
+    c->round_act = 0;
     for (int i = 0; i < 4; i++) { c->ws[i] = nullptr; c->ws_bytes[i] = 0; }
     if (stream) {
         c->stream = (cudaStream_t)stream;
@@ -73,6 +74,13 @@ int dl4jb200_ctx_destroy(dl4jb200_ctx *ctx) {
     for (int i = 0; i < 4; i++) if (ctx->ws[i]) cudaFree(ctx->ws[i]);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_ctx_set_option(dl4jb200_ctx *ctx, int option, int value) {
+    DL4J_REQUIRE(ctx, "ctx is NULL");
+    DL4J_REQUIRE(option == DL4JB200_OPT_TF32_ACTIVATIONS, "ctx_set_option: unknown option %d", option);
+    ctx->round_act = value ? 1 : 0;
     return DL4JB200_OK;
 }
 

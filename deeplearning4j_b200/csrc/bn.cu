@@ -265,6 +265,8 @@ template <int MODE>
 __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__ x, const float *__restrict__ e,
                                                        const float *__restrict__ mask_beta, float *__restrict__ out,
                                                        const float *__restrict__ coef, size_t total4, int cs, int act) {
+    const int rnd = act >> 8;  // host packs ctx->round_act above the activation code
+    act &= 0xff;
     const int Q = cs >> 2;
     size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += stride) {
@@ -291,7 +293,7 @@ __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__
             r.x = a.x * g.x + b.x * v.x + c.x; r.y = a.y * g.y + b.y * v.y + c.y;
             r.z = a.z * g.z + b.z * v.z + c.z; r.w = a.w * g.w + b.w * v.w + c.w;
         }
-        reinterpret_cast<float4 *>(out)[i] = r;
+        reinterpret_cast<float4 *>(out)[i] = dl4j_rnd4(r, rnd);
     }
 }
 
@@ -301,6 +303,8 @@ __global__ void __launch_bounds__(256) k_bn_apply_nchw(const float *__restrict__
                                                        const float *__restrict__ coef, size_t total, int C, int HW,
                                                        int act) {
     constexpr int V = VEC ? 4 : 1;
+    const int rnd = act >> 8;
+    act &= 0xff;
     size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i * V < total; i += stride) {
         size_t o = i * V;
@@ -331,6 +335,7 @@ __global__ void __launch_bounds__(256) k_bn_apply_nchw(const float *__restrict__
                 float g = (mask_beta && !(d * a + mb > 0.f)) ? 0.f : ev[j];
                 r[j] = a * g + b * d + c;
             }
+            r[j] = dl4j_rnd(r[j], rnd);
         }
         if (VEC) *reinterpret_cast<float4 *>(out + o) = make_float4(r[0], r[1 % V], r[2 % V], r[3 % V]);
         else out[o] = r[0];
@@ -414,11 +419,11 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
         p.cpad, (double)M, decay, eps, training, minibatch);
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
-        k_bn_apply_nhwc<0><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total / 4, cs, act);
+        k_bn_apply_nhwc<0><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total / 4, cs, act | (ctx->round_act << 8));
     } else {
         bool vec = (HW % 4 == 0) && al16(x) && al16(y);
-        if (vec) k_bn_apply_nchw<0, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total, C, HW, act);
-        else k_bn_apply_nchw<0, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total, C, HW, act);
+        if (vec) k_bn_apply_nchw<0, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total, C, HW, act | (ctx->round_act << 8));
+        else k_bn_apply_nchw<0, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total, C, HW, act | (ctx->round_act << 8));
     }
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
@@ -456,10 +461,10 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
                                                                                p.cpad, (double)M);
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
-        k_bn_apply_nhwc<1><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total / 4, cs, 0);
+        k_bn_apply_nhwc<1><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total / 4, cs, ctx->round_act << 8);
     } else {
-        if (vec) k_bn_apply_nchw<1, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total, C, HW, 0);
-        else k_bn_apply_nchw<1, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total, C, HW, 0);
+        if (vec) k_bn_apply_nchw<1, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total, C, HW, ctx->round_act << 8);
+        else k_bn_apply_nchw<1, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total, C, HW, ctx->round_act << 8);
     }
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
@@ -566,10 +571,10 @@ extern "C" int dl4jb200_bn_fwd_noalloc(dl4jb200_ctx *ctx, const float *x, float 
         (double)M, decay, eps, training, minibatch);
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
-        k_bn_apply_nhwc<0><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, coef, total / 4, cs, act);
+        k_bn_apply_nhwc<0><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, coef, total / 4, cs, act | (ctx->round_act << 8));
     } else {
-        if ((HW % 4 == 0) && al16(x) && al16(y)) k_bn_apply_nchw<0, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, coef, total, C, HW, act);
-        else k_bn_apply_nchw<0, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, coef, total, C, HW, act);
+        if ((HW % 4 == 0) && al16(x) && al16(y)) k_bn_apply_nchw<0, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, coef, total, C, HW, act | (ctx->round_act << 8));
+        else k_bn_apply_nchw<0, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, nullptr, nullptr, y, coef, total, C, HW, act | (ctx->round_act << 8));
     }
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;

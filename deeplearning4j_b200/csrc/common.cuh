@@ -20,6 +20,7 @@ struct dl4jb200_ctx {
     cudaStream_t stream;
     bool own_stream;
     int sm_count;
+    int round_act;  // DL4JB200_OPT_TF32_ACTIVATIONS: activation / epsilon producers store values rounded to TF32
     // scratch, grown on demand (never shrunk); slot 0: kernel partials / packed filters, slot 1: NHWC staging
     void *ws[4];
     size_t ws_bytes[4];
@@ -84,6 +85,19 @@ struct FastDiv {
         r = n - q * d;
     }
 };
+
+// round-to-nearest into TF32 (10-bit mantissa); used when the context stores activations TF32-representable so that the
+// tensor core's operand truncation becomes exact
+__device__ __forceinline__ float dl4j_tf32(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return __uint_as_float(r);
+}
+__device__ __forceinline__ float dl4j_rnd(float v, int rnd) { return rnd ? dl4j_tf32(v) : v; }
+__device__ __forceinline__ float4 dl4j_rnd4(float4 v, int rnd) {
+    if (rnd) { v.x = dl4j_tf32(v.x); v.y = dl4j_tf32(v.y); v.z = dl4j_tf32(v.z); v.w = dl4j_tf32(v.w); }
+    return v;
+}
 
 // activation codes shared by every epilogue (DL4JB200_ACT_*)
 __device__ __forceinline__ float dl4j_act(float z, int kind) {

@@ -198,7 +198,9 @@ int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     k_pack_filter<<<grid_for(ctx, (size_t)rows_p * g.Kp), 256, 0, ctx->stream>>>(w, wp, d->c_out, d->c_in, d->k_h, d->k_w, g.Cg,
                                                                                g.Kp, rows_p, 0, algo == DL4JB200_CONV_ALGO_TC_TF32, 0);
     DL4J_CHECK_LAUNCH();
-    if (algo == DL4JB200_CONV_ALGO_TC_TF32) rc = conv_tc_gemm(ctx, g, xs, wp, rows_p, bias, zs, d->c_out, z_cs, act);
+    // with DL4JB200_OPT_TF32_ACTIVATIONS an activated output (it feeds the next convolution directly) is stored rounded
+    const int act_code = act | ((ctx->round_act && act != DL4JB200_ACT_IDENTITY) ? 0x100 : 0);
+    if (algo == DL4JB200_CONV_ALGO_TC_TF32) rc = conv_tc_gemm(ctx, g, xs, wp, rows_p, bias, zs, d->c_out, z_cs, act_code);
     else rc = conv_ffma_gemm(ctx, g, xs, wp, bias, zs, d->c_out, z_cs, act);
     if (rc) return rc;
     if (z_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, zs, z, d->batch, d->c_out, d->out_h, d->out_w, z_cs);

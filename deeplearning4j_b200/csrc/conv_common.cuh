@@ -82,11 +82,7 @@ __device__ __forceinline__ void conv_tap_setup(const ConvGeom &g, int kh, int kw
     need = (1u << kh) | (1u << (16 + kw));
 }
 
-__device__ __forceinline__ float to_tf32_rna(float v) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
-    return __uint_as_float(r);
-}
+__device__ __forceinline__ float to_tf32_rna(float v) { return dl4j_tf32(v); }
 
 // host helpers implemented in conv.cu
 ConvGeom conv_geom_fwd(const dl4jb200_conv_desc *d, int x_cs);

@@ -46,14 +46,14 @@ __global__ void __launch_bounds__(256) k_stem_wgrad_finalize(const float *__rest
 
 // NCHW image -> row-packed NHWC4: dst[b][y][x_off + x][c], c < C <= 4 (padding columns / channel 3 untouched: keep them zero)
 __global__ void __launch_bounds__(256) k_nchw_to_rowpack4(const float *__restrict__ src, float *__restrict__ dst, int B, int C, int H,
-                                                          int W, int row_pitch_px, int x_off) {
+                                                          int W, int row_pitch_px, int x_off, int rnd) {
     size_t total = (size_t)B * H * W, stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
         int x = (int)(i % W);
         size_t t = i / W;
         int y = (int)(t % H), b = (int)(t / H);
         float v[4] = {0.f, 0.f, 0.f, 0.f};
-        for (int c = 0; c < C; c++) v[c] = src[(((size_t)b * C + c) * H + y) * W + x];
+        for (int c = 0; c < C; c++) v[c] = dl4j_rnd(src[(((size_t)b * C + c) * H + y) * W + x], rnd);
         *reinterpret_cast<float4 *>(dst + (((size_t)b * H + y) * row_pitch_px + x_off + x) * 4) = make_float4(v[0], v[1], v[2], v[3]);
     }
 }
@@ -85,7 +85,7 @@ int dl4jb200_nchw_to_rowpack4(dl4jb200_ctx *ctx, const float *src, float *dst, i
     DL4J_REQUIRE(C >= 1 && C <= 4 && B > 0 && H > 0 && W > 0 && x_off >= 0 && x_off + W <= row_pitch_px, "nchw_to_rowpack4: bad shape");
     size_t total = (size_t)B * H * W;
     size_t blocks = (total + 255) / 256, cap = (size_t)ctx->sm_count * 16;
-    k_nchw_to_rowpack4<<<(int)(blocks > cap ? cap : blocks), 256, 0, ctx->stream>>>(src, dst, B, C, H, W, row_pitch_px, x_off);
+    k_nchw_to_rowpack4<<<(int)(blocks > cap ? cap : blocks), 256, 0, ctx->stream>>>(src, dst, B, C, H, W, row_pitch_px, x_off, ctx->round_act);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
@@ -113,7 +113,8 @@ int dl4jb200_conv_rowpack_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, co
     t.div_Wm = FastDiv((uint32_t)d->out_w); t.div_HWm = FastDiv((uint32_t)(d->out_h * d->out_w));
     t.div_Cg = FastDiv(32u); t.div_kW = FastDiv(1u);
     t.remap = 0; t.rm_sy = t.rm_sx = 1; t.rm_H = d->out_h; t.rm_W = d->out_w;
-    return conv_tc_gemm_tma_raw(ctx, tmA, tmB, t, bias, z, d->c_out, z_cs, act, bn);
+    const int act_code = act | ((ctx->round_act && act != DL4JB200_ACT_IDENTITY) ? 0x100 : 0);
+    return conv_tc_gemm_tma_raw(ctx, tmA, tmB, t, bias, z, d->c_out, z_cs, act_code, bn);
 }
 
 int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px,

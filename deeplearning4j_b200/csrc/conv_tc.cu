@@ -186,6 +186,8 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restric
                                                           const float *__restrict__ bias, float *__restrict__ out,
                                                           ConvGeom g, int n_valid, int out_cs, int act) {
     using L = SmemLayout<BN, STAGES>;
+    const int rnd = act >> 8;  // bit 8: store the activated output rounded to TF32 (ctx->round_act)
+    act &= 0xff;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
@@ -294,6 +296,10 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restric
 #pragma unroll
                     for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);  // static indices keep v[] in registers
                 }
+                if (rnd) {
+#pragma unroll
+                    for (int e = 0; e < 32; e++) v[e] = dl4j_tf32(v[e]);
+                }
                 store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
             } else if (m < g.M) {
 #pragma unroll
@@ -303,7 +309,7 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm(const float *__restric
                     float r[4];
 #pragma unroll
                     for (int e = 0; e < 4; e++)
-                        r[e] = n + e < n_valid ? dl4j_act(v[q * 4 + e] + bias_s[cb * 32 + q * 4 + e], act) : 0.f;
+                        r[e] = n + e < n_valid ? dl4j_rnd(dl4j_act(v[q * 4 + e] + bias_s[cb * 32 + q * 4 + e], act), rnd) : 0.f;
                     *reinterpret_cast<float4 *>(orow + n) = make_float4(r[0], r[1], r[2], r[3]);
                 }
             }
@@ -474,6 +480,8 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
                                                               const float *__restrict__ bias, float *__restrict__ out,
                                                               TmaGemmGeom g, int n_valid, int out_cs, int act) {
     using L = SmemLayout<BN, STAGES>;
+    const int rnd = act >> 8;
+    act &= 0xff;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
@@ -546,6 +554,10 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
 #pragma unroll
                     for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);  // static indices keep v[] in registers
                 }
+                if (rnd) {
+#pragma unroll
+                    for (int e = 0; e < 32; e++) v[e] = dl4j_tf32(v[e]);
+                }
                 store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
             } else if (m < g.M) {
 #pragma unroll
@@ -555,7 +567,7 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
                     float r4[4];
 #pragma unroll
                     for (int e = 0; e < 4; e++)
-                        r4[e] = n + e < n_valid ? dl4j_act(v[q * 4 + e] + bias_s[cb * 32 + q * 4 + e], act) : 0.f;
+                        r4[e] = n + e < n_valid ? dl4j_rnd(dl4j_act(v[q * 4 + e] + bias_s[cb * 32 + q * 4 + e], act), rnd) : 0.f;
                     *reinterpret_cast<float4 *>(orow + n) = make_float4(r4[0], r4[1], r4[2], r4[3]);
                 }
             }
@@ -608,6 +620,8 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                                                                           int n_valid, int out_cs, int act, int n_tiles,
                                                                           int total_tiles) {
     using L = PersistSmem<BN, STAGES>;
+    const int rnd = act >> 8;
+    act &= 0xff;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
@@ -732,6 +746,10 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
 #pragma unroll
                         for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);  // static indices keep v[] in registers
                     }
+                    if (rnd) {
+#pragma unroll
+                        for (int e = 0; e < 32; e++) v[e] = dl4j_tf32(v[e]);
+                    }
                     if (REMAP) store_tile_32x32_rows(stage_smem, v, lane, out, rowoff, nb);
                     else store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
                 } else if (m < g.M) {
@@ -751,7 +769,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
 #pragma unroll
                         for (int e = 0; e < 4; e++) {
                             const int nn = n + e;
-                            r4[e] = nn < n_valid ? dl4j_act(v[q * 4 + e] + (bias ? __ldg(bias + nn) : 0.f), act) : 0.f;
+                            r4[e] = nn < n_valid ? dl4j_rnd(dl4j_act(v[q * 4 + e] + (bias ? __ldg(bias + nn) : 0.f), act), rnd) : 0.f;
                         }
                         *reinterpret_cast<float4 *>(orow + n) = make_float4(r4[0], r4[1], r4[2], r4[3]);
                     }

@@ -15,7 +15,7 @@ static inline int ew_grid(dl4jb200_ctx *ctx, size_t work_items, int threads) {
 // One block transposes a 32(channels) x 32(pixels) tile of one image through shared memory so that both
 // the global read (contiguous pixels) and the global write (contiguous channels) are coalesced.
 __global__ void __launch_bounds__(256) k_nchw_to_nhwc(const float *__restrict__ src, float *__restrict__ dst, int C,
-                                                      int HW, int cs) {
+                                                      int HW, int cs, int rnd) {
     __shared__ float tile[32][33];
     int b = blockIdx.z;
     int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(256) k_nchw_to_nhwc(const float *__restrict__ 
 #pragma unroll
     for (int i = 0; i < 4; i++) {
         int p = p0 + ty + i * 8, c = c0 + tx;
-        if (p < HW && c < cs) d[(size_t)p * cs + c] = tile[tx][ty + i * 8];
+        if (p < HW && c < cs) d[(size_t)p * cs + c] = dl4j_rnd(tile[tx][ty + i * 8], rnd);
     }
 }
 
@@ -58,23 +58,23 @@ __global__ void __launch_bounds__(256) k_nhwc_to_nchw(const float *__restrict__ 
 
 // ---------------------------------------------------------------- activations
 template <bool VEC>
-__global__ void __launch_bounds__(256) k_act_fwd(const float *__restrict__ z, float *__restrict__ a, size_t n, int act) {
+__global__ void __launch_bounds__(256) k_act_fwd(const float *__restrict__ z, float *__restrict__ a, size_t n, int act, int rnd) {
     size_t stride = (size_t)gridDim.x * blockDim.x, i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (VEC) {
         size_t n4 = n >> 2;
         for (; i < n4; i += stride) {
             float4 v = reinterpret_cast<const float4 *>(z)[i];
             v.x = dl4j_act(v.x, act); v.y = dl4j_act(v.y, act); v.z = dl4j_act(v.z, act); v.w = dl4j_act(v.w, act);
-            reinterpret_cast<float4 *>(a)[i] = v;
+            reinterpret_cast<float4 *>(a)[i] = dl4j_rnd4(v, rnd);
         }
     } else {
-        for (; i < n; i += stride) a[i] = dl4j_act(z[i], act);
+        for (; i < n; i += stride) a[i] = dl4j_rnd(dl4j_act(z[i], act), rnd);
     }
 }
 
 template <bool VEC>
 __global__ void __launch_bounds__(256) k_act_bwd(const float *__restrict__ z, const float *__restrict__ e,
-                                                 float *__restrict__ d, size_t n, int act) {
+                                                 float *__restrict__ d, size_t n, int act, int rnd) {
     size_t stride = (size_t)gridDim.x * blockDim.x, i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (VEC) {
         size_t n4 = n >> 2;
@@ -82,16 +82,16 @@ __global__ void __launch_bounds__(256) k_act_bwd(const float *__restrict__ z, co
             float4 v = reinterpret_cast<const float4 *>(z)[i], g = reinterpret_cast<const float4 *>(e)[i];
             g.x *= dl4j_act_grad(v.x, act); g.y *= dl4j_act_grad(v.y, act);
             g.z *= dl4j_act_grad(v.z, act); g.w *= dl4j_act_grad(v.w, act);
-            reinterpret_cast<float4 *>(d)[i] = g;
+            reinterpret_cast<float4 *>(d)[i] = dl4j_rnd4(g, rnd);
         }
     } else {
-        for (; i < n; i += stride) d[i] = e[i] * dl4j_act_grad(z[i], act);
+        for (; i < n; i += stride) d[i] = dl4j_rnd(e[i] * dl4j_act_grad(z[i], act), rnd);
     }
 }
 
 template <bool VEC>
 __global__ void __launch_bounds__(256) k_add_act(const float *__restrict__ a, const float *__restrict__ b,
-                                                 float *__restrict__ o, size_t n, int act) {
+                                                 float *__restrict__ o, size_t n, int act, int rnd) {
     size_t stride = (size_t)gridDim.x * blockDim.x, i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (VEC) {
         size_t n4 = n >> 2;
@@ -99,10 +99,10 @@ __global__ void __launch_bounds__(256) k_add_act(const float *__restrict__ a, co
             float4 x = reinterpret_cast<const float4 *>(a)[i], y = reinterpret_cast<const float4 *>(b)[i];
             x.x = dl4j_act(x.x + y.x, act); x.y = dl4j_act(x.y + y.y, act);
             x.z = dl4j_act(x.z + y.z, act); x.w = dl4j_act(x.w + y.w, act);
-            reinterpret_cast<float4 *>(o)[i] = x;
+            reinterpret_cast<float4 *>(o)[i] = dl4j_rnd4(x, rnd);
         }
     } else {
-        for (; i < n; i += stride) o[i] = dl4j_act(a[i] + b[i], act);
+        for (; i < n; i += stride) o[i] = dl4j_rnd(dl4j_act(a[i] + b[i], act), rnd);
     }
 }
 
@@ -110,7 +110,8 @@ static inline bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 
 // ---------------------------------------------------------------- softmax + NLL (one warp per row)
 __global__ void __launch_bounds__(256) k_softmax_nll(const float *__restrict__ z, int z_ld, const float *__restrict__ labels,
-                                                     float *__restrict__ delta, int d_ld, float *loss_rows, int B, int K) {
+                                                     float *__restrict__ delta, int d_ld, float *loss_rows, int B, int K,
+                                                     int rnd) {
     int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= B) return;
     const float *zr = z + (size_t)row * z_ld;
@@ -124,7 +125,7 @@ __global__ void __launch_bounds__(256) k_softmax_nll(const float *__restrict__ z
     float logs = logf(s), loss = 0.f, inv = 1.f / s;
     for (int k = lane; k < K; k += 32) {
         float zz = zr[k] - m, l = lr[k];
-        delta[(size_t)row * d_ld + k] = expf(zz) * inv - l;
+        delta[(size_t)row * d_ld + k] = dl4j_rnd(expf(zz) * inv - l, rnd);
         if (l != 0.f) loss -= l * (zz - logs);
     }
     for (int k = K + lane; k < d_ld; k += 32) delta[(size_t)row * d_ld + k] = 0.f;
@@ -396,7 +397,7 @@ int dl4jb200_nchw_to_nhwc(dl4jb200_ctx *ctx, const float *src, float *dst, int B
     DL4J_REQUIRE(B <= 65535, "nchw_to_nhwc: batch > 65535");
     int HW = H * W;
     dim3 grid(dl4j_ceil_div(HW, 32), dl4j_ceil_div(cs, 32), B);
-    k_nchw_to_nhwc<<<grid, 256, 0, ctx->stream>>>(src, dst, C, HW, cs);
+    k_nchw_to_nhwc<<<grid, 256, 0, ctx->stream>>>(src, dst, C, HW, cs, ctx->round_act);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
@@ -417,9 +418,9 @@ int dl4jb200_act_fwd(dl4jb200_ctx *ctx, const float *z, float *a, size_t n, int 
     if (act < 0 || act > DL4JB200_ACT_LEAKYRELU) { dl4j_set_error("act_fwd: activation %d not handled by the helper", act); return DL4JB200_NOT_SUPPORTED; }
     if (n == 0) return DL4JB200_OK;
     if ((n & 3) == 0 && aligned16(z) && aligned16(a))
-        k_act_fwd<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(z, a, n, act);
+        k_act_fwd<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(z, a, n, act, ctx->round_act);
     else
-        k_act_fwd<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(z, a, n, act);
+        k_act_fwd<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(z, a, n, act, ctx->round_act);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
@@ -429,9 +430,9 @@ int dl4jb200_act_bwd(dl4jb200_ctx *ctx, const float *z, const float *eps, float 
     if (act < 0 || act > DL4JB200_ACT_LEAKYRELU) { dl4j_set_error("act_bwd: activation %d not handled by the helper", act); return DL4JB200_NOT_SUPPORTED; }
     if (n == 0) return DL4JB200_OK;
     if ((n & 3) == 0 && aligned16(z) && aligned16(eps) && aligned16(delta))
-        k_act_bwd<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(z, eps, delta, n, act);
+        k_act_bwd<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(z, eps, delta, n, act, ctx->round_act);
     else
-        k_act_bwd<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(z, eps, delta, n, act);
+        k_act_bwd<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(z, eps, delta, n, act, ctx->round_act);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
@@ -440,9 +441,9 @@ int dl4jb200_add_act_fwd(dl4jb200_ctx *ctx, const float *a, const float *b, floa
     DL4J_REQUIRE(ctx && a && b && out, "add_act_fwd: NULL argument");
     if (n == 0) return DL4JB200_OK;
     if ((n & 3) == 0 && aligned16(a) && aligned16(b) && aligned16(out))
-        k_add_act<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(a, b, out, n, act);
+        k_add_act<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(a, b, out, n, act, ctx->round_act);
     else
-        k_add_act<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(a, b, out, n, act);
+        k_add_act<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(a, b, out, n, act, ctx->round_act);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
@@ -457,7 +458,7 @@ int dl4jb200_softmax_nll(dl4jb200_ctx *ctx, const float *z, int z_ld, const floa
     DL4J_REQUIRE(B > 0 && K > 0 && z_ld >= K && delta_ld >= K, "softmax_nll: bad shape");
     float *rows = (float *)dl4j_workspace(ctx, 0, (size_t)B * sizeof(float));
     if (!rows) return DL4JB200_ERR_CUDA;
-    k_softmax_nll<<<dl4j_ceil_div(B, 8), 256, 0, ctx->stream>>>(z, z_ld, labels, delta, delta_ld, rows, B, K);
+    k_softmax_nll<<<dl4j_ceil_div(B, 8), 256, 0, ctx->stream>>>(z, z_ld, labels, delta, delta_ld, rows, B, K, ctx->round_act);
     DL4J_CHECK_LAUNCH();
     k_sum_rows<<<1, 256, 0, ctx->stream>>>(rows, loss_sum_out, B);
     DL4J_CHECK_LAUNCH();

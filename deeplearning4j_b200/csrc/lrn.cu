@@ -7,6 +7,7 @@
 struct LrnGeom {
     int B, C, H, W, cs, halfN;
     float k, alpha, beta;
+    int rnd;  // ctx->round_act
 };
 
 template <bool NHWC>
@@ -35,7 +36,7 @@ __global__ void __launch_bounds__(256) k_lrn_fwd(const float *__restrict__ x, fl
         float s = 0.f;
         for (int j = j0; j <= j1; j++) { float v = x[base + (size_t)j * cst]; s += v * v; }
         float u = g.k + g.alpha * s;
-        y[idx] = x[idx] * powf(u, -g.beta);
+        y[idx] = dl4j_rnd(x[idx] * powf(u, -g.beta), g.rnd);
     }
 }
 
@@ -59,7 +60,7 @@ __global__ void __launch_bounds__(256) k_lrn_bwd(const float *__restrict__ x, co
             size_t o = base + (size_t)j * cst;
             R += x[o] * powf(u, -g.beta) * e[o];
         }
-        dx[idx] = e[idx] * powf(uc, -g.beta) - 2.f * g.alpha * g.beta * x[idx] * R / uc;
+        dx[idx] = dl4j_rnd(e[idx] * powf(uc, -g.beta) - 2.f * g.alpha * g.beta * x[idx] * R / uc, g.rnd);
     }
 }
 
@@ -69,7 +70,7 @@ static int lrn_geom(int B, int C, int H, int W, int layout, int cs, double k, do
     DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "%s: unknown layout %d", who, layout);
     DL4J_REQUIRE(layout == DL4JB200_NCHW || cs >= C, "%s: cs < C", who);
     DL4J_REQUIRE(n >= 1, "%s: n must be >= 1", who);
-    g = LrnGeom{B, C, H, W, layout == DL4JB200_NHWC ? cs : C, (int)n / 2, (float)k, (float)alpha, (float)beta};
+    g = LrnGeom{B, C, H, W, layout == DL4JB200_NHWC ? cs : C, (int)n / 2, (float)k, (float)alpha, (float)beta, 0};
     return DL4JB200_OK;
 }
 
@@ -86,6 +87,7 @@ int dl4jb200_lrn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, int B, int C, 
     LrnGeom g;
     int rc = lrn_geom(B, C, H, W, layout, cs, k, n, alpha, beta, g, "lrn_fwd");
     if (rc) return rc;
+    g.rnd = ctx->round_act;
     size_t total = (size_t)B * H * W * g.cs;
     if (layout == DL4JB200_NHWC) k_lrn_fwd<true><<<lrn_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, g, total);
     else k_lrn_fwd<false><<<lrn_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, g, total);
@@ -99,6 +101,7 @@ int dl4jb200_lrn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, float 
     LrnGeom g;
     int rc = lrn_geom(B, C, H, W, layout, cs, k, n, alpha, beta, g, "lrn_bwd");
     if (rc) return rc;
+    g.rnd = ctx->round_act;
     size_t total = (size_t)B * H * W * g.cs;
     if (layout == DL4JB200_NHWC) k_lrn_bwd<true><<<lrn_grid(ctx, total), 256, 0, ctx->stream>>>(x, eps, dx, g, total);
     else k_lrn_bwd<false><<<lrn_grid(ctx, total), 256, 0, ctx->stream>>>(x, eps, dx, g, total);

@@ -12,6 +12,7 @@ struct PoolGeom {
     int xcs, ycs;  // NHWC pixel strides
     FastDiv d_sH, d_sW;            // stride divisions of the backward gather
     FastDiv d_q, d_w, d_h, d_c;    // index decode of the tensor the kernel enumerates (set per launch)
+    int rnd;                       // store outputs rounded to TF32 (ctx->round_act)
 };
 
 template <int V>
@@ -94,9 +95,9 @@ __global__ void __launch_bounds__(256) k_pool_fwd(const float *__restrict__ x, f
         Vec<V> out;
 #pragma unroll
         for (int i = 0; i < V; i++) {
-            if (type == DL4JB200_POOL_AVG) out.v[i] = acc[i] / (float)(g.kH * g.kW);
-            else if (type == DL4JB200_POOL_PNORM) out.v[i] = powf(acc[i], 1.f / (float)pnorm);
-            else out.v[i] = acc[i];
+            if (type == DL4JB200_POOL_AVG) out.v[i] = dl4j_rnd(acc[i] / (float)(g.kH * g.kW), g.rnd);
+            else if (type == DL4JB200_POOL_PNORM) out.v[i] = dl4j_rnd(powf(acc[i], 1.f / (float)pnorm), g.rnd);
+            else out.v[i] = dl4j_rnd(acc[i], g.rnd);  // no-op when the producer already rounded (idempotent)
         }
         size_t o = offs<NHWC>(b, c, oh, ow, g.C, g.Ho, g.Wo, g.ycs);
         vstore<V>(y + o, out);
@@ -187,7 +188,8 @@ __global__ void __launch_bounds__(256) k_pool_bwd(const float *__restrict__ x, c
         }
         Vec<V> out;
 #pragma unroll
-        for (int i = 0; i < V; i++) out.v[i] = type == DL4JB200_POOL_AVG ? acc[i] / (float)(g.kH * g.kW) : acc[i];
+        for (int i = 0; i < V; i++)
+            out.v[i] = dl4j_rnd(type == DL4JB200_POOL_AVG ? acc[i] / (float)(g.kH * g.kW) : acc[i], g.rnd);
         vstore<V>(dx + offs<NHWC>(b, c, h, w, g.C, g.H, g.W, g.xcs), out);
     }
 }
@@ -219,7 +221,7 @@ __global__ void __launch_bounds__(256, 4) k_maxpool_bwd_nhwc_fast(const float *_
                 acc.z += a.z == me ? e.z : 0.f; acc.w += a.w == me ? e.w : 0.f;
             }
         }
-        *reinterpret_cast<float4 *>(dx + (((size_t)b * g.H + h) * g.W + w) * g.xcs + c) = acc;
+        *reinterpret_cast<float4 *>(dx + (((size_t)b * g.H + h) * g.W + w) * g.xcs + c) = dl4j_rnd4(acc, g.rnd);
     }
 }
 
@@ -252,6 +254,7 @@ int dl4jb200_pool_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     DL4J_REQUIRE(ctx && x && y, "pool_fwd: NULL argument");
     PoolGeom g;
     int rc = pool_geom(d, layout, x_cs, y_cs, g, "pool_fwd");
+    g.rnd = ctx->round_act;
     if (rc) return rc;
     DL4J_REQUIRE(pool_type >= DL4JB200_POOL_MAX && pool_type <= DL4JB200_POOL_PNORM, "pool_fwd: unknown pooling type %d", pool_type);
     DL4J_REQUIRE(pool_type != DL4JB200_POOL_PNORM || pnorm >= 1, "pool_fwd: pnorm must be >= 1");
@@ -274,6 +277,7 @@ int dl4jb200_pool_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     DL4J_REQUIRE(ctx && eps && dx, "pool_bwd: NULL argument");
     PoolGeom g;
     int rc = pool_geom(d, layout, x_cs, y_cs, g, "pool_bwd");
+    g.rnd = ctx->round_act;
     if (rc) return rc;
     if (pool_type == DL4JB200_POOL_SUM) {  // SubsamplingLayer.java:251-253 throws; the helper declines
         dl4j_set_error("pool_bwd: SUM pooling has no backprop in the reference");

@@ -25,7 +25,7 @@ def _r4(n):
 
 
 class Network:
-    def __init__(self, model, batch, device=0, algo=_lib.ALGO_TC_TF32, params=None, with_score=True):
+    def __init__(self, model, batch, device=0, algo=_lib.ALGO_TC_TF32, params=None, with_score=True, round_tf32=None):
         import torch
         self.torch = torch
         self.model, self.B, self.algo, self.with_score = model, int(batch), algo, with_score
@@ -42,6 +42,11 @@ class Network:
         h2 = C.c_void_p()
         _lib.call("dl4jb200_ctx_create", device, C.c_void_p(self.side_stream.cuda_stream), C.byref(h2))
         self.h2 = h2
+        # TF32 mode: producers store activations / epsilons TF32-representable, so the tensor cores' operand truncation
+        # is exact and the whole step sees one unbiased rounding per stored value (include/dl4jb200.h, ctx_set_option)
+        self.round_tf32 = (algo == _lib.ALGO_TC_TF32) if round_tf32 is None else bool(round_tf32)
+        for ctx in (h, h2):
+            _lib.call("dl4jb200_ctx_set_option", ctx, _lib.OPT_TF32_ACTIVATIONS, int(self.round_tf32))
         self.overlap_wgrad = True
         self.launches = 0
         self.prof, self.prof_fns, self._cur = None, set(), None

@@ -100,6 +100,14 @@ unsigned long long dl4jb200_launch_count(void);
 int dl4jb200_ctx_create(int device, void *stream, dl4jb200_ctx **out);
 int dl4jb200_ctx_destroy(dl4jb200_ctx *ctx);
 int dl4jb200_ctx_set_stream(dl4jb200_ctx *ctx, void *stream);
+/* Options. DL4JB200_OPT_TF32_ACTIVATIONS (default 0): every kernel that PRODUCES a tensor a convolution will consume
+ * (re-layout of the minibatch, BN / activation / add / pooling outputs forward and backward, softmax delta, and the
+ * outputs of convolutions with a fused activation) stores it rounded-to-nearest into TF32. The tensor cores truncate
+ * fp32 operands to TF32; with representable operands that truncation is exact, so the only TF32 error left is one
+ * unbiased rounding per stored value (2^-12 relative) instead of a biased truncation per product. Meant to be
+ * switched on together with DL4JB200_CONV_ALGO_TC_TF32; leave it off for FP32 parity runs. */
+#define DL4JB200_OPT_TF32_ACTIVATIONS 1
+int dl4jb200_ctx_set_option(dl4jb200_ctx *ctx, int option, int value);
 void *dl4jb200_ctx_stream(dl4jb200_ctx *ctx);
 int dl4jb200_ctx_sync(dl4jb200_ctx *ctx);
 /* bytes of internal scratch (split-K partials, BN partial sums, packed filters) currently held */

@@ -38,6 +38,8 @@ public class Dl4jB200 {
     public static native int dl4jb200_ctx_create(int device, Pointer stream, @Cast("dl4jb200_ctx**") PointerPointer out);
     public static native int dl4jb200_ctx_destroy(@Cast("dl4jb200_ctx*") Pointer ctx);
     public static native int dl4jb200_ctx_sync(@Cast("dl4jb200_ctx*") Pointer ctx);
+    public static final int OPT_TF32_ACTIVATIONS = 1;
+    public static native int dl4jb200_ctx_set_option(@Cast("dl4jb200_ctx*") Pointer ctx, int option, int value);
     public static native int dl4jb200_buf_register(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host, long bytes,
                     @Cast("void**") PointerPointer deviceOut);
     public static native int dl4jb200_buf_upload(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host);

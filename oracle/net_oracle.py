@@ -6,6 +6,13 @@ epsilon fan-in; nn/updater/BaseMultiLayerUpdater.java:223-309; optimize/solvers/
 The model dict and the flat parameter layout are passed in by the caller (tests / bench); nothing here is
 imported by the product package. fast=True runs the reference's literal im2col + BLAS sgemm + col2im pipeline in
 fp32 (the form timed as the CPU baseline); fast=False runs the direct double-accumulate form (parity oracle).
+
+tf32=True additionally restates the OPERAND QUANTISATION of the CUDA path's TF32 mode (include/dl4jb200.h,
+DL4JB200_OPT_TF32_ACTIVATIONS): filters are rounded to nearest TF32 when packed, convolution operands are truncated to
+TF32 by the tensor core, and every producer of a tensor that a convolution consumes stores it rounded to nearest TF32.
+All arithmetic stays the reference's; only those quantisation points are added, so the TF32 path can be checked at
+fp32-accumulation tolerance instead of at "TF32 is ~1e-3 per layer" tolerance. `unrounded` names the vertices whose
+output the CUDA path never materialises (a BatchNormalization folded into the following Add).
 """
 import numpy as np
 
@@ -16,9 +23,24 @@ _MODE = {"Strict": o.STRICT, "Truncate": o.TRUNCATE, "Same": o.SAME}
 _POOL = {"MAX": o.POOL_MAX, "AVG": o.POOL_AVG, "PNORM": o.POOL_PNORM}
 
 
+def tf32_round(a):
+    """cvt.rna.tf32.f32: round the magnitude to 10 explicit mantissa bits, ties away from zero."""
+    u = np.ascontiguousarray(a, np.float32).view(np.uint32)
+    return ((u + np.uint32(0x1000)) & np.uint32(0xFFFFE000)).view(np.float32)
+
+
+def tf32_trunc(a):
+    """What tcgen05.mma kind::tf32 does to an fp32 operand: the low 13 mantissa bits are ignored."""
+    u = np.ascontiguousarray(a, np.float32).view(np.uint32)
+    return (u & np.uint32(0xFFFFE000)).view(np.float32)
+
+
 class OracleNet:
-    def __init__(self, model, layout, P, params, fast=False):
+    def __init__(self, model, layout, P, params, fast=False, tf32=False, unrounded=()):
         self.model, self.layout, self.P, self.fast = model, layout, P, fast
+        self.tf32, self.unrounded = bool(tf32), set(unrounded)
+        self._q = tf32_round if tf32 else (lambda a: a)   # producer-side store
+        self._t = tf32_trunc if tf32 else (lambda a: a)   # tensor-core operand fetch
         self.params = np.ascontiguousarray(params, np.float32).copy()
         self.grads = np.zeros(P, np.float32)
         k = model["updater"]["kind"]
@@ -38,7 +60,7 @@ class OracleNet:
         for v in m["vertices"]:
             n, op = v["name"], v["op"]
             if op == "input":
-                act[n] = np.ascontiguousarray(x, np.float32)
+                act[n] = self._q(np.ascontiguousarray(x, np.float32))
                 continue
             a = act[v["in"][0]]
             if op == "zeropad":
@@ -46,34 +68,36 @@ class OracleNet:
                 act[n] = np.pad(a, ((0, 0), (0, 0), (t, b), (l, r)))
             elif op == "conv":
                 f = o.conv_fwd_im2col if self.fast else o.conv_fwd
-                z = f(a, self._p(n, "W"), self._p(n, "b"), stride=v["stride"], pad=v["pad"], dilation=v["dilation"],
-                      mode=_MODE[v["mode"]])
-                act[n] = o.act_fwd(z, _ACT[v["act"]]) if v["act"] != "identity" else z
+                z = f(self._t(a), self._q(self._p(n, "W")), self._p(n, "b"), stride=v["stride"], pad=v["pad"],
+                      dilation=v["dilation"], mode=_MODE[v["mode"]])
+                act[n] = self._q(o.act_fwd(z, _ACT[v["act"]])) if v["act"] != "identity" else z
             elif op == "bn":
                 y, mean, std = o.bn_fwd(a, self._p(n, "gamma"), self._p(n, "beta"), self._p(n, "mean"), self._p(n, "var"),
                                         v["decay"], v["eps"], train, m["minibatch"])
                 self.bn_saved[n] = (mean, std, y)
-                act[n] = o.act_fwd(y, _ACT[v["act"]]) if v["act"] != "identity" else y
+                y = o.act_fwd(y, _ACT[v["act"]]) if v["act"] != "identity" else y
+                act[n] = y if n in self.unrounded else self._q(y)
             elif op == "pool":
-                act[n] = o.pool_fwd(a, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]])
+                act[n] = self._q(o.pool_fwd(a, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]]))
             elif op == "add":
                 s = a + act[v["in"][1]]
-                act[n] = o.act_fwd(s, _ACT[v["act"]]) if v["act"] != "identity" else s
+                act[n] = self._q(o.act_fwd(s, _ACT[v["act"]]) if v["act"] != "identity" else s)
             elif op == "act":
-                act[n] = o.act_fwd(a, _ACT[v["act"]])
+                act[n] = self._q(o.act_fwd(a, _ACT[v["act"]]))
             elif op == "flatten":
                 act[n] = a.reshape(a.shape[0], -1)
             elif op in ("dense", "output"):
                 if self.fast:
-                    z = a @ self._p(n, "W").T + self._p(n, "b")[None, :]
+                    z = self._t(a) @ self._q(self._p(n, "W")).T + self._p(n, "b")[None, :]
                 else:
-                    z = o.dense_fwd(a, self._p(n, "W"), self._p(n, "b"))
+                    z = o.dense_fwd(self._t(a), self._q(self._p(n, "W")), self._p(n, "b"))
                 if op == "dense":
-                    act[n] = o.act_fwd(z, _ACT[v["act"]]) if v["act"] != "identity" else z
+                    act[n] = self._q(o.act_fwd(z, _ACT[v["act"]])) if v["act"] != "identity" else z
                 else:
                     act[n] = z
                     if labels is not None:
                         self.loss, self.probs, self.delta = o.softmax_nll(z, labels)
+                        self.delta = self._q(self.delta)
             else:
                 raise NotImplementedError(op)
         self.act = act
@@ -100,19 +124,23 @@ class OracleNet:
                 t, b, l, r = v["pad"]
                 give(u, np.ascontiguousarray(e[:, :, t:e.shape[2] - b, l:e.shape[3] - r]))
             elif op == "conv":
-                d = o.act_bwd(act[n], e, _ACT[v["act"]]) if v["act"] == "relu" else e
+                d = self._q(o.act_bwd(act[n], e, _ACT[v["act"]])) if v["act"] == "relu" else e
                 f = o.conv_bwd_im2col if self.fast else o.conv_bwd
-                dw, db, dx = f(act[u], self._p(n, "W"), d, stride=v["stride"], pad=v["pad"], dilation=v["dilation"],
-                               mode=_MODE[v["mode"]])
+                dw, db, dx = f(self._t(act[u]), self._q(self._p(n, "W")), self._t(d), stride=v["stride"], pad=v["pad"],
+                               dilation=v["dilation"], mode=_MODE[v["mode"]])
+                if self.tf32:  # the bias gradient is a plain fp32 column sum of the stored delta, no tensor core
+                    db = d.sum(axis=(0, 2, 3), dtype=np.float64).astype(np.float32)
                 self._p(n, "W", self.grads)[...] = dw
                 self._p(n, "b", self.grads)[...] = db
                 give(u, dx)
             elif op in ("dense", "output"):
-                d = o.act_bwd(act[n], e, _ACT[v["act"]]) if (op == "dense" and v["act"] == "relu") else e
+                d = self._q(o.act_bwd(act[n], e, _ACT[v["act"]])) if (op == "dense" and v["act"] == "relu") else e
                 if self.fast:
-                    dwf, db, dx = d.T @ act[u], d.sum(0), d @ self._p(n, "W")
+                    dwf, db, dx = self._t(d).T @ self._t(act[u]), d.sum(0), self._t(d) @ self._q(self._p(n, "W"))
                 else:
-                    dwf, db, dx = o.dense_bwd(act[u], self._p(n, "W"), d)
+                    dwf, db, dx = o.dense_bwd(self._t(act[u]), self._q(self._p(n, "W")), self._t(d))
+                    if self.tf32:
+                        db = d.sum(axis=0, dtype=np.float64).astype(np.float32)
                 self._p(n, "W", self.grads)[...] = dwf
                 self._p(n, "b", self.grads)[...] = db
                 give(u, dx)
@@ -124,15 +152,15 @@ class OracleNet:
                 self._p(n, "beta", self.grads)[...] = dbt
                 self._p(n, "mean", self.grads)[...] = 0  # BatchNormalization.java:205-208
                 self._p(n, "var", self.grads)[...] = 0
-                give(u, dx)
+                give(u, self._q(dx))
             elif op == "pool":
-                give(u, o.pool_bwd(act[u], e, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]]))
+                give(u, self._q(o.pool_bwd(act[u], e, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]])))
             elif op in ("add", "act"):
-                d = o.act_bwd(act[n], e, _ACT[v["act"]]) if v["act"] == "relu" else e
+                d = self._q(o.act_bwd(act[n], e, _ACT[v["act"]])) if v["act"] == "relu" else e
                 for uu in v["in"]:
                     give(uu, d)
             elif op == "flatten":
-                give(u, e.reshape(act[u].shape))
+                give(u, self._q(e.reshape(act[u].shape)))  # the CUDA path re-lays the epsilon out (a producer store)
             else:
                 raise NotImplementedError(op)
 

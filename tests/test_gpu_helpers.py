@@ -19,6 +19,7 @@ pytestmark = pytest.mark.gpu
 TOL_BW = 1e-5
 TOL_CONV_FP32 = 1e-4
 TOL_CONV_TF32 = 2e-3
+TOL_CONV_TF32_QUANTISED = 1e-5  # TF32 path vs the oracle on identically quantised operands (fp32 accumulation order only)
 
 
 @pytest.fixture(scope="module")
@@ -86,6 +87,16 @@ def test_conv_forward_backward_vs_oracle(H, ctx, oracle, case, algo_name):
     assert rel_err(wview, dwr) <= tol, ("dW", rel_err(wview, dwr))
     assert rel_err(bview.ravel(), dbr) <= max(tol, 1e-5), ("db", rel_err(bview.ravel(), dbr))
     assert rel_err(eps_next, dxr) <= tol, ("dx", rel_err(eps_next, dxr))
+    if algo_name == "tf32":
+        # The whole TF32 deviation above is OPERAND QUANTISATION: filters are rounded to nearest TF32 when packed, the
+        # tensor core ignores the low 13 mantissa bits of activations / deltas. Against the oracle fed operands
+        # quantised the same way the tcgen05 path is an fp32-accumulate convolution to ~1e-6.
+        from oracle.net_oracle import tf32_round, tf32_trunc
+        zq = oracle.conv_fwd(tf32_trunc(x), tf32_round(w), b, stride=s, pad=p, dilation=d, mode=mode)
+        assert rel_err(z, zq) <= TOL_CONV_TF32_QUANTISED, ("z vs quantised oracle", rel_err(z, zq))
+        dwq, _, dxq = oracle.conv_bwd(tf32_trunc(x), tf32_round(w), tf32_trunc(delta), stride=s, pad=p, dilation=d, mode=mode)
+        assert rel_err(wview, dwq) <= TOL_CONV_TF32_QUANTISED, ("dW vs quantised oracle", rel_err(wview, dwq))
+        assert rel_err(eps_next, dxq) <= TOL_CONV_TF32_QUANTISED, ("dx vs quantised oracle", rel_err(eps_next, dxq))
 
 
 def test_conv_golden_contained(H, ctx):
@@ -120,6 +131,52 @@ def test_conv_no_bias_and_fused_activation(H, ctx, oracle):
                 got = from_nhwc(dev.get(pz, (2, 6, 6, 16)), 16)
                 assert rel_err(got, oracle.act_fwd(zr, kind)) <= tol
     finally:
+        dev.free()
+
+
+def test_tf32_activation_rounding_option(H, ctx, oracle):
+    """DL4JB200_OPT_TF32_ACTIVATIONS: producers store round-to-nearest TF32 values (== tf32_round of the plain output);
+    a fused-activation convolution does too, a plain preOutput (feeds BatchNormalization) does not."""
+    from deeplearning4j_b200 import _lib
+    from oracle.net_oracle import tf32_round
+    rng = np.random.default_rng(11)
+    x = rng.standard_normal((2, 8, 6, 6)).astype(np.float32)
+    w = (rng.standard_normal((16, 8, 3, 3)) * 0.2).astype(np.float32)
+    d = H.conv_desc(x.shape, 16, (3, 3), (1, 1), (1, 1), (1, 1), "Truncate")
+    dev = Dev(ctx)
+    n = x.size
+
+    def run(opt):
+        _lib.call("dl4jb200_ctx_set_option", ctx.handle, _lib.OPT_TF32_ACTIVATIONS, opt)
+        out = {}
+        px, pw = dev.put(x), dev.put(w)
+        pn = dev.empty(n * 4)
+        _lib.call("dl4jb200_nchw_to_nhwc", ctx.handle, px, pn, 2, 8, 6, 6, 8)
+        out["relayout"] = dev.get(pn, (n,))
+        pa = dev.empty(n * 4)
+        _lib.call("dl4jb200_act_fwd", ctx.handle, px, pa, n, H.ACTIVATIONS["tanh"])
+        out["tanh"] = dev.get(pa, (n,))
+        ps = dev.empty(n * 4)
+        _lib.call("dl4jb200_add_act_fwd", ctx.handle, px, pw, ps, n, H.ACTIVATIONS["relu"])
+        out["add_relu"] = dev.get(ps, (n,))
+        for act in ("identity", "relu"):
+            pz = dev.empty(2 * 6 * 6 * 16 * 4)
+            _lib.call("dl4jb200_conv_fwd", ctx.handle, C.byref(d), pn, H.NHWC, 8, pw, None, pz, H.NHWC, 16,
+                      H.ACTIVATIONS[act], H.ALGO_TC_TF32)
+            out["conv_" + act] = dev.get(pz, (2 * 6 * 6 * 16,))
+        return out
+
+    try:
+        plain, rounded = run(0), run(1)
+        for k in ("relayout", "tanh", "add_relu"):
+            np.testing.assert_array_equal(rounded[k], tf32_round(plain[k]))
+            assert (plain[k].view(np.uint32) & 0x1FFF).any()
+        assert not (rounded["conv_relu"].view(np.uint32) & 0x1FFF).any()
+        assert (rounded["conv_identity"].view(np.uint32) & 0x1FFF).any()
+        with pytest.raises(Exception):
+            _lib.call("dl4jb200_ctx_set_option", ctx.handle, 99, 1)
+    finally:
+        _lib.call("dl4jb200_ctx_set_option", ctx.handle, _lib.OPT_TF32_ACTIVATIONS, 0)
         dev.free()
 
 

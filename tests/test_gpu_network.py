@@ -116,6 +116,38 @@ def test_vgg_like_step_parity():
     _run_case(m, 4, 10, _lib.ALGO_TC_TF32, 1, True, 2e-1, 2e-1, 5e-3)
 
 
+@pytest.mark.parametrize("which", ["lenet", "tiny_resnet", "vgg32"])
+def test_tf32_forward_chain_against_quantised_oracle(which):
+    """TF32 mode stores activations TF32-representable (DL4JB200_OPT_TF32_ACTIVATIONS), so the oracle can restate its
+    operand quantisation exactly (OracleNet(tf32=True)): what is left between the two forward chains is fp32 summation
+    order plus isolated one-ulp rounding flips, and the score agrees an order of magnitude tighter than against the
+    unquantised reference arithmetic (scripts/tf32_parity.py prints both)."""
+    from deeplearning4j_b200 import _lib, network, zoo
+    from oracle.net_oracle import OracleNet
+    model, B, fast = {"lenet": (zoo.lenet(), 16, False), "tiny_resnet": (_tiny_resnet(), 8, False),
+                      "vgg32": (zoo.vgg16(num_labels=10, input_shape=(3, 32, 32)), 4, True)}[which]
+    P, layout = zoo.param_layout(model)
+    p0 = zoo.init_params(model)
+    x, lab = _data(model, B, 10)
+    net = network.Network(model, B, algo=_lib.ALGO_TC_TF32, params=p0)
+    try:
+        assert net.round_tf32
+        ref = OracleNet(model, layout, P, p0, fast=fast, tf32=True, unrounded=net.fused_bn.keys())
+        s_ref = ref.fit(x, lab)
+        s = net.fit(x, lab)
+        net.sync()
+        s = float(s.cpu()[0])
+        assert abs(s - s_ref) <= 1e-4 * max(1.0, abs(s_ref)), (s, s_ref)
+        # every stored activation is TF32-representable (low 13 mantissa bits clear)
+        for v in model["vertices"]:
+            n = v["name"]
+            if v["op"] in ("pool", "add", "act", "bn") and n not in net.fused_bn:
+                a = net.output_host(n)
+                assert not (a.view(np.uint32) & 0x1FFF).any(), n
+    finally:
+        net.close()
+
+
 def test_resnet50_step_parity_small_batch():
     """The BASELINE model itself (224x224, 1000 classes) at batch 4 against the im2col+BLAS CPU pipeline."""
     # At batch 4 this untrained 53-BN-layer graph is ill-conditioned: the CPU pipeline in fp32 (im2col + sgemm)
