@@ -313,4 +313,49 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     return DL4JB200_OK;
 }
 
+// Backprop-data with the consumer-side bookkeeping of the vertex that owns dx folded into the GEMM epilogue:
+//   dx = relu'(act_out) * (conv_bwd_data(delta) + eps_sum)
+// (ComputationGraph.java:2044-2063 epsilon fan-in, then ActivationLayer.java:68-92 / the Add vertex' ReLU backprop).
+int dl4jb200_conv_bwd_data_fused(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *w, const float *delta, int delta_cs,
+                                 float *dx, int dx_cs, const float *eps_sum, const float *act_out, int act, int algo) {
+    DL4J_REQUIRE(ctx && w && delta && dx, "conv_bwd_data_fused: NULL argument");
+    DL4J_REQUIRE(act == DL4JB200_ACT_IDENTITY || act == DL4JB200_ACT_RELU, "conv_bwd_data_fused: only identity / relu masks");
+    DL4J_REQUIRE(act == DL4JB200_ACT_IDENTITY || act_out, "conv_bwd_data_fused: relu needs act_out");
+    int rc = check_desc(d, "conv_bwd_data_fused");
+    if (rc) return rc;
+    if ((rc = check_layout(DL4JB200_NHWC, delta_cs, d->c_out, delta, "conv_bwd_data_fused", "delta"))) return rc;
+    if ((rc = check_layout(DL4JB200_NHWC, dx_cs, d->c_in, dx, "conv_bwd_data_fused", "dx"))) return rc;
+    DL4J_REQUIRE(algo == DL4JB200_CONV_ALGO_TC_TF32 || algo == DL4JB200_CONV_ALGO_FP32, "conv_bwd_data_fused: unknown algo %d", algo);
+    const float *mask = act == DL4JB200_ACT_RELU ? act_out : nullptr;
+    const size_t n = (size_t)d->batch * d->in_h * d->in_w * dx_cs;
+    const bool strided_1x1 = d->k_h == 1 && d->k_w == 1 && (d->stride_h > 1 || d->stride_w > 1);
+    ConvGeom gb = conv_geom_bwd_data(d, delta_cs);
+    gb.use_tma = algo == DL4JB200_CONV_ALGO_TC_TF32 && conv_tc_gemm_can_tma(gb);
+    if (!gb.use_tma || strided_1x1 || (!eps_sum && !mask)) {
+        // no fused epilogue on this path: plain backprop-data into scratch, then one fused elementwise pass
+        float *tmp = dx;
+        if (eps_sum || mask) {
+            tmp = (float *)dl4j_workspace(ctx, 3, n * sizeof(float));
+            if (!tmp) return DL4JB200_ERR_CUDA;
+        }
+        // (x is not read when dw == db == NULL; pass delta to satisfy the argument check)
+        if ((rc = dl4jb200_conv_bwd(ctx, d, dx, DL4JB200_NHWC, dx_cs, w, delta, DL4JB200_NHWC, delta_cs, nullptr, nullptr, tmp,
+                                    DL4JB200_NHWC, dx_cs, algo)))
+            return rc;
+        if (tmp == dx) return DL4JB200_OK;
+        if (eps_sum) return dl4jb200_eps_sum_act_bwd(ctx, tmp, eps_sum, mask ? mask : tmp, dx, n, mask ? DL4JB200_ACT_RELU : DL4JB200_ACT_IDENTITY);
+        return dl4jb200_act_bwd(ctx, mask, tmp, dx, n, DL4JB200_ACT_RELU);
+    }
+    DL4J_REQUIRE(delta_cs >= gb.Cg, "conv_bwd_data_fused: delta pixel stride %d < %d", delta_cs, gb.Cg);
+    const int rows_b = dl4j_round_up(dx_cs > d->c_in ? dx_cs : d->c_in, 256);
+    const size_t pack_f = (size_t)rows_b * gb.Kp;
+    float *wb = (float *)dl4j_workspace(ctx, 0, pack_f * sizeof(float));
+    if (!wb) return DL4JB200_ERR_CUDA;
+    k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, 1, 1);
+    DL4J_CHECK_LAUNCH();
+    gb.epi_add = eps_sum;
+    gb.epi_mask = mask;
+    return conv_tc_gemm(ctx, gb, delta, wb, rows_b, nullptr, dx, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY | (ctx->round_act ? 0x100 : 0));
+}
+
 }  // extern "C"

@@ -19,6 +19,8 @@ struct ConvGeom {
     int use_tma;            // operands fetched by TMA (im2col mode); backprop-data then needs the filter packed tap-flipped
     int remap, rm_sy, rm_sx, rm_H, rm_W;  // output-row scatter (see TmaGemmGeom)
     FastDiv div_Wm, div_HWm, div_Cg, div_kW;
+    // fused epsilon fan-in + activation backprop of the persistent TMA kernel's epilogue (see TmaGemmGeom)
+    const float *epi_add = nullptr, *epi_mask = nullptr;
 };
 
 // tap/channel of a K index (k % 4 == 0 in all callers)

@@ -142,6 +142,50 @@ __device__ __forceinline__ void store_tile_32x32(uint32_t stage_smem, const floa
     }
 }
 
+// Same as store_tile_32x32 with the fused backprop epilogue: t = (t + add) * (mask > 0), optionally rounded to TF32.
+__device__ __forceinline__ void store_tile_32x32_fused(uint32_t stage_smem, const float (&v)[32], int lane, size_t off_base,
+                                                       size_t row_stride, int rows_valid, float *out,
+                                                       const float *__restrict__ add, const float *__restrict__ mask, int rnd) {
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        const uint32_t a = stage_smem + (uint32_t)lane * 128u + (uint32_t)((q ^ (lane & 7)) << 4);
+        asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v[q * 4]), "f"(v[q * 4 + 1]), "f"(v[q * 4 + 2]),
+                     "f"(v[q * 4 + 3]) : "memory");
+    }
+    __syncwarp();
+    const int c = lane & 7;
+    float4 ad[8], mk[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {  // issue all global reads first: 16 independent 128-bit loads in flight per lane
+        const int row = 4 * i + (lane >> 3);
+        const size_t o = off_base + (size_t)row * row_stride + c * 4;
+        ad[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        mk[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (row < rows_valid) {
+            if (add) ad[i] = *reinterpret_cast<const float4 *>(add + o);
+            if (mask) mk[i] = __ldg(reinterpret_cast<const float4 *>(mask + o));
+        }
+    }
+    // keep the consumers (mask compares) behind ALL sixteen loads: folded next to its own load, each compare would
+    // stall the in-order issue for a full DRAM latency before the next load leaves the SM
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        asm volatile("" : "+f"(mk[i].x), "+f"(mk[i].y), "+f"(mk[i].z), "+f"(mk[i].w));
+        asm volatile("" : "+f"(ad[i].x), "+f"(ad[i].y), "+f"(ad[i].z), "+f"(ad[i].w));
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int row = 4 * i + (lane >> 3);
+        float4 t;
+        const uint32_t a = stage_smem + (uint32_t)row * 128u + (uint32_t)((c ^ (row & 7)) << 4);
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(a));
+        t.x = mk[i].x > 0.f ? t.x + ad[i].x : 0.f; t.y = mk[i].y > 0.f ? t.y + ad[i].y : 0.f;
+        t.z = mk[i].z > 0.f ? t.z + ad[i].z : 0.f; t.w = mk[i].w > 0.f ? t.w + ad[i].w : 0.f;
+        if (row < rows_valid) *reinterpret_cast<float4 *>(out + off_base + (size_t)row * row_stride + c * 4) = dl4j_rnd4(t, rnd);
+    }
+}
+
 // Same, but every row has its own destination (element offset from `out`, or < 0 to skip): output-row scatter.
 __device__ __forceinline__ void store_tile_32x32_rows(uint32_t stage_smem, const float (&v)[32], int lane, float *out,
                                                       const long long (&rowoff)[8], int col0) {
@@ -596,19 +640,19 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
 }
 
 // ------------------------------------------------------------------------------------------------
-// Persistent form of the TMA-fed GEMM: one CTA per SM loops over output tiles. Six warps: 0-3 epilogue, 4 MMA issuer,
-// 5 TMA producer. The accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i (TMEM ->
+// Persistent form of the TMA-fed GEMM: one CTA per SM loops over output tiles. Ten warps: 0-3 and 6-9 epilogue, 4 MMA
+// issuer, 5 TMA producer. The accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i (TMEM ->
 // registers -> staging smem -> coalesced global stores) overlaps the TMA loads and MMAs of tile i+1, and the operand
 // pipeline never drains between tiles. This is what the small-K 1x1 convolutions need: their per-tile main loop is
 // only 2-8 K-chunks long, so set-up, drain and epilogue dominated the one-tile-per-CTA kernel.
-constexpr int PTHREADS = 192;
+constexpr int PTHREADS = 320;
 
 template <int BN, int STAGES>
 struct PersistSmem {
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 4;
     static constexpr int B_BYTES = BN * BLOCK_K * 4;
-    static constexpr int STAGING_OFF = STAGES * (A_BYTES + B_BYTES);  // 4 warps x 4 KB epilogue staging
-    static constexpr int BAR_OFF = STAGING_OFF + 4 * 4096;
+    static constexpr int STAGING_OFF = STAGES * (A_BYTES + B_BYTES);  // 8 warps x 4 KB epilogue staging
+    static constexpr int BAR_OFF = STAGING_OFF + 8 * 4096;
     static constexpr int BYTES = BAR_OFF + 256 + 1024;
 };
 
@@ -622,6 +666,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
     using L = PersistSmem<BN, STAGES>;
     const int rnd = act >> 8;
     act &= 0xff;
+    const bool fused = !REMAP && (g.epi_add != nullptr || g.epi_mask != nullptr);
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
@@ -636,7 +681,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
         tma::prefetch_desc(&tmA);
         tma::prefetch_desc(&tmB);
         for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int b = 0; b < 2; b++) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 128); }
+        for (int b = 0; b < 2; b++) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 256); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 4) tmem_alloc<2 * BN>(tmem_slot);
@@ -696,20 +741,23 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
             __syncwarp();
         }
     } else {
-        // ------------------------------ epilogue warps 0-3
-        const uint32_t stage_smem = base + L::STAGING_OFF + warp * 4096u;
+        // ------------------------------ epilogue: warps 0-3 take the even 32-column chunks of a tile, warps 6-9 the odd
+        // ones (a warp may only read the TMEM lane quadrant warp % 4, so each quadrant gets two warps). Twice the
+        // loads / stores in flight per SM: the epilogue of the HBM-bound layers is latency-, not issue-limited.
+        const int quad = warp & 3, grp = warp >= 6 ? 1 : 0;
+        const uint32_t stage_smem = base + L::STAGING_OFF + (uint32_t)(grp * 4 + quad) * 4096u;
         int i = 0;
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
             const int buf = i & 1;
             const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * BN;
             const bool full_n = n0 + BN <= n_valid;
-            const int m = m0 + warp * 32 + lane;
-            const int rows_valid = g.M - (m0 + warp * 32);
+            const int m = m0 + quad * 32 + lane;
+            const int rows_valid = g.M - (m0 + quad * 32);
             long long rowoff[8];
             if (REMAP) {
 #pragma unroll
                 for (int r8 = 0; r8 < 8; r8++) {
-                    const int mm = m0 + warp * 32 + 4 * r8 + (lane >> 3);
+                    const int mm = m0 + quad * 32 + 4 * r8 + (lane >> 3);
                     rowoff[r8] = -1;
                     if (mm < g.M) {
                         uint32_t img, rr, oy, ox;
@@ -719,14 +767,34 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                     }
                 }
             }
+            if (fused && grp == 0) {
+                // pull the epilogue's extra operands of the NEXT tile of this CTA (and, on the first pass, of this one)
+                // into L2 now: one bulk prefetch per row and tensor, a whole tile of lead time
+                for (int tp = (i == 0 ? t : t + (int)gridDim.x); tp <= t + (int)gridDim.x && tp < total_tiles; tp += gridDim.x) {
+                    const int pm = (tp / n_tiles) * BLOCK_M + quad * 32 + lane, pn = (tp % n_tiles) * BN;
+                    if (pm < g.M) {
+                        const size_t o = (size_t)pm * out_cs + pn;
+                        const uint32_t bytes = (uint32_t)(min(BN, out_cs - pn) * 4);
+                        if (g.epi_add) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(g.epi_add + o), "r"(bytes) : "memory");
+                        if (g.epi_mask) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(g.epi_mask + o), "r"(bytes) : "memory");
+                    }
+                }
+            }
             mbar_wait(tfull_bar(buf), (i >> 1) & 1);
             tc_fence_after();
-            const uint32_t acc = tmem_d + (uint32_t)(buf * BN) + ((uint32_t)(warp * 32) << 16);
+            const uint32_t acc = tmem_d + (uint32_t)(buf * BN) + ((uint32_t)(quad * 32) << 16);
+            constexpr int NCB = BN / 32;
+            if (grp >= NCB) {  // BN == 32: one chunk only, the second warp group just keeps the barrier phase moving
+                tc_fence_before();
+                mbar_arrive(tempty_bar(buf));
+                continue;
+            }
+            const int cb_last = NCB == 1 ? 0 : ((NCB - 1 - grp) & ~1) + grp;  // last chunk of this group's parity
 #pragma unroll 1
-            for (int cb = 0; cb < BN / 32; cb++) {
+            for (int cb = grp; cb < NCB; cb += (NCB == 1 ? 1 : 2)) {
                 float v[32];
                 tmem_ld32(acc + (uint32_t)(cb * 32), v);
-                if (cb == BN / 32 - 1) {  // last TMEM read of this tile: hand the accumulator back to the MMA warp
+                if (cb == cb_last) {  // last TMEM read of this warp in this tile: hand the accumulator back to the MMA warp
                     tc_fence_before();
                     mbar_arrive(tempty_bar(buf));
                 }
@@ -746,12 +814,15 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
 #pragma unroll
                         for (int e = 0; e < 32; e++) v[e] = dl4j_act(v[e], act);  // static indices keep v[] in registers
                     }
-                    if (rnd) {
+                    if (rnd && !fused) {
 #pragma unroll
                         for (int e = 0; e < 32; e++) v[e] = dl4j_tf32(v[e]);
                     }
                     if (REMAP) store_tile_32x32_rows(stage_smem, v, lane, out, rowoff, nb);
-                    else store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + warp * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
+                    else if (fused)
+                        store_tile_32x32_fused(stage_smem, v, lane, (size_t)(m0 + quad * 32) * out_cs + nb, (size_t)out_cs, rows_valid,
+                                               out, g.epi_add, g.epi_mask, rnd);
+                    else store_tile_32x32(stage_smem, v, lane, out + (size_t)(m0 + quad * 32) * out_cs + nb, (size_t)out_cs, rows_valid);
                 } else if (m < g.M) {
                     long long ro = (long long)m * out_cs;
                     if (REMAP) {
@@ -769,7 +840,12 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
 #pragma unroll
                         for (int e = 0; e < 4; e++) {
                             const int nn = n + e;
-                            r4[e] = nn < n_valid ? dl4j_rnd(dl4j_act(v[q * 4 + e] + (bias ? __ldg(bias + nn) : 0.f), act), rnd) : 0.f;
+                            float val = dl4j_act(v[q * 4 + e] + (bias ? __ldg(bias + nn) : 0.f), act);
+                            if (fused && nn < n_valid) {
+                                if (g.epi_add) val += g.epi_add[ro + nn];
+                                if (g.epi_mask && !(g.epi_mask[ro + nn] > 0.f)) val = 0.f;
+                            }
+                            r4[e] = nn < n_valid ? dl4j_rnd(val, rnd) : 0.f;
                         }
                         *reinterpret_cast<float4 *>(orow + n) = make_float4(r4[0], r4[1], r4[2], r4[3]);
                     }
@@ -1034,6 +1110,11 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
     t.M = g.M; t.num_k = g.Kp / tc::BLOCK_K; t.kW = g.kW; t.dH = g.dH; t.dW = g.dW; t.sH = sH; t.sW = sW; t.lowH = lowH; t.lowW = lowW;
     t.div_Wm = g.div_Wm; t.div_HWm = g.div_HWm; t.div_Cg = g.div_Cg; t.div_kW = g.div_kW;
     t.remap = g.remap; t.rm_sy = g.rm_sy; t.rm_sx = g.rm_sx; t.rm_H = g.rm_H; t.rm_W = g.rm_W;
+    t.epi_add = g.epi_add; t.epi_mask = g.epi_mask;
+    if ((g.epi_add || g.epi_mask) && (g.remap || !aligned_bias)) {
+        dl4j_set_error("conv_tc_gemm_tma: fused epilogue needs the unscattered persistent kernel");
+        return DL4JB200_ERR_INVALID_ARG;
+    }
     if (g.remap && !aligned_bias) { dl4j_set_error("conv_tc_gemm_tma: row scatter needs the persistent kernel"); return DL4JB200_ERR_INVALID_ARG; }
     if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
     if (!aligned_bias) {  // the persistent epilogue reads the bias with 128-bit loads

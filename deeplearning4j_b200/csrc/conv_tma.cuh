@@ -42,6 +42,11 @@ struct TmaGemmGeom {
     // optional output-row scatter: GEMM row (b, oy, ox) is stored at pixel (b, oy*rm_sy, ox*rm_sx) of an rm_H x rm_W image
     // (backprop-data of a strided 1x1 convolution computed on the compact pixel set; the rest of dx is pre-zeroed)
     int remap, rm_sy, rm_sx, rm_H, rm_W;
+    // optional fused epilogue of a backprop-data GEMM, both laid out exactly like `out`:
+    //   out = (acc + epi_add) masked by epi_mask > 0
+    // i.e. the ComputationGraph epsilon fan-in sum followed by the ReLU backprop of the vertex that owns `out`
+    // (epi_add may alias out: every element is read and written by the same thread)
+    const float *epi_add = nullptr, *epi_mask = nullptr;
 };
 struct TmaWgradGeom {
     int M, kW, dH, dW, sH, sW, lowH, lowW, Kp;

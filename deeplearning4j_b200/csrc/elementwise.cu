@@ -106,6 +106,26 @@ __global__ void __launch_bounds__(256) k_add_act(const float *__restrict__ a, co
     }
 }
 
+// epsilon fan-in + activation backprop in one pass: d = (a + b) * act'(y)
+template <bool VEC>
+__global__ void __launch_bounds__(256) k_sum_act_bwd(const float *__restrict__ a, const float *__restrict__ b,
+                                                     const float *__restrict__ y, float *__restrict__ d, size_t n, int act,
+                                                     int rnd) {
+    size_t stride = (size_t)gridDim.x * blockDim.x, i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (VEC) {
+        size_t n4 = n >> 2;
+        for (; i < n4; i += stride) {
+            float4 p = reinterpret_cast<const float4 *>(a)[i], q = reinterpret_cast<const float4 *>(b)[i];
+            float4 v = reinterpret_cast<const float4 *>(y)[i];
+            p.x = (p.x + q.x) * dl4j_act_grad(v.x, act); p.y = (p.y + q.y) * dl4j_act_grad(v.y, act);
+            p.z = (p.z + q.z) * dl4j_act_grad(v.z, act); p.w = (p.w + q.w) * dl4j_act_grad(v.w, act);
+            reinterpret_cast<float4 *>(d)[i] = dl4j_rnd4(p, rnd);
+        }
+    } else {
+        for (; i < n; i += stride) d[i] = dl4j_rnd((a[i] + b[i]) * dl4j_act_grad(y[i], act), rnd);
+    }
+}
+
 static inline bool aligned16(const void *p) { return ((uintptr_t)p & 15) == 0; }
 
 // ---------------------------------------------------------------- softmax + NLL (one warp per row)
@@ -444,6 +464,19 @@ int dl4jb200_add_act_fwd(dl4jb200_ctx *ctx, const float *a, const float *b, floa
         k_add_act<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(a, b, out, n, act, ctx->round_act);
     else
         k_add_act<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(a, b, out, n, act, ctx->round_act);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_eps_sum_act_bwd(dl4jb200_ctx *ctx, const float *a, const float *b, const float *act_out, float *delta, size_t n,
+                             int act) {
+    DL4J_REQUIRE(ctx && a && b && act_out && delta, "eps_sum_act_bwd: NULL argument");
+    if (act < 0 || act > DL4JB200_ACT_LEAKYRELU) { dl4j_set_error("eps_sum_act_bwd: activation %d not handled by the helper", act); return DL4JB200_NOT_SUPPORTED; }
+    if (n == 0) return DL4JB200_OK;
+    if ((n & 3) == 0 && aligned16(a) && aligned16(b) && aligned16(act_out) && aligned16(delta))
+        k_sum_act_bwd<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(a, b, act_out, delta, n, act, ctx->round_act);
+    else
+        k_sum_act_bwd<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(a, b, act_out, delta, n, act, ctx->round_act);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }

@@ -48,6 +48,7 @@ class Network:
         for ctx in (h, h2):
             _lib.call("dl4jb200_ctx_set_option", ctx, _lib.OPT_TF32_ACTIVATIONS, int(self.round_tf32))
         self.overlap_wgrad = True
+        self.fuse_dgrad = True  # epsilon fan-in + ReLU backprop in the backprop-data epilogue (_emit_dgrad)
         self.launches = 0
         self.prof, self.prof_fns, self._cur = None, set(), None
         self.batch_div_scale = 1  # data-parallel replicas: global minibatch = scale * B (parallel.py)
@@ -345,6 +346,7 @@ class Network:
         if self.out.get(u, 0) is None:  # flatten alias: pass straight through to its input
             return self._emit(self.vmap[u]["in"][0], fn)
         e = self._eps_buf(u)
+        self._contrib[u] = self._contrib.get(u, 0) + 1
         if u not in self._written:
             fn(self._ptr(e))
             self._written.add(u)
@@ -362,6 +364,36 @@ class Network:
         if self.out.get(u, 0) is None:
             return self._lend(self.vmap[u]["in"][0], tensor)
         self._borrowed.setdefault(u, []).append(tensor)
+        self._contrib[u] = self._contrib.get(u, 0) + 1
+
+    def _emit_dgrad(self, u, d, pw, e, n, x, xcs):
+        """Backprop-data of convolution n into the epsilon of its input u. When this is the LAST contribution u will
+        receive and u is an Add / Activation vertex with ReLU, the fan-in sum and u's ReLU backprop ride in the GEMM
+        epilogue (dl4jb200_conv_bwd_data_fused) instead of running as an accumulate + act_bwd pass each."""
+        L = _lib
+        if not self._needs_eps(u):
+            return
+        while self.out.get(u, 0) is None:  # flatten alias
+            u = self.vmap[u]["in"][0]
+            if not self._needs_eps(u):
+                return
+        uv = self.vmap[u]
+        lent = self._borrowed.get(u, [])
+        last = self._contrib.get(u, 0) + 1 == len(self.consumers[u])
+        fusable = (self.fuse_dgrad and last and uv["op"] in ("add", "act") and uv.get("act") == "relu"
+                   and not (u in self._written and lent) and len(lent) <= 1)
+        if not fusable:
+            return self._emit(u, lambda dx: self._call(
+                "dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
+                None, None, dx, L.NHWC, xcs, self.algo))
+        dst = self._eps_buf(u)
+        prior = self._ptr(dst) if u in self._written else (self._ptr(lent[0]) if lent else None)
+        self._call("dl4jb200_conv_bwd_data_fused", C.byref(d), pw, self._ptr(e), self.cs[n], self._ptr(dst), xcs, prior,
+                   self._ptr(self.out[u]), L.ACT_RELU, self.algo)
+        self._written.add(u)
+        self._borrowed.pop(u, None)
+        self._contrib[u] = self._contrib.get(u, 0) + 1
+        self._delta_done.add(u)
 
     def _resolve(self, n):
         lent = self._borrowed.get(n, [])
@@ -383,6 +415,7 @@ class Network:
     def backward(self):
         L, B = _lib, self.B
         self._written, self._borrowed = set(), {}
+        self._contrib, self._delta_done = {}, set()
         self._side_used = False
         for v in reversed(self.model["vertices"]):
             n, op = v["name"], v["op"]
@@ -417,10 +450,7 @@ class Network:
                 else:
                     wcall("dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
                           gw, gb, None, L.NHWC, xcs, self.algo)
-                    if self._needs_eps(src):
-                        self._emit(src, lambda dx, d=d, x=x, xcs=xcs, pw=pw, e=e, n=n: self._call(
-                            "dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
-                            None, None, dx, L.NHWC, xcs, self.algo))
+                    self._emit_dgrad(src, d, pw, e, n, x, xcs)
             elif op == "bn":
                 u = v["in"][0]
                 x, xcs = self._src(u)
@@ -438,7 +468,7 @@ class Network:
                 self._emit(u, lambda dx: self._call("dl4jb200_pool_bwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), self._ptr(e), am,
                                                     dx, L.NHWC, xcs, self.cs[n], _POOL[v["type"]], int(v.get("pnorm", 2)), 1e-8))
             elif op in ("add", "act"):
-                if v["act"] != "identity":
+                if v["act"] != "identity" and n not in self._delta_done:
                     self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(), _ACT[v["act"]])
                 for u in v["in"]:
                     self._lend(u, e)

@@ -249,6 +249,17 @@ int dl4jb200_lrn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, float 
 /* ElementWiseVertex Add (+ following ActivationLayer ReLU): out = act(a + b); backward mask from out.
  * NN/nn/graph/vertex/impl/ElementWiseVertex.java:81-86,126-131; NN/nn/layers/ActivationLayer.java:68-92 */
 int dl4jb200_add_act_fwd(dl4jb200_ctx *ctx, const float *a, const float *b, float *out, size_t n, int act);
+/* Epsilon fan-in and activation backprop of one vertex in a single pass: delta = act'(act_out) * (a + b)
+ * (NN/nn/graph/ComputationGraph.java:2044-2063 followed by NN/nn/layers/ActivationLayer.java:68-92). In place allowed. */
+int dl4jb200_eps_sum_act_bwd(dl4jb200_ctx *ctx, const float *a, const float *b, const float *act_out, float *delta, size_t n,
+                             int act);
+/* The same bookkeeping folded into the epilogue of the backprop-data GEMM that produces the LAST contribution to a
+ * vertex' epsilon: dx = act'(act_out) * (conv_bwd_data(delta) + eps_sum). NHWC only; eps_sum may be NULL or alias dx;
+ * act is IDENTITY (act_out ignored) or RELU. Where the tensor-core TMA path cannot take the epilogue (FP32 algo, the
+ * compact strided-1x1 walk) the same result is produced by plain backprop-data into scratch + eps_sum_act_bwd.
+ * Replaces: ConvolutionLayer.backpropGradient's epsNext (ConvolutionLayer.java:205-216) + the two calls above. */
+int dl4jb200_conv_bwd_data_fused(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *w, const float *delta, int delta_cs,
+                                 float *dx, int dx_cs, const float *eps_sum, const float *act_out, int act, int algo);
 /* ComputationGraph epsilon fan-in: dst += src (NN/nn/graph/ComputationGraph.java:2044-2063) */
 int dl4jb200_accumulate(dl4jb200_ctx *ctx, float *dst, const float *src, size_t n);
 /* softmax + NEGATIVELOGLIKELIHOOD / MCXENT output layer: p = softmax(z) row-wise, delta = p - labels,

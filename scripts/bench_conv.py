@@ -1,6 +1,7 @@
 """Micro-benchmark of one convolution layer through the C ABI (NHWC device tensors), CUDA-event timed.
 
-usage: python scripts/bench_conv.py B Cin H W Cout k stride mode [iters] [what]   (what: fwd|bwd|both)
+usage: python scripts/bench_conv.py B Cin H W Cout k stride mode [iters] [what]   (what: fwd|bwd|both|dgrad)
+what=dgrad times backprop-data alone, plain and with the fused epsilon-sum + ReLU-mask epilogue.
 Prints ms and TFLOP/s per pass. Also the command profiled with `ncu --set full` for profiles/.
 """
 import ctypes as C
@@ -41,8 +42,28 @@ def bwd():
     _lib.call("dl4jb200_conv_bwd", h, C.byref(d), p(x), 1, xcs, p(w), p(delta), 1, zcs, p(dw), p(db), p(dx), 1, xcs, 0)
 
 
-for name, fn, passes in (("fwd", fwd, 1), ("bwd", bwd, 2)):
-    if what not in (name, "both"):
+def dgrad():
+    _lib.call("dl4jb200_conv_bwd", h, C.byref(d), p(x), 1, xcs, p(w), p(delta), 1, zcs, None, None, p(dx), 1, xcs, 0)
+
+
+prior, dx2 = torch.randn_like(x), torch.empty_like(x)
+
+
+def dgrad_fused():
+    _lib.call("dl4jb200_conv_bwd_data_fused", h, C.byref(d), p(w), p(delta), zcs, p(dx2), xcs, p(prior), p(x), 1, 0)
+
+
+def unfused_chain():
+    dgrad()
+    _lib.call("dl4jb200_accumulate", h, p(dx), p(prior), dx.numel())
+    _lib.call("dl4jb200_act_bwd", h, p(x), p(dx), p(dx), dx.numel(), 1)
+
+
+cases = (("fwd", fwd, 1), ("bwd", bwd, 2))
+if what == "dgrad":
+    cases = (("dgrad", dgrad, 1), ("dgrad_fused", dgrad_fused, 1), ("dgrad+accumulate+act_bwd", unfused_chain, 1))
+for name, fn, passes in cases:
+    if what not in (name, "both", "dgrad"):
         continue
     for _ in range(3):
         fn()

@@ -180,6 +180,60 @@ def test_tf32_activation_rounding_option(H, ctx, oracle):
         dev.free()
 
 
+@pytest.mark.parametrize("case", [
+    # B, Cin, H, W, Cout, k, s, p, mode
+    (4, 64, 14, 14, 64, (3, 3), (1, 1), (1, 1), 2),      # TMA persistent kernel, fused epilogue, full tiles
+    (3, 256, 7, 7, 64, (1, 1), (1, 1), (0, 0), 1),   # 1x1, ragged last M tile (147 rows)
+    (2, 40, 9, 9, 24, (3, 3), (1, 1), (1, 1), 2),        # channel counts that are not tile multiples
+    (2, 64, 14, 14, 128, (1, 1), (2, 2), (0, 0), 1),  # strided 1x1: compact walk, elementwise fallback
+])
+@pytest.mark.parametrize("algo_name", ["fp32", "tf32"])
+def test_conv_bwd_data_fused_epilogue(H, ctx, oracle, case, algo_name):
+    """dx = relu'(act_out) * (conv_bwd_data(delta) + eps_sum): separate prior buffer, in-place prior, no prior, no mask."""
+    from deeplearning4j_b200 import _lib
+    B, Cin, Hh, W, Cout, k, s, p, mode = case
+    algo = H.ALGO_FP32 if algo_name == "fp32" else H.ALGO_TC_TF32
+    tol = TOL_CONV_FP32 if algo_name == "fp32" else TOL_CONV_TF32
+    rng = np.random.default_rng(77)
+    x = rng.standard_normal((B, Cin, Hh, W)).astype(np.float32)
+    w = (rng.standard_normal((Cout, Cin) + k) * 0.2).astype(np.float32)
+    d = H.conv_desc(x.shape, Cout, k, s, p, (1, 1), MODES[mode])
+    delta = rng.standard_normal((B, Cout, d.out_h, d.out_w)).astype(np.float32)
+    prior = rng.standard_normal(x.shape).astype(np.float32)
+    act_out = np.maximum(rng.standard_normal(x.shape), 0).astype(np.float32)  # a ReLU output: ~half zeros
+    _, _, dxr = oracle.conv_bwd(x, w, delta, stride=s, pad=p, dilation=(1, 1), mode=mode)
+    cs_in, cs_out = (Cin + 3) // 4 * 4, (Cout + 3) // 4 * 4
+    dev = Dev(ctx)
+    try:
+        pw, pd = dev.put(w), dev.put(to_nhwc(delta))
+        pp, pm = dev.put(to_nhwc(prior)), dev.put(to_nhwc(act_out))
+        n = B * Hh * W * cs_in
+
+        def run(eps_sum, mask, inplace=False):
+            pdx = dev.put(to_nhwc(prior)) if inplace else dev.empty(n * 4, fill=0)
+            _lib.call("dl4jb200_conv_bwd_data_fused", ctx.handle, C.byref(d), pw, pd, cs_out, pdx, cs_in,
+                      pdx if inplace else eps_sum, pm if mask else None, H.ACTIVATIONS["relu" if mask else "identity"], algo)
+            return from_nhwc(dev.get(pdx, (B, Hh, W, cs_in)), Cin)
+
+        scale = max(np.abs(dxr).max(), np.abs(prior).max())
+        for eps_sum, mask, inplace in ((pp, True, False), (None, True, True), (None, True, False), (pp, False, False), (None, False, False)):
+            want = dxr + (prior if (eps_sum is not None or inplace) else 0)
+            if mask:
+                want = want * (act_out > 0)
+            got = run(eps_sum, mask, inplace)
+            assert np.abs(got - want).max() <= tol * scale, (eps_sum is not None, mask, inplace, np.abs(got - want).max() / scale)
+            if mask:
+                assert not got[act_out <= 0].any()
+        # the elementwise form of the same bookkeeping
+        pa, pb_ = dev.put(to_nhwc(dxr.astype(np.float32))), dev.put(to_nhwc(prior))
+        po = dev.empty(n * 4)
+        _lib.call("dl4jb200_eps_sum_act_bwd", ctx.handle, pa, pb_, pm, po, n, H.ACTIVATIONS["relu"])
+        got = from_nhwc(dev.get(po, (B, Hh, W, cs_in)), Cin)
+        np.testing.assert_array_equal(got, ((dxr.astype(np.float32) + prior) * (act_out > 0)).astype(np.float32))
+    finally:
+        dev.free()
+
+
 def test_conv_invalid_shapes_raise_like_reference(H, ctx):
     from deeplearning4j_b200 import DL4JInvalidConfigException, DL4JInvalidInputException
     helper = H.CudnnConvolutionHelper(ctx)
