@@ -34,6 +34,8 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__r
                                                                 const float *__restrict__ center, int center_stride,
                                                                 float *__restrict__ partial, int M, int cs) {
     __shared__ float4 red[2][BN_THREADS];
+    pdl_trigger();
+    pdl_wait();
     const int Q = cs >> 2;
     const int rows_per_blk = (M + gridDim.x - 1) / gridDim.x;
     const int r0 = blockIdx.x * rows_per_blk, r1 = min(M, r0 + rows_per_blk);
@@ -171,26 +173,35 @@ __device__ __forceinline__ void bn_fold_partials(const float *__restrict__ parti
     __shared__ double sh1[32][33], sh2[32][33];
     double a = 0.0, b = 0.0;
     if (active) {
-        int i = threadIdx.y;
-        for (; i + 96 < nblk; i += 128) {  // 8 independent loads in flight: the fold is latency-, not bandwidth-bound
-            float p0 = partial[(size_t)i * 2 * cpad + c], q0 = partial[(size_t)i * 2 * cpad + cpad + c];
-            float p1 = partial[(size_t)(i + 32) * 2 * cpad + c], q1 = partial[(size_t)(i + 32) * 2 * cpad + cpad + c];
-            float p2 = partial[(size_t)(i + 64) * 2 * cpad + c], q2 = partial[(size_t)(i + 64) * 2 * cpad + cpad + c];
-            float p3 = partial[(size_t)(i + 96) * 2 * cpad + c], q3 = partial[(size_t)(i + 96) * 2 * cpad + cpad + c];
-            a += ((double)p0 + (double)p1) + ((double)p2 + (double)p3);
-            b += ((double)q0 + (double)q1) + ((double)q2 + (double)q3);
-        }
-        for (; i < nblk; i += 32) {
-            a += (double)partial[(size_t)i * 2 * cpad + c];
-            b += (double)partial[(size_t)i * 2 * cpad + cpad + c];
+        // the fold is latency-bound (a few hundred values per channel): issue every load of a 16-row batch before the
+        // first add. Row order per thread is fixed (y, y+32, y+64, ...), so the result is deterministic.
+        constexpr int U = 8;
+        for (int i = threadIdx.y; i < nblk; i += 32 * U) {
+            float p[U], q[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int r = i + 32 * u;
+                const bool ok = r < nblk;
+                p[u] = ok ? partial[(size_t)r * 2 * cpad + c] : 0.f;
+                q[u] = ok ? partial[(size_t)r * 2 * cpad + cpad + c] : 0.f;
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) { a += (double)p[u]; b += (double)q[u]; }
         }
     }
     sh1[threadIdx.y][threadIdx.x] = a;
     sh2[threadIdx.y][threadIdx.x] = b;
     __syncthreads();
-    s1 = 0.0; s2 = 0.0;
-    if (threadIdx.y == 0)
-        for (int j = 0; j < 32; j++) { s1 += sh1[j][threadIdx.x]; s2 += sh2[j][threadIdx.x]; }
+    // tree fold over the 32 y-slots (fixed shape => deterministic), 5 dependent adds instead of 32
+    for (int h = 16; h >= 1; h >>= 1) {
+        if ((int)threadIdx.y < h) {
+            sh1[threadIdx.y][threadIdx.x] += sh1[threadIdx.y + h][threadIdx.x];
+            sh2[threadIdx.y][threadIdx.x] += sh2[threadIdx.y + h][threadIdx.x];
+        }
+        __syncthreads();
+    }
+    s1 = sh1[0][threadIdx.x];
+    s2 = sh2[0][threadIdx.x];
 }
 
 __global__ void k_bn_finalize_fwd(const float *__restrict__ partial, int nblk, const float *__restrict__ pivot,
@@ -199,6 +210,8 @@ __global__ void k_bn_finalize_fwd(const float *__restrict__ partial, int nblk, c
                                   int cpad, double N, double decay, double eps, int training, int minibatch) {
     int c = blockIdx.x * 32 + threadIdx.x;
     double s1, s2;
+    pdl_trigger();
+    pdl_wait();
     bn_fold_partials(partial, training ? nblk : 0, cpad, c, c < C, s1, s2);
     if (threadIdx.y != 0 || c >= cpad) return;
     if (c >= C) {  // NHWC padding channel: stays zero
@@ -240,6 +253,8 @@ __global__ void k_bn_finalize_bwd(const float *__restrict__ partial, int nblk, c
                                   int cpad, double N) {
     int c = blockIdx.x * 32 + threadIdx.x;
     double s1, s2;
+    pdl_trigger();
+    pdl_wait();
     bn_fold_partials(partial, nblk, cpad, c, c < C, s1, s2);
     if (threadIdx.y != 0 || c >= cpad) return;
     coef[4 * cpad + c] = (c < C && beta) ? beta[c] : 0.f;  // fused-ReLU mask: (x-mean)*a + beta > 0
@@ -268,6 +283,8 @@ __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__
     const int rnd = act >> 8;  // host packs ctx->round_act above the activation code
     act &= 0xff;
     const int Q = cs >> 2;
+    pdl_trigger();
+    pdl_wait();
     size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += stride) {
         int q = (int)(i % Q);
@@ -405,7 +422,8 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
     const size_t total = (size_t)M * (layout == DL4JB200_NHWC ? cs : C);
     if (training) {
         if (layout == DL4JB200_NHWC) {
-            k_bn_partial_nhwc<0><<<p.nblk, BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, x, cs, p.partial, (int)M, cs);
+            DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_partial_nhwc<0>, dim3(p.nblk), dim3(BN_THREADS), 0, ctx->stream, x, nullptr,
+                                          BnMask{nullptr, nullptr, nullptr, 0}, x, cs, p.partial, (int)M, cs));
         } else {
             dim3 grid(C, p.nblk);
             bool vec = (HW % 4 == 0) && al16(x);
@@ -414,12 +432,13 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
         }
         DL4J_CHECK_LAUNCH();
     }
-    k_bn_finalize_fwd<<<dl4j_ceil_div(p.cpad, 32), dim3(32, 32), 0, ctx->stream>>>(
-        p.partial, p.nblk, x, layout == DL4JB200_NHWC ? 1 : HW, gamma, beta, gmean, gvar, save_mean, save_std, p.coef, C,
-        p.cpad, (double)M, decay, eps, training, minibatch);
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_fwd, dim3(dl4j_ceil_div(p.cpad, 32)), dim3(32, 32), 0, ctx->stream, p.partial, p.nblk, x,
+                                  layout == DL4JB200_NHWC ? 1 : HW, gamma, beta, gmean, gvar, save_mean, save_std, p.coef, C, p.cpad,
+                                  (double)M, decay, eps, training, minibatch));
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
-        k_bn_apply_nhwc<0><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total / 4, cs, act | (ctx->round_act << 8));
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_apply_nhwc<0>, dim3(bn_grid(ctx, total / 4)), dim3(256), 0, ctx->stream, x, residual, nullptr, y,
+                                      p.coef, total / 4, cs, act | (ctx->round_act << 8)));
     } else {
         bool vec = (HW % 4 == 0) && al16(x) && al16(y);
         if (vec) k_bn_apply_nchw<0, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, residual, nullptr, y, p.coef, total, C, HW, act | (ctx->round_act << 8));
@@ -449,19 +468,20 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
     const float *mask_beta = relu ? p.coef + 4 * (size_t)p.cpad : nullptr;
     bool vec = (HW % 4 == 0) && al16(x) && al16(eps) && al16(dx);
     if (layout == DL4JB200_NHWC) {
-        k_bn_partial_nhwc<1><<<p.nblk, BN_THREADS, 0, ctx->stream>>>(x, eps, mk, save_mean, C, p.partial, (int)M, cs);
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_partial_nhwc<1>, dim3(p.nblk), dim3(BN_THREADS), 0, ctx->stream, x, eps, mk, save_mean, C, p.partial,
+                                      (int)M, cs));
     } else {
         dim3 grid(C, p.nblk);
         if (vec) k_bn_partial_nchw<1, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, mk, save_mean, p.partial, B, C, HW, p.chunk);
         else k_bn_partial_nchw<1, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, mk, save_mean, p.partial, B, C, HW, p.chunk);
     }
     DL4J_CHECK_LAUNCH();
-    k_bn_finalize_bwd<<<dl4j_ceil_div(p.cpad, 32), dim3(32, 32), 0, ctx->stream>>>(p.partial, p.nblk, gamma, save_mean, save_std,
-                                                                               relu ? beta : nullptr, dgamma, dbeta, p.coef, C,
-                                                                               p.cpad, (double)M);
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_bwd, dim3(dl4j_ceil_div(p.cpad, 32)), dim3(32, 32), 0, ctx->stream, p.partial, p.nblk, gamma,
+                                  save_mean, save_std, relu ? beta : nullptr, dgamma, dbeta, p.coef, C, p.cpad, (double)M));
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
-        k_bn_apply_nhwc<1><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total / 4, cs, ctx->round_act << 8);
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_apply_nhwc<1>, dim3(bn_grid(ctx, total / 4)), dim3(256), 0, ctx->stream, x, eps, mask_beta, dx, p.coef,
+                                      total / 4, cs, ctx->round_act << 8));
     } else {
         if (vec) k_bn_apply_nchw<1, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total, C, HW, ctx->round_act << 8);
         else k_bn_apply_nchw<1, false><<<bn_grid(ctx, total), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total, C, HW, ctx->round_act << 8);

@@ -1,5 +1,6 @@
 // Shared host/device plumbing of libdl4jb200: context, error reporting, scratch workspace.
 #pragma once
+#include <utility>
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdint.h>
@@ -47,6 +48,31 @@ extern unsigned long long g_dl4j_launches;
         ++g_dl4j_launches;                   \
         DL4J_CUDA_TRY(cudaGetLastError());   \
     } while (0)
+
+// Programmatic dependent launch (sm_90+). A kernel that starts with pdl_trigger(); pdl_wait(); may be launched with
+// dl4j_launch_pdl: its CTAs are then scheduled while the preceding kernel of the stream drains (launch latency and
+// prologue overlap the tail), and pdl_wait() returns only when that kernel has completed and its writes are visible.
+// Both instructions are no-ops under an ordinary launch. Rule: no global memory access before pdl_wait().
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t dl4j_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                   Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
+}
+#endif
 
 #define DL4J_REQUIRE(cond, ...)            \
     do {                                   \

@@ -225,6 +225,61 @@ __global__ void __launch_bounds__(256, 4) k_maxpool_bwd_nhwc_fast(const float *_
     }
 }
 
+// Stride-2 windows (ResNet's 3x3/2 stem pool, every 2x2/2 pool): one thread owns a 2x2 patch of dx (x 4 channels).
+// The patch's four cells share their candidate windows, so eps / argmax are fetched once per window and patch instead
+// of once per window and cell: 4 window reads per 4 cells instead of 9 for k = 3 (the kernel is bound by those L2
+// reads). Per cell the contributions are added in the same order as k_maxpool_bwd_nhwc_fast (kh, kw ascending).
+__global__ void __launch_bounds__(256, 4) k_maxpool_bwd_nhwc_patch2(const float *__restrict__ eps, const int32_t *__restrict__ argmax,
+                                                                   float *__restrict__ dx, PoolGeom g, int Hp, int Wp, size_t total) {
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    pdl_trigger();
+    pdl_wait();
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+        uint32_t i = (uint32_t)idx, q, r;
+        g.d_q.divmod(i, q, r); const int c = (int)r * 4; i = q;
+        g.d_w.divmod(i, q, r); const int w0 = (int)r * 2; i = q;   // d_w / d_h hold the PATCH grid here
+        g.d_h.divmod(i, q, r); const int h0 = (int)r * 2; const int b = (int)q;
+        const int th0 = h0 + g.pT, tw0 = w0 + g.pL;  // >= 0: this kernel is only used with non-negative padding
+        const int oh_hi = min((th0 + 1) >> 1, g.Ho - 1), ow_hi = min((tw0 + 1) >> 1, g.Wo - 1);
+        const int lh = th0 - g.kH + 1, lw = tw0 - g.kW + 1;
+        const int oh_lo = lh <= 0 ? 0 : (lh + 1) >> 1, ow_lo = lw <= 0 ? 0 : (lw + 1) >> 1;
+        float4 acc[2][2];
+#pragma unroll
+        for (int a = 0; a < 2; a++)
+#pragma unroll
+            for (int d = 0; d < 2; d++) acc[a][d] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int oh = oh_hi; oh >= oh_lo; oh--) {
+            // tap row of window oh that lands on patch row a: kh = th0 + a - 2*oh, valid when 0 <= kh < kH
+            const int kh0 = th0 - 2 * oh;
+            for (int ow = ow_hi; ow >= ow_lo; ow--) {
+                const int kw0 = tw0 - 2 * ow;
+                const size_t o = (((size_t)b * g.Ho + oh) * g.Wo + ow) * g.ycs + c;
+                const int4 am = *reinterpret_cast<const int4 *>(argmax + o);
+                const float4 e = *reinterpret_cast<const float4 *>(eps + o);
+#pragma unroll
+                for (int a = 0; a < 2; a++) {
+                    const int kh = kh0 + a;
+                    if (kh < 0 || kh >= g.kH) continue;
+#pragma unroll
+                    for (int d = 0; d < 2; d++) {
+                        const int kw = kw0 + d;
+                        if (kw < 0 || kw >= g.kW) continue;
+                        const int me = kh * g.kW + kw;
+                        acc[a][d].x += am.x == me ? e.x : 0.f; acc[a][d].y += am.y == me ? e.y : 0.f;
+                        acc[a][d].z += am.z == me ? e.z : 0.f; acc[a][d].w += am.w == me ? e.w : 0.f;
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int a = 0; a < 2; a++)
+#pragma unroll
+            for (int d = 0; d < 2; d++)
+                if (h0 + a < g.H && w0 + d < g.W)
+                    *reinterpret_cast<float4 *>(dx + (((size_t)b * g.H + h0 + a) * g.W + w0 + d) * g.xcs + c) = dl4j_rnd4(acc[a][d], g.rnd);
+    }
+}
+
 static int pool_geom(const dl4jb200_conv_desc *d, int layout, int x_cs, int y_cs, PoolGeom &g, const char *who) {
     DL4J_REQUIRE(d, "%s: desc is NULL", who);
     DL4J_REQUIRE(d->batch > 0 && d->c_in > 0 && d->in_h > 0 && d->in_w > 0 && d->out_h > 0 && d->out_w > 0 &&
@@ -289,7 +344,14 @@ int dl4jb200_pool_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     DL4J_REQUIRE(pool_type != DL4JB200_POOL_PNORM || (x && y && pnorm >= 1), "pool_bwd: PNORM needs x, y and pnorm >= 1");
     g.d_q = FastDiv((uint32_t)(layout == DL4JB200_NHWC ? g.xcs / 4 : 1));
     g.d_w = FastDiv((uint32_t)g.W); g.d_h = FastDiv((uint32_t)g.H); g.d_c = FastDiv((uint32_t)g.C);
-    if (layout == DL4JB200_NHWC && pool_type == DL4JB200_POOL_MAX && argmax && g.dH == 1 && g.dW == 1) {
+    if (layout == DL4JB200_NHWC && pool_type == DL4JB200_POOL_MAX && argmax && g.dH == 1 && g.dW == 1 && g.sH == 2 && g.sW == 2 &&
+        g.pT >= 0 && g.pL >= 0) {
+        const int Hp = (g.H + 1) / 2, Wp = (g.W + 1) / 2;
+        g.d_w = FastDiv((uint32_t)Wp); g.d_h = FastDiv((uint32_t)Hp);
+        size_t total = (size_t)g.B * Hp * Wp * (g.xcs / 4);
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_maxpool_bwd_nhwc_patch2, dim3(pool_grid(ctx, total)), dim3(256), 0, ctx->stream, eps, argmax, dx, g,
+                                      Hp, Wp, total));
+    } else if (layout == DL4JB200_NHWC && pool_type == DL4JB200_POOL_MAX && argmax && g.dH == 1 && g.dW == 1) {
         size_t total = (size_t)g.B * g.H * g.W * (g.xcs / 4);
         k_maxpool_bwd_nhwc_fast<<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(eps, argmax, dx, g, total);
     } else if (layout == DL4JB200_NHWC) {
