@@ -65,9 +65,18 @@ __global__ void __launch_bounds__(256) k_pack_filter(const float *__restrict__ w
 }
 
 // dW[co][ci][kh][kw] = sum_s partial[s][co][(kh*kW+kw)*Cg + ci]   (fixed order: deterministic)
+// db_partial (optional): [splits][rows_p] per-split bias-gradient sums from the filter-gradient GEMM's extra column.
 __global__ void __launch_bounds__(256) k_wgrad_finalize(const float *__restrict__ partial, float *__restrict__ dw, int Cout,
-                                                        int Cin, int taps, int Cg, int Kp, int rows_p, int splits) {
+                                                        int Cin, int taps, int Cg, int Kp, int rows_p, int splits,
+                                                        const float *__restrict__ db_partial, float *__restrict__ db) {
     size_t total = (size_t)Cout * Cin * taps, stride = (size_t)gridDim.x * blockDim.x;
+    if (db_partial) {
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)Cout; i += stride) {
+            float acc = 0.f;
+            for (int s = 0; s < splits; s++) acc += db_partial[(size_t)s * rows_p + i];
+            db[i] = acc;
+        }
+    }
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
         int tap = (int)(i % taps);
         size_t t = i / taps;
@@ -264,20 +273,26 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     if (nblk > ctx->sm_count * 4) nblk = ctx->sm_count * 4;
     if (nblk < 1) nblk = 1;
     size_t part_f = (size_t)splits * rows_w * gf.Kp, pack_f = (size_t)rows_b * gb.Kp, col_f = (size_t)nblk * delta_cs;
+    if (col_f < (size_t)splits * rows_w) col_f = (size_t)splits * rows_w;  // or the per-split bias-gradient column
     float *ws = (float *)dl4j_workspace(ctx, 0, (part_f + pack_f + col_f) * sizeof(float));
     if (!ws) return DL4JB200_ERR_CUDA;
     float *partial = ws, *wb = ws + part_f, *colp = wb + pack_f;
 
+    // With DL4JB200_OPT_TF32_ACTIVATIONS the caller's delta is TF32-representable, so the bias gradient can ride in the
+    // filter-gradient GEMM as an extra accumulator column (delta^T x ones: exact products, fp32 accumulation) instead
+    // of a separate column-sum pass over delta.
+    const bool db_fused = dw && db && tcore && gf.use_tma && ctx->round_act;
     if (dw) {
-        if (tcore) rc = conv_tc_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
+        float *dbp = db_fused ? colp : nullptr;  // [splits][rows_w], carved from the same scratch request below
+        if (tcore) rc = conv_tc_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits, dbp);
         else rc = conv_ffma_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
         if (rc) return rc;
         k_wgrad_finalize<<<grid_for(ctx, (size_t)d->c_out * d->c_in * gf.taps), 256, 0, ctx->stream>>>(
-            partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w, splits);
+            partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w, splits, dbp, db);
         DL4J_CHECK_LAUNCH();
     }
 
-    if (db) {
+    if (db && !db_fused) {
         k_colsum_partial<<<nblk, 256, 0, ctx->stream>>>(ds, colp, gf.M, delta_cs);
         DL4J_CHECK_LAUNCH();
         k_colsum_final<<<dl4j_ceil_div(d->c_out, 32), dim3(32, 32), 0, ctx->stream>>>(colp, db, nblk, delta_cs, d->c_out);

@@ -98,6 +98,6 @@ int conv_ffma_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const 
 int conv_tc_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
                  const float *bias, float *out, int n_valid, int out_cs, int act);
 int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const float *delta, int delta_cs, int c_out,
-                  float *partial, int rows_p, int splits);
+                  float *partial, int rows_p, int splits, float *db_partial = nullptr);
 int conv_tc_wgrad_splits(dl4jb200_ctx *ctx, const ConvGeom &g, int c_out);
 bool conv_tc_gemm_can_tma(const ConvGeom &g);

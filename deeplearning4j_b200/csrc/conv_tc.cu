@@ -904,7 +904,7 @@ template <int BN, int STAGES>
 __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad_tma(const __grid_constant__ CUtensorMap tmD,
                                                                const __grid_constant__ CUtensorMap tmX,
                                                                float *__restrict__ partial, TmaWgradGeom g, int rows_p,
-                                                               int m_per_split, int k_tiles) {
+                                                               int m_per_split, int k_tiles, float *__restrict__ db_partial) {
     using L = SmemLayout<BN, STAGES>;
     constexpr int NB_ATOMS = BN / 32;
     extern __shared__ uint8_t smem_raw[];
@@ -919,6 +919,15 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad_tma(const __grid_cons
     const int kcol0 = kt * BN, co0 = ct * BLOCK_M;
     const int ms = blockIdx.y * m_per_split, me = min(g.M, ms + m_per_split);
     const int num_k = (me - ms + BLOCK_K - 1) / BLOCK_K;
+    // Bias gradient db[co] = sum over pixels of delta (ConvolutionLayer.java:257) as one more accumulator block: the CTAs
+    // of k-tile 0 multiply the same delta operand with an all-ones B tile (N = 16, the minimum for M = 128) into TMEM
+    // columns [BN, BN+16). 1 KB of ones serves every K-step; being constant, its swizzle does not matter.
+    const bool do_db = db_partial != nullptr && kt == 0;
+    const uint32_t ones_base = base + L::BAR_OFF + 1024;
+    if (do_db) {
+        for (int i = tid; i < 256; i += THREADS) asm volatile("st.shared.f32 [%0], %1;" ::"r"(ones_base + 4u * i), "f"(1.0f) : "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
 
     if (tid == 0) {
         tma::prefetch_desc(&tmD);
@@ -927,7 +936,7 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad_tma(const __grid_cons
         mbar_init(acc_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 4) tmem_alloc<BN>(tmem_slot);
+    if (warp == 4) tmem_alloc<2 * BN>(tmem_slot);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -990,8 +999,15 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad_tma(const __grid_cons
                 }
             }
         }
+        if (do_db) {
+            float v[32];
+            tmem_ld32(tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)BN, v);  // columns BN..BN+15 all hold the row's sum
+            if (co < rows_p) db_partial[(size_t)blockIdx.y * rows_p + co] = v[0];
+        }
     } else {
         constexpr uint32_t idesc = umma_idesc(BLOCK_M, BN, 1, 1);
+        constexpr uint32_t idesc_db = umma_idesc(BLOCK_M, 16, 1, 1);
+        const uint64_t od = umma_desc(ones_base, 4096, 512, 1);
         for (int it = 0; it < num_k; ++it) {
             const int s = it % STAGES;
             mbar_wait(full_bar(s), (it / STAGES) & 1);
@@ -1002,6 +1018,7 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad_tma(const __grid_cons
                     const uint64_t ad = umma_desc(a_base + s * L::A_BYTES + k * 1024, 4096, 512, 1);
                     const uint64_t bd = umma_desc(b_base + s * L::B_BYTES + k * 1024, 4096, 512, 1);
                     umma_tf32(tmem_d, ad, bd, idesc, (it | k) ? 1u : 0u);
+                    if (do_db) umma_tf32(tmem_d + (uint32_t)BN, ad, od, idesc_db, (it | k) ? 1u : 0u);
                 }
                 umma_commit(empty_bar(s));
             }
@@ -1012,22 +1029,23 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad_tma(const __grid_cons
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc<BN>(tmem_d);
+    if (warp == 4) tmem_dealloc<2 * BN>(tmem_d);
 }
 
 template <int BN, int STAGES>
 static int launch_wgrad_tma(dl4jb200_ctx *ctx, const CUtensorMap &tmD, const CUtensorMap &tmX, const TmaWgradGeom &g,
-                            float *partial, int rows_p, int splits, int m_per_split) {
+                            float *partial, int rows_p, int splits, int m_per_split, float *db_partial) {
     using L = SmemLayout<BN, STAGES>;
+    constexpr int SMEM = L::BAR_OFF + 1024 + 1024 + 1024;  // stages | barriers | 1 KB ones tile | alignment slack
     auto kern = k_conv_tc_wgrad_tma<BN, STAGES>;
     static bool configured[16] = {false};
     if (!configured[ctx->device & 15]) {
-        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
         configured[ctx->device & 15] = true;
     }
     int k_tiles = dl4j_ceil_div(g.Kp, BN), c_tiles = dl4j_ceil_div(rows_p, BLOCK_M);
     dim3 grid(k_tiles * c_tiles, splits);
-    kern<<<grid, THREADS, L::BYTES, ctx->stream>>>(tmD, tmX, partial, g, rows_p, m_per_split, k_tiles);
+    kern<<<grid, THREADS, SMEM, ctx->stream>>>(tmD, tmX, partial, g, rows_p, m_per_split, k_tiles, db_partial);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
@@ -1148,7 +1166,7 @@ int conv_tc_wgrad_splits(dl4jb200_ctx *ctx, const ConvGeom &g, int c_out) {
 }
 
 int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const float *delta, int delta_cs, int c_out,
-                  float *partial, int rows_p, int splits) {
+                  float *partial, int rows_p, int splits, float *db_partial) {
     (void)c_out;
     int mps = dl4j_round_up(dl4j_ceil_div(g.M, splits), tc::BLOCK_K);
     if (dl4j_ceil_div(g.M, mps) != splits) {
@@ -1166,11 +1184,12 @@ int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const fl
         t.M = g.M; t.kW = g.kW; t.dH = g.dH; t.dW = g.dW; t.sH = g.sH; t.sW = g.sW; t.lowH = -g.pT; t.lowW = -g.pL; t.Kp = g.Kp;
         t.div_Wm = g.div_Wm; t.div_HWm = g.div_HWm; t.div_Cg = g.div_Cg; t.div_kW = g.div_kW;
         switch (tc::wgrad_bn(g)) {
-        case 128: return tc::launch_wgrad_tma<128, 3>(ctx, tmD, tmX, t, partial, rows_p, splits, mps);
-        case 64: return tc::launch_wgrad_tma<64, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, mps);
-        default: return tc::launch_wgrad_tma<32, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, mps);
+        case 128: return tc::launch_wgrad_tma<128, 3>(ctx, tmD, tmX, t, partial, rows_p, splits, mps, db_partial);
+        case 64: return tc::launch_wgrad_tma<64, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, mps, db_partial);
+        default: return tc::launch_wgrad_tma<32, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, mps, db_partial);
         }
     }
+    if (db_partial) { dl4j_set_error("conv_tc_wgrad: the bias-gradient column needs the TMA kernel"); return DL4JB200_ERR_INVALID_ARG; }
     switch (tc::wgrad_bn(g)) {
     case 128: return tc::launch_wgrad<128, 3>(ctx, g, x, delta, delta_cs, partial, rows_p, splits, mps);
     case 64: return tc::launch_wgrad<64, 4>(ctx, g, x, delta, delta_cs, partial, rows_p, splits, mps);
@@ -1195,8 +1214,8 @@ int conv_tc_wgrad_tma_raw(dl4jb200_ctx *ctx, const CUtensorMap &tmD, const CUten
                           int rows_p, int splits, int m_per_split) {
     const int bn = t.Kp >= 128 ? 128 : (t.Kp >= 64 ? 64 : 32);
     switch (bn) {
-    case 128: return tc::launch_wgrad_tma<128, 3>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split);
-    case 64: return tc::launch_wgrad_tma<64, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split);
-    default: return tc::launch_wgrad_tma<32, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split);
+    case 128: return tc::launch_wgrad_tma<128, 3>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split, nullptr);
+    case 64: return tc::launch_wgrad_tma<64, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split, nullptr);
+    default: return tc::launch_wgrad_tma<32, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split, nullptr);
     }
 }

@@ -234,6 +234,39 @@ def test_conv_bwd_data_fused_epilogue(H, ctx, oracle, case, algo_name):
         dev.free()
 
 
+@pytest.mark.parametrize("case", [(4, 64, 14, 14, 64, (3, 3), 2), (3, 256, 7, 7, 96, (1, 1), 1), (2, 32, 9, 9, 200, (3, 3), 2)])
+def test_conv_bias_gradient_rides_in_filter_gemm(H, ctx, oracle, case):
+    """With DL4JB200_OPT_TF32_ACTIVATIONS the TF32 filter-gradient GEMM also produces db (delta^T x ones as an extra
+    accumulator column); it must equal the plain column sum of delta, and dW must be unchanged."""
+    from deeplearning4j_b200 import _lib
+    from oracle.net_oracle import tf32_round
+    B, Cin, Hh, W, Cout, k, mode = case
+    rng = np.random.default_rng(3)
+    x = tf32_round(rng.random((B, Cin, Hh, W), dtype=np.float32))
+    w = (rng.standard_normal((Cout, Cin) + k) * 0.3).astype(np.float32)
+    d = H.conv_desc(x.shape, Cout, k, (1, 1), (k[0] // 2, k[1] // 2), (1, 1), MODES[mode])
+    delta = tf32_round(rng.standard_normal((B, Cout, d.out_h, d.out_w)).astype(np.float32))
+    dwr, dbr, _ = oracle.conv_bwd(x, w, delta, stride=(1, 1), pad=(k[0] // 2, k[1] // 2), dilation=(1, 1), mode=mode)
+    cs_in, cs_out = (Cin + 3) // 4 * 4, (Cout + 3) // 4 * 4
+    dev = Dev(ctx)
+    try:
+        px, pw, pd = dev.put(to_nhwc(x)), dev.put(w), dev.put(to_nhwc(delta))
+        res = {}
+        for opt in (0, 1):
+            _lib.call("dl4jb200_ctx_set_option", ctx.handle, _lib.OPT_TF32_ACTIVATIONS, opt)
+            pdw, pdb = dev.empty(w.size * 4, fill=0), dev.empty(Cout * 4, fill=0)
+            _lib.call("dl4jb200_conv_bwd", ctx.handle, C.byref(d), px, H.NHWC, cs_in, pw, pd, H.NHWC, cs_out, pdw, pdb, None,
+                      H.NHWC, cs_in, H.ALGO_TC_TF32)
+            res[opt] = (dev.get(pdw, w.shape), dev.get(pdb, (Cout,)))
+        np.testing.assert_array_equal(res[0][0], res[1][0])
+        for opt in (0, 1):
+            assert rel_err(res[opt][1], dbr) <= 1e-5, (opt, rel_err(res[opt][1], dbr))
+            assert rel_err(res[opt][0], dwr) <= TOL_CONV_TF32_QUANTISED
+    finally:
+        _lib.call("dl4jb200_ctx_set_option", ctx.handle, _lib.OPT_TF32_ACTIVATIONS, 0)
+        dev.free()
+
+
 def test_conv_invalid_shapes_raise_like_reference(H, ctx):
     from deeplearning4j_b200 import DL4JInvalidConfigException, DL4JInvalidInputException
     helper = H.CudnnConvolutionHelper(ctx)
