@@ -71,6 +71,7 @@ int dl4jb200_ctx_destroy(dl4jb200_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (auto &kv : ctx->mirrors) cudaFree(kv.second.dev);
+    conv_filters_free(ctx);
     for (int i = 0; i < 4; i++) if (ctx->ws[i]) cudaFree(ctx->ws[i]);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;

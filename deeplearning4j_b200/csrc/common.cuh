@@ -16,6 +16,8 @@ struct MirrorBuf {
     size_t bytes;
 };
 
+struct FilterRegistry;
+void conv_filters_free(struct dl4jb200_ctx *ctx);
 struct dl4jb200_ctx {
     int device;
     cudaStream_t stream;
@@ -26,6 +28,7 @@ struct dl4jb200_ctx {
     void *ws[4];
     size_t ws_bytes[4];
     std::unordered_map<const void *, MirrorBuf> mirrors;
+    struct FilterRegistry *filters = nullptr;  // pre-packed convolution filters (conv.cu); freed by conv_filters_free
 };
 
 void dl4j_set_error(const char *fmt, ...);

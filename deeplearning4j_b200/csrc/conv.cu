@@ -1,5 +1,9 @@
 // Convolution entry points: geometry, filter packing, algorithm dispatch, split-K reduction, bias gradient,
 // and NCHW staging for callers that hold DL4J-layout ('c' order NCHW) tensors.
+#include <algorithm>
+#include <unordered_map>
+#include <vector>
+
 #include "conv_common.cuh"
 
 // ------------------------------------------------------------------ geometry
@@ -64,6 +68,72 @@ __global__ void __launch_bounds__(256) k_pack_filter(const float *__restrict__ w
     }
 }
 
+// ------------------------------------------------------------------ pre-packed filters
+// conv_fwd / conv_bwd pack the filter on every call (one small kernel each: 106 launches per ResNet-50 step). A caller
+// that knows when the parameters change registers each filter once and re-packs all of them with ONE launch after
+// every parameter update (dl4jb200_filters_repack); convolution calls on a registered `w` then use the stored operand.
+struct PackJob {  // device-visible
+    const float *w;
+    float *wp;
+    unsigned long long start;  // first flat element of this job in the batched index space
+    int Cout, Cin, kH, kW, Cg, Kp, rows_p, transposed, round_tf32, flip;
+};
+struct FilterEntry {
+    PackJob fwd, bwd;  // bwd.wp == nullptr: no backprop-data operand registered
+};
+struct FilterRegistry {
+    std::unordered_map<const float *, FilterEntry> entries;
+    PackJob *jobs_dev = nullptr;
+    int njobs = 0;
+    unsigned long long total = 0;
+    bool table_dirty = true, valid = false;
+};
+
+void conv_filters_free(dl4jb200_ctx *ctx) {
+    FilterRegistry *r = ctx->filters;
+    if (!r) return;
+    for (auto &kv : r->entries) {
+        if (kv.second.fwd.wp) cudaFree(kv.second.fwd.wp);
+        if (kv.second.bwd.wp) cudaFree(kv.second.bwd.wp);
+    }
+    if (r->jobs_dev) cudaFree(r->jobs_dev);
+    delete r;
+    ctx->filters = nullptr;
+}
+
+__global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__restrict__ jobs, int njobs, unsigned long long total) {
+    unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        int lo = 0, hi = njobs - 1;  // last job whose start <= i
+        while (lo < hi) {
+            int mid = (lo + hi + 1) >> 1;
+            if (__ldg(&jobs[mid].start) <= i) lo = mid; else hi = mid - 1;
+        }
+        const PackJob j = jobs[lo];
+        const unsigned long long e = i - j.start;
+        const int n = (int)(e / j.Kp), k = (int)(e % j.Kp), taps = j.kH * j.kW;
+        const int tap = k / j.Cg, c = k % j.Cg;
+        float v = 0.f;
+        if (tap < taps) {
+            const int co = j.transposed ? c : n, ci = j.transposed ? n : c;
+            if (co < j.Cout && ci < j.Cin) v = j.w[((size_t)co * j.Cin + ci) * taps + (j.flip ? taps - 1 - tap : tap)];
+        }
+        j.wp[e] = j.round_tf32 ? to_tf32_rna(v) : v;
+    }
+}
+
+// the stored operand for (w, direction) if one is registered, current, and laid out exactly as this call needs it
+static const float *filters_lookup(dl4jb200_ctx *ctx, const float *w, bool bwd, int Cg, int Kp, int rows_p, int round_tf32, int flip) {
+    FilterRegistry *r = ctx->filters;
+    if (!r || !r->valid) return nullptr;
+    auto it = r->entries.find(w);
+    if (it == r->entries.end()) return nullptr;
+    const PackJob &j = bwd ? it->second.bwd : it->second.fwd;
+    if (!j.wp || j.Cg != Cg || j.Kp != Kp || j.rows_p != rows_p || j.round_tf32 != round_tf32) return nullptr;
+    if (j.kH * j.kW > 1 && j.flip != flip) return nullptr;
+    return j.wp;
+}
+
 // dW[co][ci][kh][kw] = sum_s partial[s][co][(kh*kW+kw)*Cg + ci]   (fixed order: deterministic)
 // db_partial (optional): [splits][rows_p] per-split bias-gradient sums from the filter-gradient GEMM's extra column.
 __global__ void __launch_bounds__(256) k_wgrad_finalize(const float *__restrict__ partial, float *__restrict__ dw, int Cout,
@@ -77,14 +147,16 @@ __global__ void __launch_bounds__(256) k_wgrad_finalize(const float *__restrict_
             db[i] = acc;
         }
     }
+    // enumerate in the PARTIAL layout's order (ci fastest): the `splits` reads per element are coalesced and only the
+    // single write is strided (by taps floats) -- for 3x3 filters the other order made every read its own sector
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-        int tap = (int)(i % taps);
-        size_t t = i / taps;
-        int ci = (int)(t % Cin), co = (int)(t / Cin);
+        int ci = (int)(i % Cin);
+        size_t t = i / Cin;
+        int tap = (int)(t % taps), co = (int)(t / taps);
         const float *p = partial + (size_t)co * Kp + (size_t)tap * Cg + ci;
         float acc = 0.f;
         for (int s = 0; s < splits; s++) acc += p[(size_t)s * rows_p * Kp];
-        dw[i] = acc;
+        dw[((size_t)co * Cin + ci) * taps + tap] = acc;
     }
 }
 
@@ -202,11 +274,16 @@ int dl4jb200_conv_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     DL4J_REQUIRE(x_cs >= g.Cg, "conv_fwd: x pixel stride %d < %d", x_cs, g.Cg);
     g.use_tma = algo == DL4JB200_CONV_ALGO_TC_TF32 && conv_tc_gemm_can_tma(g);
     const int rows_p = dl4j_round_up(z_cs > d->c_out ? z_cs : d->c_out, 256);
-    float *wp = (float *)dl4j_workspace(ctx, 0, (size_t)rows_p * g.Kp * sizeof(float));
-    if (!wp) return DL4JB200_ERR_CUDA;
-    k_pack_filter<<<grid_for(ctx, (size_t)rows_p * g.Kp), 256, 0, ctx->stream>>>(w, wp, d->c_out, d->c_in, d->k_h, d->k_w, g.Cg,
-                                                                               g.Kp, rows_p, 0, algo == DL4JB200_CONV_ALGO_TC_TF32, 0);
-    DL4J_CHECK_LAUNCH();
+    const int tf = algo == DL4JB200_CONV_ALGO_TC_TF32;
+    const float *wp = filters_lookup(ctx, w, false, g.Cg, g.Kp, rows_p, tf, 0);
+    if (!wp) {
+        float *t = (float *)dl4j_workspace(ctx, 0, (size_t)rows_p * g.Kp * sizeof(float));
+        if (!t) return DL4JB200_ERR_CUDA;
+        k_pack_filter<<<grid_for(ctx, (size_t)rows_p * g.Kp), 256, 0, ctx->stream>>>(w, t, d->c_out, d->c_in, d->k_h, d->k_w, g.Cg, g.Kp,
+                                                                                  rows_p, 0, tf, 0);
+        DL4J_CHECK_LAUNCH();
+        wp = t;
+    }
     // with DL4JB200_OPT_TF32_ACTIVATIONS an activated output (it feeds the next convolution directly) is stored rounded
     const int act_code = act | ((ctx->round_act && act != DL4JB200_ACT_IDENTITY) ? 0x100 : 0);
     if (algo == DL4JB200_CONV_ALGO_TC_TF32) rc = conv_tc_gemm(ctx, g, xs, wp, rows_p, bias, zs, d->c_out, z_cs, act_code);
@@ -309,22 +386,92 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
         gc.use_tma = conv_tc_gemm_can_tma(gc);
         if (gc.use_tma) {
             DL4J_CUDA_TRY(cudaMemsetAsync(dxs, 0, (size_t)d->batch * d->in_h * d->in_w * dx_cs * sizeof(float), ctx->stream));
-            k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, 1, 1, gc.Cg, gc.Kp, rows_b, 1, 1, 0);
-            DL4J_CHECK_LAUNCH();
-            if ((rc = conv_tc_gemm(ctx, gc, ds, wb, rows_b, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY))) return rc;
+            const float *wq = filters_lookup(ctx, w, true, gc.Cg, gc.Kp, rows_b, 1, 0);
+            if (!wq) {
+                k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, 1, 1, gc.Cg, gc.Kp, rows_b, 1, 1, 0);
+                DL4J_CHECK_LAUNCH();
+                wq = wb;
+            }
+            if ((rc = conv_tc_gemm(ctx, gc, ds, wq, rows_b, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY))) return rc;
             if (dx_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, dxs, dx, d->batch, d->c_in, d->in_h, d->in_w, dx_cs);
             return DL4JB200_OK;
         }
     }
     if (dx) {
         DL4J_REQUIRE(delta_cs >= gb.Cg, "conv_bwd: delta pixel stride %d < %d", delta_cs, gb.Cg);
-        k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, tcore, gb.use_tma);
-        DL4J_CHECK_LAUNCH();
-        if (tcore) rc = conv_tc_gemm(ctx, gb, ds, wb, rows_b, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);
-        else rc = conv_ffma_gemm(ctx, gb, ds, wb, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);
+        const float *wq = filters_lookup(ctx, w, true, gb.Cg, gb.Kp, rows_b, tcore, gb.use_tma);
+        if (!wq) {
+            k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, tcore, gb.use_tma);
+            DL4J_CHECK_LAUNCH();
+            wq = wb;
+        }
+        if (tcore) rc = conv_tc_gemm(ctx, gb, ds, wq, rows_b, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);
+        else rc = conv_ffma_gemm(ctx, gb, ds, wq, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);
         if (rc) return rc;
         if (dx_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, dxs, dx, d->batch, d->c_in, d->in_h, d->in_w, dx_cs);
     }
+    return DL4JB200_OK;
+}
+
+int dl4jb200_filter_register(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *w, int x_cs, int z_cs, int algo,
+                             int with_bwd_data) {
+    DL4J_REQUIRE(ctx && w, "filter_register: NULL argument");
+    int rc = check_desc(d, "filter_register");
+    if (rc) return rc;
+    DL4J_REQUIRE(algo == DL4JB200_CONV_ALGO_TC_TF32 || algo == DL4JB200_CONV_ALGO_FP32, "filter_register: unknown algo %d", algo);
+    DL4J_REQUIRE(x_cs >= d->c_in && z_cs >= d->c_out && x_cs % 4 == 0 && z_cs % 4 == 0, "filter_register: bad pixel strides");
+    if (!ctx->filters) ctx->filters = new FilterRegistry();
+    FilterRegistry *r = ctx->filters;
+    DL4J_REQUIRE(r->entries.find(w) == r->entries.end(), "filter_register: this filter is already registered");
+    const int tf = algo == DL4JB200_CONV_ALGO_TC_TF32;
+    FilterEntry e{};
+    ConvGeom gf = conv_geom_fwd(d, x_cs);
+    e.fwd = PackJob{w, nullptr, 0ULL, d->c_out, d->c_in, d->k_h, d->k_w, gf.Cg, gf.Kp, dl4j_round_up(z_cs > d->c_out ? z_cs : d->c_out, 256), 0, tf, 0};
+    DL4J_CUDA_TRY(cudaMalloc(&e.fwd.wp, (size_t)e.fwd.rows_p * e.fwd.Kp * sizeof(float)));
+    if (with_bwd_data) {
+        ConvGeom gb = conv_geom_bwd_data(d, z_cs);
+        const int flip = tf && conv_tc_gemm_can_tma(gb);
+        e.bwd = PackJob{w, nullptr, 0ULL, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, dl4j_round_up(x_cs > d->c_in ? x_cs : d->c_in, 256), 1, tf, flip};
+        DL4J_CUDA_TRY(cudaMalloc(&e.bwd.wp, (size_t)e.bwd.rows_p * e.bwd.Kp * sizeof(float)));
+    }
+    r->entries[w] = e;
+    r->table_dirty = true;
+    r->valid = false;  // nothing is packed until the next dl4jb200_filters_repack
+    return DL4JB200_OK;
+}
+
+int dl4jb200_filters_repack(dl4jb200_ctx *ctx) {
+    DL4J_REQUIRE(ctx, "filters_repack: ctx is NULL");
+    FilterRegistry *r = ctx->filters;
+    if (!r || r->entries.empty()) return DL4JB200_OK;
+    if (r->table_dirty) {
+        std::vector<PackJob> jobs;
+        unsigned long long total = 0;
+        for (auto &kv : r->entries)
+            for (PackJob *j : {&kv.second.fwd, &kv.second.bwd}) {
+                if (!j->wp) continue;
+                j->start = total;
+                total += (unsigned long long)j->rows_p * j->Kp;
+                jobs.push_back(*j);
+            }
+        std::sort(jobs.begin(), jobs.end(), [](const PackJob &a, const PackJob &b) { return a.start < b.start; });
+        if (r->jobs_dev) { DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream)); cudaFree(r->jobs_dev); r->jobs_dev = nullptr; }
+        DL4J_CUDA_TRY(cudaMalloc(&r->jobs_dev, jobs.size() * sizeof(PackJob)));
+        DL4J_CUDA_TRY(cudaMemcpyAsync(r->jobs_dev, jobs.data(), jobs.size() * sizeof(PackJob), cudaMemcpyHostToDevice, ctx->stream));
+        DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));  // `jobs` is a stack vector
+        r->njobs = (int)jobs.size();
+        r->total = total;
+        r->table_dirty = false;
+    }
+    k_pack_filters_batched<<<grid_for(ctx, (size_t)r->total), 256, 0, ctx->stream>>>(r->jobs_dev, r->njobs, r->total);
+    DL4J_CHECK_LAUNCH();
+    r->valid = true;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_filters_invalidate(dl4jb200_ctx *ctx) {
+    DL4J_REQUIRE(ctx, "filters_invalidate: ctx is NULL");
+    if (ctx->filters) ctx->filters->valid = false;
     return DL4JB200_OK;
 }
 
@@ -364,13 +511,17 @@ int dl4jb200_conv_bwd_data_fused(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d,
     DL4J_REQUIRE(delta_cs >= gb.Cg, "conv_bwd_data_fused: delta pixel stride %d < %d", delta_cs, gb.Cg);
     const int rows_b = dl4j_round_up(dx_cs > d->c_in ? dx_cs : d->c_in, 256);
     const size_t pack_f = (size_t)rows_b * gb.Kp;
-    float *wb = (float *)dl4j_workspace(ctx, 0, pack_f * sizeof(float));
-    if (!wb) return DL4JB200_ERR_CUDA;
-    k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, 1, 1);
-    DL4J_CHECK_LAUNCH();
+    const float *wq = filters_lookup(ctx, w, true, gb.Cg, gb.Kp, rows_b, 1, 1);
+    if (!wq) {
+        float *wb = (float *)dl4j_workspace(ctx, 0, pack_f * sizeof(float));
+        if (!wb) return DL4JB200_ERR_CUDA;
+        k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, 1, 1);
+        DL4J_CHECK_LAUNCH();
+        wq = wb;
+    }
     gb.epi_add = eps_sum;
     gb.epi_mask = mask;
-    return conv_tc_gemm(ctx, gb, delta, wb, rows_b, nullptr, dx, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY | (ctx->round_act ? 0x100 : 0));
+    return conv_tc_gemm(ctx, gb, delta, wq, rows_b, nullptr, dx, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY | (ctx->round_act ? 0x100 : 0));
 }
 
 }  // extern "C"

@@ -66,6 +66,27 @@ class Network:
             self.pidx[(name, key)] = (off, int(np.prod(shp)), shp, pk)
         self._plan()
         torch.cuda.synchronize(self.dev)  # allocations / fills above ran on torch's default stream
+        self.prepack = True
+        self._register_filters()
+        self.params_changed()
+
+    # ------------------------------------------------------------------ pre-packed filters
+    def _register_filters(self):
+        """Every convolution / dense filter view of the flat parameter vector is registered once with the context; one
+        dl4jb200_filters_repack launch after each parameter update then replaces the per-call pack kernels."""
+        for v in self.model["vertices"]:
+            n, op = v["name"], v["op"]
+            if op not in ("conv", "dense", "output") or (self.stem and self.stem[0] == n):
+                continue
+            src, d = self._conv_desc(v) if op == "conv" else (v["in"][0], self._dense_desc(v))
+            _, xcs = self._src(src)
+            pw, _, _, _ = self._p(n, "W")
+            self._call("dl4jb200_filter_register", C.byref(d), pw, xcs, self.cs[n], self.algo, int(self._needs_eps(src)))
+
+    def params_changed(self):
+        """Call after anything other than update() wrote the flat parameter vector (broadcast, parameter averaging)."""
+        if self.prepack:
+            self._call("dl4jb200_filters_repack")
 
     # ------------------------------------------------------------------ planning
     def _buf(self, *shape, dtype=None):
@@ -536,6 +557,7 @@ class Network:
         self._call("dl4jb200_updater_apply_segments", self._ptr(self.params), self._ptr(self.grads), self._ptr(self.state), self.P,
                    self._ptr(self.seg_start), self._ptr(self.seg_cfg), len(self.layout), self.seg_cfg_host, self.n_cfg, div,
                    self._ptr(self.score_reg) if self.with_score else None)
+        self.params_changed()
 
     def _grad_normalize(self):
         """GradientNormalization over each layer's gradient view (BaseMultiLayerUpdater.java:322-380)."""
@@ -573,6 +595,7 @@ class Network:
                 st = self._ptr(self.state, off)
             self._call("dl4jb200_updater_apply", self._ptr(self.params, off), self._ptr(self.grads, off), st, n, kind,
                        float(lr), float(h1), float(h2), float(l1), float(l2), div)
+        self.params_changed()
 
     def score_terms(self):
         """Queues the L1/L2 part of the score (BaseOutputLayer.java:82-100): call before update()."""

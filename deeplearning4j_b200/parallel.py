@@ -70,6 +70,7 @@ class ParallelWrapper:
         with torch.cuda.stream(net.stream):
             dist.broadcast(net.params, src=0)
             dist.broadcast(net.state, src=0)
+        net.params_changed()
 
     def _hook(self, net):
         with self.torch.cuda.stream(net.stream):
@@ -84,4 +85,5 @@ class ParallelWrapper:
         if self.iter % self.freq == 0:
             with self.torch.cuda.stream(net.stream):
                 average_parameters(self.dist, net.params, net.state, self.world, self.avg_upd)
+            net.params_changed()
         return score

@@ -249,6 +249,20 @@ int dl4jb200_lrn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, float 
 /* ElementWiseVertex Add (+ following ActivationLayer ReLU): out = act(a + b); backward mask from out.
  * NN/nn/graph/vertex/impl/ElementWiseVertex.java:81-86,126-131; NN/nn/layers/ActivationLayer.java:68-92 */
 int dl4jb200_add_act_fwd(dl4jb200_ctx *ctx, const float *a, const float *b, float *out, size_t n, int act);
+/* Pre-packed filters. conv_fwd / conv_bwd re-pack the DL4J-layout filter W[c_out,c_in,kH,kW]
+ * (ConvolutionParamInitializer.java:144-155) into GEMM operand layout on every call. A caller that knows when the
+ * parameters change (once per iteration: StochasticGradientDescent.java:78, params.subi(update)) registers each filter
+ * view once -- with the pixel strides its convolution calls use -- and calls dl4jb200_filters_repack after every
+ * parameter update: one launch re-packs every registered filter, and conv_fwd / conv_bwd / conv_bwd_data_fused calls
+ * whose `w` is registered use the stored operand instead of launching their own pack kernel. Registration allocates
+ * (cudaMalloc); repack does not, except for the job table the first time. Until the first repack, after a new
+ * registration, or after dl4jb200_filters_invalidate, calls pack on the fly as before. Not using these three entry
+ * points changes nothing. */
+int dl4jb200_filter_register(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *w, int x_cs, int z_cs, int algo,
+                             int with_bwd_data);
+int dl4jb200_filters_repack(dl4jb200_ctx *ctx);
+int dl4jb200_filters_invalidate(dl4jb200_ctx *ctx);
+
 /* Epsilon fan-in and activation backprop of one vertex in a single pass: delta = act'(act_out) * (a + b)
  * (NN/nn/graph/ComputationGraph.java:2044-2063 followed by NN/nn/layers/ActivationLayer.java:68-92). In place allowed. */
 int dl4jb200_eps_sum_act_bwd(dl4jb200_ctx *ctx, const float *a, const float *b, const float *act_out, float *delta, size_t n,

@@ -267,6 +267,58 @@ def test_conv_bias_gradient_rides_in_filter_gemm(H, ctx, oracle, case):
         dev.free()
 
 
+def test_prepacked_filters_match_per_call_packing(H, oracle):
+    """filter_register + filters_repack: registered filters give bit-identical conv_fwd / conv_bwd / fused results, follow
+    the parameters after a repack, and fall back to per-call packing after filters_invalidate."""
+    from deeplearning4j_b200 import _lib
+    ctx = H.Context(0)  # own context: the registry lives in it
+    rng = np.random.default_rng(21)
+    B, Cin, Hh, W, Cout, k = 2, 64, 10, 10, 96, (3, 3)
+    x = rng.random((B, Cin, Hh, W), dtype=np.float32)
+    w = (rng.standard_normal((Cout, Cin) + k) * 0.2).astype(np.float32)
+    w2 = (rng.standard_normal((Cout, Cin) + k) * 0.2).astype(np.float32)
+    d = H.conv_desc(x.shape, Cout, k, (1, 1), (1, 1), (1, 1), "Same")
+    delta = rng.standard_normal((B, Cout, d.out_h, d.out_w)).astype(np.float32)
+    dev = Dev(ctx)
+    try:
+        px, pw, pd = dev.put(to_nhwc(x)), dev.put(w), dev.put(to_nhwc(delta))
+        launches = _lib.cdll().dl4jb200_launch_count
+
+        def run():
+            pz, pdx = dev.empty(B * Hh * W * Cout * 4), dev.empty(B * Hh * W * Cin * 4)
+            n0 = launches()
+            _lib.call("dl4jb200_conv_fwd", ctx.handle, C.byref(d), px, H.NHWC, Cin, pw, None, pz, H.NHWC, Cout, 0, H.ALGO_TC_TF32)
+            _lib.call("dl4jb200_conv_bwd", ctx.handle, C.byref(d), px, H.NHWC, Cin, pw, pd, H.NHWC, Cout, None, None, pdx, H.NHWC, Cin,
+                      H.ALGO_TC_TF32)
+            return dev.get(pz, (B, Hh, W, Cout)), dev.get(pdx, (B, Hh, W, Cin)), launches() - n0
+
+        z0, dx0, l0 = run()
+        _lib.call("dl4jb200_filter_register", ctx.handle, C.byref(d), pw, Cin, Cout, H.ALGO_TC_TF32, 1)
+        z1, dx1, l1 = run()                      # registered but never packed: still per-call
+        assert l1 == l0
+        _lib.call("dl4jb200_filters_repack", ctx.handle)
+        z2, dx2, l2 = run()
+        assert l2 == l0 - 2                      # both pack kernels gone
+        for a, b in ((z0, z1), (z0, z2), (dx0, dx1), (dx0, dx2)):
+            np.testing.assert_array_equal(a, b)
+        _lib.call("dl4jb200_memcpy_h2d", ctx.handle, pw, w2.ctypes.data_as(C.c_void_p), w2.nbytes)  # "the updater ran"
+        _lib.call("dl4jb200_filters_repack", ctx.handle)
+        z3, dx3, _ = run()
+        zr = oracle.conv_fwd(x, w2, None, stride=(1, 1), pad=(1, 1), dilation=(1, 1), mode=2)
+        assert rel_err(from_nhwc(z3, Cout), zr) <= TOL_CONV_TF32
+        assert np.abs(z3 - z0).max() > 0.1
+        _lib.call("dl4jb200_filters_invalidate", ctx.handle)
+        z4, dx4, l4 = run()
+        assert l4 == l0
+        np.testing.assert_array_equal(z3, z4)
+        np.testing.assert_array_equal(dx3, dx4)
+        with pytest.raises(Exception):
+            _lib.call("dl4jb200_filter_register", ctx.handle, C.byref(d), pw, Cin, Cout, H.ALGO_TC_TF32, 1)
+    finally:
+        dev.free()
+        ctx.close()
+
+
 def test_conv_invalid_shapes_raise_like_reference(H, ctx):
     from deeplearning4j_b200 import DL4JInvalidConfigException, DL4JInvalidInputException
     helper = H.CudnnConvolutionHelper(ctx)
