@@ -28,6 +28,17 @@ __device__ __forceinline__ void bn_mask_coef(const BnMask &mk, int c, int C, flo
     } else { a = 0.f; b = 0.f; }
 }
 
+// NHWC: grid (G, S). Block (g, s) reduces rows [s*rows_per, (s+1)*rows_per) of the 32-channel group g (8 channel
+// quads = one 128-byte line per pixel). 256 threads = 8 quads x 32 row lanes, 4 independent 128-bit loads in flight per
+// thread. A channel therefore has only S <= ~600/G partial rows for the finalize kernel to fold (the fold is a
+// latency-bound tail on the critical path), instead of one row per block of the whole launch.
+static inline int bn_nhwc_groups(int cs) { return (cs / 4 + 7) / 8; }
+static inline int bn_nhwc_splits(int sm_count, int cs, long long M) {
+    long long G = bn_nhwc_groups(cs), cap = ((long long)sm_count * 4 + G - 1) / G, by_rows = M / 128;
+    long long S = cap < by_rows ? cap : by_rows;
+    return (int)(S < 1 ? 1 : S);
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__restrict__ x, const float *__restrict__ e,
                                                                 BnMask mk,
@@ -37,76 +48,76 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nhwc(const float *__r
     pdl_trigger();
     pdl_wait();
     const int Q = cs >> 2;
-    const int rows_per_blk = (M + gridDim.x - 1) / gridDim.x;
-    const int r0 = blockIdx.x * rows_per_blk, r1 = min(M, r0 + rows_per_blk);
-    for (int qb = 0; qb < Q; qb += BN_THREADS) {
-        const int qc = min(BN_THREADS, Q - qb);   // quads handled in this sweep
-        const int R = BN_THREADS / qc;            // rows in flight per iteration
-        const int q = qb + (threadIdx.x % qc), rl = threadIdx.x / qc;
-        float4 a1 = make_float4(0, 0, 0, 0), a2 = a1;
-        if (rl < R) {
-            // forward pivot = first row of the tensor; backward centre = saved mean (stride 1 array)
-            float4 k;
-            if (MODE == 0) k = *reinterpret_cast<const float4 *>(center + (size_t)q * 4);
-            else {
-                int c = q * 4;
-                k.x = c + 0 < center_stride ? center[c + 0] : 0.f; k.y = c + 1 < center_stride ? center[c + 1] : 0.f;
-                k.z = c + 2 < center_stride ? center[c + 2] : 0.f; k.w = c + 3 < center_stride ? center[c + 3] : 0.f;
-            }
-            float4 ma = make_float4(0, 0, 0, 0), mb = ma;
-            if (MODE == 1 && mk.relu) {
-                int c = q * 4;
-                bn_mask_coef(mk, c, center_stride, ma.x, mb.x); bn_mask_coef(mk, c + 1, center_stride, ma.y, mb.y);
-                bn_mask_coef(mk, c + 2, center_stride, ma.z, mb.z); bn_mask_coef(mk, c + 3, center_stride, ma.w, mb.w);
-            }
-            constexpr int U = 4;  // independent loads in flight per thread (latency hiding)
-            for (int rb = r0 + rl; rb < r1; rb += U * R) {
-                float4 v[U], g[U];
+    constexpr int R = BN_THREADS / 8;  // row lanes
+    const int q = blockIdx.x * 8 + (threadIdx.x & 7), rl = threadIdx.x >> 3;
+    const int rows_per_blk = (M + gridDim.y - 1) / gridDim.y;
+    const int r0 = blockIdx.y * rows_per_blk, r1 = min(M, r0 + rows_per_blk);
+    float4 a1 = make_float4(0, 0, 0, 0), a2 = a1;
+    if (q < Q) {
+        // forward pivot = first row of the tensor; backward centre = saved mean (stride 1 array)
+        float4 k;
+        if (MODE == 0) k = *reinterpret_cast<const float4 *>(center + (size_t)q * 4);
+        else {
+            int c = q * 4;
+            k.x = c + 0 < center_stride ? center[c + 0] : 0.f; k.y = c + 1 < center_stride ? center[c + 1] : 0.f;
+            k.z = c + 2 < center_stride ? center[c + 2] : 0.f; k.w = c + 3 < center_stride ? center[c + 3] : 0.f;
+        }
+        float4 ma = make_float4(0, 0, 0, 0), mb = ma;
+        if (MODE == 1 && mk.relu) {
+            int c = q * 4;
+            bn_mask_coef(mk, c, center_stride, ma.x, mb.x); bn_mask_coef(mk, c + 1, center_stride, ma.y, mb.y);
+            bn_mask_coef(mk, c + 2, center_stride, ma.z, mb.z); bn_mask_coef(mk, c + 3, center_stride, ma.w, mb.w);
+        }
+        constexpr int U = 4;  // independent loads in flight per thread (latency hiding)
+        for (int rb = r0 + rl; rb < r1; rb += U * R) {
+            float4 v[U], g[U];
 #pragma unroll
-                for (int u = 0; u < U; u++) {
-                    int r = rb + u * R;
-                    size_t o = (size_t)r * cs + (size_t)q * 4;
-                    if (r < r1) {
-                        v[u] = *reinterpret_cast<const float4 *>(x + o);
-                        if (MODE == 1) {
-                            g[u] = *reinterpret_cast<const float4 *>(e + o);
-                        }
-                    }
+            for (int u = 0; u < U; u++) {
+                int r = rb + u * R;
+                size_t o = (size_t)r * cs + (size_t)q * 4;
+                if (r < r1) {
+                    v[u] = *reinterpret_cast<const float4 *>(x + o);
+                    if (MODE == 1) g[u] = *reinterpret_cast<const float4 *>(e + o);
                 }
+            }
 #pragma unroll
-                for (int u = 0; u < U; u++) {
-                    if (rb + u * R >= r1) break;
-                    float4 w = v[u];
-                    w.x -= k.x; w.y -= k.y; w.z -= k.z; w.w -= k.w;
-                    if (MODE == 0) {
-                        a1.x += w.x; a1.y += w.y; a1.z += w.z; a1.w += w.w;
-                        a2.x += w.x * w.x; a2.y += w.y * w.y; a2.z += w.z * w.z; a2.w += w.w * w.w;
-                    } else {
-                        float4 gg = g[u];
-                        if (mk.relu) {
-                            gg.x = w.x * ma.x + mb.x > 0.f ? gg.x : 0.f; gg.y = w.y * ma.y + mb.y > 0.f ? gg.y : 0.f;
-                            gg.z = w.z * ma.z + mb.z > 0.f ? gg.z : 0.f; gg.w = w.w * ma.w + mb.w > 0.f ? gg.w : 0.f;
-                        }
-                        a1.x += gg.x; a1.y += gg.y; a1.z += gg.z; a1.w += gg.w;
-                        a2.x += gg.x * w.x; a2.y += gg.y * w.y; a2.z += gg.z * w.z; a2.w += gg.w * w.w;
+            for (int u = 0; u < U; u++) {
+                if (rb + u * R >= r1) break;
+                float4 w = v[u];
+                w.x -= k.x; w.y -= k.y; w.z -= k.z; w.w -= k.w;
+                if (MODE == 0) {
+                    a1.x += w.x; a1.y += w.y; a1.z += w.z; a1.w += w.w;
+                    a2.x += w.x * w.x; a2.y += w.y * w.y; a2.z += w.z * w.z; a2.w += w.w * w.w;
+                } else {
+                    float4 gg = g[u];
+                    if (mk.relu) {
+                        gg.x = w.x * ma.x + mb.x > 0.f ? gg.x : 0.f; gg.y = w.y * ma.y + mb.y > 0.f ? gg.y : 0.f;
+                        gg.z = w.z * ma.z + mb.z > 0.f ? gg.z : 0.f; gg.w = w.w * ma.w + mb.w > 0.f ? gg.w : 0.f;
                     }
+                    a1.x += gg.x; a1.y += gg.y; a1.z += gg.z; a1.w += gg.w;
+                    a2.x += gg.x * w.x; a2.y += gg.y * w.y; a2.z += gg.z * w.z; a2.w += gg.w * w.w;
                 }
             }
         }
-        red[0][threadIdx.x] = a1;
-        red[1][threadIdx.x] = a2;
-        __syncthreads();
-        if (rl == 0) {
-            for (int j = 1; j < R; j++) {
-                float4 b1 = red[0][threadIdx.x + j * qc], b2 = red[1][threadIdx.x + j * qc];
-                a1.x += b1.x; a1.y += b1.y; a1.z += b1.z; a1.w += b1.w;
-                a2.x += b2.x; a2.y += b2.y; a2.z += b2.z; a2.w += b2.w;
-            }
-            float *p = partial + (size_t)blockIdx.x * 2 * cs;
-            *reinterpret_cast<float4 *>(p + (size_t)q * 4) = a1;
-            *reinterpret_cast<float4 *>(p + cs + (size_t)q * 4) = a2;
+    }
+    red[0][threadIdx.x] = a1;
+    red[1][threadIdx.x] = a2;
+    __syncthreads();
+    // tree over the 32 row lanes (offsets are multiples of 8, so a quad lane only ever meets itself); fixed shape
+    for (int o = BN_THREADS / 2; o >= 8; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+            float4 b1 = red[0][threadIdx.x + o], b2 = red[1][threadIdx.x + o];
+            float4 c1 = red[0][threadIdx.x], c2 = red[1][threadIdx.x];
+            c1.x += b1.x; c1.y += b1.y; c1.z += b1.z; c1.w += b1.w;
+            c2.x += b2.x; c2.y += b2.y; c2.z += b2.z; c2.w += b2.w;
+            red[0][threadIdx.x] = c1; red[1][threadIdx.x] = c2;
         }
         __syncthreads();
+    }
+    if (threadIdx.x < 8 && q < Q) {
+        float *p = partial + (size_t)blockIdx.y * 2 * cs;
+        *reinterpret_cast<float4 *>(p + (size_t)q * 4) = red[0][threadIdx.x];
+        *reinterpret_cast<float4 *>(p + cs + (size_t)q * 4) = red[1][threadIdx.x];
     }
 }
 
@@ -372,10 +383,7 @@ static int bn_plan(dl4jb200_ctx *ctx, int B, int C, int H, int W, int layout, in
     long long HW = (long long)H * W, M = (long long)B * HW;
     if (layout == DL4JB200_NHWC) {
         p.cpad = cs;
-        int Q = cs / 4, qc = Q < BN_THREADS ? Q : BN_THREADS, R = BN_THREADS / qc;
-        long long want = M / ((long long)R * 8);
-        long long cap = (long long)ctx->sm_count * 4;
-        p.nblk = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+        p.nblk = bn_nhwc_splits(ctx->sm_count, cs, M);
         p.chunk = 0;
     } else {
         p.cpad = C;
@@ -422,7 +430,7 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
     const size_t total = (size_t)M * (layout == DL4JB200_NHWC ? cs : C);
     if (training) {
         if (layout == DL4JB200_NHWC) {
-            DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_partial_nhwc<0>, dim3(p.nblk), dim3(BN_THREADS), 0, ctx->stream, x, nullptr,
+            DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_partial_nhwc<0>, dim3(bn_nhwc_groups(cs), p.nblk), dim3(BN_THREADS), 0, ctx->stream, x, nullptr,
                                           BnMask{nullptr, nullptr, nullptr, 0}, x, cs, p.partial, (int)M, cs));
         } else {
             dim3 grid(C, p.nblk);
@@ -468,7 +476,7 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
     const float *mask_beta = relu ? p.coef + 4 * (size_t)p.cpad : nullptr;
     bool vec = (HW % 4 == 0) && al16(x) && al16(eps) && al16(dx);
     if (layout == DL4JB200_NHWC) {
-        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_partial_nhwc<1>, dim3(p.nblk), dim3(BN_THREADS), 0, ctx->stream, x, eps, mk, save_mean, C, p.partial,
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_partial_nhwc<1>, dim3(bn_nhwc_groups(cs), p.nblk), dim3(BN_THREADS), 0, ctx->stream, x, eps, mk, save_mean, C, p.partial,
                                       (int)M, cs));
     } else {
         dim3 grid(C, p.nblk);
@@ -562,9 +570,7 @@ extern "C" int dl4jb200_bn_fwd_noalloc(dl4jb200_ctx *ctx, const float *x, float 
     int nblk;
     long long chunk = 0;
     if (layout == DL4JB200_NHWC) {
-        int Q = cs / 4, qc = Q < BN_THREADS ? Q : BN_THREADS, R = BN_THREADS / qc;
-        long long want = M / ((long long)R * 8), cap = (long long)ctx->sm_count * 4;
-        nblk = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+        nblk = bn_nhwc_splits(ctx->sm_count, cs, M);
         if (nblk > max_blk) nblk = max_blk;
     } else {
         long long cap = ((long long)ctx->sm_count * 8 + C - 1) / C, s = M / 4096;
@@ -578,7 +584,7 @@ extern "C" int dl4jb200_bn_fwd_noalloc(dl4jb200_ctx *ctx, const float *x, float 
     const size_t total = (size_t)M * cpad;
     if (training) {
         if (layout == DL4JB200_NHWC) {
-            k_bn_partial_nhwc<0><<<nblk, BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, x, cs, partial, (int)M, cs);
+            k_bn_partial_nhwc<0><<<dim3(bn_nhwc_groups(cs), nblk), BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, x, cs, partial, (int)M, cs);
         } else {
             dim3 grid(C, nblk);
             if ((HW % 4 == 0) && al16(x)) k_bn_partial_nchw<0, true><<<grid, BN_THREADS, 0, ctx->stream>>>(x, nullptr, BnMask{nullptr, nullptr, nullptr, 0}, nullptr, partial, B, C, HW, chunk);
