@@ -75,17 +75,18 @@ __global__ void __launch_bounds__(256) k_pack_filter(const float *__restrict__ w
 struct PackJob {  // device-visible
     const float *w;
     float *wp;
-    unsigned long long start;  // first flat element of this job in the batched index space
+    unsigned long long start;  // unused by the kernel (kept so that a job is self-describing in a debugger)
     int Cout, Cin, kH, kW, Cg, Kp, rows_p, transposed, round_tf32, flip;
 };
+struct PackUnit;
 struct FilterEntry {
     PackJob fwd, bwd;  // bwd.wp == nullptr: no backprop-data operand registered
 };
 struct FilterRegistry {
     std::unordered_map<const float *, FilterEntry> entries;
     PackJob *jobs_dev = nullptr;
-    int njobs = 0;
-    unsigned long long total = 0;
+    PackUnit *units_dev = nullptr;
+    int njobs = 0, nunits = 0;
     bool table_dirty = true, valid = false;
 };
 
@@ -97,28 +98,73 @@ void conv_filters_free(dl4jb200_ctx *ctx) {
         if (kv.second.bwd.wp) cudaFree(kv.second.bwd.wp);
     }
     if (r->jobs_dev) cudaFree(r->jobs_dev);
+    if (r->units_dev) cudaFree(r->units_dev);
     delete r;
     ctx->filters = nullptr;
 }
 
-__global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__restrict__ jobs, int njobs, unsigned long long total) {
-    unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-        int lo = 0, hi = njobs - 1;  // last job whose start <= i
-        while (lo < hi) {
-            int mid = (lo + hi + 1) >> 1;
-            if (__ldg(&jobs[mid].start) <= i) lo = mid; else hi = mid - 1;
+// One block per work unit. Forward operand: a unit is a run of filter rows (co); the source W[co][ci][tap] is read as one
+// contiguous span into shared memory and written out in operand order Wf[co][tap*Cg + ci] (both sides coalesced).
+// Backprop-data operand: a unit is a 32(co) x 32(ci) tile with all its taps; each co row of the tile is a contiguous
+// 32*taps span in W, and the operand rows Wb[ci][tap'*Cg + co] receive 32 consecutive co (128 bytes) per (ci, tap).
+// Padding rows / columns of the operands are zeroed once at registration and never written again.
+struct PackUnit {
+    int job, a, b, pad;  // fwd: a = first row, b = row count; bwd: a = co0, b = ci0
+};
+constexpr int PACK_SMEM_FLOATS = 12288;  // 48 KB
+
+__global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__restrict__ jobs, const PackUnit *__restrict__ units) {
+    extern __shared__ float sm[];
+    const PackUnit u = units[blockIdx.x];
+    const PackJob j = jobs[u.job];
+    const int taps = j.kH * j.kW, row_src = j.Cin * taps;
+    if (!j.transposed) {
+        const int n0 = u.a, rows = u.b;
+        const float *src = j.w + (size_t)n0 * row_src;
+        const int span = rows * row_src;
+        if (taps == 1) {  // operand row = filter row, only the pitch differs
+            for (int e = threadIdx.x; e < span; e += 256) {
+                const int r = e / j.Cin, ci = e - r * j.Cin;
+                const float v = src[e];
+                j.wp[(size_t)(n0 + r) * j.Kp + ci] = j.round_tf32 ? to_tf32_rna(v) : v;
+            }
+            return;
         }
-        const PackJob j = jobs[lo];
-        const unsigned long long e = i - j.start;
-        const int n = (int)(e / j.Kp), k = (int)(e % j.Kp), taps = j.kH * j.kW;
-        const int tap = k / j.Cg, c = k % j.Cg;
-        float v = 0.f;
-        if (tap < taps) {
-            const int co = j.transposed ? c : n, ci = j.transposed ? n : c;
-            if (co < j.Cout && ci < j.Cin) v = j.w[((size_t)co * j.Cin + ci) * taps + (j.flip ? taps - 1 - tap : tap)];
+        const bool staged = span <= PACK_SMEM_FLOATS;
+        if (staged) {
+            for (int e = threadIdx.x; e < span; e += 256) sm[e] = src[e];
+            __syncthreads();
         }
-        j.wp[e] = j.round_tf32 ? to_tf32_rna(v) : v;
+        const int kk = taps * j.Cg;
+        for (int e = threadIdx.x; e < rows * kk; e += 256) {
+            const int r = e / kk, k = e - r * kk, tap = k / j.Cg, ci = k - tap * j.Cg;
+            float v = 0.f;
+            if (ci < j.Cin) {
+                const int o = (r * j.Cin + ci) * taps + (j.flip ? taps - 1 - tap : tap);
+                v = staged ? sm[o] : src[o];
+            }
+            j.wp[(size_t)(n0 + r) * j.Kp + k] = j.round_tf32 ? to_tf32_rna(v) : v;
+        }
+    } else {
+        const int co0 = u.a, ci0 = u.b;
+        const int nco = min(32, j.Cout - co0), nci = min(32, j.Cin - ci0);
+        const int span = nci * taps;  // contiguous floats per co row of the tile
+        const bool staged = 32 * span <= PACK_SMEM_FLOATS;
+        if (staged) {
+            for (int e = threadIdx.x; e < nco * span; e += 256) {
+                const int r = e / span, t = e - r * span;
+                sm[r * span + t] = j.w[((size_t)(co0 + r) * j.Cin + ci0) * taps + t];
+            }
+            __syncthreads();
+        }
+        // destination: row ci, column tap'*Cg + co; lanes run along co
+        for (int e = threadIdx.x; e < nci * taps * 32; e += 256) {
+            const int cl = e & 31, t2 = e >> 5, tap = t2 % taps, il = t2 / taps;
+            if (cl >= nco) continue;
+            const int st = j.flip ? taps - 1 - tap : tap;
+            const float v = staged ? sm[cl * span + il * taps + st] : j.w[((size_t)(co0 + cl) * j.Cin + ci0 + il) * taps + st];
+            j.wp[(size_t)(ci0 + il) * j.Kp + (size_t)tap * j.Cg + co0 + cl] = j.round_tf32 ? to_tf32_rna(v) : v;
+        }
     }
 }
 
@@ -428,11 +474,13 @@ int dl4jb200_filter_register(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, con
     ConvGeom gf = conv_geom_fwd(d, x_cs);
     e.fwd = PackJob{w, nullptr, 0ULL, d->c_out, d->c_in, d->k_h, d->k_w, gf.Cg, gf.Kp, dl4j_round_up(z_cs > d->c_out ? z_cs : d->c_out, 256), 0, tf, 0};
     DL4J_CUDA_TRY(cudaMalloc(&e.fwd.wp, (size_t)e.fwd.rows_p * e.fwd.Kp * sizeof(float)));
+    DL4J_CUDA_TRY(cudaMemsetAsync(e.fwd.wp, 0, (size_t)e.fwd.rows_p * e.fwd.Kp * sizeof(float), ctx->stream));  // padding stays zero
     if (with_bwd_data) {
         ConvGeom gb = conv_geom_bwd_data(d, z_cs);
         const int flip = tf && conv_tc_gemm_can_tma(gb);
         e.bwd = PackJob{w, nullptr, 0ULL, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, dl4j_round_up(x_cs > d->c_in ? x_cs : d->c_in, 256), 1, tf, flip};
         DL4J_CUDA_TRY(cudaMalloc(&e.bwd.wp, (size_t)e.bwd.rows_p * e.bwd.Kp * sizeof(float)));
+        DL4J_CUDA_TRY(cudaMemsetAsync(e.bwd.wp, 0, (size_t)e.bwd.rows_p * e.bwd.Kp * sizeof(float), ctx->stream));
     }
     r->entries[w] = e;
     r->table_dirty = true;
@@ -446,24 +494,42 @@ int dl4jb200_filters_repack(dl4jb200_ctx *ctx) {
     if (!r || r->entries.empty()) return DL4JB200_OK;
     if (r->table_dirty) {
         std::vector<PackJob> jobs;
-        unsigned long long total = 0;
+        std::vector<PackUnit> units;
         for (auto &kv : r->entries)
             for (PackJob *j : {&kv.second.fwd, &kv.second.bwd}) {
                 if (!j->wp) continue;
-                j->start = total;
-                total += (unsigned long long)j->rows_p * j->Kp;
+                const int ji = (int)jobs.size(), taps = j->kH * j->kW;
+                j->start = (unsigned long long)units.size();
                 jobs.push_back(*j);
+                if (!j->transposed) {
+                    long long row = (long long)j->Cin * taps;
+                    int rows_per = (int)(4096 / row);
+                    if (rows_per < 1) rows_per = 1;
+                    for (int n0 = 0; n0 < j->Cout; n0 += rows_per)
+                        units.push_back(PackUnit{ji, n0, j->Cout - n0 < rows_per ? j->Cout - n0 : rows_per, 0});
+                } else {
+                    for (int co0 = 0; co0 < j->Cout; co0 += 32)
+                        for (int ci0 = 0; ci0 < j->Cin; ci0 += 32) units.push_back(PackUnit{ji, co0, ci0, 0});
+                }
             }
-        std::sort(jobs.begin(), jobs.end(), [](const PackJob &a, const PackJob &b) { return a.start < b.start; });
-        if (r->jobs_dev) { DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream)); cudaFree(r->jobs_dev); r->jobs_dev = nullptr; }
+        DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+        if (r->jobs_dev) { cudaFree(r->jobs_dev); r->jobs_dev = nullptr; }
+        if (r->units_dev) { cudaFree(r->units_dev); r->units_dev = nullptr; }
         DL4J_CUDA_TRY(cudaMalloc(&r->jobs_dev, jobs.size() * sizeof(PackJob)));
+        DL4J_CUDA_TRY(cudaMalloc(&r->units_dev, units.size() * sizeof(PackUnit)));
         DL4J_CUDA_TRY(cudaMemcpyAsync(r->jobs_dev, jobs.data(), jobs.size() * sizeof(PackJob), cudaMemcpyHostToDevice, ctx->stream));
-        DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));  // `jobs` is a stack vector
+        DL4J_CUDA_TRY(cudaMemcpyAsync(r->units_dev, units.data(), units.size() * sizeof(PackUnit), cudaMemcpyHostToDevice, ctx->stream));
+        DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));  // the tables are stack vectors
         r->njobs = (int)jobs.size();
-        r->total = total;
+        r->nunits = (int)units.size();
         r->table_dirty = false;
+        static bool configured[16] = {false};
+        if (!configured[ctx->device & 15]) {
+            DL4J_CUDA_TRY(cudaFuncSetAttribute(k_pack_filters_batched, cudaFuncAttributeMaxDynamicSharedMemorySize, PACK_SMEM_FLOATS * 4));
+            configured[ctx->device & 15] = true;
+        }
     }
-    k_pack_filters_batched<<<grid_for(ctx, (size_t)r->total), 256, 0, ctx->stream>>>(r->jobs_dev, r->njobs, r->total);
+    k_pack_filters_batched<<<r->nunits, 256, PACK_SMEM_FLOATS * 4, ctx->stream>>>(r->jobs_dev, r->units_dev);
     DL4J_CHECK_LAUNCH();
     r->valid = true;
     return DL4JB200_OK;
