@@ -252,52 +252,85 @@ struct UpdSegCfg {  // per-configuration constants (few distinct ones per networ
 #define DL4J_MAX_UPD_CFGS 8
 struct UpdCfgTable { UpdSegCfg c[DL4J_MAX_UPD_CFGS]; };
 
+// one element of the segmented updater; returns the new parameter value (state updated in place)
+__device__ __forceinline__ float upd_one(const UpdSegCfg &c, float wi, float gi, float *state, long long i, long long s0,
+                                         long long len, float inv_batch, double &score) {
+    float u;
+    switch (c.kind) {
+    case DL4JB200_UPD_NESTEROVS: {
+        float v = state[i], vn = c.h1 * v - c.lr * gi;
+        u = c.h1 * v - (1.f + c.h1) * vn;
+        state[i] = vn;
+    } break;
+    case DL4JB200_UPD_RMSPROP: {
+        float r = c.h1 * state[i] + (1.f - c.h1) * gi * gi;
+        state[i] = r;
+        u = c.lr * gi / sqrtf(r + c.h2);
+    } break;
+    case DL4JB200_UPD_ADADELTA: {
+        // block-local msg | msdx layout: state[2*start + j] and state[2*start + len + j]
+        const long long j = i - s0;
+        float msg = c.h1 * state[2 * s0 + j] + (1.f - c.h1) * gi * gi, msdx = state[2 * s0 + len + j];
+        u = gi * sqrtf(msdx + c.h2) / sqrtf(msg + c.h2);
+        state[2 * s0 + j] = msg;
+        state[2 * s0 + len + j] = c.h1 * msdx + (1.f - c.h1) * u * u;
+    } break;
+    case DL4JB200_UPD_NOOP: u = 0.f; break;
+    default: u = c.lr * gi;
+    }
+    if (c.l2 > 0.f) { u += c.l2 * wi; score += 0.5 * (double)c.l2 * (double)wi * (double)wi; }
+    if (c.l1 > 0.f) { u += c.l1 * (wi > 0.f ? 1.f : (wi < 0.f ? -1.f : 0.f)); score += (double)c.l1 * fabs((double)wi); }
+    return wi - u * inv_batch;
+}
+
+// A thread owns 4 consecutive elements: one segment search per quad, and when the quad lies inside one segment of a
+// stateless / flat-state updater (everything but AdaDelta's block-local layout) the five streams move as 128-bit accesses.
 __global__ void __launch_bounds__(256) k_updater_segments(float *__restrict__ w, const float *__restrict__ g,
                                                           float *__restrict__ state, long long n,
                                                           const long long *__restrict__ seg_start,
                                                           const int *__restrict__ seg_cfg, int nseg, UpdCfgTable tab,
-                                                          float inv_batch, int adadelta, double *score_partial) {
+                                                          float inv_batch, int vec_ok, double *score_partial) {
     __shared__ double sred[256];
     double score = 0.0;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        int lo = 0, hi = nseg - 1;  // last segment whose start <= i
+    const long long stride = (long long)gridDim.x * blockDim.x, nq = (n + 3) >> 2;
+    for (long long qi = (long long)blockIdx.x * blockDim.x + threadIdx.x; qi < nq; qi += stride) {
+        const long long i0 = qi << 2;
+        int lo = 0, hi = nseg - 1;  // last segment whose start <= i0
         while (lo < hi) {
             int mid = (lo + hi + 1) >> 1;
-            if (seg_start[mid] <= i) lo = mid; else hi = mid - 1;
+            if (__ldg(seg_start + mid) <= i0) lo = mid; else hi = mid - 1;
         }
-        const int ci = seg_cfg[lo];
-        if (ci < 0) continue;  // NoOp segment (BatchNormalization running statistics)
-        const UpdSegCfg c = tab.c[ci];
-        const float gi = g[i], wi = w[i];
-        float u;
-        switch (c.kind) {
-        case DL4JB200_UPD_NESTEROVS: {
-            float v = state[i], vn = c.h1 * v - c.lr * gi;
-            u = c.h1 * v - (1.f + c.h1) * vn;
-            state[i] = vn;
-        } break;
-        case DL4JB200_UPD_RMSPROP: {
-            float r = c.h1 * state[i] + (1.f - c.h1) * gi * gi;
-            state[i] = r;
-            u = c.lr * gi / sqrtf(r + c.h2);
-        } break;
-        case DL4JB200_UPD_ADADELTA: {
-            // block-local msg | msdx layout: state[2*start + j] and state[2*start + len + j]
-            const long long s0 = seg_start[lo], len = seg_start[lo + 1] - s0, j = i - s0;
-            float msg = c.h1 * state[2 * s0 + j] + (1.f - c.h1) * gi * gi, msdx = state[2 * s0 + len + j];
-            u = gi * sqrtf(msdx + c.h2) / sqrtf(msg + c.h2);
-            state[2 * s0 + j] = msg;
-            state[2 * s0 + len + j] = c.h1 * msdx + (1.f - c.h1) * u * u;
-        } break;
-        case DL4JB200_UPD_NOOP: u = 0.f; break;
-        default: u = c.lr * gi;
+        const long long s0 = __ldg(seg_start + lo), s1 = __ldg(seg_start + lo + 1);
+        const int ci = __ldg(seg_cfg + lo);
+        if (i0 + 4 <= s1 && i0 + 4 <= n && vec_ok && (ci < 0 || tab.c[ci].kind != DL4JB200_UPD_ADADELTA)) {
+            if (ci < 0) continue;  // NoOp segment (BatchNormalization running statistics)
+            const UpdSegCfg c = tab.c[ci];
+            float4 wv = *reinterpret_cast<const float4 *>(w + i0);
+            const float4 gv = *reinterpret_cast<const float4 *>(g + i0);
+            const bool has_state = c.kind == DL4JB200_UPD_NESTEROVS || c.kind == DL4JB200_UPD_RMSPROP;
+            float st[4] = {0.f, 0.f, 0.f, 0.f};
+            if (has_state) {
+                const float4 sv = *reinterpret_cast<const float4 *>(state + i0);
+                st[0] = sv.x; st[1] = sv.y; st[2] = sv.z; st[3] = sv.w;
+            }
+            // upd_one indexes state[i]: hand it the register copy with i = lane index
+            wv.x = upd_one(c, wv.x, gv.x, st, 0, 0, 0, inv_batch, score);
+            wv.y = upd_one(c, wv.y, gv.y, st, 1, 0, 0, inv_batch, score);
+            wv.z = upd_one(c, wv.z, gv.z, st, 2, 0, 0, inv_batch, score);
+            wv.w = upd_one(c, wv.w, gv.w, st, 3, 0, 0, inv_batch, score);
+            if (has_state) *reinterpret_cast<float4 *>(state + i0) = make_float4(st[0], st[1], st[2], st[3]);
+            *reinterpret_cast<float4 *>(w + i0) = wv;
+        } else {
+            int seg = lo;
+            for (long long i = i0; i < i0 + 4 && i < n; i++) {
+                while (seg + 1 < nseg && __ldg(seg_start + seg + 1) <= i) seg++;
+                const int cj = __ldg(seg_cfg + seg);
+                if (cj < 0) continue;
+                const long long t0 = __ldg(seg_start + seg), len = __ldg(seg_start + seg + 1) - t0;
+                w[i] = upd_one(tab.c[cj], w[i], g[i], state, i, t0, len, inv_batch, score);
+            }
         }
-        if (c.l2 > 0.f) { u += c.l2 * wi; score += 0.5 * (double)c.l2 * (double)wi * (double)wi; }
-        if (c.l1 > 0.f) { u += c.l1 * (wi > 0.f ? 1.f : (wi < 0.f ? -1.f : 0.f)); score += (double)c.l1 * fabs((double)wi); }
-        w[i] = wi - u * inv_batch;
     }
-    (void)adadelta;
     if (score_partial) {
         sred[threadIdx.x] = score;
         __syncthreads();
@@ -395,14 +428,15 @@ int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g,
     }
     DL4J_REQUIRE(state || !any_state, "updater_apply_segments: state is NULL");
     if (n == 0) return DL4JB200_OK;
-    int nblk = ew_grid(ctx, n, 256);
+    int nblk = ew_grid(ctx, (n + 3) / 4, 256);
     double *partial = nullptr;
     if (score_reg_out) {
         partial = (double *)dl4j_workspace(ctx, 0, (size_t)nblk * sizeof(double));
         if (!partial) return DL4JB200_ERR_CUDA;
     }
+    const int vec_ok = aligned16(w) && aligned16(g) && (!state || aligned16(state));
     k_updater_segments<<<nblk, 256, 0, ctx->stream>>>(w, g, state, (long long)n, (const long long *)seg_start_dev, seg_cfg_dev, nseg,
-                                                      tab, (float)(1.0 / batch_div), 0, partial);
+                                                      tab, (float)(1.0 / batch_div), vec_ok, partial);
     DL4J_CHECK_LAUNCH();
     if (score_reg_out) {
         k_score_fold<<<1, 256, 0, ctx->stream>>>(partial, nblk, score_reg_out);
