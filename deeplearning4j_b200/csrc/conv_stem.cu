@@ -29,8 +29,16 @@ __global__ void __launch_bounds__(256) k_pack_stem_filter(const float *__restric
 
 // dW[co][ci][kh][kw] = sum_s partial[s][co][kh*32 + ((kw+1)>>1)*8 + ((kw+1)&1)*4 + ci]
 __global__ void __launch_bounds__(256) k_stem_wgrad_finalize(const float *__restrict__ partial, float *__restrict__ dw, int Cout,
-                                                             int Cin, int kH, int kW, int Kp, int rows_p, int splits) {
+                                                             int Cin, int kH, int kW, int Kp, int rows_p, int splits,
+                                                             const float *__restrict__ db_partial, float *__restrict__ db) {
     size_t total = (size_t)Cout * Cin * kH * kW, stride = (size_t)gridDim.x * blockDim.x;
+    if (db_partial) {  // [splits][rows_p] sums from the GEMM's ones column
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)Cout; i += stride) {
+            float acc = 0.f;
+            for (int s = 0; s < splits; s++) acc += db_partial[(size_t)s * rows_p + i];
+            db[i] = acc;
+        }
+    }
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
         int kw = (int)(i % kW);
         size_t t = i / kW;
@@ -118,7 +126,7 @@ int dl4jb200_conv_rowpack_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, co
 }
 
 int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px,
-                                const float *delta, int delta_cs, float *dw) {
+                                const float *delta, int delta_cs, float *dw, float *db) {
     int rc = stem_check(ctx, d, row_pitch_px, "conv_rowpack_wgrad");
     if (rc) return rc;
     DL4J_REQUIRE(xp && delta && dw && delta_cs >= d->c_out && delta_cs % 4 == 0 && ((uintptr_t)delta & 15) == 0 && ((uintptr_t)xp & 15) == 0,
@@ -128,8 +136,12 @@ int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, 
     g.Kp = Kp; g.M = M;
     const int splits = conv_tc_wgrad_splits(ctx, g, d->c_out);
     const int mps = dl4j_round_up(dl4j_ceil_div(M, splits), 32);
-    float *partial = (float *)dl4j_workspace(ctx, 0, (size_t)splits * rows_w * Kp * sizeof(float));
+    // db: with TF32-representable deltas (DL4JB200_OPT_TF32_ACTIVATIONS) it rides in the GEMM as a ones column, else it is
+    // the plain column-sum pass
+    const bool db_fused = db && ctx->round_act;
+    float *partial = (float *)dl4j_workspace(ctx, 0, ((size_t)splits * rows_w * Kp + (db_fused ? (size_t)splits * rows_w : 0)) * sizeof(float));
     if (!partial) return DL4JB200_ERR_CUDA;
+    float *dbp = db_fused ? partial + (size_t)splits * rows_w * Kp : nullptr;
     alignas(64) CUtensorMap tmD, tmX;
     if ((rc = tma_make_2d(&tmD, delta, (uint64_t)M, (uint64_t)delta_cs, (uint64_t)delta_cs, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))) return rc;
     if ((rc = stem_xmap(&tmX, d, xp, row_pitch_px, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))) return rc;
@@ -137,11 +149,12 @@ int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, 
     t.M = M; t.kW = 1; t.dH = 1; t.dW = 1; t.sH = d->stride_h; t.sW = 1; t.lowH = -d->pad_top; t.lowW = 0; t.Kp = Kp;
     t.div_Wm = FastDiv((uint32_t)d->out_w); t.div_HWm = FastDiv((uint32_t)(d->out_h * d->out_w));
     t.div_Cg = FastDiv(32u); t.div_kW = FastDiv(1u);
-    if ((rc = conv_tc_wgrad_tma_raw(ctx, tmD, tmX, t, partial, rows_w, splits, mps))) return rc;
+    if ((rc = conv_tc_wgrad_tma_raw(ctx, tmD, tmX, t, partial, rows_w, splits, mps, dbp))) return rc;
     size_t total = (size_t)d->c_out * d->c_in * d->k_h * d->k_w;
     k_stem_wgrad_finalize<<<dl4j_ceil_div((long long)total, 256), 256, 0, ctx->stream>>>(partial, dw, d->c_out, d->c_in, d->k_h, d->k_w,
-                                                                                    Kp, rows_w, splits);
+                                                                                    Kp, rows_w, splits, dbp, db);
     DL4J_CHECK_LAUNCH();
+    if (db && !db_fused) return dl4jb200_bias_grad(ctx, delta, M, delta_cs, d->c_out, db);
     return DL4JB200_OK;
 }
 

@@ -674,7 +674,11 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
     auto tfull_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + b); };
     auto tempty_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + 2 + b); };
-    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4), bres_bar = bar_base + 8u * (2 * STAGES + 5);
+    // B-resident mode: every tile of this CTA uses the same filter columns (one N tile) and the whole K extent of the
+    // filter fits the ring's B slots, so B is fetched ONCE per CTA instead of once per tile and only A streams. The 7x7/2
+    // stem (25 088 tiles per launch, 7 K-chunks each) was bound by exactly that L2 -> SM re-fetch.
+    const bool bres = n_tiles == 1 && g.num_k <= STAGES;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
@@ -682,6 +686,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
         tma::prefetch_desc(&tmB);
         for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         for (int b = 0; b < 2; b++) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 256); }
+        mbar_init(bres_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 4) tmem_alloc<2 * BN>(tmem_slot);
@@ -695,6 +700,10 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
         // ------------------------------ TMA producer
         if (lane == 0) {
             int kit = 0;
+            if (bres && (int)blockIdx.x < total_tiles) {
+                tma::expect_tx(bres_bar, (uint32_t)(g.num_k * L::B_BYTES));
+                for (int it = 0; it < g.num_k; ++it) tma::load_2d(b_base + it * L::B_BYTES, &tmB, bres_bar, it * BLOCK_K, 0);
+            }
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
                 const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * BN;
                 uint32_t img, r, oy, ox;
@@ -707,10 +716,10 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                     uint32_t tap, c0, kh, kw;
                     g.div_Cg.divmod((uint32_t)(it * BLOCK_K), tap, c0);
                     g.div_kW.divmod(tap, kh, kw);
-                    tma::expect_tx(full_bar(s), (uint32_t)(L::A_BYTES + L::B_BYTES));
+                    tma::expect_tx(full_bar(s), (uint32_t)(bres ? L::A_BYTES : L::A_BYTES + L::B_BYTES));
                     tma::load_im2col_4d(a_base + s * L::A_BYTES, &tmA, full_bar(s), (int)c0, w0, h0, (int)img,
                                         (uint16_t)(kw * g.dW), (uint16_t)(kh * g.dH));
-                    tma::load_2d(b_base + s * L::B_BYTES, &tmB, full_bar(s), it * BLOCK_K, n0);
+                    if (!bres) tma::load_2d(b_base + s * L::B_BYTES, &tmB, full_bar(s), it * BLOCK_K, n0);
                 }
             }
         }
@@ -719,6 +728,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
         // ------------------------------ MMA issuer
         constexpr uint32_t idesc = umma_idesc(BLOCK_M, BN, 0, 0);
         int kit = 0, i = 0;
+        if (bres && (int)blockIdx.x < total_tiles) mbar_wait(bres_bar, 0);
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
             const int buf = i & 1;
             mbar_wait(tempty_bar(buf), ((i >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
@@ -730,7 +740,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                 tc_fence_after();
                 if (lane == 0) {
                     const uint64_t ad = umma_desc(a_base + s * L::A_BYTES, 16, 1024);
-                    const uint64_t bd = umma_desc(b_base + s * L::B_BYTES, 16, 1024);
+                    const uint64_t bd = umma_desc(b_base + (bres ? it : s) * L::B_BYTES, 16, 1024);
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / 8; k++) umma_tf32(acc, ad + 2u * k, bd + 2u * k, idesc, (it | k) ? 1u : 0u);
                     umma_commit(empty_bar(s));
@@ -1090,6 +1100,8 @@ static int launch_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, co
     return DL4JB200_OK;
 }
 
+// k-columns per filter-gradient tile (256-wide tiles were measured 5-15 % slower on every ResNet-50 shape: one CTA per SM
+// instead of two loses more overlap than the smaller operand traffic per MMA step wins)
 static inline int wgrad_bn(const ConvGeom &g) { return g.Kp >= 128 ? 128 : (g.Kp >= 64 ? 64 : 32); }
 
 }  // namespace tc
@@ -1206,16 +1218,18 @@ int conv_tc_gemm_tma_raw(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtens
     }
     if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
     if (bn == 128) return tc::launch_gemm_tma_persist<128, 5>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    if (bn == 64 && t.num_k == 7 && out_cs <= 64)  // 7-row stem filters: one more stage lets the filter stay resident
+        return tc::launch_gemm_tma_persist<64, 7>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
     if (bn == 64) return tc::launch_gemm_tma_persist<64, 6>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
     return tc::launch_gemm_tma_persist<32, 6>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
 }
 
 int conv_tc_wgrad_tma_raw(dl4jb200_ctx *ctx, const CUtensorMap &tmD, const CUtensorMap &tmX, const TmaWgradGeom &t, float *partial,
-                          int rows_p, int splits, int m_per_split) {
+                          int rows_p, int splits, int m_per_split, float *db_partial) {
     const int bn = t.Kp >= 128 ? 128 : (t.Kp >= 64 ? 64 : 32);
     switch (bn) {
-    case 128: return tc::launch_wgrad_tma<128, 3>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split, nullptr);
-    case 64: return tc::launch_wgrad_tma<64, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split, nullptr);
-    default: return tc::launch_wgrad_tma<32, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split, nullptr);
+    case 128: return tc::launch_wgrad_tma<128, 3>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split, db_partial);
+    case 64: return tc::launch_wgrad_tma<64, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split, db_partial);
+    default: return tc::launch_wgrad_tma<32, 4>(ctx, tmD, tmX, t, partial, rows_p, splits, m_per_split, db_partial);
     }
 }

@@ -56,7 +56,7 @@ struct TmaWgradGeom {
 int conv_tc_gemm_tma_raw(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const tcgeom::TmaGemmGeom &t,
                          const float *bias, float *out, int n_valid, int out_cs, int act, int bn);
 int conv_tc_wgrad_tma_raw(dl4jb200_ctx *ctx, const CUtensorMap &tmD, const CUtensorMap &tmX, const tcgeom::TmaWgradGeom &t,
-                          float *partial, int rows_p, int splits, int m_per_split);
+                          float *partial, int rows_p, int splits, int m_per_split, float *db_partial = nullptr);
 
 #ifdef __CUDACC__
 namespace tma {

@@ -466,8 +466,7 @@ class Network:
                     self.side_stream.wait_event(fork)
                     self._side_used = True
                 if self.stem and self.stem[0] == n:
-                    wcall("dl4jb200_conv_rowpack_wgrad", C.byref(d), self._ptr(x), self.stem[1], self._ptr(e), self.cs[n], gw)
-                    wcall("dl4jb200_bias_grad", self._ptr(e), B * d.out_h * d.out_w, self.cs[n], d.c_out, gb)
+                    wcall("dl4jb200_conv_rowpack_wgrad", C.byref(d), self._ptr(x), self.stem[1], self._ptr(e), self.cs[n], gw, gb)
                 else:
                     wcall("dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
                           gw, gb, None, L.NHWC, xcs, self.algo)

@@ -177,8 +177,10 @@ int dl4jb200_nchw_to_rowpack4(dl4jb200_ctx *ctx, const float *src, float *dst, i
                               int x_off);
 int dl4jb200_conv_rowpack_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px, const float *w,
                               const float *bias, float *z, int z_cs, int act);
+/* db may be NULL (filter gradient only); otherwise the bias gradient is produced too (inside the GEMM when
+ * DL4JB200_OPT_TF32_ACTIVATIONS is on, by a column-sum pass otherwise). */
 int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px,
-                                const float *delta, int delta_cs, float *dw);
+                                const float *delta, int delta_cs, float *dw, float *db);
 
 /* ConvolutionHelper.activate (ConvolutionHelper.java:45) and IActivation.backprop
  * (ConvolutionLayer.java:171): elementwise over n floats; in place allowed (a == z, delta == eps). */

@@ -626,9 +626,20 @@ def test_rowpacked_stem_conv_vs_oracle(H, ctx, oracle, case):
         assert rel_err(z, zr) <= TOL_CONV_TF32, rel_err(z, zr)
         pd = dev.put(to_nhwc(delta, zcs))
         pdw, pdb = dev.empty(w.nbytes), dev.empty(Cout * 4)
-        _lib.call("dl4jb200_conv_rowpack_wgrad", ctx.handle, C.byref(d), pxp, pitch, pd, zcs, pdw)
+        _lib.call("dl4jb200_conv_rowpack_wgrad", ctx.handle, C.byref(d), pxp, pitch, pd, zcs, pdw, None)
         _lib.call("dl4jb200_bias_grad", ctx.handle, pd, B * d.out_h * d.out_w, zcs, Cout, pdb)
         assert rel_err(dev.get(pdw, w.shape), dwr) <= TOL_CONV_TF32
         assert rel_err(dev.get(pdb, (Cout,)), dbr) <= 1e-5
+        # db through the entry point itself: column-sum pass (option off), ones column of the GEMM (option on, TF32-exact delta)
+        from oracle.net_oracle import tf32_round
+        dq = tf32_round(delta)
+        pdq = dev.put(to_nhwc(dq, zcs))
+        dbq = dq.sum(axis=(0, 2, 3), dtype=np.float64)
+        for opt in (0, 1):
+            _lib.call("dl4jb200_ctx_set_option", ctx.handle, _lib.OPT_TF32_ACTIVATIONS, opt)
+            pdw2, pdb2 = dev.empty(w.nbytes), dev.empty(Cout * 4)
+            _lib.call("dl4jb200_conv_rowpack_wgrad", ctx.handle, C.byref(d), pxp, pitch, pdq, zcs, pdw2, pdb2)
+            assert rel_err(dev.get(pdb2, (Cout,)), dbq) <= 1e-5, opt
     finally:
+        _lib.call("dl4jb200_ctx_set_option", ctx.handle, _lib.OPT_TF32_ACTIVATIONS, 0)
         dev.free()
