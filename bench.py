@@ -95,6 +95,20 @@ def conv_flops(net):
     return out
 
 
+def conv_alg_bytes(net):
+    """Algorithmic DRAM bytes of all convolution / dense passes of one step: forward reads x and writes z; backward reads
+    x and delta for the filter gradient and delta again, writing dx, for the data gradient (filters are negligible)."""
+    B, tot = net.B, 0.0
+    for v in net.model["vertices"]:
+        if v["op"] not in ("conv", "dense", "output"):
+            continue
+        so, si = net.shapes[v["name"]], net.shapes[v["in"][0]]
+        nout, nin = float(B) * float(np.prod(so)), float(B) * float(np.prod(si))
+        first = net.vmap[v["in"][0]]["op"] in ("input", "zeropad")
+        tot += 4.0 * (nin + nout) * (2 if first else 3)
+    return tot
+
+
 def run_reference(args, rank, world):
     """The reference arm: the reference's CPU algorithm for the same step, timed on the host cores (rank 0 only)."""
     if rank != 0:
@@ -145,6 +159,11 @@ def main():
     if args.impl == "reference":
         return run_reference(args, rank, world)
     args.warmup = max(args.warmup, 3)
+    # stdout carries exactly one JSON line: native libraries (the NCCL version banner) write to fd 1 directly, so fd 1 is
+    # pointed at stderr for the run and the line goes to a private duplicate of the original stdout
+    sys.stdout.flush()
+    json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist
@@ -275,10 +294,21 @@ def main():
         conv_fl += f * psteps
         n_conv_calls += calls
         per_layer[f"{tag}:conv_{ps}"] = {"ms": tms / psteps, "tflops": f / (tms / psteps * 1e-3) / 1e12}
+    # DRAM bytes of the same kernel family from the committed ncu capture (cold-cache, serialised): per call, like `achieved`
+    traffic, traffic_note = None, "no ncu capture found"
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_conv_traffic.json")))
+        traffic = (tr["dram_read_bytes"] + tr["dram_write_bytes"]) / max(1, n_conv_calls // psteps)
+        traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum of the %d convolution-family launches of one step "
+                        "(profiles/r01_conv_traffic.json, batch 256) / calls per step; algorithmic bytes per step: %.2f GB"
+                        % (tr["launches"], conv_alg_bytes(net) / 1e9))
+    except Exception:  # noqa: BLE001
+        pass
     tf32_peak = pk["bf16_tflops_sustained"] / 2.0
     ach = conv_fl / (conv_ms * 1e-3) / 1e12 if conv_ms else 0.0
     roofline = {"bound": "tensor", "kernel": "k_conv_tc_gemm_tma_persist / k_conv_tc_wgrad_tma (all convolution + dense calls of the step)",
-                "achieved": ach, "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak, "traffic": None,
+                "achieved": ach, "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak, "traffic": traffic,
+                "traffic_note": traffic_note,
                 "peak_note": f"TF32 dense = 0.5 x bf16_tflops_sustained ({pk['src']}); kernel timed inside a long step",
                 "share_of_step": conv_ms / (ms_eager * psteps), "calls_per_step": n_conv_calls // psteps,
                 "timing": "CUDA events per call in an eager single-stream pass of the same step (%.2f ms/step eager serial vs %.2f ms/step graph with overlapped filter gradients)" % (ms_eager, ms / args.steps)}
@@ -343,7 +373,8 @@ def main():
     }
     if cpu:
         line["cpu_baseline"] = cpu
-    print(json.dumps(line))
+    json_out.write(json.dumps(line) + "\n")
+    json_out.flush()
     finish()
 
 
