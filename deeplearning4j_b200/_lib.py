@@ -87,6 +87,7 @@ PROTOTYPES = {
     "dl4jb200_filter_register": [_vp, _vp, _vp, _i, _i, _i, _i],
     "dl4jb200_filters_repack": [_vp],
     "dl4jb200_filters_invalidate": [_vp],
+    "dl4jb200_dropout_fwd": [_vp, _vp, _vp, _vp, _sz, _d],
     "dl4jb200_eps_sum_act_bwd": [_vp, _vp, _vp, _vp, _vp, _sz, _i],
     "dl4jb200_conv_bwd_data_fused": [_vp, _vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _i, _i],
     "dl4jb200_accumulate": [_vp, _vp, _vp, _sz],

@@ -106,6 +106,23 @@ __global__ void __launch_bounds__(256) k_add_act(const float *__restrict__ a, co
     }
 }
 
+// inverted dropout with a caller-supplied 0/1 mask: y = x * mask / p   (nd4j DropOutInverted as Dropout.applyDropout uses it)
+template <bool VEC>
+__global__ void __launch_bounds__(256) k_dropout(const float *__restrict__ x, const float *__restrict__ m, float *__restrict__ y,
+                                                 size_t n, float inv_p, int rnd) {
+    size_t stride = (size_t)gridDim.x * blockDim.x, i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (VEC) {
+        size_t n4 = n >> 2;
+        for (; i < n4; i += stride) {
+            float4 v = reinterpret_cast<const float4 *>(x)[i], k = reinterpret_cast<const float4 *>(m)[i];
+            v.x = v.x * k.x * inv_p; v.y = v.y * k.y * inv_p; v.z = v.z * k.z * inv_p; v.w = v.w * k.w * inv_p;
+            reinterpret_cast<float4 *>(y)[i] = dl4j_rnd4(v, rnd);
+        }
+    } else {
+        for (; i < n; i += stride) y[i] = dl4j_rnd(x[i] * m[i] * inv_p, rnd);
+    }
+}
+
 // epsilon fan-in + activation backprop in one pass: d = (a + b) * act'(y)
 template <bool VEC>
 __global__ void __launch_bounds__(256) k_sum_act_bwd(const float *__restrict__ a, const float *__restrict__ b,
@@ -498,6 +515,19 @@ int dl4jb200_add_act_fwd(dl4jb200_ctx *ctx, const float *a, const float *b, floa
         k_add_act<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(a, b, out, n, act, ctx->round_act);
     else
         k_add_act<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(a, b, out, n, act, ctx->round_act);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+int dl4jb200_dropout_fwd(dl4jb200_ctx *ctx, const float *x, const float *mask, float *y, size_t n, double retain_prob) {
+    DL4J_REQUIRE(ctx && x && mask && y, "dropout_fwd: NULL argument");
+    DL4J_REQUIRE(retain_prob > 0.0 && retain_prob <= 1.0, "dropout_fwd: retain probability must be in (0, 1]");
+    if (n == 0) return DL4JB200_OK;
+    const float inv_p = (float)(1.0 / retain_prob);
+    if ((n & 3) == 0 && aligned16(x) && aligned16(mask) && aligned16(y))
+        k_dropout<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(x, mask, y, n, inv_p, ctx->round_act);
+    else
+        k_dropout<false><<<ew_grid(ctx, n, 256), 256, 0, ctx->stream>>>(x, mask, y, n, inv_p, ctx->round_act);
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }

@@ -47,6 +47,7 @@ class Network:
         self.round_tf32 = (algo == _lib.ALGO_TC_TF32) if round_tf32 is None else bool(round_tf32)
         for ctx in (h, h2):
             _lib.call("dl4jb200_ctx_set_option", ctx, _lib.OPT_TF32_ACTIVATIONS, int(self.round_tf32))
+        self.drop, self.mask = {}, {}
         self.overlap_wgrad = True
         self.fuse_dgrad = True  # epsilon fan-in + ReLU backprop in the backprop-data epilogue (_emit_dgrad)
         self.launches = 0
@@ -225,6 +226,48 @@ class Network:
             u = self.vmap[u]["in"][0]
         return self.out[u], self.cs[u]
 
+    def _lin(self, n, src):
+        """(tensor, cs) of the INPUT of layer n: the output of src, or its dropped copy when n has dropout and masks are
+        set (AbstractLayer.applyDropOutIfNecessary replaces the layer's input; backprop then uses that dropped input)."""
+        x, xcs = self._src(src)
+        d = self.drop.get(n)
+        return (d, xcs) if d is not None else (x, xcs)
+
+    def set_dropout_masks(self, masks):
+        """masks: {layer name: 0/1 float array shaped like that layer's input in DL4J layout ([B,C,H,W] or [B,K])}, for
+        every vertex with a "dropout" retain probability; None switches dropout off again. The masks are inputs because
+        nd4j's DropOutInverted random stream cannot be reproduced outside nd4j."""
+        t = self.torch
+        self.drop, self.mask = {}, {}
+        if not masks:
+            return
+        for v in self.model["vertices"]:
+            n, op = v["name"], v["op"]
+            if not v.get("dropout"):
+                continue
+            if op not in ("conv", "dense", "output", "pool") or (self.stem and self.stem[0] == n) or n in self.fold_pad:
+                raise NotImplementedError(f"dropout on {op} vertex {n}")
+            x, xcs = self._src(v["in"][0])
+            m = np.ascontiguousarray(masks[n], np.float32)
+            with t.cuda.stream(self.stream):
+                dev = t.zeros_like(x)
+                if m.ndim == 4:
+                    Bb, Cc, Hh, Ww = m.shape
+                    tmp = t.from_numpy(m).to(self.dev)
+                    self._call("dl4jb200_nchw_to_nhwc", self._ptr(tmp), self._ptr(dev), Bb, Cc, Hh, Ww, xcs)
+                    self.stream.synchronize()  # tmp is released when this scope ends
+                else:
+                    dev.view(self.B, -1)[:, :m.shape[1]].copy_(t.from_numpy(m).to(self.dev))
+                self.mask[n] = dev
+                self.drop[n] = t.zeros_like(x)
+
+    def _apply_dropout(self, v, train):
+        n = v["name"]
+        if train and n in self.drop:
+            x, _ = self._src(v["in"][0])
+            self._call("dl4jb200_dropout_fwd", self._ptr(x), self._ptr(self.mask[n]), self._ptr(self.drop[n]), x.numel(),
+                       float(v["dropout"]))
+
     def _conv_desc(self, v):
         n = v["name"]
         if n in self.fold_pad:
@@ -280,7 +323,8 @@ class Network:
                 continue
             if op == "conv":
                 src, d = self._conv_desc(v)
-                x, xcs = self._src(src)
+                self._apply_dropout(v, train)
+                x, xcs = self._lin(n, src)
                 pw, _, _, _ = self._p(n, "W")
                 pb, _, _, _ = self._p(n, "b")
                 if self.stem and self.stem[0] == n:
@@ -308,7 +352,8 @@ class Network:
                            int(self.model["minibatch"]), act, res)
             elif op == "pool":
                 d = self._pool_desc(v)
-                x, xcs = self._src(v["in"][0])
+                self._apply_dropout(v, train)
+                x, xcs = self._lin(n, v["in"][0])
                 am = self._ptr(self.aux[n]) if v["type"] == "MAX" else None
                 self._call("dl4jb200_pool_fwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), am, L.NHWC, xcs, self.cs[n],
                            _POOL[v["type"]], int(v.get("pnorm", 2)))
@@ -329,7 +374,8 @@ class Network:
                 if dst is not self.out[n]:
                     self._call("dl4jb200_copy2d", self._ptr(dst), chw, self._ptr(self.out[n]), self.cs[n], B, chw)
             elif op in ("dense", "output"):
-                x, xcs = self._src(v["in"][0])
+                self._apply_dropout(v, train)
+                x, xcs = self._lin(n, v["in"][0])
                 d = self._dense_desc(v)
                 pw, _, _, _ = self._p(n, "W")
                 pb, _, _, _ = self._p(n, "b")
@@ -454,7 +500,7 @@ class Network:
                     src, d = self._conv_desc(v)
                 else:
                     src, d = v["in"][0], self._dense_desc(v)
-                x, xcs = self._src(src)
+                x, xcs = self._lin(n, src)
                 pw, gw, _, _ = self._p(n, "W")
                 _, gb, _, _ = self._p(n, "b")
 
@@ -482,7 +528,7 @@ class Network:
                                                     self._ptr(ss), _ACT[v["act"]], dx, gg, gbeta, B, s[0], s[1], s[2], L.NHWC, xcs))
             elif op == "pool":
                 u = v["in"][0]
-                x, xcs = self._src(u)
+                x, xcs = self._lin(n, u)
                 d = self._pool_desc(v)
                 am = self._ptr(self.aux[n]) if v["type"] == "MAX" else None
                 self._emit(u, lambda dx: self._call("dl4jb200_pool_bwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), self._ptr(e), am,

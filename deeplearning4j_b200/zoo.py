@@ -65,9 +65,11 @@ def vgg16(num_labels=1000, input_shape=(3, 224, 224)):
             "grad_norm": None, "seed": 123}
 
 
-def alexnet(num_labels=1000, input_shape=(3, 224, 224)):
-    """ZOO/model/AlexNet.java:84-130 with the global dropOut(0.5) disabled (parity runs must feed identical
-    masks to both sides or switch dropout off; nd4j's DropOutInverted RNG is not available here)."""
+def alexnet(num_labels=1000, input_shape=(3, 224, 224), dropout=None):
+    """ZOO/model/AlexNet.java:84-130. The zoo config's global dropOut(0.5) puts inverted dropout (retain 0.5) on the INPUT
+    of every layer, conv1 and the pooling layers included (AbstractLayer.java:360-374); pass dropout=0.5 to get it --
+    the masks are then inputs of the step (Network.set_dropout_masks / OracleNet.masks), because nd4j's DropOutInverted
+    random stream is not available outside nd4j. Default: off."""
     v = [{"name": "input", "op": "input", "in": []},
          _conv("cnn1", "input", 64, (11, 11), (4, 4), (2, 2), act=RELU),
          _pool("maxpool1", "cnn1", "MAX", (3, 3), (2, 2), (1, 1)),
@@ -81,6 +83,10 @@ def alexnet(num_labels=1000, input_shape=(3, 224, 224)):
          {"name": "ffn1", "op": "dense", "in": ["flat"], "nOut": 4096, "act": RELU},
          {"name": "ffn2", "op": "dense", "in": ["ffn1"], "nOut": 4096, "act": RELU},
          {"name": "output", "op": "output", "in": ["ffn2"], "nOut": num_labels}]
+    if dropout:
+        for vv in v[1:]:
+            if vv["op"] in ("conv", "pool", "dense", "output"):
+                vv["dropout"] = float(dropout)
     return {"name": "alexnet", "input": tuple(input_shape), "vertices": v, "weight_init": ("normal", 0.01),
             "updater": {"kind": "nesterovs", "lr": 1e-2, "momentum": 0.9},
             "bias_updater": {"kind": "nesterovs", "lr": 2e-2, "momentum": 0.9},

@@ -265,6 +265,13 @@ int dl4jb200_filter_register(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, con
 int dl4jb200_filters_repack(dl4jb200_ctx *ctx);
 int dl4jb200_filters_invalidate(dl4jb200_ctx *ctx);
 
+/* Inverted dropout on a layer's input, AbstractLayer.applyDropOutIfNecessary (NN/nn/layers/AbstractLayer.java:360-374) ->
+ * Dropout.applyDropout (NN/nn/conf/dropout/Dropout.java:75): y = x * mask / retain_prob with a caller-supplied 0/1 mask in
+ * the tensor's own layout (nd4j's DropOutInverted RNG stream is not reproducible outside nd4j, so the mask is an input).
+ * The reference has no dropout backprop step in this version: the layer's gradients are taken at the dropped input and
+ * the epsilon it returns travels on unmasked. In place allowed. */
+int dl4jb200_dropout_fwd(dl4jb200_ctx *ctx, const float *x, const float *mask, float *y, size_t n, double retain_prob);
+
 /* Epsilon fan-in and activation backprop of one vertex in a single pass: delta = act'(act_out) * (a + b)
  * (NN/nn/graph/ComputationGraph.java:2044-2063 followed by NN/nn/layers/ActivationLayer.java:68-92). In place allowed. */
 int dl4jb200_eps_sum_act_bwd(dl4jb200_ctx *ctx, const float *a, const float *b, const float *act_out, float *delta, size_t n,

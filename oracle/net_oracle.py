@@ -47,6 +47,17 @@ class OracleNet:
         self.state = np.zeros(P * (2 if k == "adadelta" else 1), np.float32)
         self.pidx = {(n, key): (off, int(np.prod(shp)), shp, pk) for n, key, off, shp, pk in layout}
         self.vmap = {v["name"]: v for v in model["vertices"]}
+        self.masks = None  # {layer name: 0/1 array shaped like the layer's input}: dropout is on when set
+
+    def _layer_input(self, v, a, train):
+        """AbstractLayer.applyDropOutIfNecessary (AbstractLayer.java:360-374): in training the layer's input becomes
+        x * mask / p (nd4j DropOutInverted, Dropout.java:75); backprop uses that dropped input, and there is no dropout
+        backprop step -- the epsilon the layer returns goes to the previous layer unmasked."""
+        p = v.get("dropout")
+        if train and p and self.masks is not None:
+            a = self._q((a * self.masks[v["name"]].reshape(a.shape).astype(np.float32) * np.float32(1.0 / p)).astype(np.float32))
+        self.lin[v["name"]] = a
+        return a
 
     def _p(self, n, key, arr=None):
         off, cnt, shp, _ = self.pidx[(n, key)]
@@ -57,6 +68,7 @@ class OracleNet:
         m = self.model
         act = {}
         self.bn_saved = {}
+        self.lin = {}
         for v in m["vertices"]:
             n, op = v["name"], v["op"]
             if op == "input":
@@ -67,6 +79,7 @@ class OracleNet:
                 t, b, l, r = v["pad"]
                 act[n] = np.pad(a, ((0, 0), (0, 0), (t, b), (l, r)))
             elif op == "conv":
+                a = self._layer_input(v, a, train)
                 f = o.conv_fwd_im2col if self.fast else o.conv_fwd
                 z = f(self._t(a), self._q(self._p(n, "W")), self._p(n, "b"), stride=v["stride"], pad=v["pad"],
                       dilation=v["dilation"], mode=_MODE[v["mode"]])
@@ -78,6 +91,7 @@ class OracleNet:
                 y = o.act_fwd(y, _ACT[v["act"]]) if v["act"] != "identity" else y
                 act[n] = y if n in self.unrounded else self._q(y)
             elif op == "pool":
+                a = self._layer_input(v, a, train)
                 act[n] = self._q(o.pool_fwd(a, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]]))
             elif op == "add":
                 s = a + act[v["in"][1]]
@@ -87,6 +101,7 @@ class OracleNet:
             elif op == "flatten":
                 act[n] = a.reshape(a.shape[0], -1)
             elif op in ("dense", "output"):
+                a = self._layer_input(v, a, train)
                 if self.fast:
                     z = self._t(a) @ self._q(self._p(n, "W")).T + self._p(n, "b")[None, :]
                 else:
@@ -126,7 +141,7 @@ class OracleNet:
             elif op == "conv":
                 d = self._q(o.act_bwd(act[n], e, _ACT[v["act"]])) if v["act"] == "relu" else e
                 f = o.conv_bwd_im2col if self.fast else o.conv_bwd
-                dw, db, dx = f(self._t(act[u]), self._q(self._p(n, "W")), self._t(d), stride=v["stride"], pad=v["pad"],
+                dw, db, dx = f(self._t(self.lin[n]), self._q(self._p(n, "W")), self._t(d), stride=v["stride"], pad=v["pad"],
                                dilation=v["dilation"], mode=_MODE[v["mode"]])
                 if self.tf32:  # the bias gradient is a plain fp32 column sum of the stored delta, no tensor core
                     db = d.sum(axis=(0, 2, 3), dtype=np.float64).astype(np.float32)
@@ -136,9 +151,9 @@ class OracleNet:
             elif op in ("dense", "output"):
                 d = self._q(o.act_bwd(act[n], e, _ACT[v["act"]])) if (op == "dense" and v["act"] == "relu") else e
                 if self.fast:
-                    dwf, db, dx = self._t(d).T @ self._t(act[u]), d.sum(0), self._t(d) @ self._q(self._p(n, "W"))
+                    dwf, db, dx = self._t(d).T @ self._t(self.lin[n]), d.sum(0), self._t(d) @ self._q(self._p(n, "W"))
                 else:
-                    dwf, db, dx = o.dense_bwd(self._t(act[u]), self._q(self._p(n, "W")), self._t(d))
+                    dwf, db, dx = o.dense_bwd(self._t(self.lin[n]), self._q(self._p(n, "W")), self._t(d))
                     if self.tf32:
                         db = d.sum(axis=0, dtype=np.float64).astype(np.float32)
                 self._p(n, "W", self.grads)[...] = dwf
@@ -154,7 +169,7 @@ class OracleNet:
                 self._p(n, "var", self.grads)[...] = 0
                 give(u, self._q(dx))
             elif op == "pool":
-                give(u, self._q(o.pool_bwd(act[u], e, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]])))
+                give(u, self._q(o.pool_bwd(self.lin[n], e, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]])))
             elif op in ("add", "act"):
                 d = self._q(o.act_bwd(act[n], e, _ACT[v["act"]])) if v["act"] == "relu" else e
                 for uu in v["in"]:

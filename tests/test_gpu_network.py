@@ -228,3 +228,46 @@ def test_alexnet_step_parity_with_gradient_normalisation():
     from deeplearning4j_b200 import _lib, zoo
     m = zoo.alexnet(num_labels=10, input_shape=(3, 64, 64))
     _run_case(m, 4, 10, _lib.ALGO_FP32, 2, False, 2e-4, 2e-4, 2e-4)
+
+
+def test_alexnet_step_parity_with_dropout_masks():
+    """The zoo AlexNet configuration as it is (global dropOut(0.5): inverted dropout on the input of every layer, conv1
+    and the pooling layers included), with host-generated Bernoulli(0.5) masks fed to both sides; FP32 mode, two
+    iterations with fresh masks each."""
+    from deeplearning4j_b200 import _lib, network, zoo
+    from oracle.net_oracle import OracleNet
+    m = zoo.alexnet(num_labels=10, input_shape=(3, 64, 64), dropout=0.5)
+    B = 4
+    P, layout = zoo.param_layout(m)
+    p0 = zoo.init_params(m)
+    x, lab = _data(m, B, 10)
+    shapes = zoo.infer_shapes(m)
+    ref = OracleNet(m, layout, P, p0, fast=False)
+    net = network.Network(m, B, algo=_lib.ALGO_FP32, params=p0)
+    rng = np.random.default_rng(99)
+    try:
+        for it in range(2):
+            masks = {}
+            for v in m["vertices"]:
+                if v.get("dropout"):
+                    si = shapes[v["in"][0]]
+                    shp = (B,) + tuple(si) if v["op"] in ("conv", "pool") else (B, int(np.prod(si)))
+                    masks[v["name"]] = (rng.random(shp) < 0.5).astype(np.float32)
+            assert len(masks) == 11
+            ref.masks = masks
+            net.set_dropout_masks(masks)
+            s_ref = ref.fit(x, lab)
+            s = net.fit(x, lab)
+            net.sync()
+            assert abs(float(s.cpu()[0]) - s_ref) <= 2e-4 * max(1.0, abs(s_ref))
+            g, p = net.grads.cpu().numpy(), net.params.cpu().numpy()
+            ge = _block_errs(layout, g, ref.grads, 1e-3 * float(np.abs(ref.grads).max()))
+            assert max(ge.values()) <= 2e-4, max(ge.items(), key=lambda kv: kv[1])
+            pe = _block_errs(layout, p, ref.params, 1e-3 * float(np.abs(ref.params).max()), _noise_blocks(layout, ref.grads))
+            assert max(pe.values()) <= 2e-4, max(pe.items(), key=lambda kv: kv[1])
+        # dropout really acted: the same step without masks scores differently
+        net.set_dropout_masks(None)
+        ref.masks = None
+        assert abs(ref.fit(x, lab) - s_ref) > 1e-3
+    finally:
+        net.close()
