@@ -58,6 +58,11 @@ CONV_CASES = [  # B, Cin, H, W, Cout, k, s, p, d, mode
     (5, 3, 23, 23, 64, (11, 11), (4, 4), (2, 2), (1, 1), 1),    # AlexNet conv1 class
     (2, 192, 7, 7, 136, (3, 3), (1, 1), (0, 0), (1, 1), 2),     # ragged N (136 = 128 + 8)
     (1, 8, 4, 4, 8, (3, 3), (1, 1), (0, 0), (1, 1), 2),         # M=16 << one tile
+    # Convolution1DLayer reshapes [B,C,T] to [B,C,T,1] and runs the inherited 2-D code with kernel (k,1), stride (s,1),
+    # pad (p,0) (nn/layers/convolution/Convolution1DLayer.java): the same helper serves it
+    (3, 16, 50, 1, 24, (3, 1), (1, 1), (1, 0), (1, 1), 1),
+    (2, 32, 41, 1, 32, (5, 1), (2, 1), (0, 0), (1, 1), 2),
+    (2, 64, 33, 1, 64, (3, 1), (1, 1), (0, 0), (2, 1), 2),      # dilated, SAME, TMA-eligible channel count
 ]
 
 
@@ -356,6 +361,9 @@ POOL_CASES = [  # B, C, H, W, k, s, p, d, mode
     (2, 3, 8, 8, (2, 2), (2, 2), (0, 0), (1, 1), 0),
     (1, 2, 11, 11, (3, 3), (1, 1), (0, 0), (2, 2), 1),   # dilated
     (2, 8, 4, 4, (3, 3), (2, 2), (0, 0), (1, 1), 1),     # ResNet-50 head pool 4x4 -> 1x1
+    (2, 6, 31, 1, (3, 1), (2, 1), (0, 0), (1, 1), 1),    # Subsampling1DLayer: [B,C,T] as [B,C,T,1], kernel (k,1)
+    (2, 8, 20, 1, (2, 1), (2, 1), (0, 0), (1, 1), 2),    # stride (2,1): width stride 1 keeps it off the 2x2-patch kernel
+    (3, 8, 16, 16, (2, 2), (2, 2), (0, 0), (1, 1), 1),   # 2x2/2 (VGG / LeNet class) on the 2x2-patch backward kernel
 ]
 
 
