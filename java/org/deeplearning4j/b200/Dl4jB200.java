@@ -40,6 +40,18 @@ public class Dl4jB200 {
     public static native int dl4jb200_ctx_sync(@Cast("dl4jb200_ctx*") Pointer ctx);
     public static final int OPT_TF32_ACTIVATIONS = 1;
     public static native int dl4jb200_ctx_set_option(@Cast("dl4jb200_ctx*") Pointer ctx, int option, int value);
+    // optional fast paths (INTEGRATION.md): pre-packed filters, fused epsilon fan-in + ReLU backprop, mask-fed dropout
+    public static native int dl4jb200_filter_register(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer w, int xCs, int zCs, int algo, int withBwdData);
+    public static native int dl4jb200_filters_repack(@Cast("dl4jb200_ctx*") Pointer ctx);
+    public static native int dl4jb200_filters_invalidate(@Cast("dl4jb200_ctx*") Pointer ctx);
+    public static native int dl4jb200_conv_bwd_data_fused(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer w, @Const FloatPointer delta, int deltaCs, FloatPointer dx, int dxCs,
+                    @Const FloatPointer epsSum, @Const FloatPointer actOut, int act, int algo);
+    public static native int dl4jb200_eps_sum_act_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer a, @Const FloatPointer b,
+                    @Const FloatPointer actOut, FloatPointer delta, @Cast("size_t") long n, int act);
+    public static native int dl4jb200_dropout_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, @Const FloatPointer mask,
+                    FloatPointer y, @Cast("size_t") long n, double retainProb);
     public static native int dl4jb200_buf_register(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host, long bytes,
                     @Cast("void**") PointerPointer deviceOut);
     public static native int dl4jb200_buf_upload(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host);
