@@ -200,9 +200,17 @@ __global__ void __launch_bounds__(256) k_wgrad_finalize(const float *__restrict_
         size_t t = i / taps;
         int ci = (int)(t % Cin), co = (int)(t / Cin);
         const float *p = partial + (size_t)co * Kp + (size_t)tap * Cg + ci;
-        float acc = 0.f;
-        for (int s = 0; s < splits; s++) acc += p[(size_t)s * rows_p * Kp];
-        dw[i] = acc;
+        const size_t ss = (size_t)rows_p * Kp;
+        // four independent partial sums: the loads of one round are all in flight together (the fold is latency-bound);
+        // the combination order is fixed, so the result stays deterministic
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        int s = 0;
+        for (; s + 3 < splits; s += 4) {
+            const float v0 = p[(size_t)s * ss], v1 = p[(size_t)(s + 1) * ss], v2 = p[(size_t)(s + 2) * ss], v3 = p[(size_t)(s + 3) * ss];
+            a0 += v0; a1 += v1; a2 += v2; a3 += v3;
+        }
+        for (; s < splits; s++) a0 += p[(size_t)s * ss];
+        dw[i] = (a0 + a1) + (a2 + a3);
     }
 }
 
