@@ -239,8 +239,8 @@ def main():
     # ---- kernel-level pass: the same step issued eagerly with a CUDA-event pair around every conv / BN / pool call
     # (a replayed graph cannot carry per-kernel events); feeds the roofline and the launch count
     net.overlap_wgrad = False  # one stream: every call is timed alone (in the timed regions above the filter gradients overlap the backward chain)
-    net.profile(["dl4jb200_conv_fwd", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_wgrad",
-                 "dl4jb200_bn_fwd", "dl4jb200_bn_bwd", "dl4jb200_pool_fwd", "dl4jb200_pool_bwd"])
+    net.profile(["dl4jb200_conv_fwd", "dl4jb200_conv_fwd_bnstats", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_wgrad",
+                 "dl4jb200_bn_fwd", "dl4jb200_bn_fwd_prestats", "dl4jb200_bn_bwd", "dl4jb200_pool_fwd", "dl4jb200_pool_bwd"])
     psteps = min(args.steps, 10)
     l0 = _lib.cdll().dl4jb200_launch_count()
     p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -280,12 +280,12 @@ def main():
     conv_ms = conv_fl = 0.0
     n_conv_calls = 0
     per_layer = {}
-    conv_fns = ("dl4jb200_conv_fwd", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_rowpack_fwd",
+    conv_fns = ("dl4jb200_conv_fwd", "dl4jb200_conv_fwd_bnstats", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_rowpack_fwd",
                 "dl4jb200_conv_rowpack_wgrad")
     passes = {}  # (layer, "fwd"|"bwd") -> [ms over psteps, calls]: a layer's backward is several calls (filter / data gradient)
     for (fn, tag), times in prof.items():
         if fn in conv_fns and tag in fl:
-            e = passes.setdefault((tag, "fwd" if fn.endswith("fwd") else "bwd"), [0.0, 0])
+            e = passes.setdefault((tag, "fwd" if "_fwd" in fn else "bwd"), [0.0, 0])
             e[0] += sum(times)
             e[1] += len(times)
     for (tag, ps), (tms, calls) in passes.items():
@@ -314,16 +314,17 @@ def main():
                 "timing": "CUDA events per call in an eager single-stream pass of the same step (%.2f ms/step eager serial vs %.2f ms/step graph with overlapped filter gradients)" % (ms_eager, ms / args.steps)}
     # ---- HBM kernels (BN / pool): achieved GB/s on algorithmic bytes
     bw = {}
-    for fn, bpe in (("dl4jb200_bn_fwd", 8), ("dl4jb200_bn_bwd", 12)):
+    # (with the statistics taken in the convolution epilogue the forward is finalize + apply only: same 8 algorithmic B/elem)
+    for key, fns, bpe in (("bn_fwd", ("dl4jb200_bn_fwd", "dl4jb200_bn_fwd_prestats"), 8), ("bn_bwd", ("dl4jb200_bn_bwd",), 12)):
         tot_ms = tot_b = 0.0
         for (f2, tag), times in prof.items():
-            if f2 == fn:
+            if f2 in fns:
                 s = net.shapes[tag]
                 tot_ms += sum(times)
                 tot_b += float(B) * s[0] * s[1] * s[2] * bpe * len(times)
         if tot_ms:
-            bw[fn[9:]] = {"achieved_gbs": tot_b / (tot_ms * 1e-3) / 1e9, "frac_of_hbm": tot_b / (tot_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
-                          "share_of_step": tot_ms / (ms_eager * psteps)}
+            bw[key] = {"achieved_gbs": tot_b / (tot_ms * 1e-3) / 1e9, "frac_of_hbm": tot_b / (tot_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                       "share_of_step": tot_ms / (ms_eager * psteps)}
     for fn in ("dl4jb200_pool_fwd", "dl4jb200_pool_bwd"):
         tot_ms = tot_b = 0.0
         for (f2, tag), times in prof.items():

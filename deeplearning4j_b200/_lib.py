@@ -84,6 +84,9 @@ PROTOTYPES = {
     "dl4jb200_lrn_fwd": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _d, _d, _d, _d],
     "dl4jb200_lrn_bwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _d, _d, _d, _d],
     "dl4jb200_add_act_fwd": [_vp, _vp, _vp, _vp, _sz, _i],
+    "dl4jb200_conv_fwd_bnstats_rows": [_vp, _desc_p, _i, _i, _i, C.POINTER(C.c_int)],
+    "dl4jb200_conv_fwd_bnstats": [_vp, _desc_p, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _vp],
+    "dl4jb200_bn_fwd_prestats": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _d, _d, _i, _i, _vp, _vp, _vp, _i],
     "dl4jb200_filter_register": [_vp, _vp, _vp, _i, _i, _i, _i],
     "dl4jb200_filters_repack": [_vp],
     "dl4jb200_filters_invalidate": [_vp],

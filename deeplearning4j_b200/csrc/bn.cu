@@ -456,6 +456,31 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
     return DL4JB200_OK;
 }
 
+// Training forward on statistics some producer already took (dl4jb200_conv_fwd_bnstats): finalize + apply only.
+int dl4jb200_bn_fwd_prestats(dl4jb200_ctx *ctx, const float *x, float *y, const float *gamma, const float *beta, float *gmean,
+                             float *gvar, float *save_mean, float *save_std, int B, int C, int H, int W, int cs, double decay,
+                             double eps, int minibatch, int act, const float *residual, const float *pivot,
+                             const float *stat_partial, int stat_rows) {
+    DL4J_REQUIRE(ctx && x && y && gmean && gvar && pivot && stat_partial, "bn_fwd_prestats: NULL argument");
+    DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && stat_rows > 0, "bn_fwd_prestats: bad shape");
+    DL4J_REQUIRE(cs == C && cs % 4 == 0 && al16(x) && al16(y) && (!residual || al16(residual)),
+                 "bn_fwd_prestats: NHWC with cs == C, cs %% 4 == 0 and 16-byte aligned tensors");
+    // coefficients live in the context scratch, like bn_fwd's
+    float *coef = (float *)dl4j_workspace(ctx, 0, 5 * (size_t)cs * sizeof(float));
+    if (!coef) return DL4JB200_ERR_CUDA;
+    const long long M = (long long)B * H * W;
+    const size_t total = (size_t)M * cs;
+    // pivot may be gmean itself: k_bn_finalize_fwd reads the pivot of a channel before it updates that channel's gmean
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_fwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, 32), 0, ctx->stream, stat_partial, stat_rows,
+                                  pivot, 1, gamma, beta, gmean, gvar, save_mean, save_std, coef, C, cs, (double)M, decay, eps, 1,
+                                  minibatch));
+    DL4J_CHECK_LAUNCH();
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_apply_nhwc<0>, dim3(bn_grid(ctx, total / 4)), dim3(256), 0, ctx->stream, x, residual, nullptr, y,
+                                  coef, total / 4, cs, act | (ctx->round_act << 8)));
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
 int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const float *gamma, const float *beta,
                     const float *save_mean, const float *save_std, int act, float *dx, float *dgamma, float *dbeta, int B,
                     int C, int H, int W, int layout, int cs) {

@@ -467,6 +467,54 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     return DL4JB200_OK;
 }
 
+// Forward convolution (identity activation) that also leaves the batch-norm statistics of its output, taken in the GEMM
+// epilogue while the tile is on chip: the following BatchNormalization then skips its own partial-sum pass over z.
+static int conv_fwd_stats_geom(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int x_cs, int z_cs, int algo, ConvGeom &g, int &rows_p) {
+    g = conv_geom_fwd(d, x_cs);
+    g.use_tma = algo == DL4JB200_CONV_ALGO_TC_TF32 && x_cs >= g.Cg && conv_tc_gemm_can_tma(g);
+    rows_p = dl4j_round_up(z_cs > d->c_out ? z_cs : d->c_out, 256);
+    return conv_tc_stat_rows(ctx, g, rows_p, d->c_out, z_cs);
+}
+
+int dl4jb200_conv_fwd_bnstats_rows(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int x_cs, int z_cs, int algo, int *rows_out) {
+    DL4J_REQUIRE(ctx && rows_out, "conv_fwd_bnstats_rows: NULL argument");
+    int rc = check_desc(d, "conv_fwd_bnstats_rows");
+    if (rc) return rc;
+    ConvGeom g;
+    int rows_p;
+    *rows_out = (x_cs % 4 == 0 && z_cs % 4 == 0) ? conv_fwd_stats_geom(ctx, d, x_cs, z_cs, algo, g, rows_p) : 0;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_conv_fwd_bnstats(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_cs, const float *w,
+                              const float *bias, float *z, int z_cs, int algo, const float *pivot, float *stat_partial) {
+    DL4J_REQUIRE(ctx && x && w && z && pivot && stat_partial, "conv_fwd_bnstats: NULL argument");
+    int rc = check_desc(d, "conv_fwd_bnstats");
+    if (rc) return rc;
+    if ((rc = check_layout(DL4JB200_NHWC, x_cs, d->c_in, x, "conv_fwd_bnstats", "x"))) return rc;
+    if ((rc = check_layout(DL4JB200_NHWC, z_cs, d->c_out, z, "conv_fwd_bnstats", "z"))) return rc;
+    DL4J_REQUIRE(((uintptr_t)pivot & 15) == 0 && ((uintptr_t)stat_partial & 15) == 0 && (!bias || ((uintptr_t)bias & 15) == 0),
+                 "conv_fwd_bnstats: pivot, stat_partial and bias must be 16-byte aligned");
+    ConvGeom g;
+    int rows_p;
+    if (conv_fwd_stats_geom(ctx, d, x_cs, z_cs, algo, g, rows_p) <= 0) {
+        dl4j_set_error("conv_fwd_bnstats: this convolution cannot carry the statistics (see conv_fwd_bnstats_rows)");
+        return DL4JB200_NOT_SUPPORTED;
+    }
+    const float *wp = filters_lookup(ctx, w, false, g.Cg, g.Kp, rows_p, 1, 0);
+    if (!wp) {
+        float *t = (float *)dl4j_workspace(ctx, 0, (size_t)rows_p * g.Kp * sizeof(float));
+        if (!t) return DL4JB200_ERR_CUDA;
+        k_pack_filter<<<grid_for(ctx, (size_t)rows_p * g.Kp), 256, 0, ctx->stream>>>(w, t, d->c_out, d->c_in, d->k_h, d->k_w, g.Cg, g.Kp,
+                                                                                  rows_p, 0, 1, 0);
+        DL4J_CHECK_LAUNCH();
+        wp = t;
+    }
+    g.stat_out = stat_partial;
+    g.stat_pivot = pivot;
+    return conv_tc_gemm(ctx, g, x, wp, rows_p, bias, z, d->c_out, z_cs, DL4JB200_ACT_IDENTITY);
+}
+
 int dl4jb200_filter_register(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *w, int x_cs, int z_cs, int algo,
                              int with_bwd_data) {
     DL4J_REQUIRE(ctx && w, "filter_register: NULL argument");

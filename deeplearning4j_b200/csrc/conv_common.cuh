@@ -21,6 +21,8 @@ struct ConvGeom {
     FastDiv div_Wm, div_HWm, div_Cg, div_kW;
     // fused epsilon fan-in + activation backprop of the persistent TMA kernel's epilogue (see TmaGemmGeom)
     const float *epi_add = nullptr, *epi_mask = nullptr;
+    float *stat_out = nullptr;          // batch-norm statistics of the output (see TmaGemmGeom)
+    const float *stat_pivot = nullptr;
 };
 
 // tap/channel of a K index (k % 4 == 0 in all callers)
@@ -97,6 +99,7 @@ int conv_ffma_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const 
                     float *partial, int rows_p, int splits);
 int conv_tc_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
                  const float *bias, float *out, int n_valid, int out_cs, int act);
+int conv_tc_stat_rows(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, int n_valid, int out_cs);
 int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const float *delta, int delta_cs, int c_out,
                   float *partial, int rows_p, int splits, float *db_partial = nullptr);
 int conv_tc_wgrad_splits(dl4jb200_ctx *ctx, const ConvGeom &g, int c_out);

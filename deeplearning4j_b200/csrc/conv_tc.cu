@@ -186,6 +186,34 @@ __device__ __forceinline__ void store_tile_32x32_fused(uint32_t stage_smem, cons
     }
 }
 
+// store_tile_32x32 that also accumulates, per lane, sum(t - K) and sum((t - K)^2) of the four columns it stores, over the
+// valid rows: the batch-norm statistics of the convolution's output taken while the tile is still on chip.
+__device__ __forceinline__ void store_tile_32x32_stats(uint32_t stage_smem, const float (&v)[32], int lane, float *out_base,
+                                                       size_t row_stride, int rows_valid, const float4 &K, float4 &s, float4 &q) {
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < 8; p++) {
+        const uint32_t a = stage_smem + (uint32_t)lane * 128u + (uint32_t)((p ^ (lane & 7)) << 4);
+        asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v[p * 4]), "f"(v[p * 4 + 1]), "f"(v[p * 4 + 2]),
+                     "f"(v[p * 4 + 3]) : "memory");
+    }
+    __syncwarp();
+    const int c = lane & 7;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int row = 4 * i + (lane >> 3);
+        float4 t;
+        const uint32_t a = stage_smem + (uint32_t)row * 128u + (uint32_t)((c ^ (row & 7)) << 4);
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(a));
+        if (row < rows_valid) {
+            *reinterpret_cast<float4 *>(out_base + (size_t)row * row_stride + c * 4) = t;
+            const float dx = t.x - K.x, dy = t.y - K.y, dz = t.z - K.z, dw = t.w - K.w;
+            s.x += dx; s.y += dy; s.z += dz; s.w += dw;
+            q.x += dx * dx; q.y += dy * dy; q.z += dz * dz; q.w += dw * dw;
+        }
+    }
+}
+
 // Same, but every row has its own destination (element offset from `out`, or < 0 to skip): output-row scatter.
 __device__ __forceinline__ void store_tile_32x32_rows(uint32_t stage_smem, const float (&v)[32], int lane, float *out,
                                                       const long long (&rowoff)[8], int col0) {
@@ -656,7 +684,7 @@ struct PersistSmem {
     static constexpr int BYTES = BAR_OFF + 256 + 1024;
 };
 
-template <int BN, int STAGES, bool REMAP>
+template <int BN, int STAGES, bool REMAP, bool STATS = false>
 __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const __grid_constant__ CUtensorMap tmA,
                                                                           const __grid_constant__ CUtensorMap tmB,
                                                                           const float *__restrict__ bias,
@@ -756,6 +784,21 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
         // loads / stores in flight per SM: the epilogue of the HBM-bound layers is latency-, not issue-limited.
         const int quad = warp & 3, grp = warp >= 6 ? 1 : 0;
         const uint32_t stage_smem = base + L::STAGING_OFF + (uint32_t)(grp * 4 + quad) * 4096u;
+        // STATS: per-warp running sums of (z - K), (z - K)^2 for the columns of its chunks. The launch is sized so that
+        // gridDim.x is a multiple of n_tiles: every tile of this CTA then has the same column range and the sums stay in
+        // registers until the single flush after the tile loop.
+        constexpr int NCH = STATS ? (BN / 32 + 1) / 2 : 1;
+        float4 st_s[NCH], st_q[NCH], st_k[NCH];
+        if (STATS) {
+#pragma unroll
+            for (int j = 0; j < NCH; j++) {
+                st_s[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                st_q[j] = st_s[j];
+                const int cb = grp + 2 * j;
+                st_k[j] = cb < BN / 32 ? __ldg(reinterpret_cast<const float4 *>(g.stat_pivot + ((int)blockIdx.x % n_tiles) * BN + cb * 32) + (lane & 7))
+                                       : st_s[j];
+            }
+        }
         int i = 0;
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
             const int buf = i & 1;
@@ -800,6 +843,31 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                 continue;
             }
             const int cb_last = NCB == 1 ? 0 : ((NCB - 1 - grp) & ~1) + grp;  // last chunk of this group's parity
+            if (STATS) {  // identity activation, whole tiles only (checked on the host); chunk loop unrolled: static accumulators
+#pragma unroll
+                for (int j = 0; j < NCH; j++) {
+                    const int cb = grp + 2 * j;
+                    if (cb < NCB) {
+                        float v[32];
+                        tmem_ld32(acc + (uint32_t)(cb * 32), v);
+                        if (cb == cb_last) {
+                            tc_fence_before();
+                            mbar_arrive(tempty_bar(buf));
+                        }
+                        const int nb = n0 + cb * 32;
+                        if (bias) {
+#pragma unroll
+                            for (int q = 0; q < 8; q++) {
+                                const float4 bq = __ldg(reinterpret_cast<const float4 *>(bias + nb) + q);
+                                v[q * 4 + 0] += bq.x; v[q * 4 + 1] += bq.y; v[q * 4 + 2] += bq.z; v[q * 4 + 3] += bq.w;
+                            }
+                        }
+                        store_tile_32x32_stats(stage_smem, v, lane, out + (size_t)(m0 + quad * 32) * out_cs + nb, (size_t)out_cs, rows_valid,
+                                               st_k[j], st_s[j], st_q[j]);
+                    }
+                }
+                continue;
+            }
 #pragma unroll 1
             for (int cb = grp; cb < NCB; cb += (NCB == 1 ? 1 : 2)) {
                 float v[32];
@@ -862,10 +930,40 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                 }
             }
         }
+        if (STATS && grp < BN / 32) {
+            // flush: fold the four lanes that hold the same columns (rows r, r+1, r+2, r+3 mod 4 of every group), then
+            // lanes 0-7 write this warp's partial row: stat_out[row_id][0 | 1][column]
+            const int row_id = ((int)blockIdx.x / n_tiles) * 4 + quad, ncol0 = ((int)blockIdx.x % n_tiles) * BN;
+#pragma unroll
+            for (int j = 0; j < NCH; j++) {
+                const int cb = grp + 2 * j;
+                if (cb < BN / 32) {
+                    float4 a = st_s[j], b = st_q[j];
+#pragma unroll
+                    for (int o = 8; o <= 16; o <<= 1) {
+                        a.x += __shfl_xor_sync(0xffffffffu, a.x, o); a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
+                        a.z += __shfl_xor_sync(0xffffffffu, a.z, o); a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
+                        b.x += __shfl_xor_sync(0xffffffffu, b.x, o); b.y += __shfl_xor_sync(0xffffffffu, b.y, o);
+                        b.z += __shfl_xor_sync(0xffffffffu, b.z, o); b.w += __shfl_xor_sync(0xffffffffu, b.w, o);
+                    }
+                    if (lane < 8) {
+                        float *p = g.stat_out + (size_t)row_id * 2 * out_cs + ncol0 + cb * 32 + lane * 4;
+                        *reinterpret_cast<float4 *>(p) = a;
+                        *reinterpret_cast<float4 *>(p + out_cs) = b;
+                    }
+                }
+            }
+        }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 4) tmem_dealloc<2 * BN>(tmem_d);
+}
+
+// grid of a statistics-carrying launch: <= #SMs, <= total tiles, a multiple of n_tiles (0: impossible)
+static inline int persist_stat_grid(int sm_count, int total, int n_tiles) {
+    int g = total < sm_count ? total : sm_count;
+    return g / n_tiles * n_tiles;
 }
 
 template <int BN, int STAGES>
@@ -880,6 +978,21 @@ static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, co
     }
     const int n_tiles = dl4j_ceil_div(out_cs, BN), total = dl4j_ceil_div(g.M, BLOCK_M) * n_tiles;
     const int grid = total < ctx->sm_count ? total : ctx->sm_count;
+    if (g.stat_out) {  // batch-norm statistics in the epilogue: grid a multiple of n_tiles (see the kernel)
+        static bool configured_s[16] = {false};
+        if (!configured_s[ctx->device & 15]) {
+            DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+            configured_s[ctx->device & 15] = true;
+        }
+        const int gs = persist_stat_grid(ctx->sm_count, total, n_tiles);
+        if (g.remap || gs <= 0 || n_valid % BN != 0 || (act & 0xff) != DL4JB200_ACT_IDENTITY || g.epi_add || g.epi_mask) {
+            dl4j_set_error("conv_tc_gemm_tma: this launch cannot carry batch-norm statistics");
+            return DL4JB200_ERR_INVALID_ARG;
+        }
+        k_conv_tc_gemm_tma_persist<BN, STAGES, false, true><<<gs, PTHREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act & 0xff, n_tiles, total);
+        DL4J_CHECK_LAUNCH();
+        return DL4JB200_OK;
+    }
     if (g.remap)
         k_conv_tc_gemm_tma_persist<BN, STAGES, true><<<grid, PTHREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act, n_tiles, total);
     else
@@ -1119,6 +1232,23 @@ bool conv_tc_gemm_can_tma(const ConvGeom &g) {
     return tma_driver_ready();
 }
 
+// N-tile width of the TMA GEMM: 256-wide tiles (one UMMA of N=256, the whole TMEM as a double-buffered accumulator) when the
+// layer is wide and there are still at least ~2 tiles per SM
+static int tma_gemm_bn(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, int out_cs, bool aligned_bias) {
+    const bool wide = aligned_bias && out_cs >= 256 && n_rows_packed % 256 == 0 && g.Kp >= 256 &&
+                      (long long)dl4j_ceil_div(g.M, tc::BLOCK_M) * dl4j_ceil_div(out_cs, 256) >= 2LL * ctx->sm_count;
+    return wide ? 256 : (out_cs > 64 ? 128 : (out_cs > 32 ? 64 : 32));
+}
+
+// partial rows a statistics-carrying forward launch of this geometry writes (0: the launch cannot carry statistics)
+int conv_tc_stat_rows(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, int n_valid, int out_cs) {
+    if (!g.use_tma || g.remap) return 0;
+    const int bn = tma_gemm_bn(ctx, g, n_rows_packed, out_cs, true);
+    if (n_valid % bn != 0 || out_cs != n_valid) return 0;
+    const int n_tiles = out_cs / bn, total = dl4j_ceil_div(g.M, tc::BLOCK_M) * n_tiles;
+    return tc::persist_stat_grid(ctx->sm_count, total, n_tiles) / n_tiles * 4;
+}
+
 static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
                             const float *bias, float *out, int n_valid, int out_cs, int act) {
     // backprop-data runs as a forward walk over delta with flipped taps (the filter is packed flipped, conv.cu)
@@ -1129,11 +1259,7 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
                              CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
     const bool aligned_bias = !bias || ((uintptr_t)bias & 15) == 0;
-    // 256-wide tiles (one UMMA of N=256, the whole TMEM as a double-buffered accumulator) when the layer is wide and
-    // there are still at least ~2 tiles per SM
-    const bool wide = aligned_bias && out_cs >= 256 && n_rows_packed % 256 == 0 && g.Kp >= 256 &&
-                      (long long)dl4j_ceil_div(g.M, tc::BLOCK_M) * dl4j_ceil_div(out_cs, 256) >= 2LL * ctx->sm_count;
-    const int bn = wide ? 256 : (out_cs > 64 ? 128 : (out_cs > 32 ? 64 : 32));
+    const int bn = tma_gemm_bn(ctx, g, n_rows_packed, out_cs, aligned_bias);
     rc = tma_make_2d(&tmB, wpack, (uint64_t)n_rows_packed, (uint64_t)g.Kp, (uint64_t)g.Kp, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
     TmaGemmGeom t;
@@ -1141,6 +1267,8 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
     t.div_Wm = g.div_Wm; t.div_HWm = g.div_HWm; t.div_Cg = g.div_Cg; t.div_kW = g.div_kW;
     t.remap = g.remap; t.rm_sy = g.rm_sy; t.rm_sx = g.rm_sx; t.rm_H = g.rm_H; t.rm_W = g.rm_W;
     t.epi_add = g.epi_add; t.epi_mask = g.epi_mask;
+    t.stat_out = g.stat_out; t.stat_pivot = g.stat_pivot;
+    if (g.stat_out && !aligned_bias) { dl4j_set_error("conv_tc_gemm_tma: statistics need a 16-byte aligned bias"); return DL4JB200_ERR_INVALID_ARG; }
     if ((g.epi_add || g.epi_mask) && (g.remap || !aligned_bias)) {
         dl4j_set_error("conv_tc_gemm_tma: fused epilogue needs the unscattered persistent kernel");
         return DL4JB200_ERR_INVALID_ARG;

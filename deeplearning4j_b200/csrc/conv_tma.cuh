@@ -47,6 +47,11 @@ struct TmaGemmGeom {
     // i.e. the ComputationGraph epsilon fan-in sum followed by the ReLU backprop of the vertex that owns `out`
     // (epi_add may alias out: every element is read and written by the same thread)
     const float *epi_add = nullptr, *epi_mask = nullptr;
+    // optional batch-norm statistics of the output (forward, identity activation): per-warp partial rows
+    //   stat_out[row][0][c] = sum (z - stat_pivot[c]),  stat_out[row][1][c] = sum (z - stat_pivot[c])^2
+    // rows = (gridDim.x / n_tiles) * 4, row pitch 2 * out_cs floats (the layout k_bn_finalize folds)
+    float *stat_out = nullptr;
+    const float *stat_pivot = nullptr;
 };
 struct TmaWgradGeom {
     int M, kW, dH, dW, sH, sW, lowH, lowW, Kp;

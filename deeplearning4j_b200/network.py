@@ -70,6 +70,8 @@ class Network:
         self.prepack = True
         self._register_filters()
         self.params_changed()
+        self.fuse_bn_stats = True
+        self._plan_bn_stats()
 
     # ------------------------------------------------------------------ pre-packed filters
     def _register_filters(self):
@@ -83,6 +85,28 @@ class Network:
             _, xcs = self._src(src)
             pw, _, _, _ = self._p(n, "W")
             self._call("dl4jb200_filter_register", C.byref(d), pw, xcs, self.cs[n], self.algo, int(self._needs_eps(src)))
+
+    def _plan_bn_stats(self):
+        """Convolutions whose only consumer is a BatchNormalization take that layer's batch statistics in their GEMM
+        epilogue (dl4jb200_conv_fwd_bnstats) when the launch can carry them; the BN then runs finalize + apply only."""
+        self.stat_conv, self.stat_bn = {}, {}
+        if self.algo != _lib.ALGO_TC_TF32:
+            return
+        for v in self.model["vertices"]:
+            n = v["name"]
+            if v["op"] != "conv" or v["act"] != "identity" or v.get("dropout") or (self.stem and self.stem[0] == n):
+                continue
+            cons = self.consumers[n]
+            if len(cons) != 1 or self.vmap[cons[0]]["op"] != "bn":
+                continue
+            src, d = self._conv_desc(v)
+            _, xcs = self._src(src)
+            rows = C.c_int(0)
+            self._call("dl4jb200_conv_fwd_bnstats_rows", C.byref(d), xcs, self.cs[n], self.algo, C.byref(rows))
+            if rows.value > 0:
+                buf = self._buf(rows.value * 2 * self.cs[n])
+                self.stat_conv[n] = (cons[0], buf)
+                self.stat_bn[cons[0]] = (buf, rows.value)
 
     def params_changed(self):
         """Call after anything other than update() wrote the flat parameter vector (broadcast, parameter averaging)."""
@@ -330,6 +354,11 @@ class Network:
                 if self.stem and self.stem[0] == n:
                     self._call("dl4jb200_conv_rowpack_fwd", C.byref(d), self._ptr(x), self.stem[1], pw, pb, self._ptr(self.out[n]),
                                self.cs[n], _ACT[v["act"]])
+                elif train and self.fuse_bn_stats and n in self.stat_conv:
+                    bn, buf = self.stat_conv[n]
+                    pm, _, _, _ = self._p(bn, "mean")  # pivot of the fp32 sums: the running mean (read before it is updated)
+                    self._call("dl4jb200_conv_fwd_bnstats", C.byref(d), self._ptr(x), xcs, pw, pb, self._ptr(self.out[n]), self.cs[n],
+                               self.algo, pm, self._ptr(buf))
                 else:
                     self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
                                self.cs[n], _ACT[v["act"]], self.algo)
@@ -347,9 +376,15 @@ class Network:
                 pm, _, _, _ = self._p(bn, "mean")
                 pv, _, _, _ = self._p(bn, "var")
                 sm, ss = self.aux[bn]
-                self._call("dl4jb200_bn_fwd", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm), self._ptr(ss),
-                           B, s[0], s[1], s[2], L.NHWC, xcs, float(bnv["decay"]), float(bnv["eps"]), int(train),
-                           int(self.model["minibatch"]), act, res)
+                if train and self.fuse_bn_stats and bn in self.stat_bn:
+                    buf, rows = self.stat_bn[bn]
+                    self._call("dl4jb200_bn_fwd_prestats", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm),
+                               self._ptr(ss), B, s[0], s[1], s[2], xcs, float(bnv["decay"]), float(bnv["eps"]),
+                               int(self.model["minibatch"]), act, res, pm, self._ptr(buf), rows)
+                else:
+                    self._call("dl4jb200_bn_fwd", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm), self._ptr(ss),
+                               B, s[0], s[1], s[2], L.NHWC, xcs, float(bnv["decay"]), float(bnv["eps"]), int(train),
+                               int(self.model["minibatch"]), act, res)
             elif op == "pool":
                 d = self._pool_desc(v)
                 self._apply_dropout(v, train)

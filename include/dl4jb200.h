@@ -251,6 +251,22 @@ int dl4jb200_lrn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, float 
 /* ElementWiseVertex Add (+ following ActivationLayer ReLU): out = act(a + b); backward mask from out.
  * NN/nn/graph/vertex/impl/ElementWiseVertex.java:81-86,126-131; NN/nn/layers/ActivationLayer.java:68-92 */
 int dl4jb200_add_act_fwd(dl4jb200_ctx *ctx, const float *a, const float *b, float *out, size_t n, int act);
+/* Batch-norm statistics taken in the producing convolution's epilogue (TF32 TMA path, NHWC, identity activation).
+ * BatchNormalization.preOutput computes mean / biased variance of its input with separate reduction passes
+ * (BatchNormalization.java:262-266); when that input is the output of a convolution helper call, the sums can be taken
+ * while the GEMM tile is still on chip. conv_fwd_bnstats writes z AND per-warp partial sums of (z - pivot[c]) and
+ * (z - pivot[c])^2 into stat_partial ([rows][2][z_cs] floats, rows from conv_fwd_bnstats_rows: 0 = this convolution
+ * cannot carry them, use conv_fwd + bn_fwd); bn_fwd_prestats is bn_fwd(training) on those sums: finalize + apply only.
+ * pivot: any per-channel value near the batch mean (it only conditions the fp32 sums; the running mean is a good
+ * choice and may be passed directly -- it is read before it is updated); the same pointer goes to both calls. */
+int dl4jb200_conv_fwd_bnstats_rows(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int x_cs, int z_cs, int algo, int *rows_out);
+int dl4jb200_conv_fwd_bnstats(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_cs, const float *w,
+                              const float *bias, float *z, int z_cs, int algo, const float *pivot, float *stat_partial);
+int dl4jb200_bn_fwd_prestats(dl4jb200_ctx *ctx, const float *x, float *y, const float *gamma, const float *beta, float *gmean,
+                             float *gvar, float *save_mean, float *save_std, int B, int C, int H, int W, int cs, double decay,
+                             double eps, int minibatch, int act, const float *residual, const float *pivot,
+                             const float *stat_partial, int stat_rows);
+
 /* Pre-packed filters. conv_fwd / conv_bwd re-pack the DL4J-layout filter W[c_out,c_in,kH,kW]
  * (ConvolutionParamInitializer.java:144-155) into GEMM operand layout on every call. A caller that knows when the
  * parameters change (once per iteration: StochasticGradientDescent.java:78, params.subi(update)) registers each filter

@@ -324,6 +324,63 @@ def test_prepacked_filters_match_per_call_packing(H, oracle):
         ctx.close()
 
 
+@pytest.mark.parametrize("case", [
+    (8, 64, 14, 14, 64, (3, 3), 2),      # one 64-wide N tile, 13 M tiles
+    (4, 64, 14, 14, 256, (1, 1), 1),     # two 128-wide N tiles
+    (3, 256, 7, 7, 512, (1, 1), 1),      # four N tiles, ragged last M tile (147 rows)
+    (64, 128, 28, 28, 128, (3, 3), 2),   # 392 M tiles: every CTA accumulates over several tiles before the flush
+])
+def test_conv_epilogue_bn_statistics(H, ctx, oracle, case):
+    """conv_fwd_bnstats + bn_fwd_prestats == conv_fwd + bn_fwd (and the oracle): same z bit for bit, same normalised output,
+    saved statistics and running statistics, for a pivot far from the batch mean as well as for a good one."""
+    from deeplearning4j_b200 import _lib
+    B, Cin, Hh, W, Cout, k, mode = case
+    rng = np.random.default_rng(17)
+    x = rng.random((B, Cin, Hh, W), dtype=np.float32)
+    w = (rng.standard_normal((Cout, Cin) + k) * 0.3).astype(np.float32)
+    b = rng.standard_normal(Cout).astype(np.float32)
+    gamma = (1 + 0.1 * rng.standard_normal(Cout)).astype(np.float32)
+    beta = (0.1 * rng.standard_normal(Cout)).astype(np.float32)
+    d = H.conv_desc(x.shape, Cout, k, (1, 1), (k[0] // 2, k[1] // 2), (1, 1), MODES[mode])
+    rows = C.c_int(0)
+    _lib.call("dl4jb200_conv_fwd_bnstats_rows", ctx.handle, C.byref(d), Cin, Cout, H.ALGO_TC_TF32, C.byref(rows))
+    assert rows.value > 0
+    n_out = B * d.out_h * d.out_w * Cout
+    dev = Dev(ctx)
+    try:
+        px, pw, pb, pg, pbt = dev.put(to_nhwc(x)), dev.put(w), dev.put(b), dev.put(gamma), dev.put(beta)
+        # reference path: conv_fwd then bn_fwd
+        pz0, py0 = dev.empty(n_out * 4), dev.empty(n_out * 4)
+        gm0, gv0 = dev.put(np.zeros(Cout, np.float32)), dev.put(np.ones(Cout, np.float32))
+        sm0, ss0 = dev.empty(Cout * 4), dev.empty(Cout * 4)
+        _lib.call("dl4jb200_conv_fwd", ctx.handle, C.byref(d), px, H.NHWC, Cin, pw, pb, pz0, H.NHWC, Cout, 0, H.ALGO_TC_TF32)
+        _lib.call("dl4jb200_bn_fwd", ctx.handle, pz0, py0, pg, pbt, gm0, gv0, sm0, ss0, B, Cout, d.out_h, d.out_w, H.NHWC, Cout,
+                  0.9, 1e-5, 1, 1, H.ACTIVATIONS["relu"], None)
+        z0, y0 = dev.get(pz0, (n_out,)), dev.get(py0, (n_out,))
+        ref = [dev.get(p_, (Cout,)) for p_ in (gm0, gv0, sm0, ss0)]
+        zmean = z0.reshape(-1, Cout).mean(0)
+        for pivot_kind in ("zero", "near"):
+            pivot = np.zeros(Cout, np.float32) if pivot_kind == "zero" else (zmean + 0.05).astype(np.float32)
+            pz, py, pst = dev.empty(n_out * 4), dev.empty(n_out * 4), dev.empty(rows.value * 2 * Cout * 4, fill=0xFF)
+            # the pivot buffer doubles as the running mean here only for the "zero" case (gmean starts at 0)
+            gm = dev.put(np.zeros(Cout, np.float32))
+            pp = gm if pivot_kind == "zero" else dev.put(pivot)
+            gv, sm, ss = dev.put(np.ones(Cout, np.float32)), dev.empty(Cout * 4), dev.empty(Cout * 4)
+            _lib.call("dl4jb200_conv_fwd_bnstats", ctx.handle, C.byref(d), px, Cin, pw, pb, pz, Cout, H.ALGO_TC_TF32, pp, pst)
+            _lib.call("dl4jb200_bn_fwd_prestats", ctx.handle, pz, py, pg, pbt, gm, gv, sm, ss, B, Cout, d.out_h, d.out_w, Cout,
+                      0.9, 1e-5, 1, H.ACTIVATIONS["relu"], None, pp, pst, rows.value)
+            np.testing.assert_array_equal(dev.get(pz, (n_out,)), z0)
+            assert rel_err(dev.get(py, (n_out,)), y0) <= 2e-5, pivot_kind
+            for got_p, want in zip((gm, gv, sm, ss), ref):
+                assert rel_err(dev.get(got_p, (Cout,)), want) <= 1e-5, pivot_kind
+    finally:
+        dev.free()
+    # a convolution that cannot carry them says so
+    d2 = H.conv_desc((2, 3, 9, 9), 5, (3, 3), (1, 1), (1, 1), (1, 1), "Truncate")
+    _lib.call("dl4jb200_conv_fwd_bnstats_rows", ctx.handle, C.byref(d2), 4, 8, H.ALGO_TC_TF32, C.byref(rows))
+    assert rows.value == 0
+
+
 def test_conv_invalid_shapes_raise_like_reference(H, ctx):
     from deeplearning4j_b200 import DL4JInvalidConfigException, DL4JInvalidInputException
     helper = H.CudnnConvolutionHelper(ctx)
