@@ -73,6 +73,7 @@ PROTOTYPES = {
     "dl4jb200_bias_grad": [_vp, _vp, _i, _i, _i, _vp],
     "dl4jb200_nchw_to_rowpack4": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i],
     "dl4jb200_conv_rowpack_fwd": [_vp, _desc_p, _vp, _i, _vp, _vp, _vp, _i, _i],
+    "dl4jb200_conv_rowpack_fwd_bnstats": [_vp, _desc_p, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, C.POINTER(C.c_int)],
     "dl4jb200_conv_rowpack_wgrad": [_vp, _desc_p, _vp, _i, _vp, _i, _vp, _vp],
     "dl4jb200_act_fwd": [_vp, _vp, _vp, _sz, _i],
     "dl4jb200_act_bwd": [_vp, _vp, _vp, _vp, _sz, _i],

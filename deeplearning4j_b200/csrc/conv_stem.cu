@@ -98,8 +98,8 @@ int dl4jb200_nchw_to_rowpack4(dl4jb200_ctx *ctx, const float *src, float *dst, i
     return DL4JB200_OK;
 }
 
-int dl4jb200_conv_rowpack_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px, const float *w,
-                              const float *bias, float *z, int z_cs, int act) {
+static int rowpack_fwd_impl(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px, const float *w,
+                            const float *bias, float *z, int z_cs, int act, const float *pivot, float *stat_partial, int *rows_out) {
     int rc = stem_check(ctx, d, row_pitch_px, "conv_rowpack_fwd");
     if (rc) return rc;
     DL4J_REQUIRE(xp && w && z && z_cs >= d->c_out && z_cs % 4 == 0 && ((uintptr_t)z & 15) == 0 && ((uintptr_t)xp & 15) == 0,
@@ -122,7 +122,31 @@ int dl4jb200_conv_rowpack_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, co
     t.div_Cg = FastDiv(32u); t.div_kW = FastDiv(1u);
     t.remap = 0; t.rm_sy = t.rm_sx = 1; t.rm_H = d->out_h; t.rm_W = d->out_w;
     const int act_code = act | ((ctx->round_act && act != DL4JB200_ACT_IDENTITY) ? 0x100 : 0);
+    if (stat_partial) {  // batch-norm statistics in the epilogue (see dl4jb200_conv_fwd_bnstats)
+        const int n_tiles = dl4j_ceil_div(z_cs, bn), total = dl4j_ceil_div(t.M, 128) * n_tiles;
+        const int grid = (total < ctx->sm_count ? total : ctx->sm_count) / n_tiles * n_tiles;
+        if (act != DL4JB200_ACT_IDENTITY || d->c_out % bn != 0 || z_cs != d->c_out || grid <= 0 || !pivot || ((uintptr_t)pivot & 15) ||
+            ((uintptr_t)stat_partial & 15)) {
+            dl4j_set_error("conv_rowpack_fwd_bnstats: this convolution cannot carry the statistics");
+            return DL4JB200_NOT_SUPPORTED;
+        }
+        t.stat_out = stat_partial;
+        t.stat_pivot = pivot;
+        *rows_out = grid / n_tiles * 4;
+    }
     return conv_tc_gemm_tma_raw(ctx, tmA, tmB, t, bias, z, d->c_out, z_cs, act_code, bn);
+}
+
+int dl4jb200_conv_rowpack_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px, const float *w,
+                              const float *bias, float *z, int z_cs, int act) {
+    return rowpack_fwd_impl(ctx, d, xp, row_pitch_px, w, bias, z, z_cs, act, nullptr, nullptr, nullptr);
+}
+
+int dl4jb200_conv_rowpack_fwd_bnstats(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px,
+                                      const float *w, const float *bias, float *z, int z_cs, const float *pivot,
+                                      float *stat_partial, int *rows_out) {
+    DL4J_REQUIRE(pivot && stat_partial && rows_out, "conv_rowpack_fwd_bnstats: NULL argument");
+    return rowpack_fwd_impl(ctx, d, xp, row_pitch_px, w, bias, z, z_cs, DL4JB200_ACT_IDENTITY, pivot, stat_partial, rows_out);
 }
 
 int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px,

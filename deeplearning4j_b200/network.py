@@ -92,12 +92,18 @@ class Network:
         self.stat_conv, self.stat_bn = {}, {}
         if self.algo != _lib.ALGO_TC_TF32:
             return
+        sm_count = self.torch.cuda.get_device_properties(self.dev).multi_processor_count
         for v in self.model["vertices"]:
             n = v["name"]
-            if v["op"] != "conv" or v["act"] != "identity" or v.get("dropout") or (self.stem and self.stem[0] == n):
+            if v["op"] != "conv" or v["act"] != "identity" or v.get("dropout"):
                 continue
             cons = self.consumers[n]
             if len(cons) != 1 or self.vmap[cons[0]]["op"] != "bn":
+                continue
+            if self.stem and self.stem[0] == n:
+                # row-packed stem: the call itself reports the rows it wrote (or NOT_SUPPORTED, probed in the first forward)
+                if self.cs[n] == self.shapes[n][0] and self.cs[n] % 32 == 0:
+                    self.stat_conv[n] = (cons[0], self._buf(4 * sm_count * 2 * self.cs[n]))
                 continue
             src, d = self._conv_desc(v)
             _, xcs = self._src(src)
@@ -351,7 +357,15 @@ class Network:
                 x, xcs = self._lin(n, src)
                 pw, _, _, _ = self._p(n, "W")
                 pb, _, _, _ = self._p(n, "b")
-                if self.stem and self.stem[0] == n:
+                if self.stem and self.stem[0] == n and train and self.fuse_bn_stats and n in self.stat_conv:
+                    bn, buf = self.stat_conv[n]
+                    pm, _, _, _ = self._p(bn, "mean")
+                    rows = C.c_int(0)
+                    self._call("dl4jb200_conv_rowpack_fwd_bnstats", C.byref(d), self._ptr(x), self.stem[1], pw, pb,
+                               self._ptr(self.out[n]), self.cs[n], pm, self._ptr(buf), C.byref(rows))
+                    self.stat_bn[bn] = (buf, rows.value)
+                elif self.stem and self.stem[0] == n:
+                    self.stat_bn.pop(self.stat_conv.get(n, (None,))[0], None)
                     self._call("dl4jb200_conv_rowpack_fwd", C.byref(d), self._ptr(x), self.stem[1], pw, pb, self._ptr(self.out[n]),
                                self.cs[n], _ACT[v["act"]])
                 elif train and self.fuse_bn_stats and n in self.stat_conv:

@@ -177,6 +177,11 @@ int dl4jb200_nchw_to_rowpack4(dl4jb200_ctx *ctx, const float *src, float *dst, i
                               int x_off);
 int dl4jb200_conv_rowpack_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px, const float *w,
                               const float *bias, float *z, int z_cs, int act);
+/* conv_rowpack_fwd with the following BatchNormalization's statistics taken in the epilogue (see conv_fwd_bnstats):
+ * stat_partial must hold 4 * (number of SMs) rows of 2 * z_cs floats; *rows_out receives the rows written. */
+int dl4jb200_conv_rowpack_fwd_bnstats(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px,
+                                      const float *w, const float *bias, float *z, int z_cs, const float *pivot,
+                                      float *stat_partial, int *rows_out);
 /* db may be NULL (filter gradient only); otherwise the bias gradient is produced too (inside the GEMM when
  * DL4JB200_OPT_TF32_ACTIVATIONS is on, by a column-sum pass otherwise). */
 int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px,

@@ -695,6 +695,29 @@ def test_rowpacked_stem_conv_vs_oracle(H, ctx, oracle, case):
         _lib.call("dl4jb200_bias_grad", ctx.handle, pd, B * d.out_h * d.out_w, zcs, Cout, pdb)
         assert rel_err(dev.get(pdw, w.shape), dwr) <= TOL_CONV_TF32
         assert rel_err(dev.get(pdb, (Cout,)), dbr) <= 1e-5
+        if Cout % 32 == 0:  # the stem forward can also carry the following BatchNormalization's statistics
+            import torch
+            sms = torch.cuda.get_device_properties(0).multi_processor_count
+            gamma, beta = np.ones(Cout, np.float32), np.zeros(Cout, np.float32)
+            outs = []
+            for fusedstats in (False, True):
+                pz2, py = dev.empty(B * d.out_h * d.out_w * zcs * 4), dev.empty(B * d.out_h * d.out_w * zcs * 4)
+                gm, gv = dev.put(np.zeros(Cout, np.float32)), dev.put(np.ones(Cout, np.float32))
+                sm_, ss_ = dev.empty(Cout * 4), dev.empty(Cout * 4)
+                pg_, pbt_ = dev.put(gamma), dev.put(beta)
+                if fusedstats:
+                    pst, rows = dev.empty(4 * sms * 2 * zcs * 4), C.c_int(0)
+                    _lib.call("dl4jb200_conv_rowpack_fwd_bnstats", ctx.handle, C.byref(d), pxp, pitch, pw, pb, pz2, zcs, gm, pst, C.byref(rows))
+                    assert rows.value > 0
+                    _lib.call("dl4jb200_bn_fwd_prestats", ctx.handle, pz2, py, pg_, pbt_, gm, gv, sm_, ss_, B, Cout, d.out_h, d.out_w, zcs,
+                              0.9, 1e-5, 1, H.ACT_IDENTITY, None, gm, pst, rows.value)
+                else:
+                    _lib.call("dl4jb200_conv_rowpack_fwd", ctx.handle, C.byref(d), pxp, pitch, pw, pb, pz2, zcs, H.ACT_IDENTITY)
+                    _lib.call("dl4jb200_bn_fwd", ctx.handle, pz2, py, pg_, pbt_, gm, gv, sm_, ss_, B, Cout, d.out_h, d.out_w, H.NHWC, zcs,
+                              0.9, 1e-5, 1, 1, H.ACT_IDENTITY, None)
+                outs.append([dev.get(q_, shp) for q_, shp in ((py, (B * d.out_h * d.out_w * zcs,)), (gm, (Cout,)), (gv, (Cout,)), (sm_, (Cout,)), (ss_, (Cout,)))])
+            for a_, b_ in zip(*outs):
+                assert rel_err(b_, a_) <= 2e-5
         # db through the entry point itself: column-sum pass (option off), ones column of the GEMM (option on, TF32-exact delta)
         from oracle.net_oracle import tf32_round
         dq = tf32_round(delta)
