@@ -60,11 +60,16 @@ __device__ __forceinline__ size_t offs(int b, int c, int y, int x, int C, int Hh
     return NHWC ? (((size_t)b * Hh + y) * Ww + x) * cs + c : (((size_t)b * C + c) * Hh + y) * Ww + x;
 }
 
-template <bool NHWC>
+// KS > 0: square KS x KS window known at compile time (tap loops unrolled: the generic loop is instruction-bound on the
+// 3x3/2 stem pool); KS == 0: window from the geometry.
+template <bool NHWC, int KS = 0>
 __global__ void __launch_bounds__(256) k_pool_fwd(const float *__restrict__ x, float *__restrict__ y,
                                                   int32_t *__restrict__ argmax, PoolGeom g, int type, int pnorm,
                                                   size_t total) {
     constexpr int V = NHWC ? 4 : 1;
+    const int kH = KS ? KS : g.kH, kW = KS ? KS : g.kW;
+    pdl_trigger();
+    pdl_wait();
     size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
         int b, c, oh, ow;
@@ -73,17 +78,19 @@ __global__ void __launch_bounds__(256) k_pool_fwd(const float *__restrict__ x, f
         int best[V];
 #pragma unroll
         for (int i = 0; i < V; i++) { acc[i] = type == DL4JB200_POOL_MAX ? -FLT_MAX : 0.f; best[i] = 0; }
-        for (int kh = 0; kh < g.kH; kh++) {
+#pragma unroll KS ? KS : 1
+        for (int kh = 0; kh < kH; kh++) {
             int ih = oh * g.sH - g.pT + kh * g.dH;
             if (ih < 0 || ih >= g.H) continue;  // padding: -FLT_MAX for max (never wins), 0 for sums
-            for (int kw = 0; kw < g.kW; kw++) {
+#pragma unroll KS ? KS : 1
+            for (int kw = 0; kw < kW; kw++) {
                 int iw = ow * g.sW - g.pL + kw * g.dW;
                 if (iw < 0 || iw >= g.W) continue;
                 Vec<V> v = vload<V>(x + offs<NHWC>(b, c, ih, iw, g.C, g.H, g.W, g.xcs));
 #pragma unroll
                 for (int i = 0; i < V; i++) {
                     if (type == DL4JB200_POOL_MAX) {
-                        if (v.v[i] > acc[i]) { acc[i] = v.v[i]; best[i] = kh * g.kW + kw; }
+                        if (v.v[i] > acc[i]) { acc[i] = v.v[i]; best[i] = kh * kW + kw; }
                     } else if (type == DL4JB200_POOL_PNORM) {
                         acc[i] += powf(fabsf(v.v[i]), (float)pnorm);
                     } else {
@@ -95,7 +102,7 @@ __global__ void __launch_bounds__(256) k_pool_fwd(const float *__restrict__ x, f
         Vec<V> out;
 #pragma unroll
         for (int i = 0; i < V; i++) {
-            if (type == DL4JB200_POOL_AVG) out.v[i] = dl4j_rnd(acc[i] / (float)(g.kH * g.kW), g.rnd);
+            if (type == DL4JB200_POOL_AVG) out.v[i] = dl4j_rnd(acc[i] / (float)(kH * kW), g.rnd);
             else if (type == DL4JB200_POOL_PNORM) out.v[i] = dl4j_rnd(powf(acc[i], 1.f / (float)pnorm), g.rnd);
             else out.v[i] = dl4j_rnd(acc[i], g.rnd);  // no-op when the producer already rounded (idempotent)
         }
@@ -317,7 +324,9 @@ int dl4jb200_pool_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     g.d_w = FastDiv((uint32_t)g.Wo); g.d_h = FastDiv((uint32_t)g.Ho); g.d_c = FastDiv((uint32_t)g.C);
     if (layout == DL4JB200_NHWC) {
         size_t total = (size_t)g.B * g.Ho * g.Wo * (g.ycs / 4);
-        k_pool_fwd<true><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, argmax, g, pool_type, pnorm, total);
+        if (g.kH == 3 && g.kW == 3) k_pool_fwd<true, 3><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, argmax, g, pool_type, pnorm, total);
+        else if (g.kH == 2 && g.kW == 2) k_pool_fwd<true, 2><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, argmax, g, pool_type, pnorm, total);
+        else k_pool_fwd<true><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, argmax, g, pool_type, pnorm, total);
     } else {
         size_t total = (size_t)g.B * g.C * g.Ho * g.Wo;
         k_pool_fwd<false><<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(x, y, argmax, g, pool_type, pnorm, total);
