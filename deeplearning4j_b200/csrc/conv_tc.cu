@@ -703,10 +703,10 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
     auto tfull_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + b); };
     auto tempty_bar = [&](int b) { return bar_base + 8u * (2 * STAGES + 2 + b); };
     const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4), bres_bar = bar_base + 8u * (2 * STAGES + 5);
-    // B-resident mode: every tile of this CTA uses the same filter columns (one N tile) and the whole K extent of the
-    // filter fits the ring's B slots, so B is fetched ONCE per CTA instead of once per tile and only A streams. The 7x7/2
-    // stem (25 088 tiles per launch, 7 K-chunks each) was bound by exactly that L2 -> SM re-fetch.
-    const bool bres = n_tiles == 1 && g.num_k <= STAGES;
+    // B-resident mode: every tile of this CTA uses the same filter columns (the grid is a multiple of the N-tile count, so
+    // t % n_tiles is constant per CTA) and the whole K extent of the filter fits the ring's B slots: B is fetched ONCE
+    // per CTA instead of once per tile and only A streams (small-K 1x1 layers, the 7-row stem).
+    const bool bres = g.num_k <= STAGES && (int)gridDim.x % n_tiles == 0;  // grid multiple of n_tiles: a CTA keeps its N tile
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
@@ -730,7 +730,8 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
             int kit = 0;
             if (bres && (int)blockIdx.x < total_tiles) {
                 tma::expect_tx(bres_bar, (uint32_t)(g.num_k * L::B_BYTES));
-                for (int it = 0; it < g.num_k; ++it) tma::load_2d(b_base + it * L::B_BYTES, &tmB, bres_bar, it * BLOCK_K, 0);
+                for (int it = 0; it < g.num_k; ++it)
+                    tma::load_2d(b_base + it * L::B_BYTES, &tmB, bres_bar, it * BLOCK_K, ((int)blockIdx.x % n_tiles) * BN);
             }
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
                 const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * BN;
@@ -977,7 +978,8 @@ static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, co
         configured[ctx->device & 15] = true;
     }
     const int n_tiles = dl4j_ceil_div(out_cs, BN), total = dl4j_ceil_div(g.M, BLOCK_M) * n_tiles;
-    const int grid = total < ctx->sm_count ? total : ctx->sm_count;
+    int grid = total < ctx->sm_count ? total : ctx->sm_count;
+    if (n_tiles > 1 && g.num_k <= STAGES && grid >= 2 * n_tiles) grid = grid / n_tiles * n_tiles;  // enables the B-resident mode
     if (g.stat_out) {  // batch-norm statistics in the epilogue: grid a multiple of n_tiles (see the kernel)
         static bool configured_s[16] = {false};
         if (!configured_s[ctx->device & 15]) {
