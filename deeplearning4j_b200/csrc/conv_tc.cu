@@ -1237,9 +1237,21 @@ bool conv_tc_gemm_can_tma(const ConvGeom &g) {
 // N-tile width of the TMA GEMM: 256-wide tiles (one UMMA of N=256, the whole TMEM as a double-buffered accumulator) when the
 // layer is wide and there are still at least ~2 tiles per SM
 static int tma_gemm_bn(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, int out_cs, bool aligned_bias) {
-    const bool wide = aligned_bias && out_cs >= 256 && n_rows_packed % 256 == 0 && g.Kp >= 256 &&
-                      (long long)dl4j_ceil_div(g.M, tc::BLOCK_M) * dl4j_ceil_div(out_cs, 256) >= 2LL * ctx->sm_count;
-    return wide ? 256 : (out_cs > 64 ? 128 : (out_cs > 32 ? 64 : 32));
+    const bool can256 = aligned_bias && out_cs >= 256 && n_rows_packed % 256 == 0 && g.Kp >= 256;
+    const long long m_tiles = dl4j_ceil_div(g.M, tc::BLOCK_M);
+    const int narrow = out_cs > 64 ? 128 : (out_cs > 32 ? 64 : 32);
+    if (can256 && g.Kp >= 512) {
+        // long-K layers are bound by the per-SM TMA fill: a K-step costs ~(16 KB of A + bn * 128 B of B), and the launch
+        // takes ceil(tiles / #SMs) rounds of tiles. Pick the width with the smaller product (e.g. 98 M tiles x N = 256:
+        // one round of 256-wide tiles, 48 KB per step, beats two rounds of 128-wide ones at 32 KB).
+        auto cost = [&](int bn) {
+            const long long tiles = m_tiles * dl4j_ceil_div(out_cs, bn);
+            return (double)((tiles + ctx->sm_count - 1) / ctx->sm_count) * (16.0 + bn / 8.0);
+        };
+        return cost(256) < cost(narrow) ? 256 : narrow;
+    }
+    const bool wide = can256 && m_tiles * dl4j_ceil_div(out_cs, 256) >= 2LL * ctx->sm_count;
+    return wide ? 256 : narrow;
 }
 
 // partial rows a statistics-carrying forward launch of this geometry writes (0: the launch cannot carry statistics)
