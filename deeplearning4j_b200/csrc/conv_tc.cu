@@ -1311,10 +1311,19 @@ int conv_tc_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const f
 int conv_tc_wgrad_splits(dl4jb200_ctx *ctx, const ConvGeom &g, int c_out) {
     int bn = tc::wgrad_bn(g);
     int tiles = dl4j_ceil_div(g.Kp, bn) * dl4j_ceil_div(c_out, tc::BLOCK_M);
-    int want = dl4j_ceil_div(2 * ctx->sm_count, tiles);
     int max_splits = dl4j_ceil_div(g.M, 8 * tc::BLOCK_K);  // at least 8 k-chunks per split
-    if (want > max_splits) want = max_splits;
-    if (want < 1) want = 1;
+    if (max_splits < 1) max_splits = 1;
+    // Two CTAs of this kernel fit an SM: 2 * #SMs slots per round. A launch of tiles * s CTAs takes ceil(tiles*s / slots)
+    // rounds of ceil(chunks / s) K-chunks each; take the s with the smallest product (ties: fewer splits = less partial
+    // traffic for the finalize). Rounding 2*#SMs / tiles UP, as before, put most layers a few CTAs past one full round.
+    const long long slots = 2LL * ctx->sm_count, chunks = dl4j_ceil_div(g.M, tc::BLOCK_K);
+    int want = 1;
+    long long best = -1;
+    const int s_hi = (int)(2 * slots / tiles) + 1;
+    for (int sp = 1; sp <= max_splits && sp <= s_hi; sp++) {
+        const long long rounds = ((long long)tiles * sp + slots - 1) / slots, cost = rounds * ((chunks + sp - 1) / sp);
+        if (best < 0 || cost < best) { best = cost; want = sp; }
+    }
     int mps = dl4j_round_up(dl4j_ceil_div(g.M, want), tc::BLOCK_K);
     return dl4j_ceil_div(g.M, mps);
 }
