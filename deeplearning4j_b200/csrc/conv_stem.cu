@@ -132,7 +132,7 @@ static int rowpack_fwd_impl(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, cons
         }
         t.stat_out = stat_partial;
         t.stat_pivot = pivot;
-        *rows_out = grid / n_tiles * 4;
+        *rows_out = grid / n_tiles * (bn >= 64 ? 1 : 4);  // persist_stat_rows
     }
     return conv_tc_gemm_tma_raw(ctx, tmA, tmB, t, bias, z, d->c_out, z_cs, act_code, bn);
 }

@@ -932,9 +932,12 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
             }
         }
         if (STATS && grp < BN / 32) {
-            // flush: fold the four lanes that hold the same columns (rows r, r+1, r+2, r+3 mod 4 of every group), then
-            // lanes 0-7 write this warp's partial row: stat_out[row_id][0 | 1][column]
-            const int row_id = ((int)blockIdx.x / n_tiles) * 4 + quad, ncol0 = ((int)blockIdx.x % n_tiles) * BN;
+            // flush: fold the four lanes that hold the same columns (rows r, r+1, r+2, r+3 mod 4 of every group); then, when
+            // both warp groups are active (BN >= 64), the four lane quadrants of the CTA are combined through the staging
+            // smem so that the CTA writes ONE partial row (the finalize fold is a latency-bound tail: fewer rows, shorter)
+            constexpr bool COMBINE = BN >= 64;
+            const int ncol0 = ((int)blockIdx.x % n_tiles) * BN;
+            __syncwarp();
 #pragma unroll
             for (int j = 0; j < NCH; j++) {
                 const int cb = grp + 2 * j;
@@ -948,9 +951,39 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                         b.z += __shfl_xor_sync(0xffffffffu, b.z, o); b.w += __shfl_xor_sync(0xffffffffu, b.w, o);
                     }
                     if (lane < 8) {
-                        float *p = g.stat_out + (size_t)row_id * 2 * out_cs + ncol0 + cb * 32 + lane * 4;
-                        *reinterpret_cast<float4 *>(p) = a;
-                        *reinterpret_cast<float4 *>(p + out_cs) = b;
+                        if (COMBINE) {
+                            const uint32_t sa = stage_smem + (uint32_t)j * 256u + (uint32_t)lane * 16u;
+                            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(sa), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w) : "memory");
+                            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(sa + 128u), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
+                        } else {
+                            float *p = g.stat_out + (size_t)(((int)blockIdx.x / n_tiles) * 4 + quad) * 2 * out_cs + ncol0 + cb * 32 + lane * 4;
+                            *reinterpret_cast<float4 *>(p) = a;
+                            *reinterpret_cast<float4 *>(p + out_cs) = b;
+                        }
+                    }
+                }
+            }
+            if (COMBINE) {
+                asm volatile("bar.sync 1, 256;" ::: "memory");  // the eight epilogue warps
+                if (quad == 0 && lane < 8) {
+#pragma unroll
+                    for (int j = 0; j < NCH; j++) {
+                        const int cb = grp + 2 * j;
+                        if (cb < BN / 32) {
+                            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+#pragma unroll
+                            for (int qq = 0; qq < 4; qq++) {  // fixed order: deterministic
+                                const uint32_t sa = base + L::STAGING_OFF + (uint32_t)(grp * 4 + qq) * 4096u + (uint32_t)j * 256u + (uint32_t)lane * 16u;
+                                float4 u, w;
+                                asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(u.x), "=f"(u.y), "=f"(u.z), "=f"(u.w) : "r"(sa));
+                                asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(w.x), "=f"(w.y), "=f"(w.z), "=f"(w.w) : "r"(sa + 128u));
+                                a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w;
+                                b.x += w.x; b.y += w.y; b.z += w.z; b.w += w.w;
+                            }
+                            float *p = g.stat_out + (size_t)((int)blockIdx.x / n_tiles) * 2 * out_cs + ncol0 + cb * 32 + lane * 4;
+                            *reinterpret_cast<float4 *>(p) = a;
+                            *reinterpret_cast<float4 *>(p + out_cs) = b;
+                        }
                     }
                 }
             }
@@ -966,6 +999,9 @@ static inline int persist_stat_grid(int sm_count, int total, int n_tiles) {
     int g = total < sm_count ? total : sm_count;
     return g / n_tiles * n_tiles;
 }
+
+// partial rows such a launch writes: one per CTA column group when the CTA combines its quadrants (bn >= 64), else four
+static inline int persist_stat_rows(int grid, int n_tiles, int bn) { return grid / n_tiles * (bn >= 64 ? 1 : 4); }
 
 template <int BN, int STAGES>
 static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const TmaGemmGeom &g,
@@ -1260,7 +1296,7 @@ int conv_tc_stat_rows(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, i
     const int bn = tma_gemm_bn(ctx, g, n_rows_packed, out_cs, true);
     if (n_valid % bn != 0 || out_cs != n_valid) return 0;
     const int n_tiles = out_cs / bn, total = dl4j_ceil_div(g.M, tc::BLOCK_M) * n_tiles;
-    return tc::persist_stat_grid(ctx->sm_count, total, n_tiles) / n_tiles * 4;
+    return tc::persist_stat_rows(tc::persist_stat_grid(ctx->sm_count, total, n_tiles), n_tiles, bn);
 }
 
 static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,

@@ -49,7 +49,7 @@ struct TmaGemmGeom {
     const float *epi_add = nullptr, *epi_mask = nullptr;
     // optional batch-norm statistics of the output (forward, identity activation): per-warp partial rows
     //   stat_out[row][0][c] = sum (z - stat_pivot[c]),  stat_out[row][1][c] = sum (z - stat_pivot[c])^2
-    // rows = (gridDim.x / n_tiles) * 4, row pitch 2 * out_cs floats (the layout k_bn_finalize folds)
+    // rows = gridDim.x / n_tiles (x 4 for 32-wide tiles), row pitch 2 * out_cs floats (the layout k_bn_finalize folds)
     float *stat_out = nullptr;
     const float *stat_pivot = nullptr;
 };
