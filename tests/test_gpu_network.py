@@ -271,3 +271,43 @@ def test_alexnet_step_parity_with_dropout_masks():
         assert abs(ref.fit(x, lab) - s_ref) > 1e-3
     finally:
         net.close()
+
+
+@pytest.mark.parametrize("algo_name", ["fp32", "tf32"])
+def test_inference_forward_after_training_uses_running_statistics(algo_name):
+    """MultiLayerNetwork.output() path: after two training iterations the TEST-mode forward (BatchNormalization with the
+    running mean / var+eps it stored, no eps added again, BatchNormalization.java:274-279) matches the oracle on a new
+    minibatch, and leaves the running statistics untouched."""
+    from deeplearning4j_b200 import _lib, network, zoo
+    from oracle.net_oracle import OracleNet
+    algo = _lib.ALGO_FP32 if algo_name == "fp32" else _lib.ALGO_TC_TF32
+    # TF32: the two RmsProp(0.1) steps before it amplify the per-layer operand quantisation into the parameters (same
+    # whole-step bound as test_tiny_resnet_step_parity)
+    tol = 2e-4 if algo_name == "fp32" else 2e-1
+    m = _tiny_resnet()
+    B = 8
+    P, layout = zoo.param_layout(m)
+    p0 = zoo.init_params(m)
+    ref = OracleNet(m, layout, P, p0, fast=False)
+    net = network.Network(m, B, algo=algo, params=p0)
+    try:
+        for seed in (1, 2):
+            x, lab = _data(m, B, 10, seed=seed)
+            ref.fit(x, lab)
+            net.fit(x, lab)
+        net.sync()
+        before = net.params.cpu().numpy().copy()
+        x, lab = _data(m, B, 10, seed=3)
+        want = ref.forward(x, None, train=False)
+        net.set_batch(x, lab)
+        net.forward(False)
+        net.sync()
+        for v in m["vertices"]:
+            n = v["name"]
+            if v["op"] in ("input", "zeropad") or n in net.fused_bn:
+                continue
+            got = net.output_host(n)
+            assert rel_err(got, want[n].reshape(got.shape)) <= tol, (n, rel_err(got, want[n].reshape(got.shape)))
+        np.testing.assert_array_equal(net.params.cpu().numpy(), before)
+    finally:
+        net.close()
