@@ -146,8 +146,13 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
             j.wp[(size_t)(n0 + r) * j.Kp + k] = j.round_tf32 ? to_tf32_rna(v) : v;
         }
     } else {
-        const int co0 = u.a, ci0 = u.b;
-        const int nco = min(32, j.Cout - co0), nci = min(32, j.Cin - ci0);
+        const int co0 = u.a, nco = min(32, j.Cout - co0);
+        // a unit is a run of 32-wide ci tiles (u.pad of them): enough work per block for the small-tap filters
+        for (int sub = 0; sub < u.pad; sub++) {
+        const int ci0 = u.b + 32 * sub;
+        if (ci0 >= j.Cin) break;
+        const int nci = min(32, j.Cin - ci0);
+        if (sub) __syncthreads();  // the staging buffer is reused
         const int span = nci * taps;  // contiguous floats per co row of the tile
         const bool staged = 32 * span <= PACK_SMEM_FLOATS;
         if (staged) {
@@ -164,6 +169,7 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
             const int st = j.flip ? taps - 1 - tap : tap;
             const float v = staged ? sm[cl * span + il * taps + st] : j.w[((size_t)(co0 + cl) * j.Cin + ci0 + il) * taps + st];
             j.wp[(size_t)(ci0 + il) * j.Kp + (size_t)tap * j.Cg + co0 + cl] = j.round_tf32 ? to_tf32_rna(v) : v;
+        }
         }
     }
 }
@@ -559,13 +565,15 @@ int dl4jb200_filters_repack(dl4jb200_ctx *ctx) {
                 jobs.push_back(*j);
                 if (!j->transposed) {
                     long long row = (long long)j->Cin * taps;
-                    int rows_per = (int)(4096 / row);
+                    int rows_per = (int)(8192 / row);
                     if (rows_per < 1) rows_per = 1;
                     for (int n0 = 0; n0 < j->Cout; n0 += rows_per)
                         units.push_back(PackUnit{ji, n0, j->Cout - n0 < rows_per ? j->Cout - n0 : rows_per, 0});
                 } else {
+                    int subs = 8192 / (32 * 32 * taps);  // ~8 K elements per block
+                    if (subs < 1) subs = 1;
                     for (int co0 = 0; co0 < j->Cout; co0 += 32)
-                        for (int ci0 = 0; ci0 < j->Cin; ci0 += 32) units.push_back(PackUnit{ji, co0, ci0, 0});
+                        for (int ci0 = 0; ci0 < j->Cin; ci0 += 32 * subs) units.push_back(PackUnit{ji, co0, ci0, subs});
                 }
             }
         DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
