@@ -72,6 +72,7 @@ class Network:
         self.params_changed()
         self.fuse_bn_stats = True
         self._plan_bn_stats()
+        self._plan_forward_branches()
 
     # ------------------------------------------------------------------ pre-packed filters
     def _register_filters(self):
@@ -113,6 +114,27 @@ class Network:
                 buf = self._buf(rows.value * 2 * self.cs[n])
                 self.stat_conv[n] = (cons[0], buf)
                 self.stat_bn[cons[0]] = (buf, rows.value)
+
+    def _plan_forward_branches(self):
+        """Projection shortcuts (conv -> BN feeding an Add whose other input's BN is folded into it) do not depend on the
+        residual branch: in the forward pass they are issued on the side stream, forked when the block input is ready and
+        joined before the Add, so they fill the SMs the small-tile convolutions of the main branch leave idle."""
+        self.fwd_side, self.fwd_fork, self.fwd_join, self.fwd_mark = set(), {}, {}, set()
+        for add, (bname, other) in self.fused_add.items():
+            ov = self.vmap[other]
+            if ov["op"] != "bn" or self.consumers[other] != [add] or other in self.fused_bn:
+                continue
+            c = ov["in"][0]
+            cv = self.vmap[c]
+            if cv["op"] != "conv" or self.consumers[c] != [other] or (self.stem and self.stem[0] == c) or c in self.fold_pad:
+                continue
+            u = cv["in"][0]
+            if self.vmap[u]["op"] in ("input", "zeropad") or self.out.get(u, 0) is None or len(self.consumers[u]) < 2:
+                continue
+            self.fwd_side.update((c, other))
+            self.fwd_fork[c] = u        # side waits until u has been produced
+            self.fwd_mark.add(u)        # record an event on the main stream right after producing u
+            self.fwd_join[add] = other  # main waits for the side chain before the Add
 
     def params_changed(self):
         """Call after anything other than update() wrote the flat parameter vector (broadcast, parameter averaging)."""
@@ -345,12 +367,41 @@ class Network:
 
     # ------------------------------------------------------------------ forward (feedForward, train mode)
     def forward(self, train=True):
+        try:
+            self._forward(train)
+        finally:
+            self.__dict__.pop("_call", None)  # never leave the side-stream redirection of a shortcut branch in place
+
+    def _forward(self, train):
         L, B = _lib, self.B
+        branches = self.overlap_wgrad and bool(self.fwd_side)
+        ready, joined = {}, {}
         for v in self.model["vertices"]:
             n, op = v["name"], v["op"]
             self._cur = n
             if op in ("input", "zeropad") or self.out.get(n, 0) is None or n in self.fused_bn:
                 continue
+            if branches:
+                self.__dict__.pop("_call", None)
+                if n in self.fwd_side:
+                    if n in self.fwd_fork:
+                        self.side_stream.wait_event(ready[self.fwd_fork[n]])
+                    self._call = self._call_side  # this vertex' C-ABI calls go to the side context / stream
+                elif n in self.fwd_join:
+                    self.stream.wait_event(joined[self.fwd_join[n]])
+            self._forward_vertex(v, train)
+            if branches:
+                if n in self.fwd_mark:
+                    ready[n] = self.torch.cuda.Event()
+                    ready[n].record(self.stream)
+                if n in self.fwd_side and n in self.fwd_join.values():
+                    joined[n] = self.torch.cuda.Event()
+                    joined[n].record(self.side_stream)
+
+    def _forward_vertex(self, v, train):
+        L, B = _lib, self.B
+        n, op = v["name"], v["op"]
+        if True:
             if op == "conv":
                 src, d = self._conv_desc(v)
                 self._apply_dropout(v, train)
