@@ -235,6 +235,19 @@ def main():
     ms_e2e = f0.elapsed_time(f1)
     sampler.stop_flag = True
     sampler.join(timeout=2)
+    # what the box's host link gives a lone pinned copy of one minibatch (explains e2e on boxes where it is below
+    # bytes / step time: the prefetch then cannot hide the copy)
+    dev_x = torch.empty_like(xh, device=net.dev)
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(net.stream):
+        dev_x.copy_(xh, non_blocking=True)
+        c0.record(net.stream)
+        for _ in range(3):
+            dev_x.copy_(xh, non_blocking=True)
+        c1.record(net.stream)
+    net.sync()
+    h2d_gbs = 3 * x.nbytes / (c0.elapsed_time(c1) * 1e-3) / 1e9
+    del dev_x
 
     # ---- kernel-level pass: the same step issued eagerly with a CUDA-event pair around every conv / BN / pool call
     # (a replayed graph cannot carry per-kernel events); feeds the roofline and the launch count
@@ -369,7 +382,7 @@ def main():
                    "l2_flush": "working set (>= 10 GB of activations per step) exceeds the 126 MB L2",
                    "launch": "CUDA graph replay of the whole step" if use_graph else "eager kernel chain"},
         "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": int(x.nbytes + lab.nbytes), "d2h_bytes_per_step": 4,
-                "ms_per_step": ms_e2e / args.steps, "last_score": last},
+                "ms_per_step": ms_e2e / args.steps, "last_score": last, "h2d_link_gbs": h2d_gbs},
         "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roofline, "hbm_kernels": bw,
     }
     if cpu:
