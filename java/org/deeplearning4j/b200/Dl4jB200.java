@@ -50,6 +50,15 @@ public class Dl4jB200 {
                     @Const FloatPointer epsSum, @Const FloatPointer actOut, int act, int algo);
     public static native int dl4jb200_eps_sum_act_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer a, @Const FloatPointer b,
                     @Const FloatPointer actOut, FloatPointer delta, @Cast("size_t") long n, int act);
+    public static native int dl4jb200_conv_fwd_bnstats_rows(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    int xCs, int zCs, int algo, IntPointer rowsOut);
+    public static native int dl4jb200_conv_fwd_bnstats(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer x, int xCs, @Const FloatPointer w, @Const FloatPointer bias, FloatPointer z, int zCs, int algo,
+                    @Const FloatPointer pivot, FloatPointer statPartial);
+    public static native int dl4jb200_bn_fwd_prestats(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, FloatPointer y,
+                    @Const FloatPointer gamma, @Const FloatPointer beta, FloatPointer gMean, FloatPointer gVar, FloatPointer saveMean,
+                    FloatPointer saveStd, int b, int c, int h, int w, int cs, double decay, double eps, int minibatch, int act,
+                    @Const FloatPointer residual, @Const FloatPointer pivot, @Const FloatPointer statPartial, int statRows);
     public static native int dl4jb200_dropout_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, @Const FloatPointer mask,
                     FloatPointer y, @Cast("size_t") long n, double retainProb);
     public static native int dl4jb200_buf_register(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host, long bytes,
