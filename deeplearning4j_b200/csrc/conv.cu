@@ -123,6 +123,18 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
         const float *src = j.w + (size_t)n0 * row_src;
         const int span = rows * row_src;
         if (taps == 1) {  // operand row = filter row, only the pitch differs
+            if ((j.Cin & 3) == 0 && (j.Kp & 3) == 0 && ((uintptr_t)src & 15) == 0) {  // 128-bit both ways
+                const int c4 = j.Cin >> 2;
+#pragma unroll 4
+                for (int e = threadIdx.x; e < rows * c4; e += 256) {
+                    const int r = e / c4, q = e - r * c4;
+                    float4 v = reinterpret_cast<const float4 *>(src)[e];
+                    if (j.round_tf32) { v.x = to_tf32_rna(v.x); v.y = to_tf32_rna(v.y); v.z = to_tf32_rna(v.z); v.w = to_tf32_rna(v.w); }
+                    *reinterpret_cast<float4 *>(j.wp + (size_t)(n0 + r) * j.Kp + q * 4) = v;
+                }
+                return;
+            }
+#pragma unroll 4
             for (int e = threadIdx.x; e < span; e += 256) {
                 const int r = e / j.Cin, ci = e - r * j.Cin;
                 const float v = src[e];
@@ -132,10 +144,12 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
         }
         const bool staged = span <= PACK_SMEM_FLOATS;
         if (staged) {
+#pragma unroll 8
             for (int e = threadIdx.x; e < span; e += 256) sm[e] = src[e];
             __syncthreads();
         }
         const int kk = taps * j.Cg;
+#pragma unroll 4
         for (int e = threadIdx.x; e < rows * kk; e += 256) {
             const int r = e / kk, k = e - r * kk, tap = k / j.Cg, ci = k - tap * j.Cg;
             float v = 0.f;
@@ -156,6 +170,7 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
         const int span = nci * taps;  // contiguous floats per co row of the tile
         const bool staged = 32 * span <= PACK_SMEM_FLOATS;
         if (staged) {
+#pragma unroll 8
             for (int e = threadIdx.x; e < nco * span; e += 256) {
                 const int r = e / span, t = e - r * span;
                 sm[r * span + t] = j.w[((size_t)(co0 + r) * j.Cin + ci0) * taps + t];
@@ -163,6 +178,7 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
             __syncthreads();
         }
         // destination: row ci, column tap'*Cg + co; lanes run along co
+#pragma unroll 4
         for (int e = threadIdx.x; e < nci * taps * 32; e += 256) {
             const int cl = e & 31, t2 = e >> 5, tap = t2 % taps, il = t2 / taps;
             if (cl >= nco) continue;
