@@ -401,92 +401,91 @@ class Network:
     def _forward_vertex(self, v, train):
         L, B = _lib, self.B
         n, op = v["name"], v["op"]
-        if True:
-            if op == "conv":
-                src, d = self._conv_desc(v)
-                self._apply_dropout(v, train)
-                x, xcs = self._lin(n, src)
-                pw, _, _, _ = self._p(n, "W")
-                pb, _, _, _ = self._p(n, "b")
-                if self.stem and self.stem[0] == n and train and self.fuse_bn_stats and n in self.stat_conv:
-                    bn, buf = self.stat_conv[n]
-                    pm, _, _, _ = self._p(bn, "mean")
-                    rows = C.c_int(0)
-                    self._call("dl4jb200_conv_rowpack_fwd_bnstats", C.byref(d), self._ptr(x), self.stem[1], pw, pb,
-                               self._ptr(self.out[n]), self.cs[n], pm, self._ptr(buf), C.byref(rows))
-                    self.stat_bn[bn] = (buf, rows.value)
-                elif self.stem and self.stem[0] == n:
-                    self.stat_bn.pop(self.stat_conv.get(n, (None,))[0], None)
-                    self._call("dl4jb200_conv_rowpack_fwd", C.byref(d), self._ptr(x), self.stem[1], pw, pb, self._ptr(self.out[n]),
-                               self.cs[n], _ACT[v["act"]])
-                elif train and self.fuse_bn_stats and n in self.stat_conv:
-                    bn, buf = self.stat_conv[n]
-                    pm, _, _, _ = self._p(bn, "mean")  # pivot of the fp32 sums: the running mean (read before it is updated)
-                    self._call("dl4jb200_conv_fwd_bnstats", C.byref(d), self._ptr(x), xcs, pw, pb, self._ptr(self.out[n]), self.cs[n],
-                               self.algo, pm, self._ptr(buf))
-                else:
-                    self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
-                               self.cs[n], _ACT[v["act"]], self.algo)
-            elif op == "bn" or n in self.fused_add:
-                if op == "bn":
-                    bnv, res, act = v, None, _ACT[v["act"]]
-                else:  # Add(+ReLU) folded into the BatchNormalization that feeds it
-                    bname, other = self.fused_add[n]
-                    bnv, res, act = self.vmap[bname], self._ptr(self._src(other)[0]), _ACT[v["act"]]
-                bn = bnv["name"]
-                x, xcs = self._src(bnv["in"][0])
-                s = self.shapes[bn]
-                pg, _, _, _ = self._p(bn, "gamma")
-                pbeta, _, _, _ = self._p(bn, "beta")
+        if op == "conv":
+            src, d = self._conv_desc(v)
+            self._apply_dropout(v, train)
+            x, xcs = self._lin(n, src)
+            pw, _, _, _ = self._p(n, "W")
+            pb, _, _, _ = self._p(n, "b")
+            if self.stem and self.stem[0] == n and train and self.fuse_bn_stats and n in self.stat_conv:
+                bn, buf = self.stat_conv[n]
                 pm, _, _, _ = self._p(bn, "mean")
-                pv, _, _, _ = self._p(bn, "var")
-                sm, ss = self.aux[bn]
-                if train and self.fuse_bn_stats and bn in self.stat_bn:
-                    buf, rows = self.stat_bn[bn]
-                    self._call("dl4jb200_bn_fwd_prestats", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm),
-                               self._ptr(ss), B, s[0], s[1], s[2], xcs, float(bnv["decay"]), float(bnv["eps"]),
-                               int(self.model["minibatch"]), act, res, pm, self._ptr(buf), rows)
-                else:
-                    self._call("dl4jb200_bn_fwd", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm), self._ptr(ss),
-                               B, s[0], s[1], s[2], L.NHWC, xcs, float(bnv["decay"]), float(bnv["eps"]), int(train),
-                               int(self.model["minibatch"]), act, res)
-            elif op == "pool":
-                d = self._pool_desc(v)
-                self._apply_dropout(v, train)
-                x, xcs = self._lin(n, v["in"][0])
-                am = self._ptr(self.aux[n]) if v["type"] == "MAX" else None
-                self._call("dl4jb200_pool_fwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), am, L.NHWC, xcs, self.cs[n],
-                           _POOL[v["type"]], int(v.get("pnorm", 2)))
-            elif op == "add":
-                a, _ = self._src(v["in"][0])
-                b, _ = self._src(v["in"][1])
-                self._call("dl4jb200_add_act_fwd", self._ptr(a), self._ptr(b), self._ptr(self.out[n]), self.out[n].numel(),
-                           _ACT[v["act"]])
-            elif op == "act":
-                a, _ = self._src(v["in"][0])
-                self._call("dl4jb200_act_fwd", self._ptr(a), self._ptr(self.out[n]), a.numel(), _ACT[v["act"]])
-            elif op == "flatten":
-                x, xcs = self._src(v["in"][0])
-                s = self.shapes[v["in"][0]]
-                chw = s[0] * s[1] * s[2]
-                dst = self.out[n] if self.cs[n] == chw else self.aux[n]
-                self._call("dl4jb200_nhwc_to_nchw", self._ptr(x), self._ptr(dst), B, s[0], s[1], s[2], xcs)
-                if dst is not self.out[n]:
-                    self._call("dl4jb200_copy2d", self._ptr(dst), chw, self._ptr(self.out[n]), self.cs[n], B, chw)
-            elif op in ("dense", "output"):
-                self._apply_dropout(v, train)
-                x, xcs = self._lin(n, v["in"][0])
-                d = self._dense_desc(v)
-                pw, _, _, _ = self._p(n, "W")
-                pb, _, _, _ = self._p(n, "b")
-                act = _ACT[v["act"]] if op == "dense" else L.ACT_IDENTITY
-                self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
-                           self.cs[n], act, self.algo)
-                if op == "output" and self.labels is not None:
-                    self._call("dl4jb200_softmax_nll", self._ptr(self.out[n]), self.cs[n], self._ptr(self.labels),
-                               self._ptr(self.aux[n]), self.cs[n], self._ptr(self.loss), B, v["nOut"])
+                rows = C.c_int(0)
+                self._call("dl4jb200_conv_rowpack_fwd_bnstats", C.byref(d), self._ptr(x), self.stem[1], pw, pb,
+                           self._ptr(self.out[n]), self.cs[n], pm, self._ptr(buf), C.byref(rows))
+                self.stat_bn[bn] = (buf, rows.value)
+            elif self.stem and self.stem[0] == n:
+                self.stat_bn.pop(self.stat_conv.get(n, (None,))[0], None)
+                self._call("dl4jb200_conv_rowpack_fwd", C.byref(d), self._ptr(x), self.stem[1], pw, pb, self._ptr(self.out[n]),
+                           self.cs[n], _ACT[v["act"]])
+            elif train and self.fuse_bn_stats and n in self.stat_conv:
+                bn, buf = self.stat_conv[n]
+                pm, _, _, _ = self._p(bn, "mean")  # pivot of the fp32 sums: the running mean (read before it is updated)
+                self._call("dl4jb200_conv_fwd_bnstats", C.byref(d), self._ptr(x), xcs, pw, pb, self._ptr(self.out[n]), self.cs[n],
+                           self.algo, pm, self._ptr(buf))
             else:
-                raise NotImplementedError(op)
+                self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
+                           self.cs[n], _ACT[v["act"]], self.algo)
+        elif op == "bn" or n in self.fused_add:
+            if op == "bn":
+                bnv, res, act = v, None, _ACT[v["act"]]
+            else:  # Add(+ReLU) folded into the BatchNormalization that feeds it
+                bname, other = self.fused_add[n]
+                bnv, res, act = self.vmap[bname], self._ptr(self._src(other)[0]), _ACT[v["act"]]
+            bn = bnv["name"]
+            x, xcs = self._src(bnv["in"][0])
+            s = self.shapes[bn]
+            pg, _, _, _ = self._p(bn, "gamma")
+            pbeta, _, _, _ = self._p(bn, "beta")
+            pm, _, _, _ = self._p(bn, "mean")
+            pv, _, _, _ = self._p(bn, "var")
+            sm, ss = self.aux[bn]
+            if train and self.fuse_bn_stats and bn in self.stat_bn:
+                buf, rows = self.stat_bn[bn]
+                self._call("dl4jb200_bn_fwd_prestats", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm),
+                           self._ptr(ss), B, s[0], s[1], s[2], xcs, float(bnv["decay"]), float(bnv["eps"]),
+                           int(self.model["minibatch"]), act, res, pm, self._ptr(buf), rows)
+            else:
+                self._call("dl4jb200_bn_fwd", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm), self._ptr(ss),
+                           B, s[0], s[1], s[2], L.NHWC, xcs, float(bnv["decay"]), float(bnv["eps"]), int(train),
+                           int(self.model["minibatch"]), act, res)
+        elif op == "pool":
+            d = self._pool_desc(v)
+            self._apply_dropout(v, train)
+            x, xcs = self._lin(n, v["in"][0])
+            am = self._ptr(self.aux[n]) if v["type"] == "MAX" else None
+            self._call("dl4jb200_pool_fwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), am, L.NHWC, xcs, self.cs[n],
+                       _POOL[v["type"]], int(v.get("pnorm", 2)))
+        elif op == "add":
+            a, _ = self._src(v["in"][0])
+            b, _ = self._src(v["in"][1])
+            self._call("dl4jb200_add_act_fwd", self._ptr(a), self._ptr(b), self._ptr(self.out[n]), self.out[n].numel(),
+                       _ACT[v["act"]])
+        elif op == "act":
+            a, _ = self._src(v["in"][0])
+            self._call("dl4jb200_act_fwd", self._ptr(a), self._ptr(self.out[n]), a.numel(), _ACT[v["act"]])
+        elif op == "flatten":
+            x, xcs = self._src(v["in"][0])
+            s = self.shapes[v["in"][0]]
+            chw = s[0] * s[1] * s[2]
+            dst = self.out[n] if self.cs[n] == chw else self.aux[n]
+            self._call("dl4jb200_nhwc_to_nchw", self._ptr(x), self._ptr(dst), B, s[0], s[1], s[2], xcs)
+            if dst is not self.out[n]:
+                self._call("dl4jb200_copy2d", self._ptr(dst), chw, self._ptr(self.out[n]), self.cs[n], B, chw)
+        elif op in ("dense", "output"):
+            self._apply_dropout(v, train)
+            x, xcs = self._lin(n, v["in"][0])
+            d = self._dense_desc(v)
+            pw, _, _, _ = self._p(n, "W")
+            pb, _, _, _ = self._p(n, "b")
+            act = _ACT[v["act"]] if op == "dense" else L.ACT_IDENTITY
+            self._call("dl4jb200_conv_fwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, pb, self._ptr(self.out[n]), L.NHWC,
+                       self.cs[n], act, self.algo)
+            if op == "output" and self.labels is not None:
+                self._call("dl4jb200_softmax_nll", self._ptr(self.out[n]), self.cs[n], self._ptr(self.labels),
+                           self._ptr(self.aux[n]), self.cs[n], self._ptr(self.loss), B, v["nOut"])
+        else:
+            raise NotImplementedError(op)
 
     def _pool_desc(self, v):
         s_in, s_out = self.shapes[v["in"][0]], self.shapes[v["name"]]
