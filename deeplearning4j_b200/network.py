@@ -498,7 +498,8 @@ class Network:
     # ------------------------------------------------------------------ backward (calcBackpropGradients)
     def _eps_buf(self, u):
         if u not in self.eps:
-            self.eps[u] = self.torch.zeros_like(self.out[u])
+            with self.torch.cuda.stream(self.stream):  # the fill is ordered before the kernels that write the buffer
+                self.eps[u] = self.torch.zeros_like(self.out[u])
         return self.eps[u]
 
     def _needs_eps(self, u):
@@ -519,7 +520,8 @@ class Network:
         else:
             key = tuple(e.shape)
             if key not in self.tmp_eps:
-                self.tmp_eps[key] = self.torch.zeros_like(e)
+                with self.torch.cuda.stream(self.stream):
+                    self.tmp_eps[key] = self.torch.zeros_like(e)
             t = self.tmp_eps[key]
             fn(self._ptr(t))
             self._call("dl4jb200_accumulate", self._ptr(e), self._ptr(t), e.numel())
