@@ -25,6 +25,8 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 MODEL, BATCH, LABELS = "resnet50", 256, 1000
+WORKLOAD = ("ResNet-50 (DL4J zoo ComputationGraph, BatchNormalization) 3x224x224 full training step "
+            "(forward, backward, score, RmsProp+L1/L2 updater)")
 REF_SAMPLE_BATCH = 4
 
 
@@ -135,8 +137,8 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "resnet50_train_images_per_sec", "value": v, "unit": "images/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"ResNet-50 (DL4J zoo) 3x224x224 train step, reference CPU algorithm, sample batch {Bs}",
-                   "global_batch": Bs},
+        "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "per_gpu_batch": BATCH,
+                   "sample": f"reference CPU algorithm on the host cores, each step one full fit() at batch {Bs} of the same network"},
         "cpu_baseline": {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
                          "sample": f"{steps} full fit() iterations at batch {Bs} (im2col + OpenBLAS sgemm + col2im, OpenMP over all cores)"},
         "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
@@ -376,8 +378,7 @@ def main():
         "metric": "resnet50_train_images_per_sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "tf32" if args.algo == "tf32" else "f32", "data": "synthetic",
-        "config": {"workload": "ResNet-50 (DL4J zoo ComputationGraph, BatchNormalization) 3x224x224 full training step "
-                               "(forward, backward, score, RmsProp+L1/L2 updater)", "global_batch": B * world,
+        "config": {"workload": WORKLOAD, "global_batch": B * world,
                    "per_gpu_batch": B, "parallelism": f"dp{world}" if world > 1 else "single",
                    "l2_flush": "working set (>= 10 GB of activations per step) exceeds the 126 MB L2",
                    "launch": "CUDA graph replay of the whole step" if use_graph else "eager kernel chain"},
