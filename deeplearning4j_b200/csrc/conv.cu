@@ -236,6 +236,52 @@ __global__ void __launch_bounds__(256) k_wgrad_finalize(const float *__restrict_
     }
 }
 
+// Many-split form (small filters on large images: 59-146 splits of a few thousand outputs). A block reduces 32 outputs with
+// 8 threads each: thread (o, l) sums splits l, l+8, ... and the eight lane sums are combined in lane order through shared
+// memory -- a fixed tree, so still deterministic -- instead of one thread walking 100+ strided partials on its own.
+__global__ void __launch_bounds__(256) k_wgrad_finalize_wide(const float *__restrict__ partial, float *__restrict__ dw, int Cout,
+                                                             int Cin, int taps, int Cg, int Kp, int rows_p, int splits,
+                                                             const float *__restrict__ db_partial, float *__restrict__ db) {
+    __shared__ float red[8][33];
+    const int o = threadIdx.x & 31, l = threadIdx.x >> 5;
+    const size_t nw = (size_t)Cout * Cin * taps, total = nw + (db_partial ? (size_t)Cout : 0);
+    for (size_t base = (size_t)blockIdx.x * 32; base < total; base += (size_t)gridDim.x * 32) {
+        const size_t i = base + o;
+        float acc = 0.f;
+        float *dst = nullptr;
+        if (i < total) {
+            const float *p;
+            size_t ss;
+            if (i < nw) {
+                const int tap = (int)(i % taps);
+                const size_t t = i / taps;
+                const int ci = (int)(t % Cin), co = (int)(t / Cin);
+                p = partial + (size_t)co * Kp + (size_t)tap * Cg + ci;
+                ss = (size_t)rows_p * Kp;
+                dst = dw + i;
+            } else {
+                p = db_partial + (i - nw);
+                ss = (size_t)rows_p;
+                dst = db + (i - nw);
+            }
+            float a0 = 0.f, a1 = 0.f;
+            int sp = l;
+            for (; sp + 8 < splits; sp += 16) { a0 += p[(size_t)sp * ss]; a1 += p[(size_t)(sp + 8) * ss]; }
+            if (sp < splits) a0 += p[(size_t)sp * ss];
+            acc = a0 + a1;
+        }
+        red[l][o] = acc;
+        __syncthreads();
+        if (l == 0 && dst) {
+            float r = red[0][o];
+#pragma unroll
+            for (int q = 1; q < 8; q++) r += red[q][o];
+            *dst = r;
+        }
+        __syncthreads();
+    }
+}
+
 // bias gradient: column sums of delta[M, cs] (ConvolutionLayer.java:257). Two deterministic stages.
 __global__ void __launch_bounds__(256) k_colsum_partial(const float *__restrict__ d, float *__restrict__ partial, int M, int cs) {
     __shared__ float4 red[256];
@@ -440,8 +486,15 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
         if (tcore) rc = conv_tc_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits, dbp);
         else rc = conv_ffma_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
         if (rc) return rc;
-        k_wgrad_finalize<<<grid_for(ctx, (size_t)d->c_out * d->c_in * gf.taps), 256, 0, ctx->stream>>>(
-            partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w, splits, dbp, db);
+        const size_t n_out = (size_t)d->c_out * d->c_in * gf.taps;
+        if (splits >= 32) {
+            size_t blocks = (n_out + d->c_out + 31) / 32, cap = (size_t)ctx->sm_count * 16;
+            k_wgrad_finalize_wide<<<(int)(blocks < cap ? blocks : cap), 256, 0, ctx->stream>>>(partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg,
+                                                                                          gf.Kp, rows_w, splits, dbp, db);
+        } else {
+            k_wgrad_finalize<<<grid_for(ctx, n_out), 256, 0, ctx->stream>>>(partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w,
+                                                                            splits, dbp, db);
+        }
         DL4J_CHECK_LAUNCH();
     }
 
