@@ -107,3 +107,47 @@ def test_conv_full_size_linearity_and_identity(env):
     # and the whole thing agrees with an fp32 reference convolution exactly (all partial sums are small integers)
     ref = torch.nn.functional.conv2d(x.permute(0, 3, 1, 2), w1, padding=1).permute(0, 2, 3, 1)
     assert torch.equal(z1, ref.contiguous())
+
+
+def test_conv_epilogue_statistics_full_size(env):
+    """res2 3x3 64->64 at 28x28, batch 256 (1568 tiles, every persistent CTA accumulates ~10 tiles before its flush) and the
+    1x1 256->1024 at 7x7 (256-wide tiles, four N tiles): conv_fwd_bnstats + bn_fwd_prestats must leave every output channel
+    with mean 0 / std 1 and saved statistics equal to the directly computed moments of z -- for a pivot of 0 and for one
+    3 sigma away from the mean."""
+    torch, L, H, h, stream = env
+    for (B, Cin, Hh, W, Cout, k, mode) in ((256, 64, 28, 28, 64, 3, "Same"), (256, 256, 7, 7, 1024, 1, "Truncate")):
+        d = H.conv_desc((B, Cin, Hh, W), Cout, (k, k), (1, 1), (0, 0), (1, 1), mode)
+        rows = C.c_int(0)
+        L.call("dl4jb200_conv_fwd_bnstats_rows", h, C.byref(d), Cin, Cout, L.ALGO_TC_TF32, C.byref(rows))
+        assert rows.value > 0
+        with torch.cuda.stream(stream):
+            g = torch.Generator(device="cuda").manual_seed(3)
+            x = torch.rand(B, Hh, W, Cin, device="cuda", generator=g)
+            w = torch.randn(Cout, Cin, k, k, device="cuda", generator=g) * 0.2
+            b = torch.randn(Cout, device="cuda", generator=g)
+            z, y = torch.empty(B, d.out_h, d.out_w, Cout, device="cuda"), torch.empty(B, d.out_h, d.out_w, Cout, device="cuda")
+            z0 = torch.empty_like(z)
+            gamma, beta = torch.ones(Cout, device="cuda"), torch.zeros(Cout, device="cuda")
+            stat = torch.empty(rows.value * 2 * Cout, device="cuda")
+        stream.synchronize()
+        L.call("dl4jb200_conv_fwd", h, C.byref(d), _p(x), L.NHWC, Cin, _p(w), _p(b), _p(z0), L.NHWC, Cout, L.ACT_IDENTITY, L.ALGO_TC_TF32)
+        stream.synchronize()
+        zd = z0.double()
+        mean, var = zd.mean((0, 1, 2)), zd.var((0, 1, 2), unbiased=False)
+        for pivot in (torch.zeros(Cout, device="cuda"), (mean + 3 * var.sqrt()).float()):
+            with torch.cuda.stream(stream):
+                gm, gv = torch.zeros(Cout, device="cuda"), torch.ones(Cout, device="cuda")
+                sm, ss = torch.empty(Cout, device="cuda"), torch.empty(Cout, device="cuda")
+                stat.fill_(float("nan"))
+            stream.synchronize()
+            L.call("dl4jb200_conv_fwd_bnstats", h, C.byref(d), _p(x), Cin, _p(w), _p(b), _p(z), Cout, L.ALGO_TC_TF32, _p(pivot), _p(stat))
+            L.call("dl4jb200_bn_fwd_prestats", h, _p(z), _p(y), _p(gamma), _p(beta), _p(gm), _p(gv), _p(sm), _p(ss), B, Cout, d.out_h,
+                   d.out_w, Cout, 0.9, 1e-5, 1, L.ACT_IDENTITY, None, _p(pivot), _p(stat), rows.value)
+            stream.synchronize()
+            assert torch.equal(z, z0)
+            assert not torch.isnan(stat).any()  # every partial row was written
+            yd = y.double()
+            assert float(yd.mean((0, 1, 2)).abs().max()) < 1e-4
+            assert float((yd.std((0, 1, 2), unbiased=False) - 1).abs().max()) < 1e-4
+            np.testing.assert_allclose(sm.cpu().numpy(), mean.cpu().numpy(), rtol=1e-4, atol=1e-5)
+            np.testing.assert_allclose(ss.cpu().numpy(), (var + 1e-5).sqrt().cpu().numpy(), rtol=1e-4)
