@@ -151,3 +151,28 @@ def test_conv_epilogue_statistics_full_size(env):
             assert float((yd.std((0, 1, 2), unbiased=False) - 1).abs().max()) < 1e-4
             np.testing.assert_allclose(sm.cpu().numpy(), mean.cpu().numpy(), rtol=1e-4, atol=1e-5)
             np.testing.assert_allclose(ss.cpu().numpy(), (var + 1e-5).sqrt().cpu().numpy(), rtol=1e-4)
+
+
+def test_fused_backprop_data_epilogue_full_size(env):
+    """res2 1x1 256->64 backprop-data at batch 256 (51 M outputs): the fused epilogue (epsilon fan-in + ReLU mask inside the
+    GEMM) must equal, bit for bit, plain backprop-data followed by eps_sum_act_bwd -- same accumulators, same fp32 add."""
+    torch, L, H, h, stream = env
+    B, Cin, Hh, W, Cout = 256, 256, 28, 28, 64
+    d = H.conv_desc((B, Cin, Hh, W), Cout, (1, 1), (1, 1), (0, 0), (1, 1), "Truncate")
+    with torch.cuda.stream(stream):
+        g = torch.Generator(device="cuda").manual_seed(9)
+        w = torch.randn(Cout, Cin, 1, 1, device="cuda", generator=g) * 0.1
+        delta = torch.randn(B, Hh, W, Cout, device="cuda", generator=g)
+        prior = torch.randn(B, Hh, W, Cin, device="cuda", generator=g)
+        act_out = torch.relu(torch.randn(B, Hh, W, Cin, device="cuda", generator=g))
+        dx_f, dx_p, dx_u = torch.empty_like(prior), torch.empty_like(prior), torch.empty_like(prior)
+    stream.synchronize()
+    L.call("dl4jb200_conv_bwd_data_fused", h, C.byref(d), _p(w), _p(delta), Cout, _p(dx_f), Cin, _p(prior), _p(act_out), L.ACT_RELU,
+           L.ALGO_TC_TF32)
+    L.call("dl4jb200_conv_bwd", h, C.byref(d), _p(prior), L.NHWC, Cin, _p(w), _p(delta), L.NHWC, Cout, None, None, _p(dx_p), L.NHWC, Cin,
+           L.ALGO_TC_TF32)
+    L.call("dl4jb200_eps_sum_act_bwd", h, _p(dx_p), _p(prior), _p(act_out), _p(dx_u), dx_u.numel(), L.ACT_RELU)
+    stream.synchronize()
+    assert torch.equal(dx_f, dx_u)
+    assert float((dx_f[act_out <= 0]).abs().max()) == 0.0
+    assert float(dx_f.abs().max()) > 0.0
