@@ -176,3 +176,36 @@ def test_fused_backprop_data_epilogue_full_size(env):
     assert torch.equal(dx_f, dx_u)
     assert float((dx_f[act_out <= 0]).abs().max()) == 0.0
     assert float(dx_f.abs().max()) > 0.0
+
+
+def test_conv_backward_full_size_exact_on_integer_operands(env):
+    """res2x_branch2b backward at batch 256 (3x3 SAME 64->64, M = 200 704 pixels, 59 split-K ranges): with small-integer
+    operands every product and partial sum is exactly representable, so the TF32 filter gradient (split-K + finalize), the
+    bias gradient (column sums and, with TF32-stored deltas, the GEMM's ones column) and the data gradient must equal an
+    fp32 reference bit for bit."""
+    torch, L, H, h, stream = env
+    B, Cc, Hh, W = 256, 64, 28, 28
+    d = H.conv_desc((B, Cc, Hh, W), Cc, (3, 3), (1, 1), (0, 0), (1, 1), "Same")
+    with torch.cuda.stream(stream):
+        g = torch.Generator(device="cuda").manual_seed(11)
+        x = torch.randint(-4, 5, (B, Hh, W, Cc), device="cuda", generator=g).float()
+        w = torch.randint(-2, 3, (Cc, Cc, 3, 3), device="cuda", generator=g).float()
+        delta = torch.randint(-2, 3, (B, Hh, W, Cc), device="cuda", generator=g).float()
+        dw, db, dx = torch.empty_like(w), torch.empty(Cc, device="cuda"), torch.empty_like(x)
+    stream.synchronize()
+    xn, dn = x.permute(0, 3, 1, 2).contiguous(), delta.permute(0, 3, 1, 2).contiguous()
+    dw_ref = torch.nn.grad.conv2d_weight(xn.double(), w.shape, dn.double(), padding=1).float()
+    dx_ref = torch.nn.grad.conv2d_input(xn.shape, w.double(), dn.double(), padding=1).float().permute(0, 2, 3, 1).contiguous()
+    db_ref = delta.double().sum((0, 1, 2)).float()
+    for opt in (0, 1):
+        L.call("dl4jb200_ctx_set_option", h, L.OPT_TF32_ACTIVATIONS, opt)
+        with torch.cuda.stream(stream):
+            dw.fill_(float("nan")); db.fill_(float("nan")); dx.fill_(float("nan"))
+        stream.synchronize()
+        L.call("dl4jb200_conv_bwd", h, C.byref(d), _p(x), L.NHWC, Cc, _p(w), _p(delta), L.NHWC, Cc, _p(dw), _p(db), _p(dx), L.NHWC, Cc,
+               L.ALGO_TC_TF32)
+        stream.synchronize()
+        assert torch.equal(dw, dw_ref), opt
+        assert torch.equal(db, db_ref), opt
+        assert torch.equal(dx, dx_ref), opt
+    L.call("dl4jb200_ctx_set_option", h, L.OPT_TF32_ACTIVATIONS, 0)
