@@ -93,6 +93,38 @@ def alexnet(num_labels=1000, input_shape=(3, 224, 224), dropout=None):
             "l1": 0.0, "l2": 5e-4, "minibatch": False, "grad_norm": "RenormalizeL2PerLayer", "seed": 123}
 
 
+def simplecnn(num_labels=1000, input_shape=(3, 48, 48), dropout=None):
+    """ZOO/model/SimpleCNN.java:67-131 (zoo default input 3x48x48): SAME mode, WeightInit.RELU, four blocks of
+    [conv k, BN, conv k, BN, ReLU, avg 2x2/2, DropoutLayer(0.5)] with k = 7, 5, 3, 3 and 16, 32, 64, 128 maps, then conv3 256,
+    BN, conv3 -> numLabels and a GlobalPoolingLayer(AVG) (= average pooling over the whole remaining map). The reference
+    config has no loss layer, so fit() cannot train it (MultiLayerNetwork.java:1405-1408): a forward-only graph, ending at
+    the pooled class scores that the final softmax ActivationLayer would normalise. A DropoutLayer is dropout on the next
+    layer's input: dropout=0.5 puts it there (mask-fed, see alexnet); default off."""
+    v = [{"name": "input", "op": "input", "in": []}]
+    prev = "input"
+    hw = list(input_shape[1:])
+    for blk, (k, c) in enumerate([(7, 16), (5, 32), (3, 64), (3, 128)], 1):
+        for j in (1, 2):
+            v.append(_conv(f"b{blk}_conv{j}", prev, c, (k, k), mode="Same"))
+            if dropout and blk > 1 and j == 1:
+                v[-1]["dropout"] = float(dropout)
+            v.append(_bn(f"b{blk}_bn{j}", f"b{blk}_conv{j}", RELU if j == 2 else IDENTITY))  # ActivationLayer(ReLU) folded
+            prev = f"b{blk}_bn{j}"
+        v.append(_pool(f"b{blk}_pool", prev, "AVG", (2, 2), (2, 2), mode="Same"))
+        prev = f"b{blk}_pool"
+        hw = [(hw[0] + 1) // 2, (hw[1] + 1) // 2]
+    v.append(_conv("b5_conv1", prev, 256, (3, 3), mode="Same"))
+    if dropout:
+        v[-1]["dropout"] = float(dropout)
+    v.append(_bn("b5_bn1", "b5_conv1"))
+    v.append(_conv("b5_conv2", "b5_bn1", num_labels, (3, 3), mode="Same"))
+    v.append(_pool("global_avg", "b5_conv2", "AVG", tuple(hw), (1, 1)))
+    v.append({"name": "scores", "op": "flatten", "in": ["global_avg"]})
+    return {"name": "simplecnn", "input": tuple(input_shape), "vertices": v, "weight_init": ("relu",),
+            "updater": {"kind": "adadelta", "rho": 0.95, "eps": 1e-6}, "l1": 0.0, "l2": 0.0, "minibatch": True,
+            "grad_norm": None, "seed": 123}
+
+
 def resnet50(num_labels=1000, input_shape=(3, 224, 224)):
     """ZOO/model/ResNet50.java:89-225 (DL4J's variant: stage-2 conv block has stride 2 so stages run at
     28/14/7/4 px; the 'avgpool' is a MAX 3x3 s2). ActivationLayers following BN / Add are folded into them.
@@ -140,7 +172,7 @@ def resnet50(num_labels=1000, input_shape=(3, 224, 224)):
             "minibatch": True, "grad_norm": None, "seed": 123}
 
 
-MODELS = {"lenet": lenet, "vgg16": vgg16, "alexnet": alexnet, "resnet50": resnet50}
+MODELS = {"lenet": lenet, "vgg16": vgg16, "alexnet": alexnet, "simplecnn": simplecnn, "resnet50": resnet50}
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -221,6 +253,8 @@ def init_params(model, seed=None):
                 fan_in, fan_out = shp[1], shp[0]
             if wi[0] == "xavier":
                 vals = rng.standard_normal(n) * np.sqrt(2.0 / (fan_in + fan_out))
+            elif wi[0] == "relu":  # WeightInit.RELU: N(0, 2 / fanIn) (WeightInitUtil.java)
+                vals = rng.standard_normal(n) * np.sqrt(2.0 / fan_in)
             else:
                 vals = rng.standard_normal(n) * wi[1]
             flat[off:off + n] = vals.astype(np.float32)

@@ -326,3 +326,40 @@ def test_alexnet_full_size_step_parity():
     from deeplearning4j_b200 import _lib, zoo
     m = zoo.alexnet()
     _run_case(m, 4, 1000, _lib.ALGO_FP32, 1, False, 5e-4, 5e-4, 2e-4, seed=7)
+
+
+@pytest.mark.parametrize("algo_name", ["fp32", "tf32"])
+def test_simplecnn_forward_parity(algo_name):
+    """BASELINE's SimpleCNN configuration (zoo default 3x48x48; nine BatchNormalization layers, 7x7 / 5x5 / 3x3 SAME
+    convolutions, four avg 2x2 pools, GlobalPooling(AVG) as a whole-map average pool). The reference config has no loss
+    layer and cannot be trained, so the check is the training-mode forward pass: every activation up to the pooled class
+    scores, and the BN running statistics it leaves behind."""
+    from deeplearning4j_b200 import _lib, network, zoo
+    from oracle.net_oracle import OracleNet
+    algo = _lib.ALGO_FP32 if algo_name == "fp32" else _lib.ALGO_TC_TF32
+    tol = 1e-4 if algo_name == "fp32" else 2e-2
+    m = zoo.simplecnn(num_labels=10)
+    B = 8
+    P, layout = zoo.param_layout(m)
+    p0 = zoo.init_params(m)
+    x, lab = _data(m, B, 10)
+    ref = OracleNet(m, layout, P, p0, fast=False)
+    want = ref.forward(x, None, True)
+    net = network.Network(m, B, algo=algo, params=p0, with_score=False)
+    try:
+        net.set_batch(x, lab)
+        net.forward(True)
+        net.sync()
+        for v in m["vertices"]:
+            n = v["name"]
+            if v["op"] in ("input", "zeropad"):
+                continue
+            got = net.output_host(n)
+            assert rel_err(got, want[n].reshape(got.shape)) <= tol, (n, rel_err(got, want[n].reshape(got.shape)))
+        p = net.params.cpu().numpy()
+        for name, key, off, shp, pk in layout:  # running mean / var written by the forward pass
+            if pk == "bn_stat":
+                k = int(np.prod(shp))
+                assert rel_err(p[off:off + k], ref.params[off:off + k]) <= tol, (name, key)
+    finally:
+        net.close()
