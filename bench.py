@@ -22,12 +22,35 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+
+def _host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# CPU legs (the reference arm, cpu_baseline): the oracle's C loops are OpenMP, its GEMMs are numpy's OpenBLAS (own
+# thread pool). OpenMP workers that spin after a parallel region fight the BLAS threads for the same cores -- measured
+# here: 4.7 images/s spinning vs 8.4 passive on 8 cores -- so waiting threads sleep; and torchrun's OMP_NUM_THREADS=1 is
+# lifted for the rank that runs the CPU arm. Must be set before libgomp / OpenBLAS initialise (i.e. before numpy).
+os.environ["OMP_WAIT_POLICY"] = "PASSIVE"
+if "reference" in sys.argv or int(os.environ.get("WORLD_SIZE", "1")) == 1:
+    os.environ["OMP_NUM_THREADS"] = str(_host_threads())
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", str(min(_host_threads(), 64)))
+
 import numpy as np  # noqa: E402
 
-MODEL, BATCH, LABELS = "resnet50", 256, 1000
-WORKLOAD = ("ResNet-50 (DL4J zoo ComputationGraph, BatchNormalization) 3x224x224 full training step "
-            "(forward, backward, score, RmsProp+L1/L2 updater)")
-REF_SAMPLE_BATCH = 4
+# model -> (per-GPU batch, labels, reference-arm sample batch, workload text); batches are BASELINE.json's configs
+CONFIGS = {
+    "resnet50": (256, 1000, 32, "ResNet-50 (DL4J zoo ComputationGraph, BatchNormalization) 3x224x224 full training step "
+                                "(forward, backward, score, RmsProp+L1/L2 updater)"),
+    "vgg16": (64, 1000, 8, "VGG16 (DL4J zoo, 13 conv3x3+ReLU, 5 max-pool, softmax 25088->1000) 3x224x224 full training step "
+                           "(forward, backward, score, Nesterovs updater)"),
+    "alexnet": (128, 1000, 32, "AlexNet (DL4J zoo) 3x224x224 full training step (forward with inverted dropout 0.5 on every "
+                               "layer input, backward, score, RenormalizeL2PerLayer + Nesterovs + L2 updater)"),
+    "lenet": (64, 10, 64, "LeNet (DL4J zoo) 1x28x28 full training step (forward, backward, score, AdaDelta updater)"),
+}
 
 
 def peaks():
@@ -111,37 +134,93 @@ def conv_alg_bytes(net):
     return tot
 
 
+def blas_threads():
+    try:
+        from threadpoolctl import threadpool_info
+        return {f"{i.get('user_api')}:{i.get('internal_api')}": i.get("num_threads") for i in threadpool_info()}
+    except Exception:  # noqa: BLE001
+        return {}
+
+
+def make_masks(model, shapes, B, seed=777):
+    """Host-generated 0/1 masks for every vertex with a dropout retain probability (nd4j's DropOutInverted stream cannot be
+    reproduced outside nd4j, so the masks are inputs of the step; the bench reuses one fixed set)."""
+    rng = np.random.default_rng(seed)
+    masks = {}
+    for v in model["vertices"]:
+        p = v.get("dropout")
+        if p:
+            s = shapes[v["in"][0]]
+            masks[v["name"]] = (rng.random((B,) + tuple(s)) < p).astype(np.float32)
+    return masks or None
+
+
+def cpu_reference_step(model_name, Bs, steps, warm):
+    """Times `steps` full fit() iterations of the reference's CPU algorithm (oracle/: im2col + BLAS sgemm + col2im, the
+    multi-pass BN / pooling, updater) at batch Bs on the host cores. Imports nothing of the CUDA library."""
+    from deeplearning4j_b200 import zoo  # model tables only: shape arithmetic is routed to the oracle below
+    from oracle import oracle as o
+    from oracle.net_oracle import OracleNet
+    o.build()
+    labels = CONFIGS[model_name][1]
+    m = zoo.MODELS[model_name](dropout=0.5) if model_name == "alexnet" else zoo.MODELS[model_name]()
+    P, layout = zoo.param_layout(m, o.out_size)
+    x, lab = synthetic(m, Bs, labels)
+    p0 = zoo.init_params(m, out_size=o.out_size)
+    net = OracleNet(m, layout, P, p0, fast=True)
+    net.masks = make_masks(m, zoo.infer_shapes(m, o.out_size), Bs)
+    # Every step starts from the initial parameters: after one RmsProp(0.1) update of this untrained net most activations are
+    # denormal, and x86 denormal arithmetic made later steps 9x slower here (4 s -> 38 s at batch 32) -- a value-dependent
+    # CPU artefact the GPU does not have. Resetting keeps the CPU number reproducible and errs in the CPU's favour.
+    total = 0.0
+    for i in range(warm + steps):
+        net.params[:] = p0
+        net.state[:] = 0.0
+        t0 = time.perf_counter()
+        net.fit(x, lab)
+        if i >= warm:
+            total += time.perf_counter() - t0
+    return total / steps
+
+
 def run_reference(args, rank, world):
     """The reference arm: the reference's CPU algorithm for the same step, timed on the host cores (rank 0 only)."""
     if rank != 0:
         return
-    from deeplearning4j_b200 import zoo
-    from oracle import oracle as o
-    from oracle.net_oracle import OracleNet
-    o.build()
-    m = zoo.MODELS[MODEL]()
-    P, layout = zoo.param_layout(m)
-    Bs = REF_SAMPLE_BATCH
-    x, lab = synthetic(m, Bs, LABELS)
-    net = OracleNet(m, layout, P, zoo.init_params(m), fast=True)
-    steps, warm = max(1, min(args.steps, 8)), max(1, min(args.warmup, 2))
-    for _ in range(warm):
-        net.fit(x, lab)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        net.fit(x, lab)
-    dt = (time.perf_counter() - t0) / steps
+    B, labels, Bs, workload = CONFIGS[args.model]
+    Bs = min(Bs, args.batch or B)
+    steps, warm = max(1, min(args.steps, 3)), 1
+    dt = cpu_reference_step(args.model, Bs, steps, warm)
     v = Bs / dt
-    cores = os.cpu_count() or 1
+    cores = _host_threads()
     print(json.dumps({
-        "impl": "reference", "metric": "resnet50_train_images_per_sec", "value": v, "unit": "images/s", "n_gpus": args.gpus,
+        "impl": "reference", "metric": f"{args.model}_train_images_per_sec", "value": v, "unit": "images/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "per_gpu_batch": BATCH,
-                   "sample": f"reference CPU algorithm on the host cores, each step one full fit() at batch {Bs} of the same network"},
-        "cpu_baseline": {"value": v, "unit": "images/s", "cores": cores, "kind": "port",
-                         "sample": f"{steps} full fit() iterations at batch {Bs} (im2col + OpenBLAS sgemm + col2im, OpenMP over all cores)"},
+        "config": {"workload": workload, "global_batch": (args.batch or B) * world, "per_gpu_batch": args.batch or B, "sample_batch": Bs,
+                   "sample": f"reference CPU algorithm on the host cores; each timed step is one full fit() of the same network at "
+                             f"batch {Bs} (a bounded sample of the batch-{args.batch or B} step: images/s = {Bs} / step time; every step starts from the "
+                             f"initial parameters so that x86 denormal slow-downs of later steps do not handicap the CPU)"},
+        "cpu_baseline": {"value": v, "unit": "images/s", "cores": cores, "kind": "port", "threads": blas_threads(),
+                         "sample": f"{steps} full fit() iterations at batch {Bs} after {warm} warm-up (im2col + OpenBLAS sgemm + col2im; "
+                                   f"OpenMP loops on {os.environ.get('OMP_NUM_THREADS')} threads, passive wait policy)"},
         "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def tf32_peak(pk):
+    """(TFLOP/s, note): the TF32 dense roof. Measured on this pool's B200s by scripts/measure_tf32_peak.py (torch.matmul with
+    allow_tf32 = cuBLAS, 8192^3, burst and 4 s sustained -- the same method MEASURED_PEAKS.json uses for bf16) and committed
+    under profiles/; until that file exists the provisional 0.5 x bf16 sustained figure is used. Both are reported."""
+    half = pk["bf16_tflops_sustained"] / 2.0
+    f = os.path.join(ROOT, "profiles", "r02_tf32_peak.json")
+    if os.path.exists(f):
+        try:
+            j = json.load(open(f))
+            return float(j["tf32_tflops_sustained"]), (f"measured cuBLAS TF32 8192^3 sustained (profiles/r02_tf32_peak.json; burst "
+                                                       f"{j['tf32_tflops']:.0f}); 0.5 x bf16 sustained would be {half:.0f}")
+        except Exception:  # noqa: BLE001
+            pass
+    return half, f"TF32 dense = 0.5 x bf16_tflops_sustained ({pk['src']}), provisional: no measured TF32 peak file"
 
 
 def main():
@@ -150,7 +229,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours")
-    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--model", default="resnet50", choices=sorted(CONFIGS))
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: BASELINE.json's for the model)")
     ap.add_argument("--algo", default="tf32", choices=["tf32", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="time the eager kernel chain instead of the captured CUDA graph")
@@ -174,10 +254,14 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    m = zoo.MODELS[MODEL]()
-    B = args.batch
+    B0, LABELS, ref_batch, WORKLOAD = CONFIGS[args.model]
+    m = zoo.MODELS[args.model](dropout=0.5) if args.model == "alexnet" else zoo.MODELS[args.model]()
+    B = args.batch or B0
     algo = _lib.ALGO_TC_TF32 if args.algo == "tf32" else _lib.ALGO_FP32
     net = network.Network(m, B, device=local, algo=algo)
+    masks = make_masks(m, net.shapes, B)
+    if masks:
+        net.set_dropout_masks(masks)
     pw = parallel.ParallelWrapper(net) if world > 1 else None
     step = (lambda f=None, l=None: pw.fit(f, l)) if pw else (lambda f=None, l=None: net.fit(f, l))
     x, lab = synthetic(m, B, LABELS)
@@ -197,15 +281,23 @@ def main():
     if use_graph:
         try:
             net.capture(hook=pw._hook if pw else None, include_input=False)
-            gstep = net.fit_graph
             for _ in range(2):
-                gstep()
+                net._relayout_input()
+                net.fit_graph()
             barrier()
         except Exception as e:  # noqa: BLE001 -- capture is an optimisation: report and time the eager chain instead
             if rank == 0:
                 print(f"graph capture failed ({type(e).__name__}: {e}); timing the eager chain", file=sys.stderr)
             use_graph = False
-    run = gstep if use_graph else step
+
+    def run():
+        # one step on the resident minibatch: the NCHW -> NHWC (row-packed) re-layout of the features is part of it
+        if use_graph:
+            net._relayout_input()
+            net.fit_graph()
+        else:
+            net._relayout_input()
+            step()
 
     # ---- timed region 1: device-resident minibatch (CUDA events on the launching stream)
     sampler = ClockSampler(local)
@@ -237,6 +329,20 @@ def main():
     ms_e2e = f0.elapsed_time(f1)
     sampler.stop_flag = True
     sampler.join(timeout=2)
+
+    # ---- data-parallel check: after the timed steps every replica must hold bit-identical parameters
+    dp_check = None
+    if world > 1:
+        with torch.cuda.stream(net.stream):
+            pv = net.params.view(torch.int32)
+            chk = torch.stack([pv.sum(dtype=torch.int64), (pv.to(torch.int64) * 31 % 1000003).sum()])
+            lo, hi = chk.clone(), chk.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        net.sync()
+        dp_check = {"replicas_bit_identical": bool((lo == hi).all().item()), "ranks": world,
+                    "how": "all-reduce MIN == MAX of two integer checksums of the flat parameter vector after the timed steps"}
+
     # what the box's host link gives a lone pinned copy of one minibatch (explains e2e on boxes where it is below
     # bytes / step time: the prefetch then cannot hide the copy)
     dev_x = torch.empty_like(xh, device=net.dev)
@@ -252,11 +358,17 @@ def main():
     del dev_x
 
     # ---- kernel-level pass: the same step issued eagerly with a CUDA-event pair around every conv / BN / pool call
-    # (a replayed graph cannot carry per-kernel events); feeds the roofline and the launch count
+    # (a replayed graph cannot carry per-kernel events); feeds the roofline and the launch count. The captured graph is
+    # dropped first: on one stream the filter gradients use the main context's scratch, which may have to grow.
+    if use_graph:
+        net.release_graph()
     net.overlap_wgrad = False  # one stream: every call is timed alone (in the timed regions above the filter gradients overlap the backward chain)
     net.profile(["dl4jb200_conv_fwd", "dl4jb200_conv_fwd_bnstats", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_wgrad",
-                 "dl4jb200_bn_fwd", "dl4jb200_bn_fwd_prestats", "dl4jb200_bn_bwd", "dl4jb200_pool_fwd", "dl4jb200_pool_bwd"])
+                 "dl4jb200_conv_rowpack_fwd_bnstats", "dl4jb200_bn_fwd", "dl4jb200_bn_fwd_prestats", "dl4jb200_bn_bwd", "dl4jb200_pool_fwd", "dl4jb200_pool_bwd"])
     psteps = min(args.steps, 10)
+    step()  # untimed: lets the single-stream variant size its scratch
+    barrier()
+    net.prof = []
     l0 = _lib.cdll().dl4jb200_launch_count()
     p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -274,6 +386,7 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, ms_e2e = float(t[0]), float(t[1])
+
     def finish():
         # NCCL communicators referenced by a captured CUDA graph make destroy_process_group() block: drop the graph,
         # drain, flush and leave without the collective teardown
@@ -296,7 +409,7 @@ def main():
     n_conv_calls = 0
     per_layer = {}
     conv_fns = ("dl4jb200_conv_fwd", "dl4jb200_conv_fwd_bnstats", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_rowpack_fwd",
-                "dl4jb200_conv_rowpack_wgrad")
+                "dl4jb200_conv_rowpack_fwd_bnstats", "dl4jb200_conv_rowpack_wgrad")
     passes = {}  # (layer, "fwd"|"bwd") -> [ms over psteps, calls]: a layer's backward is several calls (filter / data gradient)
     for (fn, tag), times in prof.items():
         if fn in conv_fns and tag in fl:
@@ -310,21 +423,24 @@ def main():
         n_conv_calls += calls
         per_layer[f"{tag}:conv_{ps}"] = {"ms": tms / psteps, "tflops": f / (tms / psteps * 1e-3) / 1e12}
     # DRAM bytes of the same kernel family from the committed ncu capture (cold-cache, serialised): per call, like `achieved`
-    traffic, traffic_note = None, "no ncu capture found"
-    try:
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_conv_traffic.json")))
-        traffic = (tr["dram_read_bytes"] + tr["dram_write_bytes"]) / max(1, n_conv_calls // psteps)
-        traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum of the %d convolution-family launches of one step "
-                        "(profiles/r01_conv_traffic.json, batch 256) / calls per step; algorithmic bytes per step: %.2f GB"
-                        % (tr["launches"], conv_alg_bytes(net) / 1e9))
-    except Exception:  # noqa: BLE001
-        pass
-    tf32_peak = pk["bf16_tflops_sustained"] / 2.0
+    traffic, traffic_note = None, "no ncu capture for this model"
+    if args.model == "resnet50" and B == 256:
+        for name in ("r02_conv_traffic.json", "r01_conv_traffic.json"):
+            try:
+                tr = json.load(open(os.path.join(ROOT, "profiles", name)))
+                traffic = (tr["dram_read_bytes"] + tr["dram_write_bytes"]) / max(1, n_conv_calls // psteps)
+                traffic_note = ("dram__bytes_read.sum + dram__bytes_write.sum of the %d convolution-family launches of one step "
+                                "(profiles/%s, batch 256) / calls per step; algorithmic bytes per step: %.2f GB"
+                                % (tr["launches"], name, conv_alg_bytes(net) / 1e9))
+                break
+            except Exception:  # noqa: BLE001
+                pass
+    roof, roof_note = tf32_peak(pk)
     ach = conv_fl / (conv_ms * 1e-3) / 1e12 if conv_ms else 0.0
     roofline = {"bound": "tensor", "kernel": "k_conv_tc_gemm_tma_persist / k_conv_tc_wgrad_tma (all convolution + dense calls of the step)",
-                "achieved": ach, "peak": tf32_peak, "unit": "TFLOP/s", "frac": ach / tf32_peak, "traffic": traffic,
-                "traffic_note": traffic_note,
-                "peak_note": f"TF32 dense = 0.5 x bf16_tflops_sustained ({pk['src']}); kernel timed inside a long step",
+                "achieved": ach, "peak": roof, "unit": "TFLOP/s", "frac": ach / roof, "traffic": traffic,
+                "traffic_note": traffic_note, "peak_note": roof_note + "; kernel timed inside a long step",
+                "frac_of_half_bf16_sustained": ach / (pk["bf16_tflops_sustained"] / 2.0),
                 "share_of_step": conv_ms / (ms_eager * psteps), "calls_per_step": n_conv_calls // psteps,
                 "timing": "CUDA events per call in an eager single-stream pass of the same step (%.2f ms/step eager serial vs %.2f ms/step graph with overlapped filter gradients)" % (ms_eager, ms / args.steps)}
     # ---- HBM kernels (BN / pool): achieved GB/s on algorithmic bytes
@@ -334,9 +450,9 @@ def main():
         tot_ms = tot_b = 0.0
         for (f2, tag), times in prof.items():
             if f2 in fns:
-                s = net.shapes[tag]
+                sh = net.shapes[tag if tag in net.shapes and net.vmap[tag]["op"] == "bn" else net.fused_add.get(tag, (tag,))[0]]
                 tot_ms += sum(times)
-                tot_b += float(B) * s[0] * s[1] * s[2] * bpe * len(times)
+                tot_b += float(B) * sh[0] * sh[1] * sh[2] * bpe * len(times)
         if tot_ms:
             bw[key] = {"achieved_gbs": tot_b / (tot_ms * 1e-3) / 1e9, "frac_of_hbm": tot_b / (tot_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
                        "share_of_step": tot_ms / (ms_eager * psteps)}
@@ -358,34 +474,29 @@ def main():
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        from oracle import oracle as o
-        from oracle.net_oracle import OracleNet
-        o.build()
-        P, layout = zoo.param_layout(m)
-        xs, ls = synthetic(m, REF_SAMPLE_BATCH, LABELS)
-        ref = OracleNet(m, layout, P, zoo.init_params(m), fast=True)
-        ref.fit(xs, ls)
-        t0 = time.perf_counter()
+        Bs = min(ref_batch, B)
         nref = 2
-        for _ in range(nref):
-            ref.fit(xs, ls)
-        dt = (time.perf_counter() - t0) / nref
-        cpu = {"value": REF_SAMPLE_BATCH / dt, "unit": "images/s", "cores": os.cpu_count() or 1, "kind": "port",
-               "sample": f"{nref} full fit() iterations of the same network at batch {REF_SAMPLE_BATCH} "
-                         "(reference CPU algorithm: im2col + OpenBLAS sgemm + col2im, OpenMP over all cores)"}
+        dt = cpu_reference_step(args.model, Bs, nref, 1)
+        cpu = {"value": Bs / dt, "unit": "images/s", "cores": _host_threads(), "kind": "port", "threads": blas_threads(),
+               "sample": f"{nref} full fit() iterations of the same network at batch {Bs} after 1 warm-up "
+                         "(reference CPU algorithm: im2col + OpenBLAS sgemm + col2im, OpenMP over all cores, passive wait policy)"}
 
     line = {
-        "metric": "resnet50_train_images_per_sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "metric": f"{args.model}_train_images_per_sec", "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "tf32" if args.algo == "tf32" else "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "global_batch": B * world,
                    "per_gpu_batch": B, "parallelism": f"dp{world}" if world > 1 else "single",
-                   "l2_flush": "working set (>= 10 GB of activations per step) exceeds the 126 MB L2",
-                   "launch": "CUDA graph replay of the whole step" if use_graph else "eager kernel chain"},
+                   "l2_flush": "working set (>= 10 GB of activations per step) exceeds the 126 MB L2" if args.model != "lenet"
+                               else "none: the whole LeNet step fits L2 (latency-bound config)",
+                   "launch": ("input re-layout + CUDA graph replay of the whole step" if use_graph else "eager kernel chain"),
+                   "dropout": "fixed host-generated masks (inputs of the step)" if masks else "none"},
         "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": int(x.nbytes + lab.nbytes), "d2h_bytes_per_step": 4,
                 "ms_per_step": ms_e2e / args.steps, "last_score": last, "h2d_link_gbs": h2d_gbs},
         "gpu_launches": int(launches), "clocks": sampler.summary(), "roofline": roofline, "hbm_kernels": bw,
     }
+    if dp_check:
+        line["dp_check"] = dp_check
     if cpu:
         line["cpu_baseline"] = cpu
     json_out.write(json.dumps(line) + "\n")

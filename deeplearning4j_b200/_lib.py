@@ -14,6 +14,7 @@ MODE_STRICT, MODE_TRUNCATE, MODE_SAME = 0, 1, 2
 NCHW, NHWC = 0, 1
 POOL_MAX, POOL_AVG, POOL_SUM, POOL_PNORM = 0, 1, 2, 3
 ACT_IDENTITY, ACT_RELU, ACT_SIGMOID, ACT_TANH, ACT_LEAKYRELU = 0, 1, 2, 3, 4
+ACT_FROM_OUTPUT = 0x200
 ALGO_TC_TF32, ALGO_FP32 = 0, 1
 OPT_TF32_ACTIVATIONS = 1
 UPD_SGD, UPD_NESTEROVS, UPD_RMSPROP, UPD_ADADELTA, UPD_NOOP = 0, 1, 2, 3, 4
@@ -54,6 +55,7 @@ PROTOTYPES = {
     "dl4jb200_ctx_set_stream": [_vp, _vp],
     "dl4jb200_ctx_set_option": [_vp, _i, _i],
     "dl4jb200_ctx_sync": [_vp],
+    "dl4jb200_ctx_workspace_freeze": [_vp, _i],
     "dl4jb200_malloc": [_vp, _sz, C.POINTER(_vp)],
     "dl4jb200_free": [_vp, _vp],
     "dl4jb200_memset": [_vp, _vp, _i, _sz],
@@ -110,6 +112,7 @@ _SPECIAL = {
     "dl4jb200_ctx_stream": (_vp, [_vp]),
     "dl4jb200_ctx_workspace_bytes": (_sz, [_vp]),
     "dl4jb200_ctx_sm_count": (_i, [_vp]),
+    "dl4jb200_ctx_workspace_generation": (C.c_ulonglong, [_vp]),
 }
 
 _cdll = None

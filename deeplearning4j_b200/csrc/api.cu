@@ -15,6 +15,12 @@ void dl4j_set_error(const char *fmt, ...) {
 
 void *dl4j_workspace(dl4jb200_ctx *ctx, int slot, size_t bytes) {
     if (bytes <= ctx->ws_bytes[slot] && ctx->ws[slot]) return ctx->ws[slot];
+    if (ctx->ws_frozen) {
+        dl4j_set_error("workspace: slot %d would have to grow from %zu to %zu bytes, but the context's scratch is frozen "
+                       "(a captured CUDA graph references it): warm up with every shape before capturing, or unfreeze and "
+                       "re-capture", slot, ctx->ws_bytes[slot], bytes);
+        return nullptr;
+    }
     // grow: the old region may still be in use by enqueued kernels -> drain the stream first
     size_t want = bytes + bytes / 4 + (1 << 20);
     if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) { dl4j_set_error("workspace: stream sync failed"); return nullptr; }
@@ -27,6 +33,7 @@ void *dl4j_workspace(dl4jb200_ctx *ctx, int slot, size_t bytes) {
         return nullptr;
     }
     ctx->ws_bytes[slot] = want;
+    ctx->ws_generation++;
     return ctx->ws[slot];
 }
 
@@ -107,6 +114,14 @@ size_t dl4jb200_ctx_workspace_bytes(dl4jb200_ctx *ctx) {
 }
 
 int dl4jb200_ctx_sm_count(dl4jb200_ctx *ctx) { return ctx ? ctx->sm_count : 0; }
+
+int dl4jb200_ctx_workspace_freeze(dl4jb200_ctx *ctx, int frozen) {
+    DL4J_REQUIRE(ctx, "ctx is NULL");
+    ctx->ws_frozen = frozen != 0;
+    return DL4JB200_OK;
+}
+
+unsigned long long dl4jb200_ctx_workspace_generation(dl4jb200_ctx *ctx) { return ctx ? ctx->ws_generation : 0; }
 
 int dl4jb200_malloc(dl4jb200_ctx *ctx, size_t bytes, void **out) {
     DL4J_REQUIRE(ctx && out, "malloc: NULL argument");

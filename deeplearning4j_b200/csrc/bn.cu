@@ -419,6 +419,7 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
     DL4J_REQUIRE(ctx && x && y && gmean && gvar, "bn_fwd: NULL argument");
     DL4J_REQUIRE(!residual || layout == DL4JB200_NCHW || al16(residual), "bn_fwd: residual must be 16-byte aligned");
     DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, "bn_fwd: bad shape");
+    DL4J_REQUIRE((long long)B * H * W < (1LL << 31), "bn_fwd: B*H*W must stay below 2^31");
     DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "bn_fwd: unknown layout %d", layout);
     DL4J_REQUIRE(layout == DL4JB200_NCHW || (cs >= C && cs % 4 == 0 && al16(x) && al16(y)), "bn_fwd: NHWC needs cs %% 4 == 0, cs >= C and 16-byte aligned tensors");
     DL4J_REQUIRE(C <= 65535 * 8, "bn_fwd: too many channels");
@@ -486,6 +487,7 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
                     int C, int H, int W, int layout, int cs) {
     DL4J_REQUIRE(ctx && x && eps && save_mean && save_std && dx, "bn_bwd: NULL argument");
     DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, "bn_bwd: bad shape");
+    DL4J_REQUIRE((long long)B * H * W < (1LL << 31), "bn_bwd: B*H*W must stay below 2^31");
     DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "bn_bwd: unknown layout %d", layout);
     DL4J_REQUIRE(layout == DL4JB200_NCHW || (cs >= C && cs % 4 == 0 && al16(x) && al16(eps) && al16(dx)),
                  "bn_bwd: NHWC needs cs %% 4 == 0, cs >= C and 16-byte aligned tensors");
@@ -532,13 +534,12 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
 // obtained from cudaMalloc the first time (and whenever a larger tensor comes along). Some callers must never
 // trigger a device allocation: a serving or training loop that cannot afford the device-wide synchronisation a
 // cudaMalloc implies, a process that has handed the whole card to another allocator (nd4j workspaces or a pool
-// sized to the GPU) so that a driver allocation may simply fail, or code running where CUDA memory management is
-// not permitted (for example a cudaLaunchHostFunc callback). For them the same three kernels run with their scratch
-// in the fixed array below instead.
+// sized to the GPU) so that a driver allocation may simply fail, or a host layer whose rules forbid cudaMalloc /
+// cudaFree outside start-up. For them the same three kernels run with their scratch in the fixed array below instead.
 //
 // DL4JB200_BN_NOALLOC_FLOATS floats (4 MiB) are reserved on every GPU that loads this library, until the process
-// exits. That bounds the channel count (see DL4JB200_BN_NOALLOC_MAX_CHANNELS); B, H and W are unlimited because the
-// number of partial blocks is reduced to fit. All calls share the one array: two calls that overlap on the GPU
+// exits. That bounds the channel count (see DL4JB200_BN_NOALLOC_MAX_CHANNELS); B, H and W are bounded only by
+// B*H*W < 2^31 (the same limit as dl4jb200_bn_fwd), because the number of partial blocks is reduced to fit. All calls share the one array: two calls that overlap on the GPU
 // (different streams, different contexts on the same device) race on it -- keep such calls on one stream or
 // serialise them. Nothing in the array has to start at zero: every slot a call reads is written earlier in that
 // same call, so leftovers from the previous call are harmless.
@@ -548,7 +549,9 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
 static __device__ __align__(256) float g_bn_noalloc_scratch[DL4JB200_BN_NOALLOC_FLOATS];
 
 // In host code `g_bn_noalloc_scratch` is only a handle for the symbol, not a device address; the address a kernel can
-// use comes from cudaGetSymbolAddress, asked once per device with that device current.
+// use comes from cudaGetSymbolAddress, asked once per device with that device current. The table is filled without a
+// lock: two threads racing on a device's first call both store the same address (the lookup is idempotent), so the
+// worst case is one redundant lookup.
 static float *g_bn_noalloc_ptr[64] = {nullptr};
 
 static int bn_noalloc_scratch(dl4jb200_ctx *ctx, float **out) {
@@ -576,6 +579,7 @@ extern "C" int dl4jb200_bn_fwd_noalloc(dl4jb200_ctx *ctx, const float *x, float 
                                        int act) {
     DL4J_REQUIRE(ctx && x && y && gmean && gvar, "bn_fwd_noalloc: NULL argument");
     DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, "bn_fwd_noalloc: bad shape");
+    DL4J_REQUIRE((long long)B * H * W < (1LL << 31), "bn_fwd_noalloc: B*H*W must stay below 2^31");
     DL4J_REQUIRE(layout == DL4JB200_NCHW || layout == DL4JB200_NHWC, "bn_fwd_noalloc: unknown layout %d", layout);
     DL4J_REQUIRE(layout == DL4JB200_NCHW || (cs >= C && cs % 4 == 0 && al16(x) && al16(y)),
                  "bn_fwd_noalloc: NHWC needs cs %% 4 == 0, cs >= C and 16-byte aligned tensors");

@@ -27,6 +27,10 @@ struct dl4jb200_ctx {
     // scratch, grown on demand (never shrunk); slot 0: kernel partials / packed filters, slot 1: NHWC staging
     void *ws[4];
     size_t ws_bytes[4];
+    // A captured CUDA graph bakes scratch addresses (and tensor maps built on them) into its nodes: once frozen, a
+    // request that would have to grow a region fails instead of freeing memory the graph still references.
+    bool ws_frozen = false;
+    unsigned long long ws_generation = 0;  // bumped whenever a region is (re)allocated
     std::unordered_map<const void *, MirrorBuf> mirrors;
     struct FilterRegistry *filters = nullptr;  // pre-packed convolution filters (conv.cu); freed by conv_filters_free
 };
@@ -144,6 +148,17 @@ __device__ __forceinline__ float dl4j_act_grad(float z, int kind) {
     case DL4JB200_ACT_SIGMOID: { float s = 1.f / (1.f + expf(-z)); return s * (1.f - s); }
     case DL4JB200_ACT_TANH: { float t = tanhf(z); return 1.f - t * t; }
     case DL4JB200_ACT_LEAKYRELU: return z > 0.f ? 1.f : 0.01f;
+    default: return 1.f;
+    }
+}
+// the same derivative written in terms of the activation OUTPUT a = act(z), for callers that kept only a
+// (DL4JB200_ACT_FROM_OUTPUT): relu'(z) = [a > 0], sigmoid' = a(1-a), tanh' = 1-a^2, leakyrelu keeps the sign of z
+__device__ __forceinline__ float dl4j_act_grad_out(float a, int kind) {
+    switch (kind) {
+    case DL4JB200_ACT_RELU: return a > 0.f ? 1.f : 0.f;
+    case DL4JB200_ACT_SIGMOID: return a * (1.f - a);
+    case DL4JB200_ACT_TANH: return 1.f - a * a;
+    case DL4JB200_ACT_LEAKYRELU: return a > 0.f ? 1.f : 0.01f;
     default: return 1.f;
     }
 }

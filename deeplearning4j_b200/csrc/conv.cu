@@ -471,8 +471,9 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     int nblk = gf.M / 8;  // bias-gradient partial blocks: >= 8 pixel rows each, up to 4 per SM
     if (nblk > ctx->sm_count * 4) nblk = ctx->sm_count * 4;
     if (nblk < 1) nblk = 1;
-    size_t part_f = (size_t)splits * rows_w * gf.Kp, pack_f = (size_t)rows_b * gb.Kp, col_f = (size_t)nblk * delta_cs;
-    if (col_f < (size_t)splits * rows_w) col_f = (size_t)splits * rows_w;  // or the per-split bias-gradient column
+    // (a dx-only call needs neither the split-K partials nor the bias-gradient rows: do not inflate the scratch for them)
+    size_t part_f = dw ? (size_t)splits * rows_w * gf.Kp : 0, pack_f = (size_t)rows_b * gb.Kp, col_f = db ? (size_t)nblk * delta_cs : 0;
+    if (dw && db && col_f < (size_t)splits * rows_w) col_f = (size_t)splits * rows_w;  // or the per-split bias-gradient column
     float *ws = (float *)dl4j_workspace(ctx, 0, (part_f + pack_f + col_f) * sizeof(float));
     if (!ws) return DL4JB200_ERR_CUDA;
     float *partial = ws, *wb = ws + part_f, *colp = wb + pack_f;
@@ -505,6 +506,9 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
         DL4J_CHECK_LAUNCH();
     }
 
+    // the epsilon handed to the previous layer is an operand of that layer's GEMMs: with DL4JB200_OPT_TF32_ACTIVATIONS it is
+    // stored rounded to nearest TF32 like every other producer's output (the tensor core would otherwise truncate it)
+    const int dx_act = DL4JB200_ACT_IDENTITY | (ctx->round_act ? 0x100 : 0);
     if (dx && tcore && d->k_h == 1 && d->k_w == 1 && (d->stride_h > 1 || d->stride_w > 1) && d->pad_top == 0 && d->pad_left == 0) {
         // strided 1x1: dx is non-zero only at the sampled pixels. Run the GEMM on the compact pixel set (a plain
         // unit-stride 1x1 walk over delta, TMA-able) and scatter its rows; everything else is zero.
@@ -521,7 +525,7 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
                 DL4J_CHECK_LAUNCH();
                 wq = wb;
             }
-            if ((rc = conv_tc_gemm(ctx, gc, ds, wq, rows_b, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY))) return rc;
+            if ((rc = conv_tc_gemm(ctx, gc, ds, wq, rows_b, nullptr, dxs, d->c_in, dx_cs, dx_act))) return rc;
             if (dx_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, dxs, dx, d->batch, d->c_in, d->in_h, d->in_w, dx_cs);
             return DL4JB200_OK;
         }
@@ -534,7 +538,7 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
             DL4J_CHECK_LAUNCH();
             wq = wb;
         }
-        if (tcore) rc = conv_tc_gemm(ctx, gb, ds, wq, rows_b, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);
+        if (tcore) rc = conv_tc_gemm(ctx, gb, ds, wq, rows_b, nullptr, dxs, d->c_in, dx_cs, dx_act);
         else rc = conv_ffma_gemm(ctx, gb, ds, wq, nullptr, dxs, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY);
         if (rc) return rc;
         if (dx_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, dxs, dx, d->batch, d->c_in, d->in_h, d->in_w, dx_cs);

@@ -75,17 +75,19 @@ __global__ void __launch_bounds__(256) k_act_fwd(const float *__restrict__ z, fl
 template <bool VEC>
 __global__ void __launch_bounds__(256) k_act_bwd(const float *__restrict__ z, const float *__restrict__ e,
                                                  float *__restrict__ d, size_t n, int act, int rnd) {
+    const bool from_out = (act & DL4JB200_ACT_FROM_OUTPUT) != 0;  // z holds act(z), not z
+    act &= 0xff;
+    auto grad = [&](float v) { return from_out ? dl4j_act_grad_out(v, act) : dl4j_act_grad(v, act); };
     size_t stride = (size_t)gridDim.x * blockDim.x, i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (VEC) {
         size_t n4 = n >> 2;
         for (; i < n4; i += stride) {
             float4 v = reinterpret_cast<const float4 *>(z)[i], g = reinterpret_cast<const float4 *>(e)[i];
-            g.x *= dl4j_act_grad(v.x, act); g.y *= dl4j_act_grad(v.y, act);
-            g.z *= dl4j_act_grad(v.z, act); g.w *= dl4j_act_grad(v.w, act);
+            g.x *= grad(v.x); g.y *= grad(v.y); g.z *= grad(v.z); g.w *= grad(v.w);
             reinterpret_cast<float4 *>(d)[i] = dl4j_rnd4(g, rnd);
         }
     } else {
-        for (; i < n; i += stride) d[i] = dl4j_rnd(e[i] * dl4j_act_grad(z[i], act), rnd);
+        for (; i < n; i += stride) d[i] = dl4j_rnd(e[i] * grad(z[i]), rnd);
     }
 }
 
@@ -498,7 +500,7 @@ int dl4jb200_act_fwd(dl4jb200_ctx *ctx, const float *z, float *a, size_t n, int 
 
 int dl4jb200_act_bwd(dl4jb200_ctx *ctx, const float *z, const float *eps, float *delta, size_t n, int act) {
     DL4J_REQUIRE(ctx && z && eps && delta, "act_bwd: NULL argument");
-    if (act < 0 || act > DL4JB200_ACT_LEAKYRELU) { dl4j_set_error("act_bwd: activation %d not handled by the helper", act); return DL4JB200_NOT_SUPPORTED; }
+    if (act < 0 || (act & 0xff) > DL4JB200_ACT_LEAKYRELU || (act & ~(0xff | DL4JB200_ACT_FROM_OUTPUT))) { dl4j_set_error("act_bwd: activation %d not handled by the helper", act); return DL4JB200_NOT_SUPPORTED; }
     if (n == 0) return DL4JB200_OK;
     if ((n & 3) == 0 && aligned16(z) && aligned16(eps) && aligned16(delta))
         k_act_bwd<true><<<ew_grid(ctx, n / 4, 256), 256, 0, ctx->stream>>>(z, eps, delta, n, act, ctx->round_act);

@@ -52,6 +52,9 @@ class Network:
         self.fuse_dgrad = True  # epsilon fan-in + ReLU backprop in the backprop-data epilogue (_emit_dgrad)
         self.launches = 0
         self.prof, self.prof_fns, self._cur = None, set(), None
+        # debugging / parity aid: when set to a dict, backward() leaves in it a device copy of every vertex' final delta
+        # (the epsilon summed over its consumers, after the vertex' own activation backprop; raw epsilon for BN / pooling)
+        self.trace = None
         self.batch_div_scale = 1  # data-parallel replicas: global minibatch = scale * B (parallel.py)
         self.shapes = zoo.infer_shapes(model)
         self.P, self.layout = zoo.param_layout(model)
@@ -563,6 +566,11 @@ class Network:
         self._contrib[u] = self._contrib.get(u, 0) + 1
         self._delta_done.add(u)
 
+    def _trace(self, n, e):
+        if self.trace is not None:
+            with self.torch.cuda.stream(self.stream):
+                self.trace[n] = e.clone()
+
     def _resolve(self, n):
         lent = self._borrowed.get(n, [])
         if n in self._written:
@@ -595,8 +603,12 @@ class Network:
             else:
                 e = self._resolve(n)
             if op in ("conv", "dense", "output"):
-                if op != "output" and v["act"] == "relu":  # delta = afn.backprop(z, eps); relu'(z) == (a > 0)
-                    self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(), L.ACT_RELU)
+                if op != "output" and v["act"] != "identity":
+                    # delta = afn.backprop(z, eps) (ConvolutionLayer.java:171, BaseLayer.java:71-102); only the activated
+                    # tensor is resident, so the derivative is taken from it: relu' = [a > 0], sigmoid' = a(1-a), tanh' = 1-a^2
+                    self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(),
+                               _ACT[v["act"]] | L.ACT_FROM_OUTPUT)
+                self._trace(n, e)
                 if op == "conv":
                     src, d = self._conv_desc(v)
                 else:
@@ -619,6 +631,7 @@ class Network:
                           gw, gb, None, L.NHWC, xcs, self.algo)
                     self._emit_dgrad(src, d, pw, e, n, x, xcs)
             elif op == "bn":
+                self._trace(n, e)
                 u = v["in"][0]
                 x, xcs = self._src(u)
                 s = self.shapes[n]
@@ -628,6 +641,7 @@ class Network:
                 self._emit(u, lambda dx: self._call("dl4jb200_bn_bwd", self._ptr(x), self._ptr(e), pg, pbeta, self._ptr(sm),
                                                     self._ptr(ss), _ACT[v["act"]], dx, gg, gbeta, B, s[0], s[1], s[2], L.NHWC, xcs))
             elif op == "pool":
+                self._trace(n, e)
                 u = v["in"][0]
                 x, xcs = self._lin(n, u)
                 d = self._pool_desc(v)
@@ -636,10 +650,13 @@ class Network:
                                                     dx, L.NHWC, xcs, self.cs[n], _POOL[v["type"]], int(v.get("pnorm", 2)), 1e-8))
             elif op in ("add", "act"):
                 if v["act"] != "identity" and n not in self._delta_done:
-                    self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(), _ACT[v["act"]])
+                    self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(),
+                               _ACT[v["act"]] | L.ACT_FROM_OUTPUT)
+                self._trace(n, e)
                 for u in v["in"]:
                     self._lend(u, e)
             elif op == "flatten":
+                self._trace(n, e)
                 u = v["in"][0]
                 s = self.shapes[u]
                 chw = s[0] * s[1] * s[2]
@@ -785,7 +802,27 @@ class Network:
                 hook(self)
             self.update()
             self._graph_score = (self.loss + self.score_reg) / float(self.B)
+        # the graph's nodes hold scratch addresses of both contexts: from here on a call that would have to grow a
+        # region fails loudly instead of freeing memory the graph still references (release_graph() lifts it)
+        for ctx in (self.h, self.h2):
+            _lib.call("dl4jb200_ctx_workspace_freeze", ctx, 1)
+        self._graph_gen = self._ws_generation()
         return self._graph
+
+    def _ws_generation(self):
+        lib = _lib.cdll()
+        return (lib.dl4jb200_ctx_workspace_generation(self.h), lib.dl4jb200_ctx_workspace_generation(self.h2))
+
+    def release_graph(self):
+        """Drop the captured step and unfreeze the scratch (call before running other shapes eagerly on this network)."""
+        self.stream.synchronize()
+        self._graph = None
+        for ctx in (self.h, self.h2):
+            _lib.call("dl4jb200_ctx_workspace_freeze", ctx, 0)
+
+    def _replay(self):
+        assert self._ws_generation() == self._graph_gen, "scratch was re-allocated after capture: re-capture the step"
+        self._graph.replay()
 
     def fit_graph(self, features=None, labels=None):
         """fit() through the captured graph. New minibatches are copied into the static input buffers first."""
@@ -799,7 +836,7 @@ class Network:
             if not self._graph_has_input:
                 self._relayout_input()
         with t.cuda.stream(self.stream):
-            self._graph.replay()
+            self._replay()
         return self._graph_score
 
     # ------------------------------------------------------------------ prefetching input pipeline
@@ -846,7 +883,7 @@ class Network:
         pf["free"][slot] = ev
         if getattr(self, "_graph", None) is not None and not self._graph_has_input:
             with t.cuda.stream(self.stream):
-                self._graph.replay()
+                self._replay()
             return self._graph_score
         return self.fit(hook=hook)
 

@@ -176,14 +176,17 @@ MODELS = {"lenet": lenet, "vgg16": vgg16, "alexnet": alexnet, "simplecnn": simpl
 
 
 # ---------------------------------------------------------------------------------------------------
-def _out_hw(h, w, k, s, p, d, mode):
-    from . import _lib
+def _out_hw(h, w, k, s, p, d, mode, out_size=None):
+    if out_size is None:
+        from . import _lib
+        out_size = _lib.out_size
     m = {"Strict": 0, "Truncate": 1, "Same": 2}[mode]
-    return _lib.out_size(h, k[0], s[0], p[0], d[0], m)[0], _lib.out_size(w, k[1], s[1], p[1], d[1], m)[0]
+    return out_size(h, k[0], s[0], p[0], d[0], m)[0], out_size(w, k[1], s[1], p[1], d[1], m)[0]
 
 
-def infer_shapes(model):
-    """-> {vertex name: (C,H,W) or (n,)}; ConvolutionUtils.getOutputSize rules via the C ABI's out_size."""
+def infer_shapes(model, out_size=None):
+    """-> {vertex name: (C,H,W) or (n,)}; ConvolutionUtils.getOutputSize rules via the C ABI's out_size (callers that
+    must not load the CUDA library -- the CPU reference arm of bench.py -- pass their own `out_size(in,k,s,p,d,mode)`)."""
     shapes = {}
     for v in model["vertices"]:
         op = v["op"]
@@ -192,10 +195,10 @@ def infer_shapes(model):
             continue
         s = shapes[v["in"][0]]
         if op == "conv":
-            h, w = _out_hw(s[1], s[2], v["kernel"], v["stride"], v["pad"], v["dilation"], v["mode"])
+            h, w = _out_hw(s[1], s[2], v["kernel"], v["stride"], v["pad"], v["dilation"], v["mode"], out_size)
             shapes[v["name"]] = (v["nOut"], h, w)
         elif op == "pool":
-            h, w = _out_hw(s[1], s[2], v["kernel"], v["stride"], v["pad"], (1, 1), v["mode"])
+            h, w = _out_hw(s[1], s[2], v["kernel"], v["stride"], v["pad"], (1, 1), v["mode"], out_size)
             shapes[v["name"]] = (s[0], h, w)
         elif op == "zeropad":
             t, b, l, r = v["pad"]
@@ -209,10 +212,10 @@ def infer_shapes(model):
     return shapes
 
 
-def param_layout(model):
+def param_layout(model, out_size=None):
     """-> (total P, [(vertex name, key, offset, shape, kind)]) in flat-vector order (MultiLayerNetwork.java:561-676).
     kind: 'w' (regularised weight), 'b' (bias), 'bn_gb' (gamma/beta), 'bn_stat' (running mean/var, NoOp updater)."""
-    shapes = infer_shapes(model)
+    shapes = infer_shapes(model, out_size)
     out, off = [], 0
     for v in model["vertices"]:
         op = v["op"]
@@ -233,12 +236,12 @@ def param_layout(model):
     return off, out
 
 
-def init_params(model, seed=None):
+def init_params(model, seed=None, out_size=None):
     """Host-generated initial flat parameter vector (WeightInitUtil.java:80-150 formulas with our own seeded
     generator -- nd4j's RNG stream is unavailable). conv fanIn = Cin*kH*kW,
     fanOut = Cout*kH*kW/(sH*sW) (ConvolutionParamInitializer.java:188-189)."""
     rng = np.random.default_rng(model.get("seed", 123) if seed is None else seed)
-    P, layout = param_layout(model)
+    P, layout = param_layout(model, out_size)
     flat = np.zeros(P, np.float32)
     vmap = {v["name"]: v for v in model["vertices"]}
     wi = model["weight_init"]

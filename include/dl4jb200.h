@@ -61,6 +61,9 @@ extern "C" {
 #define DL4JB200_ACT_SIGMOID 2
 #define DL4JB200_ACT_TANH 3
 #define DL4JB200_ACT_LEAKYRELU 4
+/* OR-ed into `act` of dl4jb200_act_bwd: the `z` argument holds the activation OUTPUT a = act(z) (what a caller that
+ * activated in place still has); the derivative is then taken as relu: [a > 0], sigmoid: a(1-a), tanh: 1-a^2. */
+#define DL4JB200_ACT_FROM_OUTPUT 0x200
 
 /* convolution arithmetic: TF32 tensor cores with FP32 accumulate (throughput), or FP32 CUDA cores
  * (parity mode, plays the role AlgoMode.NO_WORKSPACE plays in the reference's tests). */
@@ -113,6 +116,13 @@ int dl4jb200_ctx_sync(dl4jb200_ctx *ctx);
 /* bytes of internal scratch (split-K partials, BN partial sums, packed filters) currently held */
 size_t dl4jb200_ctx_workspace_bytes(dl4jb200_ctx *ctx);
 int dl4jb200_ctx_sm_count(dl4jb200_ctx *ctx);
+/* The scratch regions grow on demand (cudaFree + cudaMalloc after draining the stream). A CUDA graph captured from calls
+ * on this context has their addresses baked in, so a caller that captures freezes the scratch afterwards: while frozen, a
+ * call that would need a larger region fails with ERR_CUDA and a clear message instead of freeing memory the graph still
+ * uses. workspace_generation counts (re)allocations; equal values before and after mean every baked address is still live.
+ * (Plays the role of nd4j's workspace scope checks, deeplearning4j-core/src/test/.../BaseDL4JTest.java:8-25.) */
+int dl4jb200_ctx_workspace_freeze(dl4jb200_ctx *ctx, int frozen);
+unsigned long long dl4jb200_ctx_workspace_generation(dl4jb200_ctx *ctx);
 
 int dl4jb200_malloc(dl4jb200_ctx *ctx, size_t bytes, void **out);
 int dl4jb200_free(dl4jb200_ctx *ctx, void *ptr);
@@ -188,7 +198,8 @@ int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, 
                                 const float *delta, int delta_cs, float *dw, float *db);
 
 /* ConvolutionHelper.activate (ConvolutionHelper.java:45) and IActivation.backprop
- * (ConvolutionLayer.java:171): elementwise over n floats; in place allowed (a == z, delta == eps). */
+ * (ConvolutionLayer.java:171): elementwise over n floats; in place allowed (a == z, delta == eps).
+ * act_bwd: act may carry DL4JB200_ACT_FROM_OUTPUT when only the activated tensor was kept. */
 int dl4jb200_act_fwd(dl4jb200_ctx *ctx, const float *z, float *a, size_t n, int act);
 int dl4jb200_act_bwd(dl4jb200_ctx *ctx, const float *z, const float *eps, float *delta, size_t n, int act);
 
@@ -234,7 +245,7 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
  * running where CUDA memory management is off limits. Same arguments, results and status codes as dl4jb200_bn_fwd,
  * but the per-block partial sums and per-channel coefficients live in a fixed 4 MiB array inside the library (held on
  * every GPU that loads it, until exit) instead of the context's on-demand scratch; it calls no cudaMalloc / cudaFree.
- * Limit: at most 4096 channels (cs for NHWC), otherwise DL4JB200_ERR_INVALID_ARG; B, H, W are unlimited.
+ * Limit: at most 4096 channels (cs for NHWC), otherwise DL4JB200_ERR_INVALID_ARG; B*H*W < 2^31 as for dl4jb200_bn_fwd.
  * The first call on each device looks up the array's device address (cudaGetSymbolAddress): make that first call
  * before starting any stream capture. All calls share the array, so calls that overlap on the GPU race: keep them on
  * one stream or serialise them. Nothing needs clearing between calls. */

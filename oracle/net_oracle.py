@@ -69,6 +69,7 @@ class OracleNet:
         act = {}
         self.bn_saved = {}
         self.lin = {}
+        self.z = {}  # pre-activation of every vertex with a non-identity activation: IActivation.backprop(z, eps) needs it
         for v in m["vertices"]:
             n, op = v["name"], v["op"]
             if op == "input":
@@ -83,6 +84,7 @@ class OracleNet:
                 f = o.conv_fwd_im2col if self.fast else o.conv_fwd
                 z = f(self._t(a), self._q(self._p(n, "W")), self._p(n, "b"), stride=v["stride"], pad=v["pad"],
                       dilation=v["dilation"], mode=_MODE[v["mode"]])
+                self.z[n] = z
                 act[n] = self._q(o.act_fwd(z, _ACT[v["act"]])) if v["act"] != "identity" else z
             elif op == "bn":
                 y, mean, std = o.bn_fwd(a, self._p(n, "gamma"), self._p(n, "beta"), self._p(n, "mean"), self._p(n, "var"),
@@ -95,8 +97,10 @@ class OracleNet:
                 act[n] = self._q(o.pool_fwd(a, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]]))
             elif op == "add":
                 s = a + act[v["in"][1]]
+                self.z[n] = s
                 act[n] = self._q(o.act_fwd(s, _ACT[v["act"]]) if v["act"] != "identity" else s)
             elif op == "act":
+                self.z[n] = a
                 act[n] = self._q(o.act_fwd(a, _ACT[v["act"]]))
             elif op == "flatten":
                 act[n] = a.reshape(a.shape[0], -1)
@@ -107,6 +111,7 @@ class OracleNet:
                 else:
                     z = o.dense_fwd(self._t(a), self._q(self._p(n, "W")), self._p(n, "b"))
                 if op == "dense":
+                    self.z[n] = z
                     act[n] = self._q(o.act_fwd(z, _ACT[v["act"]])) if v["act"] != "identity" else z
                 else:
                     act[n] = z
@@ -121,6 +126,7 @@ class OracleNet:
     def backward(self):
         m, act = self.model, self.act
         eps = {}
+        self.deltas = {}  # per vertex: the summed epsilon after the vertex' own activation backprop (raw for BN / pooling)
 
         def give(u, e):
             if self.vmap[u]["op"] in ("input",):
@@ -135,11 +141,13 @@ class OracleNet:
             e = self.delta if op == "output" else eps.get(n)
             if e is None:
                 continue
+            self.deltas[n] = e
             if op == "zeropad":
                 t, b, l, r = v["pad"]
                 give(u, np.ascontiguousarray(e[:, :, t:e.shape[2] - b, l:e.shape[3] - r]))
             elif op == "conv":
-                d = self._q(o.act_bwd(act[n], e, _ACT[v["act"]])) if v["act"] == "relu" else e
+                d = self._q(o.act_bwd(self.z[n], e, _ACT[v["act"]])) if v["act"] != "identity" else e
+                self.deltas[n] = d
                 f = o.conv_bwd_im2col if self.fast else o.conv_bwd
                 dw, db, dx = f(self._t(self.lin[n]), self._q(self._p(n, "W")), self._t(d), stride=v["stride"], pad=v["pad"],
                                dilation=v["dilation"], mode=_MODE[v["mode"]])
@@ -147,9 +155,10 @@ class OracleNet:
                     db = d.sum(axis=(0, 2, 3), dtype=np.float64).astype(np.float32)
                 self._p(n, "W", self.grads)[...] = dw
                 self._p(n, "b", self.grads)[...] = db
-                give(u, dx)
+                give(u, self._q(dx))  # backprop-data stores its epsilon rounded like every other producer
             elif op in ("dense", "output"):
-                d = self._q(o.act_bwd(act[n], e, _ACT[v["act"]])) if (op == "dense" and v["act"] == "relu") else e
+                d = self._q(o.act_bwd(self.z[n], e, _ACT[v["act"]])) if (op == "dense" and v["act"] != "identity") else e
+                self.deltas[n] = d
                 if self.fast:
                     dwf, db, dx = self._t(d).T @ self._t(self.lin[n]), d.sum(0), self._t(d) @ self._q(self._p(n, "W"))
                 else:
@@ -158,7 +167,7 @@ class OracleNet:
                         db = d.sum(axis=0, dtype=np.float64).astype(np.float32)
                 self._p(n, "W", self.grads)[...] = dwf
                 self._p(n, "b", self.grads)[...] = db
-                give(u, dx)
+                give(u, self._q(dx))
             elif op == "bn":
                 mean, std, y = self.bn_saved[n]
                 d = o.act_bwd(y, e, _ACT[v["act"]]) if v["act"] == "relu" else e
@@ -171,7 +180,8 @@ class OracleNet:
             elif op == "pool":
                 give(u, self._q(o.pool_bwd(self.lin[n], e, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]])))
             elif op in ("add", "act"):
-                d = self._q(o.act_bwd(act[n], e, _ACT[v["act"]])) if v["act"] == "relu" else e
+                d = self._q(o.act_bwd(self.z[n], e, _ACT[v["act"]])) if v["act"] != "identity" else e
+                self.deltas[n] = d
                 for uu in v["in"]:
                     give(uu, d)
             elif op == "flatten":

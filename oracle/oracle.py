@@ -134,8 +134,9 @@ def conv_bwd(x, w, delta, stride=(1, 1), pad=(0, 0), dilation=(1, 1), mode=TRUNC
     return dw, db, dx
 
 
-def conv_bwd_im2col(x, w, delta, stride=(1, 1), pad=(0, 0), dilation=(1, 1), mode=TRUNCATE):
-    """Literal reference pipeline (ConvolutionLayer.java:202-257): im2col, two sgemms, col2im."""
+def conv_bwd_im2col(x, w, delta, stride=(1, 1), pad=(0, 0), dilation=(1, 1), mode=TRUNCATE, acc64=False):
+    """Literal reference pipeline (ConvolutionLayer.java:202-257): im2col, two sgemms, col2im. acc64: run the
+    filter-gradient GEMM (reduction over B*Ho*Wo, up to millions of terms) in double, for use as a parity oracle."""
     x, w, delta = _f(x), _f(w), _f(delta)
     B, Cin, H, W = x.shape
     Cout, _, kH, kW = w.shape
@@ -145,7 +146,14 @@ def conv_bwd_im2col(x, w, delta, stride=(1, 1), pad=(0, 0), dilation=(1, 1), mod
     d2 = np.empty((B * Ho * Wo, Cout), np.float32)
     lib().o_nchw_to_rows(_p(delta), _p(d2), B, Cout, Ho, Wo)
     col2d = col.reshape(B * Ho * Wo, Cin * kH * kW)
-    dw = (d2.T @ col2d).reshape(w.shape)
+    if acc64:
+        dw = np.zeros((Cout, col2d.shape[1]), np.float64)
+        step = max(1, (1 << 26) // max(col2d.shape[1], Cout))  # bounded double-precision temporaries
+        for r0 in range(0, col2d.shape[0], step):
+            dw += d2[r0:r0 + step].T.astype(np.float64) @ col2d[r0:r0 + step].astype(np.float64)
+        dw = dw.astype(np.float32).reshape(w.shape)
+    else:
+        dw = (d2.T @ col2d).reshape(w.shape)
     db = d2.sum(0, dtype=np.float64).astype(np.float32)
     eps2d = d2 @ w.reshape(Cout, -1)
     dx = col2im(eps2d.reshape(B, Ho, Wo, Cin, kH, kW), H, W, stride, (pT, pL), dilation)

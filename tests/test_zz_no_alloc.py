@@ -12,7 +12,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from gpu_util import Dev, to_nhwc
+from gpu_util import Dev, from_nhwc, to_nhwc
 
 pytestmark = pytest.mark.gpu
 
@@ -31,7 +31,7 @@ def _run(lib, ctx, dev, fn, x_dev, shape, layout, cs, gamma, beta):
     return [dev.get(p, (k,)) for p, k in ((py, n), (pm, Cc), (pv, Cc), (psm, Cc), (pss, Cc))]
 
 
-def test_bn_fwd_noalloc_matches_bn_fwd_two_calls_in_a_row():
+def test_bn_fwd_noalloc_matches_bn_fwd_two_calls_in_a_row(oracle):
     from deeplearning4j_b200 import build
     build.build()
     from deeplearning4j_b200 import _lib as lib, helpers
@@ -52,6 +52,14 @@ def test_bn_fwd_noalloc_matches_bn_fwd_two_calls_in_a_row():
             for g, r in zip(got, ref):
                 assert np.isfinite(g).all()
                 assert np.abs(g.astype(np.float64) - r).max() <= TOL * max(np.abs(r).max(), 1e-30)
+            # and directly against the CPU restatement of BatchNormalization.preOutput (+ the fused ReLU)
+            gm, gv = np.zeros(Cc, np.float32), np.ones(Cc, np.float32)
+            yr, _, _ = oracle.bn_fwd(x, gamma, beta, gm, gv, 0.9, 1e-5, True, True)
+            yr = np.maximum(yr, 0.0)
+            y = got[0].reshape(B, H, W, cs) if layout == lib.NHWC else got[0].reshape(shape)
+            y = from_nhwc(y, Cc) if layout == lib.NHWC else y
+            assert np.abs(y.astype(np.float64) - yr).max() <= TOL * np.abs(yr).max()
+            assert np.abs(got[1] - gm).max() <= TOL * max(np.abs(gm).max(), 1e-30) and np.abs(got[2] - gv).max() <= TOL * np.abs(gv).max()
         # sizes beyond the fixed scratch are refused with a clear message, not silently mishandled
         big = dev.empty(16)
         with pytest.raises(lib.DL4JB200Error, match="exceed the fixed scratch"):
