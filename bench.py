@@ -312,11 +312,14 @@ def main():
     ms = e0.elapsed_time(e1)
 
     # ---- timed region 2: end to end through the public API with host buffers
+    hook = pw._hook if pw else None
+    for _ in range(2):  # untimed: the double buffers of the input pipeline are allocated on first use
+        net.prefetch(xh, labh)
+        net.fit_prefetched(hook=hook)
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     f0.record(net.stream)
     last = None
-    hook = pw._hook if pw else None
     net.prefetch(xh, labh)  # every step's pinned host->device copy happens inside the timed region ...
     for k in range(args.steps):
         if k + 1 < args.steps:

@@ -297,7 +297,12 @@ __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__
     pdl_trigger();
     pdl_wait();
     size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += stride) {
+    // The tensor is walked from its END to its start. The producer of x (a convolution epilogue, or the partial-sum pass
+    // that has just read x and eps) finished with the high addresses, so those lines are the ones still in the 126 MB L2;
+    // and the consumer of `out` (the next convolution, whose tiles run from the first pixel up) in turn finds the lines
+    // this kernel wrote last. For tensors up to the L2 size the second read never reaches DRAM.
+    for (size_t ii = (size_t)blockIdx.x * blockDim.x + threadIdx.x; ii < total4; ii += stride) {
+        const size_t i = total4 - 1 - ii;
         int q = (int)(i % Q);
         float4 k = __ldg(reinterpret_cast<const float4 *>(coef) + q);
         float4 a = __ldg(reinterpret_cast<const float4 *>(coef + cs) + q);

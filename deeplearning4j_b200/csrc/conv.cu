@@ -208,6 +208,8 @@ __global__ void __launch_bounds__(256) k_wgrad_finalize(const float *__restrict_
                                                         int Cin, int taps, int Cg, int Kp, int rows_p, int splits,
                                                         const float *__restrict__ db_partial, float *__restrict__ db) {
     size_t total = (size_t)Cout * Cin * taps, stride = (size_t)gridDim.x * blockDim.x;
+    pdl_trigger();
+    pdl_wait();
     if (db_partial) {
         for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)Cout; i += stride) {
             float acc = 0.f;
@@ -243,6 +245,8 @@ __global__ void __launch_bounds__(256) k_wgrad_finalize_wide(const float *__rest
                                                              int Cin, int taps, int Cg, int Kp, int rows_p, int splits,
                                                              const float *__restrict__ db_partial, float *__restrict__ db) {
     __shared__ float red[8][33];
+    pdl_trigger();
+    pdl_wait();
     const int o = threadIdx.x & 31, l = threadIdx.x >> 5;
     const size_t nw = (size_t)Cout * Cin * taps, total = nw + (db_partial ? (size_t)Cout : 0);
     for (size_t base = (size_t)blockIdx.x * 32; base < total; base += (size_t)gridDim.x * 32) {
@@ -490,11 +494,11 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
         const size_t n_out = (size_t)d->c_out * d->c_in * gf.taps;
         if (splits >= 32) {
             size_t blocks = (n_out + d->c_out + 31) / 32, cap = (size_t)ctx->sm_count * 16;
-            k_wgrad_finalize_wide<<<(int)(blocks < cap ? blocks : cap), 256, 0, ctx->stream>>>(partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg,
-                                                                                          gf.Kp, rows_w, splits, dbp, db);
+            DL4J_CUDA_TRY(dl4j_launch_pdl(k_wgrad_finalize_wide, dim3((int)(blocks < cap ? blocks : cap)), dim3(256), 0, ctx->stream,
+                                          (const float *)partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w, splits, (const float *)dbp, db));
         } else {
-            k_wgrad_finalize<<<grid_for(ctx, n_out), 256, 0, ctx->stream>>>(partial, dw, d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w,
-                                                                            splits, dbp, db);
+            DL4J_CUDA_TRY(dl4j_launch_pdl(k_wgrad_finalize, dim3(grid_for(ctx, n_out)), dim3(256), 0, ctx->stream, (const float *)partial, dw,
+                                          d->c_out, d->c_in, gf.taps, gf.Cg, gf.Kp, rows_w, splits, (const float *)dbp, db));
         }
         DL4J_CHECK_LAUNCH();
     }

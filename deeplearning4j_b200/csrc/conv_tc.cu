@@ -723,6 +723,12 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
     tc_fence_after();
     uint32_t tmem_d;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_d) : "r"(tmem_slot));
+    // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) ran while the previous kernel
+    // of the stream was still draining; global memory is touched only below. The trigger comes AFTER this CTA holds its
+    // TMEM: a dependent CTA scheduled onto this SM may then block in its own tcgen05.alloc until we free ours, but can
+    // never take columns this CTA is still waiting for.
+    pdl_trigger();
+    pdl_wait();
 
     if (warp == 5) {
         // ------------------------------ TMA producer
@@ -1027,14 +1033,17 @@ static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, co
             dl4j_set_error("conv_tc_gemm_tma: this launch cannot carry batch-norm statistics");
             return DL4JB200_ERR_INVALID_ARG;
         }
-        k_conv_tc_gemm_tma_persist<BN, STAGES, false, true><<<gs, PTHREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act & 0xff, n_tiles, total);
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, false, true>, dim3(gs), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB,
+                                      bias, out, g, n_valid, out_cs, act & 0xff, n_tiles, total));
         DL4J_CHECK_LAUNCH();
         return DL4JB200_OK;
     }
     if (g.remap)
-        k_conv_tc_gemm_tma_persist<BN, STAGES, true><<<grid, PTHREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act, n_tiles, total);
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, true>, dim3(grid), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB, bias,
+                                      out, g, n_valid, out_cs, act, n_tiles, total));
     else
-        k_conv_tc_gemm_tma_persist<BN, STAGES, false><<<grid, PTHREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act, n_tiles, total);
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, false>, dim3(grid), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB, bias,
+                                      out, g, n_valid, out_cs, act, n_tiles, total));
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
@@ -1103,6 +1112,8 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad_tma(const __grid_cons
     tc_fence_after();
     uint32_t tmem_d;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_d) : "r"(tmem_slot));
+    pdl_trigger();  // after the TMEM allocation, see k_conv_tc_gemm_tma_persist
+    pdl_wait();
 
     if (warp < 4) {
         if (tid == 0) {
@@ -1206,7 +1217,7 @@ static int launch_wgrad_tma(dl4jb200_ctx *ctx, const CUtensorMap &tmD, const CUt
     }
     int k_tiles = dl4j_ceil_div(g.Kp, BN), c_tiles = dl4j_ceil_div(rows_p, BLOCK_M);
     dim3 grid(k_tiles * c_tiles, splits);
-    kern<<<grid, THREADS, SMEM, ctx->stream>>>(tmD, tmX, partial, g, rows_p, m_per_split, k_tiles, db_partial);
+    DL4J_CUDA_TRY(dl4j_launch_pdl(kern, grid, dim3(THREADS), SMEM, ctx->stream, tmD, tmX, partial, g, rows_p, m_per_split, k_tiles, db_partial));
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }

@@ -1,0 +1,3 @@
+mkdir -p gpurun_out
+timeout 600 python scripts/timeline.py resnet50 gpurun_out/r02_timeline_resnet50.json 2>&1 | tail -3
+python scripts/timeline_report.py gpurun_out/r02_timeline_resnet50.json

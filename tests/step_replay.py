@@ -38,13 +38,21 @@ class Report:
     def __init__(self):
         self.rows, self.flips, self.flip_candidates = [], 0, 0
 
-    def check(self, what, name, got, ref, stages, fp_tol, mag=None, skip=None):
-        """|got - ref| <= stages*2^-11*mag + fp_tol*max|ref| elementwise; records the worst |got-ref| / max|ref|."""
+    def check(self, what, name, got, ref, stages, fp_tol, mag=None, skip=None, floor=None):
+        """|got - ref| <= stages*2^-11*mag + fp_tol*max|ref| (+ floor) elementwise; records the worst |got-ref| / max|ref|.
+        floor: absolute fp32 round-off allowance for sums that cancel to ~0 (e.g. the bias gradient of a convolution that
+        feeds a batch norm is analytically zero): 2e-6 * sum|terms| -- the bias gradient rides in the filter-gradient GEMM
+        (delta^T x ones), whose fp32 accumulator truncates; measured up to 1.2e-6 * sum|terms| over 4e5 pixels."""
         got, ref = np.asarray(got, np.float64), np.asarray(ref, np.float64)
         assert got.shape == ref.shape, (what, name, got.shape, ref.shape)
         scale = max(float(np.abs(ref).max()), 1e-30)
+        if floor is not None and float(np.max(floor)) * 100 > scale:
+            what += ".cancelling"  # the true value is round-off of a cancelling sum: judged on sum|terms|, listed apart
+            scale = max(scale, float(np.max(floor)) * 100)
         err = np.abs(got - ref)
         bound = stages * HALF_ULP * 1.002 * (np.abs(ref) if mag is None else np.asarray(mag, np.float64)) + fp_tol * scale
+        if floor is not None:
+            bound = bound + np.asarray(floor, np.float64)
         bad = err > bound
         if skip is not None:
             bad &= ~skip
@@ -69,10 +77,12 @@ def _nchw(net, t, name):
     a = t.cpu().numpy()
     if len(s) == 3:
         return np.ascontiguousarray(a[..., :s[0]].transpose(0, 3, 1, 2))
+    if a.ndim == 4:  # an aliased flatten of a 1x1 map: the buffer is the [B,1,1,cs] NHWC tensor itself
+        a = a.reshape(a.shape[0], -1)
     return a[:, :s[0]].copy()
 
 
-def replay_step(net, model, x, lab, masks=None, fp_tol=5e-5, grad_tol=1e-4, param_tol=1e-5, max_flip_frac=2e-4,
+def replay_step(net, model, x, lab, masks=None, fp_tol=1e-4, grad_tol=1e-4, param_tol=1e-5, max_flip_frac=2e-4,
                 forward_only=False):
     """Runs ONE net.fit(x, lab) and checks it vertex by vertex (see module docstring). Returns a Report.
     forward_only: a training-mode forward pass only (SimpleCNN has no loss layer and cannot be fitted)."""
@@ -185,7 +195,7 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=5e-5, grad_tol=1e-4, para
             rep.check("fwd.flatten", n, act_of(n), a.reshape(a.shape[0], -1), 0, 0.0)
         elif op in ("dense", "output"):
             a = lin_of(v)
-            z = t_(a) @ q(P(n, "W")).T + P(n, "b")[None, :]
+            z = (t_(a).astype(np.float64) @ q(P(n, "W")).T.astype(np.float64) + P(n, "b")[None, :]).astype(np.float32)
             zref[n] = z
             if op == "dense":
                 ref = o.act_fwd(z, _ACT[v["act"]]) if v["act"] != "identity" else z
@@ -221,6 +231,17 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=5e-5, grad_tol=1e-4, para
         else:
             exp[u], mag[u] = e, m
 
+    gref = np.zeros(net.P, np.float64)   # the oracle's gradient blocks (each from the GPU's inputs of that vertex)
+    gfloor = np.zeros(net.P, np.float64)  # round-off allowance for blocks that are cancelling sums
+    gtol = np.full(net.P, grad_tol)
+
+    def put(n, key, val, tol=grad_tol, floor=None):
+        off, cnt, shp, _ = net.pidx[(n, key)]
+        gref[off:off + cnt] = np.asarray(val, np.float64).reshape(-1)
+        gtol[off:off + cnt] = tol
+        if floor is not None:
+            gfloor[off:off + cnt] = np.asarray(floor, np.float64).reshape(-1)
+
     amb = {}  # vertex -> elements whose incoming epsilon passed a ReLU gate that is within round-off of zero
     for v in reversed(model["vertices"]):
         n, op = v["name"], v["op"]
@@ -237,8 +258,11 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=5e-5, grad_tol=1e-4, para
                     gate = act_of(n) > 0
                     e, m = e * gate, mag[n] * gate
                 else:
+                    # reference semantics: afn.backprop(z, eps). The CUDA path takes the derivative from the STORED output
+                    # a (sigmoid' = a(1-a), tanh' = 1-a^2); in TF32 mode a carries one rounding, which moves the derivative
+                    # by at most 2 * 2^-11 in absolute terms -- allowed for on top of the magnitudes already collected
                     g = o.act_bwd(zref[n], np.ones_like(zref[n]), _ACT[v["act"]]).astype(np.float64)
-                    e, m = e * g, mag[n] * np.abs(g)
+                    e, m = e * g, mag[n] * np.abs(g) + 2.0 * np.abs(e)
             else:
                 m = mag[n]
             # every contribution and every partial sum was stored once, rounded: `m` adds up exactly those magnitudes
@@ -250,8 +274,10 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=5e-5, grad_tol=1e-4, para
             dw, db, dx = o.conv_bwd_im2col(t_(lin_of(v)), q(P(n, "W")), t_(d), stride=v["stride"], pad=v["pad"],
                                            dilation=v["dilation"], mode=_MODE[v["mode"]], acc64=True)
             db = d.sum(axis=(0, 2, 3), dtype=np.float64)
-            rep.check("grad.conv_W", n, P(n, "W", grads), dw, 0, grad_tol)
-            rep.check("grad.conv_b", n, P(n, "b", grads), db, 0, grad_tol, mag=None)
+            # the tensor core's fp32 accumulator truncates: over reductions of > 2.6e5 pixels (the stem) the filter gradient
+            # reaches 1.2e-4 of the block max, so those get 3e-4; everything shorter is held to grad_tol
+            put(n, "W", dw, grad_tol if d.shape[0] * d.shape[2] * d.shape[3] < (1 << 18) else 3 * grad_tol)
+            put(n, "b", db, floor=2e-6 * np.abs(d).sum(axis=(0, 2, 3), dtype=np.float64))
             src = v["in"][0]
             if vmap[src]["op"] == "zeropad":
                 t, b, l, r = vmap[src]["pad"]
@@ -261,8 +287,8 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=5e-5, grad_tol=1e-4, para
         elif op in ("dense", "output"):
             a = lin_of(v)
             dwf, db, dx = t_(d).T.astype(np.float64) @ t_(a).astype(np.float64), d.sum(0, dtype=np.float64), t_(d) @ q(P(n, "W"))
-            rep.check("grad.dense_W", n, P(n, "W", grads), dwf, 0, grad_tol)
-            rep.check("grad.dense_b", n, P(n, "b", grads), db, 0, grad_tol)
+            put(n, "W", dwf)
+            put(n, "b", db, floor=2e-6 * np.abs(d).sum(0, dtype=np.float64))
             give(v["in"][0], dx)
         elif op == "bn":
             u = v["in"][0]
@@ -279,8 +305,8 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=5e-5, grad_tol=1e-4, para
                 rep.flip_candidates += int(ambiguous.sum())
                 dd = np.where(y64 > 0, d, 0).astype(np.float32)
             dx, dg, dbt = o.bn_bwd(xin, dd, gam, sm, ss)
-            rep.check("grad.bn_gamma", n, P(n, "gamma", grads), dg, 0, grad_tol * 2)
-            rep.check("grad.bn_beta", n, P(n, "beta", grads), dbt, 0, grad_tol * 2)
+            put(n, "gamma", dg, grad_tol * 2)
+            put(n, "beta", dbt, grad_tol * 2)
             assert not P(n, "mean", grads).any() and not P(n, "var", grads).any()  # BatchNormalization.java:205-208
             give(u, dx)
             if ambiguous is not None and ambiguous.any():
@@ -298,8 +324,31 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=5e-5, grad_tol=1e-4, para
         else:
             raise NotImplementedError(op)
 
+    # ---------------------------------------------------------------- gradient blocks (after the layer-wise
+    # GradientNormalization, which the step applies in place before the updater: BaseMultiLayerUpdater.java:322-380)
+    gn = OracleNet(model, net.layout, net.P, params_pre)
+    gn.grads = gref.astype(np.float32)
+    if model.get("grad_norm"):
+        spans = {}
+        for name, key, off, shp, pk in net.layout:
+            lo, hi = spans.get(name, (off, off))
+            spans[name] = (min(lo, off), max(hi, off + int(np.prod(shp))))
+        for name, (lo, hi) in spans.items():  # the allowances scale with the block
+            if model["grad_norm"] == "RenormalizeL2PerLayer":
+                gfloor[lo:hi] /= max(float(np.sqrt((gref[lo:hi] ** 2).sum())), 1e-30)
+        gn.grad_normalize()
+    kind = {"W": "W", "b": "b", "gamma": "bn_gamma", "beta": "bn_beta"}
+    for name, key, off, shp, pk in net.layout:
+        if pk == "bn_stat":
+            continue
+        cnt = int(np.prod(shp))
+        op = vmap[name]["op"]
+        what = "grad." + ("conv_" if op == "conv" else "dense_" if op in ("dense", "output") else "") + kind[key]
+        fl = gfloor[off:off + cnt]
+        rep.check(what, name, grads[off:off + cnt], gn.grads[off:off + cnt], 0, float(gtol[off]), floor=fl if fl.any() else None)
+
     # ---------------------------------------------------------------- updater and score, block by block
-    ref = OracleNet(model, net.layout, net.P, params_pre)
+    ref = OracleNet(dict(model, grad_norm=None), net.layout, net.P, params_pre)
     ref.grads[:] = grads
     ref.state[:] = state_pre
     ref.loss = loss_gpu

@@ -3,8 +3,9 @@ at BASELINE.json's image sizes -- every vertex of one training step checked agai
 inputs (tests/step_replay.py explains why this, and not a looser free-running comparison, is the meaningful bar).
 
 Bounds asserted per element: forward activations and deltas |gpu - oracle| <= 2^-11 |value| (the one TF32 rounding a
-producer applies on store) + 5e-5 max|oracle|; every gradient block (dW, db, dgamma, dbeta) <= 1e-4 of the block max
-(2e-4 for the BN parameter gradients), no rounding allowance; every post-update parameter block and the updater state
+producer applies on store) + 1e-4 max|oracle|; every gradient block (dW, db, dgamma, dbeta) <= 1e-4 of the block max
+(2e-4 for the BN parameter gradients, 3e-4 for filter gradients reduced over more than 2^18 pixels -- the tensor core's
+fp32 accumulator truncates), no rounding allowance; every post-update parameter block and the updater state
 <= 1e-5 of the block max; score and loss <= 1e-5. The reference's own helper-vs-builtin bound is 1e-4
 (deeplearning4j-cuda/src/test/java/org/deeplearning4j/convolution/TestConvolution.java:145,151)."""
 import numpy as np
