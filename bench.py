@@ -280,7 +280,7 @@ def main():
     use_graph = not args.no_graph
     if use_graph:
         try:
-            net.capture(hook=pw._hook if pw else None, include_input=False)
+            net.capture(hook=pw.hook if pw else None, include_input=False)
             for _ in range(2):
                 net._relayout_input()
                 net.fit_graph()
@@ -312,7 +312,7 @@ def main():
     ms = e0.elapsed_time(e1)
 
     # ---- timed region 2: end to end through the public API with host buffers
-    hook = pw._hook if pw else None
+    hook = pw.hook if pw else None
     for _ in range(2):  # untimed: the double buffers of the input pipeline are allocated on first use
         net.prefetch(xh, labh)
         net.fit_prefetched(hook=hook)

@@ -102,6 +102,14 @@ PROTOTYPES = {
     "dl4jb200_copy2d": [_vp, _vp, _i, _vp, _i, _i, _i],
     "dl4jb200_grad_normalize": [_vp, _vp, _sz, _i, _d],
     "dl4jb200_updater_apply_segments": [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _vp, _i, _d, _vp],
+    "dl4jb200_comm_unique_id": [_vp, _sz],
+    "dl4jb200_comm_init": [_vp, _i, _i, _vp, C.POINTER(_vp)],
+    "dl4jb200_comm_destroy": [_vp],
+    "dl4jb200_comm_allreduce_sum_f32": [_vp, _vp, _sz, _vp],
+    "dl4jb200_comm_allreduce_avg_f32": [_vp, _vp, _sz, _vp],
+    "dl4jb200_comm_allreduce_avg_spans_f32": [_vp, _vp, _vp, _vp, _i, _vp],
+    "dl4jb200_comm_broadcast_f32": [_vp, _vp, _sz, _i, _vp],
+    "dl4jb200_spans_scale_copy": [_vp, _vp, _vp, _vp, _vp, _i, _d],
     "dl4jb200_updater_apply": [_vp, _vp, _vp, _vp, _sz, _i, _d, _d, _d, _d, _d, _d],
 }
 # entry points whose return value is not a status
@@ -113,6 +121,8 @@ _SPECIAL = {
     "dl4jb200_ctx_workspace_bytes": (_sz, [_vp]),
     "dl4jb200_ctx_sm_count": (_i, [_vp]),
     "dl4jb200_ctx_workspace_generation": (C.c_ulonglong, [_vp]),
+    "dl4jb200_comm_nranks": (_i, [_vp]),
+    "dl4jb200_comm_nccl_version": (_i, []),
 }
 
 _cdll = None

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libdl4jb200.so")
-SOURCES = ["api.cu", "elementwise.cu", "pool.cu", "bn.cu", "lrn.cu", "conv.cu", "conv_ffma.cu", "conv_tc.cu", "conv_tma.cu", "conv_stem.cu"]
+SOURCES = ["api.cu", "elementwise.cu", "pool.cu", "bn.cu", "lrn.cu", "conv.cu", "conv_ffma.cu", "conv_tc.cu", "conv_tma.cu", "conv_stem.cu", "comm.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "--use_fast_math=false"]
 
@@ -46,7 +46,7 @@ def build(force=False, verbose=False):
         failed = failed or p.returncode != 0
     if failed:
         raise RuntimeError("nvcc failed")
-    subprocess.check_call([_nvcc(), "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
+    subprocess.check_call([_nvcc(), "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-ldl"])
     return LIB
 
 

@@ -302,6 +302,16 @@ __device__ __forceinline__ float upd_one(const UpdSegCfg &c, float wi, float gi,
     return wi - u * inv_batch;
 }
 
+// dst[off_i + j] = scale * src[off_i + j] over a table of spans (one block per span): moves the BatchNormalization running
+// statistics -- scattered through the flat parameter vector -- into the (always zero) slots their gradients occupy in the
+// flat gradient vector and back, so that ONE all-reduce of the gradient also averages them across replicas.
+__global__ void __launch_bounds__(256) k_spans_scale_copy(float *__restrict__ dst, const float *__restrict__ src,
+                                                          const long long *__restrict__ off, const long long *__restrict__ cnt,
+                                                          float scale) {
+    const long long o = off[blockIdx.x], n = cnt[blockIdx.x];
+    for (long long i = threadIdx.x; i < n; i += blockDim.x) dst[o + i] = scale == 0.f ? 0.f : scale * src[o + i];
+}
+
 // A thread owns 4 consecutive elements: one segment search per quad, and when the quad lies inside one segment of a
 // stateless / flat-state updater (everything but AdaDelta's block-local layout) the five streams move as 128-bit accesses.
 __global__ void __launch_bounds__(256) k_updater_segments(float *__restrict__ w, const float *__restrict__ g,
@@ -461,6 +471,15 @@ int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g,
         k_score_fold<<<1, 256, 0, ctx->stream>>>(partial, nblk, score_reg_out);
         DL4J_CHECK_LAUNCH();
     }
+    return DL4JB200_OK;
+}
+
+int dl4jb200_spans_scale_copy(dl4jb200_ctx *ctx, float *dst, const float *src, const long long *offsets_dev,
+                              const long long *counts_dev, int nspans, double scale) {
+    DL4J_REQUIRE(ctx && dst && src && (nspans == 0 || (offsets_dev && counts_dev)), "spans_scale_copy: NULL argument");
+    if (nspans == 0) return DL4JB200_OK;
+    k_spans_scale_copy<<<nspans, 256, 0, ctx->stream>>>(dst, src, offsets_dev, counts_dev, (float)scale);
+    DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
 

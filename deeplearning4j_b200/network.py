@@ -55,6 +55,9 @@ class Network:
         # debugging / parity aid: when set to a dict, backward() leaves in it a device copy of every vertex' final delta
         # (the epsilon summed over its consumers, after the vertex' own activation backprop; raw epsilon for BN / pooling)
         self.trace = None
+        # data-parallel exchange overlapped with backward (parallel.ParallelWrapper sets itself here): it is told when
+        # backward starts, after every vertex (its gradient blocks are then enqueued on both streams) and when it ends
+        self.dp = None
         self.batch_div_scale = 1  # data-parallel replicas: global minibatch = scale * B (parallel.py)
         self.shapes = zoo.infer_shapes(model)
         self.P, self.layout = zoo.param_layout(model)
@@ -593,84 +596,95 @@ class Network:
         self._written, self._borrowed = set(), {}
         self._contrib, self._delta_done = {}, set()
         self._side_used = False
+        if self.dp is not None:
+            self.dp.backward_begin(self)
         for v in reversed(self.model["vertices"]):
             n, op = v["name"], v["op"]
             self._cur = n
             if op in ("input", "zeropad") or (self.out.get(n, 0) is None and n not in self.fused_bn):
                 continue
-            if op == "output":
-                e = self.aux[n]
-            else:
-                e = self._resolve(n)
-            if op in ("conv", "dense", "output"):
-                if op != "output" and v["act"] != "identity":
-                    # delta = afn.backprop(z, eps) (ConvolutionLayer.java:171, BaseLayer.java:71-102); only the activated
-                    # tensor is resident, so the derivative is taken from it: relu' = [a > 0], sigmoid' = a(1-a), tanh' = 1-a^2
-                    self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(),
-                               _ACT[v["act"]] | L.ACT_FROM_OUTPUT)
-                self._trace(n, e)
-                if op == "conv":
-                    src, d = self._conv_desc(v)
-                else:
-                    src, d = v["in"][0], self._dense_desc(v)
-                x, xcs = self._lin(n, src)
-                pw, gw, _, _ = self._p(n, "W")
-                _, gb, _, _ = self._p(n, "b")
-
-                side = self.overlap_wgrad
-                wcall = self._call_side if side else self._call
-                if side:  # fork: the side stream may start once everything queued so far (delta is final) has run
-                    fork = self.torch.cuda.Event()
-                    fork.record(self.stream)
-                    self.side_stream.wait_event(fork)
-                    self._side_used = True
-                if self.stem and self.stem[0] == n:
-                    wcall("dl4jb200_conv_rowpack_wgrad", C.byref(d), self._ptr(x), self.stem[1], self._ptr(e), self.cs[n], gw, gb)
-                else:
-                    wcall("dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
-                          gw, gb, None, L.NHWC, xcs, self.algo)
-                    self._emit_dgrad(src, d, pw, e, n, x, xcs)
-            elif op == "bn":
-                self._trace(n, e)
-                u = v["in"][0]
-                x, xcs = self._src(u)
-                s = self.shapes[n]
-                pg, gg, _, _ = self._p(n, "gamma")
-                pbeta, gbeta, _, _ = self._p(n, "beta")
-                sm, ss = self.aux[n]
-                self._emit(u, lambda dx: self._call("dl4jb200_bn_bwd", self._ptr(x), self._ptr(e), pg, pbeta, self._ptr(sm),
-                                                    self._ptr(ss), _ACT[v["act"]], dx, gg, gbeta, B, s[0], s[1], s[2], L.NHWC, xcs))
-            elif op == "pool":
-                self._trace(n, e)
-                u = v["in"][0]
-                x, xcs = self._lin(n, u)
-                d = self._pool_desc(v)
-                am = self._ptr(self.aux[n]) if v["type"] == "MAX" else None
-                self._emit(u, lambda dx: self._call("dl4jb200_pool_bwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), self._ptr(e), am,
-                                                    dx, L.NHWC, xcs, self.cs[n], _POOL[v["type"]], int(v.get("pnorm", 2)), 1e-8))
-            elif op in ("add", "act"):
-                if v["act"] != "identity" and n not in self._delta_done:
-                    self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(),
-                               _ACT[v["act"]] | L.ACT_FROM_OUTPUT)
-                self._trace(n, e)
-                for u in v["in"]:
-                    self._lend(u, e)
-            elif op == "flatten":
-                self._trace(n, e)
-                u = v["in"][0]
-                s = self.shapes[u]
-                chw = s[0] * s[1] * s[2]
-                srcbuf = e
-                if self.cs[n] != chw:
-                    self._call("dl4jb200_copy2d", self._ptr(e), self.cs[n], self._ptr(self.aux[n]), chw, B, chw)
-                    srcbuf = self.aux[n]
-                self._emit(u, lambda dx: self._call("dl4jb200_nchw_to_nhwc", self._ptr(srcbuf), dx, B, s[0], s[1], s[2], self.cs[u]))
-            else:
-                raise NotImplementedError(op)
+            self._backward_vertex(v)
+            if self.dp is not None:
+                self.dp.vertex_done(self, n)
         if self._side_used:  # join: gradient exchange / updater must see every filter gradient
             join = self.torch.cuda.Event()
             join.record(self.side_stream)
             self.stream.wait_event(join)
+        if self.dp is not None:
+            self.dp.backward_end(self)
+
+    def _backward_vertex(self, v):
+        L, B = _lib, self.B
+        n, op = v["name"], v["op"]
+        if op == "output":
+            e = self.aux[n]
+        else:
+            e = self._resolve(n)
+        if op in ("conv", "dense", "output"):
+            if op != "output" and v["act"] != "identity":
+                # delta = afn.backprop(z, eps) (ConvolutionLayer.java:171, BaseLayer.java:71-102); only the activated
+                # tensor is resident, so the derivative is taken from it: relu' = [a > 0], sigmoid' = a(1-a), tanh' = 1-a^2
+                self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(),
+                           _ACT[v["act"]] | L.ACT_FROM_OUTPUT)
+            self._trace(n, e)
+            if op == "conv":
+                src, d = self._conv_desc(v)
+            else:
+                src, d = v["in"][0], self._dense_desc(v)
+            x, xcs = self._lin(n, src)
+            pw, gw, _, _ = self._p(n, "W")
+            _, gb, _, _ = self._p(n, "b")
+
+            side = self.overlap_wgrad
+            wcall = self._call_side if side else self._call
+            if side:  # fork: the side stream may start once everything queued so far (delta is final) has run
+                fork = self.torch.cuda.Event()
+                fork.record(self.stream)
+                self.side_stream.wait_event(fork)
+                self._side_used = True
+            if self.stem and self.stem[0] == n:
+                wcall("dl4jb200_conv_rowpack_wgrad", C.byref(d), self._ptr(x), self.stem[1], self._ptr(e), self.cs[n], gw, gb)
+            else:
+                wcall("dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
+                      gw, gb, None, L.NHWC, xcs, self.algo)
+                self._emit_dgrad(src, d, pw, e, n, x, xcs)
+        elif op == "bn":
+            self._trace(n, e)
+            u = v["in"][0]
+            x, xcs = self._src(u)
+            s = self.shapes[n]
+            pg, gg, _, _ = self._p(n, "gamma")
+            pbeta, gbeta, _, _ = self._p(n, "beta")
+            sm, ss = self.aux[n]
+            self._emit(u, lambda dx: self._call("dl4jb200_bn_bwd", self._ptr(x), self._ptr(e), pg, pbeta, self._ptr(sm),
+                                                self._ptr(ss), _ACT[v["act"]], dx, gg, gbeta, B, s[0], s[1], s[2], L.NHWC, xcs))
+        elif op == "pool":
+            self._trace(n, e)
+            u = v["in"][0]
+            x, xcs = self._lin(n, u)
+            d = self._pool_desc(v)
+            am = self._ptr(self.aux[n]) if v["type"] == "MAX" else None
+            self._emit(u, lambda dx: self._call("dl4jb200_pool_bwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), self._ptr(e), am,
+                                                dx, L.NHWC, xcs, self.cs[n], _POOL[v["type"]], int(v.get("pnorm", 2)), 1e-8))
+        elif op in ("add", "act"):
+            if v["act"] != "identity" and n not in self._delta_done:
+                self._call("dl4jb200_act_bwd", self._ptr(self.out[n]), self._ptr(e), self._ptr(e), e.numel(),
+                           _ACT[v["act"]] | L.ACT_FROM_OUTPUT)
+            self._trace(n, e)
+            for u in v["in"]:
+                self._lend(u, e)
+        elif op == "flatten":
+            self._trace(n, e)
+            u = v["in"][0]
+            s = self.shapes[u]
+            chw = s[0] * s[1] * s[2]
+            srcbuf = e
+            if self.cs[n] != chw:
+                self._call("dl4jb200_copy2d", self._ptr(e), self.cs[n], self._ptr(self.aux[n]), chw, B, chw)
+                srcbuf = self.aux[n]
+            self._emit(u, lambda dx: self._call("dl4jb200_nchw_to_nhwc", self._ptr(srcbuf), dx, B, s[0], s[1], s[2], self.cs[u]))
+        else:
+            raise NotImplementedError(op)
 
     # ------------------------------------------------------------------ updater + step (BaseMultiLayerUpdater.update)
     def _upd_args(self, cfg):

@@ -354,6 +354,39 @@ int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g,
                                     const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
                                     const double *cfg_host, int ncfg, double batch_div, float *score_reg_out);
 
+/* ------------------------------------------------------------------ data-parallel exchange --- */
+/* The plug-in point for single-box data parallelism is GradientsAccumulator.storeUpdate / applyUpdate
+ * (NN/optimize/solvers/accumulation/GradientsAccumulator.java:27-41), installed into every replica's optimizer by
+ * ParallelWrapper's TrainingMode.CUSTOM (deeplearning4j-scaleout/.../parallelism/ParallelWrapper.java:838-843) and called
+ * from StochasticGradientDescent.optimize (NN/optimize/solvers/StochasticGradientDescent.java:66-79). The reference's own
+ * implementations move threshold-encoded updates through host queues (EncodedGradientsAccumulator.java:244-315, 440-520) or
+ * average parameters with Nd4j.averageAndPropagate (ParallelWrapper.java:316-376); here the exchange is an NCCL all-reduce
+ * of the flat fp32 vectors over NVLink, enqueued on a CUDA stream (stream == NULL: the context's). One communicator per
+ * (replica, device): rank 0 creates the 128-byte id (comm_unique_id) and hands it to the other replicas -- worker threads of
+ * one JVM share it in memory, separate processes send it over whatever channel started them -- then every replica calls
+ * comm_init. NCCL is bound at run time (dlopen); without it these calls return NOT_SUPPORTED and nothing else is affected. */
+typedef struct dl4jb200_comm dl4jb200_comm;
+int dl4jb200_comm_unique_id(void *id_out, size_t bytes);
+int dl4jb200_comm_init(dl4jb200_ctx *ctx, int nranks, int rank, const void *id, dl4jb200_comm **out);
+int dl4jb200_comm_destroy(dl4jb200_comm *comm);
+int dl4jb200_comm_nranks(dl4jb200_comm *comm);
+int dl4jb200_comm_nccl_version(void);
+/* in place over n floats: sum (the raw gradient: replicas then run the identical updater with batchSize = workers * B) or
+ * average (parameters / updater state of the reference's AVERAGING mode) */
+int dl4jb200_comm_allreduce_sum_f32(dl4jb200_comm *comm, float *buf, size_t n, void *stream);
+int dl4jb200_comm_allreduce_avg_f32(dl4jb200_comm *comm, float *buf, size_t n, void *stream);
+/* average several disjoint spans of one buffer as one NCCL group (host arrays of float offsets / counts) */
+int dl4jb200_comm_allreduce_avg_spans_f32(dl4jb200_comm *comm, float *base, const long long *offsets, const long long *counts,
+                                          int nspans, void *stream);
+/* DefaultTrainer copies the master's parameters into every replica (parallelism/trainer/DefaultTrainer.java:254-311) */
+int dl4jb200_comm_broadcast_f32(dl4jb200_comm *comm, float *buf, size_t n, int root, void *stream);
+/* dst[off_i + j] = scale * src[off_i + j] for a DEVICE table of spans (scale 0 writes zeros): parks the BatchNormalization
+ * running statistics (parameters with a NoOp updater whose gradient view is identically zero,
+ * BatchNormalization.java:205-208) in their own gradient slots, scaled by 1 / workers, so that the one gradient all-reduce
+ * averages them too, and moves them back afterwards. */
+int dl4jb200_spans_scale_copy(dl4jb200_ctx *ctx, float *dst, const float *src, const long long *offsets_dev,
+                              const long long *counts_dev, int nspans, double scale);
+
 #ifdef __cplusplus
 }
 #endif

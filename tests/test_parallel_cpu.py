@@ -92,3 +92,23 @@ def test_dp_exchange_world2_gloo():
         p.join(timeout=60)
     for rank, msg in res:
         assert msg == "ok", f"rank {rank}: {msg}"
+
+
+def test_bucket_plan_covers_the_flat_gradient_in_backward_order():
+    """plan_buckets: contiguous ranges along vertex boundaries, closing from the end of the flat vector to its start."""
+    from deeplearning4j_b200 import parallel, zoo
+    from oracle import oracle as o
+    for model in (zoo.resnet50(), zoo.vgg16(), zoo.lenet()):
+        P, layout = zoo.param_layout(model, o.out_size)
+        for nb in (1, 4, 6, 1000):
+            close = parallel.plan_buckets(model, layout, P, nb)
+            order = [v["name"] for v in reversed(model["vertices"]) if v["name"] in close]
+            hi = P
+            for name in order:  # in the order backward reaches them
+                lo, h = close[name]
+                assert h == hi and lo < h
+                hi = lo
+            assert hi == 0
+            assert len(close) <= max(1, min(nb, sum(1 for v in model["vertices"] if v["op"] in ("conv", "bn", "dense", "output"))))
+        off, cnt = parallel.bn_stat_spans(layout)
+        assert int(cnt.sum()) == parallel.bn_stat_index(layout).size
