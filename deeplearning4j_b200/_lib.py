@@ -12,6 +12,8 @@ OK, NOT_SUPPORTED = 0, 1
 ERR_INVALID_ARG, ERR_CUDA, ERR_INVALID_INPUT, ERR_INVALID_CONFIG = -1, -2, -3, -4
 MODE_STRICT, MODE_TRUNCATE, MODE_SAME = 0, 1, 2
 NCHW, NHWC = 0, 1
+BUF_HOST_NEWER, BUF_SYNCED, BUF_DEVICE_NEWER = 0, 1, 2
+BUF_READ, BUF_WRITE = 1, 2
 POOL_MAX, POOL_AVG, POOL_SUM, POOL_PNORM = 0, 1, 2, 3
 ACT_IDENTITY, ACT_RELU, ACT_SIGMOID, ACT_TANH, ACT_LEAKYRELU = 0, 1, 2, 3, 4
 ACT_FROM_OUTPUT = 0x200
@@ -63,6 +65,11 @@ PROTOTYPES = {
     "dl4jb200_memcpy_d2h": [_vp, _vp, _vp, _sz],
     "dl4jb200_memcpy_d2d": [_vp, _vp, _vp, _sz],
     "dl4jb200_buf_register": [_vp, _vp, _sz, C.POINTER(_vp)],
+    "dl4jb200_buf_acquire": [_vp, _vp, _sz, _i, C.POINTER(_vp)],
+    "dl4jb200_buf_mark_host_dirty": [_vp, _vp],
+    "dl4jb200_buf_sync_to_host": [_vp, _vp],
+    "dl4jb200_buf_state": [_vp, _vp, C.POINTER(_i)],
+    "dl4jb200_ctx_transfer_bytes": [_vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)],
     "dl4jb200_buf_lookup": [_vp, _vp, C.POINTER(_vp), C.POINTER(_sz)],
     "dl4jb200_buf_upload": [_vp, _vp],
     "dl4jb200_buf_download": [_vp, _vp],

@@ -78,6 +78,7 @@ int dl4jb200_ctx_destroy(dl4jb200_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (auto &kv : ctx->mirrors) cudaFree(kv.second.dev);
+    for (auto &kv : ctx->mirror_pool) cudaFree(kv.second);
     conv_filters_free(ctx);
     for (int i = 0; i < 4; i++) if (ctx->ws[i]) cudaFree(ctx->ws[i]);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -148,6 +149,7 @@ int dl4jb200_memset(dl4jb200_ctx *ctx, void *dst, int value, size_t bytes) {
 int dl4jb200_memcpy_h2d(dl4jb200_ctx *ctx, void *dst, const void *src_host, size_t bytes) {
     DL4J_REQUIRE(ctx && dst && src_host, "memcpy_h2d: NULL argument");
     DL4J_CUDA_TRY(cudaMemcpyAsync(dst, src_host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->h2d_bytes += bytes;
     return DL4JB200_OK;
 }
 
@@ -155,6 +157,7 @@ int dl4jb200_memcpy_d2h(dl4jb200_ctx *ctx, void *dst_host, const void *src, size
     DL4J_REQUIRE(ctx && dst_host && src, "memcpy_d2h: NULL argument");
     DL4J_CUDA_TRY(cudaMemcpyAsync(dst_host, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));  // the host may read dst as soon as we return
+    ctx->d2h_bytes += bytes;
     return DL4JB200_OK;
 }
 
@@ -164,19 +167,81 @@ int dl4jb200_memcpy_d2d(dl4jb200_ctx *ctx, void *dst, const void *src, size_t by
     return DL4JB200_OK;
 }
 
-int dl4jb200_buf_register(dl4jb200_ctx *ctx, const void *host_ptr, size_t bytes, void **device_out) {
-    DL4J_REQUIRE(ctx && host_ptr && device_out, "buf_register: NULL argument");
+// ---- host-mirror registry. An INDArray under nd4j-native lives in host memory; its device copy is owned here, keyed by
+// the host address, with a state that says which side is current. Helper calls acquire their operands: an input is uploaded
+// only if the host side is newer, an output just becomes "device newer"; the host gets the bytes when (and only when) it
+// asks (sync_to_host). Chained helper calls therefore move nothing across the host link.
+static int mirror_get(dl4jb200_ctx *ctx, const void *host_ptr, size_t bytes, MirrorBuf **out) {
     auto it = ctx->mirrors.find(host_ptr);
-    if (it != ctx->mirrors.end()) {
-        if (it->second.bytes >= bytes) { *device_out = it->second.dev; return DL4JB200_OK; }
-        DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
-        cudaFree(it->second.dev);
+    if (it != ctx->mirrors.end() && it->second.bytes >= bytes) { *out = &it->second; return DL4JB200_OK; }
+    if (it != ctx->mirrors.end()) {  // grown: the old copy goes back to the pool (same stream: ordering keeps it safe)
+        ctx->mirror_pool.emplace(it->second.bytes, it->second.dev);
         ctx->mirrors.erase(it);
     }
     void *d = nullptr;
-    DL4J_CUDA_TRY(cudaMalloc(&d, bytes ? bytes : 16));
-    ctx->mirrors[host_ptr] = MirrorBuf{d, bytes};
-    *device_out = d;
+    const size_t want = bytes ? bytes : 16;
+    auto p = ctx->mirror_pool.find(want);
+    if (p != ctx->mirror_pool.end()) { d = p->second; ctx->mirror_pool.erase(p); }
+    else DL4J_CUDA_TRY(cudaMalloc(&d, want));
+    *out = &(ctx->mirrors[host_ptr] = MirrorBuf{d, want, DL4JB200_BUF_HOST_NEWER});
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_register(dl4jb200_ctx *ctx, const void *host_ptr, size_t bytes, void **device_out) {
+    DL4J_REQUIRE(ctx && host_ptr && device_out, "buf_register: NULL argument");
+    MirrorBuf *m;
+    int rc = mirror_get(ctx, host_ptr, bytes, &m);
+    if (rc) return rc;
+    *device_out = m->dev;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_acquire(dl4jb200_ctx *ctx, const void *host_ptr, size_t bytes, int access, void **device_out) {
+    DL4J_REQUIRE(ctx && host_ptr && device_out, "buf_acquire: NULL argument");
+    DL4J_REQUIRE(access >= 1 && access <= 3, "buf_acquire: access must be READ (1), WRITE (2) or both (3)");
+    MirrorBuf *m;
+    int rc = mirror_get(ctx, host_ptr, bytes, &m);
+    if (rc) return rc;
+    if ((access & DL4JB200_BUF_READ) && m->state == DL4JB200_BUF_HOST_NEWER) {
+        DL4J_CUDA_TRY(cudaMemcpyAsync(m->dev, host_ptr, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->h2d_bytes += bytes;
+        m->state = DL4JB200_BUF_SYNCED;
+    }
+    if (access & DL4JB200_BUF_WRITE) m->state = DL4JB200_BUF_DEVICE_NEWER;
+    *device_out = m->dev;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_mark_host_dirty(dl4jb200_ctx *ctx, const void *host_ptr) {
+    DL4J_REQUIRE(ctx && host_ptr, "buf_mark_host_dirty: NULL argument");
+    auto it = ctx->mirrors.find(host_ptr);
+    if (it != ctx->mirrors.end()) it->second.state = DL4JB200_BUF_HOST_NEWER;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_sync_to_host(dl4jb200_ctx *ctx, void *host_ptr) {
+    DL4J_REQUIRE(ctx && host_ptr, "buf_sync_to_host: NULL argument");
+    auto it = ctx->mirrors.find(host_ptr);
+    if (it == ctx->mirrors.end()) { dl4j_set_error("buf_sync_to_host: %p is not registered", host_ptr); return DL4JB200_ERR_INVALID_ARG; }
+    if (it->second.state != DL4JB200_BUF_DEVICE_NEWER) return DL4JB200_OK;  // the host copy is current: nothing moves
+    DL4J_CUDA_TRY(cudaMemcpyAsync(host_ptr, it->second.dev, it->second.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->d2h_bytes += it->second.bytes;
+    it->second.state = DL4JB200_BUF_SYNCED;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_buf_state(dl4jb200_ctx *ctx, const void *host_ptr, int *state_out) {
+    DL4J_REQUIRE(ctx && host_ptr && state_out, "buf_state: NULL argument");
+    auto it = ctx->mirrors.find(host_ptr);
+    *state_out = it == ctx->mirrors.end() ? -1 : it->second.state;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_ctx_transfer_bytes(dl4jb200_ctx *ctx, unsigned long long *h2d_out, unsigned long long *d2h_out) {
+    DL4J_REQUIRE(ctx, "ctx is NULL");
+    if (h2d_out) *h2d_out = ctx->h2d_bytes;
+    if (d2h_out) *d2h_out = ctx->d2h_bytes;
     return DL4JB200_OK;
 }
 
@@ -190,19 +255,23 @@ int dl4jb200_buf_lookup(dl4jb200_ctx *ctx, const void *host_ptr, void **device_o
 }
 
 int dl4jb200_buf_upload(dl4jb200_ctx *ctx, const void *host_ptr) {
-    void *d; size_t n;
-    int rc = dl4jb200_buf_lookup(ctx, host_ptr, &d, &n);
-    if (rc) return rc;
-    DL4J_CUDA_TRY(cudaMemcpyAsync(d, host_ptr, n, cudaMemcpyHostToDevice, ctx->stream));
+    DL4J_REQUIRE(ctx && host_ptr, "buf_upload: NULL argument");
+    auto it = ctx->mirrors.find(host_ptr);
+    if (it == ctx->mirrors.end()) { dl4j_set_error("buf_upload: %p is not registered", host_ptr); return DL4JB200_ERR_INVALID_ARG; }
+    DL4J_CUDA_TRY(cudaMemcpyAsync(it->second.dev, host_ptr, it->second.bytes, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->h2d_bytes += it->second.bytes;
+    it->second.state = DL4JB200_BUF_SYNCED;
     return DL4JB200_OK;
 }
 
 int dl4jb200_buf_download(dl4jb200_ctx *ctx, void *host_ptr) {
-    void *d; size_t n;
-    int rc = dl4jb200_buf_lookup(ctx, host_ptr, &d, &n);
-    if (rc) return rc;
-    DL4J_CUDA_TRY(cudaMemcpyAsync(host_ptr, d, n, cudaMemcpyDeviceToHost, ctx->stream));
+    DL4J_REQUIRE(ctx && host_ptr, "buf_download: NULL argument");
+    auto it = ctx->mirrors.find(host_ptr);
+    if (it == ctx->mirrors.end()) { dl4j_set_error("buf_download: %p is not registered", host_ptr); return DL4JB200_ERR_INVALID_ARG; }
+    DL4J_CUDA_TRY(cudaMemcpyAsync(host_ptr, it->second.dev, it->second.bytes, cudaMemcpyDeviceToHost, ctx->stream));
     DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    ctx->d2h_bytes += it->second.bytes;
+    it->second.state = DL4JB200_BUF_SYNCED;
     return DL4JB200_OK;
 }
 
@@ -210,8 +279,9 @@ int dl4jb200_buf_release(dl4jb200_ctx *ctx, const void *host_ptr) {
     DL4J_REQUIRE(ctx && host_ptr, "buf_release: NULL argument");
     auto it = ctx->mirrors.find(host_ptr);
     if (it == ctx->mirrors.end()) return DL4JB200_OK;
-    DL4J_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
-    cudaFree(it->second.dev);
+    // back to the pool, not to the driver: every use of the buffer is ordered on the context's stream, and a steady-state
+    // loop (same shapes every iteration) then allocates nothing
+    ctx->mirror_pool.emplace(it->second.bytes, it->second.dev);
     ctx->mirrors.erase(it);
     return DL4JB200_OK;
 }

@@ -14,6 +14,7 @@
 struct MirrorBuf {
     void *dev;
     size_t bytes;
+    int state;  // DL4JB200_BUF_HOST_NEWER / SYNCED / DEVICE_NEWER: which side holds the current contents
 };
 
 struct FilterRegistry;
@@ -32,6 +33,8 @@ struct dl4jb200_ctx {
     bool ws_frozen = false;
     unsigned long long ws_generation = 0;  // bumped whenever a region is (re)allocated
     std::unordered_map<const void *, MirrorBuf> mirrors;
+    std::unordered_multimap<size_t, void *> mirror_pool;  // released device buffers by size, reused by the next acquire
+    unsigned long long h2d_bytes = 0, d2h_bytes = 0;      // bytes this context moved across the host link
     struct FilterRegistry *filters = nullptr;  // pre-packed convolution filters (conv.cu); freed by conv_filters_free
 };
 

@@ -132,10 +132,27 @@ int dl4jb200_memcpy_d2h(dl4jb200_ctx *ctx, void *dst_host, const void *src, size
 int dl4jb200_memcpy_d2d(dl4jb200_ctx *ctx, void *dst, const void *src, size_t bytes);
 
 /* Host-mirror registry: maps an INDArray's host address (INDArray.data().addressPointer() under
- * nd4j-native) to a device buffer owned by the context, so that chained helper calls stay on the device
- * and bytes cross PCIe only when the host side reads or writes (replaces nd4j-cuda's
- * AtomicAllocator.getPointer, CudnnConvolutionHelper.java:442-447). */
+ * nd4j-native) to a device buffer owned by the context, with a state that says which side holds the current contents,
+ * so that chained helper calls stay on the device and bytes cross PCIe only when the host side really wrote or reads
+ * (replaces what the cuDNN helper gets from nd4j-cuda's AtomicAllocator.getPointer, CudnnConvolutionHelper.java:442-447).
+ *   buf_acquire(READ)   an operand a kernel will read : registered if new; uploaded only if the host copy is newer
+ *   buf_acquire(WRITE)  an operand a kernel will write: registered if new; becomes "device newer", nothing moves
+ *   buf_mark_host_dirty the host wrote the array (a non-helper layer, the updater): next READ acquire uploads
+ *   buf_sync_to_host    the host is about to read it : downloaded only if the device copy is newer (synchronous)
+ *   buf_release         the array died: its device buffer goes to a pool reused by later acquires of the same size
+ * buf_register / buf_upload / buf_download are the unconditional forms. ctx_transfer_bytes reports the bytes the context
+ * has moved across the host link (registry traffic and memcpy_h2d / memcpy_d2h). */
+#define DL4JB200_BUF_HOST_NEWER 0
+#define DL4JB200_BUF_SYNCED 1
+#define DL4JB200_BUF_DEVICE_NEWER 2
+#define DL4JB200_BUF_READ 1
+#define DL4JB200_BUF_WRITE 2
 int dl4jb200_buf_register(dl4jb200_ctx *ctx, const void *host_ptr, size_t bytes, void **device_out);
+int dl4jb200_buf_acquire(dl4jb200_ctx *ctx, const void *host_ptr, size_t bytes, int access, void **device_out);
+int dl4jb200_buf_mark_host_dirty(dl4jb200_ctx *ctx, const void *host_ptr);
+int dl4jb200_buf_sync_to_host(dl4jb200_ctx *ctx, void *host_ptr);
+int dl4jb200_buf_state(dl4jb200_ctx *ctx, const void *host_ptr, int *state_out); /* -1: not registered */
+int dl4jb200_ctx_transfer_bytes(dl4jb200_ctx *ctx, unsigned long long *h2d_out, unsigned long long *d2h_out);
 int dl4jb200_buf_lookup(dl4jb200_ctx *ctx, const void *host_ptr, void **device_out, size_t *bytes_out);
 int dl4jb200_buf_upload(dl4jb200_ctx *ctx, const void *host_ptr);  /* host -> device mirror */
 int dl4jb200_buf_download(dl4jb200_ctx *ctx, void *host_ptr);      /* device mirror -> host */

@@ -1,8 +1,5 @@
 package org.deeplearning4j.b200;
 
-import java.util.HashSet;
-import java.util.Set;
-
 import org.bytedeco.javacpp.FloatPointer;
 import org.bytedeco.javacpp.Pointer;
 import org.bytedeco.javacpp.PointerPointer;
@@ -22,7 +19,13 @@ import org.nd4j.linalg.factory.Nd4j;
 public final class B200Context {
     private static final ThreadLocal<B200Context> TL = ThreadLocal.withInitial(B200Context::new);
     private Pointer handle;
-    private final Set<Long> deviceDirty = new HashSet<>();
+    /**
+     * Lazy device-to-host synchronisation. nd4j-native gives no hook when host code reads an INDArray, so by default a
+     * helper result is brought back before the helper returns (done()); a caller that promises to call syncToHost()
+     * before any host-side read (e.g. a MultiLayerNetwork whose CNN stack consists of helper-backed layers only) may
+     * switch it off with -Ddl4jb200.lazySync=true and then pays PCIe only at the minibatch and parameter boundaries.
+     */
+    private final boolean lazySync = Boolean.getBoolean("dl4jb200.lazySync");
 
     private B200Context() {
         try {
@@ -58,23 +61,46 @@ public final class B200Context {
         return Nd4j.createUninitialized(shape, 'c');
     }
 
-    private FloatPointer device(INDArray a, boolean upload) {
+    private FloatPointer device(INDArray a, int access) {
         if (a == null) return null;
         Pointer host = a.data().addressPointer();
         PointerPointer<Pointer> dev = new PointerPointer<>(1);
-        check(Dl4jB200.dl4jb200_buf_register(handle, host, a.length() * 4L, dev));
-        if (upload && !deviceDirty.contains(host.address())) check(Dl4jB200.dl4jb200_buf_upload(handle, host));
+        // registered on first sight; uploaded only when the host copy is newer; WRITE access marks the device copy newer
+        check(Dl4jB200.dl4jb200_buf_acquire(handle, host, a.length() * 4L, access, dev));
         return new FloatPointer(dev.get(0));
     }
 
-    public FloatPointer in(INDArray a) { return device(a, true); }
-    public FloatPointer inout(INDArray a) { return device(a, true); }
-    public FloatPointer out(INDArray a) { return device(a, false); }
+    /** An operand a kernel reads. Host-made arrays (the minibatch, parameters after the updater ran) must have been
+     *  declared with hostWrote(); arrays produced by a helper are already current on the device. */
+    public FloatPointer in(INDArray a) {
+        if (!lazySync) hostWrote(a);  // without the lazy protocol any host array may have changed since the last call
+        return device(a, Dl4jB200.BUF_READ);
+    }
+    public FloatPointer inout(INDArray a) {
+        if (!lazySync) hostWrote(a);
+        return device(a, Dl4jB200.BUF_READ | Dl4jB200.BUF_WRITE);
+    }
+    public FloatPointer out(INDArray a) { return device(a, Dl4jB200.BUF_WRITE); }
 
-    /** Result produced on the device: bring it back for host-side consumers (non-helper layers, updater, listeners). */
-    public INDArray done(INDArray a) {
-        if (a != null) check(Dl4jB200.dl4jb200_buf_download(handle, a.data().addressPointer()));
+    /** Host code wrote this array (DataSet features, params.subi(update), a non-helper layer's output). */
+    public void hostWrote(INDArray a) {
+        if (a != null) check(Dl4jB200.dl4jb200_buf_mark_host_dirty(handle, a.data().addressPointer()));
+    }
+
+    /** Host code is about to read this array: copies it back only if the device copy is newer. */
+    public INDArray syncToHost(INDArray a) {
+        if (a != null) check(Dl4jB200.dl4jb200_buf_sync_to_host(handle, a.data().addressPointer()));
         return a;
+    }
+
+    /** Result produced on the device, handed to the layer: brought back now unless lazy synchronisation is on. Gradient
+     *  views and running statistics (the parameter boundary) always come back. */
+    public INDArray done(INDArray a) { return lazySync ? a : syncToHost(a); }
+    public INDArray doneParameter(INDArray a) { return syncToHost(a); }
+
+    /** The INDArray died (workspace closed / garbage collected): its device buffer returns to the pool. */
+    public void release(INDArray a) {
+        if (a != null) check(Dl4jB200.dl4jb200_buf_release(handle, a.data().addressPointer()));
     }
 
     public static int activationCode(IActivation afn) {

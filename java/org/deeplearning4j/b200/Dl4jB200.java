@@ -63,6 +63,26 @@ public class Dl4jB200 {
                     FloatPointer y, @Cast("size_t") long n, double retainProb);
     public static native int dl4jb200_buf_register(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host, long bytes,
                     @Cast("void**") PointerPointer deviceOut);
+    public static final int BUF_HOST_NEWER = 0, BUF_SYNCED = 1, BUF_DEVICE_NEWER = 2, BUF_READ = 1, BUF_WRITE = 2;
+    public static native int dl4jb200_buf_acquire(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host, @Cast("size_t") long bytes,
+                    int access, @Cast("void**") PointerPointer deviceOut);
+    public static native int dl4jb200_buf_mark_host_dirty(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host);
+    public static native int dl4jb200_buf_sync_to_host(@Cast("dl4jb200_ctx*") Pointer ctx, Pointer host);
+    public static native int dl4jb200_buf_release(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host);
+    public static native int dl4jb200_ctx_transfer_bytes(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("unsigned long long*") long[] h2d,
+                    @Cast("unsigned long long*") long[] d2h);
+    // data-parallel exchange (B200GradientsAccumulator)
+    public static native int dl4jb200_comm_unique_id(Pointer idOut, @Cast("size_t") long bytes);
+    public static native int dl4jb200_comm_init(@Cast("dl4jb200_ctx*") Pointer ctx, int nranks, int rank, @Const Pointer id,
+                    @Cast("dl4jb200_comm**") PointerPointer out);
+    public static native int dl4jb200_comm_destroy(@Cast("dl4jb200_comm*") Pointer comm);
+    public static native int dl4jb200_comm_allreduce_sum_f32(@Cast("dl4jb200_comm*") Pointer comm, FloatPointer buf, @Cast("size_t") long n,
+                    Pointer stream);
+    public static native int dl4jb200_comm_allreduce_avg_f32(@Cast("dl4jb200_comm*") Pointer comm, FloatPointer buf, @Cast("size_t") long n,
+                    Pointer stream);
+    public static native int dl4jb200_comm_broadcast_f32(@Cast("dl4jb200_comm*") Pointer comm, FloatPointer buf, @Cast("size_t") long n,
+                    int root, Pointer stream);
+    public static native int dl4jb200_ctx_workspace_freeze(@Cast("dl4jb200_ctx*") Pointer ctx, int frozen);
     public static native int dl4jb200_buf_upload(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host);
     public static native int dl4jb200_buf_download(@Cast("dl4jb200_ctx*") Pointer ctx, Pointer host);
     public static native int dl4jb200_out_size(int in, int kernel, int stride, int pad, int dilation, int mode, IntPointer out,
