@@ -109,6 +109,11 @@ PROTOTYPES = {
     "dl4jb200_copy2d": [_vp, _vp, _i, _vp, _i, _i, _i],
     "dl4jb200_grad_normalize": [_vp, _vp, _sz, _i, _d],
     "dl4jb200_updater_apply_segments": [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _vp, _i, _d, _vp],
+    "dl4jb200_deconv2d_fwd": [_vp, _desc_p, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i],
+    "dl4jb200_deconv2d_bwd": [_vp, _desc_p, _vp, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i],
+    "dl4jb200_bias_act": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i],
+    "dl4jb200_depthwise_fwd": [_vp, _desc_p, _i, _vp, _i, _vp, _vp, _i],
+    "dl4jb200_depthwise_bwd": [_vp, _desc_p, _i, _vp, _i, _vp, _vp, _i, _vp, _vp, _i],
     "dl4jb200_comm_unique_id": [_vp, _sz],
     "dl4jb200_comm_init": [_vp, _i, _i, _vp, C.POINTER(_vp)],
     "dl4jb200_comm_destroy": [_vp],

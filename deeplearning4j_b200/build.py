@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libdl4jb200.so")
-SOURCES = ["api.cu", "elementwise.cu", "pool.cu", "bn.cu", "lrn.cu", "conv.cu", "conv_ffma.cu", "conv_tc.cu", "conv_tma.cu", "conv_stem.cu", "comm.cu"]
+SOURCES = ["api.cu", "elementwise.cu", "pool.cu", "bn.cu", "lrn.cu", "conv.cu", "conv_ffma.cu", "conv_tc.cu", "conv_tma.cu", "conv_stem.cu", "comm.cu", "conv_variants.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "--use_fast_math=false"]
 

@@ -435,10 +435,12 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     const float *xs = x, *ds = delta;
     if (x_layout == DL4JB200_NCHW) {
         x_cs = dl4j_round_up(d->c_in, 4);
-        float *t = (float *)dl4j_workspace(ctx, 1, (size_t)d->batch * d->in_h * d->in_w * x_cs * sizeof(float));
-        if (!t) return DL4JB200_ERR_CUDA;
-        if ((rc = dl4jb200_nchw_to_nhwc(ctx, x, t, d->batch, d->c_in, d->in_h, d->in_w, x_cs))) return rc;
-        xs = t;
+        if (dw) {  // only the filter gradient reads x
+            float *t = (float *)dl4j_workspace(ctx, 1, (size_t)d->batch * d->in_h * d->in_w * x_cs * sizeof(float));
+            if (!t) return DL4JB200_ERR_CUDA;
+            if ((rc = dl4jb200_nchw_to_nhwc(ctx, x, t, d->batch, d->c_in, d->in_h, d->in_w, x_cs))) return rc;
+            xs = t;
+        }
     }
     if (delta_layout == DL4JB200_NCHW) {
         delta_cs = dl4j_round_up(d->c_out, 4);

@@ -915,6 +915,28 @@ class Network:
             return np.ascontiguousarray(a[..., :s[0]].transpose(0, 3, 1, 2))
         return a[:, :s[0]].copy()
 
+    # ------------------------------------------------------------------ checkpoint / resume (ModelSerializer layout)
+    def save_checkpoint(self, path, configuration_json="{}", save_updater=True):
+        """ModelSerializer.writeModel: the device-resident flat vectors are brought to the host (the parameter boundary) and
+        written as coefficients.bin / updaterState.bin (util/ModelSerializer.java:120-163)."""
+        from . import modelserializer as ms
+        self.stream.synchronize()
+        ms.write_model(path, configuration_json, self.params.cpu().numpy(), self.state.cpu().numpy() if save_updater else None)
+
+    def load_checkpoint(self, path):
+        """ModelSerializer.restore*: parameters (and updater state when present) go back to the device."""
+        from . import modelserializer as ms
+        t = self.torch
+        conf, params, state = ms.restore_model(path)
+        assert params.size == self.P, f"checkpoint holds {params.size} parameters, the network has {self.P}"
+        with t.cuda.stream(self.stream):
+            self.params.copy_(t.from_numpy(params), non_blocking=False)
+            if state is not None:
+                assert state.size == self.state.numel()
+                self.state.copy_(t.from_numpy(state), non_blocking=False)
+        self.params_changed()
+        return conf
+
     def close(self):
         if self.h:
             self.torch.cuda.synchronize(self.dev)

@@ -371,6 +371,30 @@ int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g,
                                     const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
                                     const double *cfg_host, int ncfg, double batch_div, float *score_reg_out);
 
+/* ------------------------------------------------------------------ layers that share the conv helper field (f4) - */
+/* Deconvolution2DLayer (NN/nn/layers/convolution/Deconvolution2DLayer.java:145-233 forward, :48-138 backward; the reference
+ * runs libnd4j's "deconv2d" / "deconv2d_bp" custom ops). d describes the DECONVOLUTION: c_in = nIn, in_h/in_w its input,
+ * c_out = nOut, out_h/out_w = stride*(in-1) + kEff - 2*pad (NN/util/ConvolutionUtils.java:63-83; Same mode is refused by the
+ * layer itself, :147-149). w is [nIn, nOut, kH, kW] 'c' (NN/nn/params/DeconvolutionParamInitializer.java:75-80). Runs on the
+ * same tcgen05 GEMMs with input and epsilon exchanged: forward = backprop-data of the mirrored convolution (+ bias,
+ * activation), filter gradient = its filter gradient, epsilon = its forward pass. */
+int dl4jb200_deconv2d_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs, const float *w,
+                          const float *bias, float *z, int z_layout, int z_cs, int act, int algo);
+int dl4jb200_deconv2d_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *x, int x_layout, int x_cs, const float *w,
+                          const float *delta, int delta_layout, int delta_cs, float *dw, float *db, float *dx, int dx_layout,
+                          int dx_cs, int algo);
+/* z = act(z + bias[c]) in place (the bias / activation step of the layers above; NCHW or NHWC) */
+int dl4jb200_bias_act(dl4jb200_ctx *ctx, float *z, const float *bias, int B, int C, int H, int W, int layout, int cs, int act);
+/* Depth-wise stage of SeparableConvolution2DLayer (NN/nn/layers/convolution/SeparableConvolution2DLayer.java:160-246 / :60-152;
+ * libnd4j "sconv2d" / "sconv2d_bp"): wd is [depthMultiplier, nIn, kH, kW] 'c', u channel = ci*depthMultiplier + m
+ * (NN/nn/params/SeparableConvolutionParamInitializer.java). NHWC. The point-wise stage is dl4jb200_conv_fwd / conv_bwd with a
+ * 1x1 kernel on u: preOutput = depthwise_fwd -> conv_fwd(1x1, bias); backprop = conv_bwd(1x1) -> depthwise_bwd. d: c_in = nIn,
+ * geometry of the depth-wise kernel; c_out is ignored. */
+int dl4jb200_depthwise_fwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int depth_mult, const float *x, int x_cs, const float *wd,
+                           float *u, int u_cs);
+int dl4jb200_depthwise_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int depth_mult, const float *x, int x_cs, const float *wd,
+                           const float *du, int u_cs, float *dwd, float *dx, int dx_cs);
+
 /* ------------------------------------------------------------------ data-parallel exchange --- */
 /* The plug-in point for single-box data parallelism is GradientsAccumulator.storeUpdate / applyUpdate
  * (NN/optimize/solvers/accumulation/GradientsAccumulator.java:27-41), installed into every replica's optimizer by

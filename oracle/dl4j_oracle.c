@@ -598,3 +598,169 @@ void o_dense_bwd(const float *x, const float *wf, const float *delta, float *dwf
             }
     }
 }
+
+/* ---- Deconvolution2DLayer (nn/layers/convolution/Deconvolution2DLayer.java:145-233 forward, :48-138 backward). The layer
+ * delegates the arithmetic to libnd4j's "deconv2d" / "deconv2d_bp" custom ops (un-vendored; restated here from the
+ * published definition of a transposed convolution that those ops implement): W is [nIn, nOut, kH, kW] 'c'
+ * (params/DeconvolutionParamInitializer.java:75-80), output size s*(in-1) + kEff - 2p (util/ConvolutionUtils.java:79-80),
+ *   z[b,co,oh,ow] = bias[co] + sum_{ci,kh,kw} x[b,ci,ih,iw] * W[ci,co,kh,kw],  oh = ih*sH - pT + kh*dH (likewise ow)
+ * PARITY UNPINNED for these two ops: the reference holds no literal vectors for them (gradient checks only,
+ * gradientcheck/CNNGradientCheckTest.java); tests pin forward against backward by a numerical gradient check. */
+void o_deconv2d_fwd(const float *x, const float *w, const float *bias, float *z, int B, int nIn, int H, int W, int nOut,
+                    int kH, int kW, int sH, int sW, int pT, int pL, int dH, int dW, int Ho, int Wo)
+{
+    size_t zn = (size_t)B * nOut * Ho * Wo;
+    double *acc = (double *)calloc(zn, sizeof(double));
+#pragma omp parallel for schedule(static)
+    for (int b = 0; b < B; b++)
+        for (int ci = 0; ci < nIn; ci++)
+            for (int ih = 0; ih < H; ih++)
+                for (int iw = 0; iw < W; iw++) {
+                    double xv = x[(((size_t)b * nIn + ci) * H + ih) * W + iw];
+                    for (int co = 0; co < nOut; co++)
+                        for (int kh = 0; kh < kH; kh++) {
+                            int oh = ih * sH - pT + kh * dH;
+                            if (oh < 0 || oh >= Ho) continue;
+                            for (int kw = 0; kw < kW; kw++) {
+                                int ow = iw * sW - pL + kw * dW;
+                                if (ow < 0 || ow >= Wo) continue;
+                                acc[(((size_t)b * nOut + co) * Ho + oh) * Wo + ow] += xv * w[(((size_t)ci * nOut + co) * kH + kh) * kW + kw];
+                            }
+                        }
+                }
+    for (size_t i = 0; i < zn; i++) {
+        int co = (int)((i / ((size_t)Ho * Wo)) % nOut);
+        z[i] = (float)(acc[i] + (bias ? (double)bias[co] : 0.0));
+    }
+    free(acc);
+}
+
+/* dW[ci,co,kh,kw] = sum x[b,ci,ih,iw] * delta[b,co,oh,ow]; db[co] = sum delta; dx[b,ci,ih,iw] = sum delta[b,co,oh,ow] * W[ci,co,kh,kw] */
+void o_deconv2d_bwd(const float *x, const float *w, const float *delta, float *dw, float *db, float *dx, int B, int nIn,
+                    int H, int W, int nOut, int kH, int kW, int sH, int sW, int pT, int pL, int dH, int dW, int Ho, int Wo)
+{
+#pragma omp parallel for schedule(static)
+    for (int ci = 0; ci < nIn; ci++)
+        for (int co = 0; co < nOut; co++)
+            for (int kh = 0; kh < kH; kh++)
+                for (int kw = 0; kw < kW; kw++) {
+                    double a = 0.0;
+                    for (int b = 0; b < B; b++)
+                        for (int ih = 0; ih < H; ih++) {
+                            int oh = ih * sH - pT + kh * dH;
+                            if (oh < 0 || oh >= Ho) continue;
+                            for (int iw = 0; iw < W; iw++) {
+                                int ow = iw * sW - pL + kw * dW;
+                                if (ow < 0 || ow >= Wo) continue;
+                                a += (double)x[(((size_t)b * nIn + ci) * H + ih) * W + iw] *
+                                     (double)delta[(((size_t)b * nOut + co) * Ho + oh) * Wo + ow];
+                            }
+                        }
+                    dw[(((size_t)ci * nOut + co) * kH + kh) * kW + kw] = (float)a;
+                }
+    if (db)
+        for (int co = 0; co < nOut; co++) {
+            double a = 0.0;
+            for (int b = 0; b < B; b++)
+                for (int i = 0; i < Ho * Wo; i++) a += delta[((size_t)b * nOut + co) * Ho * Wo + i];
+            db[co] = (float)a;
+        }
+    if (dx) {
+#pragma omp parallel for schedule(static)
+        for (int b = 0; b < B; b++)
+            for (int ci = 0; ci < nIn; ci++)
+                for (int ih = 0; ih < H; ih++)
+                    for (int iw = 0; iw < W; iw++) {
+                        double a = 0.0;
+                        for (int co = 0; co < nOut; co++)
+                            for (int kh = 0; kh < kH; kh++) {
+                                int oh = ih * sH - pT + kh * dH;
+                                if (oh < 0 || oh >= Ho) continue;
+                                for (int kw = 0; kw < kW; kw++) {
+                                    int ow = iw * sW - pL + kw * dW;
+                                    if (ow < 0 || ow >= Wo) continue;
+                                    a += (double)delta[(((size_t)b * nOut + co) * Ho + oh) * Wo + ow] *
+                                         (double)w[(((size_t)ci * nOut + co) * kH + kh) * kW + kw];
+                                }
+                            }
+                        dx[(((size_t)b * nIn + ci) * H + ih) * W + iw] = (float)a;
+                    }
+    }
+}
+
+/* ---- SeparableConvolution2DLayer (nn/layers/convolution/SeparableConvolution2DLayer.java:160-246 forward, :60-152
+ * backward; libnd4j "sconv2d" / "sconv2d_bp", un-vendored, restated from their definition): depth-wise filter
+ * Wd [depthMultiplier, nIn, kH, kW], point-wise filter Wp [nOut, nIn*depthMultiplier, 1, 1]
+ * (params/SeparableConvolutionParamInitializer.java); intermediate channel index = ci * depthMultiplier + m.
+ *   u[b, ci*mult+m, oh, ow] = sum_{kh,kw} x[b,ci, oh*sH-pT+kh*dH, ow*sW-pL+kw*dW] * Wd[m,ci,kh,kw]
+ *   z[b, co, oh, ow]        = bias[co] + sum_j u[b,j,oh,ow] * Wp[co,j]                                  (unpinned, see above) */
+void o_depthwise_fwd(const float *x, const float *wd, float *u, int B, int C, int H, int W, int mult, int kH, int kW, int sH,
+                     int sW, int pT, int pL, int dH, int dW, int Ho, int Wo)
+{
+#pragma omp parallel for schedule(static)
+    for (int b = 0; b < B; b++)
+        for (int ci = 0; ci < C; ci++)
+            for (int m = 0; m < mult; m++)
+                for (int oh = 0; oh < Ho; oh++)
+                    for (int ow = 0; ow < Wo; ow++) {
+                        double a = 0.0;
+                        for (int kh = 0; kh < kH; kh++) {
+                            int ih = oh * sH - pT + kh * dH;
+                            if (ih < 0 || ih >= H) continue;
+                            for (int kw = 0; kw < kW; kw++) {
+                                int iw = ow * sW - pL + kw * dW;
+                                if (iw < 0 || iw >= W) continue;
+                                a += (double)x[(((size_t)b * C + ci) * H + ih) * W + iw] * (double)wd[(((size_t)m * C + ci) * kH + kh) * kW + kw];
+                            }
+                        }
+                        u[(((size_t)b * C * mult + ci * mult + m) * Ho + oh) * Wo + ow] = (float)a;
+                    }
+}
+
+/* du: epsilon w.r.t. u. dwd[m,ci,kh,kw] = sum x * du; dx[b,ci,ih,iw] = sum_m,kh,kw du[b,ci*mult+m,oh,ow] * Wd[m,ci,kh,kw] */
+void o_depthwise_bwd(const float *x, const float *wd, const float *du, float *dwd, float *dx, int B, int C, int H, int W,
+                     int mult, int kH, int kW, int sH, int sW, int pT, int pL, int dH, int dW, int Ho, int Wo)
+{
+#pragma omp parallel for schedule(static)
+    for (int ci = 0; ci < C; ci++)
+        for (int m = 0; m < mult; m++)
+            for (int kh = 0; kh < kH; kh++)
+                for (int kw = 0; kw < kW; kw++) {
+                    double a = 0.0;
+                    for (int b = 0; b < B; b++)
+                        for (int oh = 0; oh < Ho; oh++) {
+                            int ih = oh * sH - pT + kh * dH;
+                            if (ih < 0 || ih >= H) continue;
+                            for (int ow = 0; ow < Wo; ow++) {
+                                int iw = ow * sW - pL + kw * dW;
+                                if (iw < 0 || iw >= W) continue;
+                                a += (double)x[(((size_t)b * C + ci) * H + ih) * W + iw] *
+                                     (double)du[(((size_t)b * C * mult + ci * mult + m) * Ho + oh) * Wo + ow];
+                            }
+                        }
+                    dwd[(((size_t)m * C + ci) * kH + kh) * kW + kw] = (float)a;
+                }
+    if (dx) {
+        size_t n = (size_t)B * C * H * W;
+        double *acc = (double *)calloc(n, sizeof(double));
+#pragma omp parallel for schedule(static)
+        for (int b = 0; b < B; b++)
+            for (int ci = 0; ci < C; ci++)
+                for (int m = 0; m < mult; m++)
+                    for (int oh = 0; oh < Ho; oh++)
+                        for (int ow = 0; ow < Wo; ow++) {
+                            double g = du[(((size_t)b * C * mult + ci * mult + m) * Ho + oh) * Wo + ow];
+                            for (int kh = 0; kh < kH; kh++) {
+                                int ih = oh * sH - pT + kh * dH;
+                                if (ih < 0 || ih >= H) continue;
+                                for (int kw = 0; kw < kW; kw++) {
+                                    int iw = ow * sW - pL + kw * dW;
+                                    if (iw < 0 || iw >= W) continue;
+                                    acc[(((size_t)b * C + ci) * H + ih) * W + iw] += g * (double)wd[(((size_t)m * C + ci) * kH + kh) * kW + kw];
+                                }
+                            }
+                        }
+        for (size_t i = 0; i < n; i++) dx[i] = (float)acc[i];
+        free(acc);
+    }
+}

@@ -276,3 +276,71 @@ def dense_bwd(x, wf, delta, need_dx=True):
     dx = np.empty_like(x) if need_dx else None
     lib().o_dense_bwd(_p(x), _p(wf), _p(delta), _p(dwf), _p(db), _p(dx), B, nIn, nOut)
     return dwf, db, dx
+
+
+def deconv_out_size(inp, k, s, p, d=1, mode=TRUNCATE):
+    """ConvolutionUtils.getDeconvolutionOutputSize (util/ConvolutionUtils.java:63-83); Same mode is refused by the layer's
+    forward pass (Deconvolution2DLayer.java:147-149)."""
+    ke = k + (k - 1) * (d - 1)
+    if mode == SAME:
+        return s * inp
+    return s * (inp - 1) + ke - 2 * p
+
+
+def deconv2d_fwd(x, w, b, stride=(1, 1), pad=(0, 0), dilation=(1, 1)):
+    """w: [nIn, nOut, kH, kW]."""
+    x, w = _f(x), _f(w)
+    B, nIn, H, W = x.shape
+    _, nOut, kH, kW = w.shape
+    Ho, Wo = deconv_out_size(H, kH, stride[0], pad[0], dilation[0]), deconv_out_size(W, kW, stride[1], pad[1], dilation[1])
+    z = np.empty((B, nOut, Ho, Wo), np.float32)
+    lib().o_deconv2d_fwd(_p(x), _p(w), _p(None if b is None else _f(b).reshape(-1)), _p(z), B, nIn, H, W, nOut, kH, kW, stride[0],
+                         stride[1], pad[0], pad[1], dilation[0], dilation[1], Ho, Wo)
+    return z
+
+
+def deconv2d_bwd(x, w, delta, stride=(1, 1), pad=(0, 0), dilation=(1, 1)):
+    x, w, delta = _f(x), _f(w), _f(delta)
+    B, nIn, H, W = x.shape
+    _, nOut, kH, kW = w.shape
+    Ho, Wo = delta.shape[2:]
+    dw, db, dx = np.empty_like(w), np.empty(nOut, np.float32), np.empty_like(x)
+    lib().o_deconv2d_bwd(_p(x), _p(w), _p(delta), _p(dw), _p(db), _p(dx), B, nIn, H, W, nOut, kH, kW, stride[0], stride[1], pad[0],
+                         pad[1], dilation[0], dilation[1], Ho, Wo)
+    return dw, db, dx
+
+
+def depthwise_fwd(x, wd, stride=(1, 1), pad=(0, 0), dilation=(1, 1), mode=TRUNCATE):
+    """wd: [depthMultiplier, nIn, kH, kW] -> u [B, nIn*mult, Ho, Wo] (channel ci*mult + m)."""
+    x, wd = _f(x), _f(wd)
+    B, Cc, H, W = x.shape
+    mult, _, kH, kW = wd.shape
+    Ho, Wo, pT, pL = conv_geometry(H, W, (kH, kW), stride, pad, dilation, mode)
+    u = np.empty((B, Cc * mult, Ho, Wo), np.float32)
+    lib().o_depthwise_fwd(_p(x), _p(wd), _p(u), B, Cc, H, W, mult, kH, kW, stride[0], stride[1], pT, pL, dilation[0], dilation[1], Ho, Wo)
+    return u
+
+
+def depthwise_bwd(x, wd, du, stride=(1, 1), pad=(0, 0), dilation=(1, 1), mode=TRUNCATE):
+    x, wd, du = _f(x), _f(wd), _f(du)
+    B, Cc, H, W = x.shape
+    mult, _, kH, kW = wd.shape
+    Ho, Wo, pT, pL = conv_geometry(H, W, (kH, kW), stride, pad, dilation, mode)
+    dwd, dx = np.empty_like(wd), np.empty_like(x)
+    lib().o_depthwise_bwd(_p(x), _p(wd), _p(du), _p(dwd), _p(dx), B, Cc, H, W, mult, kH, kW, stride[0], stride[1], pT, pL,
+                          dilation[0], dilation[1], Ho, Wo)
+    return dwd, dx
+
+
+def sepconv2d_fwd(x, wd, wp, b, stride=(1, 1), pad=(0, 0), dilation=(1, 1), mode=TRUNCATE):
+    """SeparableConvolution2DLayer.preOutput: depth-wise then point-wise (wp: [nOut, nIn*mult, 1, 1]) + bias."""
+    u = depthwise_fwd(x, wd, stride, pad, dilation, mode)
+    return conv_fwd(u, wp, b), u
+
+
+def sepconv2d_bwd(x, wd, wp, delta, stride=(1, 1), pad=(0, 0), dilation=(1, 1), mode=TRUNCATE):
+    """-> (dWd, dWp, db, dx)."""
+    u = depthwise_fwd(x, wd, stride, pad, dilation, mode)
+    dwp, db, du = conv_bwd(u, wp, delta)
+    dwd, dx = depthwise_bwd(x, wd, du, stride, pad, dilation, mode)
+    return dwd, dwp, db, dx

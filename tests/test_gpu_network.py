@@ -363,3 +363,32 @@ def test_simplecnn_forward_parity(algo_name):
                 assert rel_err(p[off:off + k], ref.params[off:off + k]) <= tol, (name, key)
     finally:
         net.close()
+
+
+def test_checkpoint_round_trip_resumes_training_bit_identically(tmp_path):
+    """ModelSerializer-layout checkpoint (coefficients.bin + updaterState.bin) written after one step and restored into a
+    fresh network: the second step gives bit-identical parameters to the uninterrupted run."""
+    import torch
+    from deeplearning4j_b200 import network, zoo
+    m = _tiny_resnet()
+    p0 = zoo.init_params(m)
+    x, lab = _data(m, 8, 10)
+    a = network.Network(m, 8, params=p0)
+    b = network.Network(m, 8, params=p0)
+    try:
+        a.fit(x, lab)
+        a.fit(x, lab)
+        a.sync()
+        b.fit(x, lab)
+        b.save_checkpoint(tmp_path / "ckpt.zip", "{}")
+        c = network.Network(m, 8, params=p0)
+        try:
+            c.load_checkpoint(tmp_path / "ckpt.zip")
+            c.fit(x, lab)
+            c.sync()
+            assert torch.equal(c.params, a.params) and torch.equal(c.state, a.state)
+        finally:
+            c.close()
+    finally:
+        a.close()
+        b.close()
