@@ -366,8 +366,9 @@ def main():
     if use_graph:
         net.release_graph()
     net.overlap_wgrad = False  # one stream: every call is timed alone (in the timed regions above the filter gradients overlap the backward chain)
-    net.profile(["dl4jb200_conv_fwd", "dl4jb200_conv_fwd_bnstats", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_wgrad",
-                 "dl4jb200_conv_rowpack_fwd_bnstats", "dl4jb200_bn_fwd", "dl4jb200_bn_fwd_prestats", "dl4jb200_bn_bwd", "dl4jb200_pool_fwd", "dl4jb200_pool_bwd"])
+    net.profile(["dl4jb200_conv_fwd", "dl4jb200_conv_fwd_bnstats", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_bwd_data_bnstats",
+                 "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_wgrad", "dl4jb200_conv_rowpack_fwd_bnstats", "dl4jb200_bn_fwd",
+                 "dl4jb200_bn_fwd_prestats", "dl4jb200_bn_bwd", "dl4jb200_bn_bwd_prestats", "dl4jb200_pool_fwd", "dl4jb200_pool_bwd"])
     psteps = min(args.steps, 10)
     step()  # untimed: lets the single-stream variant size its scratch
     barrier()
@@ -411,8 +412,8 @@ def main():
     conv_ms = conv_fl = 0.0
     n_conv_calls = 0
     per_layer = {}
-    conv_fns = ("dl4jb200_conv_fwd", "dl4jb200_conv_fwd_bnstats", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_rowpack_fwd",
-                "dl4jb200_conv_rowpack_fwd_bnstats", "dl4jb200_conv_rowpack_wgrad")
+    conv_fns = ("dl4jb200_conv_fwd", "dl4jb200_conv_fwd_bnstats", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_bwd_data_bnstats",
+                "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_fwd_bnstats", "dl4jb200_conv_rowpack_wgrad")
     passes = {}  # (layer, "fwd"|"bwd") -> [ms over psteps, calls]: a layer's backward is several calls (filter / data gradient)
     for (fn, tag), times in prof.items():
         if fn in conv_fns and tag in fl:
@@ -449,7 +450,7 @@ def main():
     # ---- HBM kernels (BN / pool): achieved GB/s on algorithmic bytes
     bw = {}
     # (with the statistics taken in the convolution epilogue the forward is finalize + apply only: same 8 algorithmic B/elem)
-    for key, fns, bpe in (("bn_fwd", ("dl4jb200_bn_fwd", "dl4jb200_bn_fwd_prestats"), 8), ("bn_bwd", ("dl4jb200_bn_bwd",), 12)):
+    for key, fns, bpe in (("bn_fwd", ("dl4jb200_bn_fwd", "dl4jb200_bn_fwd_prestats"), 8), ("bn_bwd", ("dl4jb200_bn_bwd", "dl4jb200_bn_bwd_prestats"), 12)):
         tot_ms = tot_b = 0.0
         for (f2, tag), times in prof.items():
             if f2 in fns:

@@ -109,6 +109,9 @@ PROTOTYPES = {
     "dl4jb200_copy2d": [_vp, _vp, _i, _vp, _i, _i, _i],
     "dl4jb200_grad_normalize": [_vp, _vp, _sz, _i, _d],
     "dl4jb200_updater_apply_segments": [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _vp, _i, _d, _vp],
+    "dl4jb200_conv_bwd_data_bnstats_rows": [_vp, _desc_p, _i, _i, _i, C.POINTER(C.c_int)],
+    "dl4jb200_conv_bwd_data_bnstats": [_vp, _desc_p, _vp, _vp, _i, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp],
+    "dl4jb200_bn_bwd_prestats": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _i],
     "dl4jb200_deconv2d_fwd": [_vp, _desc_p, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i],
     "dl4jb200_deconv2d_bwd": [_vp, _desc_p, _vp, _i, _i, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i],
     "dl4jb200_bias_act": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i],

@@ -530,6 +530,30 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
     return DL4JB200_OK;
 }
 
+// Backward on sums a producer already took (dl4jb200_conv_bwd_data_bnstats): finalize + apply only.
+int dl4jb200_bn_bwd_prestats(dl4jb200_ctx *ctx, const float *x, const float *eps, const float *gamma, const float *beta,
+                             const float *save_mean, const float *save_std, int act, float *dx, float *dgamma, float *dbeta, int B,
+                             int C, int H, int W, int cs, const float *stat_partial, int stat_rows) {
+    DL4J_REQUIRE(ctx && x && eps && save_mean && save_std && dx && stat_partial, "bn_bwd_prestats: NULL argument");
+    DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && stat_rows > 0, "bn_bwd_prestats: bad shape");
+    DL4J_REQUIRE((long long)B * H * W < (1LL << 31), "bn_bwd_prestats: B*H*W must stay below 2^31");
+    DL4J_REQUIRE(cs == C && cs % 4 == 0 && al16(x) && al16(eps) && al16(dx), "bn_bwd_prestats: NHWC with cs == C, cs %% 4 == 0, 16-byte aligned tensors");
+    DL4J_REQUIRE(act == DL4JB200_ACT_IDENTITY || act == DL4JB200_ACT_RELU, "bn_bwd_prestats: only IDENTITY / RELU can be fused (got %d)", act);
+    float *coef = (float *)dl4j_workspace(ctx, 0, 5 * (size_t)cs * sizeof(float));
+    if (!coef) return DL4JB200_ERR_CUDA;
+    const long long M = (long long)B * H * W;
+    const size_t total = (size_t)M * cs;
+    const bool relu = act == DL4JB200_ACT_RELU;
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_bwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, 32), 0, ctx->stream, stat_partial, stat_rows, gamma,
+                                  save_mean, save_std, relu ? beta : nullptr, dgamma, dbeta, coef, C, cs, (double)M));
+    DL4J_CHECK_LAUNCH();
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_apply_nhwc<1>, dim3(bn_grid(ctx, total / 4)), dim3(256), 0, ctx->stream, x, eps,
+                                  relu ? (const float *)(coef + 4 * (size_t)cs) : (const float *)nullptr, dx, (const float *)coef, total / 4, cs,
+                                  ctx->round_act << 8));
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------------------

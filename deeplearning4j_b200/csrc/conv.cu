@@ -733,4 +733,61 @@ int dl4jb200_conv_bwd_data_fused(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d,
     return conv_tc_gemm(ctx, gb, delta, wq, rows_b, nullptr, dx, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY | (ctx->round_act ? 0x100 : 0));
 }
 
+// Backprop-data (optionally with the fused fan-in sum / ReLU backprop of conv_bwd_data_fused) whose epilogue also takes the
+// backward sums of the BatchNormalization that owns dx -- directly (dx is that layer's epsilon) or through the Add vertex
+// the layer is folded into. The BatchNormalization's backward then needs no pass of its own over (x, eps) for the sums.
+static int bwd_bnstats_geom(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int delta_cs, int dx_cs, int algo, ConvGeom &gb, int &rows_b) {
+    gb = conv_geom_bwd_data(d, delta_cs);
+    const bool strided_1x1 = d->k_h == 1 && d->k_w == 1 && (d->stride_h > 1 || d->stride_w > 1);
+    gb.use_tma = algo == DL4JB200_CONV_ALGO_TC_TF32 && !strided_1x1 && delta_cs >= gb.Cg && conv_tc_gemm_can_tma(gb);
+    rows_b = dl4j_round_up(dx_cs > d->c_in ? dx_cs : d->c_in, 256);
+    return conv_tc_bst_rows(ctx, gb, rows_b, d->c_in, dx_cs);
+}
+
+int dl4jb200_conv_bwd_data_bnstats_rows(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int delta_cs, int dx_cs, int algo, int *rows_out) {
+    DL4J_REQUIRE(ctx && rows_out, "conv_bwd_data_bnstats_rows: NULL argument");
+    int rc = check_desc(d, "conv_bwd_data_bnstats_rows");
+    if (rc) return rc;
+    ConvGeom g;
+    int rows_b;
+    *rows_out = (delta_cs % 4 == 0 && dx_cs % 4 == 0) ? bwd_bnstats_geom(ctx, d, delta_cs, dx_cs, algo, g, rows_b) : 0;
+    return DL4JB200_OK;
+}
+
+int dl4jb200_conv_bwd_data_bnstats(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *w, const float *delta, int delta_cs,
+                                   float *dx, int dx_cs, const float *eps_sum, const float *act_out, int act, int algo,
+                                   const float *bn_x, const float *bn_gamma, const float *bn_beta, const float *bn_mean,
+                                   const float *bn_std, int bn_relu, float *stat_partial) {
+    DL4J_REQUIRE(ctx && w && delta && dx && bn_x && bn_mean && bn_std && stat_partial, "conv_bwd_data_bnstats: NULL argument");
+    DL4J_REQUIRE(act == DL4JB200_ACT_IDENTITY || act == DL4JB200_ACT_RELU, "conv_bwd_data_bnstats: only identity / relu masks");
+    DL4J_REQUIRE(act == DL4JB200_ACT_IDENTITY || act_out, "conv_bwd_data_bnstats: relu needs act_out");
+    int rc = check_desc(d, "conv_bwd_data_bnstats");
+    if (rc) return rc;
+    if ((rc = check_layout(DL4JB200_NHWC, delta_cs, d->c_out, delta, "conv_bwd_data_bnstats", "delta"))) return rc;
+    if ((rc = check_layout(DL4JB200_NHWC, dx_cs, d->c_in, dx, "conv_bwd_data_bnstats", "dx"))) return rc;
+    auto al = [](const void *p) { return !p || ((uintptr_t)p & 15) == 0; };
+    DL4J_REQUIRE(al(bn_x) && al(bn_gamma) && al(bn_beta) && al(bn_mean) && al(bn_std) && al(stat_partial) && al(eps_sum) && al(act_out),
+                 "conv_bwd_data_bnstats: every tensor / per-channel array must be 16-byte aligned");
+    ConvGeom gb;
+    int rows_b;
+    if (bwd_bnstats_geom(ctx, d, delta_cs, dx_cs, algo, gb, rows_b) <= 0) {
+        dl4j_set_error("conv_bwd_data_bnstats: this backprop-data cannot carry the sums (see conv_bwd_data_bnstats_rows)");
+        return DL4JB200_NOT_SUPPORTED;
+    }
+    const size_t pack_f = (size_t)rows_b * gb.Kp;
+    const float *wq = filters_lookup(ctx, w, true, gb.Cg, gb.Kp, rows_b, 1, 1);
+    if (!wq) {
+        float *wb = (float *)dl4j_workspace(ctx, 0, pack_f * sizeof(float));
+        if (!wb) return DL4JB200_ERR_CUDA;
+        k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, rows_b, 1, 1, 1);
+        DL4J_CHECK_LAUNCH();
+        wq = wb;
+    }
+    gb.epi_add = eps_sum;
+    gb.epi_mask = act == DL4JB200_ACT_RELU ? act_out : nullptr;
+    gb.stat_out = stat_partial;
+    gb.bst_x = bn_x; gb.bst_mean = bn_mean; gb.bst_std = bn_std; gb.bst_gamma = bn_gamma; gb.bst_beta = bn_beta; gb.bst_relu = bn_relu ? 1 : 0;
+    return conv_tc_gemm(ctx, gb, delta, wq, rows_b, nullptr, dx, d->c_in, dx_cs, DL4JB200_ACT_IDENTITY | (ctx->round_act ? 0x100 : 0));
+}
+
 }  // extern "C"

@@ -23,6 +23,9 @@ struct ConvGeom {
     const float *epi_add = nullptr, *epi_mask = nullptr;
     float *stat_out = nullptr;          // batch-norm statistics of the output (see TmaGemmGeom)
     const float *stat_pivot = nullptr;
+    // backward batch-norm sums of the vertex that owns the output of a backprop-data GEMM (see TmaGemmGeom)
+    const float *bst_x = nullptr, *bst_mean = nullptr, *bst_std = nullptr, *bst_gamma = nullptr, *bst_beta = nullptr;
+    int bst_relu = 0;
 };
 
 // tap/channel of a K index (k % 4 == 0 in all callers)
@@ -100,6 +103,7 @@ int conv_ffma_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const 
 int conv_tc_gemm(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
                  const float *bias, float *out, int n_valid, int out_cs, int act);
 int conv_tc_stat_rows(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, int n_valid, int out_cs);
+int conv_tc_bst_rows(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, int n_valid, int out_cs);
 int conv_tc_wgrad(dl4jb200_ctx *ctx, const ConvGeom &g, const float *x, const float *delta, int delta_cs, int c_out,
                   float *partial, int rows_p, int splits, float *db_partial = nullptr);
 int conv_tc_wgrad_splits(dl4jb200_ctx *ctx, const ConvGeom &g, int c_out);

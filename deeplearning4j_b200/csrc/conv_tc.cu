@@ -214,6 +214,72 @@ __device__ __forceinline__ void store_tile_32x32_stats(uint32_t stage_smem, cons
     }
 }
 
+// Backprop-data epilogue that also takes the BACKWARD batch-norm sums of the layer that owns `out` (TmaGemmGeom::bst_*):
+// t = (mask > 0 ? t + add : 0) when the fused fan-in / ReLU-backprop operands are given, stored (rounded to TF32 if asked),
+// then with x = bx[...]: xm = x - mean, e' = (relu && !(xm*a + beta > 0)) ? 0 : t, s1 += e', s2 += e' * xm for the lane's
+// four columns. Rows are handled in two batches of four so that at most twelve 128-bit loads are in flight per lane.
+__device__ __forceinline__ void store_tile_32x32_bst(uint32_t stage_smem, const float (&v)[32], int lane, size_t off_base,
+                                                     size_t row_stride, int rows_valid, float *out,
+                                                     const float *__restrict__ add, const float *__restrict__ mask, int rnd,
+                                                     const float *__restrict__ bx, const float4 &mean, const float4 &a,
+                                                     const float4 &beta, int relu, float4 &s1, float4 &s2) {
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        const uint32_t sa = stage_smem + (uint32_t)lane * 128u + (uint32_t)((q ^ (lane & 7)) << 4);
+        asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(sa), "f"(v[q * 4]), "f"(v[q * 4 + 1]), "f"(v[q * 4 + 2]),
+                     "f"(v[q * 4 + 3]) : "memory");
+    }
+    __syncwarp();
+    const int c = lane & 7;
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        float4 ad[4], mk[4], xs[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int row = 4 * (half * 4 + i) + (lane >> 3);
+            const size_t o = off_base + (size_t)row * row_stride + c * 4;
+            ad[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            mk[i] = make_float4(1.f, 1.f, 1.f, 1.f);
+            xs[i] = ad[i];
+            if (row < rows_valid) {
+                xs[i] = __ldg(reinterpret_cast<const float4 *>(bx + o));
+                if (add) ad[i] = *reinterpret_cast<const float4 *>(add + o);
+                if (mask) mk[i] = __ldg(reinterpret_cast<const float4 *>(mask + o));
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) {  // keep every consumer behind all the loads of the batch (see store_tile_32x32_fused)
+            asm volatile("" : "+f"(mk[i].x), "+f"(mk[i].y), "+f"(mk[i].z), "+f"(mk[i].w));
+            asm volatile("" : "+f"(ad[i].x), "+f"(ad[i].y), "+f"(ad[i].z), "+f"(ad[i].w));
+            asm volatile("" : "+f"(xs[i].x), "+f"(xs[i].y), "+f"(xs[i].z), "+f"(xs[i].w));
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int row = 4 * (half * 4 + i) + (lane >> 3);
+            float4 t;
+            const uint32_t sa = stage_smem + (uint32_t)row * 128u + (uint32_t)((c ^ (row & 7)) << 4);
+            asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(sa));
+            if (add || mask) {
+                t.x = mk[i].x > 0.f ? t.x + ad[i].x : 0.f; t.y = mk[i].y > 0.f ? t.y + ad[i].y : 0.f;
+                t.z = mk[i].z > 0.f ? t.z + ad[i].z : 0.f; t.w = mk[i].w > 0.f ? t.w + ad[i].w : 0.f;
+            }
+            t = dl4j_rnd4(t, rnd);  // the sums are taken of what is stored: what a separate pass would have read back
+            if (row < rows_valid) {
+                *reinterpret_cast<float4 *>(out + off_base + (size_t)row * row_stride + c * 4) = t;
+                float4 xm = xs[i];
+                xm.x -= mean.x; xm.y -= mean.y; xm.z -= mean.z; xm.w -= mean.w;
+                if (relu) {
+                    t.x = xm.x * a.x + beta.x > 0.f ? t.x : 0.f; t.y = xm.y * a.y + beta.y > 0.f ? t.y : 0.f;
+                    t.z = xm.z * a.z + beta.z > 0.f ? t.z : 0.f; t.w = xm.w * a.w + beta.w > 0.f ? t.w : 0.f;
+                }
+                s1.x += t.x; s1.y += t.y; s1.z += t.z; s1.w += t.w;
+                s2.x += t.x * xm.x; s2.y += t.y * xm.y; s2.z += t.z * xm.z; s2.w += t.w * xm.w;
+            }
+        }
+    }
+}
+
 // Same, but every row has its own destination (element offset from `out`, or < 0 to skip): output-row scatter.
 __device__ __forceinline__ void store_tile_32x32_rows(uint32_t stage_smem, const float (&v)[32], int lane, float *out,
                                                       const long long (&rowoff)[8], int col0) {
@@ -684,7 +750,8 @@ struct PersistSmem {
     static constexpr int BYTES = BAR_OFF + 256 + 1024;
 };
 
-template <int BN, int STAGES, bool REMAP, bool STATS = false>
+// STATS: 0 none, 1 forward batch-norm statistics of the output, 2 backward batch-norm sums (TmaGemmGeom::bst_*)
+template <int BN, int STAGES, bool REMAP, int STATS = 0>
 __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const __grid_constant__ CUtensorMap tmA,
                                                                           const __grid_constant__ CUtensorMap tmB,
                                                                           const float *__restrict__ bias,
@@ -694,7 +761,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
     using L = PersistSmem<BN, STAGES>;
     const int rnd = act >> 8;
     act &= 0xff;
-    const bool fused = !REMAP && (g.epi_add != nullptr || g.epi_mask != nullptr);
+    const bool fused = !REMAP && STATS != 2 && (g.epi_add != nullptr || g.epi_mask != nullptr);
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
@@ -795,15 +862,35 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
         // gridDim.x is a multiple of n_tiles: every tile of this CTA then has the same column range and the sums stay in
         // registers until the single flush after the tile loop.
         constexpr int NCH = STATS ? (BN / 32 + 1) / 2 : 1;
+        constexpr int NCH2 = STATS == 2 ? NCH : 1;
         float4 st_s[NCH], st_q[NCH], st_k[NCH];
+        float4 st_a[NCH2], st_b[NCH2];  // STATS == 2: gamma / std and beta of the gate; st_k holds the saved mean
         if (STATS) {
 #pragma unroll
             for (int j = 0; j < NCH; j++) {
                 st_s[j] = make_float4(0.f, 0.f, 0.f, 0.f);
                 st_q[j] = st_s[j];
                 const int cb = grp + 2 * j;
-                st_k[j] = cb < BN / 32 ? __ldg(reinterpret_cast<const float4 *>(g.stat_pivot + ((int)blockIdx.x % n_tiles) * BN + cb * 32) + (lane & 7))
-                                       : st_s[j];
+                const int col = ((int)blockIdx.x % n_tiles) * BN + cb * 32;
+                if constexpr (STATS == 1) {
+                    st_k[j] = cb < BN / 32 ? __ldg(reinterpret_cast<const float4 *>(g.stat_pivot + col) + (lane & 7)) : st_s[j];
+                } else if constexpr (STATS == 2) {
+                    st_k[j] = st_s[j];
+                    st_a[j] = st_s[j];
+                    st_b[j] = st_s[j];
+                    if (cb < BN / 32) {
+                        const int c4 = col + (lane & 7) * 4;
+                        st_k[j] = __ldg(reinterpret_cast<const float4 *>(g.bst_mean + c4));
+                        if (g.bst_relu) {  // identical to bn_mask_coef (bn.cu): (float)(gamma / std) in double, beta as is
+                            const float4 sd = __ldg(reinterpret_cast<const float4 *>(g.bst_std + c4));
+                            float4 gm = make_float4(1.f, 1.f, 1.f, 1.f);
+                            if (g.bst_gamma) gm = __ldg(reinterpret_cast<const float4 *>(g.bst_gamma + c4));
+                            st_a[j] = make_float4((float)((double)gm.x / (double)sd.x), (float)((double)gm.y / (double)sd.y),
+                                                  (float)((double)gm.z / (double)sd.z), (float)((double)gm.w / (double)sd.w));
+                            if (g.bst_beta) st_b[j] = __ldg(reinterpret_cast<const float4 *>(g.bst_beta + c4));
+                        }
+                    }
+                }
             }
         }
         int i = 0;
@@ -850,7 +937,24 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                 continue;
             }
             const int cb_last = NCB == 1 ? 0 : ((NCB - 1 - grp) & ~1) + grp;  // last chunk of this group's parity
-            if (STATS) {  // identity activation, whole tiles only (checked on the host); chunk loop unrolled: static accumulators
+            if constexpr (STATS == 2) {  // backprop-data + backward batch-norm sums; whole tiles only (checked on the host)
+#pragma unroll
+                for (int j = 0; j < NCH; j++) {
+                    const int cb = grp + 2 * j;
+                    if (cb < NCB) {
+                        float v[32];
+                        tmem_ld32(acc + (uint32_t)(cb * 32), v);
+                        if (cb == cb_last) {
+                            tc_fence_before();
+                            mbar_arrive(tempty_bar(buf));
+                        }
+                        store_tile_32x32_bst(stage_smem, v, lane, (size_t)(m0 + quad * 32) * out_cs + n0 + cb * 32, (size_t)out_cs, rows_valid, out,
+                                             g.epi_add, g.epi_mask, rnd, g.bst_x, st_k[j], st_a[j], st_b[j], g.bst_relu, st_s[j], st_q[j]);
+                    }
+                }
+                continue;
+            }
+            if constexpr (STATS == 1) {  // identity activation, whole tiles only (checked on the host); chunk loop unrolled: static accumulators
 #pragma unroll
                 for (int j = 0; j < NCH; j++) {
                     const int cb = grp + 2 * j;
@@ -1022,10 +1126,31 @@ static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, co
     const int n_tiles = dl4j_ceil_div(out_cs, BN), total = dl4j_ceil_div(g.M, BLOCK_M) * n_tiles;
     int grid = total < ctx->sm_count ? total : ctx->sm_count;
     if (n_tiles > 1 && g.num_k <= STAGES && grid >= 2 * n_tiles) grid = grid / n_tiles * n_tiles;  // enables the B-resident mode
+    if (g.stat_out && g.bst_x) {  // backward batch-norm sums in a backprop-data epilogue
+        if constexpr (BN == 64 || BN == 128) {
+            static bool configured_b[16] = {false};
+            if (!configured_b[ctx->device & 15]) {
+                DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+                configured_b[ctx->device & 15] = true;
+            }
+            const int gs = persist_stat_grid(ctx->sm_count, total, n_tiles);
+            if (g.remap || gs <= 0 || n_valid % BN != 0 || out_cs != n_valid || (act & 0xff) != DL4JB200_ACT_IDENTITY || bias) {
+                dl4j_set_error("conv_tc_gemm_tma: this launch cannot carry the backward batch-norm sums");
+                return DL4JB200_ERR_INVALID_ARG;
+            }
+            DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, false, 2>, dim3(gs), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB,
+                                          bias, out, g, n_valid, out_cs, act, n_tiles, total));
+            DL4J_CHECK_LAUNCH();
+            return DL4JB200_OK;
+        } else {
+            dl4j_set_error("conv_tc_gemm_tma: backward batch-norm sums need 64- or 128-wide tiles");
+            return DL4JB200_ERR_INVALID_ARG;
+        }
+    }
     if (g.stat_out) {  // batch-norm statistics in the epilogue: grid a multiple of n_tiles (see the kernel)
         static bool configured_s[16] = {false};
         if (!configured_s[ctx->device & 15]) {
-            DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+            DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
             configured_s[ctx->device & 15] = true;
         }
         const int gs = persist_stat_grid(ctx->sm_count, total, n_tiles);
@@ -1033,7 +1158,7 @@ static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, co
             dl4j_set_error("conv_tc_gemm_tma: this launch cannot carry batch-norm statistics");
             return DL4JB200_ERR_INVALID_ARG;
         }
-        DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, false, true>, dim3(gs), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB,
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, false, 1>, dim3(gs), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB,
                                       bias, out, g, n_valid, out_cs, act & 0xff, n_tiles, total));
         DL4J_CHECK_LAUNCH();
         return DL4JB200_OK;
@@ -1284,7 +1409,8 @@ bool conv_tc_gemm_can_tma(const ConvGeom &g) {
 // N-tile width of the TMA GEMM: 256-wide tiles (one UMMA of N=256, the whole TMEM as a double-buffered accumulator) when the
 // layer is wide and there are still at least ~2 tiles per SM
 static int tma_gemm_bn(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, int out_cs, bool aligned_bias) {
-    const bool can256 = aligned_bias && out_cs >= 256 && n_rows_packed % 256 == 0 && g.Kp >= 256;
+    // (the backward batch-norm sums keep five per-column values per lane and chunk in registers: 128-wide tiles at most)
+    const bool can256 = aligned_bias && out_cs >= 256 && n_rows_packed % 256 == 0 && g.Kp >= 256 && !g.bst_x;
     const long long m_tiles = dl4j_ceil_div(g.M, tc::BLOCK_M);
     const int narrow = out_cs > 64 ? 128 : (out_cs > 32 ? 64 : 32);
     if (can256 && g.Kp >= 512) {
@@ -1310,6 +1436,17 @@ int conv_tc_stat_rows(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, i
     return tc::persist_stat_rows(tc::persist_stat_grid(ctx->sm_count, total, n_tiles), n_tiles, bn);
 }
 
+// partial rows a backprop-data launch carrying the backward batch-norm sums writes (0: it cannot carry them)
+int conv_tc_bst_rows(dl4jb200_ctx *ctx, const ConvGeom &g0, int n_rows_packed, int n_valid, int out_cs) {
+    if (!g0.use_tma || g0.remap) return 0;
+    ConvGeom g = g0;
+    g.bst_x = reinterpret_cast<const float *>(16);  // any non-null value: selects the narrow tile widths
+    const int bn = tma_gemm_bn(ctx, g, n_rows_packed, out_cs, true);
+    if (bn < 64 || n_valid % bn != 0 || out_cs != n_valid) return 0;
+    const int n_tiles = out_cs / bn, total = dl4j_ceil_div(g.M, tc::BLOCK_M) * n_tiles;
+    return tc::persist_stat_rows(tc::persist_stat_grid(ctx->sm_count, total, n_tiles), n_tiles, bn);
+}
+
 static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
                             const float *bias, float *out, int n_valid, int out_cs, int act) {
     // backprop-data runs as a forward walk over delta with flipped taps (the filter is packed flipped, conv.cu)
@@ -1329,7 +1466,13 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
     t.remap = g.remap; t.rm_sy = g.rm_sy; t.rm_sx = g.rm_sx; t.rm_H = g.rm_H; t.rm_W = g.rm_W;
     t.epi_add = g.epi_add; t.epi_mask = g.epi_mask;
     t.stat_out = g.stat_out; t.stat_pivot = g.stat_pivot;
+    t.bst_x = g.bst_x; t.bst_mean = g.bst_mean; t.bst_std = g.bst_std; t.bst_gamma = g.bst_gamma; t.bst_beta = g.bst_beta;
+    t.bst_relu = g.bst_relu;
     if (g.stat_out && !aligned_bias) { dl4j_set_error("conv_tc_gemm_tma: statistics need a 16-byte aligned bias"); return DL4JB200_ERR_INVALID_ARG; }
+    if (g.bst_x && (!g.stat_out || g.remap || bias)) {
+        dl4j_set_error("conv_tc_gemm_tma: backward batch-norm sums need a stat buffer, no bias and no row scatter");
+        return DL4JB200_ERR_INVALID_ARG;
+    }
     if ((g.epi_add || g.epi_mask) && (g.remap || !aligned_bias)) {
         dl4j_set_error("conv_tc_gemm_tma: fused epilogue needs the unscattered persistent kernel");
         return DL4JB200_ERR_INVALID_ARG;

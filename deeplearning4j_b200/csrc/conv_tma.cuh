@@ -52,6 +52,15 @@ struct TmaGemmGeom {
     // rows = gridDim.x / n_tiles (x 4 for 32-wide tiles), row pitch 2 * out_cs floats (the layout k_bn_finalize folds)
     float *stat_out = nullptr;
     const float *stat_pivot = nullptr;
+    // optional BACKWARD batch-norm sums (backprop-data GEMM whose output e is the epsilon of a BatchNormalization, or of the
+    // Add vertex a BatchNormalization is folded into): while the tile is on chip the epilogue also reads that layer's input
+    // x (laid out like `out`) and leaves, in stat_out's row layout,
+    //   stat_out[row][0][c] = sum e',   stat_out[row][1][c] = sum e' * (x - mean[c]),   e' = e gated by the layer's fused ReLU
+    // (gate recomputed as (x-mean)*gamma/std + beta > 0, the expression k_bn_partial_nhwc / k_bn_apply_nhwc use) -- the
+    // sums BatchNormalization.backpropGradient needs (dBeta, dGamma*std; BatchNormalization.java:172-196), so the
+    // separate partial-sum pass over (x, e) disappears. bst_x != nullptr selects this mode.
+    const float *bst_x = nullptr, *bst_mean = nullptr, *bst_std = nullptr, *bst_gamma = nullptr, *bst_beta = nullptr;
+    int bst_relu = 0;
 };
 struct TmaWgradGeom {
     int M, kW, dH, dW, sH, sW, lowH, lowW, Kp;

@@ -77,6 +77,10 @@ class Network:
         self._register_filters()
         self.params_changed()
         self.fuse_bn_stats = True
+        # backward sums of a BatchNormalization taken in the epilogue of the backprop-data GEMM that produces its epsilon
+        # (dl4jb200_conv_bwd_data_bnstats): the layer's backward then runs finalize + apply only
+        self.fuse_bn_bwd_stats = algo == _lib.ALGO_TC_TF32
+        self._bst_plan, self._bst = {}, {}
         self._plan_bn_stats()
         self._plan_forward_branches()
 
@@ -540,6 +544,28 @@ class Network:
         self._borrowed.setdefault(u, []).append(tensor)
         self._contrib[u] = self._contrib.get(u, 0) + 1
 
+    def _bst_buffer(self, n, d, bn):
+        """Partial-sum buffer for the backward batch-norm sums carried by convolution n's backprop-data (None: it cannot)."""
+        if n not in self._bst_plan:
+            rows = C.c_int(0)
+            cs_in = self.cs[self.vmap[bn]["in"][0]] if self.out.get(self.vmap[bn]["in"][0], 0) is not None else 0
+            Cb = self.shapes[bn][0]
+            ok = (self.fuse_bn_bwd_stats and len(self.shapes[bn]) == 3 and cs_in == Cb and Cb % 4 == 0
+                  and all(self.pidx[(bn, k)][0] % 4 == 0 for k in ("gamma", "beta")))
+            if ok:
+                self._call("dl4jb200_conv_bwd_data_bnstats_rows", C.byref(d), self.cs[n], Cb, self.algo, C.byref(rows))
+            with self.torch.cuda.stream(self.stream):  # the fill is ordered before the kernels that write the buffer
+                self._bst_plan[n] = (rows.value, self._buf(rows.value * 2 * Cb)) if rows.value > 0 else None
+        return self._bst_plan[n]
+
+    def _bst_args(self, bn):
+        v = self.vmap[bn]
+        bx, _ = self._src(v["in"][0])
+        pg, _, _, _ = self._p(bn, "gamma")
+        pbeta, _, _, _ = self._p(bn, "beta")
+        sm, ss = self.aux[bn]
+        return self._ptr(bx), pg, pbeta, self._ptr(sm), self._ptr(ss), int(v["act"] == "relu")
+
     def _emit_dgrad(self, u, d, pw, e, n, x, xcs):
         """Backprop-data of convolution n into the epsilon of its input u. When this is the LAST contribution u will
         receive and u is an Add / Activation vertex with ReLU, the fan-in sum and u's ReLU backprop ride in the GEMM
@@ -557,13 +583,34 @@ class Network:
         fusable = (self.fuse_dgrad and last and uv["op"] in ("add", "act") and uv.get("act") == "relu"
                    and not (u in self._written and lent) and len(lent) <= 1)
         if not fusable:
+            # u is a BatchNormalization (with or without its folded ReLU) that only this convolution consumes: dx IS that
+            # layer's complete epsilon, so its backward sums can ride in this GEMM's epilogue
+            if (uv["op"] == "bn" and u not in self.fused_bn and self.consumers[u] == [n] and u not in self._written and not lent
+                    and uv["act"] in ("identity", "relu")):
+                plan = self._bst_buffer(n, d, u)
+                if plan is not None:
+                    dst = self._eps_buf(u)
+                    self._call("dl4jb200_conv_bwd_data_bnstats", C.byref(d), pw, self._ptr(e), self.cs[n], self._ptr(dst), xcs, None,
+                               None, L.ACT_IDENTITY, self.algo, *self._bst_args(u), self._ptr(plan[1]))
+                    self._written.add(u)
+                    self._contrib[u] = self._contrib.get(u, 0) + 1
+                    self._bst[u] = (plan[1], plan[0])
+                    return
             return self._emit(u, lambda dx: self._call(
                 "dl4jb200_conv_bwd", C.byref(d), self._ptr(x), L.NHWC, xcs, pw, self._ptr(e), L.NHWC, self.cs[n],
                 None, None, dx, L.NHWC, xcs, self.algo))
         dst = self._eps_buf(u)
         prior = self._ptr(dst) if u in self._written else (self._ptr(lent[0]) if lent else None)
-        self._call("dl4jb200_conv_bwd_data_fused", C.byref(d), pw, self._ptr(e), self.cs[n], self._ptr(dst), xcs, prior,
-                   self._ptr(self.out[u]), L.ACT_RELU, self.algo)
+        # the delta of an Add vertex is the epsilon of the BatchNormalization folded into it: same trick
+        bn = self.fused_add[u][0] if u in self.fused_add else None
+        plan = self._bst_buffer(n, d, bn) if bn is not None else None
+        if plan is not None:
+            self._call("dl4jb200_conv_bwd_data_bnstats", C.byref(d), pw, self._ptr(e), self.cs[n], self._ptr(dst), xcs, prior,
+                       self._ptr(self.out[u]), L.ACT_RELU, self.algo, *self._bst_args(bn), self._ptr(plan[1]))
+            self._bst[bn] = (plan[1], plan[0])
+        else:
+            self._call("dl4jb200_conv_bwd_data_fused", C.byref(d), pw, self._ptr(e), self.cs[n], self._ptr(dst), xcs, prior,
+                       self._ptr(self.out[u]), L.ACT_RELU, self.algo)
         self._written.add(u)
         self._borrowed.pop(u, None)
         self._contrib[u] = self._contrib.get(u, 0) + 1
@@ -595,6 +642,7 @@ class Network:
         L, B = _lib, self.B
         self._written, self._borrowed = set(), {}
         self._contrib, self._delta_done = {}, set()
+        self._bst = {}
         self._side_used = False
         if self.dp is not None:
             self.dp.backward_begin(self)
@@ -656,8 +704,14 @@ class Network:
             pg, gg, _, _ = self._p(n, "gamma")
             pbeta, gbeta, _, _ = self._p(n, "beta")
             sm, ss = self.aux[n]
-            self._emit(u, lambda dx: self._call("dl4jb200_bn_bwd", self._ptr(x), self._ptr(e), pg, pbeta, self._ptr(sm),
-                                                self._ptr(ss), _ACT[v["act"]], dx, gg, gbeta, B, s[0], s[1], s[2], L.NHWC, xcs))
+            pre = self._bst.pop(n, None)
+            if pre is not None:  # the sums were taken by the GEMM that produced e: finalize + apply only
+                self._emit(u, lambda dx: self._call("dl4jb200_bn_bwd_prestats", self._ptr(x), self._ptr(e), pg, pbeta, self._ptr(sm),
+                                                    self._ptr(ss), _ACT[v["act"]], dx, gg, gbeta, B, s[0], s[1], s[2], xcs,
+                                                    self._ptr(pre[0]), pre[1]))
+            else:
+                self._emit(u, lambda dx: self._call("dl4jb200_bn_bwd", self._ptr(x), self._ptr(e), pg, pbeta, self._ptr(sm),
+                                                    self._ptr(ss), _ACT[v["act"]], dx, gg, gbeta, B, s[0], s[1], s[2], L.NHWC, xcs))
         elif op == "pool":
             self._trace(n, e)
             u = v["in"][0]

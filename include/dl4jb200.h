@@ -371,6 +371,24 @@ int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g,
                                     const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
                                     const double *cfg_host, int ncfg, double batch_div, float *score_reg_out);
 
+/* Backward counterpart of conv_fwd_bnstats. BatchNormalization.backpropGradient needs dBeta = sum eps and
+ * sum eps * (x - mean) (BatchNormalization.java:172-196) before it can form dx: a separate reduction pass over (x, eps).
+ * When eps is produced by a helper call -- the backprop-data of the convolution that consumed the layer's output, with or
+ * without the fused fan-in sum / ReLU backprop of conv_bwd_data_fused -- the sums can be taken in that GEMM's epilogue
+ * while the tile is on chip: it additionally reads bn_x (the BatchNormalization's INPUT, laid out like dx) and writes
+ * [rows][2][dx_cs] partial sums (rows from conv_bwd_data_bnstats_rows; 0 = this call cannot carry them: TF32 TMA path,
+ * dx_cs == c_in a multiple of the tile width, no strided 1x1). bn_relu: the layer's output passed through a fused ReLU,
+ * eps is gated by (x - mean) * gamma / std + beta > 0 exactly as bn_bwd does. bn_bwd_prestats is then bn_bwd without its
+ * partial-sum pass (finalize + apply). */
+int dl4jb200_conv_bwd_data_bnstats_rows(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int delta_cs, int dx_cs, int algo, int *rows_out);
+int dl4jb200_conv_bwd_data_bnstats(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *w, const float *delta, int delta_cs,
+                                   float *dx, int dx_cs, const float *eps_sum, const float *act_out, int act, int algo,
+                                   const float *bn_x, const float *bn_gamma, const float *bn_beta, const float *bn_mean,
+                                   const float *bn_std, int bn_relu, float *stat_partial);
+int dl4jb200_bn_bwd_prestats(dl4jb200_ctx *ctx, const float *x, const float *eps, const float *gamma, const float *beta,
+                             const float *save_mean, const float *save_std, int act, float *dx, float *dgamma, float *dbeta, int B,
+                             int C, int H, int W, int cs, const float *stat_partial, int stat_rows);
+
 /* ------------------------------------------------------------------ layers that share the conv helper field (f4) - */
 /* Deconvolution2DLayer (NN/nn/layers/convolution/Deconvolution2DLayer.java:145-233 forward, :48-138 backward; the reference
  * runs libnd4j's "deconv2d" / "deconv2d_bp" custom ops). d describes the DECONVOLUTION: c_in = nIn, in_h/in_w its input,
