@@ -125,6 +125,7 @@ PROTOTYPES = {
     "dl4jb200_comm_allreduce_avg_spans_f32": [_vp, _vp, _vp, _vp, _i, _vp],
     "dl4jb200_comm_broadcast_f32": [_vp, _vp, _sz, _i, _vp],
     "dl4jb200_spans_scale_copy": [_vp, _vp, _vp, _vp, _vp, _i, _d],
+    "dl4jb200_updater_apply_segments_range": [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _vp, _i, _d, _vp, _sz, _sz, _i],
     "dl4jb200_updater_apply": [_vp, _vp, _vp, _vp, _sz, _i, _d, _d, _d, _d, _d, _d],
 }
 # entry points whose return value is not a status

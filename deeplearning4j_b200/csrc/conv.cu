@@ -524,7 +524,7 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
         gc.remap = 1; gc.rm_sy = d->stride_h; gc.rm_sx = d->stride_w; gc.rm_H = d->in_h; gc.rm_W = d->in_w;
         gc.use_tma = conv_tc_gemm_can_tma(gc);
         if (gc.use_tma) {
-            DL4J_CUDA_TRY(cudaMemsetAsync(dxs, 0, (size_t)d->batch * d->in_h * d->in_w * dx_cs * sizeof(float), ctx->stream));
+            // (dx is zero away from the sampled pixels: the GEMM's epilogue writes those zeros itself, or clears dx first)
             const float *wq = filters_lookup(ctx, w, true, gc.Cg, gc.Kp, rows_b, 1, 0);
             if (!wq) {
                 k_pack_filter<<<grid_for(ctx, pack_f), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, 1, 1, gc.Cg, gc.Kp, rows_b, 1, 1, 0);

@@ -281,8 +281,12 @@ __device__ __forceinline__ void store_tile_32x32_bst(uint32_t stage_smem, const 
 }
 
 // Same, but every row has its own destination (element offset from `out`, or < 0 to skip): output-row scatter.
+// zmask (per row, 0 when the caller pre-zeroed the tensor): the scattered rows are the stride-2 sample points of a larger
+// image whose other pixels are zero; bit 0 / 1 say that the pixel to the right / below exists, and the lane then also
+// writes zeros to the up-to-three hole pixels of its 2x2 cell, so that no separate memset pass over the tensor is needed.
 __device__ __forceinline__ void store_tile_32x32_rows(uint32_t stage_smem, const float (&v)[32], int lane, float *out,
-                                                      const long long (&rowoff)[8], int col0) {
+                                                      const long long (&rowoff)[8], int col0, const uint32_t (&zmask)[8],
+                                                      long long pix_stride, long long line_stride) {
     __syncwarp();
 #pragma unroll
     for (int q = 0; q < 8; q++) {
@@ -292,13 +296,20 @@ __device__ __forceinline__ void store_tile_32x32_rows(uint32_t stage_smem, const
     }
     __syncwarp();
     const int c = lane & 7;
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int i = 0; i < 8; i++) {
         const int row = 4 * i + (lane >> 3);
         float4 t;
         const uint32_t a = stage_smem + (uint32_t)row * 128u + (uint32_t)((c ^ (row & 7)) << 4);
         asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(a));
-        if (rowoff[i] >= 0) *reinterpret_cast<float4 *>(out + rowoff[i] + col0 + c * 4) = t;
+        if (rowoff[i] >= 0) {
+            float *p = out + rowoff[i] + col0 + c * 4;
+            *reinterpret_cast<float4 *>(p) = t;
+            if (zmask[i] & 1u) *reinterpret_cast<float4 *>(p + pix_stride) = zero;
+            if (zmask[i] & 2u) *reinterpret_cast<float4 *>(p + line_stride) = zero;
+            if ((zmask[i] & 3u) == 3u) *reinterpret_cast<float4 *>(p + line_stride + pix_stride) = zero;
+        }
     }
 }
 
@@ -901,16 +912,20 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
             const int m = m0 + quad * 32 + lane;
             const int rows_valid = g.M - (m0 + quad * 32);
             long long rowoff[8];
+            uint32_t zmask[8];
             if (REMAP) {
 #pragma unroll
                 for (int r8 = 0; r8 < 8; r8++) {
                     const int mm = m0 + quad * 32 + 4 * r8 + (lane >> 3);
                     rowoff[r8] = -1;
+                    zmask[r8] = 0;
                     if (mm < g.M) {
                         uint32_t img, rr, oy, ox;
                         g.div_HWm.divmod((uint32_t)mm, img, rr);
                         g.div_Wm.divmod(rr, oy, ox);
                         rowoff[r8] = (((long long)img * g.rm_H + (long long)oy * g.rm_sy) * g.rm_W + (long long)ox * g.rm_sx) * out_cs;
+                        if (g.rm_zero)  // the hole pixels of this sample's 2x2 cell that lie inside the image
+                            zmask[r8] = ((g.rm_sx == 2 && (int)ox * 2 + 1 < g.rm_W) ? 1u : 0u) | ((g.rm_sy == 2 && (int)oy * 2 + 1 < g.rm_H) ? 2u : 0u);
                     }
                 }
             }
@@ -1007,7 +1022,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
 #pragma unroll
                         for (int e = 0; e < 32; e++) v[e] = dl4j_tf32(v[e]);
                     }
-                    if (REMAP) store_tile_32x32_rows(stage_smem, v, lane, out, rowoff, nb);
+                    if (REMAP) store_tile_32x32_rows(stage_smem, v, lane, out, rowoff, nb, zmask, (long long)out_cs, (long long)g.rm_W * out_cs);
                     else if (fused)
                         store_tile_32x32_fused(stage_smem, v, lane, (size_t)(m0 + quad * 32) * out_cs + nb, (size_t)out_cs, rows_valid,
                                                out, g.epi_add, g.epi_mask, rnd);
@@ -1478,6 +1493,13 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
         return DL4JB200_ERR_INVALID_ARG;
     }
     if (g.remap && !aligned_bias) { dl4j_set_error("conv_tc_gemm_tma: row scatter needs the persistent kernel"); return DL4JB200_ERR_INVALID_ARG; }
+    if (g.remap) {
+        // Everything but the scattered rows is zero. When the stride is 1 or 2 per axis and every tile is a whole tile the
+        // epilogue writes those zeros itself (each sample point owns its 2x2 cell); otherwise the tensor is cleared first.
+        t.rm_zero = g.rm_sy <= 2 && g.rm_sx <= 2 && n_valid % bn == 0 && out_cs == n_valid && g.rm_sx * (g.Wm - 1) + g.rm_sx >= g.rm_W &&
+                    g.rm_sy * (g.Hm - 1) + g.rm_sy >= g.rm_H;
+        if (!t.rm_zero) DL4J_CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)g.B * g.rm_H * g.rm_W * out_cs * sizeof(float), ctx->stream));
+    }
     if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
     if (!aligned_bias) {  // the persistent epilogue reads the bias with 128-bit loads
         if (bn == 128) return tc::launch_gemm_tma<128, 3>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);

@@ -42,6 +42,7 @@ struct TmaGemmGeom {
     // optional output-row scatter: GEMM row (b, oy, ox) is stored at pixel (b, oy*rm_sy, ox*rm_sx) of an rm_H x rm_W image
     // (backprop-data of a strided 1x1 convolution computed on the compact pixel set; the rest of dx is pre-zeroed)
     int remap, rm_sy, rm_sx, rm_H, rm_W;
+    int rm_zero = 0;  // the epilogue also writes the zeros of the skipped pixels (strides <= 2), no memset before the launch
     // optional fused epilogue of a backprop-data GEMM, both laid out exactly like `out`:
     //   out = (acc + epi_add) masked by epi_mask > 0
     // i.e. the ComputationGraph epsilon fan-in sum followed by the ReLU backprop of the vertex that owns `out`

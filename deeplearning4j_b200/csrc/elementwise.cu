@@ -318,11 +318,12 @@ __global__ void __launch_bounds__(256) k_updater_segments(float *__restrict__ w,
                                                           float *__restrict__ state, long long n,
                                                           const long long *__restrict__ seg_start,
                                                           const int *__restrict__ seg_cfg, int nseg, UpdCfgTable tab,
-                                                          float inv_batch, int vec_ok, double *score_partial) {
+                                                          float inv_batch, int vec_ok, double *score_partial, long long q_lo,
+                                                          long long q_hi) {
     __shared__ double sred[256];
     double score = 0.0;
-    const long long stride = (long long)gridDim.x * blockDim.x, nq = (n + 3) >> 2;
-    for (long long qi = (long long)blockIdx.x * blockDim.x + threadIdx.x; qi < nq; qi += stride) {
+    const long long stride = (long long)gridDim.x * blockDim.x;  // quads [q_lo, q_hi) of the flat vector
+    for (long long qi = q_lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; qi < q_hi; qi += stride) {
         const long long i0 = qi << 2;
         int lo = 0, hi = nseg - 1;  // last segment whose start <= i0
         while (lo < hi) {
@@ -370,7 +371,7 @@ __global__ void __launch_bounds__(256) k_updater_segments(float *__restrict__ w,
         if (threadIdx.x == 0) score_partial[blockIdx.x] = sred[0];
     }
 }
-__global__ void __launch_bounds__(256) k_score_fold(const double *partial, int nblk, float *score_out) {
+__global__ void __launch_bounds__(256) k_score_fold(const double *partial, int nblk, float *score_out, int accumulate) {
     __shared__ double s[256];
     double a = 0.0;
     for (int i = threadIdx.x; i < nblk; i += 256) a += partial[i];
@@ -380,7 +381,7 @@ __global__ void __launch_bounds__(256) k_score_fold(const double *partial, int n
         if (threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) score_out[0] = (float)s[0];
+    if (threadIdx.x == 0) score_out[0] = (float)(s[0] + (accumulate ? (double)score_out[0] : 0.0));
 }
 
 // ---------------------------------------------------------------- gradient normalisation (BaseMultiLayerUpdater.preApply)
@@ -441,12 +442,14 @@ int dl4jb200_grad_normalize(dl4jb200_ctx *ctx, float *g, size_t n, int mode, dou
     return DL4JB200_OK;
 }
 
-int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n,
-                                    const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
-                                    const double *cfg_host, int ncfg, double batch_div, float *score_reg_out) {
+int dl4jb200_updater_apply_segments_range(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n,
+                                          const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
+                                          const double *cfg_host, int ncfg, double batch_div, float *score_reg_out, size_t lo,
+                                          size_t hi, int score_accumulate) {
     DL4J_REQUIRE(ctx && w && g && seg_start_dev && seg_cfg_dev && cfg_host, "updater_apply_segments: NULL argument");
     DL4J_REQUIRE(nseg > 0 && ncfg > 0 && ncfg <= DL4J_MAX_UPD_CFGS, "updater_apply_segments: 1..%d configurations supported", DL4J_MAX_UPD_CFGS);
     DL4J_REQUIRE(batch_div > 0, "updater_apply_segments: batch_div must be positive");
+    DL4J_REQUIRE(lo <= hi && hi <= n && lo % 4 == 0 && (hi % 4 == 0 || hi == n), "updater_apply_segments: range [%zu, %zu) must lie in [0, n] on multiples of 4", lo, hi);
     UpdCfgTable tab;
     int any_state = 0;
     for (int i = 0; i < ncfg; i++) {
@@ -456,8 +459,9 @@ int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g,
         if (tab.c[i].kind != DL4JB200_UPD_SGD && tab.c[i].kind != DL4JB200_UPD_NOOP) any_state = 1;
     }
     DL4J_REQUIRE(state || !any_state, "updater_apply_segments: state is NULL");
-    if (n == 0) return DL4JB200_OK;
-    int nblk = ew_grid(ctx, (n + 3) / 4, 256);
+    if (hi == lo) return DL4JB200_OK;
+    const long long q_lo = (long long)(lo >> 2), q_hi = (long long)((hi + 3) >> 2);
+    int nblk = ew_grid(ctx, (size_t)(q_hi - q_lo), 256);
     double *partial = nullptr;
     if (score_reg_out) {
         partial = (double *)dl4j_workspace(ctx, 0, (size_t)nblk * sizeof(double));
@@ -465,13 +469,20 @@ int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g,
     }
     const int vec_ok = aligned16(w) && aligned16(g) && (!state || aligned16(state));
     k_updater_segments<<<nblk, 256, 0, ctx->stream>>>(w, g, state, (long long)n, (const long long *)seg_start_dev, seg_cfg_dev, nseg,
-                                                      tab, (float)(1.0 / batch_div), vec_ok, partial);
+                                                      tab, (float)(1.0 / batch_div), vec_ok, partial, q_lo, q_hi);
     DL4J_CHECK_LAUNCH();
     if (score_reg_out) {
-        k_score_fold<<<1, 256, 0, ctx->stream>>>(partial, nblk, score_reg_out);
+        k_score_fold<<<1, 256, 0, ctx->stream>>>(partial, nblk, score_reg_out, score_accumulate);
         DL4J_CHECK_LAUNCH();
     }
     return DL4JB200_OK;
+}
+
+int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n,
+                                    const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
+                                    const double *cfg_host, int ncfg, double batch_div, float *score_reg_out) {
+    return dl4jb200_updater_apply_segments_range(ctx, w, g, state, n, seg_start_dev, seg_cfg_dev, nseg, cfg_host, ncfg, batch_div,
+                                                 score_reg_out, 0, n, 0);
 }
 
 int dl4jb200_spans_scale_copy(dl4jb200_ctx *ctx, float *dst, const float *src, const long long *offsets_dev,

@@ -638,12 +638,13 @@ class Network:
             self._call("dl4jb200_accumulate", self._ptr(e), self._ptr(t), e.numel())
         return e
 
-    def backward(self):
+    def backward(self, join_side=True):
         L, B = _lib, self.B
         self._written, self._borrowed = set(), {}
         self._contrib, self._delta_done = {}, set()
         self._bst = {}
         self._side_used = False
+        self._side_before_last, self._last_wgrad = None, None
         if self.dp is not None:
             self.dp.backward_begin(self)
         for v in reversed(self.model["vertices"]):
@@ -654,10 +655,14 @@ class Network:
             self._backward_vertex(v)
             if self.dp is not None:
                 self.dp.vertex_done(self, n)
+        self._join_pending = None
         if self._side_used:  # join: gradient exchange / updater must see every filter gradient
             join = self.torch.cuda.Event()
             join.record(self.side_stream)
-            self.stream.wait_event(join)
+            if join_side:
+                self.stream.wait_event(join)
+            else:
+                self._join_pending = join  # update() joins, after it has done everything that does not need the last one
         if self.dp is not None:
             self.dp.backward_end(self)
 
@@ -686,6 +691,11 @@ class Network:
             side = self.overlap_wgrad
             wcall = self._call_side if side else self._call
             if side:  # fork: the side stream may start once everything queued so far (delta is final) has run
+                # (remember where the side stream stood before the LAST filter gradient of the pass -- the first layer's,
+                # which depends on the very last epsilon: update() does not have to wait for that one kernel, see there)
+                self._side_before_last = self.torch.cuda.Event()
+                self._side_before_last.record(self.side_stream)
+                self._last_wgrad = n
                 fork = self.torch.cuda.Event()
                 fork.record(self.stream)
                 self.side_stream.wait_event(fork)
@@ -779,16 +789,50 @@ class Network:
         self.n_cfg = len(cfgs)
 
     def update(self):
-        """All updater blocks + the L1/L2 score terms in one launch (update_per_block is the per-array form)."""
+        """All updater blocks + the L1/L2 score terms in one launch (update_per_block is the per-array form).
+        After backward(join_side=False) the filter gradients may still be running on the side stream: everything except the
+        LAST layer backward reached (the first convolution -- its filter gradient depends on the very last epsilon and is
+        the tail of the step) is updated and re-packed as soon as the other gradients are final, and that layer's slice
+        of the flat vector follows when its gradient arrives."""
         m = self.model
-        self._grad_normalize()
         if not hasattr(self, "seg_start"):
             self._build_segments()
         div = float(self.B * self.batch_div_scale) if m["minibatch"] else 1.0
-        self._call("dl4jb200_updater_apply_segments", self._ptr(self.params), self._ptr(self.grads), self._ptr(self.state), self.P,
-                   self._ptr(self.seg_start), self._ptr(self.seg_cfg), len(self.layout), self.seg_cfg_host, self.n_cfg, div,
-                   self._ptr(self.score_reg) if self.with_score else None)
-        self.params_changed()
+        score = self._ptr(self.score_reg) if self.with_score else None
+        args = (self._ptr(self.params), self._ptr(self.grads), self._ptr(self.state), self.P, self._ptr(self.seg_start),
+                self._ptr(self.seg_cfg), len(self.layout), self.seg_cfg_host, self.n_cfg, div, score)
+        pending = getattr(self, "_join_pending", None)
+        self._join_pending = None
+        late = self._late_span() if pending is not None else None
+        if late is None:
+            if pending is not None:
+                self.stream.wait_event(pending)
+            self._grad_normalize()
+            self._call("dl4jb200_updater_apply_segments", *args)
+            self.params_changed()
+            return
+        lo, hi = late
+        self.stream.wait_event(self._side_before_last)  # every filter gradient but the last one
+        first = True
+        for a, b in ((0, lo), (hi, self.P)):
+            if b > a:
+                self._call("dl4jb200_updater_apply_segments_range", *args, a, b, 0 if first else 1)
+                first = False
+        self.params_changed()                            # the registered filters do not include the late layer's
+        self.stream.wait_event(pending)
+        self._call("dl4jb200_updater_apply_segments_range", *args, lo, hi, 0 if first else 1)
+
+    def _late_span(self):
+        """Flat-vector range of the layer whose filter gradient is issued last, when the split update applies."""
+        n = self._last_wgrad
+        if (n is None or self._side_before_last is None or self.model.get("grad_norm") or self.dp is not None
+                or not (self.stem and self.stem[0] == n)):  # (its filter must not be among the re-packed ones)
+            return None
+        offs = [(off, off + cnt) for (name, key), (off, cnt, shp, pk) in self.pidx.items() if name == n]
+        lo, hi = min(o[0] for o in offs), max(o[1] for o in offs)
+        if lo % 4 or (hi % 4 and hi != self.P):
+            return None
+        return lo, hi
 
     def _grad_normalize(self):
         """GradientNormalization over each layer's gradient view (BaseMultiLayerUpdater.java:322-380)."""
@@ -843,7 +887,7 @@ class Network:
         if features is not None:
             self.set_batch(features, labels)
         self.forward(True)
-        self.backward()
+        self.backward(join_side=hook is not None)
         if hook is not None:
             hook(self)  # data-parallel gradient exchange (parallel.py)
         self.update()  # also leaves the L1/L2 part of the score (pre-update weights) in score_reg
@@ -865,7 +909,7 @@ class Network:
             if include_input:
                 self._relayout_input()
             self.forward(True)
-            self.backward()
+            self.backward(join_side=hook is not None)
             if hook is not None:
                 hook(self)
             self.update()

@@ -370,6 +370,14 @@ int dl4jb200_grad_normalize(dl4jb200_ctx *ctx, float *g, size_t n, int mode, dou
 int dl4jb200_updater_apply_segments(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n,
                                     const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
                                     const double *cfg_host, int ncfg, double batch_div, float *score_reg_out);
+/* The same on the elements [lo, hi) of the flat vectors only (lo, hi multiples of 4, or hi == n); score_accumulate != 0 adds
+ * this range's regularisation term to *score_reg_out instead of overwriting it. Lets a caller update everything whose
+ * gradient is final while the last filter gradient (the first layer's: backward reaches it last) is still being computed,
+ * and finish that layer's slice afterwards. */
+int dl4jb200_updater_apply_segments_range(dl4jb200_ctx *ctx, float *w, const float *g, float *state, size_t n,
+                                          const int64_t *seg_start_dev, const int32_t *seg_cfg_dev, int nseg,
+                                          const double *cfg_host, int ncfg, double batch_div, float *score_reg_out, size_t lo,
+                                          size_t hi, int score_accumulate);
 
 /* Backward counterpart of conv_fwd_bnstats. BatchNormalization.backpropGradient needs dBeta = sum eps and
  * sum eps * (x - mean) (BatchNormalization.java:172-196) before it can form dx: a separate reduction pass over (x, eps).
