@@ -11,10 +11,16 @@ from deeplearning4j_b200 import zoo  # noqa: E402
 
 prof = json.load(open(sys.argv[1]))["per_layer"]
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 256
+model = sys.argv[3] if len(sys.argv) > 3 else "resnet50"
 pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
 TF, BW = pk["bf16_tflops_sustained"] / 2 * 1e12, pk["hbm_gbs"] * 1e9
-m = zoo.resnet50()
-shp = zoo.infer_shapes(m)
+try:  # the measured TF32 dense peak of this pool (scripts/measure_tf32_peak.py), else the provisional half-BF16 figure
+    TF = json.load(open(os.path.join(ROOT, "profiles", "r02_tf32_peak.json")))["tf32_tflops_sustained"] * 1e12
+except Exception:  # noqa: BLE001
+    pass
+from oracle import oracle as _o  # noqa: E402  (shape arithmetic without the CUDA library: runs on the CPU box)
+m = zoo.MODELS[model]()
+shp = zoo.infer_shapes(m, _o.out_size)
 vm = {v["name"]: v for v in m["vertices"]}
 rows = []
 for v in m["vertices"]:
