@@ -68,6 +68,25 @@ __global__ void __launch_bounds__(256) k_pack_filter(const float *__restrict__ w
     }
 }
 
+// Backprop-data operand of ONE stride phase of a strided convolution (see bwd_data_phases): the sub-filter made of the
+// taps kh = a + sH*j, kw = b + sW*j', transposed and tap-flipped:  Wb[n = ci][k = (J*J' - 1 - (j*J' + j'))*Cg + co]
+__global__ void __launch_bounds__(256) k_pack_filter_phase(const float *__restrict__ w, float *__restrict__ wp, int Cout, int Cin,
+                                                           int kH, int kW, int Cg, int Kp, int rows_p, int a, int b, int sH, int sW,
+                                                           int Ja, int Jb) {
+    size_t total = (size_t)rows_p * Kp, stride = (size_t)gridDim.x * blockDim.x;
+    const int taps = Ja * Jb;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        int n = (int)(i / Kp), k = (int)(i % Kp);
+        int tap = k / Cg, co = k % Cg;
+        float v = 0.f;
+        if (tap < taps && co < Cout && n < Cin) {
+            const int ft = taps - 1 - tap, j = ft / Jb, jj = ft - j * Jb;
+            v = w[(((size_t)co * Cin + n) * kH + (a + sH * j)) * kW + (b + sW * jj)];
+        }
+        wp[i] = to_tf32_rna(v);
+    }
+}
+
 // ------------------------------------------------------------------ pre-packed filters
 // conv_fwd / conv_bwd pack the filter on every call (one small kernel each: 106 launches per ResNet-50 step). A caller
 // that knows when the parameters change registers each filter once and re-packs all of them with ONE launch after
@@ -354,6 +373,55 @@ static int check_layout(int layout, int cs, int C, const void *p, const char *wh
     return DL4JB200_OK;
 }
 
+// Backprop-data of a STRIDED convolution with a kernel larger than 1x1 on the TMA / tcgen05 path. The transposed walk
+// iy = (y + pT - kh) / sH is only defined where the division is exact, which im2col-mode TMA cannot express -- the gather
+// kernel handled it at ~20 TFLOP/s (AlexNet's 5x5 stride-2 layer: 1.4 ms of a 3.7 ms step). Decomposed by stride phase it
+// is sH*sW ordinary unit-stride problems: the input pixels with (y + pT) mod sH == a only ever meet the taps kh = a + sH*j,
+// and for them oy = (y + pT - a)/sH - j walks delta with unit stride. Phase (a, b) is therefore the backprop-data of a
+// unit-stride convolution with the J_a x J_b sub-filter, padding (c_a, c_b) = ((y0 + pT - a)/sH, ...), run on the compact
+// pixel set y = y0 + sH*i and scattered into dx by the output-row remap; the phases tile dx exactly, nothing is zeroed.
+// Returns 1 when the shape does not qualify (caller falls back to the gather kernel).
+static int bwd_data_phases(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const float *w, const float *ds, int delta_cs, float *dxs,
+                           int dx_cs, float *wb, size_t wb_floats) {
+    const int sH = d->stride_h, sW = d->stride_w;
+    if (d->dil_h != 1 || d->dil_w != 1 || d->k_h < sH || d->k_w < sW) return 1;
+    const int rows_b = dl4j_round_up(dx_cs > d->c_in ? dx_cs : d->c_in, 256);
+    struct Phase { dl4jb200_conv_desc pd; ConvGeom g; int a, b, y0, x0, Ja, Jb; };
+    Phase ph[64];
+    int np = 0;
+    if (sH * sW > 64) return 1;
+    for (int a = 0; a < sH; a++)
+        for (int b = 0; b < sW; b++) {
+            Phase &p = ph[np];
+            p.a = a; p.b = b;
+            p.y0 = ((a - d->pad_top) % sH + sH) % sH; p.x0 = ((b - d->pad_left) % sW + sW) % sW;
+            const int na = p.y0 < d->in_h ? (d->in_h - 1 - p.y0) / sH + 1 : 0, nb = p.x0 < d->in_w ? (d->in_w - 1 - p.x0) / sW + 1 : 0;
+            if (na == 0 || nb == 0) continue;
+            p.Ja = (d->k_h - a + sH - 1) / sH; p.Jb = (d->k_w - b + sW - 1) / sW;
+            p.pd = *d;
+            p.pd.in_h = na; p.pd.in_w = nb; p.pd.k_h = p.Ja; p.pd.k_w = p.Jb; p.pd.stride_h = p.pd.stride_w = 1;
+            p.pd.pad_top = (p.y0 + d->pad_top - a) / sH; p.pd.pad_left = (p.x0 + d->pad_left - b) / sW;
+            p.g = conv_geom_bwd_data(&p.pd, delta_cs);
+            if (delta_cs < p.g.Cg || !conv_tc_gemm_can_tma(p.g) || (size_t)rows_b * p.g.Kp > wb_floats) return 1;
+            p.g.use_tma = 1;
+            p.g.remap = 1; p.g.rm_sy = sH; p.g.rm_sx = sW; p.g.rm_H = d->in_h; p.g.rm_W = d->in_w; p.g.rm_keep = 1;
+            np++;
+        }
+    const int dx_act = DL4JB200_ACT_IDENTITY | (ctx->round_act ? 0x100 : 0);
+    for (int i = 0; i < np; i++) {
+        Phase &p = ph[i];
+        const size_t n = (size_t)rows_b * p.g.Kp;
+        size_t blocks = (n + 255) / 256, cap = (size_t)ctx->sm_count * 8;
+        k_pack_filter_phase<<<(int)(blocks > cap ? cap : blocks), 256, 0, ctx->stream>>>(w, wb, d->c_out, d->c_in, d->k_h, d->k_w, p.g.Cg, p.g.Kp,
+                                                                                      rows_b, p.a, p.b, sH, sW, p.Ja, p.Jb);
+        DL4J_CHECK_LAUNCH();
+        float *base = dxs + ((size_t)p.y0 * d->in_w + p.x0) * dx_cs;  // pixel (y0, x0) of image 0: the remap strides from there
+        int rc = conv_tc_gemm(ctx, p.g, ds, wb, rows_b, nullptr, base, d->c_in, dx_cs, dx_act);
+        if (rc) return rc;
+    }
+    return DL4JB200_OK;
+}
+
 extern "C" {
 
 int dl4jb200_bias_grad(dl4jb200_ctx *ctx, const float *delta, int M, int cs, int C, float *db) {
@@ -532,6 +600,14 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
                 wq = wb;
             }
             if ((rc = conv_tc_gemm(ctx, gc, ds, wq, rows_b, nullptr, dxs, d->c_in, dx_cs, dx_act))) return rc;
+            if (dx_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, dxs, dx, d->batch, d->c_in, d->in_h, d->in_w, dx_cs);
+            return DL4JB200_OK;
+        }
+    }
+    if (dx && tcore && (d->stride_h > 1 || d->stride_w > 1) && (d->k_h > 1 || d->k_w > 1)) {
+        rc = bwd_data_phases(ctx, d, w, ds, delta_cs, dxs, dx_cs, wb, pack_f);
+        if (rc < 0) return rc;
+        if (rc == DL4JB200_OK) {
             if (dx_layout == DL4JB200_NCHW) return dl4jb200_nhwc_to_nchw(ctx, dxs, dx, d->batch, d->c_in, d->in_h, d->in_w, dx_cs);
             return DL4JB200_OK;
         }

@@ -18,6 +18,7 @@ struct ConvGeom {
     int fast;               // taps are an affine offset from a per-row base pointer (see conv_row_setup)
     int use_tma;            // operands fetched by TMA (im2col mode); backprop-data then needs the filter packed tap-flipped
     int remap, rm_sy, rm_sx, rm_H, rm_W;  // output-row scatter (see TmaGemmGeom)
+    int rm_keep = 0;        // the pixels between the scattered rows belong to other launches: neither zero nor clear them
     FastDiv div_Wm, div_HWm, div_Cg, div_kW;
     // fused epsilon fan-in + activation backprop of the persistent TMA kernel's epilogue (see TmaGemmGeom)
     const float *epi_add = nullptr, *epi_mask = nullptr;

@@ -1496,9 +1496,9 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
     if (g.remap) {
         // Everything but the scattered rows is zero. When the stride is 1 or 2 per axis and every tile is a whole tile the
         // epilogue writes those zeros itself (each sample point owns its 2x2 cell); otherwise the tensor is cleared first.
-        t.rm_zero = g.rm_sy <= 2 && g.rm_sx <= 2 && n_valid % bn == 0 && out_cs == n_valid && g.rm_sx * (g.Wm - 1) + g.rm_sx >= g.rm_W &&
+        t.rm_zero = !g.rm_keep && g.rm_sy <= 2 && g.rm_sx <= 2 && n_valid % bn == 0 && out_cs == n_valid && g.rm_sx * (g.Wm - 1) + g.rm_sx >= g.rm_W &&
                     g.rm_sy * (g.Hm - 1) + g.rm_sy >= g.rm_H;
-        if (!t.rm_zero) DL4J_CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)g.B * g.rm_H * g.rm_W * out_cs * sizeof(float), ctx->stream));
+        if (!t.rm_zero && !g.rm_keep) DL4J_CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)g.B * g.rm_H * g.rm_W * out_cs * sizeof(float), ctx->stream));
     }
     if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
     if (!aligned_bias) {  // the persistent epilogue reads the bias with 128-bit loads
