@@ -1,5 +1,6 @@
-// Few-channel, stride-2 "stem" convolution (ResNet-50's 7x7 s2 on 3 channels; AlexNet/VGG-style first layers with
-// stride_w == 2) on the TMA + tcgen05 path.
+// Few-channel first-layer ("stem") convolution (ResNet-50's 7x7 s2 on 3 channels, VGG16's 3x3 s1, LeNet's 5x5 s1: any
+// stride_w <= 8 with k_w <= 7) on the TMA + tcgen05 path. The text below describes the stride-2 case; for stride s the
+// "pixel" pitch is 4*s floats.
 //
 // With C_in <= 4 a K-chunk of 32 values spans 8 filter taps, which im2col-mode TMA (one tap per instruction, >= 32
 // channels) cannot deliver. But in NHWC4 memory the taps of one filter ROW are contiguous: for output column ow and
@@ -68,20 +69,22 @@ __global__ void __launch_bounds__(256) k_nchw_to_rowpack4(const float *__restric
 
 static int stem_check(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int row_pitch_px, const char *who) {
     DL4J_REQUIRE(ctx && d, "%s: NULL argument", who);
-    if (d->c_in > 4 || d->stride_w != 2 || d->k_w > 7 || d->k_h > 16 || d->dil_h != 1 || d->dil_w != 1 || !tma_driver_ready() ||
-        d->pad_top > 127 || d->stride_h > 8) {
-        dl4j_set_error("%s: row-packed path needs c_in <= 4, stride_w == 2, k_w <= 7, no dilation", who);
+    if (d->c_in > 4 || d->stride_w < 1 || d->stride_w > 8 || d->k_w > 7 || d->k_h > 16 || d->dil_h != 1 || d->dil_w != 1 ||
+        !tma_driver_ready() || d->pad_top > 127 || d->stride_h > 8) {
+        dl4j_set_error("%s: row-packed path needs c_in <= 4, stride_w <= 8, k_w <= 7, no dilation", who);
         return DL4JB200_NOT_SUPPORTED;
     }
-    DL4J_REQUIRE(row_pitch_px % 2 == 0 && row_pitch_px >= 2 * d->out_w + 6 && row_pitch_px >= d->pad_left + 1 + d->in_w,
-                 "%s: row_pitch_px must be even and >= max(2*out_w + 6, pad_left + 1 + in_w)", who);
+    DL4J_REQUIRE(row_pitch_px % 2 == 0 && row_pitch_px >= d->stride_w * (d->out_w - 1) + 8 && row_pitch_px >= d->pad_left + 1 + d->in_w,
+                 "%s: row_pitch_px must be even and >= max(stride_w*(out_w-1) + 8, pad_left + 1 + in_w)", who);
     return DL4JB200_OK;
 }
 
 static int stem_xmap(CUtensorMap *tm, const dl4jb200_conv_desc *d, const float *xp, int row_pitch_px, uint32_t pixels,
                      CUtensorMapSwizzle swz) {
-    // tensor {C = 32 floats, W = out_w window starts (pitch 8 floats), H = in_h rows, N}; taps only along H
-    return tma_make_im2col_pitched(tm, xp, d->batch, d->in_h, d->out_w, 32, 8, (long long)row_pitch_px * 4,
+    // tensor {C = 32 floats, W = out_w window starts (pitch stride_w pixels = 4*stride_w floats), H = in_h rows, N}; taps only
+    // along H. Window ow covers packed pixels stride_w*ow .. +7, i.e. image columns stride_w*ow - pad_left - 1 .. : one
+    // leading dummy tap, then the k_w <= 7 real ones (the filter is packed accordingly, independent of the stride).
+    return tma_make_im2col_pitched(tm, xp, d->batch, d->in_h, d->out_w, 32, 4 * d->stride_w, (long long)row_pitch_px * 4,
                                    (long long)d->in_h * row_pitch_px * 4, 0, -d->pad_top, d->out_w, d->out_h, 1, d->stride_h, pixels, swz);
 }
 

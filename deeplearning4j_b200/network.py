@@ -231,10 +231,10 @@ class Network:
             return
         v = self.vmap[users[0]]
         src, d = self._conv_desc(v)
-        if src != inp or d.c_in > 4 or d.stride_w != 2 or d.k_w > 7 or d.k_h > 16 or d.dil_h != 1 or d.dil_w != 1 \
-                or v["act"] not in ("identity", "relu"):
+        if src != inp or d.c_in > 4 or d.stride_w > 8 or d.k_w > 7 or d.k_h > 16 or d.dil_h != 1 or d.dil_w != 1 \
+                or v["act"] not in ("identity", "relu") or v.get("dropout"):
             return
-        pitch = max(2 * d.out_w + 6, d.pad_left + 1 + d.in_w)
+        pitch = max(d.stride_w * (d.out_w - 1) + 8, d.pad_left + 1 + d.in_w)
         pitch += pitch % 2
         self.stem = (v["name"], pitch, d.pad_left + 1)
         self.out[inp] = self._buf(self.B, d.in_h, pitch, 4)  # padding columns stay zero
