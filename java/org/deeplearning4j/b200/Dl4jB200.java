@@ -110,4 +110,41 @@ public class Dl4jB200 {
                     int h, int w, int layout, int cs, double k, double n, double alpha, double beta);
     public static native int dl4jb200_lrn_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, @Const FloatPointer eps,
                     FloatPointer dx, int b, int c, int h, int w, int layout, int cs, double k, double n, double alpha, double beta);
+
+    // ---- layers that share the convolution helper field (Deconvolution2D, SeparableConvolution2D), fused backward sums,
+    // activation backprop, allocation-free batch norm. The entry points of include/dl4jb200.h that only the device-resident
+    // step driver uses (updaters, re-layouts, softmax loss, raw memory) are not bound by hand here: JavaCPP's parser
+    // generates them from the header when they are needed.
+    public static final int ACT_FROM_OUTPUT = 0x200;
+    public static native int dl4jb200_act_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer z, @Const FloatPointer eps,
+                    FloatPointer delta, @Cast("size_t") long n, int act);
+    public static native int dl4jb200_bias_grad(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer delta, int m, int cs, int c,
+                    FloatPointer db);
+    public static native int dl4jb200_bias_act(@Cast("dl4jb200_ctx*") Pointer ctx, FloatPointer z, @Const FloatPointer bias, int b, int c,
+                    int h, int w, int layout, int cs, int act);
+    public static native int dl4jb200_deconv2d_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer x, int xLayout, int xCs, @Const FloatPointer w, @Const FloatPointer bias, FloatPointer z,
+                    int zLayout, int zCs, int act, int algo);
+    public static native int dl4jb200_deconv2d_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer x, int xLayout, int xCs, @Const FloatPointer w, @Const FloatPointer delta, int deltaLayout,
+                    int deltaCs, FloatPointer dw, FloatPointer db, FloatPointer dx, int dxLayout, int dxCs, int algo);
+    public static native int dl4jb200_depthwise_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    int depthMult, @Const FloatPointer x, int xCs, @Const FloatPointer wd, FloatPointer u, int uCs);
+    public static native int dl4jb200_depthwise_bwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    int depthMult, @Const FloatPointer x, int xCs, @Const FloatPointer wd, @Const FloatPointer du, int uCs,
+                    FloatPointer dwd, FloatPointer dx, int dxCs);
+    public static native int dl4jb200_conv_bwd_data_bnstats_rows(@Cast("dl4jb200_ctx*") Pointer ctx,
+                    @Cast("const dl4jb200_conv_desc*") IntPointer d, int deltaCs, int dxCs, int algo, IntPointer rowsOut);
+    public static native int dl4jb200_conv_bwd_data_bnstats(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
+                    @Const FloatPointer w, @Const FloatPointer delta, int deltaCs, FloatPointer dx, int dxCs, @Const FloatPointer epsSum,
+                    @Const FloatPointer actOut, int act, int algo, @Const FloatPointer bnX, @Const FloatPointer bnGamma,
+                    @Const FloatPointer bnBeta, @Const FloatPointer bnMean, @Const FloatPointer bnStd, int bnRelu, FloatPointer statPartial);
+    public static native int dl4jb200_bn_bwd_prestats(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, @Const FloatPointer eps,
+                    @Const FloatPointer gamma, @Const FloatPointer beta, @Const FloatPointer saveMean, @Const FloatPointer saveStd, int act,
+                    FloatPointer dx, FloatPointer dgamma, FloatPointer dbeta, int b, int c, int h, int w, int cs,
+                    @Const FloatPointer statPartial, int statRows);
+    public static native int dl4jb200_bn_fwd_noalloc(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, FloatPointer y,
+                    @Const FloatPointer gamma, @Const FloatPointer beta, FloatPointer gmean, FloatPointer gvar, FloatPointer saveMean,
+                    FloatPointer saveStd, int b, int c, int h, int w, int layout, int cs, double decay, double eps, int training,
+                    int minibatch, int act);
 }

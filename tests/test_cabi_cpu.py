@@ -66,3 +66,13 @@ def test_no_gpu_means_error_not_fallback(lib):
     from deeplearning4j_b200 import helpers
     with pytest.raises(Exception):
         helpers.Context(0)
+
+
+def test_java_binding_names_exist_in_the_header():
+    """java/ cannot be compiled in this image (no JDK); at least every native method Dl4jB200.java declares must be an entry
+    point include/dl4jb200.h declares, so the reference-side glue cannot drift from the C ABI unnoticed."""
+    java = open(os.path.join(ROOT, "java", "org", "deeplearning4j", "b200", "Dl4jB200.java")).read()
+    natives = set(re.findall(r"native\s+[^;(]*?\b(dl4jb200_[a-z0-9_]+)\s*\(", java))
+    assert len(natives) >= 45
+    missing = sorted(natives - set(_declared_symbols()))
+    assert not missing, missing
