@@ -287,7 +287,9 @@ __global__ void k_bn_finalize_bwd(const float *__restrict__ partial, int nblk, c
 
 // ------------------------------------------------------------------ pass 3: apply
 // MODE 0: y = act((x-centre)*a + c).  MODE 1: dx = a*e' + b*(x-centre) + c, e' = eps masked by act_out.
-template <int MODE>
+// FIXQ: the launch's stride (gridDim.x * 256) is a multiple of the channel-quad count, so a thread meets the same four
+// channels in every iteration and keeps their coefficients in registers (no per-element modulo, no coefficient re-loads).
+template <int MODE, bool FIXQ = false>
 __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__ x, const float *__restrict__ e,
                                                        const float *__restrict__ mask_beta, float *__restrict__ out,
                                                        const float *__restrict__ coef, size_t total4, int cs, int act) {
@@ -297,16 +299,25 @@ __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__
     pdl_trigger();
     pdl_wait();
     size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t first = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    float4 k, a, b, c, m;
+    auto load_coef = [&](int q) {
+        k = __ldg(reinterpret_cast<const float4 *>(coef) + q);
+        a = __ldg(reinterpret_cast<const float4 *>(coef + cs) + q);
+        c = __ldg(reinterpret_cast<const float4 *>(coef + 3 * (size_t)cs) + q);
+        if (MODE == 1) {
+            b = __ldg(reinterpret_cast<const float4 *>(coef + 2 * (size_t)cs) + q);
+            if (mask_beta) m = __ldg(reinterpret_cast<const float4 *>(mask_beta) + q);
+        }
+    };
+    if (FIXQ && first < total4) load_coef((int)((total4 - 1 - first) % Q));
     // The tensor is walked from its END to its start. The producer of x (a convolution epilogue, or the partial-sum pass
     // that has just read x and eps) finished with the high addresses, so those lines are the ones still in the 126 MB L2;
     // and the consumer of `out` (the next convolution, whose tiles run from the first pixel up) in turn finds the lines
     // this kernel wrote last. For tensors up to the L2 size the second read never reaches DRAM.
-    for (size_t ii = (size_t)blockIdx.x * blockDim.x + threadIdx.x; ii < total4; ii += stride) {
+    for (size_t ii = first; ii < total4; ii += stride) {
         const size_t i = total4 - 1 - ii;
-        int q = (int)(i % Q);
-        float4 k = __ldg(reinterpret_cast<const float4 *>(coef) + q);
-        float4 a = __ldg(reinterpret_cast<const float4 *>(coef + cs) + q);
-        float4 c = __ldg(reinterpret_cast<const float4 *>(coef + 3 * (size_t)cs) + q);
+        if (!FIXQ) load_coef((int)(i % Q));
         float4 v = reinterpret_cast<const float4 *>(x)[i];
         v.x -= k.x; v.y -= k.y; v.z -= k.z; v.w -= k.w;
         float4 r;
@@ -316,10 +327,8 @@ __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__
             r.x = dl4j_act(v.x * a.x + c.x + res.x, act); r.y = dl4j_act(v.y * a.y + c.y + res.y, act);
             r.z = dl4j_act(v.z * a.z + c.z + res.z, act); r.w = dl4j_act(v.w * a.w + c.w + res.w, act);
         } else {
-            float4 b = __ldg(reinterpret_cast<const float4 *>(coef + 2 * (size_t)cs) + q);
             float4 g = reinterpret_cast<const float4 *>(e)[i];
             if (mask_beta) {  // fused ReLU of the forward: recompute its mask instead of re-reading the activation
-                float4 m = __ldg(reinterpret_cast<const float4 *>(mask_beta) + q);
                 g.x = v.x * a.x + m.x > 0.f ? g.x : 0.f; g.y = v.y * a.y + m.y > 0.f ? g.y : 0.f;
                 g.z = v.z * a.z + m.z > 0.f ? g.z : 0.f; g.w = v.w * a.w + m.w > 0.f ? g.w : 0.f;
             }
@@ -328,6 +337,21 @@ __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__
         }
         reinterpret_cast<float4 *>(out)[i] = dl4j_rnd4(r, rnd);
     }
+}
+
+// launches k_bn_apply_nhwc, with per-thread fixed channels whenever a grid close to the usual one makes the stride a multiple
+// of the channel-quad count
+template <int MODE>
+static cudaError_t bn_launch_apply_nhwc(dl4jb200_ctx *ctx, int grid, const float *x, const float *e, const float *mask_beta, float *out,
+                                        const float *coef, size_t total4, int cs, int act) {
+    const int Q = cs >> 2;
+    int g = grid;
+    bool fix = false;
+    for (int t = 0; t < 4 && !fix; t++) {  // grid, grid-1, ... : 256 * g divisible by Q (Q is a power of two in every zoo model)
+        if (g - t >= 1 && ((long long)(g - t) * 256) % Q == 0) { g -= t; fix = true; }
+    }
+    if (fix) return dl4j_launch_pdl(k_bn_apply_nhwc<MODE, true>, dim3(g), dim3(256), 0, ctx->stream, x, e, mask_beta, out, coef, total4, cs, act);
+    return dl4j_launch_pdl(k_bn_apply_nhwc<MODE, false>, dim3(grid), dim3(256), 0, ctx->stream, x, e, mask_beta, out, coef, total4, cs, act);
 }
 
 template <int MODE, bool VEC>
@@ -451,7 +475,7 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
                                   (double)M, decay, eps, training, minibatch));
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
-        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_apply_nhwc<0>, dim3(bn_grid(ctx, total / 4)), dim3(256), 0, ctx->stream, x, residual, nullptr, y,
+        DL4J_CUDA_TRY(bn_launch_apply_nhwc<0>(ctx, bn_grid(ctx, total / 4), x, residual, nullptr, y,
                                       p.coef, total / 4, cs, act | (ctx->round_act << 8)));
     } else {
         bool vec = (HW % 4 == 0) && al16(x) && al16(y);
@@ -481,7 +505,7 @@ int dl4jb200_bn_fwd_prestats(dl4jb200_ctx *ctx, const float *x, float *y, const 
                                   pivot, 1, gamma, beta, gmean, gvar, save_mean, save_std, coef, C, cs, (double)M, decay, eps, 1,
                                   minibatch));
     DL4J_CHECK_LAUNCH();
-    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_apply_nhwc<0>, dim3(bn_grid(ctx, total / 4)), dim3(256), 0, ctx->stream, x, residual, nullptr, y,
+    DL4J_CUDA_TRY(bn_launch_apply_nhwc<0>(ctx, bn_grid(ctx, total / 4), x, residual, nullptr, y,
                                   coef, total / 4, cs, act | (ctx->round_act << 8)));
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
@@ -520,7 +544,7 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
                                   save_mean, save_std, relu ? beta : nullptr, dgamma, dbeta, p.coef, C, p.cpad, (double)M));
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
-        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_apply_nhwc<1>, dim3(bn_grid(ctx, total / 4)), dim3(256), 0, ctx->stream, x, eps, mask_beta, dx, p.coef,
+        DL4J_CUDA_TRY(bn_launch_apply_nhwc<1>(ctx, bn_grid(ctx, total / 4), x, eps, mask_beta, dx, p.coef,
                                       total / 4, cs, ctx->round_act << 8));
     } else {
         if (vec) k_bn_apply_nchw<1, true><<<bn_grid(ctx, total / 4), 256, 0, ctx->stream>>>(x, eps, mask_beta, dx, p.coef, total, C, HW, ctx->round_act << 8);
@@ -547,7 +571,7 @@ int dl4jb200_bn_bwd_prestats(dl4jb200_ctx *ctx, const float *x, const float *eps
     DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_bwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, 32), 0, ctx->stream, stat_partial, stat_rows, gamma,
                                   save_mean, save_std, relu ? beta : nullptr, dgamma, dbeta, coef, C, cs, (double)M));
     DL4J_CHECK_LAUNCH();
-    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_apply_nhwc<1>, dim3(bn_grid(ctx, total / 4)), dim3(256), 0, ctx->stream, x, eps,
+    DL4J_CUDA_TRY(bn_launch_apply_nhwc<1>(ctx, bn_grid(ctx, total / 4), x, eps,
                                   relu ? (const float *)(coef + 4 * (size_t)cs) : (const float *)nullptr, dx, (const float *)coef, total / 4, cs,
                                   ctx->round_act << 8));
     DL4J_CHECK_LAUNCH();
