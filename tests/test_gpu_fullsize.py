@@ -153,6 +153,48 @@ def test_conv_epilogue_statistics_full_size(env):
             np.testing.assert_allclose(ss.cpu().numpy(), (var + 1e-5).sqrt().cpu().numpy(), rtol=1e-4)
 
 
+def test_epilogue_statistics_with_a_pivot_far_from_the_batch_mean(env):
+    """The epilogue sums are taken about a pivot (the layer's running mean). When the pivot is far from the batch mean --
+    step 0 on unnormalised inputs, a distribution shift -- var = E[(z-K)^2] - E[z-K]^2 cancels in fp32; this pins how far:
+    measured 8.6e-6 (30 sigma off) and 1.2e-4 (100 sigma off) relative error of the saved std, 1e-7 of the mean -- the
+    per-lane fp32 sums are short (one lane sees 1/32 of a CTA's rows) and are folded in double, so the cancellation stays
+    far below the parity tolerance; asserted at 1e-4 / 1e-3. The running mean moves 10 % of the way per step, so such an
+    offset does not persist; bn_fwd's own statistics pass pivots on a sample of the data."""
+    torch, L, H, h, stream = env
+    B, Cin, Hh, W, Cout, k = 64, 64, 28, 28, 64, 3
+    d = H.conv_desc((B, Cin, Hh, W), Cout, (k, k), (1, 1), (0, 0), (1, 1), "Same")
+    rows = C.c_int(0)
+    L.call("dl4jb200_conv_fwd_bnstats_rows", h, C.byref(d), Cin, Cout, L.ALGO_TC_TF32, C.byref(rows))
+    assert rows.value > 0
+    with torch.cuda.stream(stream):
+        g = torch.Generator(device="cuda").manual_seed(5)
+        x = torch.rand(B, Hh, W, Cin, device="cuda", generator=g)
+        w = torch.randn(Cout, Cin, k, k, device="cuda", generator=g) * 0.2
+        b = torch.randn(Cout, device="cuda", generator=g)
+        z, y = torch.empty(B, d.out_h, d.out_w, Cout, device="cuda"), torch.empty(B, d.out_h, d.out_w, Cout, device="cuda")
+        gamma, beta = torch.ones(Cout, device="cuda"), torch.zeros(Cout, device="cuda")
+        stat = torch.empty(rows.value * 2 * Cout, device="cuda")
+    stream.synchronize()
+    L.call("dl4jb200_conv_fwd", h, C.byref(d), _p(x), L.NHWC, Cin, _p(w), _p(b), _p(z), L.NHWC, Cout, L.ACT_IDENTITY, L.ALGO_TC_TF32)
+    stream.synchronize()
+    zd = z.double()
+    mean, std = zd.mean((0, 1, 2)), (zd.var((0, 1, 2), unbiased=False) + 1e-5).sqrt()
+    for nsig, tol in ((30.0, 1e-4), (100.0, 1e-3)):
+        with torch.cuda.stream(stream):
+            pivot = (mean + nsig * std).float()
+            gm, gv = torch.zeros(Cout, device="cuda"), torch.ones(Cout, device="cuda")
+            sm, ss = torch.empty(Cout, device="cuda"), torch.empty(Cout, device="cuda")
+        stream.synchronize()
+        L.call("dl4jb200_conv_fwd_bnstats", h, C.byref(d), _p(x), Cin, _p(w), _p(b), _p(z), Cout, L.ALGO_TC_TF32, _p(pivot), _p(stat))
+        L.call("dl4jb200_bn_fwd_prestats", h, _p(z), _p(y), _p(gamma), _p(beta), _p(gm), _p(gv), _p(sm), _p(ss), B, Cout, d.out_h,
+               d.out_w, Cout, 0.9, 1e-5, 1, L.ACT_IDENTITY, None, _p(pivot), _p(stat), rows.value)
+        stream.synchronize()
+        e_std = float(((ss.double() - std) / std).abs().max())
+        e_mean = float((sm.double() - mean).abs().max() / mean.abs().max())
+        print(f"pivot {nsig} sigma off: rel err of std {e_std:.2e}, of mean {e_mean:.2e}")
+        assert e_std <= tol and e_mean <= 1e-5
+
+
 def test_fused_backprop_data_epilogue_full_size(env):
     """res2 1x1 256->64 backprop-data at batch 256 (51 M outputs): the fused epilogue (epsilon fan-in + ReLU mask inside the
     GEMM) must equal, bit for bit, plain backprop-data followed by eps_sum_act_bwd -- same accumulators, same fp32 add."""
