@@ -97,6 +97,8 @@ PROTOTYPES = {
     "dl4jb200_conv_fwd_bnstats_rows": [_vp, _desc_p, _i, _i, _i, C.POINTER(C.c_int)],
     "dl4jb200_conv_fwd_bnstats": [_vp, _desc_p, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _vp],
     "dl4jb200_bn_fwd_prestats": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _d, _d, _i, _i, _vp, _vp, _vp, _i],
+    "dl4jb200_bn_fwd_prestats_maxpool": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _d, _d, _i, _i, _vp, _vp, _i,
+                                         _desc_p],
     "dl4jb200_filter_register": [_vp, _vp, _vp, _i, _i, _i, _i],
     "dl4jb200_filters_repack": [_vp],
     "dl4jb200_filters_invalidate": [_vp],

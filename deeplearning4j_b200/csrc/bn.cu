@@ -8,6 +8,8 @@
 // element) so that var = E[(x-K)^2] - E[x-K]^2 does not cancel catastrophically in fp32.
 // Algorithmic traffic: forward 8 B/elem + one extra read (12 moved), backward 12 B/elem + extra read of x
 // and eps (20 moved); the extra reads are what a conv-epilogue fusion removes later.
+#include <float.h>
+
 #include "common.cuh"
 
 #define BN_THREADS 256
@@ -339,6 +341,60 @@ __global__ void __launch_bounds__(256) k_bn_apply_nhwc(const float *__restrict__
     }
 }
 
+// Forward apply + the fused activation + the max-pooling layer that is the batch norm's only consumer, in one pass:
+// y_pool[b,oh,ow,c] = max over the window of rnd(act((x - mean) * a + beta)), argmax = first maximum in (kh, kw) row-major
+// order exactly as SubsamplingLayer's IsMax picks it (SubsamplingLayer.java:205-218). The normalised tensor itself is
+// never written or read back (ResNet-50's stem: 822 MB each way per step). Every tap value is rounded exactly as the
+// stand-alone apply pass would have stored it, so values, ties and indices are those of the two-kernel path.
+struct BnPoolGeom {
+    int B, H, W, Ho, Wo, kH, kW, sH, sW, pT, pL, xcs, ycs;
+    FastDiv d_q, d_w, d_h;
+};
+
+template <int KS>
+__global__ void __launch_bounds__(256) k_bn_act_maxpool_nhwc(const float *__restrict__ x, float *__restrict__ y, int32_t *__restrict__ argmax,
+                                                             const float *__restrict__ coef, BnPoolGeom g, size_t total, int act) {
+    const int rnd = act >> 8;
+    act &= 0xff;
+    const int kH = KS ? KS : g.kH, kW = KS ? KS : g.kW;
+    pdl_trigger();
+    pdl_wait();
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+        uint32_t q, ow, oh, b, r;
+        g.d_q.divmod((uint32_t)idx, r, q);  // total < 2^32 (checked on the host)
+        g.d_w.divmod(r, r, ow);
+        g.d_h.divmod(r, b, oh);
+        const float4 k = __ldg(reinterpret_cast<const float4 *>(coef) + q);
+        const float4 a = __ldg(reinterpret_cast<const float4 *>(coef + g.xcs) + q);
+        const float4 c = __ldg(reinterpret_cast<const float4 *>(coef + 3 * (size_t)g.xcs) + q);
+        float4 best = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX);
+        int bi[4] = {0, 0, 0, 0};
+#pragma unroll KS ? KS : 1
+        for (int kh = 0; kh < kH; kh++) {
+            const int ih = (int)oh * g.sH - g.pT + kh;
+            if (ih < 0 || ih >= g.H) continue;
+#pragma unroll KS ? KS : 1
+            for (int kw = 0; kw < kW; kw++) {
+                const int iw = (int)ow * g.sW - g.pL + kw;
+                if (iw < 0 || iw >= g.W) continue;
+                float4 v = *reinterpret_cast<const float4 *>(x + (((size_t)b * g.H + ih) * g.W + iw) * g.xcs + (size_t)q * 4);
+                v.x = dl4j_act((v.x - k.x) * a.x + c.x, act); v.y = dl4j_act((v.y - k.y) * a.y + c.y, act);
+                v.z = dl4j_act((v.z - k.z) * a.z + c.z, act); v.w = dl4j_act((v.w - k.w) * a.w + c.w, act);
+                v = dl4j_rnd4(v, rnd);
+                const int t = kh * kW + kw;
+                if (v.x > best.x) { best.x = v.x; bi[0] = t; }
+                if (v.y > best.y) { best.y = v.y; bi[1] = t; }
+                if (v.z > best.z) { best.z = v.z; bi[2] = t; }
+                if (v.w > best.w) { best.w = v.w; bi[3] = t; }
+            }
+        }
+        const size_t o = (((size_t)b * g.Ho + oh) * g.Wo + ow) * g.ycs + (size_t)q * 4;
+        *reinterpret_cast<float4 *>(y + o) = best;
+        if (argmax) *reinterpret_cast<int4 *>(argmax + o) = make_int4(bi[0], bi[1], bi[2], bi[3]);
+    }
+}
+
 // launches k_bn_apply_nhwc, with per-thread fixed channels whenever a grid close to the usual one makes the stride a multiple
 // of the channel-quad count
 template <int MODE>
@@ -507,6 +563,40 @@ int dl4jb200_bn_fwd_prestats(dl4jb200_ctx *ctx, const float *x, float *y, const 
     DL4J_CHECK_LAUNCH();
     DL4J_CUDA_TRY(bn_launch_apply_nhwc<0>(ctx, bn_grid(ctx, total / 4), x, residual, nullptr, y,
                                   coef, total / 4, cs, act | (ctx->round_act << 8)));
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+// bn_fwd_prestats whose apply pass also performs the MAX pooling layer that consumes the normalised (and activated) tensor.
+int dl4jb200_bn_fwd_prestats_maxpool(dl4jb200_ctx *ctx, const float *x, float *y_pool, int32_t *argmax, const float *gamma,
+                                     const float *beta, float *gmean, float *gvar, float *save_mean, float *save_std, int B, int C,
+                                     int H, int W, int cs, double decay, double eps, int minibatch, int act, const float *pivot,
+                                     const float *stat_partial, int stat_rows, const dl4jb200_conv_desc *pool) {
+    DL4J_REQUIRE(ctx && x && y_pool && gmean && gvar && pivot && stat_partial && pool, "bn_fwd_prestats_maxpool: NULL argument");
+    DL4J_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && stat_rows > 0, "bn_fwd_prestats_maxpool: bad shape");
+    DL4J_REQUIRE(cs == C && cs % 4 == 0 && al16(x) && al16(y_pool) && (!argmax || al16(argmax)),
+                 "bn_fwd_prestats_maxpool: NHWC with cs == C, cs %% 4 == 0 and 16-byte aligned tensors");
+    DL4J_REQUIRE(pool->batch == B && pool->c_in == C && pool->in_h == H && pool->in_w == W && pool->dil_h == 1 && pool->dil_w == 1 &&
+                     pool->k_h > 0 && pool->k_w > 0 && pool->stride_h > 0 && pool->stride_w > 0 && pool->out_h > 0 && pool->out_w > 0,
+                 "bn_fwd_prestats_maxpool: the pooling descriptor does not describe a window over this tensor (no dilation)");
+    const size_t total = (size_t)B * pool->out_h * pool->out_w * (cs / 4);
+    DL4J_REQUIRE(total < (1ull << 32), "bn_fwd_prestats_maxpool: more than 2^32 output quads");
+    float *coef = (float *)dl4j_workspace(ctx, 0, 5 * (size_t)cs * sizeof(float));
+    if (!coef) return DL4JB200_ERR_CUDA;
+    const long long M = (long long)B * H * W;
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_fwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, 32), 0, ctx->stream, stat_partial, stat_rows,
+                                  pivot, 1, gamma, beta, gmean, gvar, save_mean, save_std, coef, C, cs, (double)M, decay, eps, 1,
+                                  minibatch));
+    DL4J_CHECK_LAUNCH();
+    BnPoolGeom g{B, H, W, pool->out_h, pool->out_w, pool->k_h, pool->k_w, pool->stride_h, pool->stride_w, pool->pad_top, pool->pad_left, cs, cs,
+                 FastDiv((uint32_t)(cs / 4)), FastDiv((uint32_t)pool->out_w), FastDiv((uint32_t)pool->out_h)};
+    const int grid = bn_grid(ctx, total), code = act | (ctx->round_act << 8);
+    if (g.kH == 3 && g.kW == 3)
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_act_maxpool_nhwc<3>, dim3(grid), dim3(256), 0, ctx->stream, x, y_pool, argmax, (const float *)coef, g, total, code));
+    else if (g.kH == 2 && g.kW == 2)
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_act_maxpool_nhwc<2>, dim3(grid), dim3(256), 0, ctx->stream, x, y_pool, argmax, (const float *)coef, g, total, code));
+    else
+        DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_act_maxpool_nhwc<0>, dim3(grid), dim3(256), 0, ctx->stream, x, y_pool, argmax, (const float *)coef, g, total, code));
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }

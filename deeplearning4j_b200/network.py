@@ -212,6 +212,21 @@ class Network:
             if op == "output":
                 self.aux[n] = self._buf(B, cs)  # delta = p - labels
         self._plan_stem()
+        # BatchNormalization (+ folded ReLU) whose only consumer is a MAX pooling layer: when the batch statistics come from
+        # the producing convolution's epilogue, the apply pass pools on the fly and the normalised tensor is never written
+        # (dl4jb200_bn_fwd_prestats_maxpool; ResNet-50's stem). pool_fuse[bn] = pool vertex; decided per forward pass.
+        self.pool_fuse, self.fused_pool_active, self.fuse_bn_pool = {}, set(), True
+        for v in self.model["vertices"]:
+            if v["op"] != "bn" or v["name"] in self.fused_bn or v["act"] not in ("identity", "relu"):
+                continue
+            cons = self.consumers[v["name"]]
+            if len(cons) != 1:
+                continue
+            pv = self.vmap[cons[0]]
+            s3 = self.shapes[v["name"]]
+            if (pv["op"] == "pool" and pv["type"] == "MAX" and not pv.get("dropout") and len(s3) == 3 and s3[0] % 4 == 0
+                    and self.cs[v["name"]] == s3[0] and self.cs[pv["name"]] == s3[0] and tuple(pv.get("dilation", (1, 1))) == (1, 1)):
+                self.pool_fuse[v["name"]] = pv["name"]
         self.loss = self._buf(1)
         self.score_reg = self._buf(1)
         self.tmp_eps = {}
@@ -384,6 +399,7 @@ class Network:
 
     def _forward(self, train):
         L, B = _lib, self.B
+        self._pool_done, self.fused_pool_active = set(), set()
         branches = self.overlap_wgrad and bool(self.fwd_side)
         ready, joined = {}, {}
         for v in self.model["vertices"]:
@@ -450,7 +466,17 @@ class Network:
             pm, _, _, _ = self._p(bn, "mean")
             pv, _, _, _ = self._p(bn, "var")
             sm, ss = self.aux[bn]
-            if train and self.fuse_bn_stats and bn in self.stat_bn:
+            if (train and self.fuse_bn_stats and bn in self.stat_bn and op == "bn" and self.fuse_bn_pool
+                    and bn in self.pool_fuse and self.algo == L.ALGO_TC_TF32):
+                buf, rows = self.stat_bn[bn]
+                pn = self.pool_fuse[bn]
+                pd = self._pool_desc(self.vmap[pn])
+                self._call("dl4jb200_bn_fwd_prestats_maxpool", self._ptr(x), self._ptr(self.out[pn]), self._ptr(self.aux[pn]), pg, pbeta,
+                           pm, pv, self._ptr(sm), self._ptr(ss), B, s[0], s[1], s[2], xcs, float(bnv["decay"]), float(bnv["eps"]),
+                           int(self.model["minibatch"]), act, pm, self._ptr(buf), rows, C.byref(pd))
+                self._pool_done.add(pn)
+                self.fused_pool_active.add(bn)  # out[bn] is NOT written in this pass
+            elif train and self.fuse_bn_stats and bn in self.stat_bn:
                 buf, rows = self.stat_bn[bn]
                 self._call("dl4jb200_bn_fwd_prestats", self._ptr(x), self._ptr(self.out[n]), pg, pbeta, pm, pv, self._ptr(sm),
                            self._ptr(ss), B, s[0], s[1], s[2], xcs, float(bnv["decay"]), float(bnv["eps"]),
@@ -460,6 +486,8 @@ class Network:
                            B, s[0], s[1], s[2], L.NHWC, xcs, float(bnv["decay"]), float(bnv["eps"]), int(train),
                            int(self.model["minibatch"]), act, res)
         elif op == "pool":
+            if n in self._pool_done:  # already produced by the fused batch-norm apply pass of its input
+                return
             d = self._pool_desc(v)
             self._apply_dropout(v, train)
             x, xcs = self._lin(n, v["in"][0])

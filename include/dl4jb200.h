@@ -379,6 +379,17 @@ int dl4jb200_updater_apply_segments_range(dl4jb200_ctx *ctx, float *w, const flo
                                           const double *cfg_host, int ncfg, double batch_div, float *score_reg_out, size_t lo,
                                           size_t hi, int score_accumulate);
 
+/* bn_fwd_prestats with the MAX pooling layer that is the normalised tensor's only consumer folded into the apply pass
+ * (BatchNormalization -> ActivationLayer -> SubsamplingLayer(MAX), ResNet-50's stem,
+ * deeplearning4j-zoo/.../zoo/model/ResNet50.java:181-189): y_pool / argmax are what dl4jb200_pool_fwd would have produced from
+ * the BN's (activated, TF32-rounded if the context rounds) output -- same values, same first-maximum window indices -- but that
+ * output itself is never written. `pool` is the pooling descriptor (dl4jb200_pool_fwd's; no dilation); NHWC, cs == C. The
+ * backward pass needs nothing else: pool_bwd takes argmax, bn_bwd recomputes the activation gate from x. */
+int dl4jb200_bn_fwd_prestats_maxpool(dl4jb200_ctx *ctx, const float *x, float *y_pool, int32_t *argmax, const float *gamma,
+                                     const float *beta, float *gmean, float *gvar, float *save_mean, float *save_std, int B, int C,
+                                     int H, int W, int cs, double decay, double eps, int minibatch, int act, const float *pivot,
+                                     const float *stat_partial, int stat_rows, const dl4jb200_conv_desc *pool);
+
 /* Backward counterpart of conv_fwd_bnstats. BatchNormalization.backpropGradient needs dBeta = sum eps and
  * sum eps * (x - mean) (BatchNormalization.java:172-196) before it can form dx: a separate reduction pass over (x, eps).
  * When eps is produced by a helper call -- the backprop-data of the convolution that consumed the layer's output, with or

@@ -82,6 +82,37 @@ def _nchw(net, t, name):
     return a[:, :s[0]].copy()
 
 
+def _tap_views(o, shape, taps, v):
+    """yields (tap index, slices into the zero-padded input) for every tap of a pooling window (no dilation)."""
+    (kH, kW), (sH, sW) = v["kernel"], v["stride"]
+    Ho, Wo, pT, pL = o.conv_geometry(shape[2], shape[3], v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]])
+    assert taps.shape[2:] == (Ho, Wo)
+    Hp, Wp = max(pT + shape[2], (Ho - 1) * sH + kH), max(pL + shape[3], (Wo - 1) * sW + kW)
+    views = [(kh * kW + kw, (slice(None), slice(None), slice(kh, kh + sH * (Ho - 1) + 1, sH), slice(kw, kw + sW * (Wo - 1) + 1, sW)))
+             for kh in range(kH) for kw in range(kW)]
+    return views, (Hp, Wp, pT, pL)
+
+
+def _gather_taps(o, a, taps, v):
+    """value of the window tap `taps` names (kh * kW + kw), per pooled element."""
+    views, (Hp, Wp, pT, pL) = _tap_views(o, a.shape, taps, v)
+    ap = np.full(a.shape[:2] + (Hp, Wp), -np.inf, np.float32)
+    ap[:, :, pT:pT + a.shape[2], pL:pL + a.shape[3]] = a
+    out = np.zeros(taps.shape, np.float32)
+    for t, sl in views:
+        np.copyto(out, ap[sl], where=taps == t)
+    return out
+
+
+def _scatter_taps(o, d, taps, v, in_shape):
+    """SubsamplingLayer.backpropGradient for MAX with given taps: each epsilon goes to the input cell its tap names."""
+    views, (Hp, Wp, pT, pL) = _tap_views(o, in_shape, taps, v)
+    dxp = np.zeros(tuple(in_shape[:2]) + (Hp, Wp), np.float64)
+    for t, sl in views:
+        dxp[sl] += np.where(taps == t, d, 0)
+    return dxp[:, :, pT:pT + in_shape[2], pL:pL + in_shape[3]]
+
+
 def replay_step(net, model, x, lab, masks=None, fp_tol=1e-4, grad_tol=1e-4, param_tol=1e-5, max_flip_frac=2e-4,
                 forward_only=False):
     """Runs ONE net.fit(x, lab) and checks it vertex by vertex (see module docstring). Returns a Report.
@@ -146,6 +177,8 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=1e-4, grad_tol=1e-4, para
         return act_of(v["in"][0])
 
     zref = {}      # oracle pre-activations (for sigmoid / tanh backprop)
+    pooled_bn = {}  # BN vertex folded into its max-pooling consumer -> the oracle's unrounded normalised (+activated) tensor
+    taps = {}      # such a pooling vertex -> the window taps the GPU saved (routes the backward pass)
     bn_y = {}      # oracle BN output before the fused activation, from the GPU's saved statistics (float64)
 
     # ---------------------------------------------------------------- forward, vertex by vertex
@@ -175,8 +208,25 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=1e-4, grad_tol=1e-4, para
             bn_y[n] = y
             if n in net.fused_bn:
                 continue  # checked with the Add it is folded into
+            if n in getattr(net, "fused_pool_active", ()):
+                # folded into the max-pooling layer that consumes it (never written): the pooling branch below checks the
+                # GPU's pooled output and saved taps against the oracle's pooling of the oracle's normalised tensor
+                ref = o.act_fwd(y, _ACT[v["act"]]) if v["act"] != "identity" else y
+                pooled_bn[n] = np.asarray(ref, np.float32)
+                A[n] = q(ref)
+                continue
             ref = o.act_fwd(y, _ACT[v["act"]]) if v["act"] != "identity" else y
             rep.check("fwd.bn", n, act_of(n), ref, st, fp_tol)
+        elif op == "pool" and v["in"][0] in pooled_bn:
+            # BatchNormalization + ReLU + MAX pooling in one pass: rounding is monotone, so the stored maximum is the rounded
+            # maximum of the unrounded normalised window -- same allowance as a stored BatchNormalization output. The saved
+            # tap must hold that maximum (a different tap is only acceptable where two taps agree to within that allowance).
+            a = pooled_bn[v["in"][0]]
+            ref = o.pool_fwd(a, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]])
+            rep.check("fwd.pool", n, act_of(n), ref, st, fp_tol)
+            taps[n] = _nchw(net, net.aux[n], n)
+            # two taps that round to the same stored value tie (the first wins): up to one full ulp = two roundings apart
+            rep.check("fwd.pool_tap", n, _gather_taps(o, a, taps[n], v), ref, 2 * st, fp_tol)
         elif op == "pool":
             a = lin_of(v)
             ref = o.pool_fwd(a, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]])
@@ -313,6 +363,9 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=1e-4, grad_tol=1e-4, para
                 assert ambiguous.mean() <= max_flip_frac, (n, float(ambiguous.mean()))
                 amb.setdefault(u, np.zeros(xin.shape, bool))
                 amb[u] |= ambiguous
+        elif op == "pool" and n in taps:
+            # its input was never materialised: route by the taps the GPU saved (validated in the forward pass above)
+            give(v["in"][0], _scatter_taps(o, d, taps[n], v, act_of(v["in"][0]).shape))
         elif op == "pool":
             dx = o.pool_bwd(lin_of(v), d, v["kernel"], v["stride"], v["pad"], (1, 1), _MODE[v["mode"]], _POOL[v["type"]])
             give(v["in"][0], dx)

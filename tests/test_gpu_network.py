@@ -142,7 +142,7 @@ def test_tf32_forward_chain_against_quantised_oracle(which):
         # every stored activation is TF32-representable (low 13 mantissa bits clear)
         for v in model["vertices"]:
             n = v["name"]
-            if v["op"] in ("pool", "add", "act", "bn") and n not in net.fused_bn:
+            if v["op"] in ("pool", "add", "act", "bn") and n not in net.fused_bn and n not in net.fused_pool_active:
                 a = net.output_host(n)
                 assert not (a.view(np.uint32) & 0x1FFF).any(), n
     finally:
@@ -173,8 +173,8 @@ def test_resnet50_step_parity_small_batch():
             net.backward()
             net.sync()
             for v in m["vertices"]:
-                if v["op"] in ("input", "zeropad") or v["name"] in net.fused_bn:  # folded into the following Add
-                    continue
+                if v["op"] in ("input", "zeropad") or v["name"] in net.fused_bn or v["name"] in net.fused_pool_active:
+                    continue  # folded into the following Add / max-pooling layer: never materialised
                 got = net.output_host(v["name"])
                 assert rel_err(got, ref.act[v["name"]].reshape(got.shape)) <= tol_fwd, (algo, v["name"])
             assert abs(float(net.loss.cpu()[0]) - ref.loss) <= tol_fwd * abs(ref.loss)
@@ -186,6 +186,33 @@ def test_resnet50_step_parity_small_batch():
             assert cos >= min_cos, (algo, cos)
         finally:
             net.close()
+
+
+def test_bn_folded_into_max_pooling_is_bit_identical():
+    """ResNet-50's stem BatchNormalization + ReLU applied inside the max-pooling pass (the normalised 112x112 tensor is never
+    written) is a traffic change only: two training steps leave parameters, updater state and score bit-identical to the steps
+    that run the two layers separately."""
+    from deeplearning4j_b200 import _lib, network, zoo
+    m = zoo.resnet50()
+    B = 8
+    p0 = zoo.init_params(m)
+    batches = [_data(m, B, 1000, seed=s) for s in (1, 2)]
+    res = []
+    for fuse in (False, True):
+        net = network.Network(m, B, algo=_lib.ALGO_TC_TF32, params=p0)
+        try:
+            net.fuse_bn_pool = fuse
+            scores = []
+            for x, lab in batches:
+                scores.append(float(net.fit(x, lab).cpu()[0]))
+            net.sync()
+            assert (net.fused_pool_active == {"stem-batch1"}) if fuse else not net.fused_pool_active
+            res.append((net.params.cpu().numpy().copy(), net.state.cpu().numpy().copy(), scores))
+        finally:
+            net.close()
+    np.testing.assert_array_equal(res[0][0], res[1][0])
+    np.testing.assert_array_equal(res[0][1], res[1][1])
+    assert res[0][2] == res[1][2]
 
 
 def test_graph_replay_and_prefetch_match_eager():
@@ -352,7 +379,7 @@ def test_simplecnn_forward_parity(algo_name):
         net.sync()
         for v in m["vertices"]:
             n = v["name"]
-            if v["op"] in ("input", "zeropad"):
+            if v["op"] in ("input", "zeropad") or n in net.fused_pool_active:  # folded into its max-pooling consumer
                 continue
             got = net.output_host(n)
             assert rel_err(got, want[n].reshape(got.shape)) <= tol, (n, rel_err(got, want[n].reshape(got.shape)))

@@ -73,3 +73,21 @@ def test_replay_walks_a_sequential_net_with_dense_layers():
     from deeplearning4j_b200 import zoo
     rep = _run(zoo.lenet(), 8, 10, True)
     assert rep.worst("grad.dense_W")[2] < 1e-5
+
+
+def test_tap_routing_matches_the_pooling_oracle():
+    """_gather_taps / _scatter_taps (used where BatchNormalization is folded into its max-pooling consumer) against the oracle's
+    own SubsamplingLayer forward / backward, padded and unpadded windows."""
+    from oracle import oracle as o
+    from step_replay import _gather_taps, _scatter_taps
+    rng = np.random.default_rng(3)
+    for shape, k, s, pad, mode in (((2, 3, 11, 12), (3, 3), (2, 2), (0, 0), "Truncate"), ((2, 4, 9, 9), (3, 3), (2, 2), (1, 1), "Truncate"),
+                                   ((1, 2, 7, 8), (2, 3), (1, 2), (0, 0), "Same")):
+        x = rng.standard_normal(shape).astype(np.float32)
+        v = {"kernel": k, "stride": s, "pad": pad, "mode": mode}
+        m = {"Strict": 0, "Truncate": 1, "Same": 2}[mode]
+        y, am = o.pool_fwd(x, k, s, pad, (1, 1), m, o.POOL_MAX, want_argmax=True)
+        np.testing.assert_array_equal(_gather_taps(o, x, am, v), y)
+        d = rng.standard_normal(y.shape).astype(np.float32)
+        want = o.pool_bwd(x, d, k, s, pad, (1, 1), m, o.POOL_MAX)
+        np.testing.assert_allclose(_scatter_taps(o, d, am, v, x.shape), want, rtol=0, atol=1e-6)
