@@ -19,6 +19,7 @@ ACT_IDENTITY, ACT_RELU, ACT_SIGMOID, ACT_TANH, ACT_LEAKYRELU = 0, 1, 2, 3, 4
 ACT_FROM_OUTPUT = 0x200
 ALGO_TC_TF32, ALGO_FP32 = 0, 1
 OPT_TF32_ACTIVATIONS = 1
+OPT_PAIR_TILES = 2
 UPD_SGD, UPD_NESTEROVS, UPD_RMSPROP, UPD_ADADELTA, UPD_NOOP = 0, 1, 2, 3, 4
 
 

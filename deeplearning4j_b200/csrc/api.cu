@@ -60,6 +60,8 @@ int dl4jb200_ctx_create(int device, void *stream, dl4jb200_ctx **out) {
     c->device = device;
     c->sm_count = prop.multiProcessorCount;
     c->round_act = 0;
+    const char *pt = getenv("DL4JB200_PAIR_TILES");  // default of DL4JB200_OPT_PAIR_TILES for contexts of this process (A/B runs, tests)
+    c->pair_tiles = (pt && pt[0] == '1') ? 1 : 0;
     for (int i = 0; i < 4; i++) { c->ws[i] = nullptr; c->ws_bytes[i] = 0; }
     if (stream) {
         c->stream = (cudaStream_t)stream;
@@ -88,8 +90,9 @@ int dl4jb200_ctx_destroy(dl4jb200_ctx *ctx) {
 
 int dl4jb200_ctx_set_option(dl4jb200_ctx *ctx, int option, int value) {
     DL4J_REQUIRE(ctx, "ctx is NULL");
-    DL4J_REQUIRE(option == DL4JB200_OPT_TF32_ACTIVATIONS, "ctx_set_option: unknown option %d", option);
-    ctx->round_act = value ? 1 : 0;
+    DL4J_REQUIRE(option == DL4JB200_OPT_TF32_ACTIVATIONS || option == DL4JB200_OPT_PAIR_TILES, "ctx_set_option: unknown option %d", option);
+    if (option == DL4JB200_OPT_TF32_ACTIVATIONS) ctx->round_act = value ? 1 : 0;
+    else ctx->pair_tiles = value ? 1 : 0;
     return DL4JB200_OK;
 }
 

@@ -180,20 +180,24 @@ __global__ void __launch_bounds__(BN_THREADS) k_bn_partial_nchw(const float *__r
 // ------------------------------------------------------------------ pass 2: finalize (one thread per channel)
 // coef layout: [4][cpad] = centre, a, b, c   with  y = (x-centre)*a + c            (forward; b unused)
 //                                              dx = a*e + b*(x-centre) + c          (backward)
-// Folds partial[nblk][2][cpad] for channel c over the 32 threads (threadIdx.y) that share it; result valid for y == 0.
+// Folds partial[nblk][2][cpad] for channel c over the BN_FY threads (threadIdx.y) that share it; result valid for y == 0.
+// A block is 32 channels x BN_FY = 256 threads, not 1024: the finalize kernels run next to the side stream's filter-gradient
+// CTAs, and a 1024-thread block does not fit into the registers those leave free on an SM (it waited ~10 us for one to
+// drain, on the critical path, 102 times per ResNet-50 step); 256 threads are resident at once.
+#define BN_FY 8
 __device__ __forceinline__ void bn_fold_partials(const float *__restrict__ partial, int nblk, int cpad, int c, bool active,
                                                  double &s1, double &s2) {
-    __shared__ double sh1[32][33], sh2[32][33];
+    __shared__ double sh1[BN_FY][33], sh2[BN_FY][33];
     double a = 0.0, b = 0.0;
     if (active) {
         // the fold is latency-bound (a few hundred values per channel): issue every load of a 16-row batch before the
-        // first add. Row order per thread is fixed (y, y+32, y+64, ...), so the result is deterministic.
+        // first add. Row order per thread is fixed (y, y+BN_FY, y+2*BN_FY, ...), so the result is deterministic.
         constexpr int U = 8;
-        for (int i = threadIdx.y; i < nblk; i += 32 * U) {
+        for (int i = threadIdx.y; i < nblk; i += BN_FY * U) {
             float p[U], q[U];
 #pragma unroll
             for (int u = 0; u < U; u++) {
-                const int r = i + 32 * u;
+                const int r = i + BN_FY * u;
                 const bool ok = r < nblk;
                 p[u] = ok ? partial[(size_t)r * 2 * cpad + c] : 0.f;
                 q[u] = ok ? partial[(size_t)r * 2 * cpad + cpad + c] : 0.f;
@@ -205,8 +209,8 @@ __device__ __forceinline__ void bn_fold_partials(const float *__restrict__ parti
     sh1[threadIdx.y][threadIdx.x] = a;
     sh2[threadIdx.y][threadIdx.x] = b;
     __syncthreads();
-    // tree fold over the 32 y-slots (fixed shape => deterministic), 5 dependent adds instead of 32
-    for (int h = 16; h >= 1; h >>= 1) {
+    // tree fold over the BN_FY y-slots (fixed shape => deterministic)
+    for (int h = BN_FY / 2; h >= 1; h >>= 1) {
         if ((int)threadIdx.y < h) {
             sh1[threadIdx.y][threadIdx.x] += sh1[threadIdx.y + h][threadIdx.x];
             sh2[threadIdx.y][threadIdx.x] += sh2[threadIdx.y + h][threadIdx.x];
@@ -526,7 +530,7 @@ int dl4jb200_bn_fwd(dl4jb200_ctx *ctx, const float *x, float *y, const float *ga
         }
         DL4J_CHECK_LAUNCH();
     }
-    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_fwd, dim3(dl4j_ceil_div(p.cpad, 32)), dim3(32, 32), 0, ctx->stream, p.partial, p.nblk, x,
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_fwd, dim3(dl4j_ceil_div(p.cpad, 32)), dim3(32, BN_FY), 0, ctx->stream, p.partial, p.nblk, x,
                                   layout == DL4JB200_NHWC ? 1 : HW, gamma, beta, gmean, gvar, save_mean, save_std, p.coef, C, p.cpad,
                                   (double)M, decay, eps, training, minibatch));
     DL4J_CHECK_LAUNCH();
@@ -557,7 +561,7 @@ int dl4jb200_bn_fwd_prestats(dl4jb200_ctx *ctx, const float *x, float *y, const 
     const long long M = (long long)B * H * W;
     const size_t total = (size_t)M * cs;
     // pivot may be gmean itself: k_bn_finalize_fwd reads the pivot of a channel before it updates that channel's gmean
-    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_fwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, 32), 0, ctx->stream, stat_partial, stat_rows,
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_fwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, BN_FY), 0, ctx->stream, stat_partial, stat_rows,
                                   pivot, 1, gamma, beta, gmean, gvar, save_mean, save_std, coef, C, cs, (double)M, decay, eps, 1,
                                   minibatch));
     DL4J_CHECK_LAUNCH();
@@ -584,7 +588,7 @@ int dl4jb200_bn_fwd_prestats_maxpool(dl4jb200_ctx *ctx, const float *x, float *y
     float *coef = (float *)dl4j_workspace(ctx, 0, 5 * (size_t)cs * sizeof(float));
     if (!coef) return DL4JB200_ERR_CUDA;
     const long long M = (long long)B * H * W;
-    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_fwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, 32), 0, ctx->stream, stat_partial, stat_rows,
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_fwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, BN_FY), 0, ctx->stream, stat_partial, stat_rows,
                                   pivot, 1, gamma, beta, gmean, gvar, save_mean, save_std, coef, C, cs, (double)M, decay, eps, 1,
                                   minibatch));
     DL4J_CHECK_LAUNCH();
@@ -630,7 +634,7 @@ int dl4jb200_bn_bwd(dl4jb200_ctx *ctx, const float *x, const float *eps, const f
         else k_bn_partial_nchw<1, false><<<grid, BN_THREADS, 0, ctx->stream>>>(x, eps, mk, save_mean, p.partial, B, C, HW, p.chunk);
     }
     DL4J_CHECK_LAUNCH();
-    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_bwd, dim3(dl4j_ceil_div(p.cpad, 32)), dim3(32, 32), 0, ctx->stream, p.partial, p.nblk, gamma,
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_bwd, dim3(dl4j_ceil_div(p.cpad, 32)), dim3(32, BN_FY), 0, ctx->stream, p.partial, p.nblk, gamma,
                                   save_mean, save_std, relu ? beta : nullptr, dgamma, dbeta, p.coef, C, p.cpad, (double)M));
     DL4J_CHECK_LAUNCH();
     if (layout == DL4JB200_NHWC) {
@@ -658,7 +662,7 @@ int dl4jb200_bn_bwd_prestats(dl4jb200_ctx *ctx, const float *x, const float *eps
     const long long M = (long long)B * H * W;
     const size_t total = (size_t)M * cs;
     const bool relu = act == DL4JB200_ACT_RELU;
-    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_bwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, 32), 0, ctx->stream, stat_partial, stat_rows, gamma,
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_bn_finalize_bwd, dim3(dl4j_ceil_div(cs, 32)), dim3(32, BN_FY), 0, ctx->stream, stat_partial, stat_rows, gamma,
                                   save_mean, save_std, relu ? beta : nullptr, dgamma, dbeta, coef, C, cs, (double)M));
     DL4J_CHECK_LAUNCH();
     DL4J_CUDA_TRY(bn_launch_apply_nhwc<1>(ctx, bn_grid(ctx, total / 4), x, eps,
@@ -764,7 +768,7 @@ extern "C" int dl4jb200_bn_fwd_noalloc(dl4jb200_ctx *ctx, const float *x, float 
         }
         DL4J_CHECK_LAUNCH();
     }
-    k_bn_finalize_fwd<<<dl4j_ceil_div(cpad, 32), dim3(32, 32), 0, ctx->stream>>>(
+    k_bn_finalize_fwd<<<dl4j_ceil_div(cpad, 32), dim3(32, BN_FY), 0, ctx->stream>>>(
         partial, nblk, x, layout == DL4JB200_NHWC ? 1 : HW, gamma, beta, gmean, gvar, save_mean, save_std, coef, C, cpad,
         (double)M, decay, eps, training, minibatch);
     DL4J_CHECK_LAUNCH();

@@ -25,6 +25,7 @@ struct dl4jb200_ctx {
     bool own_stream;
     int sm_count;
     int round_act;  // DL4JB200_OPT_TF32_ACTIVATIONS: activation / epsilon producers store values rounded to TF32
+    int pair_tiles = 0;  // DL4JB200_OPT_PAIR_TILES: 256-row tiles on CTA pairs (tcgen05 cta_group::2) where they apply
     // scratch, grown on demand (never shrunk); slot 0: kernel partials / packed filters, slot 1: NHWC staging
     void *ws[4];
     size_t ws_bytes[4];
@@ -80,6 +81,26 @@ inline cudaError_t dl4j_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
+}
+// the same, as thread-block clusters of cluster_x CTAs along x (gridDim.x must be a multiple of it)
+template <typename... KArgs, typename... Args>
+inline cudaError_t dl4j_launch_pdl_cluster(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, int cluster_x,
+                                           Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = (unsigned)cluster_x;
+    at[1].val.clusterDim.y = 1;
+    at[1].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 2;
     return cudaLaunchKernelEx(&cfg, kern, KArgs(std::forward<Args>(args))...);
 }
 #endif

@@ -83,6 +83,44 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
         : "memory");
 }
+// ---- CTA pairs (cluster of two CTAs on one TPC, tcgen05 cta_group::2): one UMMA of M = 256 spans both SMs -- each CTA holds
+// its own 128 rows of A and its own 128 accumulator lanes, and only HALF of the B tile (the instruction reads the other
+// half out of the partner's shared memory), so a K-step brings 16 KB + BN * 64 B into each SM instead of 16 KB + BN * 128 B.
+// The even CTA (rank 0) issues the MMAs; both CTAs' TMA loads complete on ITS full barrier; its commits are multicast to
+// both CTAs' barriers.
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of the same shared-memory offset in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_alloc2(uint32_t dst_smem) {  // the same warp of BOTH CTAs, same dst offset
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "n"(COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(COLS) : "memory");
+}
+__device__ __forceinline__ void umma_commit2(uint32_t bar) {  // arrives on `bar` of both CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"((uint16_t)3)
+                 : "memory");
+}
+__device__ __forceinline__ void umma_tf32_2(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+}
 // 32 lanes x 32 consecutive fp32 columns: thread i of the warp receives row (lane base + i)
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
     uint32_t r[32];
@@ -752,27 +790,34 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
 // only 2-8 K-chunks long, so set-up, drain and epilogue dominated the one-tile-per-CTA kernel.
 constexpr int PTHREADS = 320;
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, bool PAIR = false>
 struct PersistSmem {
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 4;
-    static constexpr int B_BYTES = BN * BLOCK_K * 4;
+    static constexpr int B_BYTES = (PAIR ? BN / 2 : BN) * BLOCK_K * 4;  // a CTA of a pair holds half of the B tile
     static constexpr int STAGING_OFF = STAGES * (A_BYTES + B_BYTES);  // 8 warps x 4 KB epilogue staging
     static constexpr int BAR_OFF = STAGING_OFF + 8 * 4096;
     static constexpr int BYTES = BAR_OFF + 256 + 1024;
 };
 
 // STATS: 0 none, 1 forward batch-norm statistics of the output, 2 backward batch-norm sums (TmaGemmGeom::bst_*)
-template <int BN, int STAGES, bool REMAP, int STATS = 0>
+// PAIR: launched as clusters of two CTAs; a tile is 256 rows x BN, CTA `rank` owns rows [128 * rank, 128 * rank + 128) -- its
+// own A stream, its own accumulator lanes and epilogue -- and loads B rows [rank * BN/2, +BN/2) only (see the cta_group::2
+// helpers above). total_tiles counts those 256-row tiles; tmB's box is BN/2 rows.
+template <int BN, int STAGES, bool REMAP, int STATS = 0, bool PAIR = false>
 __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const __grid_constant__ CUtensorMap tmA,
                                                                           const __grid_constant__ CUtensorMap tmB,
                                                                           const float *__restrict__ bias,
                                                                           float *__restrict__ out, TmaGemmGeom g,
                                                                           int n_valid, int out_cs, int act, int n_tiles,
                                                                           int total_tiles) {
-    using L = PersistSmem<BN, STAGES>;
+    using L = PersistSmem<BN, STAGES, PAIR>;
     const int rnd = act >> 8;
     act &= 0xff;
     const bool fused = !REMAP && STATS != 2 && (g.epi_add != nullptr || g.epi_mask != nullptr);
+    // tile-loop identity: a lone CTA, or one CTA pair (cluster dims (2,1,1): rank == blockIdx.x & 1)
+    const int rank = PAIR ? (int)(blockIdx.x & 1u) : 0;
+    const int unit = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, units = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    constexpr int TILE_M = PAIR ? 2 * BLOCK_M : BLOCK_M;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
@@ -784,21 +829,27 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
     // B-resident mode: every tile of this CTA uses the same filter columns (the grid is a multiple of the N-tile count, so
     // t % n_tiles is constant per CTA) and the whole K extent of the filter fits the ring's B slots: B is fetched ONCE
     // per CTA instead of once per tile and only A streams (small-K 1x1 layers, the 7-row stem).
-    const bool bres = g.num_k <= STAGES && (int)gridDim.x % n_tiles == 0;  // grid multiple of n_tiles: a CTA keeps its N tile
+    const bool bres = g.num_k <= STAGES && units % n_tiles == 0;  // grid multiple of n_tiles: a CTA keeps its N tile
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         tma::prefetch_desc(&tmA);
         tma::prefetch_desc(&tmB);
         for (int s = 0; s < STAGES; s++) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int b = 0; b < 2; b++) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 256); }
+        // accumulator hand-back: every epilogue lane arrives; in a pair one lane per epilogue warp of BOTH CTAs arrives on
+        // the leader's barrier
+        for (int b = 0; b < 2; b++) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), PAIR ? 16 : 256); }
         mbar_init(bres_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 4) tmem_alloc<2 * BN>(tmem_slot);
+    if (warp == 4) {
+        if (PAIR) tmem_alloc2<2 * BN>(tmem_slot);
+        else tmem_alloc<2 * BN>(tmem_slot);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    if (PAIR) cluster_sync_all();  // the partner's barriers exist before anything is signalled across
     uint32_t tmem_d;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_d) : "r"(tmem_slot));
     // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) ran while the previous kernel
@@ -812,13 +863,17 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
         // ------------------------------ TMA producer
         if (lane == 0) {
             int kit = 0;
-            if (bres && (int)blockIdx.x < total_tiles) {
-                tma::expect_tx(bres_bar, (uint32_t)(g.num_k * L::B_BYTES));
-                for (int it = 0; it < g.num_k; ++it)
-                    tma::load_2d(b_base + it * L::B_BYTES, &tmB, bres_bar, it * BLOCK_K, ((int)blockIdx.x % n_tiles) * BN);
+            const int nb_off = PAIR ? rank * (BN / 2) : 0;  // this CTA's share of the B tile
+            if (bres && unit < total_tiles) {
+                if (rank == 0) tma::expect_tx(bres_bar, (uint32_t)(g.num_k * L::B_BYTES * (PAIR ? 2 : 1)));
+                const uint32_t lead = PAIR ? mapa_rank(bres_bar, 0) : bres_bar;
+                for (int it = 0; it < g.num_k; ++it) {
+                    if (PAIR) tma::load_2d_pair(b_base + it * L::B_BYTES, &tmB, lead, it * BLOCK_K, (unit % n_tiles) * BN + nb_off);
+                    else tma::load_2d(b_base + it * L::B_BYTES, &tmB, bres_bar, it * BLOCK_K, (unit % n_tiles) * BN);
+                }
             }
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-                const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * BN;
+            for (int t = unit; t < total_tiles; t += units) {
+                const int m0 = (t / n_tiles) * TILE_M + rank * BLOCK_M, n0 = (t % n_tiles) * BN + nb_off;
                 uint32_t img, r, oy, ox;
                 g.div_HWm.divmod((uint32_t)m0, img, r);
                 g.div_Wm.divmod(r, oy, ox);
@@ -829,20 +884,30 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                     uint32_t tap, c0, kh, kw;
                     g.div_Cg.divmod((uint32_t)(it * BLOCK_K), tap, c0);
                     g.div_kW.divmod(tap, kh, kw);
-                    tma::expect_tx(full_bar(s), (uint32_t)(bres ? L::A_BYTES : L::A_BYTES + L::B_BYTES));
-                    tma::load_im2col_4d(a_base + s * L::A_BYTES, &tmA, full_bar(s), (int)c0, w0, h0, (int)img,
-                                        (uint16_t)(kw * g.dW), (uint16_t)(kh * g.dH));
-                    if (!bres) tma::load_2d(b_base + s * L::B_BYTES, &tmB, full_bar(s), it * BLOCK_K, n0);
+                    if (PAIR) {
+                        // both CTAs' bytes complete on the leader's barrier (its expect_tx may come after the partner's
+                        // first bytes: the phase cannot complete before the leader's own arrive)
+                        if (rank == 0) tma::expect_tx(full_bar(s), 2u * (uint32_t)(bres ? L::A_BYTES : L::A_BYTES + L::B_BYTES));
+                        const uint32_t lead = mapa_rank(full_bar(s), 0);
+                        tma::load_im2col_4d_pair(a_base + s * L::A_BYTES, &tmA, lead, (int)c0, w0, h0, (int)img, (uint16_t)(kw * g.dW),
+                                                 (uint16_t)(kh * g.dH));
+                        if (!bres) tma::load_2d_pair(b_base + s * L::B_BYTES, &tmB, lead, it * BLOCK_K, n0);
+                    } else {
+                        tma::expect_tx(full_bar(s), (uint32_t)(bres ? L::A_BYTES : L::A_BYTES + L::B_BYTES));
+                        tma::load_im2col_4d(a_base + s * L::A_BYTES, &tmA, full_bar(s), (int)c0, w0, h0, (int)img,
+                                            (uint16_t)(kw * g.dW), (uint16_t)(kh * g.dH));
+                        if (!bres) tma::load_2d(b_base + s * L::B_BYTES, &tmB, full_bar(s), it * BLOCK_K, n0);
+                    }
                 }
             }
         }
         __syncwarp();
     } else if (warp == 4) {
         // ------------------------------ MMA issuer
-        constexpr uint32_t idesc = umma_idesc(BLOCK_M, BN, 0, 0);
+        constexpr uint32_t idesc = umma_idesc(TILE_M, BN, 0, 0);
         int kit = 0, i = 0;
-        if (bres && (int)blockIdx.x < total_tiles) mbar_wait(bres_bar, 0);
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+        if (bres && unit < total_tiles && rank == 0) mbar_wait(bres_bar, 0);
+        for (int t = unit; t < total_tiles && rank == 0; t += units, ++i) {  // in a pair only the leader issues
             const int buf = i & 1;
             mbar_wait(tempty_bar(buf), ((i >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
             tc_fence_after();
@@ -855,12 +920,19 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                     const uint64_t ad = umma_desc(a_base + s * L::A_BYTES, 16, 1024);
                     const uint64_t bd = umma_desc(b_base + (bres ? it : s) * L::B_BYTES, 16, 1024);
 #pragma unroll
-                    for (int k = 0; k < BLOCK_K / 8; k++) umma_tf32(acc, ad + 2u * k, bd + 2u * k, idesc, (it | k) ? 1u : 0u);
-                    umma_commit(empty_bar(s));
+                    for (int k = 0; k < BLOCK_K / 8; k++) {
+                        if (PAIR) umma_tf32_2(acc, ad + 2u * k, bd + 2u * k, idesc, (it | k) ? 1u : 0u);
+                        else umma_tf32(acc, ad + 2u * k, bd + 2u * k, idesc, (it | k) ? 1u : 0u);
+                    }
+                    if (PAIR) umma_commit2(empty_bar(s));  // frees the slot in both CTAs
+                    else umma_commit(empty_bar(s));
                 }
                 __syncwarp();
             }
-            if (lane == 0) umma_commit(tfull_bar(buf));
+            if (lane == 0) {
+                if (PAIR) umma_commit2(tfull_bar(buf));
+                else umma_commit(tfull_bar(buf));
+            }
             __syncwarp();
         }
     } else {
@@ -882,7 +954,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                 st_s[j] = make_float4(0.f, 0.f, 0.f, 0.f);
                 st_q[j] = st_s[j];
                 const int cb = grp + 2 * j;
-                const int col = ((int)blockIdx.x % n_tiles) * BN + cb * 32;
+                const int col = (unit % n_tiles) * BN + cb * 32;
                 if constexpr (STATS == 1) {
                     st_k[j] = cb < BN / 32 ? __ldg(reinterpret_cast<const float4 *>(g.stat_pivot + col) + (lane & 7)) : st_s[j];
                 } else if constexpr (STATS == 2) {
@@ -904,10 +976,20 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                 }
             }
         }
+        // hand an accumulator buffer back to the MMA issuer (the caller has fenced its TMEM reads)
+        const uint32_t lead_tempty[2] = {PAIR ? mapa_rank(tempty_bar(0), 0) : 0u, PAIR ? mapa_rank(tempty_bar(1), 0) : 0u};
+        auto release_acc = [&](int b) {
+            if (PAIR) {
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(lead_tempty[b]);
+            } else {
+                mbar_arrive(tempty_bar(b));
+            }
+        };
         int i = 0;
-        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+        for (int t = unit; t < total_tiles; t += units, ++i) {
             const int buf = i & 1;
-            const int m0 = (t / n_tiles) * BLOCK_M, n0 = (t % n_tiles) * BN;
+            const int m0 = (t / n_tiles) * TILE_M + rank * BLOCK_M, n0 = (t % n_tiles) * BN;
             const bool full_n = n0 + BN <= n_valid;
             const int m = m0 + quad * 32 + lane;
             const int rows_valid = g.M - (m0 + quad * 32);
@@ -932,8 +1014,8 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
             if (fused && grp == 0) {
                 // pull the epilogue's extra operands of the NEXT tile of this CTA (and, on the first pass, of this one)
                 // into L2 now: one bulk prefetch per row and tensor, a whole tile of lead time
-                for (int tp = (i == 0 ? t : t + (int)gridDim.x); tp <= t + (int)gridDim.x && tp < total_tiles; tp += gridDim.x) {
-                    const int pm = (tp / n_tiles) * BLOCK_M + quad * 32 + lane, pn = (tp % n_tiles) * BN;
+                for (int tp = (i == 0 ? t : t + units); tp <= t + units && tp < total_tiles; tp += units) {
+                    const int pm = (tp / n_tiles) * TILE_M + rank * BLOCK_M + quad * 32 + lane, pn = (tp % n_tiles) * BN;
                     if (pm < g.M) {
                         const size_t o = (size_t)pm * out_cs + pn;
                         const uint32_t bytes = (uint32_t)(min(BN, out_cs - pn) * 4);
@@ -948,7 +1030,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
             constexpr int NCB = BN / 32;
             if (grp >= NCB) {  // BN == 32: one chunk only, the second warp group just keeps the barrier phase moving
                 tc_fence_before();
-                mbar_arrive(tempty_bar(buf));
+                release_acc(buf);
                 continue;
             }
             const int cb_last = NCB == 1 ? 0 : ((NCB - 1 - grp) & ~1) + grp;  // last chunk of this group's parity
@@ -961,7 +1043,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                         tmem_ld32(acc + (uint32_t)(cb * 32), v);
                         if (cb == cb_last) {
                             tc_fence_before();
-                            mbar_arrive(tempty_bar(buf));
+                            release_acc(buf);
                         }
                         store_tile_32x32_bst(stage_smem, v, lane, (size_t)(m0 + quad * 32) * out_cs + n0 + cb * 32, (size_t)out_cs, rows_valid, out,
                                              g.epi_add, g.epi_mask, rnd, g.bst_x, st_k[j], st_a[j], st_b[j], g.bst_relu, st_s[j], st_q[j]);
@@ -978,7 +1060,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                         tmem_ld32(acc + (uint32_t)(cb * 32), v);
                         if (cb == cb_last) {
                             tc_fence_before();
-                            mbar_arrive(tempty_bar(buf));
+                            release_acc(buf);
                         }
                         const int nb = n0 + cb * 32;
                         if (bias) {
@@ -1000,7 +1082,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                 tmem_ld32(acc + (uint32_t)(cb * 32), v);
                 if (cb == cb_last) {  // last TMEM read of this warp in this tile: hand the accumulator back to the MMA warp
                     tc_fence_before();
-                    mbar_arrive(tempty_bar(buf));
+                    release_acc(buf);
                 }
                 const int nb = n0 + cb * 32;
                 if (full_n) {
@@ -1061,7 +1143,8 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
             // both warp groups are active (BN >= 64), the four lane quadrants of the CTA are combined through the staging
             // smem so that the CTA writes ONE partial row (the finalize fold is a latency-bound tail: fewer rows, shorter)
             constexpr bool COMBINE = BN >= 64;
-            const int ncol0 = ((int)blockIdx.x % n_tiles) * BN;
+            const int ncol0 = (unit % n_tiles) * BN;
+            const int srow = PAIR ? (unit / n_tiles) * 2 + rank : unit / n_tiles;  // this CTA's partial row
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < NCH; j++) {
@@ -1081,7 +1164,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                             asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(sa), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w) : "memory");
                             asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(sa + 128u), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
                         } else {
-                            float *p = g.stat_out + (size_t)(((int)blockIdx.x / n_tiles) * 4 + quad) * 2 * out_cs + ncol0 + cb * 32 + lane * 4;
+                            float *p = g.stat_out + (size_t)(srow * 4 + quad) * 2 * out_cs + ncol0 + cb * 32 + lane * 4;
                             *reinterpret_cast<float4 *>(p) = a;
                             *reinterpret_cast<float4 *>(p + out_cs) = b;
                         }
@@ -1105,7 +1188,7 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
                                 a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w;
                                 b.x += w.x; b.y += w.y; b.z += w.z; b.w += w.w;
                             }
-                            float *p = g.stat_out + (size_t)((int)blockIdx.x / n_tiles) * 2 * out_cs + ncol0 + cb * 32 + lane * 4;
+                            float *p = g.stat_out + (size_t)srow * 2 * out_cs + ncol0 + cb * 32 + lane * 4;
                             *reinterpret_cast<float4 *>(p) = a;
                             *reinterpret_cast<float4 *>(p + out_cs) = b;
                         }
@@ -1116,7 +1199,11 @@ __global__ void __launch_bounds__(PTHREADS, 1) k_conv_tc_gemm_tma_persist(const 
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc<2 * BN>(tmem_d);
+    if (PAIR) cluster_sync_all();  // the partner has finished with the paired allocation (and with this CTA's barriers)
+    if (warp == 4) {
+        if (PAIR) tmem_dealloc2<2 * BN>(tmem_d);
+        else tmem_dealloc<2 * BN>(tmem_d);
+    }
 }
 
 // grid of a statistics-carrying launch: <= #SMs, <= total tiles, a multiple of n_tiles (0: impossible)
@@ -1128,64 +1215,76 @@ static inline int persist_stat_grid(int sm_count, int total, int n_tiles) {
 // partial rows such a launch writes: one per CTA column group when the CTA combines its quadrants (bn >= 64), else four
 static inline int persist_stat_rows(int grid, int n_tiles, int bn) { return grid / n_tiles * (bn >= 64 ? 1 : 4); }
 
-template <int BN, int STAGES>
-static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const TmaGemmGeom &g,
-                                   const float *bias, float *out, int n_valid, int out_cs, int act) {
-    using L = PersistSmem<BN, STAGES>;
+// one instantiation of the persistent kernel: shared-memory opt-in once per device, then the (clustered) PDL launch
+template <int BN, int STAGES, bool REMAP, int STATS, bool PAIR>
+static int launch_persist_variant(dl4jb200_ctx *ctx, int grid, const CUtensorMap &tmA, const CUtensorMap &tmB, const TmaGemmGeom &g,
+                                  const float *bias, float *out, int n_valid, int out_cs, int act, int n_tiles, int total) {
+    using L = PersistSmem<BN, STAGES, PAIR>;
+    auto kern = k_conv_tc_gemm_tma_persist<BN, STAGES, REMAP, STATS, PAIR>;
     static bool configured[16] = {false};
     if (!configured[ctx->device & 15]) {
-        DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
-        DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
         configured[ctx->device & 15] = true;
     }
-    const int n_tiles = dl4j_ceil_div(out_cs, BN), total = dl4j_ceil_div(g.M, BLOCK_M) * n_tiles;
-    int grid = total < ctx->sm_count ? total : ctx->sm_count;
-    if (n_tiles > 1 && g.num_k <= STAGES && grid >= 2 * n_tiles) grid = grid / n_tiles * n_tiles;  // enables the B-resident mode
+    if (PAIR)
+        DL4J_CUDA_TRY(dl4j_launch_pdl_cluster(kern, dim3(grid), dim3(PTHREADS), L::BYTES, ctx->stream, 2, tmA, tmB, bias, out, g, n_valid, out_cs,
+                                              act, n_tiles, total));
+    else
+        DL4J_CUDA_TRY(dl4j_launch_pdl(kern, dim3(grid), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB, bias, out, g, n_valid, out_cs, act,
+                                      n_tiles, total));
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+// pipeline depth of the pair kernels: a stage is 16 KB of A + BN * 64 B of B
+template <int BN>
+struct PairStages { static constexpr int N = BN == 256 ? 5 : (BN == 128 ? 7 : 8); };
+
+// pair: tiles are 256 rows, tmB was built with a BN/2-row box, the grid is twice the number of pairs
+template <int BN, int STAGES>
+static int launch_gemm_tma_persist(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const TmaGemmGeom &g,
+                                   const float *bias, float *out, int n_valid, int out_cs, int act, bool pair = false) {
+    constexpr int PS = PairStages<BN>::N;
+    const int n_tiles = dl4j_ceil_div(out_cs, BN), tile_m = pair ? 2 * BLOCK_M : BLOCK_M, total = dl4j_ceil_div(g.M, tile_m) * n_tiles;
+    const int slots = pair ? ctx->sm_count / 2 : ctx->sm_count, stages = pair ? PS : STAGES, mult = pair ? 2 : 1;
+    int units = total < slots ? total : slots;
+    if (n_tiles > 1 && g.num_k <= stages && units >= 2 * n_tiles) units = units / n_tiles * n_tiles;  // enables the B-resident mode
+    if constexpr (BN < 64) {
+        if (pair) { dl4j_set_error("conv_tc_gemm_tma: CTA pairs need tiles of at least 64 columns"); return DL4JB200_ERR_INVALID_ARG; }
+    }
     if (g.stat_out && g.bst_x) {  // backward batch-norm sums in a backprop-data epilogue
         if constexpr (BN == 64 || BN == 128) {
-            static bool configured_b[16] = {false};
-            if (!configured_b[ctx->device & 15]) {
-                DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
-                configured_b[ctx->device & 15] = true;
-            }
-            const int gs = persist_stat_grid(ctx->sm_count, total, n_tiles);
+            const int gs = persist_stat_grid(slots, total, n_tiles);
             if (g.remap || gs <= 0 || n_valid % BN != 0 || out_cs != n_valid || (act & 0xff) != DL4JB200_ACT_IDENTITY || bias) {
                 dl4j_set_error("conv_tc_gemm_tma: this launch cannot carry the backward batch-norm sums");
                 return DL4JB200_ERR_INVALID_ARG;
             }
-            DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, false, 2>, dim3(gs), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB,
-                                          bias, out, g, n_valid, out_cs, act, n_tiles, total));
-            DL4J_CHECK_LAUNCH();
-            return DL4JB200_OK;
+            if (pair) return launch_persist_variant<BN, PS, false, 2, true>(ctx, gs * mult, tmA, tmB, g, bias, out, n_valid, out_cs, act, n_tiles, total);
+            return launch_persist_variant<BN, STAGES, false, 2, false>(ctx, gs, tmA, tmB, g, bias, out, n_valid, out_cs, act, n_tiles, total);
         } else {
             dl4j_set_error("conv_tc_gemm_tma: backward batch-norm sums need 64- or 128-wide tiles");
             return DL4JB200_ERR_INVALID_ARG;
         }
     }
     if (g.stat_out) {  // batch-norm statistics in the epilogue: grid a multiple of n_tiles (see the kernel)
-        static bool configured_s[16] = {false};
-        if (!configured_s[ctx->device & 15]) {
-            DL4J_CUDA_TRY(cudaFuncSetAttribute(k_conv_tc_gemm_tma_persist<BN, STAGES, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
-            configured_s[ctx->device & 15] = true;
-        }
-        const int gs = persist_stat_grid(ctx->sm_count, total, n_tiles);
+        const int gs = persist_stat_grid(slots, total, n_tiles);
         if (g.remap || gs <= 0 || n_valid % BN != 0 || (act & 0xff) != DL4JB200_ACT_IDENTITY || g.epi_add || g.epi_mask) {
             dl4j_set_error("conv_tc_gemm_tma: this launch cannot carry batch-norm statistics");
             return DL4JB200_ERR_INVALID_ARG;
         }
-        DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, false, 1>, dim3(gs), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB,
-                                      bias, out, g, n_valid, out_cs, act & 0xff, n_tiles, total));
-        DL4J_CHECK_LAUNCH();
-        return DL4JB200_OK;
+        if constexpr (BN >= 64) {
+            if (pair) return launch_persist_variant<BN, PS, false, 1, true>(ctx, gs * mult, tmA, tmB, g, bias, out, n_valid, out_cs, act & 0xff, n_tiles, total);
+        }
+        return launch_persist_variant<BN, STAGES, false, 1, false>(ctx, gs, tmA, tmB, g, bias, out, n_valid, out_cs, act & 0xff, n_tiles, total);
     }
-    if (g.remap)
-        DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, true>, dim3(grid), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB, bias,
-                                      out, g, n_valid, out_cs, act, n_tiles, total));
-    else
-        DL4J_CUDA_TRY(dl4j_launch_pdl(k_conv_tc_gemm_tma_persist<BN, STAGES, false>, dim3(grid), dim3(PTHREADS), L::BYTES, ctx->stream, tmA, tmB, bias,
-                                      out, g, n_valid, out_cs, act, n_tiles, total));
-    DL4J_CHECK_LAUNCH();
-    return DL4JB200_OK;
+    if constexpr (BN >= 64) {
+        if (pair) {
+            if (g.remap) return launch_persist_variant<BN, PS, true, 0, true>(ctx, units * 2, tmA, tmB, g, bias, out, n_valid, out_cs, act, n_tiles, total);
+            return launch_persist_variant<BN, PS, false, 0, true>(ctx, units * 2, tmA, tmB, g, bias, out, n_valid, out_cs, act, n_tiles, total);
+        }
+    }
+    if (g.remap) return launch_persist_variant<BN, STAGES, true, 0, false>(ctx, units, tmA, tmB, g, bias, out, n_valid, out_cs, act, n_tiles, total);
+    return launch_persist_variant<BN, STAGES, false, 0, false>(ctx, units, tmA, tmB, g, bias, out, n_valid, out_cs, act, n_tiles, total);
 }
 
 template <int BN, int STAGES>
@@ -1442,13 +1541,26 @@ static int tma_gemm_bn(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, 
     return wide ? 256 : narrow;
 }
 
+// 256-row tiles on CTA pairs (see the cta_group::2 helpers): wherever the persistent kernel runs with tiles of at least 64
+// columns and the layer has two or more 128-row tiles
+static bool tma_gemm_pair(dl4jb200_ctx *ctx, const ConvGeom &g, int bn, bool aligned_bias) {
+    return ctx->pair_tiles && aligned_bias && bn >= 64 && g.M > tc::BLOCK_M && ctx->sm_count >= 2;
+}
+
+// partial rows a statistics-carrying launch writes: tiles / grid follow launch_gemm_tma_persist
+static int tma_gemm_stat_rows(dl4jb200_ctx *ctx, const ConvGeom &g, int bn, int out_cs) {
+    const bool pair = tma_gemm_pair(ctx, g, bn, true);
+    const int n_tiles = out_cs / bn, total = dl4j_ceil_div(g.M, pair ? 2 * tc::BLOCK_M : tc::BLOCK_M) * n_tiles;
+    const int grid = tc::persist_stat_grid(pair ? ctx->sm_count / 2 : ctx->sm_count, total, n_tiles) * (pair ? 2 : 1);
+    return tc::persist_stat_rows(grid, n_tiles, bn);
+}
+
 // partial rows a statistics-carrying forward launch of this geometry writes (0: the launch cannot carry statistics)
 int conv_tc_stat_rows(dl4jb200_ctx *ctx, const ConvGeom &g, int n_rows_packed, int n_valid, int out_cs) {
     if (!g.use_tma || g.remap) return 0;
     const int bn = tma_gemm_bn(ctx, g, n_rows_packed, out_cs, true);
     if (n_valid % bn != 0 || out_cs != n_valid) return 0;
-    const int n_tiles = out_cs / bn, total = dl4j_ceil_div(g.M, tc::BLOCK_M) * n_tiles;
-    return tc::persist_stat_rows(tc::persist_stat_grid(ctx->sm_count, total, n_tiles), n_tiles, bn);
+    return tma_gemm_stat_rows(ctx, g, bn, out_cs);
 }
 
 // partial rows a backprop-data launch carrying the backward batch-norm sums writes (0: it cannot carry them)
@@ -1458,8 +1570,7 @@ int conv_tc_bst_rows(dl4jb200_ctx *ctx, const ConvGeom &g0, int n_rows_packed, i
     g.bst_x = reinterpret_cast<const float *>(16);  // any non-null value: selects the narrow tile widths
     const int bn = tma_gemm_bn(ctx, g, n_rows_packed, out_cs, true);
     if (bn < 64 || n_valid % bn != 0 || out_cs != n_valid) return 0;
-    const int n_tiles = out_cs / bn, total = dl4j_ceil_div(g.M, tc::BLOCK_M) * n_tiles;
-    return tc::persist_stat_rows(tc::persist_stat_grid(ctx->sm_count, total, n_tiles), n_tiles, bn);
+    return tma_gemm_stat_rows(ctx, g, bn, out_cs);
 }
 
 static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *src, const float *wpack, int n_rows_packed,
@@ -1468,12 +1579,13 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
     const int lowH = g.transposed ? g.pT - (g.kH - 1) * g.dH : -g.pT, lowW = g.transposed ? g.pL - (g.kW - 1) * g.dW : -g.pL;
     const int sH = g.transposed ? 1 : g.sH, sW = g.transposed ? 1 : g.sW;
     alignas(64) CUtensorMap tmA, tmB;
+    const bool aligned_bias = !bias || ((uintptr_t)bias & 15) == 0;
     int rc = tma_make_im2col(&tmA, src, g.B, g.Hs, g.Ws, g.Cg, g.cs_src, lowW, lowH, g.Wm, g.Hm, sW, sH, tc::BLOCK_M,
                              CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
-    const bool aligned_bias = !bias || ((uintptr_t)bias & 15) == 0;
     const int bn = tma_gemm_bn(ctx, g, n_rows_packed, out_cs, aligned_bias);
-    rc = tma_make_2d(&tmB, wpack, (uint64_t)n_rows_packed, (uint64_t)g.Kp, (uint64_t)g.Kp, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B);
+    const bool pair = tma_gemm_pair(ctx, g, bn, aligned_bias);  // each CTA of a pair fetches half of the filter tile
+    rc = tma_make_2d(&tmB, wpack, (uint64_t)n_rows_packed, (uint64_t)g.Kp, (uint64_t)g.Kp, (uint32_t)(pair ? bn / 2 : bn), CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
     TmaGemmGeom t;
     t.M = g.M; t.num_k = g.Kp / tc::BLOCK_K; t.kW = g.kW; t.dH = g.dH; t.dW = g.dW; t.sH = sH; t.sW = sW; t.lowH = lowH; t.lowW = lowW;
@@ -1500,14 +1612,14 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
                     g.rm_sy * (g.Hm - 1) + g.rm_sy >= g.rm_H;
         if (!t.rm_zero && !g.rm_keep) DL4J_CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)g.B * g.rm_H * g.rm_W * out_cs * sizeof(float), ctx->stream));
     }
-    if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act, pair);
     if (!aligned_bias) {  // the persistent epilogue reads the bias with 128-bit loads
         if (bn == 128) return tc::launch_gemm_tma<128, 3>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
         if (bn == 64) return tc::launch_gemm_tma<64, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
         return tc::launch_gemm_tma<32, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
     }
-    if (bn == 128) return tc::launch_gemm_tma_persist<128, 5>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
-    if (bn == 64) return tc::launch_gemm_tma_persist<64, 6>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
+    if (bn == 128) return tc::launch_gemm_tma_persist<128, 5>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act, pair);
+    if (bn == 64) return tc::launch_gemm_tma_persist<64, 6>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act, pair);
     return tc::launch_gemm_tma_persist<32, 6>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act);
 }
 

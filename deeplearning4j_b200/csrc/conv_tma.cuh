@@ -93,5 +93,19 @@ __device__ __forceinline__ void load_im2col_4d(uint32_t dst, const CUtensorMap *
         "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
         : "memory");
 }
+// CTA-pair forms (cta_group::2): the data lands in THIS CTA's shared memory, the completion is signalled on an mbarrier
+// given as a shared::cluster address (the pair leader's full barrier). Plain unicast loads of this GPU's own tensors.
+__device__ __forceinline__ void load_2d_pair(uint32_t dst, const CUtensorMap *m, uint32_t cluster_bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+                 "l"(reinterpret_cast<uint64_t>(m)), "r"(cluster_bar), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void load_im2col_4d_pair(uint32_t dst, const CUtensorMap *m, uint32_t cluster_bar, int c, int w, int h, int n,
+                                                    uint16_t off_w, uint16_t off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(dst),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(cluster_bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+        : "memory");
+}
 }  // namespace tma
 #endif

@@ -110,6 +110,14 @@ int dl4jb200_ctx_set_stream(dl4jb200_ctx *ctx, void *stream);
  * unbiased rounding per stored value (2^-12 relative) instead of a biased truncation per product. Meant to be
  * switched on together with DL4JB200_CONV_ALGO_TC_TF32; leave it off for FP32 parity runs. */
 #define DL4JB200_OPT_TF32_ACTIVATIONS 1
+/* DL4JB200_OPT_PAIR_TILES (default 0, or 1 when the environment holds DL4JB200_PAIR_TILES=1 at ctx_create): the tensor-core
+ * convolution GEMMs run 256-row tiles on pairs of CTAs (two SMs of one TPC, tcgen05 cta_group::2) wherever the layer has at
+ * least two 128-row tiles and 64 output columns, so that each SM streams only half of the filter tile. Convolution outputs
+ * are bit-identical either way (same products, same accumulation order per output element); epilogue batch-norm statistics
+ * are grouped per CTA and therefore differ in fp32 summation order. Off by default: measured on B200 it moves 25 % fewer
+ * bytes into the SMs but is 0-10 % slower on every ResNet-50 shape (the layers are bound by L2 sector reads of the im2col
+ * operand and by tile quantisation, not by per-SM fill) and 0-3 % faster on VGG16's (profiles/r02_pair_tiles.md). */
+#define DL4JB200_OPT_PAIR_TILES 2
 int dl4jb200_ctx_set_option(dl4jb200_ctx *ctx, int option, int value);
 void *dl4jb200_ctx_stream(dl4jb200_ctx *ctx);
 int dl4jb200_ctx_sync(dl4jb200_ctx *ctx);
