@@ -374,23 +374,38 @@ __global__ void __launch_bounds__(256) k_bn_act_maxpool_nhwc(const float *__rest
         const float4 c = __ldg(reinterpret_cast<const float4 *>(coef + 3 * (size_t)g.xcs) + q);
         float4 best = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX);
         int bi[4] = {0, 0, 0, 0};
+        auto tap = [&](float4 v, int t) {
+            v.x = dl4j_act((v.x - k.x) * a.x + c.x, act); v.y = dl4j_act((v.y - k.y) * a.y + c.y, act);
+            v.z = dl4j_act((v.z - k.z) * a.z + c.z, act); v.w = dl4j_act((v.w - k.w) * a.w + c.w, act);
+            v = dl4j_rnd4(v, rnd);
+            if (v.x > best.x) { best.x = v.x; bi[0] = t; }
+            if (v.y > best.y) { best.y = v.y; bi[1] = t; }
+            if (v.z > best.z) { best.z = v.z; bi[2] = t; }
+            if (v.w > best.w) { best.w = v.w; bi[3] = t; }
+        };
+        const int ih0 = (int)oh * g.sH - g.pT, iw0 = (int)ow * g.sW - g.pL;
+        if (KS && ih0 >= 0 && iw0 >= 0 && ih0 + KS <= g.H && iw0 + KS <= g.W) {
+            // window entirely inside the image (every window of an unpadded layer): all KS*KS loads are issued before the
+            // first use -- the bounds-checked loop below serialises them behind their branches and runs latency-bound
+            float4 v[KS ? KS * KS : 1];
+            const float *xp = x + (((size_t)b * g.H + ih0) * g.W + iw0) * g.xcs + (size_t)q * 4;
+#pragma unroll
+            for (int kh = 0; kh < KS; kh++)
+#pragma unroll
+                for (int kw = 0; kw < KS; kw++) v[kh * KS + kw] = *reinterpret_cast<const float4 *>(xp + ((size_t)kh * g.W + kw) * g.xcs);
+#pragma unroll
+            for (int t = 0; t < KS * KS; t++) tap(v[t], t);
+        } else {
 #pragma unroll KS ? KS : 1
-        for (int kh = 0; kh < kH; kh++) {
-            const int ih = (int)oh * g.sH - g.pT + kh;
-            if (ih < 0 || ih >= g.H) continue;
+            for (int kh = 0; kh < kH; kh++) {
+                const int ih = ih0 + kh;
+                if (ih < 0 || ih >= g.H) continue;
 #pragma unroll KS ? KS : 1
-            for (int kw = 0; kw < kW; kw++) {
-                const int iw = (int)ow * g.sW - g.pL + kw;
-                if (iw < 0 || iw >= g.W) continue;
-                float4 v = *reinterpret_cast<const float4 *>(x + (((size_t)b * g.H + ih) * g.W + iw) * g.xcs + (size_t)q * 4);
-                v.x = dl4j_act((v.x - k.x) * a.x + c.x, act); v.y = dl4j_act((v.y - k.y) * a.y + c.y, act);
-                v.z = dl4j_act((v.z - k.z) * a.z + c.z, act); v.w = dl4j_act((v.w - k.w) * a.w + c.w, act);
-                v = dl4j_rnd4(v, rnd);
-                const int t = kh * kW + kw;
-                if (v.x > best.x) { best.x = v.x; bi[0] = t; }
-                if (v.y > best.y) { best.y = v.y; bi[1] = t; }
-                if (v.z > best.z) { best.z = v.z; bi[2] = t; }
-                if (v.w > best.w) { best.w = v.w; bi[3] = t; }
+                for (int kw = 0; kw < kW; kw++) {
+                    const int iw = iw0 + kw;
+                    if (iw < 0 || iw >= g.W) continue;
+                    tap(*reinterpret_cast<const float4 *>(x + (((size_t)b * g.H + ih) * g.W + iw) * g.xcs + (size_t)q * 4), kh * kW + kw);
+                }
             }
         }
         const size_t o = (((size_t)b * g.Ho + oh) * g.Wo + ow) * g.ycs + (size_t)q * 4;

@@ -78,24 +78,40 @@ __global__ void __launch_bounds__(256) k_pool_fwd(const float *__restrict__ x, f
         int best[V];
 #pragma unroll
         for (int i = 0; i < V; i++) { acc[i] = type == DL4JB200_POOL_MAX ? -FLT_MAX : 0.f; best[i] = 0; }
-#pragma unroll KS ? KS : 1
-        for (int kh = 0; kh < kH; kh++) {
-            int ih = oh * g.sH - g.pT + kh * g.dH;
-            if (ih < 0 || ih >= g.H) continue;  // padding: -FLT_MAX for max (never wins), 0 for sums
-#pragma unroll KS ? KS : 1
-            for (int kw = 0; kw < kW; kw++) {
-                int iw = ow * g.sW - g.pL + kw * g.dW;
-                if (iw < 0 || iw >= g.W) continue;
-                Vec<V> v = vload<V>(x + offs<NHWC>(b, c, ih, iw, g.C, g.H, g.W, g.xcs));
+        auto tap = [&](const Vec<V> &v, int t) {
 #pragma unroll
-                for (int i = 0; i < V; i++) {
-                    if (type == DL4JB200_POOL_MAX) {
-                        if (v.v[i] > acc[i]) { acc[i] = v.v[i]; best[i] = kh * kW + kw; }
-                    } else if (type == DL4JB200_POOL_PNORM) {
-                        acc[i] += powf(fabsf(v.v[i]), (float)pnorm);
-                    } else {
-                        acc[i] += v.v[i];
-                    }
+            for (int i = 0; i < V; i++) {
+                if (type == DL4JB200_POOL_MAX) {
+                    if (v.v[i] > acc[i]) { acc[i] = v.v[i]; best[i] = t; }
+                } else if (type == DL4JB200_POOL_PNORM) {
+                    acc[i] += powf(fabsf(v.v[i]), (float)pnorm);
+                } else {
+                    acc[i] += v.v[i];
+                }
+            }
+        };
+        const int ih0 = oh * g.sH - g.pT, iw0 = ow * g.sW - g.pL;
+        if (KS && ih0 >= 0 && iw0 >= 0 && ih0 + (KS - 1) * g.dH < g.H && iw0 + (KS - 1) * g.dW < g.W) {
+            // window entirely inside the image: issue all KS*KS loads before the first use (the bounds-checked loop
+            // serialises them behind their branches and runs latency-bound)
+            Vec<V> v[KS ? KS * KS : 1];
+#pragma unroll
+            for (int kh = 0; kh < KS; kh++)
+#pragma unroll
+                for (int kw = 0; kw < KS; kw++)
+                    v[kh * KS + kw] = vload<V>(x + offs<NHWC>(b, c, ih0 + kh * g.dH, iw0 + kw * g.dW, g.C, g.H, g.W, g.xcs));
+#pragma unroll
+            for (int t = 0; t < KS * KS; t++) tap(v[t], t);
+        } else {
+#pragma unroll KS ? KS : 1
+            for (int kh = 0; kh < kH; kh++) {
+                int ih = ih0 + kh * g.dH;
+                if (ih < 0 || ih >= g.H) continue;  // padding: -FLT_MAX for max (never wins), 0 for sums
+#pragma unroll KS ? KS : 1
+                for (int kw = 0; kw < kW; kw++) {
+                    int iw = iw0 + kw * g.dW;
+                    if (iw < 0 || iw >= g.W) continue;
+                    tap(vload<V>(x + offs<NHWC>(b, c, ih, iw, g.C, g.H, g.W, g.xcs)), kh * kW + kw);
                 }
             }
         }
@@ -236,6 +252,9 @@ __global__ void __launch_bounds__(256, 4) k_maxpool_bwd_nhwc_fast(const float *_
 // The patch's four cells share their candidate windows, so eps / argmax are fetched once per window and patch instead
 // of once per window and cell: 4 window reads per 4 cells instead of 9 for k = 3 (the kernel is bound by those L2
 // reads). Per cell the contributions are added in the same order as k_maxpool_bwd_nhwc_fast (kh, kw ascending).
+// SMALL (kH, kW <= 3): a patch meets at most 2 x 2 windows, all fetched up front (8 independent loads in flight instead of
+// one dependent pair per loop iteration; same summation order per cell: window rows / columns descending = taps ascending).
+template <bool SMALL>
 __global__ void __launch_bounds__(256, 4) k_maxpool_bwd_nhwc_patch2(const float *__restrict__ eps, const int32_t *__restrict__ argmax,
                                                                    float *__restrict__ dx, PoolGeom g, int Hp, int Wp, size_t total) {
     size_t stride = (size_t)gridDim.x * blockDim.x;
@@ -255,25 +274,58 @@ __global__ void __launch_bounds__(256, 4) k_maxpool_bwd_nhwc_patch2(const float 
         for (int a = 0; a < 2; a++)
 #pragma unroll
             for (int d = 0; d < 2; d++) acc[a][d] = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int oh = oh_hi; oh >= oh_lo; oh--) {
-            // tap row of window oh that lands on patch row a: kh = th0 + a - 2*oh, valid when 0 <= kh < kH
-            const int kh0 = th0 - 2 * oh;
-            for (int ow = ow_hi; ow >= ow_lo; ow--) {
-                const int kw0 = tw0 - 2 * ow;
-                const size_t o = (((size_t)b * g.Ho + oh) * g.Wo + ow) * g.ycs + c;
-                const int4 am = *reinterpret_cast<const int4 *>(argmax + o);
-                const float4 e = *reinterpret_cast<const float4 *>(eps + o);
+        if (SMALL) {
+            int4 am[2][2];
+            float4 e[2][2];
 #pragma unroll
-                for (int a = 0; a < 2; a++) {
-                    const int kh = kh0 + a;
-                    if (kh < 0 || kh >= g.kH) continue;
+            for (int i = 0; i < 2; i++)
 #pragma unroll
-                    for (int d = 0; d < 2; d++) {
-                        const int kw = kw0 + d;
-                        if (kw < 0 || kw >= g.kW) continue;
-                        const int me = kh * g.kW + kw;
-                        acc[a][d].x += am.x == me ? e.x : 0.f; acc[a][d].y += am.y == me ? e.y : 0.f;
-                        acc[a][d].z += am.z == me ? e.z : 0.f; acc[a][d].w += am.w == me ? e.w : 0.f;
+                for (int j = 0; j < 2; j++) {
+                    const int oh = oh_hi - i, ow = ow_hi - j;
+                    am[i][j] = make_int4(-1, -1, -1, -1);  // matches no tap
+                    e[i][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (oh >= oh_lo && ow >= ow_lo) {
+                        const size_t o = (((size_t)b * g.Ho + oh) * g.Wo + ow) * g.ycs + c;
+                        am[i][j] = *reinterpret_cast<const int4 *>(argmax + o);
+                        e[i][j] = *reinterpret_cast<const float4 *>(eps + o);
+                    }
+                }
+#pragma unroll
+            for (int i = 0; i < 2; i++)
+#pragma unroll
+                for (int j = 0; j < 2; j++)
+#pragma unroll
+                    for (int a = 0; a < 2; a++) {
+                        const int kh = th0 - 2 * (oh_hi - i) + a;
+#pragma unroll
+                        for (int d = 0; d < 2; d++) {
+                            const int kw = tw0 - 2 * (ow_hi - j) + d;
+                            const int me = ((unsigned)kh < (unsigned)g.kH && (unsigned)kw < (unsigned)g.kW) ? kh * g.kW + kw : -2;
+                            acc[a][d].x += am[i][j].x == me ? e[i][j].x : 0.f; acc[a][d].y += am[i][j].y == me ? e[i][j].y : 0.f;
+                            acc[a][d].z += am[i][j].z == me ? e[i][j].z : 0.f; acc[a][d].w += am[i][j].w == me ? e[i][j].w : 0.f;
+                        }
+                    }
+        } else {
+            for (int oh = oh_hi; oh >= oh_lo; oh--) {
+                // tap row of window oh that lands on patch row a: kh = th0 + a - 2*oh, valid when 0 <= kh < kH
+                const int kh0 = th0 - 2 * oh;
+                for (int ow = ow_hi; ow >= ow_lo; ow--) {
+                    const int kw0 = tw0 - 2 * ow;
+                    const size_t o = (((size_t)b * g.Ho + oh) * g.Wo + ow) * g.ycs + c;
+                    const int4 am = *reinterpret_cast<const int4 *>(argmax + o);
+                    const float4 e = *reinterpret_cast<const float4 *>(eps + o);
+#pragma unroll
+                    for (int a = 0; a < 2; a++) {
+                        const int kh = kh0 + a;
+                        if (kh < 0 || kh >= g.kH) continue;
+#pragma unroll
+                        for (int d = 0; d < 2; d++) {
+                            const int kw = kw0 + d;
+                            if (kw < 0 || kw >= g.kW) continue;
+                            const int me = kh * g.kW + kw;
+                            acc[a][d].x += am.x == me ? e.x : 0.f; acc[a][d].y += am.y == me ? e.y : 0.f;
+                            acc[a][d].z += am.z == me ? e.z : 0.f; acc[a][d].w += am.w == me ? e.w : 0.f;
+                        }
                     }
                 }
             }
@@ -358,8 +410,8 @@ int dl4jb200_pool_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
         const int Hp = (g.H + 1) / 2, Wp = (g.W + 1) / 2;
         g.d_w = FastDiv((uint32_t)Wp); g.d_h = FastDiv((uint32_t)Hp);
         size_t total = (size_t)g.B * Hp * Wp * (g.xcs / 4);
-        DL4J_CUDA_TRY(dl4j_launch_pdl(k_maxpool_bwd_nhwc_patch2, dim3(pool_grid(ctx, total)), dim3(256), 0, ctx->stream, eps, argmax, dx, g,
-                                      Hp, Wp, total));
+        DL4J_CUDA_TRY(dl4j_launch_pdl((g.kH <= 3 && g.kW <= 3) ? k_maxpool_bwd_nhwc_patch2<true> : k_maxpool_bwd_nhwc_patch2<false>,
+                                      dim3(pool_grid(ctx, total)), dim3(256), 0, ctx->stream, eps, argmax, dx, g, Hp, Wp, total));
     } else if (layout == DL4JB200_NHWC && pool_type == DL4JB200_POOL_MAX && argmax && g.dH == 1 && g.dW == 1) {
         size_t total = (size_t)g.B * g.H * g.W * (g.xcs / 4);
         k_maxpool_bwd_nhwc_fast<<<pool_grid(ctx, total), 256, 0, ctx->stream>>>(eps, argmax, dx, g, total);
