@@ -62,7 +62,7 @@ int dl4jb200_ctx_create(int device, void *stream, dl4jb200_ctx **out) {
     c->round_act = 0;
     const char *pt = getenv("DL4JB200_PAIR_TILES");  // default of DL4JB200_OPT_PAIR_TILES for contexts of this process (A/B runs, tests)
     c->pair_tiles = (pt && pt[0] == '1') ? 1 : 0;
-    for (int i = 0; i < 4; i++) { c->ws[i] = nullptr; c->ws_bytes[i] = 0; }
+    for (int i = 0; i < DL4J_WS_SLOTS; i++) { c->ws[i] = nullptr; c->ws_bytes[i] = 0; }
     if (stream) {
         c->stream = (cudaStream_t)stream;
         c->own_stream = false;
@@ -82,7 +82,7 @@ int dl4jb200_ctx_destroy(dl4jb200_ctx *ctx) {
     for (auto &kv : ctx->mirrors) cudaFree(kv.second.dev);
     for (auto &kv : ctx->mirror_pool) cudaFree(kv.second);
     conv_filters_free(ctx);
-    for (int i = 0; i < 4; i++) if (ctx->ws[i]) cudaFree(ctx->ws[i]);
+    for (int i = 0; i < DL4J_WS_SLOTS; i++) if (ctx->ws[i]) cudaFree(ctx->ws[i]);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return DL4JB200_OK;
@@ -113,7 +113,7 @@ int dl4jb200_ctx_sync(dl4jb200_ctx *ctx) {
 
 size_t dl4jb200_ctx_workspace_bytes(dl4jb200_ctx *ctx) {
     size_t s = 0;
-    if (ctx) for (int i = 0; i < 4; i++) s += ctx->ws_bytes[i];
+    if (ctx) for (int i = 0; i < DL4J_WS_SLOTS; i++) s += ctx->ws_bytes[i];
     return s;
 }
 

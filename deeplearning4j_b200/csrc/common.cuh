@@ -17,6 +17,7 @@ struct MirrorBuf {
     int state;  // DL4JB200_BUF_HOST_NEWER / SYNCED / DEVICE_NEWER: which side holds the current contents
 };
 
+#define DL4J_WS_SLOTS 5
 struct FilterRegistry;
 void conv_filters_free(struct dl4jb200_ctx *ctx);
 struct dl4jb200_ctx {
@@ -26,9 +27,10 @@ struct dl4jb200_ctx {
     int sm_count;
     int round_act;  // DL4JB200_OPT_TF32_ACTIVATIONS: activation / epsilon producers store values rounded to TF32
     int pair_tiles = 0;  // DL4JB200_OPT_PAIR_TILES: 256-row tiles on CTA pairs (tcgen05 cta_group::2) where they apply
-    // scratch, grown on demand (never shrunk); slot 0: kernel partials / packed filters, slot 1: NHWC staging
-    void *ws[4];
-    size_t ws_bytes[4];
+    // scratch, grown on demand (never shrunk); slot 0: kernel partials / packed filters, slots 1-3: NHWC staging,
+    // slot 4: split-K partial accumulators of the dense-layer GEMMs
+    void *ws[DL4J_WS_SLOTS];
+    size_t ws_bytes[DL4J_WS_SLOTS];
     // A captured CUDA graph bakes scratch addresses (and tensor maps built on them) into its nodes: once frozen, a
     // request that would have to grow a region fails instead of freeing memory the graph still references.
     bool ws_frozen = false;

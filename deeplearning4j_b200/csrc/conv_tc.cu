@@ -661,14 +661,20 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_wgrad(const float *__restri
 // TMA for the BN x 32 filter tile; both signal the stage's mbarrier with their byte count. No per-element address
 // arithmetic is left on the SM; padding, stride and image borders are resolved by the TMA unit (zero fill).
 
+// Split-K (gridDim.z > 1): CTA (x, y, z) accumulates K-chunks [z * k_per_split, (z+1) * k_per_split) of its tile and stores the raw
+// accumulator at out + z * split_stride (the caller passes no bias, identity activation, and folds the splits with
+// k_splitk_finalize) -- for GEMMs with a handful of tiles and a long K, i.e. the dense layers at minibatch-sized M.
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_constant__ CUtensorMap tmA,
                                                               const __grid_constant__ CUtensorMap tmB,
                                                               const float *__restrict__ bias, float *__restrict__ out,
-                                                              TmaGemmGeom g, int n_valid, int out_cs, int act) {
+                                                              TmaGemmGeom g, int n_valid, int out_cs, int act, int k_per_split,
+                                                              size_t split_stride) {
     using L = SmemLayout<BN, STAGES>;
     const int rnd = act >> 8;
     act &= 0xff;
+    const int k_lo = (int)blockIdx.z * k_per_split, k_hi = min(g.num_k, k_lo + k_per_split);
+    out += (size_t)blockIdx.z * split_stride;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t a_base = base, b_base = base + STAGES * L::A_BYTES, bar_base = base + L::BAR_OFF;
@@ -687,6 +693,9 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 4) tmem_alloc<BN>(tmem_slot);
+    __syncthreads();
+    pdl_trigger();  // after the TMEM allocation (see k_conv_tc_gemm_tma_persist); no-ops under an ordinary launch
+    pdl_wait();
     float *bias_s = reinterpret_cast<float *>(smem_raw + (base - smem_u32(smem_raw)) + L::BIAS_OFF);
     if (tid < BN) bias_s[tid] = (bias && n0 + tid < n_valid) ? __ldg(bias + n0 + tid) : 0.f;
     tc_fence_before();
@@ -702,9 +711,9 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
             g.div_HWm.divmod((uint32_t)m0, img, r);
             g.div_Wm.divmod(r, oy, ox);
             const int w0 = (int)ox * g.sW + g.lowW, h0 = (int)oy * g.sH + g.lowH;
-            for (int it = 0; it < g.num_k; ++it) {
-                const int s = it % STAGES;
-                mbar_wait(empty_bar(s), ((it / STAGES) & 1) ^ 1);
+            for (int it = k_lo; it < k_hi; ++it) {
+                const int j = it - k_lo, s = j % STAGES;
+                mbar_wait(empty_bar(s), ((j / STAGES) & 1) ^ 1);
                 uint32_t tap, c0, kh, kw;
                 g.div_Cg.divmod((uint32_t)(it * BLOCK_K), tap, c0);
                 g.div_kW.divmod(tap, kh, kw);
@@ -761,15 +770,15 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
         }
     } else {
         constexpr uint32_t idesc = umma_idesc(BLOCK_M, BN, 0, 0);
-        for (int it = 0; it < g.num_k; ++it) {
-            const int s = it % STAGES;
-            mbar_wait(full_bar(s), (it / STAGES) & 1);
+        for (int j = 0; j < k_hi - k_lo; ++j) {
+            const int s = j % STAGES;
+            mbar_wait(full_bar(s), (j / STAGES) & 1);
             tc_fence_after();
             if (lane == 0) {
                 const uint64_t ad = umma_desc(a_base + s * L::A_BYTES, 16, 1024);
                 const uint64_t bd = umma_desc(b_base + s * L::B_BYTES, 16, 1024);
 #pragma unroll
-                for (int k = 0; k < BLOCK_K / 8; k++) umma_tf32(tmem_d, ad + 2u * k, bd + 2u * k, idesc, (it | k) ? 1u : 0u);
+                for (int k = 0; k < BLOCK_K / 8; k++) umma_tf32(tmem_d, ad + 2u * k, bd + 2u * k, idesc, (j | k) ? 1u : 0u);
                 umma_commit(empty_bar(s));
             }
             __syncwarp();
@@ -780,6 +789,50 @@ __global__ void __launch_bounds__(THREADS) k_conv_tc_gemm_tma(const __grid_const
     tc_fence_before();
     __syncthreads();
     if (warp == 4) tmem_dealloc<BN>(tmem_d);
+}
+
+// Folds the split-K partials of k_conv_tc_gemm_tma in split order (deterministic) and applies what the single-pass epilogue
+// would have: bias, activation, the optional fused backprop epilogue out = (acc + add) masked by mask > 0, TF32 rounding.
+__global__ void __launch_bounds__(256) k_splitk_finalize(const float *__restrict__ partial, float *__restrict__ out,
+                                                         const float *__restrict__ bias, const float *__restrict__ epi_add,
+                                                         const float *__restrict__ epi_mask, int M, int n_valid, int out_cs,
+                                                         int splits, size_t split_stride, int act) {
+    const int rnd = act >> 8;
+    act &= 0xff;
+    pdl_trigger();
+    pdl_wait();
+    const int Q = out_cs >> 2;
+    const size_t total = (size_t)M * Q, stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const int q = (int)(i % Q);
+        const size_t o = (i / Q) * out_cs + (size_t)q * 4;
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+        int sp = 0;
+        for (; sp + 1 < splits; sp += 2) {  // two independent chains: both loads of a round in flight; fixed combination order
+            const float4 u = *reinterpret_cast<const float4 *>(partial + (size_t)sp * split_stride + o);
+            const float4 w = *reinterpret_cast<const float4 *>(partial + (size_t)(sp + 1) * split_stride + o);
+            a0.x += u.x; a0.y += u.y; a0.z += u.z; a0.w += u.w;
+            a1.x += w.x; a1.y += w.y; a1.z += w.z; a1.w += w.w;
+        }
+        if (sp < splits) {
+            const float4 u = *reinterpret_cast<const float4 *>(partial + (size_t)sp * split_stride + o);
+            a0.x += u.x; a0.y += u.y; a0.z += u.z; a0.w += u.w;
+        }
+        float r[4] = {a0.x + a1.x, a0.y + a1.y, a0.z + a1.z, a0.w + a1.w};
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const int n = q * 4 + e;
+            float v = 0.f;
+            if (n < n_valid) {
+                v = dl4j_act(r[e] + (bias ? __ldg(bias + n) : 0.f), act);
+                if (epi_add) v += epi_add[o + e];
+                if (epi_mask && !(epi_mask[o + e] > 0.f)) v = 0.f;
+                v = dl4j_rnd(v, rnd);
+            }
+            r[e] = v;
+        }
+        *reinterpret_cast<float4 *>(out + o) = make_float4(r[0], r[1], r[2], r[3]);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1298,7 +1351,37 @@ static int launch_gemm_tma(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUte
         configured[ctx->device & 15] = true;
     }
     dim3 grid(dl4j_ceil_div(g.M, BLOCK_M), dl4j_ceil_div(out_cs, BN));
-    kern<<<grid, THREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act);
+    kern<<<grid, THREADS, L::BYTES, ctx->stream>>>(tmA, tmB, bias, out, g, n_valid, out_cs, act, g.num_k, (size_t)0);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+// split-K form: `splits` CTAs per tile write raw partials (row pitch out_cs, rows padded to whole tiles) into scratch slot 4,
+// k_splitk_finalize folds them into out
+template <int BN, int STAGES>
+static int launch_gemm_tma_splitk(dl4jb200_ctx *ctx, const CUtensorMap &tmA, const CUtensorMap &tmB, const TmaGemmGeom &g,
+                                  const float *bias, float *out, int n_valid, int out_cs, int act, int splits) {
+    using L = SmemLayout<BN, STAGES>;
+    auto kern = k_conv_tc_gemm_tma<BN, STAGES>;
+    static bool configured[16] = {false};
+    if (!configured[ctx->device & 15]) {
+        DL4J_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::BYTES));
+        configured[ctx->device & 15] = true;
+    }
+    const int m_tiles = dl4j_ceil_div(g.M, BLOCK_M), kps = dl4j_ceil_div(g.num_k, splits);
+    splits = dl4j_ceil_div(g.num_k, kps);  // no empty split
+    const size_t split_stride = (size_t)m_tiles * BLOCK_M * out_cs;
+    float *partial = (float *)dl4j_workspace(ctx, 4, (size_t)splits * split_stride * sizeof(float));
+    if (!partial) return DL4JB200_ERR_CUDA;
+    dim3 grid(m_tiles, dl4j_ceil_div(out_cs, BN), splits);
+    // n_valid = out_cs for the partial pass: every column of the tile is stored (the padding columns hold zeros)
+    DL4J_CUDA_TRY(dl4j_launch_pdl(kern, grid, dim3(THREADS), L::BYTES, ctx->stream, tmA, tmB, (const float *)nullptr, partial, g, out_cs, out_cs,
+                                  (int)DL4JB200_ACT_IDENTITY, kps, split_stride));
+    DL4J_CHECK_LAUNCH();
+    const size_t items = (size_t)g.M * (out_cs / 4);
+    const size_t blocks = (items + 255) / 256, cap = (size_t)ctx->sm_count * 8;
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_splitk_finalize, dim3((unsigned)(blocks < cap ? blocks : cap)), dim3(256), 0, ctx->stream, (const float *)partial,
+                                  out, bias, g.epi_add, g.epi_mask, g.M, n_valid, out_cs, splits, split_stride, act));
     DL4J_CHECK_LAUNCH();
     return DL4JB200_OK;
 }
@@ -1584,7 +1667,17 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
                              CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
     const int bn = tma_gemm_bn(ctx, g, n_rows_packed, out_cs, aligned_bias);
-    const bool pair = tma_gemm_pair(ctx, g, bn, aligned_bias);  // each CTA of a pair fetches half of the filter tile
+    // A handful of tiles and a long K (the dense layers: M = minibatch, i.e. one or two row tiles): split K over enough CTAs to
+    // fill the machine and fold the partial accumulators afterwards. Otherwise 4-32 CTAs walk hundreds of K-chunks one TMA
+    // round trip at a time (VGG16's 25088 -> 1000 output layer: 247 us for a 100 MB weight read).
+    int splits = 0;
+    if (!g.stat_out && !g.remap && out_cs % 4 == 0 && bn <= 128 && dl4j_ceil_div(g.M, tc::BLOCK_M) <= 2 && g.Kp / tc::BLOCK_K >= 32) {
+        const long long tiles = (long long)dl4j_ceil_div(g.M, tc::BLOCK_M) * dl4j_ceil_div(out_cs, bn);
+        splits = (int)(ctx->sm_count / tiles);
+        if (splits > g.Kp / tc::BLOCK_K / 8) splits = g.Kp / tc::BLOCK_K / 8;  // at least eight K-chunks per split
+        if (tiles * 4 > ctx->sm_count || splits < 2) splits = 0;
+    }
+    const bool pair = !splits && tma_gemm_pair(ctx, g, bn, aligned_bias);  // each CTA of a pair fetches half of the filter tile
     rc = tma_make_2d(&tmB, wpack, (uint64_t)n_rows_packed, (uint64_t)g.Kp, (uint64_t)g.Kp, (uint32_t)(pair ? bn / 2 : bn), CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
     TmaGemmGeom t;
@@ -1611,6 +1704,11 @@ static int conv_tc_gemm_tma(dl4jb200_ctx *ctx, const ConvGeom &g, const float *s
         t.rm_zero = !g.rm_keep && g.rm_sy <= 2 && g.rm_sx <= 2 && n_valid % bn == 0 && out_cs == n_valid && g.rm_sx * (g.Wm - 1) + g.rm_sx >= g.rm_W &&
                     g.rm_sy * (g.Hm - 1) + g.rm_sy >= g.rm_H;
         if (!t.rm_zero && !g.rm_keep) DL4J_CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)g.B * g.rm_H * g.rm_W * out_cs * sizeof(float), ctx->stream));
+    }
+    if (splits) {
+        if (bn == 128) return tc::launch_gemm_tma_splitk<128, 3>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act, splits);
+        if (bn == 64) return tc::launch_gemm_tma_splitk<64, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act, splits);
+        return tc::launch_gemm_tma_splitk<32, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act, splits);
     }
     if (bn == 256) return tc::launch_gemm_tma_persist<256, 4>(ctx, tmA, tmB, t, bias, out, n_valid, out_cs, act, pair);
     if (!aligned_bias) {  // the persistent epilogue reads the bias with 128-bit loads
