@@ -63,6 +63,10 @@ CONV_CASES = [  # B, Cin, H, W, Cout, k, s, p, d, mode
     (3, 16, 50, 1, 24, (3, 1), (1, 1), (1, 0), (1, 1), 1),
     (2, 32, 41, 1, 32, (5, 1), (2, 1), (0, 0), (1, 1), 2),
     (2, 64, 33, 1, 64, (3, 1), (1, 1), (0, 0), (2, 1), 2),      # dilated, SAME, TMA-eligible channel count
+    # DenseLayer / OutputLayer shapes run as 1x1 convolutions on a 1x1 map: M = minibatch (one row tile), long K -> the split-K
+    # form of the GEMM (partial accumulators per K range, ordered fold with bias), ragged N = 1000; backprop-data N = 2048
+    (64, 2048, 1, 1, 1000, (1, 1), (1, 1), (0, 0), (1, 1), 1),
+    (130, 1024, 1, 1, 1024, (1, 1), (1, 1), (0, 0), (1, 1), 1),  # two row tiles (one ragged), split-K in both directions
 ]
 
 
@@ -191,6 +195,7 @@ def test_tf32_activation_rounding_option(H, ctx, oracle):
     (3, 256, 7, 7, 64, (1, 1), (1, 1), (0, 0), 1),   # 1x1, ragged last M tile (147 rows)
     (2, 40, 9, 9, 24, (3, 3), (1, 1), (1, 1), 2),        # channel counts that are not tile multiples
     (2, 64, 14, 14, 128, (1, 1), (2, 2), (0, 0), 1),  # strided 1x1: compact walk, elementwise fallback
+    (64, 2048, 1, 1, 1024, (1, 1), (1, 1), (0, 0), 1),  # dense-shaped: split-K GEMM, the fused epilogue runs in its fold
 ])
 @pytest.mark.parametrize("algo_name", ["fp32", "tf32"])
 def test_conv_bwd_data_fused_epilogue(H, ctx, oracle, case, algo_name):
