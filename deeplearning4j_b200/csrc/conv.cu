@@ -556,7 +556,14 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
     // filter-gradient GEMM as an extra accumulator column (delta^T x ones: exact products, fp32 accumulation) instead
     // of a separate column-sum pass over delta.
     const bool db_fused = dw && db && tcore && gf.use_tma && ctx->round_act;
-    if (dw) {
+    // One split of a 1x1 filter whose K needs no padding: the GEMM's [c_out][K] output IS dW (and its ones column IS db), so it
+    // writes them in place and the reduce / un-pack pass -- a 2 x |W| copy for the dense layers, whose M is the minibatch --
+    // is skipped (AlexNet's three dense layers: 0.2 ms of a 2.5 ms step).
+    const bool dw_direct = dw && tcore && gf.use_tma && splits == 1 && gf.taps == 1 && gf.Kp == d->c_in && ((uintptr_t)dw & 15) == 0 &&
+                           (!db || db_fused);
+    if (dw_direct) {
+        if ((rc = conv_tc_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, dw, d->c_out, 1, db_fused ? db : nullptr))) return rc;
+    } else if (dw) {
         float *dbp = db_fused ? colp : nullptr;  // [splits][rows_w], carved from the same scratch request below
         if (tcore) rc = conv_tc_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits, dbp);
         else rc = conv_ffma_wgrad(ctx, gf, xs, ds, delta_cs, d->c_out, partial, rows_w, splits);
