@@ -10,28 +10,35 @@
 // with unit stride along W: exactly what the generic TMA kernels consume. The caller stores the image row-packed:
 // [B][H][row_pitch_px][4] with the image starting at pixel pL+1 (so every window start is pixel-pair aligned with one
 // leading dummy tap) and zeros in the padding columns; padding in H is resolved by the TMA unit.
+//
+// Filter rows wider than 7 taps (AlexNet's 11x11/4) take two 32-float K-chunks per row: chunk c holds window pixels
+// 8c .. 8c+7, fetched from the same tensor map with a W offset of 8c packed pixels = 8c / stride_w window starts -- which is
+// why k_w in 8..15 needs a stride_w that divides 8. The second chunk of an 11-tap row is half padding (4 of its 8 taps).
 #include "conv_common.cuh"
 #include "conv_tma.cuh"
 
 int conv_tc_wgrad_splits(dl4jb200_ctx *ctx, const ConvGeom &g, int c_out);
 
-// W[co][ci][kh][kw] -> Wp[n][kh*32 + kp*8 + j*4 + ci],  kw = 2*kp + j - 1  (kw == -1 / >= kW / ci >= Cin: zero)
+// chunks of 8 window pixels per filter row: the window is one dummy tap + k_w real ones
+static inline int stem_chunks(const dl4jb200_conv_desc *d) { return (d->k_w + 1 + 7) / 8; }
+
+// W[co][ci][kh][kw] -> Wp[n][(kh*nchunk + c)*32 + p8*4 + ci],  kw = 8*c + p8 - 1  (kw == -1 / >= kW / ci >= Cin: zero)
 __global__ void __launch_bounds__(256) k_pack_stem_filter(const float *__restrict__ w, float *__restrict__ wp, int Cout, int Cin,
-                                                          int kH, int kW, int Kp, int rows_p) {
+                                                          int kH, int kW, int Kp, int rows_p, int nchunk) {
     size_t total = (size_t)rows_p * Kp, stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
         int n = (int)(i / Kp), k = (int)(i % Kp);
-        int kh = k >> 5, r = k & 31, kp = r >> 3, j = (r >> 2) & 1, ci = r & 3, kw = 2 * kp + j - 1;
+        int kc = k >> 5, r = k & 31, kh = kc / nchunk, c = kc - kh * nchunk, ci = r & 3, kw = 8 * c + (r >> 2) - 1;
         float v = 0.f;
         if (n < Cout && kh < kH && kw >= 0 && kw < kW && ci < Cin) v = w[(((size_t)n * Cin + ci) * kH + kh) * kW + kw];
         wp[i] = to_tf32_rna(v);
     }
 }
 
-// dW[co][ci][kh][kw] = sum_s partial[s][co][kh*32 + ((kw+1)>>1)*8 + ((kw+1)&1)*4 + ci]
+// dW[co][ci][kh][kw] = sum_s partial[s][co][(kh*nchunk + (kw+1)/8)*32 + ((kw+1)%8)*4 + ci]
 __global__ void __launch_bounds__(256) k_stem_wgrad_finalize(const float *__restrict__ partial, float *__restrict__ dw, int Cout,
                                                              int Cin, int kH, int kW, int Kp, int rows_p, int splits,
-                                                             const float *__restrict__ db_partial, float *__restrict__ db) {
+                                                             const float *__restrict__ db_partial, float *__restrict__ db, int nchunk) {
     size_t total = (size_t)Cout * Cin * kH * kW, stride = (size_t)gridDim.x * blockDim.x;
     if (db_partial) {  // [splits][rows_p] sums from the GEMM's ones column
         for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)Cout; i += stride) {
@@ -45,7 +52,7 @@ __global__ void __launch_bounds__(256) k_stem_wgrad_finalize(const float *__rest
         size_t t = i / kW;
         int kh = (int)(t % kH); t /= kH;
         int ci = (int)(t % Cin), co = (int)(t / Cin);
-        int k = kh * 32 + ((kw + 1) >> 1) * 8 + ((kw + 1) & 1) * 4 + ci;
+        int k = (kh * nchunk + ((kw + 1) >> 3)) * 32 + ((kw + 1) & 7) * 4 + ci;
         const float *p = partial + (size_t)co * Kp + k;
         float acc = 0.f;
         for (int s = 0; s < splits; s++) acc += p[(size_t)s * rows_p * Kp];
@@ -69,13 +76,13 @@ __global__ void __launch_bounds__(256) k_nchw_to_rowpack4(const float *__restric
 
 static int stem_check(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int row_pitch_px, const char *who) {
     DL4J_REQUIRE(ctx && d, "%s: NULL argument", who);
-    if (d->c_in > 4 || d->stride_w < 1 || d->stride_w > 8 || d->k_w > 7 || d->k_h > 16 || d->dil_h != 1 || d->dil_w != 1 ||
-        !tma_driver_ready() || d->pad_top > 127 || d->stride_h > 8) {
-        dl4j_set_error("%s: row-packed path needs c_in <= 4, stride_w <= 8, k_w <= 7, no dilation", who);
+    if (d->c_in > 4 || d->stride_w < 1 || d->stride_w > 8 || d->k_w > 15 || (d->k_w > 7 && 8 % d->stride_w != 0) || d->k_h > 16 ||
+        d->dil_h != 1 || d->dil_w != 1 || !tma_driver_ready() || d->pad_top > 127 || d->stride_h > 8) {
+        dl4j_set_error("%s: row-packed path needs c_in <= 4, stride_w <= 8, k_w <= 7 (<= 15 when stride_w divides 8), no dilation", who);
         return DL4JB200_NOT_SUPPORTED;
     }
-    DL4J_REQUIRE(row_pitch_px % 2 == 0 && row_pitch_px >= d->stride_w * (d->out_w - 1) + 8 && row_pitch_px >= d->pad_left + 1 + d->in_w,
-                 "%s: row_pitch_px must be even and >= max(stride_w*(out_w-1) + 8, pad_left + 1 + in_w)", who);
+    DL4J_REQUIRE(row_pitch_px % 2 == 0 && row_pitch_px >= d->stride_w * (d->out_w - 1) + 8 * stem_chunks(d) && row_pitch_px >= d->pad_left + 1 + d->in_w,
+                 "%s: row_pitch_px must be even and >= max(stride_w*(out_w-1) + 8*chunks, pad_left + 1 + in_w)", who);
     return DL4JB200_OK;
 }
 
@@ -84,7 +91,9 @@ static int stem_xmap(CUtensorMap *tm, const dl4jb200_conv_desc *d, const float *
     // tensor {C = 32 floats, W = out_w window starts (pitch stride_w pixels = 4*stride_w floats), H = in_h rows, N}; taps only
     // along H. Window ow covers packed pixels stride_w*ow .. +7, i.e. image columns stride_w*ow - pad_left - 1 .. : one
     // leading dummy tap, then the k_w <= 7 real ones (the filter is packed accordingly, independent of the stride).
-    return tma_make_im2col_pitched(tm, xp, d->batch, d->in_h, d->out_w, 32, 4 * d->stride_w, (long long)row_pitch_px * 4,
+    // (a second chunk of a wide filter row starts 8 / stride_w windows further right: the W extent includes those starts)
+    const int extra = (stem_chunks(d) - 1) * (8 / d->stride_w);
+    return tma_make_im2col_pitched(tm, xp, d->batch, d->in_h, d->out_w + extra, 32, 4 * d->stride_w, (long long)row_pitch_px * 4,
                                    (long long)d->in_h * row_pitch_px * 4, 0, -d->pad_top, d->out_w, d->out_h, 1, d->stride_h, pixels, swz);
 }
 
@@ -109,20 +118,23 @@ static int rowpack_fwd_impl(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, cons
                  "conv_rowpack_fwd: bad output / input buffer");
     if (act < 0 || act > DL4JB200_ACT_LEAKYRELU) { dl4j_set_error("conv_rowpack_fwd: activation %d not handled", act); return DL4JB200_NOT_SUPPORTED; }
     if (bias && ((uintptr_t)bias & 15)) { dl4j_set_error("conv_rowpack_fwd: bias must be 16-byte aligned"); return DL4JB200_NOT_SUPPORTED; }
-    const int Kp = d->k_h * 32, rows_p = dl4j_round_up(z_cs, 256);
+    const int nchunk = stem_chunks(d), Kp = d->k_h * nchunk * 32, rows_p = dl4j_round_up(z_cs, 256);
     float *wp = (float *)dl4j_workspace(ctx, 0, (size_t)rows_p * Kp * sizeof(float));
     if (!wp) return DL4JB200_ERR_CUDA;
-    k_pack_stem_filter<<<dl4j_ceil_div((long long)rows_p * Kp, 256), 256, 0, ctx->stream>>>(w, wp, d->c_out, d->c_in, d->k_h, d->k_w, Kp, rows_p);
+    k_pack_stem_filter<<<dl4j_ceil_div((long long)rows_p * Kp, 256), 256, 0, ctx->stream>>>(w, wp, d->c_out, d->c_in, d->k_h, d->k_w, Kp, rows_p,
+                                                                                            nchunk);
     DL4J_CHECK_LAUNCH();
     alignas(64) CUtensorMap tmA, tmB;
     if ((rc = stem_xmap(&tmA, d, xp, row_pitch_px, 128, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
     const int bn = z_cs > 64 ? 128 : (z_cs > 32 ? 64 : 32);
     if ((rc = tma_make_2d(&tmB, wp, (uint64_t)rows_p, (uint64_t)Kp, (uint64_t)Kp, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
     tcgeom::TmaGemmGeom t;
-    t.M = d->batch * d->out_h * d->out_w; t.num_k = d->k_h; t.kW = 1; t.dH = 1; t.dW = 1; t.sH = d->stride_h; t.sW = 1;
+    // K-chunk it = (filter row it / nchunk, chunk it % nchunk): the kernels read it as a "tap" (kh, kw) with W dilation 8 / stride_w
+    t.M = d->batch * d->out_h * d->out_w; t.num_k = d->k_h * nchunk; t.kW = nchunk; t.dH = 1; t.dW = nchunk > 1 ? 8 / d->stride_w : 1;
+    t.sH = d->stride_h; t.sW = 1;
     t.lowH = -d->pad_top; t.lowW = 0;
     t.div_Wm = FastDiv((uint32_t)d->out_w); t.div_HWm = FastDiv((uint32_t)(d->out_h * d->out_w));
-    t.div_Cg = FastDiv(32u); t.div_kW = FastDiv(1u);
+    t.div_Cg = FastDiv(32u); t.div_kW = FastDiv((uint32_t)nchunk);
     t.remap = 0; t.rm_sy = t.rm_sx = 1; t.rm_H = d->out_h; t.rm_W = d->out_w;
     const int act_code = act | ((ctx->round_act && act != DL4JB200_ACT_IDENTITY) ? 0x100 : 0);
     if (stat_partial) {  // batch-norm statistics in the epilogue (see dl4jb200_conv_fwd_bnstats)
@@ -158,7 +170,7 @@ int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, 
     if (rc) return rc;
     DL4J_REQUIRE(xp && delta && dw && delta_cs >= d->c_out && delta_cs % 4 == 0 && ((uintptr_t)delta & 15) == 0 && ((uintptr_t)xp & 15) == 0,
                  "conv_rowpack_wgrad: bad buffer");
-    const int Kp = d->k_h * 32, rows_w = dl4j_round_up(d->c_out, 128), M = d->batch * d->out_h * d->out_w;
+    const int nchunk = stem_chunks(d), Kp = d->k_h * nchunk * 32, rows_w = dl4j_round_up(d->c_out, 128), M = d->batch * d->out_h * d->out_w;
     ConvGeom g;  // only the fields the split heuristic reads
     g.Kp = Kp; g.M = M;
     const int splits = conv_tc_wgrad_splits(ctx, g, d->c_out);
@@ -173,13 +185,14 @@ int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, 
     if ((rc = tma_make_2d(&tmD, delta, (uint64_t)M, (uint64_t)delta_cs, (uint64_t)delta_cs, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))) return rc;
     if ((rc = stem_xmap(&tmX, d, xp, row_pitch_px, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))) return rc;
     tcgeom::TmaWgradGeom t;
-    t.M = M; t.kW = 1; t.dH = 1; t.dW = 1; t.sH = d->stride_h; t.sW = 1; t.lowH = -d->pad_top; t.lowW = 0; t.Kp = Kp;
+    t.M = M; t.kW = nchunk; t.dH = 1; t.dW = nchunk > 1 ? 8 / d->stride_w : 1; t.sH = d->stride_h; t.sW = 1; t.lowH = -d->pad_top; t.lowW = 0;
+    t.Kp = Kp;
     t.div_Wm = FastDiv((uint32_t)d->out_w); t.div_HWm = FastDiv((uint32_t)(d->out_h * d->out_w));
-    t.div_Cg = FastDiv(32u); t.div_kW = FastDiv(1u);
+    t.div_Cg = FastDiv(32u); t.div_kW = FastDiv((uint32_t)nchunk);
     if ((rc = conv_tc_wgrad_tma_raw(ctx, tmD, tmX, t, partial, rows_w, splits, mps, dbp))) return rc;
     size_t total = (size_t)d->c_out * d->c_in * d->k_h * d->k_w;
     k_stem_wgrad_finalize<<<dl4j_ceil_div((long long)total, 256), 256, 0, ctx->stream>>>(partial, dw, d->c_out, d->c_in, d->k_h, d->k_w,
-                                                                                    Kp, rows_w, splits, dbp, db);
+                                                                                    Kp, rows_w, splits, dbp, db, nchunk);
     DL4J_CHECK_LAUNCH();
     if (db && !db_fused) return dl4jb200_bias_grad(ctx, delta, M, delta_cs, d->c_out, db);
     return DL4JB200_OK;

@@ -233,8 +233,8 @@ class Network:
         self.labels = None
 
     def _plan_stem(self):
-        """First-layer convolution on <= 4 channels with stride_w 2 (ResNet-50's 7x7/2): keep the minibatch row-packed
-        so the TMA-fed kernels can run it (dl4jb200_conv_rowpack_*)."""
+        """First-layer convolution on <= 4 channels (ResNet-50's 7x7/2, VGG16's 3x3/1, LeNet's 5x5/1, AlexNet's 11x11/4): keep
+        the minibatch row-packed so the TMA-fed kernels can run it (dl4jb200_conv_rowpack_*)."""
         self.stem = None
         if self.algo != _lib.ALGO_TC_TF32:
             return
@@ -246,10 +246,11 @@ class Network:
             return
         v = self.vmap[users[0]]
         src, d = self._conv_desc(v)
-        if src != inp or d.c_in > 4 or d.stride_w > 8 or d.k_w > 7 or d.k_h > 16 or d.dil_h != 1 or d.dil_w != 1 \
-                or v["act"] not in ("identity", "relu") or v.get("dropout"):
+        if src != inp or d.c_in > 4 or d.stride_w > 8 or d.k_w > 15 or (d.k_w > 7 and 8 % d.stride_w) or d.k_h > 16 \
+                or d.dil_h != 1 or d.dil_w != 1 or v["act"] not in ("identity", "relu") or v.get("dropout"):
             return
-        pitch = max(d.stride_w * (d.out_w - 1) + 8, d.pad_left + 1 + d.in_w)
+        chunks = (d.k_w + 1 + 7) // 8  # 8-pixel K-chunks per filter row (AlexNet's 11x11/4: two)
+        pitch = max(d.stride_w * (d.out_w - 1) + 8 * chunks, d.pad_left + 1 + d.in_w)
         pitch += pitch % 2
         self.stem = (v["name"], pitch, d.pad_left + 1)
         self.out[inp] = self._buf(self.B, d.in_h, pitch, 4)  # padding columns stay zero

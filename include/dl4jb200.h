@@ -201,11 +201,12 @@ int dl4jb200_conv_bwd(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, const floa
  * (ConvolutionLayer.java:257). dl4jb200_conv_bwd computes it too; this is for callers that split the backward. */
 int dl4jb200_bias_grad(dl4jb200_ctx *ctx, const float *delta, int M, int cs, int C, float *db);
 
-/* Row-packed first-layer ("stem") convolution: c_in <= 4, stride_w <= 8, k_w <= 7, no dilation -- ResNet-50's
- * 7x7/2 on 3 channels (deeplearning4j-zoo/.../zoo/model/ResNet50.java:181-186), VGG16's 3x3/1, LeNet's 5x5/1. Same arithmetic as
+/* Row-packed first-layer ("stem") convolution: c_in <= 4, stride_w <= 8, k_w <= 7 (k_w <= 15 when stride_w divides 8: the
+ * filter row then takes two 8-pixel K-chunks), no dilation -- ResNet-50's 7x7/2 on 3 channels
+ * (deeplearning4j-zoo/.../zoo/model/ResNet50.java:181-186), VGG16's 3x3/1, LeNet's 5x5/1, AlexNet's 11x11/4. Same arithmetic as
  * dl4jb200_conv_fwd / the filter-gradient half of dl4jb200_conv_bwd, but the input is held row-packed so that TMA can
  * feed the tensor cores: xp = [B][in_h][row_pitch_px][4] floats, image pixel x at column pad_left + 1 + x, every other
- * column (and channel 3) zero; row_pitch_px even and >= max(stride_w*(out_w-1) + 8, pad_left + 1 + in_w). Padding rows are not
+ * column (and channel 3) zero; row_pitch_px even and >= max(stride_w*(out_w-1) + 8*ceil((k_w+1)/8), pad_left + 1 + in_w). Padding rows are not
  * stored (the TMA unit zero-fills them). Returns NOT_SUPPORTED when the shape does not qualify.
  * dl4jb200_nchw_to_rowpack4 writes a DL4J-layout minibatch into such a buffer (pads must already be zero). */
 int dl4jb200_nchw_to_rowpack4(dl4jb200_ctx *ctx, const float *src, float *dst, int B, int C, int H, int W, int row_pitch_px,

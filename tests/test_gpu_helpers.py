@@ -672,7 +672,10 @@ def test_relayout_roundtrip(H, ctx):
                                   (2, 3, 24, 28, 64, 3, 1, 1),    # VGG16-style 3x3 stride 1
                                   (3, 1, 28, 28, 20, 5, 1, 2),    # LeNet's 5x5 stride 1
                                   (2, 3, 33, 29, 32, 7, 4, 2),    # stride 4
-                                  (2, 2, 19, 23, 24, 5, 3, 0)])   # stride 3, no padding
+                                  (2, 2, 19, 23, 24, 5, 3, 0),    # stride 3, no padding
+                                  (2, 3, 59, 63, 64, 11, 4, 2),   # AlexNet's 11x11 stride 4: two 8-pixel K-chunks per filter row
+                                  (2, 3, 40, 44, 32, 9, 2, 4),    # 9 taps, stride 2 (second chunk two windows... four starts right)
+                                  (3, 4, 21, 25, 16, 15, 1, 7)])  # the widest row: 15 taps + the dummy fill both chunks
 def test_rowpacked_stem_conv_vs_oracle(H, ctx, oracle, case):
     """dl4jb200_conv_rowpack_fwd / _wgrad (TMA-fed stem path) against the oracle's ordinary convolution."""
     from deeplearning4j_b200 import _lib
@@ -685,7 +688,7 @@ def test_rowpacked_stem_conv_vs_oracle(H, ctx, oracle, case):
     zr = oracle.conv_fwd(x, w, b, stride=(s, s), pad=(p, p))
     delta = rng.standard_normal(zr.shape).astype(np.float32)
     dwr, dbr, _ = oracle.conv_bwd(x, w, delta, stride=(s, s), pad=(p, p), need_dx=False)
-    pitch = max(s * (d.out_w - 1) + 8, p + 1 + W)
+    pitch = max(s * (d.out_w - 1) + 8 * ((k + 1 + 7) // 8), p + 1 + W)
     pitch += pitch % 2
     zcs = (Cout + 3) // 4 * 4
     dev = Dev(ctx)
