@@ -247,7 +247,7 @@ class Network:
         v = self.vmap[users[0]]
         src, d = self._conv_desc(v)
         if src != inp or d.c_in > 4 or d.stride_w > 8 or d.k_w > 15 or (d.k_w > 7 and 8 % d.stride_w) or d.k_h > 16 \
-                or d.dil_h != 1 or d.dil_w != 1 or v["act"] not in ("identity", "relu") or v.get("dropout"):
+                or d.dil_h != 1 or d.dil_w != 1 or v["act"] not in ("identity", "relu"):
             return
         chunks = (d.k_w + 1 + 7) // 8  # 8-pixel K-chunks per filter row (AlexNet's 11x11/4: two)
         pitch = max(d.stride_w * (d.out_w - 1) + 8 * chunks, d.pad_left + 1 + d.in_w)
@@ -323,13 +323,18 @@ class Network:
             n, op = v["name"], v["op"]
             if not v.get("dropout"):
                 continue
-            if op not in ("conv", "dense", "output", "pool") or (self.stem and self.stem[0] == n) or n in self.fold_pad:
+            if op not in ("conv", "dense", "output", "pool") or n in self.fold_pad:
                 raise NotImplementedError(f"dropout on {op} vertex {n}")
             x, xcs = self._src(v["in"][0])
             m = np.ascontiguousarray(masks[n], np.float32)
             with t.cuda.stream(self.stream):
                 dev = t.zeros_like(x)
-                if m.ndim == 4:
+                if self.stem and self.stem[0] == n:  # the first layer's input is held row-packed: so is its mask
+                    Bb, Cc, Hh, Ww = m.shape
+                    tmp = t.from_numpy(m).to(self.dev)
+                    self._call("dl4jb200_nchw_to_rowpack4", self._ptr(tmp), self._ptr(dev), Bb, Cc, Hh, Ww, self.stem[1], self.stem[2])
+                    self.stream.synchronize()
+                elif m.ndim == 4:
                     Bb, Cc, Hh, Ww = m.shape
                     tmp = t.from_numpy(m).to(self.dev)
                     self._call("dl4jb200_nchw_to_nhwc", self._ptr(tmp), self._ptr(dev), Bb, Cc, Hh, Ww, xcs)

@@ -5,7 +5,7 @@ tail -4 gpurun_out/r02_tests.log
 python scripts/one_step.py 1 1 > gpurun_out/one_step_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 4000 --csv --log-file gpurun_out/r02_launches_all.csv python scripts/one_step.py 1 1 > gpurun_out/ncu1.log 2>&1
 echo "launch list rc=$?"
-python scripts/agg_launches.py gpurun_out/r02_launches_all.csv --last-step k_nchw_to_rowpack4 --out gpurun_out/r02_launches_step.csv > gpurun_out/r02_launches_step.summary.txt; head -3 gpurun_out/r02_launches_step.summary.txt
+python scripts/agg_launches.py gpurun_out/r02_launches_all.csv --last-step k_pack_stem_filter --out gpurun_out/r02_launches_step.csv > gpurun_out/r02_launches_step.summary.txt; head -3 gpurun_out/r02_launches_step.summary.txt
 python scripts/conv_traffic.py gpurun_out/r02_launches_step.csv gpurun_out/r02_conv_traffic.json
 rm -f gpurun_out/r02_launches_all.csv
 cp gpurun_out/r02_conv_traffic.json profiles/r02_conv_traffic.json

@@ -173,6 +173,10 @@ def replay_step(net, model, x, lab, masks=None, fp_tol=1e-4, grad_tol=1e-4, para
         """the layer's input as the GPU saw it (dropped copy when the layer has dropout)."""
         n = v["name"]
         if n in net.drop:
+            if getattr(net, "stem", None) and net.stem[0] == n:  # row-packed first layer: [B, H, pitch, 4], image at column x_off
+                Cc, Hh, Ww = net.shapes[v["in"][0]]
+                a = net.drop[n].cpu().numpy()
+                return np.ascontiguousarray(a[:, :, net.stem[2]:net.stem[2] + Ww, :Cc].transpose(0, 3, 1, 2))
             return _nchw(net, net.drop[n], v["in"][0])
         return act_of(v["in"][0])
 
