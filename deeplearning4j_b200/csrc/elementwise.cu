@@ -402,11 +402,30 @@ __global__ void __launch_bounds__(256) k_score_fold(const double *partial, int n
 }
 
 // ---------------------------------------------------------------- gradient normalisation (BaseMultiLayerUpdater.preApply)
+// (a gradient block starts anywhere in the flat vector: scalar head up to the first 16-byte boundary, 128-bit body with two
+// loads in flight and four independent double accumulators per thread, scalar tail -- the one-float-per-iteration form ran
+// at 1.3 TB/s on its dependent double-add chain)
 __global__ void __launch_bounds__(256) k_sumsq_partial(const float *__restrict__ g, size_t n, double *partial) {
     __shared__ double s[256];
-    double a = 0.0;
-    size_t stride = (size_t)gridDim.x * blockDim.x;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) { double v = g[i]; a += v * v; }
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+    size_t head = ((16 - ((uintptr_t)g & 15)) & 15) >> 2;
+    if (head > n) head = n;
+    const size_t n4 = (n - head) >> 2, tail0 = head + (n4 << 2);
+    const float4 *g4 = reinterpret_cast<const float4 *>(g + head);
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    size_t i = tid;
+    for (; i + stride < n4; i += 2 * stride) {
+        const float4 u = g4[i], w = g4[i + stride];
+        a0 += (double)u.x * u.x + (double)w.x * w.x; a1 += (double)u.y * u.y + (double)w.y * w.y;
+        a2 += (double)u.z * u.z + (double)w.z * w.z; a3 += (double)u.w * u.w + (double)w.w * w.w;
+    }
+    if (i < n4) {
+        const float4 u = g4[i];
+        a0 += (double)u.x * u.x; a1 += (double)u.y * u.y; a2 += (double)u.z * u.z; a3 += (double)u.w * u.w;
+    }
+    if (tid < head) { const double v = g[tid]; a0 += v * v; }
+    if (tail0 + tid < n) { const double v = g[tail0 + tid]; a1 += v * v; }  // < 4 elements
+    const double a = (a0 + a1) + (a2 + a3);
     s[threadIdx.x] = a;
     __syncthreads();
     for (int o = 128; o; o >>= 1) {
