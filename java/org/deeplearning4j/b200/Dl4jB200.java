@@ -39,6 +39,7 @@ public class Dl4jB200 {
     public static native int dl4jb200_ctx_destroy(@Cast("dl4jb200_ctx*") Pointer ctx);
     public static native int dl4jb200_ctx_sync(@Cast("dl4jb200_ctx*") Pointer ctx);
     public static final int OPT_TF32_ACTIVATIONS = 1;
+    public static final int OPT_PAIR_TILES = 2;   // 256-row tiles on CTA pairs (off by default, see dl4jb200.h)
     public static native int dl4jb200_ctx_set_option(@Cast("dl4jb200_ctx*") Pointer ctx, int option, int value);
     // optional fast paths (INTEGRATION.md): pre-packed filters, fused epsilon fan-in + ReLU backprop, mask-fed dropout
     public static native int dl4jb200_filter_register(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer d,
@@ -59,6 +60,11 @@ public class Dl4jB200 {
                     @Const FloatPointer gamma, @Const FloatPointer beta, FloatPointer gMean, FloatPointer gVar, FloatPointer saveMean,
                     FloatPointer saveStd, int b, int c, int h, int w, int cs, double decay, double eps, int minibatch, int act,
                     @Const FloatPointer residual, @Const FloatPointer pivot, @Const FloatPointer statPartial, int statRows);
+    public static native int dl4jb200_bn_fwd_prestats_maxpool(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, FloatPointer yPool,
+                    IntPointer argmax, @Const FloatPointer gamma, @Const FloatPointer beta, FloatPointer gMean, FloatPointer gVar,
+                    FloatPointer saveMean, FloatPointer saveStd, int b, int c, int h, int w, int cs, double decay, double eps,
+                    int minibatch, int act, @Const FloatPointer pivot, @Const FloatPointer statPartial, int statRows,
+                    @Cast("const dl4jb200_conv_desc*") IntPointer pool);
     public static native int dl4jb200_dropout_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, @Const FloatPointer mask,
                     FloatPointer y, @Cast("size_t") long n, double retainProb);
     public static native int dl4jb200_buf_register(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host, long bytes,
