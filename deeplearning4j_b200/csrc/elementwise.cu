@@ -636,6 +636,17 @@ int dl4jb200_softmax_nll(dl4jb200_ctx *ctx, const float *z, int z_ld, const floa
     return DL4JB200_OK;
 }
 
+__global__ void k_score_combine(const float *__restrict__ loss_sum, const float *__restrict__ reg, float *__restrict__ score, float b) {
+    score[0] = (loss_sum[0] + (reg ? reg[0] : 0.f)) / b;
+}
+
+int dl4jb200_score_combine(dl4jb200_ctx *ctx, const float *loss_sum, const float *reg, float *score, int minibatch) {
+    DL4J_REQUIRE(ctx && loss_sum && score && minibatch > 0, "score_combine: bad argument");
+    k_score_combine<<<1, 1, 0, ctx->stream>>>(loss_sum, reg, score, (float)minibatch);
+    DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
 int dl4jb200_l1l2_score(dl4jb200_ctx *ctx, const float *w, size_t n, double l1, double l2, float *score_acc) {
     DL4J_REQUIRE(ctx && w && score_acc, "l1l2_score: NULL argument");
     if (n == 0 || (l1 == 0.0 && l2 == 0.0)) return DL4JB200_OK;

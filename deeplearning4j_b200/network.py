@@ -229,6 +229,7 @@ class Network:
                 self.pool_fuse[v["name"]] = pv["name"]
         self.loss = self._buf(1)
         self.score_reg = self._buf(1)
+        self.score = self._buf(1)
         self.tmp_eps = {}
         self.labels = None
 
@@ -925,8 +926,12 @@ class Network:
         if hook is not None:
             hook(self)  # data-parallel gradient exchange (parallel.py)
         self.update()  # also leaves the L1/L2 part of the score (pre-update weights) in score_reg
-        with self.torch.cuda.stream(self.stream):
-            return (self.loss + self.score_reg) / float(self.B)
+        return self._score()
+
+    def _score(self):
+        """(loss sum + L1/L2 terms) / minibatch into self.score (a library kernel: the captured step holds no framework kernels)."""
+        self._call("dl4jb200_score_combine", self._ptr(self.loss), self._ptr(self.score_reg), self._ptr(self.score), self.B)
+        return self.score
 
     # ------------------------------------------------------------------ CUDA graph of one iteration
     def capture(self, hook=None, include_input=True):
@@ -947,7 +952,7 @@ class Network:
             if hook is not None:
                 hook(self)
             self.update()
-            self._graph_score = (self.loss + self.score_reg) / float(self.B)
+            self._graph_score = self._score()
         # the graph's nodes hold scratch addresses of both contexts: from here on a call that would have to grow a
         # region fails loudly instead of freeing memory the graph still references (release_graph() lifts it)
         for ctx in (self.h, self.h2):

@@ -352,6 +352,10 @@ int dl4jb200_softmax_nll(dl4jb200_ctx *ctx, const float *z, int z_ld, const floa
 /* Regularisation part of the score: score_acc[0] += l1*sum|w| + 0.5*l2*sum w^2 over n weights
  * (ConvolutionLayer.calcL1/calcL2, NN/nn/layers/convolution/ConvolutionLayer.java:98-123; BaseLayer likewise). */
 int dl4jb200_l1l2_score(dl4jb200_ctx *ctx, const float *w, size_t n, double l1, double l2, float *score_acc);
+/* The iteration's score as the network reports it: score[0] = (loss_sum[0] + reg[0]) / minibatch, loss_sum from
+ * dl4jb200_softmax_nll, reg the L1/L2 terms (NULL: none) -- BaseOutputLayer.computeScore, NN/nn/layers/BaseOutputLayer.java:82-100.
+ * One more node of the captured step instead of host-framework arithmetic on device scalars. */
+int dl4jb200_score_combine(dl4jb200_ctx *ctx, const float *loss_sum, const float *reg, float *score, int minibatch);
 /* Row-strided copy dst[r, 0:cols] = src[r, 0:cols], dst[r, cols:dst_ld] = 0 (CnnToFeedForwardPreProcessor
  * reshape when the row length is not a multiple of the 4-float channel granule). */
 int dl4jb200_copy2d(dl4jb200_ctx *ctx, const float *src, int src_ld, float *dst, int dst_ld, int rows, int cols);
