@@ -1592,7 +1592,10 @@ static inline int wgrad_bn(const ConvGeom &g) { return g.Kp >= 128 ? 128 : (g.Kp
 
 // TMA path applies when every K-chunk is 32 channels of one tap and the gather is a plain (strided) window walk.
 bool conv_tc_gemm_can_tma(const ConvGeom &g) {
-    if (g.Cg % 32 != 0 || g.Kp != g.K) return false;
+    // (a 1x1 window has a single tap, so a 32-channel chunk can never straddle two taps: any channel count of at least 32 that
+    // keeps pixels 16-byte aligned will do -- the last chunk's channels beyond C are zero-filled by the TMA unit and meet the
+    // zero columns [K, Kp) of the packed filter; dense layers with 500 / 1000 inputs or outputs take this path)
+    if (g.taps == 1 ? (g.Cg % 4 != 0 || g.Cg < 32 || g.cs_src % 4 != 0) : (g.Cg % 32 != 0 || g.Kp != g.K)) return false;
     if (g.transposed && (g.sH != 1 || g.sW != 1)) return false;
     if (g.kH > 16 || g.kW > 16 || g.dH * (g.kH - 1) > 255 || g.dW * (g.kW - 1) > 255) return false;
     const int lowH = g.transposed ? g.pT - (g.kH - 1) * g.dH : -g.pT, lowW = g.transposed ? g.pL - (g.kW - 1) * g.dW : -g.pL;

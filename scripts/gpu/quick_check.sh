@@ -1,4 +1,6 @@
 timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
-timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
+for m in lenet alexnet resnet50; do
+timeout 300 python bench.py --model $m --steps 20 --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
 import json,sys
-j=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('resnet50', round(j['value']), round(j['ms_per_step'],3), round(j['e2e']['value']), j['gpu_launches'], j['e2e'].get('last_score'))"
+j=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$m', round(j['value']), round(j['ms_per_step'],3), round(j['e2e']['value']), j['gpu_launches'])"
+done

@@ -67,6 +67,11 @@ CONV_CASES = [  # B, Cin, H, W, Cout, k, s, p, d, mode
     # form of the GEMM (partial accumulators per K range, ordered fold with bias), ragged N = 1000; backprop-data N = 2048
     (64, 2048, 1, 1, 1000, (1, 1), (1, 1), (0, 0), (1, 1), 1),
     (130, 1024, 1, 1, 1024, (1, 1), (1, 1), (0, 0), (1, 1), 1),  # two row tiles (one ragged), split-K in both directions
+    # 1x1 windows whose channel counts are not multiples of 32 still take the TMA path (single tap: the ragged last K-chunk
+    # is zero-filled): forward C = 40, backprop-data C = 72; and LeNet's dense shapes 800 -> 500 -> 10
+    (3, 40, 9, 9, 72, (1, 1), (1, 1), (0, 0), (1, 1), 1),
+    (64, 800, 1, 1, 500, (1, 1), (1, 1), (0, 0), (1, 1), 1),
+    (64, 500, 1, 1, 10, (1, 1), (1, 1), (0, 0), (1, 1), 1),
 ]
 
 
