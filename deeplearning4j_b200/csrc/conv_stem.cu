@@ -40,11 +40,15 @@ __global__ void __launch_bounds__(256) k_stem_wgrad_finalize(const float *__rest
                                                              int Cin, int kH, int kW, int Kp, int rows_p, int splits,
                                                              const float *__restrict__ db_partial, float *__restrict__ db, int nchunk) {
     size_t total = (size_t)Cout * Cin * kH * kW, stride = (size_t)gridDim.x * blockDim.x;
+    pdl_trigger();
+    pdl_wait();
     if (db_partial) {  // [splits][rows_p] sums from the GEMM's ones column
         for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < (size_t)Cout; i += stride) {
-            float acc = 0.f;
-            for (int s = 0; s < splits; s++) acc += db_partial[(size_t)s * rows_p + i];
-            db[i] = acc;
+            float a0 = 0.f, a1 = 0.f;
+            int s = 0;
+            for (; s + 1 < splits; s += 2) { a0 += db_partial[(size_t)s * rows_p + i]; a1 += db_partial[(size_t)(s + 1) * rows_p + i]; }
+            if (s < splits) a0 += db_partial[(size_t)s * rows_p + i];
+            db[i] = a0 + a1;
         }
     }
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
@@ -54,9 +58,17 @@ __global__ void __launch_bounds__(256) k_stem_wgrad_finalize(const float *__rest
         int ci = (int)(t % Cin), co = (int)(t / Cin);
         int k = (kh * nchunk + ((kw + 1) >> 3)) * 32 + ((kw + 1) & 7) * 4 + ci;
         const float *p = partial + (size_t)co * Kp + k;
-        float acc = 0.f;
-        for (int s = 0; s < splits; s++) acc += p[(size_t)s * rows_p * Kp];
-        dw[i] = acc;
+        const size_t ss = (size_t)rows_p * Kp;
+        // four independent partial sums: the loads of a round are in flight together (the fold over ~148 splits is a latency
+        // chain otherwise, and this kernel is the tail of the step); fixed combination order, deterministic
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        int s = 0;
+        for (; s + 3 < splits; s += 4) {
+            const float v0 = p[(size_t)s * ss], v1 = p[(size_t)(s + 1) * ss], v2 = p[(size_t)(s + 2) * ss], v3 = p[(size_t)(s + 3) * ss];
+            a0 += v0; a1 += v1; a2 += v2; a3 += v3;
+        }
+        for (; s < splits; s++) a0 += p[(size_t)s * ss];
+        dw[i] = (a0 + a1) + (a2 + a3);
     }
 }
 
@@ -191,8 +203,8 @@ int dl4jb200_conv_rowpack_wgrad(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, 
     t.div_Cg = FastDiv(32u); t.div_kW = FastDiv((uint32_t)nchunk);
     if ((rc = conv_tc_wgrad_tma_raw(ctx, tmD, tmX, t, partial, rows_w, splits, mps, dbp))) return rc;
     size_t total = (size_t)d->c_out * d->c_in * d->k_h * d->k_w;
-    k_stem_wgrad_finalize<<<dl4j_ceil_div((long long)total, 256), 256, 0, ctx->stream>>>(partial, dw, d->c_out, d->c_in, d->k_h, d->k_w,
-                                                                                    Kp, rows_w, splits, dbp, db, nchunk);
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_stem_wgrad_finalize, dim3((unsigned)dl4j_ceil_div((long long)total, 256)), dim3(256), 0, ctx->stream,
+                                  (const float *)partial, dw, d->c_out, d->c_in, d->k_h, d->k_w, Kp, rows_w, splits, (const float *)dbp, db, nchunk));
     DL4J_CHECK_LAUNCH();
     if (db && !db_fused) return dl4jb200_bias_grad(ctx, delta, M, delta_cs, d->c_out, db);
     return DL4JB200_OK;
