@@ -96,7 +96,18 @@ struct PackJob {  // device-visible
     float *wp;
     unsigned long long start;  // unused by the kernel (kept so that a job is self-describing in a debugger)
     int Cout, Cin, kH, kW, Cg, Kp, rows_p, transposed, round_tf32, flip;
+    // divisors of the pack kernel's index arithmetic (it is ALU-bound on integer division otherwise): taps*Cg, Cg, taps,
+    // Cin/4, 32*taps
+    FastDiv d_kk, d_Cg, d_taps, d_c4, d_span32;
 };
+static void pack_job_divs(PackJob &j) {
+    const uint32_t taps = (uint32_t)(j.kH * j.kW);
+    j.d_kk = FastDiv(taps * (uint32_t)j.Cg);
+    j.d_Cg = FastDiv((uint32_t)j.Cg);
+    j.d_taps = FastDiv(taps);
+    j.d_c4 = FastDiv((uint32_t)(j.Cin >> 2 ? j.Cin >> 2 : 1));
+    j.d_span32 = FastDiv(32u * taps);
+}
 struct PackUnit;
 struct FilterEntry {
     PackJob fwd, bwd;  // bwd.wp == nullptr: no backprop-data operand registered
@@ -146,7 +157,7 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
                 const int c4 = j.Cin >> 2;
 #pragma unroll 4
                 for (int e = threadIdx.x; e < rows * c4; e += 256) {
-                    const int r = e / c4, q = e - r * c4;
+                    const int r = (int)j.d_c4.div((uint32_t)e), q = e - r * c4;
                     float4 v = reinterpret_cast<const float4 *>(src)[e];
                     if (j.round_tf32) { v.x = to_tf32_rna(v.x); v.y = to_tf32_rna(v.y); v.z = to_tf32_rna(v.z); v.w = to_tf32_rna(v.w); }
                     *reinterpret_cast<float4 *>(j.wp + (size_t)(n0 + r) * j.Kp + q * 4) = v;
@@ -170,7 +181,7 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
         const int kk = taps * j.Cg;
 #pragma unroll 4
         for (int e = threadIdx.x; e < rows * kk; e += 256) {
-            const int r = e / kk, k = e - r * kk, tap = k / j.Cg, ci = k - tap * j.Cg;
+            const int r = (int)j.d_kk.div((uint32_t)e), k = e - r * kk, tap = (int)j.d_Cg.div((uint32_t)k), ci = k - tap * j.Cg;
             float v = 0.f;
             if (ci < j.Cin) {
                 const int o = (r * j.Cin + ci) * taps + (j.flip ? taps - 1 - tap : tap);
@@ -191,7 +202,7 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
         if (staged) {
 #pragma unroll 8
             for (int e = threadIdx.x; e < nco * span; e += 256) {
-                const int r = e / span, t = e - r * span;
+                const int r = nci == 32 ? (int)j.d_span32.div((uint32_t)e) : e / span, t = e - r * span;
                 sm[r * span + t] = j.w[((size_t)(co0 + r) * j.Cin + ci0) * taps + t];
             }
             __syncthreads();
@@ -199,7 +210,7 @@ __global__ void __launch_bounds__(256) k_pack_filters_batched(const PackJob *__r
         // destination: row ci, column tap'*Cg + co; lanes run along co
 #pragma unroll 4
         for (int e = threadIdx.x; e < nci * taps * 32; e += 256) {
-            const int cl = e & 31, t2 = e >> 5, tap = t2 % taps, il = t2 / taps;
+            const int cl = e & 31, t2 = e >> 5, il = (int)j.d_taps.div((uint32_t)t2), tap = t2 - il * taps;
             if (cl >= nco) continue;
             const int st = j.flip ? taps - 1 - tap : tap;
             const float v = staged ? sm[cl * span + il * taps + st] : j.w[((size_t)(co0 + cl) * j.Cin + ci0 + il) * taps + st];
@@ -697,12 +708,14 @@ int dl4jb200_filter_register(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, con
     FilterEntry e{};
     ConvGeom gf = conv_geom_fwd(d, x_cs);
     e.fwd = PackJob{w, nullptr, 0ULL, d->c_out, d->c_in, d->k_h, d->k_w, gf.Cg, gf.Kp, dl4j_round_up(z_cs > d->c_out ? z_cs : d->c_out, 256), 0, tf, 0};
+    pack_job_divs(e.fwd);
     DL4J_CUDA_TRY(cudaMalloc(&e.fwd.wp, (size_t)e.fwd.rows_p * e.fwd.Kp * sizeof(float)));
     DL4J_CUDA_TRY(cudaMemsetAsync(e.fwd.wp, 0, (size_t)e.fwd.rows_p * e.fwd.Kp * sizeof(float), ctx->stream));  // padding stays zero
     if (with_bwd_data) {
         ConvGeom gb = conv_geom_bwd_data(d, z_cs);
         const int flip = tf && conv_tc_gemm_can_tma(gb);
         e.bwd = PackJob{w, nullptr, 0ULL, d->c_out, d->c_in, d->k_h, d->k_w, gb.Cg, gb.Kp, dl4j_round_up(x_cs > d->c_in ? x_cs : d->c_in, 256), 1, tf, flip};
+        pack_job_divs(e.bwd);
         DL4J_CUDA_TRY(cudaMalloc(&e.bwd.wp, (size_t)e.bwd.rows_p * e.bwd.Kp * sizeof(float)));
         DL4J_CUDA_TRY(cudaMemsetAsync(e.bwd.wp, 0, (size_t)e.bwd.rows_p * e.bwd.Kp * sizeof(float), ctx->stream));
     }
