@@ -86,6 +86,28 @@ __global__ void __launch_bounds__(256) k_nchw_to_rowpack4(const float *__restric
     }
 }
 
+// Four pixels of a row per thread when W % 4 == 0 and the planes are 16-byte aligned: one 128-bit load per plane, four 128-bit
+// stores (the one-pixel form runs at 3.5 TB/s on the 155 MB ResNet-50 minibatch, and this pass is inside the timed step).
+__global__ void __launch_bounds__(256) k_nchw_to_rowpack4_v4(const float *__restrict__ src, float *__restrict__ dst, int B, int C, int H,
+                                                             int W4, int row_pitch_px, int x_off, int rnd, FastDiv d_w4, FastDiv d_h) {
+    const size_t total = (size_t)B * H * W4, stride = (size_t)gridDim.x * blockDim.x, plane = (size_t)H * W4 * 4;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        uint32_t t, x4, b, y;
+        d_w4.divmod((uint32_t)i, t, x4);
+        d_h.divmod(t, b, y);
+        float4 v[4] = {make_float4(0, 0, 0, 0), make_float4(0, 0, 0, 0), make_float4(0, 0, 0, 0), make_float4(0, 0, 0, 0)};
+        const float *s = src + (size_t)b * C * plane + ((size_t)y * W4 + x4) * 4;
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+            if (c < C) v[c] = dl4j_rnd4(*reinterpret_cast<const float4 *>(s + (size_t)c * plane), rnd);
+        float4 *d = reinterpret_cast<float4 *>(dst + (((size_t)b * H + y) * row_pitch_px + x_off + (size_t)x4 * 4) * 4);
+        d[0] = make_float4(v[0].x, v[1].x, v[2].x, v[3].x);
+        d[1] = make_float4(v[0].y, v[1].y, v[2].y, v[3].y);
+        d[2] = make_float4(v[0].z, v[1].z, v[2].z, v[3].z);
+        d[3] = make_float4(v[0].w, v[1].w, v[2].w, v[3].w);
+    }
+}
+
 static int stem_check(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *d, int row_pitch_px, const char *who) {
     DL4J_REQUIRE(ctx && d, "%s: NULL argument", who);
     if (d->c_in > 4 || d->stride_w < 1 || d->stride_w > 8 || d->k_w > 15 || (d->k_w > 7 && 8 % d->stride_w != 0) || d->k_h > 16 ||
@@ -116,6 +138,14 @@ int dl4jb200_nchw_to_rowpack4(dl4jb200_ctx *ctx, const float *src, float *dst, i
     DL4J_REQUIRE(ctx && src && dst, "nchw_to_rowpack4: NULL argument");
     DL4J_REQUIRE(C >= 1 && C <= 4 && B > 0 && H > 0 && W > 0 && x_off >= 0 && x_off + W <= row_pitch_px, "nchw_to_rowpack4: bad shape");
     size_t total = (size_t)B * H * W;
+    if (W % 4 == 0 && ((uintptr_t)src & 15) == 0 && total / 4 < (1ull << 32)) {
+        const size_t items = total / 4, blocks4 = (items + 255) / 256, cap4 = (size_t)ctx->sm_count * 16;
+        k_nchw_to_rowpack4_v4<<<(int)(blocks4 > cap4 ? cap4 : blocks4), 256, 0, ctx->stream>>>(src, dst, B, C, H, W / 4, row_pitch_px, x_off,
+                                                                                              ctx->round_act, FastDiv((uint32_t)(W / 4)),
+                                                                                              FastDiv((uint32_t)H));
+        DL4J_CHECK_LAUNCH();
+        return DL4JB200_OK;
+    }
     size_t blocks = (total + 255) / 256, cap = (size_t)ctx->sm_count * 16;
     k_nchw_to_rowpack4<<<(int)(blocks > cap ? cap : blocks), 256, 0, ctx->stream>>>(src, dst, B, C, H, W, row_pitch_px, x_off, ctx->round_act);
     DL4J_CHECK_LAUNCH();
