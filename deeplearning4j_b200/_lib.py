@@ -110,6 +110,7 @@ PROTOTYPES = {
     "dl4jb200_softmax_nll": [_vp, _vp, _i, _vp, _vp, _i, _vp, _i, _i],
     "dl4jb200_l1l2_score": [_vp, _vp, _sz, _d, _d, _vp],
     "dl4jb200_score_combine": [_vp, _vp, _vp, _vp, _i],
+    "dl4jb200_pool_bwd_bnstats": [_vp, _desc_p, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, C.POINTER(C.c_int)],
     "dl4jb200_copy2d": [_vp, _vp, _i, _vp, _i, _i, _i],
     "dl4jb200_grad_normalize": [_vp, _vp, _sz, _i, _d],
     "dl4jb200_updater_apply_segments": [_vp, _vp, _vp, _vp, _sz, _vp, _vp, _i, _vp, _i, _d, _vp],

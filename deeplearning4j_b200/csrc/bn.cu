@@ -414,6 +414,122 @@ __global__ void __launch_bounds__(256) k_bn_act_maxpool_nhwc(const float *__rest
     }
 }
 
+// ------------------------------------------------------------------ MAX-pooling backward that also takes the BN backward sums
+// The epsilon of a BatchNormalization whose only consumer is a stride-2 MAX pooling layer (ResNet-50's stem) is produced by
+// that layer's backprop. This is k_maxpool_bwd_nhwc_patch2 (pool.cu: one thread per 2x2 patch of dx x 4 channels, the <= 2x2
+// candidate windows fetched up front, same per-cell summation order and rounding) which, while the patch is in registers,
+// also reads the batch norm's input x, recomputes the fused-ReLU gate exactly as k_bn_partial_nhwc does and accumulates
+// sum e', sum e' * (x - mean) for its channel quad -- the launch's stride is a multiple of the quad count, so a thread keeps
+// its channels. One partial row per block in k_bn_finalize_bwd's layout: the separate partial-sum pass over (x, eps)
+// (1.6 GB for the stem) disappears.
+struct PoolBstGeom {
+    int B, H, W, Ho, Wo, kH, kW, pT, pL, cs, Hp, Wp, rnd;
+    FastDiv d_q, d_wp, d_hp;
+};
+
+__global__ void __launch_bounds__(256) k_maxpool_bwd_bnsums_nhwc(const float *__restrict__ eps, const int32_t *__restrict__ argmax,
+                                                                 float *__restrict__ dx, const float *__restrict__ x, BnMask mk,
+                                                                 const float *__restrict__ mean, float *__restrict__ partial, PoolBstGeom g,
+                                                                 size_t total) {
+    __shared__ float4 red[2][256];
+    pdl_trigger();
+    pdl_wait();
+    const int Q = g.cs >> 2, q = (int)(threadIdx.x % (unsigned)Q), c = q * 4;  // (gridDim.x * 256) % Q == 0: fixed per thread
+    const float4 k = *reinterpret_cast<const float4 *>(mean + c);
+    float4 ma = make_float4(0, 0, 0, 0), mb = ma;
+    if (mk.relu) {
+        bn_mask_coef(mk, c, g.cs, ma.x, mb.x); bn_mask_coef(mk, c + 1, g.cs, ma.y, mb.y);
+        bn_mask_coef(mk, c + 2, g.cs, ma.z, mb.z); bn_mask_coef(mk, c + 3, g.cs, ma.w, mb.w);
+    }
+    float4 a1 = make_float4(0, 0, 0, 0), a2 = a1;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += stride) {
+        uint32_t t, qq, wp, hp, b;
+        g.d_q.divmod((uint32_t)idx, t, qq);  // qq == q (see above)
+        (void)qq;
+        g.d_wp.divmod(t, t, wp);
+        g.d_hp.divmod(t, b, hp);
+        const int h0 = (int)hp * 2, w0 = (int)wp * 2;
+        const int th0 = h0 + g.pT, tw0 = w0 + g.pL;
+        const int oh_hi = min((th0 + 1) >> 1, g.Ho - 1), ow_hi = min((tw0 + 1) >> 1, g.Wo - 1);
+        const int lh = th0 - g.kH + 1, lw = tw0 - g.kW + 1;
+        const int oh_lo = lh <= 0 ? 0 : (lh + 1) >> 1, ow_lo = lw <= 0 ? 0 : (lw + 1) >> 1;
+        float4 v[2][2];
+#pragma unroll
+        for (int a = 0; a < 2; a++)
+#pragma unroll
+            for (int d = 0; d < 2; d++) {
+                v[a][d] = make_float4(0, 0, 0, 0);
+                if (h0 + a < g.H && w0 + d < g.W) v[a][d] = *reinterpret_cast<const float4 *>(x + (((size_t)b * g.H + h0 + a) * g.W + w0 + d) * g.cs + c);
+            }
+        int4 am[2][2];
+        float4 e[2][2];
+#pragma unroll
+        for (int i = 0; i < 2; i++)
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int oh = oh_hi - i, ow = ow_hi - j;
+                am[i][j] = make_int4(-1, -1, -1, -1);
+                e[i][j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (oh >= oh_lo && ow >= ow_lo) {
+                    const size_t o = (((size_t)b * g.Ho + oh) * g.Wo + ow) * g.cs + c;
+                    am[i][j] = *reinterpret_cast<const int4 *>(argmax + o);
+                    e[i][j] = *reinterpret_cast<const float4 *>(eps + o);
+                }
+            }
+        float4 acc[2][2];
+#pragma unroll
+        for (int a = 0; a < 2; a++)
+#pragma unroll
+            for (int d = 0; d < 2; d++) acc[a][d] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int i = 0; i < 2; i++)
+#pragma unroll
+            for (int j = 0; j < 2; j++)
+#pragma unroll
+                for (int a = 0; a < 2; a++) {
+                    const int kh = th0 - 2 * (oh_hi - i) + a;
+#pragma unroll
+                    for (int d = 0; d < 2; d++) {
+                        const int kw = tw0 - 2 * (ow_hi - j) + d;
+                        const int me = ((unsigned)kh < (unsigned)g.kH && (unsigned)kw < (unsigned)g.kW) ? kh * g.kW + kw : -2;
+                        acc[a][d].x += am[i][j].x == me ? e[i][j].x : 0.f; acc[a][d].y += am[i][j].y == me ? e[i][j].y : 0.f;
+                        acc[a][d].z += am[i][j].z == me ? e[i][j].z : 0.f; acc[a][d].w += am[i][j].w == me ? e[i][j].w : 0.f;
+                    }
+                }
+#pragma unroll
+        for (int a = 0; a < 2; a++)
+#pragma unroll
+            for (int d = 0; d < 2; d++) {
+                if (h0 + a >= g.H || w0 + d >= g.W) continue;
+                const float4 r = dl4j_rnd4(acc[a][d], g.rnd);
+                *reinterpret_cast<float4 *>(dx + (((size_t)b * g.H + h0 + a) * g.W + w0 + d) * g.cs + c) = r;
+                float4 w = v[a][d], gg = r;
+                w.x -= k.x; w.y -= k.y; w.z -= k.z; w.w -= k.w;
+                if (mk.relu) {
+                    gg.x = w.x * ma.x + mb.x > 0.f ? gg.x : 0.f; gg.y = w.y * ma.y + mb.y > 0.f ? gg.y : 0.f;
+                    gg.z = w.z * ma.z + mb.z > 0.f ? gg.z : 0.f; gg.w = w.w * ma.w + mb.w > 0.f ? gg.w : 0.f;
+                }
+                a1.x += gg.x; a1.y += gg.y; a1.z += gg.z; a1.w += gg.w;
+                a2.x += gg.x * w.x; a2.y += gg.y * w.y; a2.z += gg.z * w.z; a2.w += gg.w * w.w;
+            }
+    }
+    red[0][threadIdx.x] = a1;
+    red[1][threadIdx.x] = a2;
+    __syncthreads();
+    if ((int)threadIdx.x < Q) {  // fold the 256 / Q threads that share this quad, in thread order (deterministic)
+        float4 s1 = red[0][threadIdx.x], s2 = red[1][threadIdx.x];
+        for (int t = threadIdx.x + Q; t < 256; t += Q) {
+            const float4 b1 = red[0][t], b2 = red[1][t];
+            s1.x += b1.x; s1.y += b1.y; s1.z += b1.z; s1.w += b1.w;
+            s2.x += b2.x; s2.y += b2.y; s2.z += b2.z; s2.w += b2.w;
+        }
+        float *p = partial + (size_t)blockIdx.x * 2 * g.cs;
+        *reinterpret_cast<float4 *>(p + c) = s1;
+        *reinterpret_cast<float4 *>(p + g.cs + c) = s2;
+    }
+}
+
 // launches k_bn_apply_nhwc, with per-thread fixed channels whenever a grid close to the usual one makes the stride a multiple
 // of the channel-quad count
 template <int MODE>
@@ -684,6 +800,40 @@ int dl4jb200_bn_bwd_prestats(dl4jb200_ctx *ctx, const float *x, const float *eps
                                   relu ? (const float *)(coef + 4 * (size_t)cs) : (const float *)nullptr, dx, (const float *)coef, total / 4, cs,
                                   ctx->round_act << 8));
     DL4J_CHECK_LAUNCH();
+    return DL4JB200_OK;
+}
+
+// MAX-pooling backward (stride-2 windows of at most 3x3, NHWC, saved taps) that also leaves the backward sums of the
+// BatchNormalization whose output the pooling layer consumed: dx is what dl4jb200_pool_bwd writes; stat_partial receives
+// *rows_out rows ([2][cs] each) for dl4jb200_bn_bwd_prestats. stat_partial must hold 4 * (number of SMs) rows.
+int dl4jb200_pool_bwd_bnstats(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *pool, const float *eps, const int32_t *argmax, float *dx,
+                              int cs, const float *bn_x, const float *gamma, const float *beta, const float *save_mean,
+                              const float *save_std, int bn_relu, float *stat_partial, int *rows_out) {
+    DL4J_REQUIRE(ctx && pool && eps && argmax && dx && bn_x && save_mean && save_std && stat_partial && rows_out,
+                 "pool_bwd_bnstats: NULL argument");
+    const int C = pool->c_in, H = pool->in_h, W = pool->in_w, B = pool->batch;
+    if (pool->stride_h != 2 || pool->stride_w != 2 || pool->pad_top < 0 || pool->pad_left < 0 || pool->dil_h != 1 || pool->dil_w != 1 ||
+        pool->k_h > 3 || pool->k_w > 3 || cs != C || C % 4 != 0 || 256 % (C / 4) != 0) {
+        dl4j_set_error("pool_bwd_bnstats: needs stride-2 windows of at most 3x3 without dilation, non-negative padding, cs == C and "
+                       "C/4 dividing 256 (got k %dx%d stride %dx%d C %d cs %d)", pool->k_h, pool->k_w, pool->stride_h, pool->stride_w, C, cs);
+        return DL4JB200_NOT_SUPPORTED;
+    }
+    DL4J_REQUIRE(B > 0 && H > 0 && W > 0 && pool->out_h > 0 && pool->out_w > 0 && pool->k_h > 0 && pool->k_w > 0, "pool_bwd_bnstats: bad shape");
+    DL4J_REQUIRE(al16(eps) && al16(argmax) && al16(dx) && al16(bn_x) && al16(save_mean) && al16(stat_partial),
+                 "pool_bwd_bnstats: tensors must be 16-byte aligned");
+    const int Hp = (H + 1) / 2, Wp = (W + 1) / 2;
+    const size_t total = (size_t)B * Hp * Wp * (C / 4);
+    DL4J_REQUIRE(total < (1ull << 32), "pool_bwd_bnstats: tensor too large");
+    size_t blocks = (total + 255) / 256;
+    const size_t cap = (size_t)ctx->sm_count * 4;  // one partial row per block: keep the finalize fold short
+    if (blocks > cap) blocks = cap;
+    PoolBstGeom g{B, H, W, pool->out_h, pool->out_w, pool->k_h, pool->k_w, pool->pad_top, pool->pad_left, cs, Hp, Wp, ctx->round_act,
+                  FastDiv((uint32_t)(C / 4)), FastDiv((uint32_t)Wp), FastDiv((uint32_t)Hp)};
+    const BnMask mk{gamma, beta, save_std, bn_relu ? 1 : 0};
+    DL4J_CUDA_TRY(dl4j_launch_pdl(k_maxpool_bwd_bnsums_nhwc, dim3((unsigned)blocks), dim3(256), 0, ctx->stream, eps, argmax, dx, bn_x, mk, save_mean,
+                                  stat_partial, g, total));
+    DL4J_CHECK_LAUNCH();
+    *rows_out = (int)blocks;
     return DL4JB200_OK;
 }
 

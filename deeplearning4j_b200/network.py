@@ -80,7 +80,7 @@ class Network:
         # backward sums of a BatchNormalization taken in the epilogue of the backprop-data GEMM that produces its epsilon
         # (dl4jb200_conv_bwd_data_bnstats): the layer's backward then runs finalize + apply only
         self.fuse_bn_bwd_stats = algo == _lib.ALGO_TC_TF32
-        self._bst_plan, self._bst = {}, {}
+        self._bst_plan, self._bst, self._pool_bst = {}, {}, {}
         self._plan_bn_stats()
         self._plan_forward_branches()
 
@@ -593,6 +593,27 @@ class Network:
                 self._bst_plan[n] = (rows.value, self._buf(rows.value * 2 * Cb)) if rows.value > 0 else None
         return self._bst_plan[n]
 
+    def _pool_bst_plan(self, v, d):
+        """Partial-sum buffer when MAX pooling layer v can carry the backward sums of the BatchNormalization feeding it
+        (dl4jb200_pool_bwd_bnstats), else None."""
+        n, u = v["name"], v["in"][0]
+        if n not in self._pool_bst:
+            uv = self.vmap[u]
+            Cb = self.shapes[u][0]
+            ok = (self.fuse_bn_bwd_stats and uv["op"] == "bn" and u not in self.fused_bn and self.consumers[u] == [n]
+                  and uv["act"] in ("identity", "relu") and v["type"] == "MAX" and not v.get("dropout")
+                  and len(self.shapes[u]) == 3 and self.cs[u] == Cb and self.cs[n] == Cb and Cb % 4 == 0 and 256 % (Cb // 4) == 0
+                  and self.out.get(uv["in"][0], 0) is not None and self.cs[uv["in"][0]] == Cb
+                  and d.stride_h == 2 and d.stride_w == 2 and d.k_h <= 3 and d.k_w <= 3 and d.pad_top >= 0 and d.pad_left >= 0
+                  and all(self.pidx[(u, k)][0] % 4 == 0 for k in ("gamma", "beta")))
+            buf = None
+            if ok:
+                sms = self.torch.cuda.get_device_properties(self.dev).multi_processor_count
+                with self.torch.cuda.stream(self.stream):
+                    buf = self._buf(4 * sms * 2 * Cb)
+            self._pool_bst[n] = buf
+        return self._pool_bst[n]
+
     def _bst_args(self, bn):
         v = self.vmap[bn]
         bx, _ = self._src(v["in"][0])
@@ -763,6 +784,16 @@ class Network:
             x, xcs = self._lin(n, u)
             d = self._pool_desc(v)
             am = self._ptr(self.aux[n]) if v["type"] == "MAX" else None
+            plan = self._pool_bst_plan(v, d)
+            if plan is not None:  # this layer's backprop IS the epsilon of the batch norm below it: take that layer's sums here
+                rows = C.c_int(0)
+                dst = self._eps_buf(u)
+                self._call("dl4jb200_pool_bwd_bnstats", C.byref(d), self._ptr(e), am, self._ptr(dst), self.cs[n], *self._bst_args(u),
+                           self._ptr(plan), C.byref(rows))
+                self._written.add(u)
+                self._contrib[u] = self._contrib.get(u, 0) + 1
+                self._bst[u] = (plan, rows.value)
+                return
             self._emit(u, lambda dx: self._call("dl4jb200_pool_bwd", C.byref(d), self._ptr(x), self._ptr(self.out[n]), self._ptr(e), am,
                                                 dx, L.NHWC, xcs, self.cs[n], _POOL[v["type"]], int(v.get("pnorm", 2)), 1e-8))
         elif op in ("add", "act"):

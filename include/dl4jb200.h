@@ -403,6 +403,17 @@ int dl4jb200_bn_fwd_prestats_maxpool(dl4jb200_ctx *ctx, const float *x, float *y
                                      int H, int W, int cs, double decay, double eps, int minibatch, int act, const float *pivot,
                                      const float *stat_partial, int stat_rows, const dl4jb200_conv_desc *pool);
 
+/* SubsamplingLayer.backpropGradient for MAX pooling (SubsamplingLayer.java:205-218, 263; saved taps, NHWC, stride-2 windows of
+ * at most 3x3, non-negative padding) that also takes the backward sums of the BatchNormalization whose output the pooling
+ * layer consumed (BatchNormalization.java:172-196): dx is exactly what dl4jb200_pool_bwd writes -- the epsilon of that
+ * batch norm -- and while each 2x2 patch of it is in registers the kernel reads the batch norm's input bn_x (laid out like
+ * dx), recomputes the fused-ReLU gate as dl4jb200_bn_bwd does and leaves sum e', sum e' * (x - mean) in stat_partial
+ * (*rows_out rows of 2 * cs floats; the buffer must hold 4 * #SMs rows) for dl4jb200_bn_bwd_prestats. The partial-sum pass
+ * over (x, eps) -- 1.6 GB for ResNet-50's stem -- disappears. cs == C, C/4 must divide 256; NOT_SUPPORTED otherwise. */
+int dl4jb200_pool_bwd_bnstats(dl4jb200_ctx *ctx, const dl4jb200_conv_desc *pool, const float *eps, const int32_t *argmax, float *dx,
+                              int cs, const float *bn_x, const float *gamma, const float *beta, const float *save_mean,
+                              const float *save_std, int bn_relu, float *stat_partial, int *rows_out);
+
 /* Backward counterpart of conv_fwd_bnstats. BatchNormalization.backpropGradient needs dBeta = sum eps and
  * sum eps * (x - mean) (BatchNormalization.java:172-196) before it can form dx: a separate reduction pass over (x, eps).
  * When eps is produced by a helper call -- the backprop-data of the convolution that consumed the layer's output, with or

@@ -92,3 +92,80 @@ def test_bn_maxpool_rejects_mismatched_descriptor():
     finally:
         dev.free()
         ctx.close()
+
+
+BWD_CASES = [  # B, C, H, W, pool kernel, pool pad, relu
+    (4, 64, 30, 30, (3, 3), (0, 0), True),     # the stem's window; even size, last row / column outside every window
+    (3, 64, 17, 19, (3, 3), (1, 1), True),     # odd sizes (ragged patch grid), padded border
+    (2, 128, 16, 16, (2, 2), (0, 0), False),   # non-overlapping windows, identity activation
+    (2, 32, 9, 11, (3, 2), (0, 1), True),      # non-square window
+]
+
+
+@pytest.mark.parametrize("round_act", [0, 1])
+@pytest.mark.parametrize("case", BWD_CASES)
+def test_pool_bwd_bnstats_matches_two_calls(oracle, case, round_act):
+    """dl4jb200_pool_bwd_bnstats + dl4jb200_bn_bwd_prestats == dl4jb200_pool_bwd + dl4jb200_bn_bwd: the routed epsilon bit for
+    bit, dgamma / dbeta / dx to fp32 summation order; and the oracle's SubsamplingLayer + BatchNormalization backprop."""
+    from deeplearning4j_b200 import _lib as L, helpers as H
+    import torch
+    B, Cc, Hh, W, pk, ppad, relu = case
+    rng = np.random.default_rng(11)
+    x = (rng.standard_normal((B, Cc, Hh, W)) * 1.3 + 0.2).astype(np.float32)
+    gamma = (1 + 0.1 * rng.standard_normal(Cc)).astype(np.float32)
+    beta = (0.1 * rng.standard_normal(Cc)).astype(np.float32)
+    pd = H.conv_desc((B, Cc, Hh, W), Cc, pk, (2, 2), ppad, (1, 1), "Truncate")
+    pe = rng.standard_normal((B, Cc, pd.out_h, pd.out_w)).astype(np.float32)
+    act = L.ACT_RELU if relu else L.ACT_IDENTITY
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    ctx = H.Context(0)
+    L.call("dl4jb200_ctx_set_option", ctx.handle, L.OPT_TF32_ACTIVATIONS, round_act)
+    dev = Dev(ctx)
+    try:
+        n, n_out = B * Hh * W * Cc, B * pd.out_h * pd.out_w * Cc
+        px, pg, pb, ppe = dev.put(to_nhwc(x)), dev.put(gamma), dev.put(beta), dev.put(to_nhwc(pe))
+        gm, gv = dev.put(np.zeros(Cc, np.float32)), dev.put(np.ones(Cc, np.float32))
+        sm, ss, py, pyp, pam = dev.empty(Cc * 4), dev.empty(Cc * 4), dev.empty(n * 4), dev.empty(n_out * 4), dev.empty(n_out * 4)
+        L.call("dl4jb200_bn_fwd", ctx.handle, px, py, pg, pb, gm, gv, sm, ss, B, Cc, Hh, W, L.NHWC, Cc, 0.9, 1e-5, 1, 1, act, None)
+        L.call("dl4jb200_pool_fwd", ctx.handle, C.byref(pd), py, pyp, pam, L.NHWC, Cc, Cc, L.POOL_MAX, 2)
+        e0, dx0, dg0, db0 = dev.empty(n * 4, fill=0xFF), dev.empty(n * 4), dev.empty(Cc * 4), dev.empty(Cc * 4)
+        L.call("dl4jb200_pool_bwd", ctx.handle, C.byref(pd), py, pyp, ppe, pam, e0, L.NHWC, Cc, Cc, L.POOL_MAX, 2, 1e-8)
+        L.call("dl4jb200_bn_bwd", ctx.handle, px, e0, pg, pb, sm, ss, act, dx0, dg0, db0, B, Cc, Hh, W, L.NHWC, Cc)
+        e1, dx1, dg1, db1 = dev.empty(n * 4, fill=0xFF), dev.empty(n * 4), dev.empty(Cc * 4), dev.empty(Cc * 4)
+        pst, rows = dev.empty(4 * sms * 2 * Cc * 4, fill=0xFF), C.c_int(0)
+        L.call("dl4jb200_pool_bwd_bnstats", ctx.handle, C.byref(pd), ppe, pam, e1, Cc, px, pg, pb, sm, ss, int(relu), pst, C.byref(rows))
+        assert 0 < rows.value <= 4 * sms
+        L.call("dl4jb200_bn_bwd_prestats", ctx.handle, px, e1, pg, pb, sm, ss, act, dx1, dg1, db1, B, Cc, Hh, W, Cc, pst, rows.value)
+        np.testing.assert_array_equal(dev.get(e1, (n,)), dev.get(e0, (n,)))
+        a0, a1 = dev.get(dx0, (B, Hh, W, Cc)), dev.get(dx1, (B, Hh, W, Cc))
+        assert rel_err(a1, a0) <= (1e-3 if round_act else 2e-6), rel_err(a1, a0)
+        assert rel_err(dev.get(dg1, (Cc,)), dev.get(dg0, (Cc,))) <= 1e-5
+        assert rel_err(dev.get(db1, (Cc,)), dev.get(db0, (Cc,))) <= 1e-5
+        y = from_nhwc(dev.get(py, (B, Hh, W, Cc)), Cc)
+        e_full = oracle.pool_bwd(y, pe, pk, (2, 2), ppad, (1, 1), oracle.TRUNCATE, oracle.POOL_MAX)
+        if relu:
+            e_full = np.where(y > 0, e_full, 0).astype(np.float32)
+        dxr, dgr, dbr = oracle.bn_bwd(x, e_full, gamma, dev.get(sm, (Cc,)), dev.get(ss, (Cc,)))
+        assert rel_err(from_nhwc(a1, Cc), dxr) <= (2e-3 if round_act else 2e-5)
+        tol_sum = 1e-3 if round_act else 1e-4
+        assert rel_err(dev.get(dg1, (Cc,)), dgr) <= tol_sum and rel_err(dev.get(db1, (Cc,)), dbr) <= tol_sum
+    finally:
+        dev.free()
+        ctx.close()
+
+
+def test_pool_bwd_bnstats_declines_other_windows():
+    from deeplearning4j_b200 import _lib as L, helpers as H
+    ctx = H.Context(0)
+    dev = Dev(ctx)
+    try:
+        B, Cc, Hh, W = 2, 64, 9, 9
+        pd = H.conv_desc((B, Cc, Hh, W), Cc, (3, 3), (1, 1), (0, 0), (1, 1), "Truncate")   # stride 1
+        p = dev.empty(B * Hh * W * Cc * 4, fill=0)
+        v = dev.put(np.ones(Cc, np.float32))
+        rows = C.c_int(0)
+        with pytest.raises(Exception, match="stride"):
+            L.call("dl4jb200_pool_bwd_bnstats", ctx.handle, C.byref(pd), p, p, p, Cc, p, v, v, v, v, 1, p, C.byref(rows))
+    finally:
+        dev.free()
+        ctx.close()
