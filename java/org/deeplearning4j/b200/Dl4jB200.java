@@ -65,6 +65,10 @@ public class Dl4jB200 {
                     FloatPointer saveMean, FloatPointer saveStd, int b, int c, int h, int w, int cs, double decay, double eps,
                     int minibatch, int act, @Const FloatPointer pivot, @Const FloatPointer statPartial, int statRows,
                     @Cast("const dl4jb200_conv_desc*") IntPointer pool);
+    public static native int dl4jb200_pool_bwd_bnstats(@Cast("dl4jb200_ctx*") Pointer ctx, @Cast("const dl4jb200_conv_desc*") IntPointer pool,
+                    @Const FloatPointer eps, @Const IntPointer argmax, FloatPointer dx, int cs, @Const FloatPointer bnX,
+                    @Const FloatPointer gamma, @Const FloatPointer beta, @Const FloatPointer saveMean, @Const FloatPointer saveStd,
+                    int bnRelu, FloatPointer statPartial, IntPointer rowsOut);
     public static native int dl4jb200_dropout_fwd(@Cast("dl4jb200_ctx*") Pointer ctx, @Const FloatPointer x, @Const FloatPointer mask,
                     FloatPointer y, @Cast("size_t") long n, double retainProb);
     public static native int dl4jb200_buf_register(@Cast("dl4jb200_ctx*") Pointer ctx, @Const Pointer host, long bytes,
