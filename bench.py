@@ -368,7 +368,8 @@ def main():
     net.overlap_wgrad = False  # one stream: every call is timed alone (in the timed regions above the filter gradients overlap the backward chain)
     net.profile(["dl4jb200_conv_fwd", "dl4jb200_conv_fwd_bnstats", "dl4jb200_conv_bwd", "dl4jb200_conv_bwd_data_fused", "dl4jb200_conv_bwd_data_bnstats",
                  "dl4jb200_conv_rowpack_fwd", "dl4jb200_conv_rowpack_wgrad", "dl4jb200_conv_rowpack_fwd_bnstats", "dl4jb200_bn_fwd",
-                 "dl4jb200_bn_fwd_prestats", "dl4jb200_bn_bwd", "dl4jb200_bn_bwd_prestats", "dl4jb200_pool_fwd", "dl4jb200_pool_bwd"])
+                 "dl4jb200_bn_fwd_prestats", "dl4jb200_bn_bwd", "dl4jb200_bn_bwd_prestats", "dl4jb200_pool_fwd", "dl4jb200_pool_bwd",
+                 "dl4jb200_bn_fwd_prestats_maxpool", "dl4jb200_pool_bwd_bnstats"])
     psteps = min(args.steps, 10)
     step()  # untimed: lets the single-stream variant size its scratch
     barrier()
@@ -457,17 +458,23 @@ def main():
                 sh = net.shapes[tag if tag in net.shapes and net.vmap[tag]["op"] == "bn" else net.fused_add.get(tag, (tag,))[0]]
                 tot_ms += sum(times)
                 tot_b += float(B) * sh[0] * sh[1] * sh[2] * bpe * len(times)
+            elif key == "bn_fwd" and f2 == "dl4jb200_bn_fwd_prestats_maxpool":
+                # BN + ReLU + max-pool in one pass: reads the BN's input, writes the pooled tensor and its taps
+                sh, so = net.shapes[tag], net.shapes[net.pool_fuse[tag]]
+                tot_ms += sum(times)
+                tot_b += (4.0 * B * sh[0] * sh[1] * sh[2] + 8.0 * B * so[0] * so[1] * so[2]) * len(times)
         if tot_ms:
             bw[key] = {"achieved_gbs": tot_b / (tot_ms * 1e-3) / 1e9, "frac_of_hbm": tot_b / (tot_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
                        "share_of_step": tot_ms / (ms_eager * psteps)}
     for fn in ("dl4jb200_pool_fwd", "dl4jb200_pool_bwd"):
         tot_ms = tot_b = 0.0
         for (f2, tag), times in prof.items():
-            if f2 == fn:
+            if f2 == fn or (fn == "dl4jb200_pool_bwd" and f2 == "dl4jb200_pool_bwd_bnstats"):
                 so, si = net.shapes[tag], net.shapes[net.vmap[tag]["in"][0]]
                 n_in, n_out = float(B) * si[0] * si[1] * si[2], float(B) * so[0] * so[1] * so[2]
                 tot_ms += sum(times)
-                tot_b += (4 * (n_in + n_out) + 4 * n_out) * len(times)
+                # (the statistics-carrying backward also reads the batch norm's input once: 4 more bytes per input element)
+                tot_b += (4 * (n_in + n_out) + 4 * n_out + (4 * n_in if f2 == "dl4jb200_pool_bwd_bnstats" else 0)) * len(times)
         if tot_ms:
             bw[fn[9:]] = {"achieved_gbs": tot_b / (tot_ms * 1e-3) / 1e9, "frac_of_hbm": tot_b / (tot_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
                           "share_of_step": tot_ms / (ms_eager * psteps)}

@@ -1,3 +1,6 @@
 mkdir -p gpurun_out
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_conv_tc_gemm_tma_persist -s 3 -c 1 -o gpurun_out/r30_res2_3x3 python scripts/pair_bench.py "res2 3x3" > gpurun_out/r30_ncu.log 2>&1
-echo "ncu rc=$?"; tail -2 gpurun_out/r30_ncu.log
+timeout 600 python bench.py --model resnet50 --steps 20 --warmup 5 --dump-profile gpurun_out/r02_prof_resnet50.json > gpurun_out/r02_bench_resnet50.json 2> gpurun_out/r02_bench_resnet50.err
+python -c "
+import json
+j=json.load(open('gpurun_out/r02_bench_resnet50.json')); print(round(j['value']), round(j['ms_per_step'],3), round(j['e2e']['value']), {k:(round(v['achieved_gbs']),round(v['frac_of_hbm'],3),round(v['share_of_step'],3)) for k,v in j['hbm_kernels'].items()}, j['cpu_baseline']['value'])"
+tail -2 gpurun_out/r02_bench_resnet50.err
