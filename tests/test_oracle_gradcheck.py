@@ -1,0 +1,152 @@
+"""CPU: numerical gradient checks of the oracle's backward passes -- the reference's own way of pinning backprop
+(deeplearning4j-core/src/test/java/org/deeplearning4j/gradientcheck/CNNGradientCheckTest.java, BNGradientCheckTest.java,
+LRNGradientCheckTests.java, all through GradientCheckUtil: central differences against the analytic gradient, max relative
+error 1e-3). The reference holds no literal expected values for gradients, so this is what stands behind every `oracle.*_bwd`
+the GPU parity tests compare with: for a scalar loss L = sum(forward(x, params) * r) with a fixed random r, the analytic
+gradient is backward(r); it is compared with (L(p + h) - L(p - h)) / 2h on a random sample of coordinates of every input.
+The oracle computes in float32, so h is 1e-2 on O(1) values and L is accumulated in float64: the round-off of one forward is
+~1e-7 * sum|z r| / h, the truncation error h^2/6 * f''' -- both far below the 2e-3 allowed here."""
+import numpy as np
+import pytest
+
+H_STEP = 1e-2
+MAX_REL = 2e-3
+SAMPLES = 12
+
+
+def _loss(z, r):
+    return float(np.sum(z.astype(np.float64) * r.astype(np.float64)))
+
+
+def _check(name, forward, params, analytic, r, rng, h=H_STEP, tol=MAX_REL):
+    """forward(*params) -> z; analytic[i] = dL/dparams[i] (None: not checked)."""
+    for i, (p, g) in enumerate(zip(params, analytic)):
+        if g is None:
+            continue
+        assert g.shape == p.shape, (name, i, g.shape, p.shape)
+        scale = max(float(np.abs(g).max()), 1e-6)
+        flat = p.reshape(-1)
+        for j in rng.choice(flat.size, size=min(SAMPLES, flat.size), replace=False):
+            old = flat[j]
+            flat[j] = old + h
+            lp = _loss(forward(*params), r)
+            flat[j] = old - h
+            lm = _loss(forward(*params), r)
+            flat[j] = old
+            num = (lp - lm) / (2 * h)
+            assert abs(num - float(g.reshape(-1)[j])) <= tol * scale, (name, "input", i, "coord", int(j), num, float(g.reshape(-1)[j]), scale)
+
+
+@pytest.mark.parametrize("case", [((2, 3, 7, 8), 4, (3, 3), (1, 1), (1, 1), (1, 1), 1), ((2, 4, 9, 9), 5, (3, 3), (2, 2), (0, 0), (1, 1), 2),
+                                  ((1, 2, 9, 9), 3, (3, 3), (1, 1), (0, 0), (2, 2), 2), ((2, 3, 8, 8), 6, (1, 1), (2, 2), (0, 0), (1, 1), 1),
+                                  ((2, 2, 11, 10), 3, (5, 3), (2, 1), (2, 1), (1, 1), 1)])
+def test_convolution_backward(oracle, case):
+    shape, cout, k, s, p, d, mode = case
+    rng = np.random.default_rng(1)
+    x = rng.standard_normal(shape).astype(np.float32)
+    w = (rng.standard_normal((cout, shape[1]) + k) * 0.5).astype(np.float32)
+    b = rng.standard_normal(cout).astype(np.float32)
+    fwd = lambda x_, w_, b_: oracle.conv_fwd(x_, w_, b_, stride=s, pad=p, dilation=d, mode=mode)
+    r = rng.standard_normal(fwd(x, w, b).shape).astype(np.float32)
+    dw, db, dx = oracle.conv_bwd(x, w, r, stride=s, pad=p, dilation=d, mode=mode)
+    _check("conv", fwd, [x, w, b], [dx, dw, db], r, rng)
+    dw2, db2, dx2 = oracle.conv_bwd_im2col(x, w, r, stride=s, pad=p, dilation=d, mode=mode)   # the reference's im2col + gemm pipeline
+    np.testing.assert_allclose(dw2, dw, rtol=0, atol=1e-4 * np.abs(dw).max())
+    np.testing.assert_allclose(dx2, dx, rtol=0, atol=1e-4 * np.abs(dx).max())
+
+
+@pytest.mark.parametrize("ptype", ["MAX", "AVG", "PNORM"])
+@pytest.mark.parametrize("case", [((2, 3, 8, 8), (2, 2), (2, 2), (0, 0), 1), ((2, 2, 9, 11), (3, 3), (2, 2), (1, 1), 1), ((1, 3, 7, 7), (3, 2), (1, 2), (0, 0), 2)])
+def test_subsampling_backward(oracle, case, ptype):
+    shape, k, s, p, mode = case
+    rng = np.random.default_rng(2)
+    # distinct values with gaps larger than 2h: a max-pooling window must keep its winner under the perturbation
+    x = (rng.permutation(int(np.prod(shape))).reshape(shape) * 0.05 - 2.0).astype(np.float32)
+    if ptype == "PNORM":
+        x = np.abs(x) + 0.5  # |x|^p is not differentiable at 0
+    pt = {"MAX": oracle.POOL_MAX, "AVG": oracle.POOL_AVG, "PNORM": oracle.POOL_PNORM}[ptype]
+    fwd = lambda x_: oracle.pool_fwd(x_, k, s, p, (1, 1), mode, pt, 2)
+    r = rng.standard_normal(fwd(x).shape).astype(np.float32)
+    dx = oracle.pool_bwd(x, r, k, s, p, (1, 1), mode, pt, 2)
+    _check("pool-" + ptype, fwd, [x], [dx], r, rng)
+
+
+@pytest.mark.parametrize("shape", [(4, 3, 5, 6), (6, 8, 3, 3), (16, 5, 1, 1)])
+def test_batch_normalization_backward(oracle, shape):
+    rng = np.random.default_rng(3)
+    x = (rng.standard_normal(shape) * 1.5 + 0.3).astype(np.float32)
+    gamma = (1 + 0.2 * rng.standard_normal(shape[1])).astype(np.float32)
+    beta = (0.2 * rng.standard_normal(shape[1])).astype(np.float32)
+
+    def fwd(x_, g_, b_):
+        return oracle.bn_fwd(x_, g_, b_, np.zeros(shape[1], np.float32), np.ones(shape[1], np.float32), 0.9, 1e-5, True)[0]
+    _, mean, std = oracle.bn_fwd(x, gamma, beta, np.zeros(shape[1], np.float32), np.ones(shape[1], np.float32), 0.9, 1e-5, True)
+    r = rng.standard_normal(shape).astype(np.float32)
+    dx, dg, db = oracle.bn_bwd(x, r, gamma, mean, std)
+    # (the batch statistics move with x: the analytic dx includes d mean / d var, BatchNormalization.java:172-196)
+    _check("bn", fwd, [x, gamma, beta], [dx, dg, db], r, rng, tol=4e-3)
+
+
+def test_local_response_normalization_backward(oracle):
+    rng = np.random.default_rng(4)
+    x = (rng.standard_normal((2, 7, 4, 5)) * 2.0).astype(np.float32)
+    kw = dict(k=2.0, n=5.0, alpha=1e-2, beta=0.75)   # a large alpha so that the normaliser actually depends on x
+    fwd = lambda x_: oracle.lrn_fwd(x_, **kw)
+    r = rng.standard_normal(x.shape).astype(np.float32)
+    _check("lrn", fwd, [x], [oracle.lrn_bwd(x, r, **kw)], r, rng)
+
+
+@pytest.mark.parametrize("kind", ["relu", "sigmoid", "tanh"])
+def test_activation_backward(oracle, kind):
+    rng = np.random.default_rng(5)
+    z = rng.standard_normal((3, 17)).astype(np.float32)
+    z[np.abs(z) < 0.05] += 0.2   # keep ReLU away from its kink
+    code = {"relu": oracle.ACT_RELU, "sigmoid": oracle.ACT_SIGMOID, "tanh": oracle.ACT_TANH}[kind]
+    fwd = lambda z_: oracle.act_fwd(z_, code)
+    r = rng.standard_normal(z.shape).astype(np.float32)
+    _check("act-" + kind, fwd, [z], [oracle.act_bwd(z, r, code)], r, rng)
+
+
+def test_softmax_negative_log_likelihood_delta(oracle):
+    """delta = dL/dz of the summed loss (BaseOutputLayer: p - labels for softmax + MCXENT)."""
+    rng = np.random.default_rng(6)
+    z = rng.standard_normal((5, 7)).astype(np.float32)
+    lab = np.zeros((5, 7), np.float32)
+    lab[np.arange(5), rng.integers(0, 7, 5)] = 1.0
+    _, _, delta = oracle.softmax_nll(z, lab)
+    flat = z.reshape(-1)
+    for j in rng.choice(flat.size, size=SAMPLES, replace=False):
+        old = flat[j]
+        flat[j] = old + H_STEP
+        lp = oracle.softmax_nll(z, lab)[0]
+        flat[j] = old - H_STEP
+        lm = oracle.softmax_nll(z, lab)[0]
+        flat[j] = old
+        assert abs((lp - lm) / (2 * H_STEP) - float(delta.reshape(-1)[j])) <= MAX_REL, (int(j),)
+
+
+@pytest.mark.parametrize("case", [((2, 3, 5, 6), 4, (3, 3), (2, 2), (0, 0)), ((2, 4, 4, 4), 3, (2, 2), (2, 2), (0, 0)), ((1, 2, 6, 5), 3, (3, 3), (1, 1), (1, 1))])
+def test_deconvolution2d_backward(oracle, case):
+    shape, nout, k, s, p = case
+    rng = np.random.default_rng(7)
+    x = rng.standard_normal(shape).astype(np.float32)
+    w = (rng.standard_normal((shape[1], nout) + k) * 0.5).astype(np.float32)
+    b = rng.standard_normal(nout).astype(np.float32)
+    fwd = lambda x_, w_, b_: oracle.deconv2d_fwd(x_, w_, b_, stride=s, pad=p)
+    r = rng.standard_normal(fwd(x, w, b).shape).astype(np.float32)
+    dw, db, dx = oracle.deconv2d_bwd(x, w, r, stride=s, pad=p)
+    _check("deconv2d", fwd, [x, w, b], [dx, dw, db], r, rng)
+
+
+@pytest.mark.parametrize("case", [((2, 3, 7, 7), 2, 5, (3, 3), (1, 1), (1, 1), 1), ((2, 4, 8, 9), 1, 6, (3, 3), (2, 2), (0, 0), 2)])
+def test_separable_convolution2d_backward(oracle, case):
+    shape, mult, nout, k, s, p, mode = case
+    rng = np.random.default_rng(8)
+    x = rng.standard_normal(shape).astype(np.float32)
+    wd = (rng.standard_normal((mult, shape[1]) + k) * 0.5).astype(np.float32)
+    wp = (rng.standard_normal((nout, shape[1] * mult, 1, 1)) * 0.5).astype(np.float32)
+    b = rng.standard_normal(nout).astype(np.float32)
+    fwd = lambda x_, wd_, wp_, b_: oracle.sepconv2d_fwd(x_, wd_, wp_, b_, stride=s, pad=p, mode=mode)[0]
+    r = rng.standard_normal(fwd(x, wd, wp, b).shape).astype(np.float32)
+    dwd, dwp, db, dx = oracle.sepconv2d_bwd(x, wd, wp, r, stride=s, pad=p, mode=mode)
+    _check("sepconv2d", fwd, [x, wd, wp, b], [dx, dwd, dwp, db], r, rng)
