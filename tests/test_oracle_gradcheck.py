@@ -150,3 +150,60 @@ def test_separable_convolution2d_backward(oracle, case):
     r = rng.standard_normal(fwd(x, wd, wp, b).shape).astype(np.float32)
     dwd, dwp, db, dx = oracle.sepconv2d_bwd(x, wd, wp, r, stride=s, pad=p, mode=mode)
     _check("sepconv2d", fwd, [x, wd, wp, b], [dx, dwd, dwp, db], r, rng)
+
+
+def test_whole_network_gradient(oracle):
+    """The network-level oracle (oracle/net_oracle.py: ComputationGraph forward / calcBackpropGradients over a residual graph
+    with BatchNormalization, MAX pooling, strided 1x1 and SAME 3x3 convolutions, Add fan-in, softmax output) against central
+    differences of its own summed loss, parameter by parameter -- the whole-network form of the reference's gradient checks.
+    The flat gradient is d(sum of per-example losses)/d(params) before the updater divides by the minibatch size; the
+    running-statistics slots of BatchNormalization carry no gradient (BatchNormalization.java:205-208)."""
+    from deeplearning4j_b200 import zoo
+    from oracle.net_oracle import OracleNet
+    from test_gpu_network import _tiny_resnet
+    m = _tiny_resnet()
+    B = 6
+    P, layout = zoo.param_layout(m)
+    p0 = zoo.init_params(m)
+    rng = np.random.default_rng(9)
+    x = rng.random((B,) + tuple(m["input"]), dtype=np.float32)
+    lab = np.zeros((B, 10), np.float32)
+    lab[np.arange(B), rng.integers(0, 10, B)] = 1.0
+    net = OracleNet(m, layout, P, p0)
+    net.forward(x, lab, True)
+    net.backward()
+    g = net.grads.astype(np.float64).copy()
+
+    def loss_at(params):
+        n2 = OracleNet(m, layout, P, params)
+        n2.forward(x, lab, True)
+        return float(n2.loss)
+
+    # ReLU and max-pooling make the loss piecewise smooth: a step that carries some activation across a kink leaves an O(h)
+    # error, float32 round-off of the loss (~1e-6) an O(1/h) one. Each coordinate is therefore tried with a shrinking step
+    # (the reference's checks avoid the issue by using smooth activations and double precision, which this float32
+    # restatement does not offer) and must match for one of them; a coordinate that sits within 1e-4 of a kink cannot,
+    # so up to 3 % of the sample may miss.
+    checked, missed = 0, []
+    for name, key, off, shp, pk in layout:
+        cnt = int(np.prod(shp))
+        if pk == "bn_stat":
+            assert not g[off:off + cnt].any(), (name, key)
+            continue
+        scale = max(float(np.abs(g[off:off + cnt]).max()), 1e-3)
+        for j in rng.choice(cnt, size=min(3, cnt), replace=False):
+            best = np.inf
+            for h in (2e-3, 1e-3, 5e-4, 2.5e-4):
+                p = p0.copy()
+                p[off + j] += h
+                lp = loss_at(p)
+                p[off + j] -= 2 * h
+                lm = loss_at(p)
+                best = min(best, abs((lp - lm) / (2 * h) - g[off + j]))
+                if best <= 1e-2 * scale + 5e-3:
+                    break
+            checked += 1
+            if best > 1e-2 * scale + 5e-3:
+                missed.append((name, key, int(j), float(g[off + j]), float(best), scale))
+    assert checked > 40
+    assert len(missed) <= 0.03 * checked, missed
