@@ -170,7 +170,7 @@ class OracleNet:
                 give(u, self._q(dx))
             elif op == "bn":
                 mean, std, y = self.bn_saved[n]
-                d = o.act_bwd(y, e, _ACT[v["act"]]) if v["act"] == "relu" else e
+                d = o.act_bwd(y, e, _ACT[v["act"]]) if v["act"] != "identity" else e  # y: the pre-activation batch-norm output
                 dx, dg, dbt = o.bn_bwd(act[u], d, self._p(n, "gamma"), mean, std)
                 self._p(n, "gamma", self.grads)[...] = dg
                 self._p(n, "beta", self.grads)[...] = dbt

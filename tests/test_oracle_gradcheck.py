@@ -207,3 +207,50 @@ def test_whole_network_gradient(oracle):
                 missed.append((name, key, int(j), float(g[off + j]), float(best), scale))
     assert checked > 40
     assert len(missed) <= 0.03 * checked, missed
+
+
+def test_whole_network_gradient_smooth_variant(oracle):
+    """The same residual graph with tanh instead of ReLU and average instead of max pooling -- a smooth loss, which is how the
+    reference's gradient checks are set up -- held to 2e-3 of each block's largest gradient with a single step size."""
+    import copy
+    from deeplearning4j_b200 import zoo
+    from oracle.net_oracle import OracleNet
+    from test_gpu_network import _tiny_resnet
+    m = copy.deepcopy(_tiny_resnet())
+    for v in m["vertices"]:
+        if v.get("act") == "relu":
+            v["act"] = "tanh"
+        if v["op"] == "pool":
+            v["type"] = "AVG"
+    B = 6
+    P, layout = zoo.param_layout(m)
+    p0 = zoo.init_params(m)
+    rng = np.random.default_rng(9)
+    x = rng.random((B,) + tuple(m["input"]), dtype=np.float32)
+    lab = np.zeros((B, 10), np.float32)
+    lab[np.arange(B), rng.integers(0, 10, B)] = 1.0
+    net = OracleNet(m, layout, P, p0)
+    net.forward(x, lab, True)
+    net.backward()
+    g = net.grads.astype(np.float64).copy()
+
+    def loss_at(params):
+        n2 = OracleNet(m, layout, P, params)
+        n2.forward(x, lab, True)
+        return float(n2.loss)
+
+    h, checked = 2e-3, 0
+    for name, key, off, shp, pk in layout:
+        cnt = int(np.prod(shp))
+        if pk == "bn_stat":
+            continue
+        scale = max(float(np.abs(g[off:off + cnt]).max()), 1e-3)
+        for j in rng.choice(cnt, size=min(3, cnt), replace=False):
+            p = p0.copy()
+            p[off + j] += h
+            lp = loss_at(p)
+            p[off + j] -= 2 * h
+            lm = loss_at(p)
+            assert abs((lp - lm) / (2 * h) - g[off + j]) <= 2e-3 * scale + 2e-3, (name, key, int(j), (lp - lm) / (2 * h), g[off + j], scale)
+            checked += 1
+    assert checked > 40
