@@ -254,3 +254,80 @@ def test_whole_network_gradient_smooth_variant(oracle):
             assert abs((lp - lm) / (2 * h) - g[off + j]) <= 2e-3 * scale + 2e-3, (name, key, int(j), (lp - lm) / (2 * h), g[off + j], scale)
             checked += 1
     assert checked > 40
+
+
+def _gradcheck_net(m, B, K, masks_seed=None, h=2e-3, tol=2e-3, per_block=3, only=None):
+    from deeplearning4j_b200 import zoo
+    from oracle.net_oracle import OracleNet
+    P, layout = zoo.param_layout(m)
+    p0 = zoo.init_params(m)
+    rng = np.random.default_rng(21)
+    x = rng.random((B,) + tuple(m["input"]), dtype=np.float32)
+    lab = np.zeros((B, K), np.float32)
+    lab[np.arange(B), rng.integers(0, K, B)] = 1.0
+    masks = None
+    if masks_seed is not None:  # inverted dropout with fixed masks (inputs of the step, as in the GPU tests)
+        from oracle import oracle as o
+        shapes = zoo.infer_shapes(m, o.out_size)
+        mr = np.random.default_rng(masks_seed)
+        masks = {v["name"]: (mr.random((B,) + tuple(shapes[v["in"][0]])) < v["dropout"]).astype(np.float32)
+                 for v in m["vertices"] if v.get("dropout")}
+
+    def make(params):
+        n = OracleNet(m, layout, P, params)
+        n.masks = masks
+        n.forward(x, lab, True)
+        return n
+    net = make(p0)
+    net.backward()
+    g = net.grads.astype(np.float64).copy()
+    # Directional derivatives along random +-1 directions of each parameter block: the signal g.s grows with the block size
+    # while the float32 round-off of the loss (~1e-5 here) does not -- single coordinates of the early layers, whose
+    # gradients are ~1e-2 behind two saturating activations and dropout, would drown in it.
+    checked = 0
+    for name, key, off, shp, pk in layout:
+        cnt = int(np.prod(shp))
+        if pk == "bn_stat" or (only is not None and name not in only):
+            continue
+        gb = g[off:off + cnt]
+        scale = max(float(np.linalg.norm(gb)), 1e-3)
+        for _ in range(per_block):
+            sgn = rng.choice(np.array([-1.0, 1.0], np.float32), size=cnt)
+            p = p0.copy()
+            p[off:off + cnt] += np.float32(h) * sgn
+            lp = float(make(p).loss)
+            p = p0.copy()
+            p[off:off + cnt] -= np.float32(h) * sgn
+            lm = float(make(p).loss)
+            num, ana = (lp - lm) / (2 * h), float(gb @ sgn.astype(np.float64))
+            assert abs(num - ana) <= tol * scale + 1e-3, (name, key, num, ana, scale)
+            checked += 1
+    return checked
+
+
+def test_sequential_net_with_dense_layers_and_dropout_gradient(oracle):
+    """MultiLayerNetwork-style chain (conv -> pool -> conv -> pool -> flatten -> dense -> dense -> softmax) with smooth
+    activations, SAME / strided windows, a CnnToFeedForward flatten and the zoo AlexNet's inverted dropout on every layer
+    input (mask-fed)."""
+    from deeplearning4j_b200 import zoo
+    v = [{"name": "input", "op": "input", "in": []},
+         zoo._conv("c1", "input", 6, (5, 5), (2, 2), (2, 2), act="tanh"),
+         zoo._pool("p1", "c1", "AVG", (3, 3), (2, 2), (1, 1)),
+         zoo._conv("c2", "p1", 8, (3, 3), mode="Same", act="sigmoid"),
+         zoo._pool("p2", "c2", "PNORM", (2, 2), (2, 2)),
+         {"name": "flat", "op": "flatten", "in": ["p2"]},
+         {"name": "f1", "op": "dense", "in": ["flat"], "nOut": 12, "act": "tanh"},
+         {"name": "f2", "op": "dense", "in": ["f1"], "nOut": 9, "act": "sigmoid"},
+         {"name": "output", "op": "output", "in": ["f2"], "nOut": 5}]
+    for vv in v[1:]:
+        if vv["op"] in ("conv", "pool", "dense", "output"):
+            vv["dropout"] = 0.5
+    m = {"name": "seq", "input": (2, 17, 19), "vertices": v, "weight_init": ("normal", 0.4),
+         "updater": {"kind": "nesterovs", "lr": 1e-2, "momentum": 0.9}, "l1": 0.0, "l2": 0.0, "minibatch": True, "grad_norm": None,
+         "seed": 5}
+    assert _gradcheck_net(m, 5, 5, masks_seed=None, h=2e-3, tol=1e-2) >= 20
+    # With dropout the reference replaces a layer's input by x * mask / p (AbstractLayer.java:360-374) but has NO dropout
+    # backprop step: the epsilon a layer hands down is not multiplied by the mask, so below the topmost dropout the
+    # "gradient" is not the derivative of the loss -- by the reference's construction, which the oracle restates. Only the
+    # output layer's blocks (computed from its dropped input and its own delta) are true derivatives and checked here.
+    assert _gradcheck_net(m, 5, 5, masks_seed=77, h=2e-3, tol=1e-2, only=("output",)) >= 6
